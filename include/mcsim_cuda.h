@@ -1,0 +1,200 @@
+/* mcsim_cuda.h -- thin C ABI between the C++ plugin (libmcsim.so) and the sm_100a kernels
+ * (libmcsim_cuda.so).  Plain pointers and sizes; no exceptions, no torch types; every call
+ * returns an int status (0 = ok) and leaves a message for mcsim_cuda_last_error().
+ *
+ * Each entry point names the reference code it replaces (paths relative to the reference
+ * repository ajaayc/Probability-of-Collision-for-Safe-Planning):
+ *
+ *   mcsim_cuda_mc_run        mcsimplugin/MCSimulator.h:287-347 (initParticles, moveParticles,
+ *                            checkParticleCollisions, getCollisionProportion) inside the loop
+ *                            of EKF_GaussProp :649-864, collision test :257-285
+ *   mcsim_cuda_gmm_truncate  mcsimplugin/MCSimulator.h:570-642 (truncateGMM) +
+ *                            mcsimplugin/GM_Model.h:83-116 (sampleNPoints)
+ *   mcsim_cuda_gmm_run       the GMM branch of EKF_GaussProp :672-678, :766-772, :804-817, :843-856
+ *   mcsim_cuda_em_*          armadillo-8.400.0/include/armadillo_bits/gmm_full_meat.hpp:2390-2800
+ *                            (em_iterate / em_generate_acc / em_update_params / em_fix_params)
+ *   mcsim_cuda_score_plans   the MC loop above, batched over many plans (BASELINE.json config 4)
+ *
+ * All host arrays are caller-owned.  Unless stated otherwise, pointers are HOST pointers and the
+ * call copies in / out on the context's stream and synchronises before returning.
+ */
+#ifndef MCSIM_CUDA_H
+#define MCSIM_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MCSIM_PRISM_STRIDE 8      /* cx, cy, cos(phi), sin(phi), hx, hy, zlo, zhi */
+#define MCSIM_MAX_HULLS 8
+#define MCSIM_MAX_PAIRS 1024      /* live (hull, box) pairs held in __constant__ memory */
+#define MCSIM_MAX_LANDMARKS 16
+#define MCSIM_MAX_WAYPOINTS 1024
+#define MCSIM_MAX_GAUSSIANS 16
+
+typedef struct mcsim_cuda_ctx mcsim_cuda_ctx;
+
+/* status codes */
+enum {
+    MCSIM_OK = 0,
+    MCSIM_ERR_CUDA = 1,       /* a CUDA runtime call failed (message has the CUDA error string) */
+    MCSIM_ERR_ARG = 2,        /* bad argument / limits exceeded */
+    MCSIM_ERR_NODEVICE = 3,   /* no sm_100 device visible: there is NO CPU fallback */
+    MCSIM_ERR_DRAWS = 4,      /* injected draws buffer too short */
+    MCSIM_ERR_DEGENERATE = 5  /* GMM component with < 2 collision-free samples (reference: UB) */
+};
+
+/* ---- context ---------------------------------------------------------------------------- */
+/* device: CUDA ordinal.  Creates one non-blocking stream; fails with MCSIM_ERR_NODEVICE when no
+ * CUDA device is present (the product has no CPU path). */
+int mcsim_cuda_create(int device, mcsim_cuda_ctx** out);
+void mcsim_cuda_destroy(mcsim_cuda_ctx* ctx);
+const char* mcsim_cuda_last_error(void);
+/* cudaStream_t of the context as an opaque pointer (so a caller can record CUDA events on it). */
+void* mcsim_cuda_stream(mcsim_cuda_ctx* ctx);
+/* number of kernels this context has launched so far (bench.py's gpu_launches). */
+uint64_t mcsim_cuda_launch_count(mcsim_cuda_ctx* ctx);
+
+/* ---- scene ------------------------------------------------------------------------------ */
+/* Replaces OpenRAVE's collision world for this path (MCSimulator.h:269-285).  boxes: n_boxes x 8
+ * doubles in the world frame, hulls: n_hulls x 8 doubles in the robot frame (z absolute).  The
+ * live (hull, box) pairs -- z-intervals overlapping with positive length -- are flattened into
+ * an FP32 table in __constant__ memory, grouped by hull. */
+int mcsim_cuda_set_scene(mcsim_cuda_ctx* ctx, const double* boxes, int n_boxes,
+                         const double* hulls, int n_hulls);
+
+/* ---- Monte-Carlo rollouts --------------------------------------------------------------- */
+typedef struct {
+    /* plan */
+    int T;                       /* waypoints (setPathLength) */
+    const double* trajectory;    /* 3 x T component-major: x_0..x_{T-1} y_0.. th_0.. (setTrajectory) */
+    const double* odometry;      /* 3 x (T-1) component-major: rot1.., trans.., rot2.. (setOdometry) */
+    /* noise model */
+    double alphas[4];            /* squared alphas (setAlphas) */
+    double Q;                    /* range variance (setQ) */
+    int n_landmarks;
+    const double* landmarks;     /* x_0..x_{L-1} y_0..y_{L-1} (setLandmarks) */
+    double cov0[9];              /* Sigma_0 row-major (setInitialCovariance) */
+    /* rollouts */
+    uint64_t n_rollouts;         /* rollouts THIS call simulates */
+    uint64_t rollout_offset;     /* global id of the first one (multi-GPU shards / resume) */
+    /* mode */
+    int mode;                    /* MCSIM_MODE_REPLAY or MCSIM_MODE_PHILOX */
+    int estimator;               /* MCSIM_EST_REFERENCE (collision tested on the particle, which is
+                                    moved by the real robot's noisy command: MCSimulator.h:754-761)
+                                    or MCSIM_EST_CLOSEDLOOP (tested on the real state) */
+    int early_exit;              /* 1: a rollout stops at its first hit (flags only);
+                                    0: full per-rollout counts as the reference keeps them (:344) */
+    uint64_t seed;               /* Philox key */
+    /* MCSIM_MODE_REPLAY inputs */
+    const double* applied;       /* 3 x (T-1) component-major noisy commands u~_t of the shared
+                                    real-robot thread (host-computed, see mcsim_host_thread) */
+    const double* z0;            /* 3 x n_rollouts standard normals, rollout-major (the order
+                                    mvnrnd fills them: glue_mvnrnd_meat.hpp:89-147) or NULL in
+                                    PHILOX mode */
+    double near_eps;             /* |clearance| < near_eps marks a near-contact pose (audit only) */
+} mcsim_mc_params;
+
+enum { MCSIM_MODE_REPLAY = 0, MCSIM_MODE_PHILOX = 1 };
+enum { MCSIM_EST_REFERENCE = 0, MCSIM_EST_CLOSEDLOOP = 1 };
+
+typedef struct {
+    uint64_t hits;               /* rollouts with >= 1 colliding waypoint */
+    uint64_t near_contact;       /* poses with |clearance| < near_eps (audit launches only) */
+    uint64_t executed_steps;     /* rollout-steps actually executed (early exit skips the rest) */
+    uint64_t pair_tests;         /* SAT pair tests actually executed */
+    /* optional outputs, may be NULL */
+    uint64_t* first_hit_hist;    /* [T] rollouts whose first hit is at waypoint t */
+    uint32_t* counts;            /* [n_rollouts] colliding waypoints per rollout (early_exit = 0)
+                                    or 0/1 flags (early_exit = 1) */
+    float* poses;                /* [T x 3 x n_rollouts] pose tested at every waypoint (audit) */
+    float* clearance;            /* [T x n_rollouts] signed clearance (audit) */
+    float kernel_ms;             /* device time of the rollout kernel (CUDA events) */
+} mcsim_mc_result;
+
+/* Runs n_rollouts rollouts over the plan.  Audit outputs (poses / clearance / near_contact) are
+ * produced iff result->poses or result->clearance is non-NULL; that launch has no early exit. */
+int mcsim_cuda_mc_run(mcsim_cuda_ctx* ctx, const mcsim_mc_params* p, mcsim_mc_result* r);
+
+/* Device-resident variant used for throughput measurement: uploads the plan once ... */
+int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* ctx, const mcsim_mc_params* p);
+/* ... then launches the rollout kernel only (no host copies inside); counters accumulate on the
+ * device until mcsim_cuda_mc_collect.  Asynchronous on the context's stream. */
+int mcsim_cuda_mc_launch(mcsim_cuda_ctx* ctx, uint64_t n_rollouts, uint64_t rollout_offset);
+int mcsim_cuda_mc_collect(mcsim_cuda_ctx* ctx, mcsim_mc_result* r);
+
+/* ---- host thread of the reference estimator ---------------------------------------------- */
+/* The single closed-loop "real robot" of EKF_GaussProp (MCSimulator.h:685-800): controller gain
+ * (:532-553), applied control (:719-726), EKFpredict (:868-881), sampleOdometry (:391-410),
+ * 8 sampleObservation draws (:383-387, :786-789), EKFupdate (:883-929); FP64, on the HOST (it is
+ * O(T) scalar work, shared by all rollouts in replay mode).  normals: 11 x (T-1) standard
+ * normals in consumption order (3 odometry + L observations per step).
+ * Outputs (each may be NULL): applied_noisy 3 x (T-1) component-major = u~_t handed to
+ * moveParticles (:760); applied 3 x (T-1) = commanded u_t; real_path 3 x T; mu_path 3 x T,
+ * cov_path T x 9 row-major; obs (T-1) x L. */
+int mcsim_host_thread(const mcsim_mc_params* p, const double* normals, size_t n_normals,
+                      double* applied_noisy, double* applied, double* real_path,
+                      double* mu_path, double* cov_path, double* obs);
+
+/* ---- GMM truncation (moment matching) ---------------------------------------------------- */
+typedef struct {
+    int K;                       /* components (setNumGaussians) */
+    const double* weights;       /* [K] */
+    const double* means;         /* [K x 3] */
+    const double* covs;          /* [K x 9] row-major */
+    uint64_t n_samples;          /* numGMMSamples (setNumGMMSamples) */
+    int mode;                    /* MCSIM_MODE_REPLAY: counts + normals injected; MCSIM_MODE_PHILOX */
+    const int* counts;           /* [K] multinomial counts (replay; GM_Model.h:89-93) */
+    const double* normals;       /* 3 x n_samples standard normals in consumption order: component
+                                    0's samples first, sample-major (GM_Model.h:101-112) */
+    uint64_t seed;               /* Philox key */
+    uint64_t stream_id;          /* Philox subsequence (waypoint index / trajectory id) */
+} mcsim_gmm_truncate_params;
+
+typedef struct {
+    double weights[MCSIM_MAX_GAUSSIANS];
+    double means[MCSIM_MAX_GAUSSIANS * 3];
+    double covs[MCSIM_MAX_GAUSSIANS * 9];
+    uint64_t n_coll[MCSIM_MAX_GAUSSIANS];
+    uint64_t n_free[MCSIM_MAX_GAUSSIANS];
+    double p_collision;          /* sum n_coll / n_samples (MCSimulator.h:633-641) */
+    int degenerate;              /* components with < 2 free samples: previous moments kept, weight
+                                    from n_free (reference: undefined behaviour) */
+} mcsim_gmm_truncate_result;
+
+/* One truncateGMM (MCSimulator.h:570-642): sample, collision-test, refit every component by the
+ * mean / unbiased covariance of its collision-free samples, reweight by free-sample share. */
+int mcsim_cuda_gmm_truncate(mcsim_cuda_ctx* ctx, const mcsim_gmm_truncate_params* p,
+                            mcsim_gmm_truncate_result* r);
+
+typedef struct {
+    int K;
+    uint64_t n_samples;
+    /* replay mode only: the reference's draw stream for one runGMMEstimation, in consumption
+     * order: 3N (waypoint 0), then per step 3 (odometry) + L (observations) + 3N (truncation). */
+    const double* normals;
+    size_t n_normals;
+    const int* counts;           /* [T x K] multinomial counts per waypoint (replay) */
+} mcsim_gmm_run_params;
+
+typedef struct {
+    double P;                    /* 1 - prod_t (1 - p_t)  (MCSimulator.h:848-856) */
+    double* probabilities;       /* [T] optional */
+    double* gmm_pre;             /* [T x K x 13] optional: w, mu[3], cov[9] before each truncation */
+    double* gmm_post;            /* [K x 13] optional: mixture after the last truncation */
+    int degenerate;
+    float kernel_ms;             /* summed device time of the truncation kernels */
+} mcsim_gmm_run_result;
+
+/* Whole GMM branch of EKF_GaussProp for one plan; plan / noise parameters come from mc (its
+ * n_rollouts, z0 and applied fields are ignored). */
+int mcsim_cuda_gmm_run(mcsim_cuda_ctx* ctx, const mcsim_mc_params* mc, const mcsim_gmm_run_params* g,
+                       mcsim_gmm_run_result* r);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MCSIM_CUDA_H */
