@@ -1,0 +1,204 @@
+// mc_rollout_sm100.cuh -- Monte-Carlo rollout kernel: one thread per rollout, pose (and, in Philox
+// mode, the rollout's own real-robot/EKF thread) held in registers across all waypoints.
+//
+// Replaces the particle loop of the reference (mcsimplugin/MCSimulator.h):
+//   initParticles :287-297 (x0 = mu0 + chol(Sigma0) z), moveParticles :300-322,
+//   checkParticleCollisions :333-347, getCollisionProportion :324-330,
+//   and in Philox mode the per-step body of EKF_GaussProp :692-830 per rollout.
+#ifndef MCSIM_MC_ROLLOUT_CUH
+#define MCSIM_MC_ROLLOUT_CUH
+
+#include "estimator_math.h"
+#include "philox.h"
+#include "sat_device.cuh"
+
+// per-step plan record staged in shared memory (floats)
+//   replay : u~ = (rot1, trans, rot2)                               3 floats
+//   philox : x*_t (3), u*_t (3), M_t (3) = generateM_EKF(u*_t)      9 floats
+#define MC_REPLAY_STRIDE 3
+#define MC_PHILOX_STRIDE 9
+
+struct McPlanConst {
+    int T;
+    int pad;
+    double mu0d[3]; // FP64 copies for the replay-mode start pose (injected draws are FP64)
+    double chold[6];
+    float mu0[3];
+    float chol[6];  // lower Cholesky factor of Sigma0: l00 l10 l11 l20 l21 l22
+    float sqrtQ;
+    mcsim_math::NoiseModel<float> nm;
+};
+__constant__ McPlanConst c_mc;
+
+// counters block in global memory
+enum { CNT_HITS = 0, CNT_NEAR = 1, CNT_STEPS = 2, CNT_TESTS = 3, CNT_HIST = 4 };
+
+struct McLaunch {
+    const float* plan;            // [T-1 or T][stride]
+    const double* z0;             // replay: 3 x n standard normals (rollout-major) for THIS launch
+    unsigned long long n;         // rollouts in this launch
+    unsigned long long offset;    // global id of rollout 0
+    unsigned k0, k1;              // Philox key
+    unsigned long long* counters; // [4 + T]
+    unsigned* counts;             // optional [n]
+    float* poses;                 // optional audit [T][3][n]
+    float* clearance;             // optional audit [T][n]
+    float near_eps;
+};
+
+template <int MODE, bool AUDIT, bool EARLY_EXIT, int EST, int NL>
+__global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
+    using namespace mcsim_math;
+    extern __shared__ float s_plan[];
+    __shared__ unsigned s_cnt[4];
+    __shared__ unsigned s_hist[MCSIM_MAX_WAYPOINTS];
+
+    const int T = c_mc.T;
+    constexpr int STRIDE = (MODE == MCSIM_MODE_REPLAY) ? MC_REPLAY_STRIDE : MC_PHILOX_STRIDE;
+    const int n_plan = (MODE == MCSIM_MODE_REPLAY) ? (T - 1) * STRIDE : T * STRIDE;
+    for (int i = threadIdx.x; i < n_plan; i += blockDim.x) s_plan[i] = a.plan[i];
+    for (int i = threadIdx.x; i < T; i += blockDim.x) s_hist[i] = 0;
+    if (threadIdx.x < 4) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+
+    unsigned my_hits = 0, my_near = 0, my_steps = 0, my_tests = 0;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
+        const unsigned long long id = a.offset + i;
+        // ---- initial particle: x0 = mu0 + L z (initParticles, glue_mvnrnd_meat.hpp:89-147)
+        float z[3] = {0.f, 0.f, 0.f};
+        if (MODE == MCSIM_MODE_PHILOX) {
+            mcsim_rng::u32x4 c = {unsigned(id), unsigned(id >> 32), 0u, unsigned(mcsim_rng::PURPOSE_INIT)};
+            c = mcsim_rng::philox4x32_10(c, a.k0, a.k1);
+            float z3;
+            mcsim_rng::box_muller(c.x, c.y, z[0], z[1]);
+            mcsim_rng::box_muller(c.z, c.w, z[2], z3);
+        }
+        float p[3];
+        if (MODE == MCSIM_MODE_REPLAY) {
+            // FP64 for the start pose only (3 FMAs): the injected draws are FP64
+            const double z0 = a.z0[3 * i], z1 = a.z0[3 * i + 1], z2 = a.z0[3 * i + 2];
+            p[0] = float(c_mc.mu0d[0] + c_mc.chold[0] * z0);
+            p[1] = float(c_mc.mu0d[1] + c_mc.chold[1] * z0 + c_mc.chold[2] * z1);
+            p[2] = float(c_mc.mu0d[2] + c_mc.chold[3] * z0 + c_mc.chold[4] * z1 + c_mc.chold[5] * z2);
+        } else {
+            p[0] = c_mc.mu0[0] + c_mc.chol[0] * z[0];
+            p[1] = c_mc.mu0[1] + c_mc.chol[1] * z[0] + c_mc.chol[2] * z[1];
+            p[2] = c_mc.mu0[2] + c_mc.chol[3] * z[0] + c_mc.chol[4] * z[1] + c_mc.chol[5] * z[2];
+        }
+        // Philox mode: this rollout's own real robot + EKF
+        float real[3], mu[3], S[9];
+        if (MODE == MCSIM_MODE_PHILOX) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { mu[k] = c_mc.mu0[k]; real[k] = (EST == MCSIM_EST_CLOSEDLOOP) ? p[k] : c_mc.mu0[k]; }
+            S[0] = c_mc.chol[0] * c_mc.chol[0];
+            S[1] = S[3] = c_mc.chol[0] * c_mc.chol[1];
+            S[2] = S[6] = c_mc.chol[0] * c_mc.chol[3];
+            S[4] = c_mc.chol[1] * c_mc.chol[1] + c_mc.chol[2] * c_mc.chol[2];
+            S[5] = S[7] = c_mc.chol[1] * c_mc.chol[3] + c_mc.chol[2] * c_mc.chol[4];
+            S[8] = c_mc.chol[3] * c_mc.chol[3] + c_mc.chol[4] * c_mc.chol[4] + c_mc.chol[5] * c_mc.chol[5];
+        }
+
+        unsigned count = 0;
+        int first = -1;
+        for (int t = 0; t < T; ++t) {
+            // ---- collision test at waypoint t (checkParticleCollisions)
+            const float* q = (MODE == MCSIM_MODE_PHILOX && EST == MCSIM_EST_CLOSEDLOOP) ? real : p;
+            float sn, cs;
+            sincos_t(q[2], sn, cs);
+            bool hit;
+            if (AUDIT) {
+                const float cl = robot_clearance(q[0], q[1], cs, sn);
+                hit = cl <= 0.0f;
+                my_near += (fabsf(cl) < a.near_eps);
+                my_tests += c_scene.n_pairs;
+                if (a.clearance) a.clearance[(size_t)t * a.n + i] = cl;
+                if (a.poses) {
+                    a.poses[((size_t)t * 3 + 0) * a.n + i] = q[0];
+                    a.poses[((size_t)t * 3 + 1) * a.n + i] = q[1];
+                    a.poses[((size_t)t * 3 + 2) * a.n + i] = q[2];
+                }
+            } else {
+                hit = robot_hits(q[0], q[1], cs, sn, my_tests);
+            }
+            ++my_steps;
+            if (hit) {
+                if (first < 0) first = t;
+                ++count;
+                if (EARLY_EXIT) break;
+            }
+            if (t == T - 1) break;
+            // ---- move to waypoint t+1
+            if (MODE == MCSIM_MODE_REPLAY) {
+                const float u[3] = {s_plan[t * STRIDE], s_plan[t * STRIDE + 1], s_plan[t * STRIDE + 2]};
+                float nx[3];
+                predict_pose(p, u, nx);
+                p[0] = nx[0]; p[1] = nx[1]; p[2] = nx[2];
+            } else {
+                const float* r = s_plan + t * STRIDE;
+                const float xs[3] = {r[0], r[1], r[2]};
+                const float us[3] = {r[3], r[4], r[5]};
+                const float M[3] = {r[6], r[7], r[8]};
+                const float xg[3] = {r[STRIDE], r[STRIDE + 1], r[STRIDE + 2]};
+                const int L = NL > 0 ? NL : c_mc.nm.L;
+                // noise draws of this step: 3 odometry + L observation normals
+                float zn[NL > 0 ? 4 * ((3 + NL + 3) / 4) : 4 * ((3 + MCSIM_MAX_LANDMARKS + 3) / 4)];
+                const int nblk = (3 + L + 3) >> 2;
+#pragma unroll
+                for (int j = 0; j < nblk; ++j) {
+                    mcsim_rng::u32x4 c = {unsigned(id), unsigned(id >> 32), unsigned(t * 8 + j), unsigned(mcsim_rng::PURPOSE_STEP)};
+                    c = mcsim_rng::philox4x32_10(c, a.k0, a.k1);
+                    mcsim_rng::box_muller(c.x, c.y, zn[4 * j], zn[4 * j + 1]);
+                    mcsim_rng::box_muller(c.z, c.w, zn[4 * j + 2], zn[4 * j + 3]);
+                }
+                float u[3], pmu[3], pS[9], un[3], nx[3];
+                applied_control(xs, mu, xg, us, u);
+                ekf_predict(mu, S, u, M, pmu, pS);
+                sample_odometry(c_mc.nm, u, zn, un);
+                predict_pose(real, un, nx);
+                real[0] = nx[0]; real[1] = nx[1]; real[2] = nx[2];
+                if (EST == MCSIM_EST_REFERENCE) {
+                    predict_pose(p, un, nx);
+                    p[0] = nx[0]; p[1] = nx[1]; p[2] = nx[2];
+                }
+                float zobs[MCSIM_MAX_LANDMARKS];
+#pragma unroll
+                for (int l = 0; l < L; ++l) zobs[l] = range_to(c_mc.nm, real, l) + zn[3 + l] * c_mc.sqrtQ;
+                ekf_update(c_mc.nm, pmu, pS, zobs, L);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) mu[k] = pmu[k];
+#pragma unroll
+                for (int k = 0; k < 9; ++k) S[k] = pS[k];
+            }
+        }
+        if (count) {
+            ++my_hits;
+            atomicAdd(&s_hist[first], 1u);
+        }
+        if (a.counts) a.counts[i] = count;
+    }
+
+    // ---- aggregation: warp reduce -> shared -> one 64-bit atomic per counter per block
+    my_hits = __reduce_add_sync(0xffffffffu, my_hits);
+    my_near = __reduce_add_sync(0xffffffffu, my_near);
+    // steps / tests can exceed 2^32 per warp only for > 10^7 rollouts per thread: not reachable
+    const unsigned long long w_steps = __reduce_add_sync(0xffffffffu, my_steps);
+    unsigned long long w_tests = my_tests;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) w_tests += __shfl_xor_sync(0xffffffffu, w_tests, o);
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&s_cnt[CNT_HITS], my_hits);
+        atomicAdd(&s_cnt[CNT_NEAR], my_near);
+        atomicAdd(&a.counters[CNT_STEPS], w_steps);
+        atomicAdd(&a.counters[CNT_TESTS], w_tests);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (s_cnt[CNT_HITS]) atomicAdd(&a.counters[CNT_HITS], (unsigned long long)s_cnt[CNT_HITS]);
+        if (s_cnt[CNT_NEAR]) atomicAdd(&a.counters[CNT_NEAR], (unsigned long long)s_cnt[CNT_NEAR]);
+    }
+    for (int t = threadIdx.x; t < T; t += blockDim.x)
+        if (s_hist[t]) atomicAdd(&a.counters[CNT_HIST + t], (unsigned long long)s_hist[t]);
+}
+
+#endif
