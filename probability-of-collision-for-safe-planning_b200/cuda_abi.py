@@ -1,0 +1,239 @@
+"""ctypes view of include/mcsim_cuda.h (libmcsim_cuda.so) -- the thin C ABI over the sm_100a kernels.
+
+This is the binding a Python maintainer of the reference would add; the structs
+mirror the header field by field.  Loading fails loudly when the library has not been built, and
+`Context()` fails loudly when there is no CUDA device: there is no CPU fallback.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libmcsim_cuda.so")
+
+MAX_GAUSSIANS = 16
+MAX_WAYPOINTS = 1024
+MODE_REPLAY, MODE_PHILOX = 0, 1
+EST_REFERENCE, EST_CLOSEDLOOP = 0, 1
+
+_dp = C.POINTER(C.c_double)
+_fp = C.POINTER(C.c_float)
+
+
+class McParams(C.Structure):
+    _fields_ = [
+        ("T", C.c_int), ("trajectory", _dp), ("odometry", _dp),
+        ("alphas", C.c_double * 4), ("Q", C.c_double),
+        ("n_landmarks", C.c_int), ("landmarks", _dp), ("cov0", C.c_double * 9),
+        ("n_rollouts", C.c_uint64), ("rollout_offset", C.c_uint64),
+        ("mode", C.c_int), ("estimator", C.c_int), ("early_exit", C.c_int), ("seed", C.c_uint64),
+        ("applied", _dp), ("z0", _dp), ("near_eps", C.c_double),
+    ]
+
+
+class McResult(C.Structure):
+    _fields_ = [
+        ("hits", C.c_uint64), ("near_contact", C.c_uint64), ("executed_steps", C.c_uint64),
+        ("pair_tests", C.c_uint64),
+        ("first_hit_hist", C.POINTER(C.c_uint64)), ("counts", C.POINTER(C.c_uint32)),
+        ("poses", _fp), ("clearance", _fp), ("kernel_ms", C.c_float),
+    ]
+
+
+class GmmTruncateParams(C.Structure):
+    _fields_ = [
+        ("K", C.c_int), ("weights", _dp), ("means", _dp), ("covs", _dp),
+        ("n_samples", C.c_uint64), ("mode", C.c_int), ("counts", C.POINTER(C.c_int)),
+        ("normals", _dp), ("seed", C.c_uint64), ("stream_id", C.c_uint64),
+    ]
+
+
+class GmmTruncateResult(C.Structure):
+    _fields_ = [
+        ("weights", C.c_double * MAX_GAUSSIANS), ("means", C.c_double * (MAX_GAUSSIANS * 3)),
+        ("covs", C.c_double * (MAX_GAUSSIANS * 9)),
+        ("n_coll", C.c_uint64 * MAX_GAUSSIANS), ("n_free", C.c_uint64 * MAX_GAUSSIANS),
+        ("p_collision", C.c_double), ("degenerate", C.c_int),
+    ]
+
+
+class GmmRunParams(C.Structure):
+    _fields_ = [
+        ("K", C.c_int), ("n_samples", C.c_uint64), ("normals", _dp), ("n_normals", C.c_size_t),
+        ("counts", C.POINTER(C.c_int)),
+    ]
+
+
+class GmmRunResult(C.Structure):
+    _fields_ = [
+        ("P", C.c_double), ("probabilities", _dp), ("gmm_pre", _dp), ("gmm_post", _dp),
+        ("degenerate", C.c_int), ("kernel_ms", C.c_float),
+    ]
+
+
+_lib = None
+
+
+def lib():
+    """The loaded libmcsim_cuda.so; raises if it is missing (no silent fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.isfile(LIB_PATH):
+            raise RuntimeError(
+                "%s is missing: build it with __graft_entry__.build() or `make -C %s`; "
+                "this package has no CPU fallback" % (LIB_PATH, os.path.dirname(LIB_PATH)))
+        L = C.CDLL(LIB_PATH)
+        vp = C.c_void_p
+        L.mcsim_cuda_create.argtypes = [C.c_int, C.POINTER(vp)]
+        L.mcsim_cuda_destroy.argtypes = [vp]
+        L.mcsim_cuda_destroy.restype = None
+        L.mcsim_cuda_last_error.restype = C.c_char_p
+        L.mcsim_cuda_stream.argtypes = [vp]
+        L.mcsim_cuda_stream.restype = vp
+        L.mcsim_cuda_launch_count.argtypes = [vp]
+        L.mcsim_cuda_launch_count.restype = C.c_uint64
+        L.mcsim_cuda_set_scene.argtypes = [vp, _dp, C.c_int, _dp, C.c_int]
+        L.mcsim_cuda_mc_run.argtypes = [vp, C.POINTER(McParams), C.POINTER(McResult)]
+        L.mcsim_cuda_mc_prepare.argtypes = [vp, C.POINTER(McParams)]
+        L.mcsim_cuda_mc_launch.argtypes = [vp, C.c_uint64, C.c_uint64]
+        L.mcsim_cuda_mc_collect.argtypes = [vp, C.POINTER(McResult)]
+        L.mcsim_host_thread.argtypes = [C.POINTER(McParams), _dp, C.c_size_t, _dp, _dp, _dp, _dp, _dp, _dp]
+        for name, at in (("mcsim_cuda_gmm_truncate", [vp, C.POINTER(GmmTruncateParams), C.POINTER(GmmTruncateResult)]),
+                         ("mcsim_cuda_gmm_run", [vp, C.POINTER(McParams), C.POINTER(GmmRunParams), C.POINTER(GmmRunResult)])):
+            if hasattr(L, name):
+                getattr(L, name).argtypes = at
+        _lib = L
+    return _lib
+
+
+class McsimCudaError(RuntimeError):
+    pass
+
+
+def check(rc):
+    if rc != 0:
+        raise McsimCudaError("mcsim_cuda error %d: %s" % (rc, lib().mcsim_cuda_last_error().decode()))
+
+
+def dptr(a):
+    """double* of a C-contiguous float64 array (or NULL)."""
+    if a is None:
+        return _dp()
+    assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data_as(_dp)
+
+
+def make_mc_params(plan, n_rollouts=0, mode=MODE_PHILOX, estimator=EST_REFERENCE, early_exit=True,
+                   seed=0x5AFEC0DE, rollout_offset=0, applied=None, z0=None, near_eps=1e-4):
+    """plan: dict(trajectory[3,T], odometry[3,T-1], alphas[4], Q, landmarks[2,L], cov0[3,3]).
+    Returns (McParams, keepalive list of the arrays its pointers refer to)."""
+    tr = np.ascontiguousarray(plan["trajectory"], dtype=np.float64)
+    od = np.ascontiguousarray(plan["odometry"], dtype=np.float64)
+    lm = np.ascontiguousarray(plan["landmarks"], dtype=np.float64)
+    keep = [tr, od, lm]
+    p = McParams()
+    p.T = tr.shape[1]
+    p.trajectory, p.odometry, p.landmarks = dptr(tr), dptr(od), dptr(lm)
+    p.alphas = (C.c_double * 4)(*[float(v) for v in plan["alphas"]])
+    p.Q = float(plan["Q"])
+    p.n_landmarks = lm.shape[1]
+    p.cov0 = (C.c_double * 9)(*[float(v) for v in np.asarray(plan["cov0"], dtype=np.float64).reshape(9)])
+    p.n_rollouts, p.rollout_offset = int(n_rollouts), int(rollout_offset)
+    p.mode, p.estimator, p.early_exit, p.seed = mode, estimator, int(bool(early_exit)), int(seed)
+    if applied is not None:
+        ap = np.ascontiguousarray(applied, dtype=np.float64)
+        keep.append(ap)
+        p.applied = dptr(ap)
+    if z0 is not None:
+        zz = np.ascontiguousarray(z0, dtype=np.float64)
+        keep.append(zz)
+        p.z0 = dptr(zz)
+    p.near_eps = float(near_eps)
+    return p, keep
+
+
+def host_thread(plan, normals):
+    """The reference's shared real-robot thread (FP64, host): returns dict of arrays."""
+    p, keep = make_mc_params(plan)
+    T, L = p.T, p.n_landmarks
+    nz = np.ascontiguousarray(normals, dtype=np.float64)
+    out = dict(applied_noisy=np.zeros((3, T - 1)), applied=np.zeros((3, T - 1)), real_path=np.zeros((3, T)),
+               mu_path=np.zeros((3, T)), cov_path=np.zeros((T, 9)), obs=np.zeros((T - 1, L)))
+    rc = lib().mcsim_host_thread(C.byref(p), dptr(nz), nz.size, dptr(out["applied_noisy"]), dptr(out["applied"]),
+                                 dptr(out["real_path"]), dptr(out["mu_path"]), dptr(out["cov_path"]), dptr(out["obs"]))
+    if rc != 0:
+        raise McsimCudaError("mcsim_host_thread error %d" % rc)
+    return out
+
+
+class Context:
+    """One CUDA context handle (device + stream) of libmcsim_cuda.so."""
+
+    def __init__(self, device=0):
+        self._h = C.c_void_p()
+        check(lib().mcsim_cuda_create(int(device), C.byref(self._h)))
+        self.device = device
+
+    def close(self):
+        if self._h:
+            lib().mcsim_cuda_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def stream(self):
+        return lib().mcsim_cuda_stream(self._h)
+
+    @property
+    def launch_count(self):
+        return int(lib().mcsim_cuda_launch_count(self._h))
+
+    def set_scene(self, boxes, hulls):
+        b = np.ascontiguousarray(boxes, dtype=np.float64).reshape(-1, 8)
+        h = np.ascontiguousarray(hulls, dtype=np.float64).reshape(-1, 8)
+        check(lib().mcsim_cuda_set_scene(self._h, dptr(b), b.shape[0], dptr(h), h.shape[0]))
+
+    def mc_run(self, params, want_counts=False, want_hist=False, audit=False):
+        """Runs params.n_rollouts rollouts; returns a dict."""
+        n, T = int(params.n_rollouts), int(params.T)
+        r = McResult()
+        out = {}
+        if want_hist:
+            out["first_hit_hist"] = np.zeros(T, dtype=np.uint64)
+            r.first_hit_hist = out["first_hit_hist"].ctypes.data_as(C.POINTER(C.c_uint64))
+        if want_counts:
+            out["counts"] = np.zeros(n, dtype=np.uint32)
+            r.counts = out["counts"].ctypes.data_as(C.POINTER(C.c_uint32))
+        if audit:
+            out["poses"] = np.zeros((T, 3, n), dtype=np.float32)
+            out["clearance"] = np.zeros((T, n), dtype=np.float32)
+            r.poses = out["poses"].ctypes.data_as(_fp)
+            r.clearance = out["clearance"].ctypes.data_as(_fp)
+        check(lib().mcsim_cuda_mc_run(self._h, C.byref(params), C.byref(r)))
+        out.update(hits=int(r.hits), near_contact=int(r.near_contact), executed_steps=int(r.executed_steps),
+                   pair_tests=int(r.pair_tests), kernel_ms=float(r.kernel_ms),
+                   P=(r.hits / n if n else 0.0))
+        return out
+
+    def mc_prepare(self, params):
+        check(lib().mcsim_cuda_mc_prepare(self._h, C.byref(params)))
+
+    def mc_launch(self, n, offset=0):
+        check(lib().mcsim_cuda_mc_launch(self._h, int(n), int(offset)))
+
+    def mc_collect(self, T=0, want_hist=False):
+        r = McResult()
+        out = {}
+        if want_hist:
+            out["first_hit_hist"] = np.zeros(T, dtype=np.uint64)
+            r.first_hit_hist = out["first_hit_hist"].ctypes.data_as(C.POINTER(C.c_uint64))
+        check(lib().mcsim_cuda_mc_collect(self._h, C.byref(r)))
+        out.update(hits=int(r.hits), near_contact=int(r.near_contact), executed_steps=int(r.executed_steps),
+                   pair_tests=int(r.pair_tests))
+        return out

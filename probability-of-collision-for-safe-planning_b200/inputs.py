@@ -1,0 +1,63 @@
+"""Input side of the hot path: the two plan pickles and the parameter defaults of the reference driver.
+
+* `trajectory.dat` / `odometry.dat` are Python-2 protocol-0 pickles (hw2_astar.py:198-204): a list of
+  T `[x, y, theta]` lists and a list of T-1 `ndarray(3,)` `[rot1, trans, rot2]`.
+* The reference driver sends numbers as Python-2 `str(float)` joined by spaces
+  (MCSimulation.py:81-85, :195-198), i.e. rounded to 12 significant digits: `py2_str`.
+* Parameter defaults: gaussprop.py:36 (alphas), :39 (Q), :45-46 (landmarks), :56 (Sigma0);
+  MCSimulation.py:164 (numParticles), :204-205 (numGaussians, numGMMSamples).
+"""
+import json
+import pickle
+
+import numpy as np
+
+
+def py2_str(x):
+    """Python-2 str(float): repr with 12 significant digits ('%.12g'), '.0' appended to integers."""
+    s = "%.12g" % float(x)
+    if "." not in s and "e" not in s and "n" not in s and "i" not in s:
+        s += ".0"
+    return s
+
+
+def default_params():
+    return dict(
+        alphas=np.square(np.array([0.00025, 0.0025, 0.0025, 0.0025])),
+        Q=float(np.square(0.2)),
+        landmarks=np.array([[3, -3, 0, 0, -3, 3, -3, 3], [0, 0, 2, -2, 2, 2, -2, -2]], dtype=np.float64),
+        cov0=0.001 * np.identity(3),
+        num_particles=10000,
+        num_gaussians=3,
+        num_gmm_samples=10000,
+    )
+
+
+def plan_from_pickles(trajectory_path, odometry_path, as_sent=True):
+    """Returns dict(trajectory[3,T], odometry[3,T-1]) + default parameters.  as_sent=True applies the
+    12-digit rounding of the driver's string marshalling, so the arrays are what the plugin saw."""
+    with open(trajectory_path, "rb") as f:
+        tr = np.array(pickle.load(f, encoding="latin1"), dtype=np.float64).T
+    with open(odometry_path, "rb") as f:
+        od = np.array(pickle.load(f, encoding="latin1"), dtype=np.float64).T
+    if as_sent:
+        tr = np.array([[float(py2_str(v)) for v in row] for row in tr])
+        od = np.array([[float(py2_str(v)) for v in row] for row in od])
+    plan = default_params()
+    plan.update(trajectory=np.ascontiguousarray(tr), odometry=np.ascontiguousarray(od))
+    return plan
+
+
+def load_plan_json(path):
+    with open(path) as f:
+        d = json.load(f)
+    plan = {}
+    for k, v in d.items():
+        plan[k] = np.array(v, dtype=np.float64) if isinstance(v, list) else v
+    return plan
+
+
+def save_plan_json(plan, path):
+    d = {k: (np.asarray(v).tolist() if isinstance(v, np.ndarray) else v) for k, v in plan.items()}
+    with open(path, "w") as f:
+        json.dump(d, f, indent=0)
