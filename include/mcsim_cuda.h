@@ -58,6 +58,12 @@ void* mcsim_cuda_stream(mcsim_cuda_ctx* ctx);
 /* number of kernels this context has launched so far (bench.py's gpu_launches). */
 uint64_t mcsim_cuda_launch_count(mcsim_cuda_ctx* ctx);
 
+/* Measures the FP32 FMA-pipe peak (TFLOP/s, FFMA = 2 flops) and the SFU peak (10^12 MUFU op/s) of
+ * the device with register-resident dependent chains, timed with CUDA events on the context's
+ * stream for about `ms` milliseconds each.  These are the roofline denominators of the MC path
+ * (MEASURED_PEAKS.json has HBM and tensor peaks only). */
+int mcsim_cuda_measure_peaks(mcsim_cuda_ctx* ctx, double ms, double* fp32_tflops, double* mufu_tops);
+
 /* ---- scene ------------------------------------------------------------------------------ */
 /* Replaces OpenRAVE's collision world for this path (MCSimulator.h:269-285).  boxes: n_boxes x 8
  * doubles in the world frame, hulls: n_hulls x 8 doubles in the robot frame (z absolute).  The

@@ -93,6 +93,7 @@ def lib():
         L.mcsim_cuda_stream.restype = vp
         L.mcsim_cuda_launch_count.argtypes = [vp]
         L.mcsim_cuda_launch_count.restype = C.c_uint64
+        L.mcsim_cuda_measure_peaks.argtypes = [vp, C.c_double, _dp, _dp]
         L.mcsim_cuda_set_scene.argtypes = [vp, _dp, C.c_int, _dp, C.c_int]
         L.mcsim_cuda_mc_run.argtypes = [vp, C.POINTER(McParams), C.POINTER(McResult)]
         L.mcsim_cuda_mc_prepare.argtypes = [vp, C.POINTER(McParams)]
@@ -193,6 +194,12 @@ class Context:
     @property
     def launch_count(self):
         return int(lib().mcsim_cuda_launch_count(self._h))
+
+    def measure_peaks(self, ms=200.0):
+        """(FP32 TFLOP/s, SFU 1e12 op/s) measured with register-resident chains."""
+        a, b = C.c_double(), C.c_double()
+        check(lib().mcsim_cuda_measure_peaks(self._h, float(ms), C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def set_scene(self, boxes, hulls):
         b = np.ascontiguousarray(boxes, dtype=np.float64).reshape(-1, 8)

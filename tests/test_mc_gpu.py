@@ -1,0 +1,139 @@
+"""GPU parity tests of the MC rollout kernel, through the C ABI (include/mcsim_cuda.h).
+
+Deterministic (replay) mode: injected draws; per-rollout collision counts / flags must be bit-exact
+with the reference estimator (oracle/_ref, golden vectors in tests/golden/mc_replay_*.npz) except
+for rollouts that have a pose within NEAR_EPS of contact, which are counted and reported
+separately (BASELINE.json north_star); poses within 1e-5 relative.
+Philox mode: P inside the 99 % confidence interval of the reference's run-to-run mean."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLD, golden
+
+pytestmark = pytest.mark.gpu
+
+NEAR_EPS = 1e-4     # metres: |clearance| below this marks a near-contact pose
+POSE_RTOL = 1e-5    # north_star: propagated poses within 1e-5 relative
+
+
+def _replay(ctx, plan, scene, draws, N, **kw):
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    ctx.set_scene(scene["boxes"], scene["hulls"])
+    ht = abi.host_thread(plan, draws[3 * N:])
+    p, keep = abi.make_mc_params(plan, n_rollouts=N, mode=abi.MODE_REPLAY, applied=ht["applied_noisy"],
+                                 z0=draws[:3 * N], near_eps=NEAR_EPS, early_exit=kw.pop("early_exit", False))
+    return ctx.mc_run(p, **kw)
+
+
+@pytest.mark.parametrize("name", ["pr2test2", "pr2custom"])
+def test_replay_counts_bit_exact_vs_reference_golden(ctx, plan, scenes, name):
+    g = golden("mc_replay_%s.npz" % name)
+    N = g["counts"].shape[0]
+    out = _replay(ctx, plan, scenes[name], g["draws"], N, want_counts=True, want_hist=True)
+    near = (np.abs(g["clearance"].astype(np.float64)) < NEAR_EPS).any(axis=0)  # rollouts with a near-contact pose
+    clean = ~near
+    assert clean.sum() >= 0.95 * N
+    np.testing.assert_array_equal(out["counts"][clean], g["counts"][clean])
+    # hit count: exact on the clean set; the near-contact rollouts are reported, not asserted
+    assert int((out["counts"][clean] > 0).sum()) == int((g["counts"][clean] > 0).sum())
+    n_diff = int((out["counts"][near] != g["counts"][near]).sum())
+    print("%s: N=%d hits gpu=%d ref=%d; near-contact rollouts=%d (of which %d differ)" %
+          (name, N, out["hits"], int((g["counts"] > 0).sum()), int(near.sum()), n_diff))
+    assert abs(out["hits"] - int((g["counts"] > 0).sum())) <= int(near.sum())
+    assert out["executed_steps"] == N * plan["trajectory"].shape[1]
+    assert int(out["first_hit_hist"].sum()) == out["hits"]
+
+
+@pytest.mark.parametrize("name", ["pr2test2", "pr2custom"])
+def test_replay_poses_and_clearance(ctx, plan, scenes, name):
+    g = golden("mc_replay_%s.npz" % name)
+    N = g["counts"].shape[0]
+    out = _replay(ctx, plan, scenes[name], g["draws"], N, want_counts=True, audit=True)
+    poses = np.transpose(out["poses"], (0, 2, 1))[:, :64, :].astype(np.float64)   # [T, 64, 3]
+    ref = g["poses_first64"]
+    # angles live on [0, 2 pi]: compare on the circle
+    d = poses - ref
+    d[..., 2] = (d[..., 2] + np.pi) % (2 * np.pi) - np.pi
+    scale = np.maximum(np.abs(ref), 1.0)
+    assert np.max(np.abs(d) / scale) < POSE_RTOL
+    np.testing.assert_allclose(out["clearance"], g["clearance"], atol=2e-5)
+    gpu_near = int((np.abs(out["clearance"]) < NEAR_EPS).sum())
+    assert out["near_contact"] == gpu_near
+    # flags from the audit launch agree with the exhaustive launch wherever the pose is not near contact
+    far = np.abs(g["clearance"]) >= NEAR_EPS
+    np.testing.assert_array_equal((out["clearance"] <= 0)[far], (g["clearance"] <= 0)[far])
+
+
+def test_replay_early_exit_flags(ctx, plan, scenes):
+    g = golden("mc_replay_pr2test2.npz")
+    N = g["counts"].shape[0]
+    full = _replay(ctx, plan, scenes["pr2test2"], g["draws"], N, want_counts=True)
+    ee = _replay(ctx, plan, scenes["pr2test2"], g["draws"], N, want_counts=True, want_hist=True, early_exit=True)
+    np.testing.assert_array_equal(ee["counts"], (full["counts"] > 0).astype(np.uint32))
+    assert ee["hits"] == full["hits"]
+    assert ee["executed_steps"] < full["executed_steps"]
+
+
+def test_replay_vs_live_reference_random_draws(ctx, plan, scenes):
+    """Fresh seeds and sizes (incl. ragged, non-multiple-of-warp N) against the reference run live."""
+    import oracle_ref
+    if not oracle_ref.available():
+        pytest.skip("oracle/_ref not built")
+    T = plan["trajectory"].shape[1]
+    for seed, N in ((1, 1), (2, 33), (3, 257), (4, 1500)):
+        draws = np.random.Generator(np.random.PCG64(seed)).standard_normal(3 * N + 11 * (T - 1))
+        ref = oracle_ref.mc_run(plan, scenes["pr2test2"]["boxes"], scenes["pr2test2"]["hulls"], N, draws=draws)
+        out = _replay(ctx, plan, scenes["pr2test2"], draws, N, want_counts=True)
+        near = (np.abs(ref["clearance"]) < NEAR_EPS).any(axis=0)
+        np.testing.assert_array_equal(out["counts"][~near], ref["counts"][~near])
+
+
+def test_zero_rollouts(ctx, plan, scenes):
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    ctx.set_scene(scenes["pr2test2"]["boxes"], scenes["pr2test2"]["hulls"])
+    p, keep = abi.make_mc_params(plan, n_rollouts=0, mode=abi.MODE_PHILOX)
+    out = ctx.mc_run(p)
+    assert out["hits"] == 0 and out["executed_steps"] == 0
+
+
+def test_philox_inside_reference_confidence_interval(ctx, plan, scenes):
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    dist = json.load(open(os.path.join(GOLD, "mc_dist_pr2test2.json")))
+    half = 2.576 * dist["std"] / np.sqrt(dist["runs"])
+    ctx.set_scene(scenes["pr2test2"]["boxes"], scenes["pr2test2"]["hulls"])
+    N = 1 << 20
+    p, keep = abi.make_mc_params(plan, n_rollouts=N, mode=abi.MODE_PHILOX, early_exit=True)
+    out = ctx.mc_run(p)
+    print("philox P=%.5f reference mean=%.5f +- %.5f (99%% CI)" % (out["P"], dist["mean"], half))
+    assert abs(out["P"] - dist["mean"]) < half
+    # early exit does not change the estimate
+    p2, keep2 = abi.make_mc_params(plan, n_rollouts=N, mode=abi.MODE_PHILOX, early_exit=False)
+    out2 = ctx.mc_run(p2, want_counts=True)
+    assert out2["hits"] == out["hits"]
+    assert out2["executed_steps"] == N * plan["trajectory"].shape[1]
+
+
+def test_philox_shard_invariance(ctx, plan, scenes):
+    """Rollout-id-derived counters: the hit total does not depend on how ids are split."""
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    ctx.set_scene(scenes["pr2test2"]["boxes"], scenes["pr2test2"]["hulls"])
+    N = 100003
+    p, keep = abi.make_mc_params(plan, n_rollouts=N, mode=abi.MODE_PHILOX)
+    whole = ctx.mc_run(p, want_hist=True)
+    for G in (2, 4, 8):
+        hits, hist = 0, np.zeros_like(whole["first_hit_hist"])
+        for g in range(G):
+            lo, hi = g * N // G, (g + 1) * N // G
+            pg, kg = abi.make_mc_params(plan, n_rollouts=hi - lo, rollout_offset=lo, mode=abi.MODE_PHILOX)
+            o = ctx.mc_run(pg, want_hist=True)
+            hits += o["hits"]
+            hist += o["first_hit_hist"]
+        assert hits == whole["hits"]
+        np.testing.assert_array_equal(hist, whole["first_hit_hist"])
