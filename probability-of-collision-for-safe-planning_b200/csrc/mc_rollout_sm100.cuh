@@ -13,9 +13,9 @@
 #include "sat_device.cuh"
 
 // per-step plan record staged in shared memory (floats)
-//   replay : u~ = (rot1, trans, rot2)                               3 floats
+//   replay : u~ = (rot1, trans, rot2) as 3 FP64 values             6 floats
 //   philox : x*_t (3), u*_t (3), M_t (3) = generateM_EKF(u*_t)      9 floats
-#define MC_REPLAY_STRIDE 3
+#define MC_REPLAY_STRIDE 6
 #define MC_PHILOX_STRIDE 9
 
 struct McPlanConst {
@@ -46,10 +46,17 @@ struct McLaunch {
     float near_eps;
 };
 
+// FP64 angle in [0, 4 pi] -> FP32 angle in [-pi, pi] (rounding error <= 1.2e-7 rad, not accumulated)
+__device__ __forceinline__ float reduce_angle(double a) {
+    if (a > MCSIM_PI) a -= 2 * MCSIM_PI;
+    if (a > MCSIM_PI) a -= 2 * MCSIM_PI;
+    return float(a);
+}
+
 template <int MODE, bool AUDIT, bool EARLY_EXIT, int EST, int NL>
 __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
     using namespace mcsim_math;
-    extern __shared__ float s_plan[];
+    extern __shared__ __align__(16) float s_plan[];
     __shared__ unsigned s_cnt[4];
     __shared__ unsigned s_hist[MCSIM_MAX_WAYPOINTS];
 
@@ -99,13 +106,18 @@ __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
             S[8] = c_mc.chol[3] * c_mc.chol[3] + c_mc.chol[4] * c_mc.chol[4] + c_mc.chol[5] * c_mc.chol[5];
         }
 
+        // Replay mode keeps the heading in FP64: theta is a running sum of angles near 2 pi, where an
+        // FP32 state would lose 2.4e-7 rad per addition and, through trans * d(theta), ~2e-5 m over
+        // 55 steps (measured); x and y stay FP32.  Only the reduced angle is rounded to FP32.
+        double th = (MODE == MCSIM_MODE_REPLAY) ? (c_mc.mu0d[2] + c_mc.chold[3] * a.z0[3 * i] + c_mc.chold[4] * a.z0[3 * i + 1] + c_mc.chold[5] * a.z0[3 * i + 2]) : 0.0;
         unsigned count = 0;
         int first = -1;
         for (int t = 0; t < T; ++t) {
             // ---- collision test at waypoint t (checkParticleCollisions)
             const float* q = (MODE == MCSIM_MODE_PHILOX && EST == MCSIM_EST_CLOSEDLOOP) ? real : p;
             float sn, cs;
-            sincos_t(q[2], sn, cs);
+            if (MODE == MCSIM_MODE_REPLAY) sincos_t(reduce_angle(th), sn, cs);
+            else sincos_t(q[2], sn, cs);
             bool hit;
             if (AUDIT) {
                 const float cl = robot_clearance(q[0], q[1], cs, sn);
@@ -116,7 +128,7 @@ __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
                 if (a.poses) {
                     a.poses[((size_t)t * 3 + 0) * a.n + i] = q[0];
                     a.poses[((size_t)t * 3 + 1) * a.n + i] = q[1];
-                    a.poses[((size_t)t * 3 + 2) * a.n + i] = q[2];
+                    a.poses[((size_t)t * 3 + 2) * a.n + i] = (MODE == MCSIM_MODE_REPLAY) ? float(th) : q[2];
                 }
             } else {
                 hit = robot_hits(q[0], q[1], cs, sn, my_tests);
@@ -130,10 +142,13 @@ __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
             if (t == T - 1) break;
             // ---- move to waypoint t+1
             if (MODE == MCSIM_MODE_REPLAY) {
-                const float u[3] = {s_plan[t * STRIDE], s_plan[t * STRIDE + 1], s_plan[t * STRIDE + 2]};
-                float nx[3];
-                predict_pose(p, u, nx);
-                p[0] = nx[0]; p[1] = nx[1]; p[2] = nx[2];
+                const double* u = reinterpret_cast<const double*>(s_plan) + 3 * t;
+                float s1, c1;
+                sincos_t(reduce_angle(th + u[0]), s1, c1);
+                const float tr = float(u[1]);
+                p[0] = fmaf(tr, c1, p[0]);
+                p[1] = fmaf(tr, s1, p[1]);
+                th = angle_wrap(th + u[0] + u[2]);
             } else {
                 const float* r = s_plan + t * STRIDE;
                 const float xs[3] = {r[0], r[1], r[2]};

@@ -258,7 +258,7 @@ extern "C" int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* c, const mcsim_mc_params* p
     if (p->mode == MCSIM_MODE_REPLAY) {
         plan.resize(size_t(T > 1 ? T - 1 : 1) * MC_REPLAY_STRIDE, 0.f);
         for (int t = 0; t < T - 1; ++t)
-            for (int k = 0; k < 3; ++k) plan[t * MC_REPLAY_STRIDE + k] = float(p->applied[k * (T - 1) + t]);
+            for (int k = 0; k < 3; ++k) memcpy(&plan[t * MC_REPLAY_STRIDE + 2 * k], &p->applied[k * (T - 1) + t], sizeof(double));
     } else {
         plan.resize(size_t(T) * MC_PHILOX_STRIDE, 0.f);
         for (int t = 0; t < T; ++t) {
