@@ -131,6 +131,11 @@ int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* ctx, const mcsim_mc_params* p);
  * device until mcsim_cuda_mc_collect.  Asynchronous on the context's stream. */
 int mcsim_cuda_mc_launch(mcsim_cuda_ctx* ctx, uint64_t n_rollouts, uint64_t rollout_offset);
 int mcsim_cuda_mc_collect(mcsim_cuda_ctx* ctx, mcsim_mc_result* r);
+/* DEVICE pointer of the counter block the launches accumulate into: uint64[4 + T] =
+ * {hits, near_contact, executed_steps, pair_tests, first_hit_hist[T]}.  A multi-GPU caller
+ * all-reduces (sum) this buffer on the context's stream between mc_launch and mc_collect
+ * (bench.py does it with torch.distributed/NCCL); allocated at mcsim_cuda_create, never moves. */
+void* mcsim_cuda_mc_counters(mcsim_cuda_ctx* ctx);
 
 /* ---- host thread of the reference estimator ---------------------------------------------- */
 /* The single closed-loop "real robot" of EKF_GaussProp (MCSimulator.h:685-800): controller gain

@@ -85,6 +85,8 @@ extern "C" int mcsim_cuda_create(int device, mcsim_cuda_ctx** out) {
     CK(cudaEventCreate(&c->ev1));
     CK(cudaMallocHost((void**)&c->h_counters, sizeof(unsigned long long) * (4 + MCSIM_MAX_WAYPOINTS)));
     CK(cudaMallocHost((void**)&c->h_gmm, sizeof(double) * 4096));
+    CK(c->counters.reserve(sizeof(unsigned long long) * (4 + MCSIM_MAX_WAYPOINTS)));
+    CK(cudaMemset(c->counters.p, 0, sizeof(unsigned long long) * (4 + MCSIM_MAX_WAYPOINTS)));
     *out = c;
     return MCSIM_OK;
 }
@@ -320,6 +322,8 @@ extern "C" int mcsim_cuda_mc_launch(mcsim_cuda_ctx* c, uint64_t n, uint64_t offs
     CK(cudaSetDevice(c->device));
     return mc_launch_impl(c, n, offset, nullptr, nullptr, nullptr, nullptr);
 }
+
+extern "C" void* mcsim_cuda_mc_counters(mcsim_cuda_ctx* c) { return c ? c->counters.p : nullptr; }
 
 extern "C" int mcsim_cuda_mc_collect(mcsim_cuda_ctx* c, mcsim_mc_result* r) {
     if (!c || !r || !c->mc_prepared) return fail(MCSIM_ERR_ARG, "mc_collect: nothing prepared");

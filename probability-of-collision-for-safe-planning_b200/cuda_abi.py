@@ -99,6 +99,8 @@ def lib():
         L.mcsim_cuda_mc_prepare.argtypes = [vp, C.POINTER(McParams)]
         L.mcsim_cuda_mc_launch.argtypes = [vp, C.c_uint64, C.c_uint64]
         L.mcsim_cuda_mc_collect.argtypes = [vp, C.POINTER(McResult)]
+        L.mcsim_cuda_mc_counters.argtypes = [vp]
+        L.mcsim_cuda_mc_counters.restype = vp
         L.mcsim_host_thread.argtypes = [C.POINTER(McParams), _dp, C.c_size_t, _dp, _dp, _dp, _dp, _dp, _dp]
         for name, at in (("mcsim_cuda_gmm_truncate", [vp, C.POINTER(GmmTruncateParams), C.POINTER(GmmTruncateResult)]),
                          ("mcsim_cuda_gmm_run", [vp, C.POINTER(McParams), C.POINTER(GmmRunParams), C.POINTER(GmmRunResult)])):
@@ -233,6 +235,18 @@ class Context:
 
     def mc_launch(self, n, offset=0):
         check(lib().mcsim_cuda_mc_launch(self._h, int(n), int(offset)))
+
+    def mc_counters_tensor(self, T):
+        """torch int64 view (no copy) of the device counter block uint64[4 + T], for the NCCL all-reduce
+        of a multi-GPU run; the block is allocated at its maximum size when the context is created."""
+        import torch
+
+        class _Raw:
+            pass
+        raw = _Raw()
+        raw.__cuda_array_interface__ = dict(shape=(4 + int(T),), typestr="<i8", version=2,
+                                            data=(int(lib().mcsim_cuda_mc_counters(self._h)), False))
+        return torch.as_tensor(raw, device="cuda:%d" % self.device)
 
     def mc_collect(self, T=0, want_hist=False):
         r = McResult()
