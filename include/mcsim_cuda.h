@@ -63,6 +63,9 @@ uint64_t mcsim_cuda_launch_count(mcsim_cuda_ctx* ctx);
  * stream for about `ms` milliseconds each.  These are the roofline denominators of the MC path
  * (MEASURED_PEAKS.json has HBM and tensor peaks only). */
 int mcsim_cuda_measure_peaks(mcsim_cuda_ctx* ctx, double ms, double* fp32_tflops, double* mufu_tops);
+/* One pipe at a time: which = 0 scalar FFMA chain (TFLOP/s), 1 MUFU chain (10^12 op/s),
+ * 2 packed FP32 pairs, fma.rn.f32x2 / SASS FFMA2 (TFLOP/s). */
+int mcsim_cuda_measure_peak(mcsim_cuda_ctx* ctx, int which, double ms, double* out);
 
 /* ---- scene ------------------------------------------------------------------------------ */
 /* Replaces OpenRAVE's collision world for this path (MCSimulator.h:269-285).  boxes: n_boxes x 8

@@ -110,35 +110,43 @@ extern "C" void* mcsim_cuda_stream(mcsim_cuda_ctx* c) { return c ? (void*)c->str
 extern "C" uint64_t mcsim_cuda_launch_count(mcsim_cuda_ctx* c) { return c ? c->launches : 0; }
 
 // ---- peaks ----------------------------------------------------------------------------------
-extern "C" int mcsim_cuda_measure_peaks(mcsim_cuda_ctx* c, double ms, double* fp32_tflops, double* mufu_tops) {
-    if (!c) return fail(MCSIM_ERR_ARG, "measure_peaks: NULL context");
+// which: 0 = FFMA chain (TFLOP/s), 1 = MUFU chain (10^12 op/s), 2 = packed FFMA2 chain (TFLOP/s)
+extern "C" int mcsim_cuda_measure_peak(mcsim_cuda_ctx* c, int which, double ms, double* out) {
+    if (!c || !out || which < 0 || which > 2) return fail(MCSIM_ERR_ARG, "measure_peak: bad arguments");
     CK(cudaSetDevice(c->device));
     float* d = nullptr;
     CK(cudaMalloc(&d, 64));
     const int grid = c->n_sm * 8, block = 256;
-    for (int which = 0; which < 2; ++which) {
-        int iters = 4096;
-        double rate = 0;
-        for (int rep = 0; rep < 4; ++rep) {  // rep 0 warms up, later reps are sized to ~ms
-            CK(cudaEventRecord(c->ev0, c->stream));
-            if (which == 0) fma_peak_kernel<<<grid, block, 0, c->stream>>>(d, iters, 0.999f, 0.001f);
-            else mufu_peak_kernel<<<grid, block, 0, c->stream>>>(d, iters);
-            ++c->launches;
-            CK(cudaEventRecord(c->ev1, c->stream));
-            CK(cudaStreamSynchronize(c->stream));
-            float t = 0;
-            CK(cudaEventElapsedTime(&t, c->ev0, c->ev1));
-            const double ops = double(grid) * block * double(iters) * 8.0 * (which == 0 ? 2.0 : 1.0);
-            const double r = ops / (double(t) * 1e-3) / 1e12;
-            if (rep > 0 && r > rate) rate = r;
-            const double scale = (t > 0 ? ms / t : 8.0);
-            iters = int(iters * (scale > 8 ? 8 : (scale < 0.125 ? 0.125 : scale)));
-            if (iters < 64) iters = 64;
-        }
-        if (which == 0 && fp32_tflops) *fp32_tflops = rate;
-        if (which == 1 && mufu_tops) *mufu_tops = rate;
+    int iters = 4096;
+    double rate = 0;
+    for (int rep = 0; rep < 4; ++rep) {  // rep 0 warms up, later reps are sized to ~ms
+        CK(cudaEventRecord(c->ev0, c->stream));
+        if (which == 0) fma_peak_kernel<<<grid, block, 0, c->stream>>>(d, iters, 0.999f, 0.001f);
+        else if (which == 1) mufu_peak_kernel<<<grid, block, 0, c->stream>>>(d, iters);
+        else fma2_peak_kernel<<<grid, block, 0, c->stream>>>(d, iters, 0.999f, 0.001f);
+        ++c->launches;
+        CK(cudaEventRecord(c->ev1, c->stream));
+        CK(cudaStreamSynchronize(c->stream));
+        float t = 0;
+        CK(cudaEventElapsedTime(&t, c->ev0, c->ev1));
+        const double per = which == 0 ? 2.0 : (which == 1 ? 1.0 : 4.0);
+        const double ops = double(grid) * block * double(iters) * 8.0 * per;
+        const double r = ops / (double(t) * 1e-3) / 1e12;
+        if (rep > 0 && r > rate) rate = r;
+        const double scale = (t > 0 ? ms / t : 8.0);
+        iters = int(iters * (scale > 8 ? 8 : (scale < 0.125 ? 0.125 : scale)));
+        if (iters < 64) iters = 64;
     }
     CK(cudaFree(d));
+    *out = rate;
+    return MCSIM_OK;
+}
+
+extern "C" int mcsim_cuda_measure_peaks(mcsim_cuda_ctx* c, double ms, double* fp32_tflops, double* mufu_tops) {
+    double v = 0;
+    int rc;
+    if (fp32_tflops) { rc = mcsim_cuda_measure_peak(c, 0, ms, &v); if (rc) return rc; *fp32_tflops = v; }
+    if (mufu_tops) { rc = mcsim_cuda_measure_peak(c, 1, ms, &v); if (rc) return rc; *mufu_tops = v; }
     return MCSIM_OK;
 }
 

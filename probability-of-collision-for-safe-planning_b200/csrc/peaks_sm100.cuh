@@ -38,4 +38,23 @@ __global__ void __launch_bounds__(256) mufu_peak_kernel(float* out, int iters) {
     if (s == 12345.678f) out[0] = s;
 }
 
+// packed FP32 pairs (fma.rn.f32x2 -> SASS FFMA2): 8 independent chains of 2 lanes; iters x 8 x 4 flops per thread
+__device__ __forceinline__ unsigned long long ffma2(unsigned long long x, unsigned long long a, unsigned long long b) {
+    asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(x) : "l"(a), "l"(b));
+    return x;
+}
+__global__ void __launch_bounds__(256) fma2_peak_kernel(float* out, int iters, float a, float b) {
+    float2 av = make_float2(a, a), bv = make_float2(b, b), v = make_float2(threadIdx.x, threadIdx.x + 0.5f);
+    const unsigned long long aa = *reinterpret_cast<unsigned long long*>(&av), bb = *reinterpret_cast<unsigned long long*>(&bv);
+    unsigned long long x0 = *reinterpret_cast<unsigned long long*>(&v), x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3;
+    unsigned long long x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+#pragma unroll 8
+    for (int i = 0; i < iters; ++i) {
+        x0 = ffma2(x0, aa, bb); x1 = ffma2(x1, aa, bb); x2 = ffma2(x2, aa, bb); x3 = ffma2(x3, aa, bb);
+        x4 = ffma2(x4, aa, bb); x5 = ffma2(x5, aa, bb); x6 = ffma2(x6, aa, bb); x7 = ffma2(x7, aa, bb);
+    }
+    const unsigned long long s = x0 ^ x1 ^ x2 ^ x3 ^ x4 ^ x5 ^ x6 ^ x7;
+    if (s == 12345ull) out[0] = float(s);
+}
+
 #endif

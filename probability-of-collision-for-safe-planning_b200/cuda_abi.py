@@ -94,6 +94,7 @@ def lib():
         L.mcsim_cuda_launch_count.argtypes = [vp]
         L.mcsim_cuda_launch_count.restype = C.c_uint64
         L.mcsim_cuda_measure_peaks.argtypes = [vp, C.c_double, _dp, _dp]
+        L.mcsim_cuda_measure_peak.argtypes = [vp, C.c_int, C.c_double, _dp]
         L.mcsim_cuda_set_scene.argtypes = [vp, _dp, C.c_int, _dp, C.c_int]
         L.mcsim_cuda_mc_run.argtypes = [vp, C.POINTER(McParams), C.POINTER(McResult)]
         L.mcsim_cuda_mc_prepare.argtypes = [vp, C.POINTER(McParams)]
@@ -202,6 +203,12 @@ class Context:
         a, b = C.c_double(), C.c_double()
         check(lib().mcsim_cuda_measure_peaks(self._h, float(ms), C.byref(a), C.byref(b)))
         return a.value, b.value
+
+    def measure_peak(self, which, ms=200.0):
+        """which: 0 FFMA (TFLOP/s), 1 MUFU (1e12 op/s), 2 packed FFMA2 (TFLOP/s)."""
+        a = C.c_double()
+        check(lib().mcsim_cuda_measure_peak(self._h, int(which), float(ms), C.byref(a)))
+        return a.value
 
     def set_scene(self, boxes, hulls):
         b = np.ascontiguousarray(boxes, dtype=np.float64).reshape(-1, 8)
