@@ -204,9 +204,13 @@ typedef struct {
 } mcsim_gmm_run_result;
 
 /* Whole GMM branch of EKF_GaussProp for one plan; plan / noise parameters come from mc (its
- * n_rollouts, z0 and applied fields are ignored). */
+ * n_rollouts, z0 and applied fields are ignored): mc->mode selects replay / Philox, mc->seed is
+ * the Philox key and mc->rollout_offset the Philox subsequence (a trajectory id). */
 int mcsim_cuda_gmm_run(mcsim_cuda_ctx* ctx, const mcsim_mc_params* mc, const mcsim_gmm_run_params* g,
                        mcsim_gmm_run_result* r);
+
+/* bytes the last *_run call copied host->device and device->host (bench.py's e2e accounting) */
+void mcsim_cuda_io_bytes(mcsim_cuda_ctx* ctx, uint64_t* h2d, uint64_t* d2h);
 
 #ifdef __cplusplus
 }

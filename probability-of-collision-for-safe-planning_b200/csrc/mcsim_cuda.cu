@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "mc_rollout_sm100.cuh"
+#include "gmm_sm100.cuh"
 #include "peaks_sm100.cuh"
 
 static thread_local char g_err[512] = "";
@@ -56,9 +57,13 @@ struct mcsim_cuda_ctx {
     mcsim_mc_params mc;                        // prepared parameters (pointers not retained)
     bool mc_prepared = false;
     int mc_T = 0;
-    // GMM / EM state
-    DevBuf gmm_in, gmm_out, gmm_normals;
+    // FP64 scene for the replay-mode GMM SAT
+    DevBuf hulls_d, pairs_d;
+    int n_hulls = 0;
+    // GMM state
+    DevBuf gmm_comps, gmm_stats, gmm_hist, gmm_counts, gmm_normals, gmm_steps, gmm_prob, gmm_pre, gmm_post, gmm_trunc, gmm_nout, gmm_deg;
     double* h_gmm = nullptr;  // pinned staging
+    uint64_t h2d_bytes = 0, d2h_bytes = 0;  // bytes copied by the last run call
 };
 
 extern "C" const char* mcsim_cuda_last_error(void) { return g_err; }
@@ -97,7 +102,10 @@ extern "C" void mcsim_cuda_destroy(mcsim_cuda_ctx* c) {
     cudaStreamSynchronize(c->stream);
     c->plan.release(); c->z0.release(); c->counters.release(); c->counts.release();
     c->poses.release(); c->clearance.release();
-    c->gmm_in.release(); c->gmm_out.release(); c->gmm_normals.release();
+    c->hulls_d.release(); c->pairs_d.release();
+    c->gmm_comps.release(); c->gmm_stats.release(); c->gmm_hist.release(); c->gmm_counts.release();
+    c->gmm_normals.release(); c->gmm_steps.release(); c->gmm_prob.release(); c->gmm_pre.release();
+    c->gmm_post.release(); c->gmm_trunc.release(); c->gmm_nout.release(); c->gmm_deg.release();
     if (c->h_counters) cudaFreeHost(c->h_counters);
     if (c->h_gmm) cudaFreeHost(c->h_gmm);
     cudaEventDestroy(c->ev0);
@@ -159,6 +167,8 @@ extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int 
     SceneConst sc;
     memset(&sc, 0, sizeof(sc));
     std::vector<float4> pairs;
+    std::vector<HullD> hd(n_hulls);
+    std::vector<PairD> pd;
     sc.n_hulls = n_hulls;
     for (int h = 0; h < n_hulls; ++h) {
         const double* hu = hulls + h * MCSIM_PRISM_STRIDE;
@@ -173,8 +183,10 @@ extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int 
             const double q = bx[2] * bx[1] - bx[3] * bx[0];
             pairs.push_back(make_float4(float(bx[0]), float(bx[1]), float(bx[2]), float(bx[3])));
             pairs.push_back(make_float4(float(bx[4]), float(bx[5]), float(p), float(q)));
+            pd.push_back(PairD{bx[0], bx[1], bx[2], bx[3], bx[4], bx[5]});
         }
         r.count = int(pairs.size() / 2) - r.first;
+        hd[h] = HullD{hu[0], hu[1], hu[2], hu[3], hu[4], hu[5], r.first, r.count};
         const float reach = float(sqrt(hu[0] * hu[0] + hu[1] * hu[1]) + sqrt(hu[4] * hu[4] + hu[5] * hu[5]));
         if (reach > sc.reach) sc.reach = reach;
     }
@@ -184,6 +196,11 @@ extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int 
     CK(cudaStreamSynchronize(c->stream));
     CK(cudaMemcpyToSymbol(c_scene, &sc, sizeof(sc)));
     if (!pairs.empty()) CK(cudaMemcpyToSymbol(c_pairs, pairs.data(), pairs.size() * sizeof(float4)));
+    CK(c->hulls_d.reserve(sizeof(HullD) * hd.size()));
+    CK(cudaMemcpy(c->hulls_d.p, hd.data(), sizeof(HullD) * hd.size(), cudaMemcpyHostToDevice));
+    CK(c->pairs_d.reserve(sizeof(PairD) * (pd.size() ? pd.size() : 1)));
+    if (!pd.empty()) CK(cudaMemcpy(c->pairs_d.p, pd.data(), sizeof(PairD) * pd.size(), cudaMemcpyHostToDevice));
+    c->n_hulls = n_hulls;
     c->scene_set = true;
     c->n_pairs = sc.n_pairs;
     return MCSIM_OK;
@@ -379,4 +396,255 @@ extern "C" int mcsim_cuda_mc_run(mcsim_cuda_ctx* c, const mcsim_mc_params* p, mc
     if (rc) return rc;
     CK(cudaEventElapsedTime(&r->kernel_ms, c->ev0, c->ev1));
     return MCSIM_OK;
+}
+
+// ---- GMM mode -----------------------------------------------------------------------------------
+// two standard normals from one Philox block, host side (the host thread of a Philox-mode GMM run)
+static void host_normals(uint64_t seed, unsigned stream_id, int T, int per_step, std::vector<double>& out) {
+    out.resize(size_t(T > 1 ? T - 1 : 0) * per_step);
+    for (int t = 0; t < T - 1; ++t) {
+        for (int j = 0; j < per_step; j += 4) {
+            mcsim_rng::u32x4 c = {unsigned(t), stream_id, unsigned(j >> 2), unsigned(mcsim_rng::PURPOSE_GMM_HOST)};
+            c = mcsim_rng::philox4x32_10(c, unsigned(seed), unsigned(seed >> 32));
+            const unsigned w[4] = {c.x, c.y, c.z, c.w};
+            for (int h = 0; h < 2; ++h) {
+                const double u1 = (double(w[2 * h]) + 0.5) * (1.0 / 4294967296.0);
+                const double u2 = (double(w[2 * h + 1]) + 0.5) * (1.0 / 4294967296.0);
+                const double r = sqrt(-2.0 * log(u1));
+                const double n0 = r * cos(2 * MCSIM_PI * u2), n1 = r * sin(2 * MCSIM_PI * u2);
+                if (j + 2 * h < per_step) out[size_t(t) * per_step + j + 2 * h] = n0;
+                if (j + 2 * h + 1 < per_step) out[size_t(t) * per_step + j + 2 * h + 1] = n1;
+            }
+        }
+    }
+}
+
+static int gmm_reserve(mcsim_cuda_ctx* c, int T, int K) {
+    CK(c->gmm_comps.reserve(sizeof(double) * MCSIM_MAX_GAUSSIANS * GMM_COMP));
+    CK(c->gmm_stats.reserve(sizeof(double) * MCSIM_MAX_GAUSSIANS * GMM_STAT));
+    CK(c->gmm_hist.reserve(sizeof(unsigned) * MCSIM_MAX_GAUSSIANS));
+    CK(c->gmm_prob.reserve(sizeof(double) * T));
+    CK(c->gmm_pre.reserve(sizeof(double) * size_t(T) * K * GMM_REC));
+    CK(c->gmm_post.reserve(sizeof(double) * K * GMM_REC));
+    CK(c->gmm_trunc.reserve(sizeof(double) * K * GMM_REC));
+    CK(c->gmm_nout.reserve(sizeof(unsigned long long) * 2 * MCSIM_MAX_GAUSSIANS));
+    CK(c->gmm_deg.reserve(sizeof(int)));
+    CK(c->gmm_steps.reserve(sizeof(GmmStepTable) * (T > 1 ? T - 1 : 1)));
+    CK(cudaMemsetAsync(c->gmm_stats.p, 0, sizeof(double) * MCSIM_MAX_GAUSSIANS * GMM_STAT, c->stream));
+    CK(cudaMemsetAsync(c->gmm_hist.p, 0, sizeof(unsigned) * MCSIM_MAX_GAUSSIANS, c->stream));
+    CK(cudaMemsetAsync(c->gmm_deg.p, 0, sizeof(int), c->stream));
+    return MCSIM_OK;
+}
+
+static void gmm_fill_launch(mcsim_cuda_ctx* c, GmmLaunch& a, int K, int T, int L, uint64_t n, uint64_t seed, unsigned stream_id) {
+    memset(&a, 0, sizeof(a));
+    a.K = K; a.T = T; a.L = L; a.n = n;
+    a.comps = (double*)c->gmm_comps.p;
+    a.stats = (double*)c->gmm_stats.p;
+    a.hist = (unsigned*)c->gmm_hist.p;
+    a.k0 = unsigned(seed); a.k1 = unsigned(seed >> 32);
+    a.stream_id = stream_id;
+    a.hulls_d = (const HullD*)c->hulls_d.p;
+    a.pairs_d = (const PairD*)c->pairs_d.p;
+    a.n_hulls = c->n_hulls;
+    a.steps = (const GmmStepTable*)c->gmm_steps.p;
+    a.probabilities = (double*)c->gmm_prob.p;
+    a.degenerate = (int*)c->gmm_deg.p;
+}
+
+// the three launches of one waypoint
+static int gmm_launch_waypoint(mcsim_cuda_ctx* c, const GmmLaunch& a, int mode) {
+    const int block = 256;
+    unsigned long long want = (a.n + block - 1) / block;
+    const unsigned long long cap = (unsigned long long)c->n_sm * 8;
+    const unsigned grid = unsigned(want < cap ? (want ? want : 1) : cap);
+    if (mode == MCSIM_MODE_PHILOX) {
+        gmm_count_kernel<<<grid, block, 0, c->stream>>>(a);
+        gmm_sample_kernel<MCSIM_MODE_PHILOX><<<grid, block, 0, c->stream>>>(a);
+        c->launches += 2;
+    } else {
+        gmm_sample_kernel<MCSIM_MODE_REPLAY><<<grid, block, 0, c->stream>>>(a);
+        c->launches += 1;
+    }
+    gmm_refit_kernel<<<1, 32, 0, c->stream>>>(a);
+    c->launches += 1;
+    CK(cudaGetLastError());
+    return MCSIM_OK;
+}
+
+extern "C" int mcsim_cuda_gmm_run(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, const mcsim_gmm_run_params* g,
+                                  mcsim_gmm_run_result* r) {
+    if (!c || !mc || !g || !r) return fail(MCSIM_ERR_ARG, "gmm_run: NULL argument");
+    if (!c->scene_set) return fail(MCSIM_ERR_ARG, "gmm_run: mcsim_cuda_set_scene has not been called");
+    const int T = mc->T, K = g->K, L = mc->n_landmarks;
+    const uint64_t N = g->n_samples;
+    if (T < 1 || T > MCSIM_MAX_WAYPOINTS || !mc->trajectory || (T > 1 && !mc->odometry)) return fail(MCSIM_ERR_ARG, "gmm_run: bad plan");
+    if (K < 1 || K > MCSIM_MAX_GAUSSIANS) return fail(MCSIM_ERR_ARG, "gmm_run: K=%d out of range 1..%d", K, MCSIM_MAX_GAUSSIANS);
+    if (L < 0 || L > MCSIM_MAX_LANDMARKS || (L && !mc->landmarks)) return fail(MCSIM_ERR_ARG, "gmm_run: bad landmarks");
+    if (N < 1) return fail(MCSIM_ERR_ARG, "gmm_run: n_samples must be positive");
+    const int mode = mc->mode;
+    const int per_step = 3 + L;
+    CK(cudaSetDevice(c->device));
+    c->h2d_bytes = c->d2h_bytes = 0;
+
+    // ---- the shared real-robot thread (host, FP64): applied commands and observations of every step
+    std::vector<double> hn;
+    if (mode == MCSIM_MODE_REPLAY) {
+        if (!g->normals || !g->counts) return fail(MCSIM_ERR_ARG, "gmm_run: replay mode needs normals and counts");
+        const size_t need = 3 * N + size_t(T - 1) * (per_step + 3 * N);
+        if (g->n_normals < need) return fail(MCSIM_ERR_DRAWS, "gmm_run: %zu normals given, %zu needed", g->n_normals, need);
+        hn.resize(size_t(T - 1) * per_step);
+        for (int t = 0; t < T - 1; ++t)
+            memcpy(&hn[size_t(t) * per_step], g->normals + 3 * N + size_t(t) * (per_step + 3 * N), sizeof(double) * per_step);
+    } else if (mode == MCSIM_MODE_PHILOX) {
+        host_normals(mc->seed, unsigned(mc->rollout_offset), T, per_step, hn);
+    } else {
+        return fail(MCSIM_ERR_ARG, "gmm_run: unknown mode %d", mode);
+    }
+    std::vector<double> applied(size_t(3) * (T > 1 ? T - 1 : 1)), obs(size_t(T > 1 ? T - 1 : 1) * (L ? L : 1));
+    if (T > 1) {
+        int rc = mcsim_host_thread(mc, hn.data(), hn.size(), nullptr, applied.data(), nullptr, nullptr, nullptr, obs.data());
+        if (rc) return fail(rc, "gmm_run: host thread failed (%d)", rc);
+    }
+    std::vector<GmmStepTable> steps(T > 1 ? T - 1 : 1);
+    mcsim_math::NoiseModel<double> nmd;
+    for (int k = 0; k < 4; ++k) nmd.alpha[k] = mc->alphas[k];
+    for (int t = 0; t < T - 1; ++t) {
+        double us[3];
+        for (int k = 0; k < 3; ++k) { us[k] = mc->odometry[k * (T - 1) + t]; steps[t].u[k] = applied[k * (T - 1) + t]; }
+        mcsim_math::motion_noise(nmd, us, steps[t].M);
+        for (int l = 0; l < L; ++l) steps[t].z[l] = obs[size_t(t) * L + l];
+    }
+
+    int rc = gmm_reserve(c, T, K);
+    if (rc) return rc;
+    // ---- initial mixture: K copies of N(x*_0, Sigma_0), weights 1/K (GM_Model::initModel, GM_Model.h:57-77)
+    std::vector<double> comps(size_t(K) * GMM_COMP);
+    double Lo[6];
+    if (!gmm_chol3(mc->cov0, Lo)) return fail(MCSIM_ERR_ARG, "gmm_run: initial covariance is not positive definite");
+    for (int k = 0; k < K; ++k) {
+        double* cp = &comps[size_t(k) * GMM_COMP];
+        cp[0] = 1.0 / K;
+        for (int i = 0; i < 3; ++i) cp[1 + i] = mc->trajectory[i * T];
+        for (int i = 0; i < 9; ++i) cp[4 + i] = mc->cov0[i];
+        for (int i = 0; i < 6; ++i) cp[13 + i] = Lo[i];
+    }
+    CK(cudaMemcpyAsync(c->gmm_comps.p, comps.data(), sizeof(double) * comps.size(), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->gmm_steps.p, steps.data(), sizeof(GmmStepTable) * steps.size(), cudaMemcpyHostToDevice, c->stream));
+    c->h2d_bytes += sizeof(double) * comps.size() + sizeof(GmmStepTable) * steps.size();
+    std::vector<double> pre0(size_t(K) * GMM_REC);
+    for (int k = 0; k < K; ++k) memcpy(&pre0[size_t(k) * GMM_REC], &comps[size_t(k) * GMM_COMP], sizeof(double) * GMM_REC);
+    CK(cudaMemcpyAsync(c->gmm_pre.p, pre0.data(), sizeof(double) * pre0.size(), cudaMemcpyHostToDevice, c->stream));
+    std::vector<double> sn;  // replay: the 3N sample normals of every waypoint, contiguous
+    if (mode == MCSIM_MODE_REPLAY) {
+        sn.resize(size_t(T) * 3 * N);
+        for (int t = 0; t < T; ++t) {
+            const size_t off = t == 0 ? 0 : 3 * N + size_t(t - 1) * (per_step + 3 * N) + per_step;
+            memcpy(&sn[size_t(t) * 3 * N], g->normals + off, sizeof(double) * 3 * N);
+        }
+        CK(c->gmm_normals.reserve(sizeof(double) * sn.size()));
+        CK(c->gmm_counts.reserve(sizeof(int) * size_t(T) * K));
+        CK(cudaMemcpyAsync(c->gmm_normals.p, sn.data(), sizeof(double) * sn.size(), cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->gmm_counts.p, g->counts, sizeof(int) * size_t(T) * K, cudaMemcpyHostToDevice, c->stream));
+        c->h2d_bytes += sizeof(double) * sn.size() + sizeof(int) * size_t(T) * K;
+    }
+    GmmLaunch a;
+    gmm_fill_launch(c, a, K, T, L, N, mc->seed, unsigned(mc->rollout_offset));
+    a.Q = mc->Q;
+    for (int l = 0; l < L; ++l) { a.lx[l] = mc->landmarks[l]; a.ly[l] = mc->landmarks[L + l]; }
+    a.rec_pre = (double*)c->gmm_pre.p;
+    a.rec_post = (double*)c->gmm_post.p;
+    a.do_ekf = 1;
+    a.counts_replay = (const int*)c->gmm_counts.p;
+    CK(cudaEventRecord(c->ev0, c->stream));
+    for (int t = 0; t < T; ++t) {
+        a.t = t;
+        a.normals = mode == MCSIM_MODE_REPLAY ? (const double*)c->gmm_normals.p + size_t(t) * 3 * N : nullptr;
+        rc = gmm_launch_waypoint(c, a, mode);
+        if (rc) return rc;
+    }
+    CK(cudaEventRecord(c->ev1, c->stream));
+    std::vector<double> prob(T);
+    int deg = 0;
+    CK(cudaMemcpyAsync(prob.data(), c->gmm_prob.p, sizeof(double) * T, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(&deg, c->gmm_deg.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    c->d2h_bytes += sizeof(double) * T + sizeof(int);
+    if (r->gmm_pre) { CK(cudaMemcpyAsync(r->gmm_pre, c->gmm_pre.p, sizeof(double) * size_t(T) * K * GMM_REC, cudaMemcpyDeviceToHost, c->stream)); c->d2h_bytes += sizeof(double) * size_t(T) * K * GMM_REC; }
+    if (r->gmm_post) { CK(cudaMemcpyAsync(r->gmm_post, c->gmm_post.p, sizeof(double) * K * GMM_REC, cudaMemcpyDeviceToHost, c->stream)); c->d2h_bytes += sizeof(double) * K * GMM_REC; }
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaEventElapsedTime(&r->kernel_ms, c->ev0, c->ev1));
+    // P = 1 - prod_t (1 - p_t)  (MCSimulator.h:848-856)
+    double free_all = 1.0;
+    for (int t = 0; t < T; ++t) free_all *= (1.0 - prob[t]);
+    r->P = 1.0 - free_all;
+    r->degenerate = deg;
+    if (r->probabilities) memcpy(r->probabilities, prob.data(), sizeof(double) * T);
+    return MCSIM_OK;
+}
+
+extern "C" int mcsim_cuda_gmm_truncate(mcsim_cuda_ctx* c, const mcsim_gmm_truncate_params* p, mcsim_gmm_truncate_result* r) {
+    if (!c || !p || !r) return fail(MCSIM_ERR_ARG, "gmm_truncate: NULL argument");
+    if (!c->scene_set) return fail(MCSIM_ERR_ARG, "gmm_truncate: mcsim_cuda_set_scene has not been called");
+    const int K = p->K;
+    const uint64_t N = p->n_samples;
+    if (K < 1 || K > MCSIM_MAX_GAUSSIANS || !p->weights || !p->means || !p->covs) return fail(MCSIM_ERR_ARG, "gmm_truncate: bad mixture");
+    if (p->mode == MCSIM_MODE_REPLAY && (!p->counts || !p->normals)) return fail(MCSIM_ERR_ARG, "gmm_truncate: replay mode needs counts and normals");
+    if (p->mode != MCSIM_MODE_REPLAY && p->mode != MCSIM_MODE_PHILOX) return fail(MCSIM_ERR_ARG, "gmm_truncate: unknown mode %d", p->mode);
+    CK(cudaSetDevice(c->device));
+    int rc = gmm_reserve(c, 1, K);
+    if (rc) return rc;
+    std::vector<double> comps(size_t(K) * GMM_COMP);
+    uint64_t total = 0;
+    for (int k = 0; k < K; ++k) {
+        double* cp = &comps[size_t(k) * GMM_COMP];
+        cp[0] = p->weights[k];
+        for (int i = 0; i < 3; ++i) cp[1 + i] = p->means[k * 3 + i];
+        for (int i = 0; i < 9; ++i) cp[4 + i] = p->covs[k * 9 + i];
+        if (!gmm_chol3(cp + 4, cp + 13)) return fail(MCSIM_ERR_ARG, "gmm_truncate: covariance of component %d is not positive definite", k);
+        if (p->mode == MCSIM_MODE_REPLAY) { if (p->counts[k] < 0) return fail(MCSIM_ERR_ARG, "gmm_truncate: negative count"); total += uint64_t(p->counts[k]); }
+    }
+    if (p->mode == MCSIM_MODE_REPLAY && total != N) return fail(MCSIM_ERR_DRAWS, "gmm_truncate: counts sum to %llu, n_samples is %llu", (unsigned long long)total, (unsigned long long)N);
+    CK(cudaMemcpyAsync(c->gmm_comps.p, comps.data(), sizeof(double) * comps.size(), cudaMemcpyHostToDevice, c->stream));
+    if (p->mode == MCSIM_MODE_REPLAY) {
+        CK(c->gmm_normals.reserve(sizeof(double) * 3 * (N ? N : 1)));
+        CK(c->gmm_counts.reserve(sizeof(int) * K));
+        if (N) CK(cudaMemcpyAsync(c->gmm_normals.p, p->normals, sizeof(double) * 3 * N, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->gmm_counts.p, p->counts, sizeof(int) * K, cudaMemcpyHostToDevice, c->stream));
+    }
+    GmmLaunch a;
+    gmm_fill_launch(c, a, K, 1, 0, N, p->seed, unsigned(p->stream_id));
+    a.t = 0;
+    a.counts_replay = (const int*)c->gmm_counts.p;
+    a.normals = (const double*)c->gmm_normals.p;
+    a.trunc_out = (double*)c->gmm_trunc.p;
+    a.n_out = (unsigned long long*)c->gmm_nout.p;
+    a.do_ekf = 0;
+    rc = gmm_launch_waypoint(c, a, p->mode);
+    if (rc) return rc;
+    std::vector<double> out(size_t(K) * GMM_REC);
+    unsigned long long nout[2 * MCSIM_MAX_GAUSSIANS];
+    double prob = 0;
+    int deg = 0;
+    CK(cudaMemcpyAsync(out.data(), c->gmm_trunc.p, sizeof(double) * out.size(), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(nout, c->gmm_nout.p, sizeof(unsigned long long) * 2 * K, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(&prob, c->gmm_prob.p, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(&deg, c->gmm_deg.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    memset(r, 0, sizeof(*r));
+    for (int k = 0; k < K; ++k) {
+        r->weights[k] = out[size_t(k) * GMM_REC];
+        for (int i = 0; i < 3; ++i) r->means[k * 3 + i] = out[size_t(k) * GMM_REC + 1 + i];
+        for (int i = 0; i < 9; ++i) r->covs[k * 9 + i] = out[size_t(k) * GMM_REC + 4 + i];
+        r->n_coll[k] = nout[k];
+        r->n_free[k] = nout[K + k];
+    }
+    r->p_collision = prob;
+    r->degenerate = deg;
+    return MCSIM_OK;
+}
+
+/* bytes the last *_run call copied host->device and device->host (bench.py's e2e accounting) */
+extern "C" void mcsim_cuda_io_bytes(mcsim_cuda_ctx* c, uint64_t* h2d, uint64_t* d2h) {
+    if (h2d) *h2d = c ? c->h2d_bytes : 0;
+    if (d2h) *d2h = c ? c->d2h_bytes : 0;
 }

@@ -103,10 +103,10 @@ def lib():
         L.mcsim_cuda_mc_counters.argtypes = [vp]
         L.mcsim_cuda_mc_counters.restype = vp
         L.mcsim_host_thread.argtypes = [C.POINTER(McParams), _dp, C.c_size_t, _dp, _dp, _dp, _dp, _dp, _dp]
-        for name, at in (("mcsim_cuda_gmm_truncate", [vp, C.POINTER(GmmTruncateParams), C.POINTER(GmmTruncateResult)]),
-                         ("mcsim_cuda_gmm_run", [vp, C.POINTER(McParams), C.POINTER(GmmRunParams), C.POINTER(GmmRunResult)])):
-            if hasattr(L, name):
-                getattr(L, name).argtypes = at
+        L.mcsim_cuda_gmm_truncate.argtypes = [vp, C.POINTER(GmmTruncateParams), C.POINTER(GmmTruncateResult)]
+        L.mcsim_cuda_gmm_run.argtypes = [vp, C.POINTER(McParams), C.POINTER(GmmRunParams), C.POINTER(GmmRunResult)]
+        L.mcsim_cuda_io_bytes.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.mcsim_cuda_io_bytes.restype = None
         _lib = L
     return _lib
 
@@ -265,3 +265,62 @@ class Context:
         out.update(hits=int(r.hits), near_contact=int(r.near_contact), executed_steps=int(r.executed_steps),
                    pair_tests=int(r.pair_tests))
         return out
+
+    def io_bytes(self):
+        """(host->device, device->host) bytes copied by the last *_run call."""
+        a, b = C.c_uint64(), C.c_uint64()
+        lib().mcsim_cuda_io_bytes(self._h, C.byref(a), C.byref(b))
+        return int(a.value), int(b.value)
+
+    def gmm_run(self, plan, K, n_samples, mode=MODE_PHILOX, seed=0x5AFEC0DE, stream_id=0, draws=None, counts=None,
+                record=False):
+        """runGMMEstimation of one plan (MCSimulator.h:354-358 -> the GMM branch of EKF_GaussProp).
+        Replay mode: draws = the reference's normal stream of the run, counts[T, K] = multinomial counts."""
+        p, keep = make_mc_params(plan, mode=mode, seed=seed, rollout_offset=stream_id)
+        T = int(p.T)
+        g = GmmRunParams()
+        g.K, g.n_samples = int(K), int(n_samples)
+        if draws is not None:
+            dr = np.ascontiguousarray(draws, dtype=np.float64)
+            keep.append(dr)
+            g.normals, g.n_normals = dptr(dr), dr.size
+        if counts is not None:
+            cn = np.ascontiguousarray(counts, dtype=np.int32)
+            keep.append(cn)
+            g.counts = cn.ctypes.data_as(C.POINTER(C.c_int))
+        r = GmmRunResult()
+        out = dict(probabilities=np.zeros(T))
+        r.probabilities = dptr(out["probabilities"])
+        if record:
+            out["gmm_pre"] = np.zeros((T, int(K), 13))
+            out["gmm_post"] = np.zeros((int(K), 13))
+            r.gmm_pre, r.gmm_post = dptr(out["gmm_pre"]), dptr(out["gmm_post"])
+        check(lib().mcsim_cuda_gmm_run(self._h, C.byref(p), C.byref(g), C.byref(r)))
+        out.update(P=float(r.P), degenerate=int(r.degenerate), kernel_ms=float(r.kernel_ms))
+        return out
+
+    def gmm_truncate(self, weights, means, covs, n_samples, mode=MODE_PHILOX, counts=None, normals=None,
+                     seed=0x5AFEC0DE, stream_id=0):
+        """One truncateGMM (MCSimulator.h:570-642) of the mixture (weights[K], means[K,3], covs[K,3,3])."""
+        w = np.ascontiguousarray(weights, dtype=np.float64)
+        m = np.ascontiguousarray(means, dtype=np.float64).reshape(-1, 3)
+        cv = np.ascontiguousarray(covs, dtype=np.float64).reshape(-1, 9)
+        K = w.shape[0]
+        p = GmmTruncateParams()
+        p.K, p.weights, p.means, p.covs = K, dptr(w), dptr(m), dptr(cv)
+        p.n_samples, p.mode, p.seed, p.stream_id = int(n_samples), int(mode), int(seed), int(stream_id)
+        keep = [w, m, cv]
+        if counts is not None:
+            cn = np.ascontiguousarray(counts, dtype=np.int32)
+            keep.append(cn)
+            p.counts = cn.ctypes.data_as(C.POINTER(C.c_int))
+        if normals is not None:
+            nz = np.ascontiguousarray(normals, dtype=np.float64)
+            keep.append(nz)
+            p.normals = dptr(nz)
+        r = GmmTruncateResult()
+        check(lib().mcsim_cuda_gmm_truncate(self._h, C.byref(p), C.byref(r)))
+        return dict(weights=np.array(r.weights[:K]), means=np.array(r.means[:3 * K]).reshape(K, 3),
+                    covs=np.array(r.covs[:9 * K]).reshape(K, 3, 3), n_coll=np.array(r.n_coll[:K], dtype=np.uint64),
+                    n_free=np.array(r.n_free[:K], dtype=np.uint64), p_collision=float(r.p_collision),
+                    degenerate=int(r.degenerate))

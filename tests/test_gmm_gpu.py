@@ -1,0 +1,113 @@
+"""GPU parity tests of the GMM mode (sample -> collide -> moment refit per waypoint), through the C ABI.
+
+Deterministic (replay) mode: the reference's own runGMMEstimation() (oracle/_ref, golden vectors in
+tests/golden/gmm_replay_*.npz: injected normals + the multinomial counts it drew) must be reproduced:
+per-waypoint colliding fractions exactly (the replay-mode SAT is FP64, so the flags are the reference's),
+mixture weights / means / covariances and P(collision) within 1e-4 relative (BASELINE.json north_star).
+Philox mode: P inside the spread of the reference's own run-to-run distribution; statistical only."""
+import numpy as np
+import pytest
+
+from conftest import golden
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-4  # north_star: GMM weights/means/covariances and P(collision) within 1e-4 relative
+
+
+def _assert_mixture_close(ours, ref, what):
+    # weights and means: relative to max(|ref|, 1) (angles and coordinates near 0 have no relative scale);
+    # covariances: relative to the component's largest variance
+    np.testing.assert_allclose(ours[..., 0], ref[..., 0], rtol=RTOL, atol=RTOL, err_msg=what + " weights")
+    np.testing.assert_allclose(ours[..., 1:4], ref[..., 1:4], rtol=RTOL, atol=RTOL, err_msg=what + " means")
+    scale = np.abs(ref[..., 4:]).max(axis=-1, keepdims=True)
+    assert np.max(np.abs(ours[..., 4:] - ref[..., 4:]) / scale) < RTOL, what + " covariances"
+
+
+@pytest.mark.parametrize("K", [1, 3])
+def test_gmm_replay_matches_reference_golden(ctx, plan, scenes, K):
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    g = golden("gmm_replay_pr2test2_K%d.npz" % K)
+    ctx.set_scene(scenes["pr2test2"]["boxes"], scenes["pr2test2"]["hulls"])
+    out = ctx.gmm_run(plan, K, int(g["n_samples"]), mode=abi.MODE_REPLAY, draws=g["draws"], counts=g["gmm_counts"], record=True)
+    assert out["degenerate"] == 0
+    # colliding fraction per waypoint: exact (integer count / N)
+    np.testing.assert_array_equal(out["probabilities"], g["probabilities"])
+    assert abs(out["P"] - float(g["P"])) <= RTOL * float(g["P"])
+    _assert_mixture_close(out["gmm_pre"], g["gmm_pre"], "pre-truncation mixtures")
+    _assert_mixture_close(out["gmm_post"], g["gmm_post"], "final mixture")
+
+
+def test_gmm_replay_vs_live_reference(ctx, plan, scenes):
+    """Fresh draws, other K / N (incl. a component count that is not a warp multiple), reference run live."""
+    import oracle_ref
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    if not oracle_ref.available():
+        pytest.skip("oracle/_ref not built")
+    T = plan["trajectory"].shape[1]
+    sc = scenes["pr2test2"]
+    ctx.set_scene(sc["boxes"], sc["hulls"])
+    for seed, K, N in ((11, 2, 777), (12, 5, 1501)):
+        draws = np.random.Generator(np.random.PCG64(seed)).standard_normal(3 * N * T + 11 * (T - 1))
+        try:
+            ref = oracle_ref.gmm_run(plan, sc["boxes"], sc["hulls"], K, N, draws=draws, multinomial_seed=seed)
+        except RuntimeError:
+            continue  # the reference throws when a component loses all its samples
+        out = ctx.gmm_run(plan, K, N, mode=abi.MODE_REPLAY, draws=draws, counts=ref["gmm_counts"], record=True)
+        np.testing.assert_array_equal(out["probabilities"], ref["probabilities"])
+        assert abs(out["P"] - ref["P"]) <= RTOL * ref["P"]
+        _assert_mixture_close(out["gmm_pre"], ref["gmm_pre"], "pre-truncation mixtures K=%d" % K)
+
+
+def test_gmm_truncate_single_shot_matches_first_waypoint(ctx, plan, scenes):
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    g = golden("gmm_replay_pr2test2_K3.npz")
+    N, K = int(g["n_samples"]), 3
+    ctx.set_scene(scenes["pr2test2"]["boxes"], scenes["pr2test2"]["hulls"])
+    pre = g["gmm_pre"][0]
+    out = ctx.gmm_truncate(pre[:, 0], pre[:, 1:4], pre[:, 4:].reshape(K, 3, 3), N, mode=abi.MODE_REPLAY,
+                           counts=g["gmm_counts"][0], normals=g["draws"][:3 * N])
+    assert out["p_collision"] == g["probabilities"][0]
+    assert int(out["n_coll"].sum() + out["n_free"].sum()) == N
+    np.testing.assert_array_equal(out["n_coll"] + out["n_free"], g["gmm_counts"][0].astype(np.uint64))
+    np.testing.assert_allclose(out["weights"], out["n_free"] / out["n_free"].sum(), rtol=1e-15)
+
+
+def test_gmm_truncate_rejects_bad_counts(ctx, scenes):
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    ctx.set_scene(scenes["pr2test2"]["boxes"], scenes["pr2test2"]["hulls"])
+    with pytest.raises(abi.McsimCudaError):
+        ctx.gmm_truncate([1.0], [[0, 0, 0]], [np.eye(3) * 1e-3], 10, mode=abi.MODE_REPLAY, counts=[9], normals=np.zeros(30))
+    with pytest.raises(abi.McsimCudaError):
+        ctx.gmm_truncate([1.0], [[0, 0, 0]], [-np.eye(3)], 10)
+
+
+def test_gmm_philox_statistics(ctx, plan, scenes):
+    """Philox mode: the estimate is a random variable (one shared real-robot thread per run, exactly as in the
+    reference); its mean over trajectories must agree with the reference's own run-to-run mean."""
+    import oracle_ref
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    sc = scenes["pr2test2"]
+    ctx.set_scene(sc["boxes"], sc["hulls"])
+    K, N, R = 3, 4000, 48
+    ours = np.array([ctx.gmm_run(plan, K, N, mode=abi.MODE_PHILOX, stream_id=i)["P"] for i in range(R)])
+    # same call twice: bit-identical counts -> identical P up to FP64 atomics order
+    again = ctx.gmm_run(plan, K, N, mode=abi.MODE_PHILOX, stream_id=0)["P"]
+    assert abs(again - ours[0]) < 1e-9
+    if not oracle_ref.available():
+        pytest.skip("oracle/_ref not built")
+    ref = []
+    for s in range(R):
+        try:
+            ref.append(oracle_ref.gmm_run(plan, sc["boxes"], sc["hulls"], K, N, mt_seed=s, multinomial_seed=s, record=False)["P"])
+        except RuntimeError:
+            pass
+    ref = np.array(ref)
+    half = 2.576 * np.sqrt(ours.var(ddof=1) / len(ours) + ref.var(ddof=1) / len(ref))
+    print("GMM philox: ours mean %.4f (std %.4f), reference mean %.4f (std %.4f), 99%% half-width %.4f" %
+          (ours.mean(), ours.std(ddof=1), ref.mean(), ref.std(ddof=1), half))
+    assert abs(ours.mean() - ref.mean()) < half
