@@ -102,8 +102,9 @@ typedef struct {
     const double* applied;       /* 3 x (T-1) component-major noisy commands u~_t of the shared
                                     real-robot thread (host-computed, see mcsim_host_thread) */
     const double* z0;            /* 3 x n_rollouts standard normals, rollout-major (the order
-                                    mvnrnd fills them: glue_mvnrnd_meat.hpp:89-147) or NULL in
-                                    PHILOX mode */
+                                    mvnrnd fills them: glue_mvnrnd_meat.hpp:89-147); NULL: every
+                                    rollout draws its start pose from its own Philox block
+                                    (always so in PHILOX mode) */
     double near_eps;             /* |clearance| < near_eps marks a near-contact pose (audit only) */
 } mcsim_mc_params;
 
@@ -152,6 +153,12 @@ void* mcsim_cuda_mc_counters(mcsim_cuda_ctx* ctx);
 int mcsim_host_thread(const mcsim_mc_params* p, const double* normals, size_t n_normals,
                       double* applied_noisy, double* applied, double* real_path,
                       double* mu_path, double* cov_path, double* obs);
+
+/* Standard normals of a Philox-driven host thread: per_step x (T-1) doubles in consumption order,
+ * counter = (step, stream_id, block, PURPOSE_GMM_HOST), key = seed; Box-Muller in FP64.  Used when
+ * the shared real-robot thread is not replayed from a draws file (plugin modes "shared" and the
+ * Philox GMM mode). */
+int mcsim_host_normals(uint64_t seed, uint32_t stream_id, int T, int per_step, double* out);
 
 /* ---- GMM truncation (moment matching) ---------------------------------------------------- */
 typedef struct {

@@ -6,6 +6,9 @@ The directory name carries hyphens (it is the one the build contract names); imp
 `pcoll_b200` through the shim module at the repository root.
 """
 from . import cuda_abi  # noqa: F401
+from . import plugin  # noqa: F401
 from .inputs import default_params, load_plan_json, plan_from_pickles, py2_str  # noqa: F401
+from .plugin import MCModule, McsimError, push_parameters  # noqa: F401
 
-__all__ = ["cuda_abi", "default_params", "load_plan_json", "plan_from_pickles", "py2_str"]
+__all__ = ["cuda_abi", "plugin", "MCModule", "McsimError", "push_parameters", "default_params", "load_plan_json",
+           "plan_from_pickles", "py2_str"]

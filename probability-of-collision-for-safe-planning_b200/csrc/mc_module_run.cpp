@@ -1,0 +1,261 @@
+// mc_module_run.cpp -- the run* commands and the run-control additions of MCModule (see mc_module.h).
+#include <cmath>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+#include <stdexcept>
+
+#include "mc_module.h"
+
+namespace mcsim {
+namespace {
+
+void cuda_check(int rc, const char* what) {
+    if (rc != MCSIM_OK) throw std::runtime_error(std::string(what) + ": " + mcsim_cuda_last_error());
+}
+
+template <typename T>
+std::vector<T> read_binary(const std::string& path) {
+    std::ifstream f(path, std::ios::binary | std::ios::ate);
+    if (!f) throw std::runtime_error("cannot open " + path);
+    const std::streamsize bytes = f.tellg();
+    if (bytes < 0 || bytes % std::streamsize(sizeof(T)) != 0) throw std::runtime_error(path + ": size is not a multiple of the element size");
+    std::vector<T> v(size_t(bytes) / sizeof(T));
+    f.seekg(0);
+    if (bytes && !f.read(reinterpret_cast<char*>(v.data()), bytes)) throw std::runtime_error("short read on " + path);
+    return v;
+}
+
+}  // namespace
+
+void MCModule::fill_params(mcsim_mc_params& p) const {
+    if (!ctx_) throw std::runtime_error("this module was created without a CUDA device (device < 0): run commands are unavailable, there is no CPU fallback");
+    if (alphas_.size() < 4) throw std::runtime_error("setAlphas has not been sent");
+    if (path_length_ < 1 || trajectory_.size() != size_t(3) * path_length_) throw std::runtime_error("setPathLength / setTrajectory have not been sent");
+    if (odometry_.size() != size_t(3) * (path_length_ - 1)) throw std::runtime_error("setOdometry has not been sent (or was sent before a different setPathLength)");
+    if (landmarks_.size() != size_t(2) * num_landmarks_) throw std::runtime_error("setNumLandmarks / setLandmarks have not been sent");
+    if (!cov0_set_) throw std::runtime_error("setInitialCovariance has not been sent");
+    if (scene_.n_hulls() < 1) throw std::runtime_error("no collision geometry: create the module with a scene, or send setScene / setGeometry");
+    std::memset(&p, 0, sizeof(p));
+    p.T = path_length_;
+    p.trajectory = trajectory_.data();
+    p.odometry = odometry_.data();
+    for (int i = 0; i < 4; ++i) p.alphas[i] = alphas_[i];
+    p.Q = Q_;
+    p.n_landmarks = num_landmarks_;
+    p.landmarks = landmarks_.data();
+    std::memcpy(p.cov0, cov0_, sizeof(cov0_));
+    p.estimator = estimator_;
+    p.early_exit = early_exit_;
+    p.seed = seed_;
+    p.near_eps = 1e-4;
+}
+
+// mcsimplugin.cpp:75-81 -> MCSimulator::runSimulation (MCSimulator.h:361-365): returns P(collision) as text
+bool MCModule::runSimulation(std::ostream& sout, std::istream&) {
+    mcsim_mc_params p;
+    fill_params(p);
+    const int T = p.T, L = p.n_landmarks;
+    const uint64_t N = uint64_t(num_particles_);
+    p.n_rollouts = N;
+    std::vector<double> applied_noisy(size_t(3) * (T > 1 ? T - 1 : 1));
+    if (mode_ == Mode::kPhilox) {
+        p.mode = MCSIM_MODE_PHILOX;
+        p.rollout_offset = rollout_offset_ + run_index_ * N;
+    } else {
+        // one shared real-robot thread on the host (FP64), replayed by every rollout
+        const size_t per_step = size_t(3 + L), need_host = per_step * size_t(T - 1);
+        std::vector<double> hn;
+        const double* host_normals = nullptr;
+        if (mode_ == Mode::kDeterministic) {
+            if (draws_.size() < 3 * N + need_host)
+                throw std::runtime_error("runSimulation: deterministic mode needs " + std::to_string(3 * N + need_host) + " draws, " + std::to_string(draws_.size()) + " loaded");
+            p.z0 = draws_.data();            // 3N particle normals first (initParticles), then 3 + L per step
+            host_normals = draws_.data() + 3 * N;
+            p.rollout_offset = rollout_offset_;
+        } else {
+            hn.resize(need_host ? need_host : 1);
+            if (T > 1) cuda_check(mcsim_host_normals(seed_, uint32_t(run_index_), T, int(per_step), hn.data()), "mcsim_host_normals");
+            host_normals = hn.data();
+            p.rollout_offset = rollout_offset_ + run_index_ * N;  // fresh particles every run
+        }
+        if (T > 1) {
+            const int rc = mcsim_host_thread(&p, host_normals, need_host, applied_noisy.data(), nullptr, nullptr, nullptr, nullptr, nullptr);
+            if (rc) throw std::runtime_error("mcsim_host_thread failed (" + std::to_string(rc) + ")");
+        }
+        p.mode = MCSIM_MODE_REPLAY;
+        p.applied = applied_noisy.data();
+    }
+    mcsim_mc_result r;
+    std::memset(&r, 0, sizeof(r));
+    first_hit_hist_.assign(size_t(T), 0);
+    r.first_hit_hist = first_hit_hist_.data();
+    cuda_check(mcsim_cuda_mc_run(ctx_, &p, &r), "mcsim_cuda_mc_run");
+    ++run_index_;
+    last_hits_ = r.hits; last_n_ = N; last_steps_ = r.executed_steps; last_tests_ = r.pair_tests; last_kernel_ms_ = r.kernel_ms;
+    last_degenerate_ = 0;
+    // getCollisionProportion (MCSimulator.h:324-330): nonzeros / (1.0 * N); N = 0 gives NaN there as well
+    const double collprop = double(r.hits) / (1.0 * double(N));
+    sout << collprop;  // default ostream formatting, 6 significant digits (mcsimplugin.cpp:79)
+    return true;
+}
+
+// mcsimplugin.cpp:66-72 -> MCSimulator::runGMMEstimation (MCSimulator.h:354-358)
+bool MCModule::runGMMEstimation(std::ostream& sout, std::istream&) {
+    mcsim_mc_params p;
+    fill_params(p);
+    if (num_gaussians_ < 1) throw std::runtime_error("setNumGaussians has not been sent");
+    if (num_gmm_samples_ < 1) throw std::runtime_error("setNumGMMSamples has not been sent");
+    const int T = p.T, K = num_gaussians_;
+    mcsim_gmm_run_params g;
+    std::memset(&g, 0, sizeof(g));
+    g.K = K;
+    g.n_samples = uint64_t(num_gmm_samples_);
+    if (mode_ == Mode::kDeterministic) {
+        if (gmm_counts_.size() != size_t(T) * K) throw std::runtime_error("runGMMEstimation: deterministic mode needs T x K multinomial counts (setGMMCounts / setGMMCountsFile)");
+        p.mode = MCSIM_MODE_REPLAY;
+        g.normals = draws_.data();
+        g.n_normals = draws_.size();
+        g.counts = gmm_counts_.data();
+    } else {
+        p.mode = MCSIM_MODE_PHILOX;
+        p.rollout_offset = rollout_offset_ + run_index_;  // Philox subsequence of this run
+    }
+    probabilities_.assign(size_t(T), 0.0);
+    gmm_post_.assign(size_t(K) * 13, 0.0);
+    gmm_post_K_ = K;
+    mcsim_gmm_run_result r;
+    std::memset(&r, 0, sizeof(r));
+    r.probabilities = probabilities_.data();
+    r.gmm_post = gmm_post_.data();
+    cuda_check(mcsim_cuda_gmm_run(ctx_, &p, &g, &r), "mcsim_cuda_gmm_run");
+    ++run_index_;
+    last_kernel_ms_ = r.kernel_ms;
+    last_degenerate_ = r.degenerate;
+    last_n_ = g.n_samples; last_hits_ = 0; last_steps_ = uint64_t(T) * g.n_samples; last_tests_ = 0;
+    sout << r.P;
+    return true;
+}
+
+// ---- additions ---------------------------------------------------------------------------------------------------
+bool MCModule::setSeed(std::ostream&, std::istream& sinput) {
+    unsigned long long s;
+    if (!(sinput >> s)) throw std::runtime_error("setSeed: an unsigned integer expected");
+    seed_ = s;
+    run_index_ = 0;
+    return true;
+}
+
+bool MCModule::setMode(std::ostream&, std::istream& sinput) {
+    std::string m;
+    sinput >> m;
+    if (m == "shared") mode_ = Mode::kShared;
+    else if (m == "philox") mode_ = Mode::kPhilox;
+    else if (m == "deterministic") mode_ = Mode::kDeterministic;
+    else throw std::runtime_error("setMode: shared | philox | deterministic expected, got '" + m + "'");
+    return true;
+}
+
+bool MCModule::setDrawsFile(std::ostream&, std::istream& sinput) {
+    std::string path;
+    if (!(sinput >> path)) throw std::runtime_error("setDrawsFile: a path expected");
+    draws_ = read_binary<double>(path);
+    return true;
+}
+
+bool MCModule::setDraws(std::ostream&, std::istream& sinput) {
+    size_t n;
+    if (!(sinput >> n)) throw std::runtime_error("setDraws: a count expected");
+    draws_.resize(n);
+    for (size_t i = 0; i < n; ++i) if (!(sinput >> draws_[i])) throw std::runtime_error("setDraws: fewer numbers than announced");
+    return true;
+}
+
+bool MCModule::setGMMCountsFile(std::ostream&, std::istream& sinput) {
+    std::string path;
+    if (!(sinput >> path)) throw std::runtime_error("setGMMCountsFile: a path expected");
+    gmm_counts_ = read_binary<int>(path);
+    return true;
+}
+
+bool MCModule::setGMMCounts(std::ostream&, std::istream& sinput) {
+    size_t n;
+    if (!(sinput >> n)) throw std::runtime_error("setGMMCounts: a count expected");
+    gmm_counts_.resize(n);
+    for (size_t i = 0; i < n; ++i) if (!(sinput >> gmm_counts_[i])) throw std::runtime_error("setGMMCounts: fewer numbers than announced");
+    return true;
+}
+
+bool MCModule::setEarlyExit(std::ostream&, std::istream& sinput) {
+    int v;
+    if (!(sinput >> v)) throw std::runtime_error("setEarlyExit: 0 or 1 expected");
+    early_exit_ = v != 0;
+    return true;
+}
+
+bool MCModule::setEstimator(std::ostream&, std::istream& sinput) {
+    std::string m;
+    sinput >> m;
+    if (m == "reference") estimator_ = MCSIM_EST_REFERENCE;
+    else if (m == "closedloop") estimator_ = MCSIM_EST_CLOSEDLOOP;
+    else throw std::runtime_error("setEstimator: reference | closedloop expected");
+    return true;
+}
+
+bool MCModule::setRolloutOffset(std::ostream&, std::istream& sinput) {
+    unsigned long long v;
+    if (!(sinput >> v)) throw std::runtime_error("setRolloutOffset: an unsigned integer expected");
+    rollout_offset_ = v;
+    return true;
+}
+
+bool MCModule::setGeometry(std::ostream&, std::istream& sinput) {
+    int nb, nh;
+    if (!(sinput >> nb >> nh) || nb < 0 || nh < 1) throw std::runtime_error("setGeometry: <n_boxes> <n_hulls> expected");
+    Scene sc;
+    sc.boxes.resize(size_t(nb) * 8);
+    sc.hulls.resize(size_t(nh) * 8);
+    for (auto& v : sc.boxes) if (!(sinput >> v)) throw std::runtime_error("setGeometry: too few numbers");
+    for (auto& v : sc.hulls) if (!(sinput >> v)) throw std::runtime_error("setGeometry: too few numbers");
+    scene_ = sc;
+    upload_scene();
+    return true;
+}
+
+bool MCModule::setScene(std::ostream&, std::istream& sinput) {
+    std::string path, d;
+    if (!(sinput >> path)) throw std::runtime_error("setScene: a path expected");
+    std::vector<std::string> dirs;
+    while (sinput >> d) dirs.push_back(d);
+    scene_ = load_scene_xml(path, dirs);
+    if (scene_.n_hulls() < 1) throw std::runtime_error("setScene: " + path + " has no robot geometry");
+    upload_scene();
+    return true;
+}
+
+bool MCModule::getWaypointProbabilities(std::ostream& sout, std::istream&) {
+    sout.precision(17);
+    for (size_t i = 0; i < probabilities_.size(); ++i) sout << (i ? " " : "") << probabilities_[i];
+    return true;
+}
+
+bool MCModule::getFirstHitHistogram(std::ostream& sout, std::istream&) {
+    for (size_t i = 0; i < first_hit_hist_.size(); ++i) sout << (i ? " " : "") << first_hit_hist_[i];
+    return true;
+}
+
+bool MCModule::getGMM(std::ostream& sout, std::istream&) {
+    sout.precision(17);
+    for (int g = 0; g < gmm_post_K_; ++g) {
+        for (int k = 0; k < 13; ++k) sout << (k ? " " : "") << gmm_post_[size_t(g) * 13 + k];
+        sout << "\n";
+    }
+    return true;
+}
+
+bool MCModule::getStats(std::ostream& sout, std::istream&) {
+    sout << last_hits_ << " " << last_n_ << " " << last_steps_ << " " << last_tests_ << " " << last_kernel_ms_ << " " << last_degenerate_;
+    return true;
+}
+
+}  // namespace mcsim

@@ -73,8 +73,11 @@ __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
     for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
         const unsigned long long id = a.offset + i;
         // ---- initial particle: x0 = mu0 + L z (initParticles, glue_mvnrnd_meat.hpp:89-147)
+        // injected draws (replay with a z0 table) or the rollout's own Philox block (Philox mode, and the
+        // "shared" mode of the plugin: replayed host thread + device-generated particles, z0 == NULL)
         float z[3] = {0.f, 0.f, 0.f};
-        if (MODE == MCSIM_MODE_PHILOX) {
+        const bool injected = (MODE == MCSIM_MODE_REPLAY) && a.z0 != nullptr;
+        if (!injected) {
             mcsim_rng::u32x4 c = {unsigned(id), unsigned(id >> 32), 0u, unsigned(mcsim_rng::PURPOSE_INIT)};
             c = mcsim_rng::philox4x32_10(c, a.k0, a.k1);
             float z3;
@@ -82,12 +85,16 @@ __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
             mcsim_rng::box_muller(c.z, c.w, z[2], z3);
         }
         float p[3];
+        double th = 0.0;  // replay mode keeps the heading in FP64 (see below)
         if (MODE == MCSIM_MODE_REPLAY) {
             // FP64 for the start pose only (3 FMAs): the injected draws are FP64
-            const double z0 = a.z0[3 * i], z1 = a.z0[3 * i + 1], z2 = a.z0[3 * i + 2];
+            const double z0 = injected ? a.z0[3 * i] : double(z[0]);
+            const double z1 = injected ? a.z0[3 * i + 1] : double(z[1]);
+            const double z2 = injected ? a.z0[3 * i + 2] : double(z[2]);
             p[0] = float(c_mc.mu0d[0] + c_mc.chold[0] * z0);
             p[1] = float(c_mc.mu0d[1] + c_mc.chold[1] * z0 + c_mc.chold[2] * z1);
-            p[2] = float(c_mc.mu0d[2] + c_mc.chold[3] * z0 + c_mc.chold[4] * z1 + c_mc.chold[5] * z2);
+            th = c_mc.mu0d[2] + c_mc.chold[3] * z0 + c_mc.chold[4] * z1 + c_mc.chold[5] * z2;
+            p[2] = float(th);
         } else {
             p[0] = c_mc.mu0[0] + c_mc.chol[0] * z[0];
             p[1] = c_mc.mu0[1] + c_mc.chol[1] * z[0] + c_mc.chol[2] * z[1];
@@ -109,7 +116,6 @@ __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
         // Replay mode keeps the heading in FP64: theta is a running sum of angles near 2 pi, where an
         // FP32 state would lose 2.4e-7 rad per addition and, through trans * d(theta), ~2e-5 m over
         // 55 steps (measured); x and y stay FP32.  Only the reduced angle is rounded to FP32.
-        double th = (MODE == MCSIM_MODE_REPLAY) ? (c_mc.mu0d[2] + c_mc.chold[3] * a.z0[3 * i] + c_mc.chold[4] * a.z0[3 * i + 1] + c_mc.chold[5] * a.z0[3 * i + 2]) : 0.0;
         unsigned count = 0;
         int first = -1;
         for (int t = 0; t < T; ++t) {

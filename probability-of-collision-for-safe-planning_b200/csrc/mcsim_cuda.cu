@@ -369,14 +369,18 @@ extern "C" int mcsim_cuda_mc_run(mcsim_cuda_ctx* c, const mcsim_mc_params* p, mc
     if (!r) return fail(MCSIM_ERR_ARG, "mc_run: result is NULL");
     int rc = mcsim_cuda_mc_prepare(c, p);
     if (rc) return rc;
+    c->h2d_bytes = sizeof(McPlanConst) + sizeof(float) * size_t(p->T) * MC_PHILOX_STRIDE;
+    c->d2h_bytes = sizeof(unsigned long long) * (4 + p->T);
     const uint64_t n = p->n_rollouts;
     const int T = p->T;
     const double* d_z0 = nullptr;
     if (p->mode == MCSIM_MODE_REPLAY) {
-        if (!p->z0 && n) return fail(MCSIM_ERR_ARG, "mc_run: replay mode needs z0");
-        CK(c->z0.reserve(sizeof(double) * 3 * (n ? n : 1)));
-        if (n) CK(cudaMemcpyAsync(c->z0.p, p->z0, sizeof(double) * 3 * n, cudaMemcpyHostToDevice, c->stream));
-        d_z0 = (const double*)c->z0.p;
+        if (p->z0 && n) {  // injected particles; z0 == NULL: the kernel draws them from Philox
+            CK(c->z0.reserve(sizeof(double) * 3 * n));
+            CK(cudaMemcpyAsync(c->z0.p, p->z0, sizeof(double) * 3 * n, cudaMemcpyHostToDevice, c->stream));
+            c->h2d_bytes += sizeof(double) * 3 * n;
+            d_z0 = (const double*)c->z0.p;
+        }
     }
     unsigned* d_counts = nullptr;
     float *d_poses = nullptr, *d_clear = nullptr;
@@ -389,7 +393,7 @@ extern "C" int mcsim_cuda_mc_run(mcsim_cuda_ctx* c, const mcsim_mc_params* p, mc
     CK(cudaEventRecord(c->ev0, c->stream));
     if (n) { rc = mc_launch_impl(c, n, p->rollout_offset, d_z0, d_counts, d_poses, d_clear); if (rc) return rc; }
     CK(cudaEventRecord(c->ev1, c->stream));
-    if (d_counts) CK(cudaMemcpyAsync(r->counts, d_counts, sizeof(unsigned) * n, cudaMemcpyDeviceToHost, c->stream));
+    if (d_counts) { CK(cudaMemcpyAsync(r->counts, d_counts, sizeof(unsigned) * n, cudaMemcpyDeviceToHost, c->stream)); c->d2h_bytes += sizeof(unsigned) * n; }
     if (d_poses && r->poses) CK(cudaMemcpyAsync(r->poses, d_poses, sizeof(float) * 3 * T * n, cudaMemcpyDeviceToHost, c->stream));
     if (d_clear && r->clearance) CK(cudaMemcpyAsync(r->clearance, d_clear, sizeof(float) * T * n, cudaMemcpyDeviceToHost, c->stream));
     rc = mcsim_cuda_mc_collect(c, r);
@@ -400,8 +404,8 @@ extern "C" int mcsim_cuda_mc_run(mcsim_cuda_ctx* c, const mcsim_mc_params* p, mc
 
 // ---- GMM mode -----------------------------------------------------------------------------------
 // two standard normals from one Philox block, host side (the host thread of a Philox-mode GMM run)
-static void host_normals(uint64_t seed, unsigned stream_id, int T, int per_step, std::vector<double>& out) {
-    out.resize(size_t(T > 1 ? T - 1 : 0) * per_step);
+extern "C" int mcsim_host_normals(uint64_t seed, uint32_t stream_id, int T, int per_step, double* out) {
+    if (!out || T < 1 || per_step < 1) return MCSIM_ERR_ARG;
     for (int t = 0; t < T - 1; ++t) {
         for (int j = 0; j < per_step; j += 4) {
             mcsim_rng::u32x4 c = {unsigned(t), stream_id, unsigned(j >> 2), unsigned(mcsim_rng::PURPOSE_GMM_HOST)};
@@ -417,6 +421,11 @@ static void host_normals(uint64_t seed, unsigned stream_id, int T, int per_step,
             }
         }
     }
+    return MCSIM_OK;
+}
+static void host_normals(uint64_t seed, unsigned stream_id, int T, int per_step, std::vector<double>& out) {
+    out.resize(size_t(T > 1 ? T - 1 : 0) * per_step);
+    if (!out.empty()) mcsim_host_normals(seed, stream_id, T, per_step, out.data());
 }
 
 static int gmm_reserve(mcsim_cuda_ctx* c, int T, int K) {

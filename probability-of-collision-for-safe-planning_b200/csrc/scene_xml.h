@@ -1,0 +1,24 @@
+// scene_xml.h -- obstacle / robot prisms extracted from an OpenRAVE environment XML (see scene_xml.cpp).
+#ifndef MCSIM_SCENE_XML_H
+#define MCSIM_SCENE_XML_H
+
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace mcsim {
+
+struct Scene {
+    std::vector<double> boxes;  // n x 8: cx, cy, cos(yaw), sin(yaw), hx, hy, zlo, zhi   (world frame)
+    std::vector<double> hulls;  // m x 8: same layout in the robot frame, z absolute
+    double robot_pose[3] = {0, 0, 0};
+    bool has_robot = false;
+    int n_boxes() const { return int(boxes.size() / 8); }
+    int n_hulls() const { return int(hulls.size() / 8); }
+};
+
+// Throws std::runtime_error with a message naming the file / tag on any problem.
+Scene load_scene_xml(const std::string& env_path, const std::vector<std::string>& fixture_dirs);
+
+}  // namespace mcsim
+#endif

@@ -1,0 +1,101 @@
+"""GPU tests of the drop-in boundary: the MCSimulation.py command sequence against libmcsim.so, checked against the
+reference estimator's golden vectors (deterministic mode) and its run-to-run distribution (shared / philox modes)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLD, ROOT, golden
+
+pytestmark = pytest.mark.gpu
+
+
+def _module(plan, scene_xml_name, n, **kw):
+    import pcoll_b200
+    mod = pcoll_b200.MCModule(os.path.join(ROOT, "data", "scenes", scene_xml_name + ".env.xml"), device=0)
+    pcoll_b200.push_parameters(mod, plan, num_particles=n, **kw)
+    return mod
+
+
+@pytest.mark.parametrize("name", ["pr2test2", "pr2custom"])
+def test_run_simulation_deterministic_matches_reference_text(plan, name, tmp_path):
+    g = golden("mc_replay_%s.npz" % name)
+    N = g["counts"].shape[0]
+    mod = _module(plan, name, N)
+    f = tmp_path / "draws.f64"
+    g["draws"].astype("<f8").tofile(f)
+    mod.SendCommand("setMode deterministic")
+    mod.SendCommand("setDrawsFile %s" % f)
+    near = (np.abs(g["clearance"].astype(np.float64)) < 1e-4).any(axis=0)
+    for ee in (0, 1):
+        mod.SendCommand("setEarlyExit %d" % ee)
+        text = mod.SendCommand("runSimulation")
+        hits = int(mod.SendCommand("getStats").split()[0])
+        # bit-exact hit count unless a near-contact rollout flips (none does on the committed draws)
+        assert abs(hits - int((g["counts"] > 0).sum())) <= int(near.sum())
+        if hits == int((g["counts"] > 0).sum()):
+            assert text == "%g" % float(g["P"])          # `sout << collprop`: default ostream formatting
+        hist = np.array(mod.SendCommand("getFirstHitHistogram").split(), dtype=np.int64)
+        assert hist.sum() == hits and hist.shape[0] == plan["trajectory"].shape[1]
+    mod.close()
+
+
+@pytest.mark.parametrize("K", [1, 3])
+def test_run_gmm_estimation_deterministic_matches_reference(plan, K, tmp_path):
+    g = golden("gmm_replay_pr2test2_K%d.npz" % K)
+    N = int(g["n_samples"])
+    mod = _module(plan, "pr2test2", N, num_gaussians=K)
+    g["draws"].astype("<f8").tofile(tmp_path / "d.f64")
+    g["gmm_counts"].astype("<i4").tofile(tmp_path / "c.i32")
+    mod.SendCommand("setMode deterministic")
+    mod.SendCommand("setDrawsFile %s" % (tmp_path / "d.f64"))
+    mod.SendCommand("setGMMCountsFile %s" % (tmp_path / "c.i32"))
+    text = mod.SendCommand("runGMMEstimation")
+    assert text == "%g" % float(g["P"])
+    prob = np.array(mod.SendCommand("getWaypointProbabilities").split(), dtype=np.float64)
+    np.testing.assert_array_equal(prob, g["probabilities"])
+    post = np.array(mod.SendCommand("getGMM").split(), dtype=np.float64).reshape(K, 13)
+    np.testing.assert_allclose(post[:, :4], g["gmm_post"][:, :4], rtol=1e-4, atol=1e-4)
+    mod.close()
+
+
+def test_shared_mode_reproduces_the_reference_run_to_run_law(plan):
+    """Default mode: every runSimulation is one draw of the reference's estimator (one shared real robot per run), so
+    the returned values scatter like the reference's own runs (tests/golden/mc_dist_pr2test2.json)."""
+    dist = json.load(open(os.path.join(GOLD, "mc_dist_pr2test2.json")))
+    mod = _module(plan, "pr2test2", dist["particles"])
+    mod.SendCommand("setSeed 12345")
+    ours = np.array([float(mod.SendCommand("runSimulation")) for _ in range(200)])
+    ref = np.array(dist["P"])
+    half = 2.576 * np.sqrt(ours.var(ddof=1) / len(ours) + ref.var(ddof=1) / len(ref))
+    print("shared mode: mean %.4f std %.4f | reference mean %.4f std %.4f | 99%% half-width %.4f" %
+          (ours.mean(), ours.std(ddof=1), ref.mean(), ref.std(ddof=1), half))
+    assert abs(ours.mean() - ref.mean()) < half
+    assert 0.5 * ref.std(ddof=1) < ours.std(ddof=1) < 2.0 * ref.std(ddof=1)
+    assert len(set(ours)) > 20                       # successive runs use fresh draws
+    mod.SendCommand("setSeed 12345")                 # same seed: same sequence of results
+    again = [float(mod.SendCommand("runSimulation")) for _ in range(3)]
+    assert again == list(ours[:3])
+    # philox mode: expectation of the above
+    mod.SendCommand("setMode philox")
+    mod.SendCommand("setNumParticles 1000000")
+    p = float(mod.SendCommand("runSimulation"))
+    assert abs(p - ref.mean()) < 2.576 * ref.std(ddof=1) / np.sqrt(len(ref))
+    mod.close()
+
+
+def test_gmm_default_mode_runs_and_scatter(plan):
+    mod = _module(plan, "pr2test2", 10000, num_gaussians=3)
+    mod.SendCommand("setSeed 99")
+    vals = [float(mod.SendCommand("runGMMEstimation")) for _ in range(5)]
+    assert all(0.0 <= v <= 1.0 for v in vals) and len(set(vals)) > 1
+    mod.close()
+
+
+def test_run_without_parameters_is_an_error():
+    import pcoll_b200
+    mod = pcoll_b200.MCModule(os.path.join(ROOT, "data", "scenes", "pr2test2.env.xml"), device=0)
+    with pytest.raises(pcoll_b200.McsimError, match="setAlphas"):
+        mod.SendCommand("runSimulation")
+    mod.close()
