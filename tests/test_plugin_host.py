@@ -146,3 +146,11 @@ def test_create_on_a_missing_device_is_loud(scenes):
         pytest.skip("GPU present")
     with pytest.raises(pcoll_b200.McsimError, match="no CPU fallback"):
         pcoll_b200.MCModule(scenes["pr2test2"], device=0)
+
+
+def test_openrave_adapter_compiles_against_the_stand_in_headers():
+    """OpenRAVE and Boost are not in this image: csrc/openrave_adapter.cpp is syntax-checked against tests/stub_openrave."""
+    import subprocess
+    csrc = os.path.join(ROOT, "probability-of-collision-for-safe-planning_b200", "csrc")
+    r = subprocess.run(["make", "-C", csrc, "openrave-syntax"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
