@@ -106,6 +106,10 @@ typedef struct {
                                     rollout draws its start pose from its own Philox block
                                     (always so in PHILOX mode) */
     double near_eps;             /* |clearance| < near_eps marks a near-contact pose (audit only) */
+    int precise;                 /* PHILOX mode only.  0: packed two-rollouts-per-thread kernel with MUFU
+                                    approximations (mc_philox2_sm100.cuh); 1: scalar kernel with IEEE
+                                    division / sqrt / libm trigonometry (same Philox counters and draw
+                                    order; audit launches always use it) */
 } mcsim_mc_params;
 
 enum { MCSIM_MODE_REPLAY = 0, MCSIM_MODE_PHILOX = 1 };

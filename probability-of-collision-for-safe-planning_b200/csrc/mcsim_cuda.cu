@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "mc_rollout_sm100.cuh"
+#include "mc_philox2_sm100.cuh"
 #include "gmm_sm100.cuh"
 #include "peaks_sm100.cuh"
 
@@ -182,7 +183,7 @@ extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int 
             const double p = bx[2] * bx[0] + bx[3] * bx[1];
             const double q = bx[2] * bx[1] - bx[3] * bx[0];
             pairs.push_back(make_float4(float(bx[0]), float(bx[1]), float(bx[2]), float(bx[3])));
-            pairs.push_back(make_float4(float(bx[4]), float(bx[5]), float(p), float(q)));
+            pairs.push_back(make_float4(float(bx[4]), float(bx[5]), -float(p), -float(q)));
             pd.push_back(PairD{bx[0], bx[1], bx[2], bx[3], bx[4], bx[5]});
         }
         r.count = int(pairs.size() / 2) - r.first;
@@ -245,6 +246,11 @@ static mc_kernel_t pick_kernel(int mode, bool audit, bool ee, int est, int L) {
               : pick_nl<MCSIM_MODE_PHILOX, false, false, MCSIM_EST_REFERENCE>(L);
 }
 
+static mc_kernel_t pick_packed(bool ee, int est) {
+    if (est == MCSIM_EST_CLOSEDLOOP) return ee ? mc_philox2_kernel<true, MCSIM_EST_CLOSEDLOOP, 8> : mc_philox2_kernel<false, MCSIM_EST_CLOSEDLOOP, 8>;
+    return ee ? mc_philox2_kernel<true, MCSIM_EST_REFERENCE, 8> : mc_philox2_kernel<false, MCSIM_EST_REFERENCE, 8>;
+}
+
 static int mc_check(const mcsim_cuda_ctx* c, const mcsim_mc_params* p) {
     if (!c || !p) return fail(MCSIM_ERR_ARG, "mc: NULL context or params");
     if (!c->scene_set) return fail(MCSIM_ERR_ARG, "mc: mcsim_cuda_set_scene has not been called");
@@ -299,11 +305,23 @@ extern "C" int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* c, const mcsim_mc_params* p
             }
         }
     }
+    // packed kernel's table (x*, u*, M, M0 + M2 per waypoint) in __constant__ memory
+    std::vector<float> plan2;
+    if (p->mode == MCSIM_MODE_PHILOX && T <= MC_PLAN2_MAX_T) {
+        plan2.assign(size_t(T) * MC_PLAN2_STRIDE, 0.f);
+        for (int t = 0; t < T; ++t) {
+            const float* r = &plan[size_t(t) * MC_PHILOX_STRIDE];
+            float* w = &plan2[size_t(t) * MC_PLAN2_STRIDE];
+            for (int k = 0; k < 9; ++k) w[k] = r[k];
+            w[9] = r[6] + r[8];
+        }
+    }
     CK(c->plan.reserve(plan.size() * sizeof(float)));
     CK(c->counters.reserve(sizeof(unsigned long long) * (4 + MCSIM_MAX_WAYPOINTS)));
     CK(cudaStreamSynchronize(c->stream));
     CK(cudaMemcpyToSymbolAsync(c_mc, &pc, sizeof(pc), 0, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemcpyAsync(c->plan.p, plan.data(), plan.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    if (!plan2.empty()) CK(cudaMemcpyToSymbolAsync(c_plan2, plan2.data(), plan2.size() * sizeof(float), 0, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * (4 + T), c->stream));
     CK(cudaStreamSynchronize(c->stream));  // plan is a stack vector
     c->mc = *p;
@@ -317,7 +335,9 @@ static int mc_launch_impl(mcsim_cuda_ctx* c, uint64_t n, uint64_t offset, const 
                           float* d_poses, float* d_clear) {
     const mcsim_mc_params& p = c->mc;
     const bool audit = d_poses || d_clear;
-    mc_kernel_t k = pick_kernel(p.mode, audit, p.early_exit != 0, p.estimator, p.n_landmarks);
+    const bool packed = p.mode == MCSIM_MODE_PHILOX && !audit && !p.precise && p.n_landmarks == 8 && c->mc_T <= MC_PLAN2_MAX_T;
+    mc_kernel_t k = packed ? pick_packed(p.early_exit != 0, p.estimator)
+                           : pick_kernel(p.mode, audit, p.early_exit != 0, p.estimator, p.n_landmarks);
     McLaunch a;
     a.plan = (const float*)c->plan.p;
     a.z0 = d_z0;
@@ -330,10 +350,11 @@ static int mc_launch_impl(mcsim_cuda_ctx* c, uint64_t n, uint64_t offset, const 
     a.poses = d_poses;
     a.clearance = d_clear;
     a.near_eps = float(p.near_eps);
-    const int block = 256;
-    const size_t smem = sizeof(float) * size_t(c->mc_T) * MC_PHILOX_STRIDE;
-    unsigned long long want = (n + block - 1) / block;
-    const unsigned long long cap = (unsigned long long)c->n_sm * 8;  // persistent: whole waves of resident CTAs
+    const int block = packed ? 128 : 256;
+    const size_t smem = packed ? 0 : sizeof(float) * size_t(c->mc_T) * MC_PHILOX_STRIDE;
+    unsigned long long want = packed ? ((n + 1) / 2 + block - 1) / block : (n + block - 1) / block;
+    // persistent: whole waves of resident CTAs (packed: 4 x 128 threads per SM at <= 128 registers)
+    const unsigned long long cap = (unsigned long long)c->n_sm * (packed ? 4 : 8);
     const unsigned grid = unsigned(want < cap ? (want ? want : 1) : cap);
     k<<<grid, block, smem, c->stream>>>(a);
     ++c->launches;

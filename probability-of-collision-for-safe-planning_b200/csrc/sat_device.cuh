@@ -8,7 +8,7 @@
 // (|projected centre distance| - r_hull - r_box) <= 0.
 //
 // Table layout (FP32, __constant__): live (hull, box) pairs grouped by hull, 32 B per pair:
-//     lo = (cx, cy, cos phi, sin phi)   hi = (hx, hy, p, q),  p = cb cx + sb cy,  q = cb cy - sb cx
+//     lo = (cx, cy, cos phi, sin phi)   hi = (hx, hy, -p, -q),  p = cb cx + sb cy,  q = cb cy - sb cx
 // p and q fold the box-frame projection of the box centre, so the four centre projections cost
 // 8 FFMA and no subtraction of centres (see DESIGN.md "SAT instruction count").
 #ifndef MCSIM_SAT_DEVICE_CUH
@@ -60,8 +60,8 @@ __device__ __forceinline__ float pair_gap(const HullPose& h, const float4 lo, co
     // centre distance along hull axes and along box axes
     const float drx = fabsf(fmaf(h.ch, lo.x, fmaf(h.sh, lo.y, -h.ph)));
     const float dry = fabsf(fmaf(h.ch, lo.y, fmaf(-h.sh, lo.x, -h.qh)));
-    const float dbx = fabsf(fmaf(-lo.z, h.hcx, fmaf(-lo.w, h.hcy, hi.z)));
-    const float dby = fabsf(fmaf(-lo.z, h.hcy, fmaf(lo.w, h.hcx, hi.w)));
+    const float dbx = fabsf(fmaf(lo.z, h.hcx, fmaf(lo.w, h.hcy, hi.z)));
+    const float dby = fabsf(fmaf(lo.z, h.hcy, fmaf(-lo.w, h.hcx, hi.w)));
     float g = drx - fmaf(hi.x, c, fmaf(hi.y, s, h.hx));
     g = fmaxf(g, dry - fmaf(hi.x, s, fmaf(hi.y, c, h.hy)));
     g = fmaxf(g, dbx - fmaf(h.hx, c, fmaf(h.hy, s, hi.x)));
@@ -75,8 +75,8 @@ __device__ __forceinline__ bool pair_hit(const HullPose& h, const float4 lo, con
     const float s = fabsf(h.sh * lo.z - h.ch * lo.w);
     const float drx = fabsf(fmaf(h.ch, lo.x, fmaf(h.sh, lo.y, -h.ph)));
     const float dry = fabsf(fmaf(h.ch, lo.y, fmaf(-h.sh, lo.x, -h.qh)));
-    const float dbx = fabsf(fmaf(-lo.z, h.hcx, fmaf(-lo.w, h.hcy, hi.z)));
-    const float dby = fabsf(fmaf(-lo.z, h.hcy, fmaf(lo.w, h.hcx, hi.w)));
+    const float dbx = fabsf(fmaf(lo.z, h.hcx, fmaf(lo.w, h.hcy, hi.z)));
+    const float dby = fabsf(fmaf(lo.z, h.hcy, fmaf(-lo.w, h.hcx, hi.w)));
     return (drx <= fmaf(hi.x, c, fmaf(hi.y, s, h.hx))) & (dry <= fmaf(hi.x, s, fmaf(hi.y, c, h.hy))) &
            (dbx <= fmaf(h.hx, c, fmaf(h.hy, s, hi.x))) & (dby <= fmaf(h.hx, s, fmaf(h.hy, c, hi.y)));
 }
