@@ -54,9 +54,14 @@ __device__ __forceinline__ Philox2 philox_pair(unsigned long long id0, unsigned 
 }
 
 // ---- packed SAT: both lanes against every live pair ------------------------------------------------
-// Same test as pair_hit (sat_device.cuh); per pair and per two rollouts 4 + 8 + 8 packed FP32
-// instructions and 8 FSETP.  hit0 / hit1 accumulate the lanes' flags.
-__device__ __forceinline__ void robot_hits2(f2 x, f2 y, f2 ct, f2 st, bool& hit0, bool& hit1) {
+// The same separating-axis test as pair_hit (sat_device.cuh) on the orientation-grouped table
+// (mcsim_cuda_set_scene): per class of boxes sharing an axis direction (mod 90 degrees) the relative
+// rotation (c, s), the hull centre in the class frame (gx, gy) and the hull's radii on the class
+// axes (rbx, rby) are computed once (12 packed instructions); per pair and per two rollouts that
+// leaves 8 FFMA2 + 4 FADD2 and 8 FSETP.  Every live pair is still tested at every step.
+// Table records (float4, shared memory): class header (cos, sin, count, -), then per pair
+// (cx, cy, hx, hy), (-p, -q, -, -) with p = cb cx + sb cy, q = cb cy - sb cx.
+__device__ __forceinline__ void robot_hits2(const float4* __restrict__ tab, f2 x, f2 y, f2 ct, f2 st, bool& hit0, bool& hit1) {
     const int nh = c_scene.n_hulls;
     for (int hI = 0; hI < nh; ++hI) {
         const HullRec& hr = c_scene.hulls[hI];
@@ -64,27 +69,36 @@ __device__ __forceinline__ void robot_hits2(f2 x, f2 y, f2 ct, f2 st, bool& hit0
         const f2 hcy = fma2(st, hr.ox, fma2(ct, hr.oy, y));
         const f2 ch = fma2(ct, hr.cp, mul2(neg2(st), hr.sp));
         const f2 sh = fma2(st, hr.cp, mul2(ct, hr.sp));
-        const f2 ph = fma2(ch, hcx, mul2(sh, hcy));
-        const f2 qh = fma2(ch, hcy, mul2(neg2(sh), hcx));
-        const float hhx = hr.hx, hhy = hr.hy;
-        const int end = hr.first + hr.count;
+        const f2 nph = neg2(fma2(ch, hcx, mul2(sh, hcy)));
+        const f2 nqh = neg2(fma2(ch, hcy, mul2(neg2(sh), hcx)));
+        const f2 hhx = bc(hr.hx), hhy = bc(hr.hy);
+        const float4* g = tab + hr.g_first;
+        for (int gi = 0; gi < hr.n_groups; ++gi) {
+            const float4 head = g[0];
+            const int cnt = __float_as_int(head.z);
+            const f2 c = abs2(fma2(ch, head.x, mul2(sh, head.y)));
+            const f2 s = abs2(fma2(sh, head.x, mul2(neg2(ch), head.y)));
+            const f2 gx = fma2(hcx, head.x, mul2(hcy, head.y));
+            const f2 gy = fma2(hcy, head.x, mul2(neg2(hcx), head.y));
+            const f2 rbx = fma2(c, hhx, mul2(s, hhy));
+            const f2 rby = fma2(s, hhx, mul2(c, hhy));
+            ++g;
 #pragma unroll 4
-        for (int b = hr.first; b < end; ++b) {
-            const float4 lo4 = c_pairs[2 * b];      // cx, cy, cos phi, sin phi
-            const float4 hi4 = c_pairs[2 * b + 1];  // hx, hy, -p, -q
-            const f2 c = fma2(ch, lo4.z, mul2(sh, lo4.w));
-            const f2 s = fma2(sh, lo4.z, mul2(neg2(ch), lo4.w));
-            const f2 drx = fma2(ch, lo4.x, fma2(sh, lo4.y, neg2(ph)));
-            const f2 dry = fma2(ch, lo4.y, fma2(neg2(sh), lo4.x, neg2(qh)));
-            const f2 dbx = fma2(hcx, lo4.z, fma2(hcy, lo4.w, hi4.z));
-            const f2 dby = fma2(hcy, lo4.z, fma2(neg2(hcx), lo4.w, hi4.w));
-            const f2 ac = abs2(c), as = abs2(s);
-            const f2 r0 = fma2(ac, hi4.x, fma2(as, hi4.y, hhx));
-            const f2 r1 = fma2(as, hi4.x, fma2(ac, hi4.y, hhy));
-            const f2 r2 = fma2(ac, hhx, fma2(as, hhy, hi4.x));
-            const f2 r3 = fma2(as, hhx, fma2(ac, hhy, hi4.y));
-            if ((fabsf(lo(drx)) <= lo(r0)) & (fabsf(lo(dry)) <= lo(r1)) & (fabsf(lo(dbx)) <= lo(r2)) & (fabsf(lo(dby)) <= lo(r3))) hit0 = true;
-            if ((fabsf(hi(drx)) <= hi(r0)) & (fabsf(hi(dry)) <= hi(r1)) & (fabsf(hi(dbx)) <= hi(r2)) & (fabsf(hi(dby)) <= hi(r3))) hit1 = true;
+            for (int b = 0; b < cnt; ++b) {
+                const float4 A = g[2 * b];                                           // cx, cy, hx, hy
+                const float2 B = *reinterpret_cast<const float2*>(g + 2 * b + 1);    // -p, -q
+                const f2 drx = fma2(ch, A.x, fma2(sh, A.y, nph));
+                const f2 dry = fma2(ch, A.y, fma2(neg2(sh), A.x, nqh));
+                const f2 r0 = fma2(c, A.z, fma2(s, A.w, hhx));
+                const f2 r1 = fma2(s, A.z, fma2(c, A.w, hhy));
+                const f2 dbx = add2(gx, B.x);
+                const f2 dby = add2(gy, B.y);
+                const f2 r2 = add2(rbx, A.z);
+                const f2 r3 = add2(rby, A.w);
+                if ((fabsf(lo(drx)) <= lo(r0)) & (fabsf(lo(dry)) <= lo(r1)) & (fabsf(lo(dbx)) <= lo(r2)) & (fabsf(lo(dby)) <= lo(r3))) hit0 = true;
+                if ((fabsf(hi(drx)) <= hi(r0)) & (fabsf(hi(dry)) <= hi(r1)) & (fabsf(hi(dbx)) <= hi(r2)) & (fabsf(hi(dby)) <= hi(r3))) hit1 = true;
+            }
+            g += 2 * cnt;
         }
     }
 }
@@ -100,9 +114,11 @@ __device__ __forceinline__ void move2(f2 p[3], const f2 u[3]) {
 
 template <bool EARLY_EXIT, int EST, int NL>
 __global__ void __launch_bounds__(128, 4) mc_philox2_kernel(const McLaunch a) {
+    extern __shared__ __align__(16) float4 s_tab[];
     __shared__ unsigned s_cnt[2];
     __shared__ unsigned s_hist[MCSIM_MAX_WAYPOINTS];
     const int T = c_mc.T;
+    for (int i = threadIdx.x; i < a.sat2_n; i += blockDim.x) s_tab[i] = a.sat2[i];
     for (int i = threadIdx.x; i < T; i += blockDim.x) s_hist[i] = 0;
     if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
     __syncthreads();
@@ -151,7 +167,7 @@ __global__ void __launch_bounds__(128, 4) mc_philox2_kernel(const McLaunch a) {
             f2 sn, cs;
             sincos2(q[2], sn, cs);
             bool h0 = false, h1 = false;
-            robot_hits2(q[0], q[1], cs, sn, h0, h1);
+            robot_hits2(s_tab, q[0], q[1], cs, sn, h0, h1);
             if (EARLY_EXIT) {
                 my_steps += (valid0 && cnt0 == 0) + (valid1 && cnt1 == 0);
             }

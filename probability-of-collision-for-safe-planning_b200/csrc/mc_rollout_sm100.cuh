@@ -44,6 +44,8 @@ struct McLaunch {
     float* poses;                 // optional audit [T][3][n]
     float* clearance;             // optional audit [T][n]
     float near_eps;
+    const float4* sat2;           // orientation-grouped pair table (packed kernel), sat2_n float4 records
+    int sat2_n;
 };
 
 // FP64 angle in [0, 4 pi] -> FP32 angle in [-pi, pi] (rounding error <= 1.2e-7 rad, not accumulated)

@@ -61,6 +61,9 @@ struct mcsim_cuda_ctx {
     // FP64 scene for the replay-mode GMM SAT
     DevBuf hulls_d, pairs_d;
     int n_hulls = 0;
+    // orientation-grouped FP32 pair table of the packed Philox kernel (staged into shared memory)
+    DevBuf sat2;
+    int sat2_n = 0;  // float4 records
     // GMM state
     DevBuf gmm_comps, gmm_stats, gmm_hist, gmm_counts, gmm_normals, gmm_steps, gmm_prob, gmm_pre, gmm_post, gmm_trunc, gmm_nout, gmm_deg;
     double* h_gmm = nullptr;  // pinned staging
@@ -103,7 +106,7 @@ extern "C" void mcsim_cuda_destroy(mcsim_cuda_ctx* c) {
     cudaStreamSynchronize(c->stream);
     c->plan.release(); c->z0.release(); c->counters.release(); c->counts.release();
     c->poses.release(); c->clearance.release();
-    c->hulls_d.release(); c->pairs_d.release();
+    c->hulls_d.release(); c->pairs_d.release(); c->sat2.release();
     c->gmm_comps.release(); c->gmm_stats.release(); c->gmm_hist.release(); c->gmm_counts.release();
     c->gmm_normals.release(); c->gmm_steps.release(); c->gmm_prob.release(); c->gmm_pre.release();
     c->gmm_post.release(); c->gmm_trunc.release(); c->gmm_nout.release(); c->gmm_deg.release();
@@ -160,6 +163,7 @@ extern "C" int mcsim_cuda_measure_peaks(mcsim_cuda_ctx* c, double ms, double* fp
 }
 
 // ---- scene ----------------------------------------------------------------------------------
+static inline float __int_as_float_host(int v) { float f; memcpy(&f, &v, sizeof(f)); return f; }
 extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int n_boxes,
                                     const double* hulls, int n_hulls) {
     if (!c || n_boxes < 0 || n_hulls < 1 || n_hulls > MCSIM_MAX_HULLS || !hulls || (n_boxes && !boxes))
@@ -168,6 +172,7 @@ extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int 
     SceneConst sc;
     memset(&sc, 0, sizeof(sc));
     std::vector<float4> pairs;
+    std::vector<float4> sat2;  // per hull: per orientation class: header (cb, sb, count, 0), then 2 float4 per pair
     std::vector<HullD> hd(n_hulls);
     std::vector<PairD> pd;
     sc.n_hulls = n_hulls;
@@ -187,6 +192,45 @@ extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int 
             pd.push_back(PairD{bx[0], bx[1], bx[2], bx[3], bx[4], bx[5]});
         }
         r.count = int(pairs.size() / 2) - r.first;
+        // ---- the same live pairs grouped by orientation class.  A box (phi, hx, hy) is the box
+        // (phi - k 90 deg, extents swapped for odd k): the axis is canonicalised into [0, 90 deg), so all
+        // axis-aligned boxes of a scene share one class per hull.  Per class the kernel computes the
+        // relative rotation, the hull centre in the class frame and the hull's radii on the class axes
+        // once; per pair it is left with 12 packed FP32 instructions instead of 20.
+        struct Canon { double cb, sb, cx, cy, hx, hy; };
+        std::vector<Canon> live;
+        for (int b = 0; b < n_boxes; ++b) {
+            const double* bx = boxes + b * MCSIM_PRISM_STRIDE;
+            if (!((hu[6] < bx[7]) && (bx[6] < hu[7]))) continue;
+            double cb = bx[2], sb = bx[3], hx = bx[4], hy = bx[5];
+            if (fabs(cb) < 1e-12) cb = 0;
+            if (fabs(sb) < 1e-12) sb = 0;
+            for (int k = 0; k < 4 && !(cb > 0 && sb >= 0); ++k) {  // rotate the frame by +90 deg: u' = v = (-sb, cb)
+                const double t = cb; cb = -sb; sb = t;
+                std::swap(hx, hy);
+            }
+            live.push_back(Canon{cb, sb, bx[0], bx[1], hx, hy});
+        }
+        r.g_first = int(sat2.size());
+        r.n_groups = 0;
+        std::vector<char> done(live.size(), 0);
+        for (size_t i = 0; i < live.size(); ++i) {
+            if (done[i]) continue;
+            const size_t header = sat2.size();
+            sat2.push_back(make_float4(float(live[i].cb), float(live[i].sb), 0.f, 0.f));
+            int cnt = 0;
+            for (size_t j = i; j < live.size(); ++j) {
+                if (done[j] || fabs(live[j].cb - live[i].cb) > 1e-9 || fabs(live[j].sb - live[i].sb) > 1e-9) continue;
+                done[j] = 1;
+                const Canon& q = live[j];
+                const double pp = live[i].cb * q.cx + live[i].sb * q.cy, qq = live[i].cb * q.cy - live[i].sb * q.cx;
+                sat2.push_back(make_float4(float(q.cx), float(q.cy), float(q.hx), float(q.hy)));
+                sat2.push_back(make_float4(-float(pp), -float(qq), 0.f, 0.f));
+                ++cnt;
+            }
+            sat2[header].z = __int_as_float_host(cnt);
+            ++r.n_groups;
+        }
         hd[h] = HullD{hu[0], hu[1], hu[2], hu[3], hu[4], hu[5], r.first, r.count};
         const float reach = float(sqrt(hu[0] * hu[0] + hu[1] * hu[1]) + sqrt(hu[4] * hu[4] + hu[5] * hu[5]));
         if (reach > sc.reach) sc.reach = reach;
@@ -201,6 +245,9 @@ extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int 
     CK(cudaMemcpy(c->hulls_d.p, hd.data(), sizeof(HullD) * hd.size(), cudaMemcpyHostToDevice));
     CK(c->pairs_d.reserve(sizeof(PairD) * (pd.size() ? pd.size() : 1)));
     if (!pd.empty()) CK(cudaMemcpy(c->pairs_d.p, pd.data(), sizeof(PairD) * pd.size(), cudaMemcpyHostToDevice));
+    CK(c->sat2.reserve(sizeof(float4) * (sat2.size() ? sat2.size() : 1)));
+    if (!sat2.empty()) CK(cudaMemcpy(c->sat2.p, sat2.data(), sizeof(float4) * sat2.size(), cudaMemcpyHostToDevice));
+    c->sat2_n = int(sat2.size());
     c->n_hulls = n_hulls;
     c->scene_set = true;
     c->n_pairs = sc.n_pairs;
@@ -350,12 +397,15 @@ static int mc_launch_impl(mcsim_cuda_ctx* c, uint64_t n, uint64_t offset, const 
     a.poses = d_poses;
     a.clearance = d_clear;
     a.near_eps = float(p.near_eps);
+    a.sat2 = (const float4*)c->sat2.p;
+    a.sat2_n = c->sat2_n;
     const int block = packed ? 128 : 256;
-    const size_t smem = packed ? 0 : sizeof(float) * size_t(c->mc_T) * MC_PHILOX_STRIDE;
+    const size_t smem = packed ? sizeof(float4) * size_t(c->sat2_n) : sizeof(float) * size_t(c->mc_T) * MC_PHILOX_STRIDE;
     unsigned long long want = packed ? ((n + 1) / 2 + block - 1) / block : (n + block - 1) / block;
     // persistent: whole waves of resident CTAs (packed: 4 x 128 threads per SM at <= 128 registers)
     const unsigned long long cap = (unsigned long long)c->n_sm * (packed ? 4 : 8);
     const unsigned grid = unsigned(want < cap ? (want ? want : 1) : cap);
+    if (smem > 40 * 1024) CK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     k<<<grid, block, smem, c->stream>>>(a);
     ++c->launches;
     CK(cudaGetLastError());
@@ -390,7 +440,8 @@ extern "C" int mcsim_cuda_mc_run(mcsim_cuda_ctx* c, const mcsim_mc_params* p, mc
     if (!r) return fail(MCSIM_ERR_ARG, "mc_run: result is NULL");
     int rc = mcsim_cuda_mc_prepare(c, p);
     if (rc) return rc;
-    c->h2d_bytes = sizeof(McPlanConst) + sizeof(float) * size_t(p->T) * MC_PHILOX_STRIDE;
+    c->h2d_bytes = sizeof(McPlanConst) + sizeof(float) * size_t(p->T) * MC_PHILOX_STRIDE +
+                   ((p->mode == MCSIM_MODE_PHILOX && p->T <= MC_PLAN2_MAX_T) ? sizeof(float) * size_t(p->T) * MC_PLAN2_STRIDE : 0);
     c->d2h_bytes = sizeof(unsigned long long) * (4 + p->T);
     const uint64_t n = p->n_rollouts;
     const int T = p->T;

@@ -20,6 +20,7 @@ struct HullRec {
     float ox, oy, cp, sp;  // centre and axis in the robot frame
     float hx, hy;          // half extents
     int first, count;      // slice of c_pairs
+    int g_first, n_groups; // slice of the orientation-grouped table (float4 units; mc_philox2_sm100.cuh)
 };
 
 struct SceneConst {
