@@ -220,6 +220,54 @@ typedef struct {
 int mcsim_cuda_gmm_run(mcsim_cuda_ctx* ctx, const mcsim_mc_params* mc, const mcsim_gmm_run_params* g,
                        mcsim_gmm_run_result* r);
 
+/* ---- EM fit of full-covariance 3-D mixtures (BASELINE.json config 5) ------------------------ */
+/* Replaces arma::gmm_full::learn(X, K, dist, keep_existing, km_iter = 0, em_iter, var_floor)
+ * (armadillo-8.400.0/include/armadillo_bits/gmm_full_meat.hpp:764-890): em_iterate :2390-2484,
+ * init_constants :980-1046, em_generate_acc :2646-2734 (the data-parallel E-step + sufficient
+ * statistics), em_update_params :2542-2639 (reduce + M-step), em_fix_params :2741-2800.
+ * n_fits independent fits (one per waypoint buffer) run in the same launches. */
+typedef struct {
+    int K;                       /* components per fit, 1..MCSIM_MAX_GAUSSIANS */
+    int n_fits;                  /* independent fits in this call */
+    uint64_t n;                  /* samples per fit held by THIS context (its shard) */
+    uint64_t n_total;            /* samples per fit over all shards (hefts = sum r / n_total,
+                                    avg_log_p = sum lse / n_total); 0 means n */
+    const float* x;              /* HOST [n_fits][3][n] FP32, component-major per fit (x.., y.., theta..);
+                                    NULL: reuse the samples already resident from the previous call */
+    const double* hefts;         /* [n_fits][K]    initial parameters (seed mode keep_existing) */
+    const double* means;         /* [n_fits][K][3] */
+    const double* fcovs;         /* [n_fits][K][9] symmetric */
+    int iters;                   /* em_iter */
+    double var_floor;            /* <= 0: DBL_MIN, as learn() does (:868) */
+} mcsim_em_params;
+
+typedef struct {
+    double* hefts;               /* HOST out, same shapes as the inputs */
+    double* means;
+    double* fcovs;
+    double* avg_log_p;           /* [n_fits][iters] optional: average log-likelihood under the parameters
+                                    BEFORE each iteration's update (what em_iterate tests, :2447);
+                                    NaN for iterations skipped after convergence */
+    int* iters_run;              /* [n_fits] optional */
+    float kernel_ms;             /* device time of all E/M launches of the call */
+} mcsim_em_result;
+
+/* Upload + iterate + download, single device. */
+int mcsim_cuda_em_fit(mcsim_cuda_ctx* ctx, const mcsim_em_params* p, mcsim_em_result* r);
+/* Split form for sharded samples (one context per GPU): prepare uploads samples and parameters and
+ * computes the E-step constants; every iteration is estep (accumulates this shard's statistics),
+ * an all-reduce (sum) by the caller of the FP64 block em_stats() on the context's stream, mstep
+ * (identical on every shard); collect downloads the parameters.  All asynchronous on the stream
+ * except prepare's and collect's host copies. */
+int mcsim_cuda_em_prepare(mcsim_cuda_ctx* ctx, const mcsim_em_params* p);
+int mcsim_cuda_em_estep(mcsim_cuda_ctx* ctx);
+int mcsim_cuda_em_mstep(mcsim_cuda_ctx* ctx);
+int mcsim_cuda_em_collect(mcsim_cuda_ctx* ctx, mcsim_em_result* r);
+/* DEVICE pointer and length (doubles) of the statistics block: [n_fits][K * 10 + 1] =
+ * per component {sum r, sum r d (3), sum r d d^T (xx xy xz yy yz zz)} with d = x - current mean,
+ * then sum of log-likelihoods. */
+void* mcsim_cuda_em_stats(mcsim_cuda_ctx* ctx, uint64_t* n_doubles);
+
 /* bytes the last *_run call copied host->device and device->host (bench.py's e2e accounting) */
 void mcsim_cuda_io_bytes(mcsim_cuda_ctx* ctx, uint64_t* h2d, uint64_t* d2h);
 

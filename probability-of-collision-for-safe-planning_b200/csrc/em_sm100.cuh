@@ -1,0 +1,290 @@
+// em_sm100.cuh -- EM fit of K full-covariance 3-D Gaussian components (BASELINE.json config 5).
+//
+// Replaces the vendored Armadillo 8.400.0 EM the reference ships (SURVEY.md A13;
+// armadillo_bits/gmm_full_meat.hpp): em_generate_acc :2646-2734 becomes em_estep_kernel (responsibilities
+// are never materialised: log-likelihoods, log-sum-exp and the weighted sums stay in registers),
+// em_update_params :2542-2639 + em_fix_params :2741-2800 + the convergence test of em_iterate
+// :2447-2465 + init_constants :980-1046 become em_mstep_kernel (one CTA per fit, FP64).
+//
+// Samples: FP32, component-major per fit (x[n], y[n], theta[n]) -- 12 B per sample and iteration
+// from HBM.  Sufficient statistics are accumulated about the CURRENT component mean
+// (d = x - mu_g, which the Mahalanobis form needs anyway):  sum r, sum r d, sum r d d^T;
+// new mean = mu_g + sum r d / sum r, new cov = sum r d d^T / sum r - delta delta^T.  Algebraically
+// this is the reference's sum r x x^T / sum r - mean mean^T (:2591-2600) without its cancellation,
+// which FP32 partial sums could not afford (|x|^2 ~ 10, cov ~ 1e-3).
+#ifndef MCSIM_EM_CUH
+#define MCSIM_EM_CUH
+
+#include <float.h>
+
+#include "mcsim_cuda.h"
+
+#define EM_COMP_STRIDE 12  // floats per component: mu[3], b00 b01 b02 b11 b12 b22, cst, pad[2]
+#define EM_NSTAT 10        // sum r, sum r d[3], sum r dd^T [xx xy xz yy yz zz]
+
+struct EmLaunch {
+    const float* x;        // [n_fits][3][n]
+    unsigned long long n;  // samples per fit in this shard
+    double n_total;        // samples per fit over all shards
+    int K, n_fits, iters;
+    int iter;              // index of the iteration being run
+    double var_floor;
+    float* comps;          // [n_fits][K][EM_COMP_STRIDE] E-step constants (FP32)
+    double* hefts;         // [n_fits][K]
+    double* means;         // [n_fits][K][3]
+    double* fcovs;         // [n_fits][K][9]
+    double* stats;         // [n_fits][K * 10 + 1]
+    double* old_avg;       // [n_fits]
+    int* done;             // [n_fits] 0 running, 1 converged, 2 non-finite likelihood (reference: learn() fails)
+    int* iters_run;        // [n_fits]
+    double* trace;         // [n_fits][iters] avg_log_p before each update
+};
+
+// ---- E-step ------------------------------------------------------------------------------------------
+// K: components of the model; G0: first component whose statistics THIS launch accumulates (at most 8
+// per launch: 80 FP32 accumulators per thread).  K > 8 takes a second launch with G0 = 8 that
+// recomputes the log-likelihoods; the log-likelihood sum is accumulated by the G0 = 0 launch only.
+template <int K, int G0>
+__global__ void __launch_bounds__(256) em_estep_kernel(const EmLaunch a) {
+    constexpr int KG = (K - G0) < 8 ? (K - G0) : 8;
+    constexpr int NACC = KG * EM_NSTAT + 1;
+    __shared__ float s_c[K * EM_COMP_STRIDE];
+    __shared__ double s_acc[NACC];
+    const int fit = blockIdx.y;
+    if (a.done[fit]) return;
+    for (int i = threadIdx.x; i < K * EM_COMP_STRIDE; i += blockDim.x) s_c[i] = a.comps[(size_t)fit * K * EM_COMP_STRIDE + i];
+    for (int i = threadIdx.x; i < NACC; i += blockDim.x) s_acc[i] = 0.0;
+    __syncthreads();
+
+    const float* xs = a.x + (size_t)fit * 3 * a.n;
+    const float* ys = xs + a.n;
+    const float* ts = ys + a.n;
+    float acc[KG][EM_NSTAT];
+#pragma unroll
+    for (int g = 0; g < KG; ++g)
+#pragma unroll
+        for (int k = 0; k < EM_NSTAT; ++k) acc[g][k] = 0.f;
+    float lsum = 0.f;
+
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
+        const float x = __ldg(xs + i), y = __ldg(ys + i), t = __ldg(ts + i);
+        float ll[K];
+        float m = -FLT_MAX;
+#pragma unroll
+        for (int g = 0; g < K; ++g) {
+            const float* c = s_c + g * EM_COMP_STRIDE;
+            const float d0 = x - c[0], d1 = y - c[1], d2 = t - c[2];
+            // -1/2 d^T A d + cst with b = -1/2 A (off-diagonals doubled)
+            const float q0 = fmaf(c[3], d0, fmaf(c[4], d1, c[5] * d2));
+            const float q1 = fmaf(c[6], d1, c[7] * d2);
+            ll[g] = fmaf(d0, q0, fmaf(d1, q1, fmaf(c[8] * d2, d2, c[9])));
+            m = fmaxf(m, ll[g]);
+        }
+        float s = 0.f;
+#pragma unroll
+        for (int g = 0; g < K; ++g) {
+            ll[g] = exp2f((ll[g] - m) * 1.4426950408889634f);
+            s += ll[g];
+        }
+        if (G0 == 0) lsum += m + __logf(s);
+        const float inv = __frcp_rn(s);
+#pragma unroll
+        for (int gg = 0; gg < KG; ++gg) {
+            const float* c = s_c + (G0 + gg) * EM_COMP_STRIDE;
+            const float r = ll[G0 + gg] * inv;
+            const float d0 = x - c[0], d1 = y - c[1], d2 = t - c[2];
+            const float r0 = r * d0, r1 = r * d1, r2 = r * d2;
+            acc[gg][0] += r;
+            acc[gg][1] += r0;
+            acc[gg][2] += r1;
+            acc[gg][3] += r2;
+            acc[gg][4] = fmaf(r0, d0, acc[gg][4]);
+            acc[gg][5] = fmaf(r0, d1, acc[gg][5]);
+            acc[gg][6] = fmaf(r0, d2, acc[gg][6]);
+            acc[gg][7] = fmaf(r1, d1, acc[gg][7]);
+            acc[gg][8] = fmaf(r1, d2, acc[gg][8]);
+            acc[gg][9] = fmaf(r2, d2, acc[gg][9]);
+        }
+    }
+
+    // warp shuffle reduction (FP32 within the warp's <= 32 partial sums is widened to FP64 first)
+#pragma unroll
+    for (int g = 0; g < KG; ++g)
+#pragma unroll
+        for (int k = 0; k < EM_NSTAT; ++k) {
+            double v = acc[g][k];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if ((threadIdx.x & 31) == 0) atomicAdd(&s_acc[g * EM_NSTAT + k], v);
+        }
+    if (G0 == 0) {
+        double v = lsum;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) atomicAdd(&s_acc[NACC - 1], v);
+    }
+    __syncthreads();
+    double* st = a.stats + (size_t)fit * (K * EM_NSTAT + 1);
+    for (int i = threadIdx.x; i < KG * EM_NSTAT; i += blockDim.x) atomicAdd(&st[G0 * EM_NSTAT + i], s_acc[i]);
+    if (G0 == 0 && threadIdx.x == 0) atomicAdd(&st[K * EM_NSTAT], s_acc[NACC - 1]);
+}
+
+// ---- M-step, parameter sanitising, convergence test and the next iteration's constants (FP64) --------
+// lower Cholesky factor of a symmetric 3x3 (row-major 9); false when not positive definite
+__device__ __forceinline__ bool em_chol3(const double* A, double* L) {
+    if (!(A[0] > 0.0)) return false;
+    L[0] = sqrt(A[0]);
+    L[1] = A[3] / L[0];
+    L[3] = A[6] / L[0];
+    const double d1 = A[4] - L[1] * L[1];
+    if (!(d1 > 0.0)) return false;
+    L[2] = sqrt(d1);
+    L[4] = (A[7] - L[3] * L[1]) / L[2];
+    const double d2 = A[8] - L[3] * L[3] - L[4] * L[4];
+    if (!(d2 > 0.0)) return false;
+    L[5] = sqrt(d2);
+    return isfinite(L[0]) && isfinite(L[2]) && isfinite(L[5]);
+}
+
+__device__ __forceinline__ double em_det3(const double* A) {
+    return A[0] * (A[4] * A[8] - A[5] * A[7]) - A[1] * (A[3] * A[8] - A[5] * A[6]) + A[2] * (A[3] * A[7] - A[4] * A[6]);
+}
+
+// init_constants (:980-1046) for one component: inverse covariance (from the Cholesky factor, as
+// inv_sympd does), log|Sigma|; "last resort" diagonal treatment when either fails.  Writes the
+// FP32 E-step record: mu, b = -1/2 Sigma^-1 (off-diagonals doubled), cst = log_det_etc + log heft.
+__device__ __forceinline__ void em_constants(const double* mean, const double* C, double heft, float* rec) {
+    double Lo[6], inv[6], log_det;
+    const double det = em_det3(C);
+    const bool ok = em_chol3(C, Lo) && isfinite(log(det)) && det > 0.0;
+    if (ok) {
+        // inverse of L (lower), then Sigma^-1 = L^-T L^-1
+        const double i00 = 1.0 / Lo[0], i11 = 1.0 / Lo[2], i22 = 1.0 / Lo[5];
+        const double i10 = -Lo[1] * i00 * i11;
+        const double i21 = -Lo[4] * i11 * i22;
+        const double i20 = -(Lo[3] * i00 + Lo[4] * i10) * i22;
+        inv[0] = i00 * i00 + i10 * i10 + i20 * i20;  // 00
+        inv[1] = i10 * i11 + i20 * i21;              // 01
+        inv[2] = i20 * i22;                          // 02
+        inv[3] = i11 * i11 + i21 * i21;              // 11
+        inv[4] = i21 * i22;                          // 12
+        inv[5] = i22 * i22;                          // 22
+        log_det = 2.0 * (log(Lo[0]) + log(Lo[2]) + log(Lo[5]));
+    } else {
+        log_det = 0.0;
+        inv[1] = inv[2] = inv[4] = 0.0;
+        const int dg[3] = {0, 4, 8}, iv[3] = {0, 3, 5};
+        for (int d = 0; d < 3; ++d) {
+            const double v = fmax(C[dg[d]], DBL_MIN);
+            inv[iv[d]] = 1.0 / v;
+            log_det += log(v);
+        }
+    }
+    const double cst = -(1.5 * log(2.0 * 3.14159265358979323846) + 0.5 * log_det) + log(fmax(heft, DBL_MIN));
+    rec[0] = float(mean[0]); rec[1] = float(mean[1]); rec[2] = float(mean[2]);
+    rec[3] = float(-0.5 * inv[0]); rec[4] = float(-inv[1]); rec[5] = float(-inv[2]);
+    rec[6] = float(-0.5 * inv[3]); rec[7] = float(-inv[4]); rec[8] = float(-0.5 * inv[5]);
+    rec[9] = float(cst);
+    rec[10] = rec[11] = 0.f;
+}
+
+// One CTA per fit, thread g = component g.  prep_only: compute the E-step constants of the initial
+// parameters (the init_constants call that opens iteration 1) and nothing else.
+__global__ void __launch_bounds__(32) em_mstep_kernel(const EmLaunch a, int prep_only) {
+    const int fit = blockIdx.x, g = threadIdx.x, K = a.K;
+    __shared__ double s_heft[MCSIM_MAX_GAUSSIANS];
+    __shared__ double s_mean[MCSIM_MAX_GAUSSIANS][3];
+    double* hefts = a.hefts + (size_t)fit * K;
+    double* means = a.means + (size_t)fit * K * 3;
+    double* fcovs = a.fcovs + (size_t)fit * K * 9;
+    double* st = a.stats + (size_t)fit * (K * EM_NSTAT + 1);
+    if (!prep_only && a.done[fit]) return;
+    double C[9], mean[3], heft = 0.0;
+    if (g < K) {
+        heft = hefts[g];
+        for (int d = 0; d < 3; ++d) mean[d] = means[g * 3 + d];
+        for (int k = 0; k < 9; ++k) C[k] = fcovs[g * 9 + k];
+    }
+    if (!prep_only) {
+        // ---- em_update_params (:2583-2638): conditional update of component g
+        if (g < K) {
+            const double* s = st + g * EM_NSTAT;
+            const double sr = fmax(s[0], DBL_MIN);
+            if (isfinite(sr)) {
+                const double d0 = s[1] / sr, d1 = s[2] / sr, d2 = s[3] / sr;
+                double N[9];
+                N[0] = s[4] / sr - d0 * d0; N[1] = s[5] / sr - d0 * d1; N[2] = s[6] / sr - d0 * d2;
+                N[4] = s[7] / sr - d1 * d1; N[5] = s[8] / sr - d1 * d2; N[8] = s[9] / sr - d2 * d2;
+                N[3] = N[1]; N[6] = N[2]; N[7] = N[5];
+                if (N[0] < a.var_floor) N[0] = a.var_floor;
+                if (N[4] < a.var_floor) N[4] = a.var_floor;
+                if (N[8] < a.var_floor) N[8] = a.var_floor;
+                bool fin = true;
+                for (int k = 0; k < 9; ++k) fin = fin && isfinite(N[k]);
+                double Lo[6];
+                const double det = em_det3(N);
+                if (fin && det > 0.0 && isfinite(log(det)) && em_chol3(N, Lo)) {
+                    heft = sr / a.n_total;
+                    mean[0] += d0; mean[1] += d1; mean[2] += d2;
+                    for (int k = 0; k < 9; ++k) C[k] = N[k];
+                }
+            }
+            // ---- em_fix_params (:2755-2765): variance floor / ceiling / NaN
+            const int dg[3] = {0, 4, 8};
+            for (int d = 0; d < 3; ++d) {
+                double& v = C[dg[d]];
+                if (v < a.var_floor) v = a.var_floor;
+                else if (v > DBL_MAX) v = DBL_MAX;
+                else if (isnan(v)) v = 1.0;
+            }
+            s_heft[g] = heft;
+            for (int d = 0; d < 3; ++d) s_mean[g][d] = mean[d];
+        }
+        __syncthreads();
+        if (g == 0) {
+            // duplicate components (:2770-2787): equal heft (within epsilon) and identical mean -> heft 0
+            for (int g1 = 0; g1 < K; ++g1) {
+                if (!(s_heft[g1] > 0.0)) continue;
+                for (int g2 = g1 + 1; g2 < K; ++g2)
+                    if (s_heft[g2] > 0.0 && fabs(s_heft[g1] - s_heft[g2]) <= DBL_EPSILON &&
+                        s_mean[g1][0] == s_mean[g2][0] && s_mean[g1][1] == s_mean[g2][1] && s_mean[g1][2] == s_mean[g2][2])
+                        s_heft[g2] = 0.0;
+            }
+            // heft floor / clip / NaN, renormalise (:2789-2799)
+            double sum = 0.0;
+            for (int k = 0; k < K; ++k) {
+                double& h = s_heft[k];
+                if (h < DBL_MIN) h = DBL_MIN;
+                else if (h > 1.0) h = 1.0;
+                else if (isnan(h)) h = 1.0 / K;
+                sum += h;
+            }
+            if (sum < 1.0 - DBL_EPSILON || sum > 1.0 + DBL_EPSILON)
+                for (int k = 0; k < K; ++k) s_heft[k] /= sum;
+            // convergence test of em_iterate (:2447-2465)
+            const double avg = st[K * EM_NSTAT] / a.n_total;
+            if (a.trace) a.trace[(size_t)fit * a.iters + a.iter] = avg;
+            a.iters_run[fit] = a.iter + 1;
+            if (!isfinite(avg)) { a.done[fit] = 2; }
+            else if (fabs(a.old_avg[fit] - avg) <= DBL_EPSILON) { a.done[fit] = 1; }
+            a.old_avg[fit] = avg;
+        }
+        __syncthreads();
+        if (g < K) {
+            heft = s_heft[g];
+            hefts[g] = heft;
+            for (int d = 0; d < 3; ++d) means[g * 3 + d] = mean[d];
+            for (int k = 0; k < 9; ++k) fcovs[g * 9 + k] = C[k];
+        }
+        // statistics consumed: zero them for the next E-step
+        for (int i = g; i < K * EM_NSTAT + 1; i += blockDim.x) st[i] = 0.0;
+    }
+    // ---- init_constants for the next E-step (also floors the hefts at DBL_MIN, :1040-1045)
+    if (g < K) {
+        if (heft < DBL_MIN) { heft = DBL_MIN; hefts[g] = heft; }
+        em_constants(mean, C, heft, a.comps + ((size_t)fit * K + g) * EM_COMP_STRIDE);
+    }
+}
+
+#endif

@@ -14,6 +14,7 @@
 #include "mc_rollout_sm100.cuh"
 #include "mc_philox2_sm100.cuh"
 #include "gmm_sm100.cuh"
+#include "em_sm100.cuh"
 #include "peaks_sm100.cuh"
 
 static thread_local char g_err[512] = "";
@@ -67,6 +68,13 @@ struct mcsim_cuda_ctx {
     // GMM state
     DevBuf gmm_comps, gmm_stats, gmm_hist, gmm_counts, gmm_normals, gmm_steps, gmm_prob, gmm_pre, gmm_post, gmm_trunc, gmm_nout, gmm_deg;
     double* h_gmm = nullptr;  // pinned staging
+    // EM state
+    DevBuf em_x, em_comps, em_hefts, em_means, em_fcovs, em_stats, em_old, em_done, em_iters, em_trace;
+    EmLaunch em;
+    bool em_prepared = false;
+    bool em_x_valid = false;
+    uint64_t em_x_n = 0;
+    int em_x_fits = 0;
     uint64_t h2d_bytes = 0, d2h_bytes = 0;  // bytes copied by the last run call
 };
 
@@ -107,6 +115,8 @@ extern "C" void mcsim_cuda_destroy(mcsim_cuda_ctx* c) {
     c->plan.release(); c->z0.release(); c->counters.release(); c->counts.release();
     c->poses.release(); c->clearance.release();
     c->hulls_d.release(); c->pairs_d.release(); c->sat2.release();
+    c->em_x.release(); c->em_comps.release(); c->em_hefts.release(); c->em_means.release(); c->em_fcovs.release();
+    c->em_stats.release(); c->em_old.release(); c->em_done.release(); c->em_iters.release(); c->em_trace.release();
     c->gmm_comps.release(); c->gmm_stats.release(); c->gmm_hist.release(); c->gmm_counts.release();
     c->gmm_normals.release(); c->gmm_steps.release(); c->gmm_prob.release(); c->gmm_pre.release();
     c->gmm_post.release(); c->gmm_trunc.release(); c->gmm_nout.release(); c->gmm_deg.release();
@@ -728,4 +738,150 @@ extern "C" int mcsim_cuda_gmm_truncate(mcsim_cuda_ctx* c, const mcsim_gmm_trunca
 extern "C" void mcsim_cuda_io_bytes(mcsim_cuda_ctx* c, uint64_t* h2d, uint64_t* d2h) {
     if (h2d) *h2d = c ? c->h2d_bytes : 0;
     if (d2h) *d2h = c ? c->d2h_bytes : 0;
+}
+
+// ---- EM fit (BASELINE config 5) ---------------------------------------------------------------------
+typedef void (*em_kernel_t)(const EmLaunch);
+template <int K>
+static void em_pick(em_kernel_t& k0, em_kernel_t& k1) {
+    k0 = em_estep_kernel<K, 0>;
+    k1 = nullptr;
+    if constexpr (K > 8) k1 = em_estep_kernel<K, 8>;
+}
+static bool em_kernels(int K, em_kernel_t& k0, em_kernel_t& k1) {
+    switch (K) {
+        case 1: em_pick<1>(k0, k1); return true;    case 2: em_pick<2>(k0, k1); return true;
+        case 3: em_pick<3>(k0, k1); return true;    case 4: em_pick<4>(k0, k1); return true;
+        case 5: em_pick<5>(k0, k1); return true;    case 6: em_pick<6>(k0, k1); return true;
+        case 7: em_pick<7>(k0, k1); return true;    case 8: em_pick<8>(k0, k1); return true;
+        case 9: em_pick<9>(k0, k1); return true;    case 10: em_pick<10>(k0, k1); return true;
+        case 11: em_pick<11>(k0, k1); return true;  case 12: em_pick<12>(k0, k1); return true;
+        case 13: em_pick<13>(k0, k1); return true;  case 14: em_pick<14>(k0, k1); return true;
+        case 15: em_pick<15>(k0, k1); return true;  case 16: em_pick<16>(k0, k1); return true;
+    }
+    return false;
+}
+
+extern "C" int mcsim_cuda_em_prepare(mcsim_cuda_ctx* c, const mcsim_em_params* p) {
+    if (!c || !p) return fail(MCSIM_ERR_ARG, "em: NULL context or params");
+    if (p->K < 1 || p->K > MCSIM_MAX_GAUSSIANS) return fail(MCSIM_ERR_ARG, "em: K=%d out of range 1..%d", p->K, MCSIM_MAX_GAUSSIANS);
+    if (p->n_fits < 1 || p->n_fits > 65535) return fail(MCSIM_ERR_ARG, "em: n_fits=%d out of range 1..65535", p->n_fits);
+    if (p->iters < 0) return fail(MCSIM_ERR_ARG, "em: negative iteration count");
+    if (!p->hefts || !p->means || !p->fcovs) return fail(MCSIM_ERR_ARG, "em: initial parameters are NULL (seed mode is keep_existing)");
+    if (!p->x && !(c->em_x_valid && c->em_x_n == p->n && c->em_x_fits == p->n_fits))
+        return fail(MCSIM_ERR_ARG, "em: x is NULL and no resident samples of this shape");
+    CK(cudaSetDevice(c->device));
+    const int K = p->K, F = p->n_fits;
+    const size_t nx = size_t(F) * 3 * p->n;
+    c->h2d_bytes = sizeof(double) * size_t(F) * K * 13;
+    if (p->x) {
+        CK(c->em_x.reserve(sizeof(float) * (nx ? nx : 1)));
+        if (nx) CK(cudaMemcpyAsync(c->em_x.p, p->x, sizeof(float) * nx, cudaMemcpyHostToDevice, c->stream));
+        c->em_x_valid = true; c->em_x_n = p->n; c->em_x_fits = F;
+        c->h2d_bytes += sizeof(float) * nx;
+    }
+    const int iters = p->iters > 0 ? p->iters : 1;
+    CK(c->em_comps.reserve(sizeof(float) * size_t(F) * K * EM_COMP_STRIDE));
+    CK(c->em_hefts.reserve(sizeof(double) * size_t(F) * K));
+    CK(c->em_means.reserve(sizeof(double) * size_t(F) * K * 3));
+    CK(c->em_fcovs.reserve(sizeof(double) * size_t(F) * K * 9));
+    CK(c->em_stats.reserve(sizeof(double) * size_t(F) * (K * EM_NSTAT + 1)));
+    CK(c->em_old.reserve(sizeof(double) * F));
+    CK(c->em_done.reserve(sizeof(int) * F));
+    CK(c->em_iters.reserve(sizeof(int) * F));
+    CK(c->em_trace.reserve(sizeof(double) * size_t(F) * iters));
+    CK(cudaMemcpyAsync(c->em_hefts.p, p->hefts, sizeof(double) * size_t(F) * K, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->em_means.p, p->means, sizeof(double) * size_t(F) * K * 3, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->em_fcovs.p, p->fcovs, sizeof(double) * size_t(F) * K * 9, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemsetAsync(c->em_stats.p, 0, sizeof(double) * size_t(F) * (K * EM_NSTAT + 1), c->stream));
+    CK(cudaMemsetAsync(c->em_done.p, 0, sizeof(int) * F, c->stream));
+    CK(cudaMemsetAsync(c->em_iters.p, 0, sizeof(int) * F, c->stream));
+    {   // old_avg_log_p = -inf (:2436); trace = NaN
+        std::vector<double> init(size_t(F) * iters + F);
+        for (int f = 0; f < F; ++f) init[f] = -INFINITY;
+        for (size_t i = 0; i < size_t(F) * iters; ++i) init[F + i] = NAN;
+        CK(cudaMemcpyAsync(c->em_old.p, init.data(), sizeof(double) * F, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->em_trace.p, init.data() + F, sizeof(double) * size_t(F) * iters, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaStreamSynchronize(c->stream));
+    }
+    EmLaunch& a = c->em;
+    a.x = (const float*)c->em_x.p;
+    a.n = p->n;
+    a.n_total = double(p->n_total ? p->n_total : p->n);
+    a.K = K; a.n_fits = F; a.iters = p->iters; a.iter = 0;
+    a.var_floor = p->var_floor > 0 ? p->var_floor : DBL_MIN;
+    a.comps = (float*)c->em_comps.p; a.hefts = (double*)c->em_hefts.p; a.means = (double*)c->em_means.p;
+    a.fcovs = (double*)c->em_fcovs.p; a.stats = (double*)c->em_stats.p; a.old_avg = (double*)c->em_old.p;
+    a.done = (int*)c->em_done.p; a.iters_run = (int*)c->em_iters.p; a.trace = (double*)c->em_trace.p;
+    em_mstep_kernel<<<F, 32, 0, c->stream>>>(a, 1);
+    ++c->launches;
+    CK(cudaGetLastError());
+    c->em_prepared = true;
+    return MCSIM_OK;
+}
+
+extern "C" int mcsim_cuda_em_estep(mcsim_cuda_ctx* c) {
+    if (!c || !c->em_prepared) return fail(MCSIM_ERR_ARG, "em_estep: mcsim_cuda_em_prepare has not been called");
+    CK(cudaSetDevice(c->device));
+    em_kernel_t k0, k1;
+    if (!em_kernels(c->em.K, k0, k1)) return fail(MCSIM_ERR_ARG, "em_estep: bad K");
+    // chunks per fit: fill the machine with whole waves (4 CTAs of 256 threads per SM), but keep at
+    // least ~8 samples per thread so the per-CTA reduction stays small next to the streaming loop
+    const unsigned long long per_cta = 256ull * 8;
+    unsigned long long chunks = (c->em.n + per_cta - 1) / per_cta;
+    const unsigned long long cap = (unsigned long long)(c->n_sm * 4 + c->em.n_fits - 1) / c->em.n_fits;
+    if (chunks > cap) chunks = cap;
+    if (chunks < 1) chunks = 1;
+    const dim3 grid((unsigned)chunks, (unsigned)c->em.n_fits);
+    k0<<<grid, 256, 0, c->stream>>>(c->em);
+    ++c->launches;
+    if (k1) { k1<<<grid, 256, 0, c->stream>>>(c->em); ++c->launches; }
+    CK(cudaGetLastError());
+    return MCSIM_OK;
+}
+
+extern "C" int mcsim_cuda_em_mstep(mcsim_cuda_ctx* c) {
+    if (!c || !c->em_prepared) return fail(MCSIM_ERR_ARG, "em_mstep: mcsim_cuda_em_prepare has not been called");
+    CK(cudaSetDevice(c->device));
+    em_mstep_kernel<<<c->em.n_fits, 32, 0, c->stream>>>(c->em, 0);
+    ++c->launches;
+    ++c->em.iter;
+    CK(cudaGetLastError());
+    return MCSIM_OK;
+}
+
+extern "C" void* mcsim_cuda_em_stats(mcsim_cuda_ctx* c, uint64_t* n_doubles) {
+    if (!c || !c->em_prepared) return nullptr;
+    if (n_doubles) *n_doubles = uint64_t(c->em.n_fits) * (c->em.K * EM_NSTAT + 1);
+    return c->em_stats.p;
+}
+
+extern "C" int mcsim_cuda_em_collect(mcsim_cuda_ctx* c, mcsim_em_result* r) {
+    if (!c || !r || !c->em_prepared) return fail(MCSIM_ERR_ARG, "em_collect: nothing prepared");
+    CK(cudaSetDevice(c->device));
+    const size_t F = c->em.n_fits, K = c->em.K;
+    c->d2h_bytes = 0;
+    if (r->hefts) { CK(cudaMemcpyAsync(r->hefts, c->em_hefts.p, sizeof(double) * F * K, cudaMemcpyDeviceToHost, c->stream)); c->d2h_bytes += sizeof(double) * F * K; }
+    if (r->means) { CK(cudaMemcpyAsync(r->means, c->em_means.p, sizeof(double) * F * K * 3, cudaMemcpyDeviceToHost, c->stream)); c->d2h_bytes += sizeof(double) * F * K * 3; }
+    if (r->fcovs) { CK(cudaMemcpyAsync(r->fcovs, c->em_fcovs.p, sizeof(double) * F * K * 9, cudaMemcpyDeviceToHost, c->stream)); c->d2h_bytes += sizeof(double) * F * K * 9; }
+    if (r->avg_log_p && c->em.iters > 0) CK(cudaMemcpyAsync(r->avg_log_p, c->em_trace.p, sizeof(double) * F * c->em.iters, cudaMemcpyDeviceToHost, c->stream));
+    if (r->iters_run) CK(cudaMemcpyAsync(r->iters_run, c->em_iters.p, sizeof(int) * F, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return MCSIM_OK;
+}
+
+extern "C" int mcsim_cuda_em_fit(mcsim_cuda_ctx* c, const mcsim_em_params* p, mcsim_em_result* r) {
+    if (!r) return fail(MCSIM_ERR_ARG, "em_fit: result is NULL");
+    int rc = mcsim_cuda_em_prepare(c, p);
+    if (rc) return rc;
+    CK(cudaEventRecord(c->ev0, c->stream));
+    for (int it = 0; it < p->iters; ++it) {
+        if ((rc = mcsim_cuda_em_estep(c))) return rc;
+        if ((rc = mcsim_cuda_em_mstep(c))) return rc;
+    }
+    CK(cudaEventRecord(c->ev1, c->stream));
+    rc = mcsim_cuda_em_collect(c, r);
+    if (rc) return rc;
+    CK(cudaEventElapsedTime(&r->kernel_ms, c->ev0, c->ev1));
+    return MCSIM_OK;
 }

@@ -41,6 +41,20 @@ class McResult(C.Structure):
     ]
 
 
+class EmParams(C.Structure):
+    _fields_ = [
+        ("K", C.c_int), ("n_fits", C.c_int), ("n", C.c_uint64), ("n_total", C.c_uint64),
+        ("x", _fp), ("hefts", _dp), ("means", _dp), ("fcovs", _dp), ("iters", C.c_int), ("var_floor", C.c_double),
+    ]
+
+
+class EmResult(C.Structure):
+    _fields_ = [
+        ("hefts", _dp), ("means", _dp), ("fcovs", _dp), ("avg_log_p", _dp), ("iters_run", C.POINTER(C.c_int)),
+        ("kernel_ms", C.c_float),
+    ]
+
+
 class GmmTruncateParams(C.Structure):
     _fields_ = [
         ("K", C.c_int), ("weights", _dp), ("means", _dp), ("covs", _dp),
@@ -106,6 +120,13 @@ def lib():
         L.mcsim_host_normals.argtypes = [C.c_uint64, C.c_uint32, C.c_int, C.c_int, _dp]
         L.mcsim_cuda_gmm_truncate.argtypes = [vp, C.POINTER(GmmTruncateParams), C.POINTER(GmmTruncateResult)]
         L.mcsim_cuda_gmm_run.argtypes = [vp, C.POINTER(McParams), C.POINTER(GmmRunParams), C.POINTER(GmmRunResult)]
+        L.mcsim_cuda_em_fit.argtypes = [vp, C.POINTER(EmParams), C.POINTER(EmResult)]
+        L.mcsim_cuda_em_prepare.argtypes = [vp, C.POINTER(EmParams)]
+        L.mcsim_cuda_em_estep.argtypes = [vp]
+        L.mcsim_cuda_em_mstep.argtypes = [vp]
+        L.mcsim_cuda_em_collect.argtypes = [vp, C.POINTER(EmResult)]
+        L.mcsim_cuda_em_stats.argtypes = [vp, C.POINTER(C.c_uint64)]
+        L.mcsim_cuda_em_stats.restype = vp
         L.mcsim_cuda_io_bytes.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.mcsim_cuda_io_bytes.restype = None
         _lib = L
@@ -300,6 +321,72 @@ class Context:
         check(lib().mcsim_cuda_gmm_run(self._h, C.byref(p), C.byref(g), C.byref(r)))
         out.update(P=float(r.P), degenerate=int(r.degenerate), kernel_ms=float(r.kernel_ms))
         return out
+
+    # ---- EM fit (BASELINE config 5; replaces arma::gmm_full::learn(keep_existing), gmm_full_meat.hpp:764-890)
+    def _em_params(self, x, hefts, means, fcovs, iters, var_floor, n_total):
+        h = np.ascontiguousarray(hefts, dtype=np.float64)
+        F, K = (1, h.shape[0]) if h.ndim == 1 else h.shape
+        m = np.ascontiguousarray(means, dtype=np.float64).reshape(F, K, 3)
+        cv = np.ascontiguousarray(fcovs, dtype=np.float64).reshape(F, K, 9)
+        p = EmParams()
+        keep = [h, m, cv]
+        if x is not None:
+            xx = np.ascontiguousarray(x, dtype=np.float32).reshape(F, 3, -1)
+            keep.append(xx)
+            p.x, p.n = xx.ctypes.data_as(_fp), xx.shape[2]
+        else:
+            p.n = int(self._em_n)
+        self._em_n = int(p.n)
+        p.K, p.n_fits, p.n_total = K, F, int(n_total)
+        p.hefts, p.means, p.fcovs = dptr(h), dptr(m), dptr(cv)
+        p.iters, p.var_floor = int(iters), float(var_floor)
+        return p, keep, (F, K)
+
+    def _em_result(self, F, K, iters):
+        out = dict(hefts=np.zeros((F, K)), means=np.zeros((F, K, 3)), fcovs=np.zeros((F, K, 3, 3)),
+                   avg_log_p=np.full((F, max(iters, 1)), np.nan), iters_run=np.zeros(F, dtype=np.int32))
+        r = EmResult()
+        r.hefts, r.means, r.fcovs, r.avg_log_p = dptr(out["hefts"]), dptr(out["means"]), dptr(out["fcovs"]), dptr(out["avg_log_p"])
+        r.iters_run = out["iters_run"].ctypes.data_as(C.POINTER(C.c_int))
+        return r, out
+
+    def em_fit(self, x, hefts, means, fcovs, iters, var_floor=1e-10):
+        """x: [F, 3, n] (or [3, n]) FP32 samples, component-major per fit, or None to reuse the resident ones;
+        hefts [F, K], means [F, K, 3], fcovs [F, K, 3, 3]: initial parameters.  Returns a dict."""
+        p, keep, (F, K) = self._em_params(x, hefts, means, fcovs, iters, var_floor, 0)
+        r, out = self._em_result(F, K, iters)
+        check(lib().mcsim_cuda_em_fit(self._h, C.byref(p), C.byref(r)))
+        out["kernel_ms"] = float(r.kernel_ms)
+        return out
+
+    def em_prepare(self, x, hefts, means, fcovs, iters, var_floor=1e-10, n_total=0):
+        p, keep, self._em_shape = self._em_params(x, hefts, means, fcovs, iters, var_floor, n_total)
+        self._em_iters = int(iters)
+        check(lib().mcsim_cuda_em_prepare(self._h, C.byref(p)))
+
+    def em_estep(self):
+        check(lib().mcsim_cuda_em_estep(self._h))
+
+    def em_mstep(self):
+        check(lib().mcsim_cuda_em_mstep(self._h))
+
+    def em_collect(self):
+        F, K = self._em_shape
+        r, out = self._em_result(F, K, self._em_iters)
+        check(lib().mcsim_cuda_em_collect(self._h, C.byref(r)))
+        return out
+
+    def em_stats_tensor(self):
+        """torch float64 view (no copy) of the device statistics block [F * (K * 10 + 1)] for the all-reduce."""
+        import torch
+        n = C.c_uint64()
+        ptr = lib().mcsim_cuda_em_stats(self._h, C.byref(n))
+
+        class _Raw:
+            pass
+        raw = _Raw()
+        raw.__cuda_array_interface__ = dict(shape=(int(n.value),), typestr="<f8", version=2, data=(int(ptr), False))
+        return torch.as_tensor(raw, device="cuda:%d" % self.device)
 
     def gmm_truncate(self, weights, means, covs, n_samples, mode=MODE_PHILOX, counts=None, normals=None,
                      seed=0x5AFEC0DE, stream_id=0):

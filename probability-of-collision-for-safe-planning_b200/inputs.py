@@ -61,3 +61,29 @@ def save_plan_json(plan, path):
     d = {k: (np.asarray(v).tolist() if isinstance(v, np.ndarray) else v) for k, v in plan.items()}
     with open(path, "w") as f:
         json.dump(d, f, indent=0)
+
+
+def synthetic_em_problem(seed, n, K, centre=(3.0, 1.0, 1.5)):
+    """BASELINE config 5 workload generator: n samples of a seeded 3-component mixture
+    around `centre` (a trajectory pose; covariances of 1e-3 scale, like the propagated beliefs), and
+    `keep_existing` initial parameters for a K-component fit (seeded perturbations of sample points).
+    Returns (x float32 [3, n], hefts [K], means [K, 3], fcovs [K, 3, 3])."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    c = np.asarray(centre, dtype=np.float64)
+    mus = c + rng.normal(0.0, 0.08, size=(3, 3))
+    covs = []
+    for _ in range(3):
+        a = rng.normal(0.0, 1.0, size=(3, 3))
+        covs.append(1e-3 * (a @ a.T / 3.0 + 0.5 * np.eye(3)))
+    w = np.array([0.5, 0.3, 0.2])
+    comp = rng.choice(3, size=n, p=w)
+    x = np.empty((n, 3))
+    for g in range(3):
+        idx = np.nonzero(comp == g)[0]
+        x[idx] = rng.multivariate_normal(mus[g], covs[g], size=idx.size)
+    x32 = np.ascontiguousarray(x.T, dtype=np.float32)
+    pick = rng.choice(n, size=K, replace=False)
+    means = x32.T[pick].astype(np.float64) + rng.normal(0.0, 0.01, size=(K, 3))
+    fcovs = np.tile(np.cov(x32.astype(np.float64)) + 1e-6 * np.eye(3), (K, 1, 1))
+    hefts = np.full(K, 1.0 / K)
+    return x32, hefts, means, fcovs

@@ -1,0 +1,104 @@
+"""GPU parity tests of the EM operator (BASELINE config 5) through the C ABI (mcsim_cuda_em_*).
+
+Oracle: the reference repository's vendored Armadillo 8.400.0 gmm_full::learn(keep_existing, km_iter = 0)
+(SURVEY.md A13): committed known-answer vectors tests/golden/em_K*.npz (made by tests/golden/make_em.py)
+and, where oracle/_ref is present, live runs on fresh seeds.  Bar (BASELINE.json north_star): hefts,
+means and covariances within 1e-4 relative (covariances relative to the largest entry of the
+component's matrix; means relative to max(|mean|, 1))."""
+import numpy as np
+import pytest
+
+from conftest import golden
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-4
+
+
+def _errors(out, hefts, means, fcovs, f=0):
+    eh = np.max(np.abs(out["hefts"][f] - hefts) / np.maximum(np.abs(hefts), 1e-3))
+    em = np.max(np.abs(out["means"][f] - means) / np.maximum(np.abs(means), 1.0))
+    scale = np.max(np.abs(fcovs), axis=(1, 2), keepdims=True)
+    ec = np.max(np.abs(out["fcovs"][f] - fcovs) / scale)
+    return eh, em, ec
+
+
+@pytest.mark.parametrize("K", [1, 3, 8, 16])
+def test_em_matches_armadillo_golden(ctx, K):
+    g = golden("em_K%d.npz" % K)
+    for it in (1, 5, 20):
+        out = ctx.em_fit(g["x"], g["hefts0"], g["means0"], g["fcovs0"], it)
+        eh, em, ec = _errors(out, g["hefts_%d" % it], g["means_%d" % it], g["fcovs_%d" % it])
+        print("K=%d iters=%d: heft err %.2e mean err %.2e cov err %.2e" % (K, it, eh, em, ec))
+        assert out["iters_run"][0] == it
+        assert max(eh, em, ec) < RTOL
+        np.testing.assert_allclose(out["hefts"].sum(), 1.0, atol=1e-12)
+
+
+def test_em_batched_fits_equal_single_fits(ctx):
+    """n_fits > 1 in one call == the same fits one by one (independent accumulators per fit)."""
+    import pcoll_b200
+    probs = [pcoll_b200.inputs.synthetic_em_problem(100 + f, 5001, 3, centre=(f * 0.5, 1.0, 0.3 * f)) for f in range(5)]
+    x = np.stack([p[0] for p in probs]); h = np.stack([p[1] for p in probs])
+    m = np.stack([p[2] for p in probs]); c = np.stack([p[3] for p in probs])
+    both = ctx.em_fit(x, h, m, c, 4)
+    for f in range(5):
+        one = ctx.em_fit(x[f], h[f], m[f], c[f], 4)
+        np.testing.assert_allclose(both["means"][f], one["means"][0], rtol=1e-9, atol=1e-12)
+        np.testing.assert_allclose(both["fcovs"][f], one["fcovs"][0], rtol=1e-6, atol=1e-12)
+        np.testing.assert_allclose(both["hefts"][f], one["hefts"][0], rtol=1e-9)
+
+
+def test_em_vs_live_reference_ragged_sizes(ctx):
+    import oracle_ref
+    import pcoll_b200
+    if not oracle_ref.available():
+        pytest.skip("oracle/_ref not built")
+    for seed, n, K in ((1, 257, 2), (2, 1000, 5), (3, 33333, 12)):
+        x, h, m, c = pcoll_b200.inputs.synthetic_em_problem(seed, n, K)
+        rm, rc, rh, rl = oracle_ref.em_fit(x.T.astype(np.float64), m, c.reshape(K, 9), h, 3)
+        out = ctx.em_fit(x, h, m, c, 3)
+        eh, em, ec = _errors(out, rh, rm, rc.reshape(K, 3, 3))
+        print("n=%d K=%d: heft err %.2e mean err %.2e cov err %.2e" % (n, K, eh, em, ec))
+        assert max(eh, em, ec) < RTOL
+
+
+def test_em_log_likelihood_is_monotone_and_resident_reuse(ctx):
+    """EM never decreases the average log-likelihood (size-independent property, full config-5 size);
+    second call reuses the resident samples (x = None)."""
+    import pcoll_b200
+    x, h, m, c = pcoll_b200.inputs.synthetic_em_problem(7, 1_000_000, 6)
+    out = ctx.em_fit(x, h, m, c, 10)
+    tr = out["avg_log_p"][0]
+    assert np.all(np.isfinite(tr)) and np.all(np.diff(tr) > -1e-5), tr
+    again = ctx.em_fit(None, h, m, c, 10)
+    np.testing.assert_allclose(again["means"], out["means"], rtol=1e-6)
+
+
+def test_em_split_api_two_shards_equal_whole(ctx):
+    """estep on two half shards + summed statistics + mstep == the unsharded fit (what the NCCL
+    all-reduce does across GPUs), run on one device with two contexts."""
+    import torch
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    x, h, m, c = pcoll_b200.inputs.synthetic_em_problem(11, 20000, 4)
+    whole = ctx.em_fit(x, h, m, c, 5)
+    a, b = abi.Context(0), abi.Context(0)
+    try:
+        a.em_prepare(x[:, :10000], h, m, c, 5, n_total=20000)
+        b.em_prepare(x[:, 10000:], h, m, c, 5, n_total=20000)
+        for _ in range(5):
+            a.em_estep(); b.em_estep()
+            torch.cuda.synchronize()
+            sa, sb = a.em_stats_tensor(), b.em_stats_tensor()
+            tot = sa + sb
+            sa.copy_(tot); sb.copy_(tot)
+            torch.cuda.synchronize()
+            a.em_mstep(); b.em_mstep()
+        ra, rb = a.em_collect(), b.em_collect()
+    finally:
+        a.close(); b.close()
+    np.testing.assert_array_equal(ra["means"], rb["means"])
+    np.testing.assert_allclose(ra["means"], whole["means"], rtol=1e-6)
+    np.testing.assert_allclose(ra["fcovs"], whole["fcovs"], rtol=1e-4, atol=1e-9)
+    np.testing.assert_allclose(ra["hefts"], whole["hefts"], rtol=1e-5)
