@@ -268,6 +268,46 @@ int mcsim_cuda_em_collect(mcsim_cuda_ctx* ctx, mcsim_em_result* r);
  * then sum of log-likelihoods. */
 void* mcsim_cuda_em_stats(mcsim_cuda_ctx* ctx, uint64_t* n_doubles);
 
+/* ---- batched plan scoring (BASELINE.json config 4) ------------------------------------------- */
+/* The Philox-mode rollout law of mcsim_cuda_mc_run (EKF_GaussProp, MCSimulator.h:649-864, one
+ * real-robot / EKF thread and one particle per rollout) for n_plans plans of T waypoints against the
+ * current scene, `rollouts` rollouts per plan; rollout ids are (plan_offset + plan) << 32 | rollout, so
+ * the result of a plan does not depend on how plans are split over calls or GPUs. */
+typedef struct {
+    int T;                       /* waypoints per plan, 2..MCSIM_MAX_WAYPOINTS */
+    int n_plans;
+    const double* trajectories;  /* [n_plans][3][T]   component-major per plan (setTrajectory layout) */
+    const double* odometry;      /* [n_plans][3][T-1] component-major per plan (setOdometry layout) */
+    double alphas[4];
+    double Q;
+    int n_landmarks;             /* must be 8 on this path */
+    const double* landmarks;
+    double cov0[9];
+    uint64_t rollouts;           /* per plan, <= 2^32 */
+    uint64_t plan_offset;        /* global id of plan 0 (shards of a batch) */
+    int estimator;               /* MCSIM_EST_* */
+    int early_exit;
+    uint64_t seed;
+    double margin;               /* broad phase: rollouts within `margin` metres of the nominal waypoint
+                                    test only the boxes within reach of it (exact, see score_sm100.cuh);
+                                    < 0: every live pair at every step */
+} mcsim_score_params;
+
+typedef struct {
+    uint64_t* hits;              /* [n_plans] optional */
+    double* P;                   /* [n_plans] optional: hits / rollouts */
+    uint64_t executed_steps;     /* rollout-steps executed */
+    uint64_t pair_tests;         /* SAT pair tests executed (nominal = executed_steps x live pairs) */
+    float kernel_ms;
+} mcsim_score_result;
+
+int mcsim_cuda_score_plans(mcsim_cuda_ctx* ctx, const mcsim_score_params* p, mcsim_score_result* r);
+/* Device-resident form: prepare uploads the plan tables, launch scores them (asynchronous, may be
+ * repeated), collect downloads hits / counters and zeroes them. */
+int mcsim_cuda_score_prepare(mcsim_cuda_ctx* ctx, const mcsim_score_params* p);
+int mcsim_cuda_score_launch(mcsim_cuda_ctx* ctx);
+int mcsim_cuda_score_collect(mcsim_cuda_ctx* ctx, mcsim_score_result* r);
+
 /* bytes the last *_run call copied host->device and device->host (bench.py's e2e accounting) */
 void mcsim_cuda_io_bytes(mcsim_cuda_ctx* ctx, uint64_t* h2d, uint64_t* d2h);
 

@@ -112,6 +112,124 @@ __device__ __forceinline__ void move2(f2 p[3], const f2 u[3]) {
     p[2] = wrap2(add2(add2(p[2], u[0]), u[2]));
 }
 
+// state of the two rollouts of a thread: particle, real robot, EKF mean and covariance
+// (symmetric: s00 s01 s02 s11 s12 s22)
+struct Rollout2 {
+    f2 p[3], real[3], mu[3], S[6];
+};
+
+// x0 = mu0 + L z (initParticles), real robot and EKF at the nominal start (MCSimulator.h:656-657)
+template <int EST>
+__device__ __forceinline__ void init2(Rollout2& st, const float* mu0, unsigned long long id0, unsigned long long id1, unsigned k0, unsigned k1) {
+    const Philox2 r = philox_pair(id0, id1, 0u, unsigned(mcsim_rng::PURPOSE_INIT), k0, k1);
+    f2 z0, z1, z2, z3;
+    box_muller2(r.a.x, r.a.y, r.b.x, r.b.y, z0, z1);
+    box_muller2(r.a.z, r.a.w, r.b.z, r.b.w, z2, z3);
+    st.p[0] = fma2(z0, c_mc.chol[0], mu0[0]);
+    st.p[1] = fma2(z0, c_mc.chol[1], fma2(z1, c_mc.chol[2], mu0[1]));
+    st.p[2] = fma2(z0, c_mc.chol[3], fma2(z1, c_mc.chol[4], fma2(z2, c_mc.chol[5], mu0[2])));
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { st.mu[k] = bc(mu0[k]); st.real[k] = (EST == MCSIM_EST_CLOSEDLOOP) ? st.p[k] : bc(mu0[k]); }
+    st.S[0] = bc(c_mc.chol[0] * c_mc.chol[0]);
+    st.S[1] = bc(c_mc.chol[0] * c_mc.chol[1]);
+    st.S[2] = bc(c_mc.chol[0] * c_mc.chol[3]);
+    st.S[3] = bc(c_mc.chol[1] * c_mc.chol[1] + c_mc.chol[2] * c_mc.chol[2]);
+    st.S[4] = bc(c_mc.chol[1] * c_mc.chol[3] + c_mc.chol[2] * c_mc.chol[4]);
+    st.S[5] = bc(c_mc.chol[3] * c_mc.chol[3] + c_mc.chol[4] * c_mc.chol[4] + c_mc.chol[5] * c_mc.chol[5]);
+}
+
+// one step t -> t+1 of both rollouts' real robot + EKF (+ particle); r = plan record of waypoint t
+// (MC_PLAN2_STRIDE floats, the next record follows it)
+template <int EST, int NL>
+__device__ __forceinline__ void step2(Rollout2& st, const float* r, int t, unsigned long long id0, unsigned long long id1, unsigned k0, unsigned k1) {
+    f2 (&p)[3] = st.p;
+    f2 (&real)[3] = st.real;
+    f2 (&mu)[3] = st.mu;
+    f2 (&S)[6] = st.S;
+    // ---- step t -> t+1 of this rollout's own real robot + EKF
+    // noise: block 0 = (rot1, trans, rot2, obs 0), block 1 = obs 1..4, block 2 = obs 5..7
+    f2 zn[4 * ((3 + NL + 3) / 4)];
+#pragma unroll
+    for (int jb = 0; jb < (3 + NL + 3) / 4; ++jb) {
+        const Philox2 w = philox_pair(id0, id1, unsigned(t * 8 + jb), unsigned(mcsim_rng::PURPOSE_STEP), k0, k1);
+        box_muller2(w.a.x, w.a.y, w.b.x, w.b.y, zn[4 * jb], zn[4 * jb + 1]);
+        box_muller2(w.a.z, w.a.w, w.b.z, w.b.w, zn[4 * jb + 2], zn[4 * jb + 3]);
+    }
+    // applied control (generateL + :719-726): u = u_req = inverseOdometry(mu, x*_{t+1}); u*_0 at t = 0
+    f2 u[3];
+    if (t == 0) {
+        u[0] = bc(r[3]); u[1] = bc(r[4]); u[2] = bc(r[5]);
+    } else {
+        const f2 dx = add2(neg2(mu[0]), r[MC_PLAN2_STRIDE + 0]);
+        const f2 dy = add2(neg2(mu[1]), r[MC_PLAN2_STRIDE + 1]);
+        u[0] = wrap2(sub2(atan2_2(dy, dx), mu[2]));
+        u[1] = sqrt2(fma2(dx, dx, mul2(dy, dy)));
+        u[2] = wrap2(sub2(add2(neg2(mu[2]), r[MC_PLAN2_STRIDE + 2]), u[0]));
+    }
+    // EKF predict: Sigma' = G Sigma G^T + V M V^T (M from the nominal command), mu' = g(mu, u)
+    {
+        f2 sm, cm;
+        sincos2(add2(mu[2], u[0]), sm, cm);
+        const f2 g02 = mul2(neg2(u[1]), sm), g12 = mul2(u[1], cm);
+        const f2 t0 = fma2(g02, S[5], S[2]);  // new s02 before R
+        const f2 t1 = fma2(g12, S[5], S[4]);  // new s12 before R
+        f2 n00 = fma2(g02, add2(S[2], t0), S[0]);
+        f2 n01 = fma2(g02, t1, fma2(g12, S[2], S[1]));
+        f2 n11 = fma2(g12, add2(S[4], t1), S[3]);
+        const f2 am = mul2(g02, r[6]), bm = mul2(g12, r[6]);
+        const f2 c1 = mul2(cm, r[7]), d1 = mul2(sm, r[7]);
+        S[0] = fma2(g02, am, fma2(cm, c1, n00));
+        S[1] = fma2(g12, am, fma2(sm, c1, n01));
+        S[2] = add2(t0, am);
+        S[3] = fma2(g12, bm, fma2(sm, d1, n11));
+        S[4] = add2(t1, bm);
+        S[5] = add2(S[5], r[9]);
+        mu[0] = fma2(u[1], cm, mu[0]);
+        mu[1] = fma2(u[1], sm, mu[1]);
+        mu[2] = wrap2(add2(add2(mu[2], u[0]), u[2]));
+    }
+    // sampleOdometry: u~ = u + z * sqrt(variance), variances from the APPLIED command
+    f2 un[3];
+    {
+        const f2 r1 = mul2(u[0], u[0]), tr = mul2(u[1], u[1]), r2 = mul2(u[2], u[2]);
+        const f2 v0 = fma2(r1, c_mc.nm.alpha[0], mul2(tr, c_mc.nm.alpha[1]));
+        const f2 v1 = fma2(tr, c_mc.nm.alpha[2], mul2(add2(r1, r2), c_mc.nm.alpha[3]));
+        const f2 v2 = fma2(r2, c_mc.nm.alpha[0], mul2(tr, c_mc.nm.alpha[1]));
+        un[0] = fma2(zn[0], sqrt2(v0), u[0]);
+        un[1] = fma2(zn[1], sqrt2(v1), u[1]);
+        un[2] = fma2(zn[2], sqrt2(v2), u[2]);
+    }
+    move2(real, un);
+    if (EST == MCSIM_EST_REFERENCE) move2(p, un);
+    // 8 sequential scalar range updates (EKFupdate); z_l = |real - m_l| + sqrt(Q) n_l
+#pragma unroll
+    for (int l = 0; l < NL; ++l) {
+        const float lx = c_mc.nm.lx[l], ly = c_mc.nm.ly[l];
+        const f2 ex = add2(real[0], -lx), ey = add2(real[1], -ly);
+        const f2 eq = fma2(ex, ex, mul2(ey, ey));
+        const f2 z = fma2(zn[3 + l], c_mc.sqrtQ, mul2(eq, rsqrt2(eq)));
+        const f2 dx = add2(mu[0], -lx), dy = add2(mu[1], -ly);
+        const f2 qq = fma2(dx, dx, mul2(dy, dy));
+        const f2 rs = rsqrt2(qq);
+        const f2 h0v = mul2(dx, rs), h1v = mul2(dy, rs);
+        const f2 a0 = fma2(S[0], h0v, mul2(S[1], h1v));
+        const f2 a1 = fma2(S[1], h0v, mul2(S[3], h1v));
+        const f2 a2 = fma2(S[2], h0v, mul2(S[4], h1v));
+        const f2 inv = rcp2(fma2(h0v, a0, fma2(h1v, a1, c_mc.nm.Q)));
+        const f2 innov = fma2(neg2(qq), rs, z);
+        const f2 k0v = mul2(a0, inv), k1v = mul2(a1, inv), k2v = mul2(a2, inv);
+        mu[0] = fma2(k0v, innov, mu[0]);
+        mu[1] = fma2(k1v, innov, mu[1]);
+        mu[2] = fma2(k2v, innov, mu[2]);
+        S[0] = fma2(neg2(k0v), a0, S[0]);
+        S[1] = fma2(neg2(k0v), a1, S[1]);
+        S[2] = fma2(neg2(k0v), a2, S[2]);
+        S[3] = fma2(neg2(k1v), a1, S[3]);
+        S[4] = fma2(neg2(k1v), a2, S[4]);
+        S[5] = fma2(neg2(k2v), a2, S[5]);
+    }
+}
+
 template <bool EARLY_EXIT, int EST, int NL>
 __global__ void __launch_bounds__(128, 4) mc_philox2_kernel(const McLaunch a) {
     extern __shared__ __align__(16) float4 s_tab[];
@@ -136,34 +254,14 @@ __global__ void __launch_bounds__(128, 4) mc_philox2_kernel(const McLaunch a) {
         const bool valid0 = i0 < a.n;
         const bool valid1 = i1 < a.n;
         const unsigned long long id0 = a.offset + i0, id1 = a.offset + i1;
-        // ---- x0 = mu0 + L z (initParticles)
-        f2 p[3];
-        {
-            const Philox2 r = philox_pair(id0, id1, 0u, unsigned(mcsim_rng::PURPOSE_INIT), a.k0, a.k1);
-            f2 z0, z1, z2, z3;
-            box_muller2(r.a.x, r.a.y, r.b.x, r.b.y, z0, z1);
-            box_muller2(r.a.z, r.a.w, r.b.z, r.b.w, z2, z3);
-            p[0] = fma2(z0, c_mc.chol[0], c_mc.mu0[0]);
-            p[1] = fma2(z0, c_mc.chol[1], fma2(z1, c_mc.chol[2], c_mc.mu0[1]));
-            p[2] = fma2(z0, c_mc.chol[3], fma2(z1, c_mc.chol[4], fma2(z2, c_mc.chol[5], c_mc.mu0[2])));
-        }
-        f2 real[3], mu[3];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) { mu[k] = bc(c_mc.mu0[k]); real[k] = (EST == MCSIM_EST_CLOSEDLOOP) ? p[k] : bc(c_mc.mu0[k]); }
-        // Sigma, symmetric: s00 s01 s02 s11 s12 s22
-        f2 S[6];
-        S[0] = bc(c_mc.chol[0] * c_mc.chol[0]);
-        S[1] = bc(c_mc.chol[0] * c_mc.chol[1]);
-        S[2] = bc(c_mc.chol[0] * c_mc.chol[3]);
-        S[3] = bc(c_mc.chol[1] * c_mc.chol[1] + c_mc.chol[2] * c_mc.chol[2]);
-        S[4] = bc(c_mc.chol[1] * c_mc.chol[3] + c_mc.chol[2] * c_mc.chol[4]);
-        S[5] = bc(c_mc.chol[3] * c_mc.chol[3] + c_mc.chol[4] * c_mc.chol[4] + c_mc.chol[5] * c_mc.chol[5]);
+        Rollout2 st;
+        init2<EST>(st, c_mc.mu0, id0, id1, a.k0, a.k1);
 
         unsigned cnt0 = 0, cnt1 = 0;
         int first0 = -1, first1 = -1;
         for (int t = 0; t < T; ++t) {
             // ---- collision test at waypoint t
-            const f2* q = (EST == MCSIM_EST_CLOSEDLOOP) ? real : p;
+            const f2* q = (EST == MCSIM_EST_CLOSEDLOOP) ? st.real : st.p;
             f2 sn, cs;
             sincos2(q[2], sn, cs);
             bool h0 = false, h1 = false;
@@ -176,89 +274,7 @@ __global__ void __launch_bounds__(128, 4) mc_philox2_kernel(const McLaunch a) {
             if (EARLY_EXIT && __all_sync(0xffffffffu, (cnt0 || !valid0) && (cnt1 || !valid1))) break;
             if (t == T - 1) break;
 
-            // ---- step t -> t+1 of this rollout's own real robot + EKF
-            const float* r = c_plan2 + t * MC_PLAN2_STRIDE;
-            // noise: block 0 = (rot1, trans, rot2, obs 0), block 1 = obs 1..4, block 2 = obs 5..7
-            f2 zn[4 * ((3 + NL + 3) / 4)];
-#pragma unroll
-            for (int jb = 0; jb < (3 + NL + 3) / 4; ++jb) {
-                const Philox2 w = philox_pair(id0, id1, unsigned(t * 8 + jb), unsigned(mcsim_rng::PURPOSE_STEP), a.k0, a.k1);
-                box_muller2(w.a.x, w.a.y, w.b.x, w.b.y, zn[4 * jb], zn[4 * jb + 1]);
-                box_muller2(w.a.z, w.a.w, w.b.z, w.b.w, zn[4 * jb + 2], zn[4 * jb + 3]);
-            }
-            // applied control (generateL + :719-726): u = u_req = inverseOdometry(mu, x*_{t+1}); u*_0 at t = 0
-            f2 u[3];
-            if (t == 0) {
-                u[0] = bc(r[3]); u[1] = bc(r[4]); u[2] = bc(r[5]);
-            } else {
-                const f2 dx = add2(neg2(mu[0]), r[MC_PLAN2_STRIDE + 0]);
-                const f2 dy = add2(neg2(mu[1]), r[MC_PLAN2_STRIDE + 1]);
-                u[0] = wrap2(sub2(atan2_2(dy, dx), mu[2]));
-                u[1] = sqrt2(fma2(dx, dx, mul2(dy, dy)));
-                u[2] = wrap2(sub2(add2(neg2(mu[2]), r[MC_PLAN2_STRIDE + 2]), u[0]));
-            }
-            // EKF predict: Sigma' = G Sigma G^T + V M V^T (M from the nominal command), mu' = g(mu, u)
-            {
-                f2 sm, cm;
-                sincos2(add2(mu[2], u[0]), sm, cm);
-                const f2 g02 = mul2(neg2(u[1]), sm), g12 = mul2(u[1], cm);
-                const f2 t0 = fma2(g02, S[5], S[2]);  // new s02 before R
-                const f2 t1 = fma2(g12, S[5], S[4]);  // new s12 before R
-                f2 n00 = fma2(g02, add2(S[2], t0), S[0]);
-                f2 n01 = fma2(g02, t1, fma2(g12, S[2], S[1]));
-                f2 n11 = fma2(g12, add2(S[4], t1), S[3]);
-                const f2 am = mul2(g02, r[6]), bm = mul2(g12, r[6]);
-                const f2 c1 = mul2(cm, r[7]), d1 = mul2(sm, r[7]);
-                S[0] = fma2(g02, am, fma2(cm, c1, n00));
-                S[1] = fma2(g12, am, fma2(sm, c1, n01));
-                S[2] = add2(t0, am);
-                S[3] = fma2(g12, bm, fma2(sm, d1, n11));
-                S[4] = add2(t1, bm);
-                S[5] = add2(S[5], r[9]);
-                mu[0] = fma2(u[1], cm, mu[0]);
-                mu[1] = fma2(u[1], sm, mu[1]);
-                mu[2] = wrap2(add2(add2(mu[2], u[0]), u[2]));
-            }
-            // sampleOdometry: u~ = u + z * sqrt(variance), variances from the APPLIED command
-            f2 un[3];
-            {
-                const f2 r1 = mul2(u[0], u[0]), tr = mul2(u[1], u[1]), r2 = mul2(u[2], u[2]);
-                const f2 v0 = fma2(r1, c_mc.nm.alpha[0], mul2(tr, c_mc.nm.alpha[1]));
-                const f2 v1 = fma2(tr, c_mc.nm.alpha[2], mul2(add2(r1, r2), c_mc.nm.alpha[3]));
-                const f2 v2 = fma2(r2, c_mc.nm.alpha[0], mul2(tr, c_mc.nm.alpha[1]));
-                un[0] = fma2(zn[0], sqrt2(v0), u[0]);
-                un[1] = fma2(zn[1], sqrt2(v1), u[1]);
-                un[2] = fma2(zn[2], sqrt2(v2), u[2]);
-            }
-            move2(real, un);
-            if (EST == MCSIM_EST_REFERENCE) move2(p, un);
-            // 8 sequential scalar range updates (EKFupdate); z_l = |real - m_l| + sqrt(Q) n_l
-#pragma unroll
-            for (int l = 0; l < NL; ++l) {
-                const float lx = c_mc.nm.lx[l], ly = c_mc.nm.ly[l];
-                const f2 ex = add2(real[0], -lx), ey = add2(real[1], -ly);
-                const f2 eq = fma2(ex, ex, mul2(ey, ey));
-                const f2 z = fma2(zn[3 + l], c_mc.sqrtQ, mul2(eq, rsqrt2(eq)));
-                const f2 dx = add2(mu[0], -lx), dy = add2(mu[1], -ly);
-                const f2 qq = fma2(dx, dx, mul2(dy, dy));
-                const f2 rs = rsqrt2(qq);
-                const f2 h0v = mul2(dx, rs), h1v = mul2(dy, rs);
-                const f2 a0 = fma2(S[0], h0v, mul2(S[1], h1v));
-                const f2 a1 = fma2(S[1], h0v, mul2(S[3], h1v));
-                const f2 a2 = fma2(S[2], h0v, mul2(S[4], h1v));
-                const f2 inv = rcp2(fma2(h0v, a0, fma2(h1v, a1, c_mc.nm.Q)));
-                const f2 innov = fma2(neg2(qq), rs, z);
-                const f2 k0v = mul2(a0, inv), k1v = mul2(a1, inv), k2v = mul2(a2, inv);
-                mu[0] = fma2(k0v, innov, mu[0]);
-                mu[1] = fma2(k1v, innov, mu[1]);
-                mu[2] = fma2(k2v, innov, mu[2]);
-                S[0] = fma2(neg2(k0v), a0, S[0]);
-                S[1] = fma2(neg2(k0v), a1, S[1]);
-                S[2] = fma2(neg2(k0v), a2, S[2]);
-                S[3] = fma2(neg2(k1v), a1, S[3]);
-                S[4] = fma2(neg2(k1v), a2, S[4]);
-                S[5] = fma2(neg2(k2v), a2, S[5]);
-            }
+            step2<EST, NL>(st, c_plan2 + t * MC_PLAN2_STRIDE, t, id0, id1, a.k0, a.k1);
         }
         if (!EARLY_EXIT) my_steps += (unsigned(valid0) + unsigned(valid1)) * unsigned(T);
         if (cnt0 && valid0) { ++my_hits; atomicAdd(&s_hist[first0], 1u); }

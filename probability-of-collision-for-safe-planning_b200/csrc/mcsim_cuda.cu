@@ -15,6 +15,7 @@
 #include "mc_philox2_sm100.cuh"
 #include "gmm_sm100.cuh"
 #include "em_sm100.cuh"
+#include "score_sm100.cuh"
 #include "peaks_sm100.cuh"
 
 static thread_local char g_err[512] = "";
@@ -68,6 +69,11 @@ struct mcsim_cuda_ctx {
     // GMM state
     DevBuf gmm_comps, gmm_stats, gmm_hist, gmm_counts, gmm_normals, gmm_steps, gmm_prob, gmm_pre, gmm_post, gmm_trunc, gmm_nout, gmm_deg;
     double* h_gmm = nullptr;  // pinned staging
+    // scoring state
+    DevBuf pairs_f, sc_plans, sc_hits, sc_counters;
+    ScoreLaunch sc;
+    bool sc_prepared = false;
+    int sc_ee = 0, sc_est = 0;
     // EM state
     DevBuf em_x, em_comps, em_hefts, em_means, em_fcovs, em_stats, em_old, em_done, em_iters, em_trace;
     EmLaunch em;
@@ -115,6 +121,7 @@ extern "C" void mcsim_cuda_destroy(mcsim_cuda_ctx* c) {
     c->plan.release(); c->z0.release(); c->counters.release(); c->counts.release();
     c->poses.release(); c->clearance.release();
     c->hulls_d.release(); c->pairs_d.release(); c->sat2.release();
+    c->pairs_f.release(); c->sc_plans.release(); c->sc_hits.release(); c->sc_counters.release();
     c->em_x.release(); c->em_comps.release(); c->em_hefts.release(); c->em_means.release(); c->em_fcovs.release();
     c->em_stats.release(); c->em_old.release(); c->em_done.release(); c->em_iters.release(); c->em_trace.release();
     c->gmm_comps.release(); c->gmm_stats.release(); c->gmm_hist.release(); c->gmm_counts.release();
@@ -255,6 +262,8 @@ extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int 
     CK(cudaMemcpy(c->hulls_d.p, hd.data(), sizeof(HullD) * hd.size(), cudaMemcpyHostToDevice));
     CK(c->pairs_d.reserve(sizeof(PairD) * (pd.size() ? pd.size() : 1)));
     if (!pd.empty()) CK(cudaMemcpy(c->pairs_d.p, pd.data(), sizeof(PairD) * pd.size(), cudaMemcpyHostToDevice));
+    CK(c->pairs_f.reserve(sizeof(float4) * (pairs.size() ? pairs.size() : 1)));
+    if (!pairs.empty()) CK(cudaMemcpy(c->pairs_f.p, pairs.data(), sizeof(float4) * pairs.size(), cudaMemcpyHostToDevice));
     CK(c->sat2.reserve(sizeof(float4) * (sat2.size() ? sat2.size() : 1)));
     if (!sat2.empty()) CK(cudaMemcpy(c->sat2.p, sat2.data(), sizeof(float4) * sat2.size(), cudaMemcpyHostToDevice));
     c->sat2_n = int(sat2.size());
@@ -882,6 +891,129 @@ extern "C" int mcsim_cuda_em_fit(mcsim_cuda_ctx* c, const mcsim_em_params* p, mc
     CK(cudaEventRecord(c->ev1, c->stream));
     rc = mcsim_cuda_em_collect(c, r);
     if (rc) return rc;
+    CK(cudaEventElapsedTime(&r->kernel_ms, c->ev0, c->ev1));
+    return MCSIM_OK;
+}
+
+// ---- batched plan scoring (BASELINE config 4) -------------------------------------------------------
+typedef void (*score_kernel_t)(const ScoreLaunch);
+static score_kernel_t pick_score(int est, bool ee) {
+    if (est == MCSIM_EST_CLOSEDLOOP) return ee ? score_plans_kernel<MCSIM_EST_CLOSEDLOOP, 8, true> : score_plans_kernel<MCSIM_EST_CLOSEDLOOP, 8, false>;
+    return ee ? score_plans_kernel<MCSIM_EST_REFERENCE, 8, true> : score_plans_kernel<MCSIM_EST_REFERENCE, 8, false>;
+}
+
+extern "C" int mcsim_cuda_score_prepare(mcsim_cuda_ctx* c, const mcsim_score_params* p) {
+    if (!c || !p) return fail(MCSIM_ERR_ARG, "score: NULL context or params");
+    if (!c->scene_set) return fail(MCSIM_ERR_ARG, "score: mcsim_cuda_set_scene has not been called");
+    if (p->T < 2 || p->T > MCSIM_MAX_WAYPOINTS) return fail(MCSIM_ERR_ARG, "score: T=%d out of range 2..%d", p->T, MCSIM_MAX_WAYPOINTS);
+    if (p->n_plans < 1 || !p->trajectories || !p->odometry) return fail(MCSIM_ERR_ARG, "score: no plans");
+    if (p->n_landmarks != 8 || !p->landmarks) return fail(MCSIM_ERR_ARG, "score: this path is built for 8 landmarks (got %d)", p->n_landmarks);
+    if (p->rollouts > (1ull << 32)) return fail(MCSIM_ERR_ARG, "score: more than 2^32 rollouts per plan");
+    CK(cudaSetDevice(c->device));
+    const int T = p->T, L = p->n_landmarks, NP = p->n_plans;
+    McPlanConst pc;
+    memset(&pc, 0, sizeof(pc));
+    pc.T = T;
+    double Lo[6];
+    if (!chol3(p->cov0, Lo)) return fail(MCSIM_ERR_ARG, "score: initial covariance is not symmetric positive definite");
+    for (int k = 0; k < 6; ++k) { pc.chold[k] = Lo[k]; pc.chol[k] = float(Lo[k]); }
+    pc.sqrtQ = float(sqrt(p->Q));
+    mcsim_math::NoiseModel<double> nmd;
+    for (int k = 0; k < 4; ++k) { pc.nm.alpha[k] = float(p->alphas[k]); nmd.alpha[k] = p->alphas[k]; }
+    pc.nm.Q = float(p->Q);
+    pc.nm.L = L;
+    for (int l = 0; l < L; ++l) { pc.nm.lx[l] = float(p->landmarks[l]); pc.nm.ly[l] = float(p->landmarks[L + l]); }
+    std::vector<float> tab(size_t(NP) * T * MC_PLAN2_STRIDE, 0.f);
+    for (int q = 0; q < NP; ++q) {
+        const double* tr = p->trajectories + size_t(q) * 3 * T;
+        const double* od = p->odometry + size_t(q) * 3 * (T - 1);
+        for (int t = 0; t < T; ++t) {
+            float* w = &tab[(size_t(q) * T + t) * MC_PLAN2_STRIDE];
+            for (int k = 0; k < 3; ++k) w[k] = float(tr[k * T + t]);
+            if (t < T - 1) {
+                double us[3], M[3];
+                for (int k = 0; k < 3; ++k) { us[k] = od[k * (T - 1) + t]; w[3 + k] = float(us[k]); }
+                mcsim_math::motion_noise(nmd, us, M);  // generateM_EKF(u*_t), MCSimulator.h:698-701
+                for (int k = 0; k < 3; ++k) w[6 + k] = float(M[k]);
+                w[9] = float(M[0]) + float(M[2]);
+            }
+        }
+    }
+    CK(c->sc_plans.reserve(tab.size() * sizeof(float)));
+    CK(c->sc_hits.reserve(sizeof(unsigned long long) * NP));
+    CK(c->sc_counters.reserve(sizeof(unsigned long long) * 2));
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaMemcpyToSymbolAsync(c_mc, &pc, sizeof(pc), 0, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->sc_plans.p, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemsetAsync(c->sc_hits.p, 0, sizeof(unsigned long long) * NP, c->stream));
+    CK(cudaMemsetAsync(c->sc_counters.p, 0, sizeof(unsigned long long) * 2, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->h2d_bytes = sizeof(pc) + tab.size() * sizeof(float);
+    c->mc_prepared = false;  // c_mc now holds this batch's noise model
+    ScoreLaunch& a = c->sc;
+    a.plans = (const float*)c->sc_plans.p;
+    a.pairs = (const float4*)c->pairs_f.p;
+    a.T = T; a.n_plans = NP; a.n_pairs = c->n_pairs;
+    // whole waves of resident CTAs: one CTA per plan when there are enough plans, else split the rollouts
+    const int want = c->n_sm * 4;
+    int chunks = (want + NP - 1) / NP;
+    const unsigned long long max_chunks = (p->rollouts + 255) / 256;
+    if ((unsigned long long)chunks > max_chunks) chunks = int(max_chunks ? max_chunks : 1);
+    a.chunks = chunks < 1 ? 1 : chunks;
+    a.rollouts = p->rollouts;
+    a.plan_offset = p->plan_offset;
+    a.k0 = unsigned(p->seed); a.k1 = unsigned(p->seed >> 32);
+    a.margin = float(p->margin);
+    a.hits = (unsigned long long*)c->sc_hits.p;
+    a.counters = (unsigned long long*)c->sc_counters.p;
+    c->sc_ee = p->early_exit; c->sc_est = p->estimator;
+    c->sc_prepared = true;
+    return MCSIM_OK;
+}
+
+extern "C" int mcsim_cuda_score_launch(mcsim_cuda_ctx* c) {
+    if (!c || !c->sc_prepared) return fail(MCSIM_ERR_ARG, "score_launch: mcsim_cuda_score_prepare has not been called");
+    CK(cudaSetDevice(c->device));
+    const ScoreLaunch& a = c->sc;
+    score_kernel_t k = pick_score(c->sc_est, c->sc_ee != 0);
+    const size_t smem = sizeof(float4) * 2 * size_t(a.n_pairs) + sizeof(float) * size_t(a.T) * MC_PLAN2_STRIDE +
+                        sizeof(unsigned short) * size_t(a.T) * SCORE_CAND_CAP + size_t(a.T) + 16;
+    if (smem > 200 * 1024) return fail(MCSIM_ERR_ARG, "score: %zu bytes of shared memory needed (T=%d, %d pairs)", smem, a.T, a.n_pairs);
+    if (smem > 40 * 1024) CK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    k<<<unsigned(a.n_plans) * unsigned(a.chunks), 128, smem, c->stream>>>(a);
+    ++c->launches;
+    CK(cudaGetLastError());
+    return MCSIM_OK;
+}
+
+extern "C" int mcsim_cuda_score_collect(mcsim_cuda_ctx* c, mcsim_score_result* r) {
+    if (!c || !r || !c->sc_prepared) return fail(MCSIM_ERR_ARG, "score_collect: nothing prepared");
+    CK(cudaSetDevice(c->device));
+    const int NP = c->sc.n_plans;
+    std::vector<unsigned long long> h(size_t(NP) + 2);
+    CK(cudaMemcpyAsync(h.data(), c->sc_hits.p, sizeof(unsigned long long) * NP, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(h.data() + NP, c->sc_counters.p, sizeof(unsigned long long) * 2, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemsetAsync(c->sc_hits.p, 0, sizeof(unsigned long long) * NP, c->stream));
+    CK(cudaMemsetAsync(c->sc_counters.p, 0, sizeof(unsigned long long) * 2, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->d2h_bytes = sizeof(unsigned long long) * (size_t(NP) + 2);
+    for (int q = 0; q < NP; ++q) {
+        if (r->hits) r->hits[q] = h[q];
+        if (r->P) r->P[q] = c->sc.rollouts ? double(h[q]) / double(c->sc.rollouts) : 0.0;
+    }
+    r->executed_steps = h[NP];
+    r->pair_tests = h[NP + 1];
+    return MCSIM_OK;
+}
+
+extern "C" int mcsim_cuda_score_plans(mcsim_cuda_ctx* c, const mcsim_score_params* p, mcsim_score_result* r) {
+    if (!r) return fail(MCSIM_ERR_ARG, "score_plans: result is NULL");
+    int rc = mcsim_cuda_score_prepare(c, p);
+    if (rc) return rc;
+    CK(cudaEventRecord(c->ev0, c->stream));
+    if ((rc = mcsim_cuda_score_launch(c))) return rc;
+    CK(cudaEventRecord(c->ev1, c->stream));
+    if ((rc = mcsim_cuda_score_collect(c, r))) return rc;
     CK(cudaEventElapsedTime(&r->kernel_ms, c->ev0, c->ev1));
     return MCSIM_OK;
 }

@@ -55,6 +55,22 @@ class EmResult(C.Structure):
     ]
 
 
+class ScoreParams(C.Structure):
+    _fields_ = [
+        ("T", C.c_int), ("n_plans", C.c_int), ("trajectories", _dp), ("odometry", _dp),
+        ("alphas", C.c_double * 4), ("Q", C.c_double), ("n_landmarks", C.c_int), ("landmarks", _dp),
+        ("cov0", C.c_double * 9), ("rollouts", C.c_uint64), ("plan_offset", C.c_uint64),
+        ("estimator", C.c_int), ("early_exit", C.c_int), ("seed", C.c_uint64), ("margin", C.c_double),
+    ]
+
+
+class ScoreResult(C.Structure):
+    _fields_ = [
+        ("hits", C.POINTER(C.c_uint64)), ("P", _dp), ("executed_steps", C.c_uint64), ("pair_tests", C.c_uint64),
+        ("kernel_ms", C.c_float),
+    ]
+
+
 class GmmTruncateParams(C.Structure):
     _fields_ = [
         ("K", C.c_int), ("weights", _dp), ("means", _dp), ("covs", _dp),
@@ -120,6 +136,10 @@ def lib():
         L.mcsim_host_normals.argtypes = [C.c_uint64, C.c_uint32, C.c_int, C.c_int, _dp]
         L.mcsim_cuda_gmm_truncate.argtypes = [vp, C.POINTER(GmmTruncateParams), C.POINTER(GmmTruncateResult)]
         L.mcsim_cuda_gmm_run.argtypes = [vp, C.POINTER(McParams), C.POINTER(GmmRunParams), C.POINTER(GmmRunResult)]
+        L.mcsim_cuda_score_plans.argtypes = [vp, C.POINTER(ScoreParams), C.POINTER(ScoreResult)]
+        L.mcsim_cuda_score_prepare.argtypes = [vp, C.POINTER(ScoreParams)]
+        L.mcsim_cuda_score_launch.argtypes = [vp]
+        L.mcsim_cuda_score_collect.argtypes = [vp, C.POINTER(ScoreResult)]
         L.mcsim_cuda_em_fit.argtypes = [vp, C.POINTER(EmParams), C.POINTER(EmResult)]
         L.mcsim_cuda_em_prepare.argtypes = [vp, C.POINTER(EmParams)]
         L.mcsim_cuda_em_estep.argtypes = [vp]
@@ -320,6 +340,53 @@ class Context:
             r.gmm_pre, r.gmm_post = dptr(out["gmm_pre"]), dptr(out["gmm_post"])
         check(lib().mcsim_cuda_gmm_run(self._h, C.byref(p), C.byref(g), C.byref(r)))
         out.update(P=float(r.P), degenerate=int(r.degenerate), kernel_ms=float(r.kernel_ms))
+        return out
+
+    # ---- batched plan scoring (BASELINE config 4)
+    def _score_params(self, model, trajectories, odometry, rollouts, plan_offset, estimator, early_exit, seed, margin):
+        tr = np.ascontiguousarray(trajectories, dtype=np.float64)
+        od = np.ascontiguousarray(odometry, dtype=np.float64)
+        lm = np.ascontiguousarray(model["landmarks"], dtype=np.float64)
+        assert tr.ndim == 3 and tr.shape[1] == 3 and od.shape == (tr.shape[0], 3, tr.shape[2] - 1)
+        p = ScoreParams()
+        p.T, p.n_plans = tr.shape[2], tr.shape[0]
+        p.trajectories, p.odometry, p.landmarks = dptr(tr), dptr(od), dptr(lm)
+        p.alphas = (C.c_double * 4)(*[float(v) for v in model["alphas"]])
+        p.Q, p.n_landmarks = float(model["Q"]), lm.shape[1]
+        p.cov0 = (C.c_double * 9)(*[float(v) for v in np.asarray(model["cov0"], dtype=np.float64).reshape(9)])
+        p.rollouts, p.plan_offset = int(rollouts), int(plan_offset)
+        p.estimator, p.early_exit, p.seed, p.margin = int(estimator), int(bool(early_exit)), int(seed), float(margin)
+        return p, [tr, od, lm]
+
+    def _score_result(self, n_plans):
+        out = dict(hits=np.zeros(n_plans, dtype=np.uint64), P=np.zeros(n_plans))
+        r = ScoreResult()
+        r.hits, r.P = out["hits"].ctypes.data_as(C.POINTER(C.c_uint64)), dptr(out["P"])
+        return r, out
+
+    def score_plans(self, model, trajectories, odometry, rollouts, plan_offset=0, estimator=EST_REFERENCE,
+                    early_exit=False, seed=0x5AFEC0DE, margin=1.5):
+        """model: dict(alphas, Q, landmarks[2, 8], cov0); trajectories [n, 3, T], odometry [n, 3, T-1]."""
+        p, keep = self._score_params(model, trajectories, odometry, rollouts, plan_offset, estimator, early_exit, seed, margin)
+        r, out = self._score_result(int(p.n_plans))
+        check(lib().mcsim_cuda_score_plans(self._h, C.byref(p), C.byref(r)))
+        out.update(executed_steps=int(r.executed_steps), pair_tests=int(r.pair_tests), kernel_ms=float(r.kernel_ms))
+        return out
+
+    def score_prepare(self, model, trajectories, odometry, rollouts, **kw):
+        p, keep = self._score_params(model, trajectories, odometry, rollouts, kw.get("plan_offset", 0),
+                                     kw.get("estimator", EST_REFERENCE), kw.get("early_exit", False),
+                                     kw.get("seed", 0x5AFEC0DE), kw.get("margin", 1.5))
+        self._score_n = int(p.n_plans)
+        check(lib().mcsim_cuda_score_prepare(self._h, C.byref(p)))
+
+    def score_launch(self):
+        check(lib().mcsim_cuda_score_launch(self._h))
+
+    def score_collect(self):
+        r, out = self._score_result(self._score_n)
+        check(lib().mcsim_cuda_score_collect(self._h, C.byref(r)))
+        out.update(executed_steps=int(r.executed_steps), pair_tests=int(r.pair_tests))
         return out
 
     # ---- EM fit (BASELINE config 5; replaces arma::gmm_full::learn(keep_existing), gmm_full_meat.hpp:764-890)

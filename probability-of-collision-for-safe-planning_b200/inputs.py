@@ -87,3 +87,71 @@ def synthetic_em_problem(seed, n, K, centre=(3.0, 1.0, 1.5)):
     fcovs = np.tile(np.cov(x32.astype(np.float64)) + 1e-6 * np.eye(3), (K, 1, 1))
     hefts = np.full(K, 1.0 / K)
     return x32, hefts, means, fcovs
+
+
+# ---- BASELINE config 4 workload: synthetic obstacle field + A*-style lattice plans ------
+def synthetic_obstacle_field(seed=4096, n_boxes=256, room=40.0):
+    """n_boxes z-prisms [cx, cy, cos, sin, hx, hy, zlo, zhi]: centre uniform in the room, half extents
+    U(0.1, 0.5) m, yaw U(0, pi), z in [0, 0.2]."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    c = rng.uniform(-room / 2, room / 2, size=(n_boxes, 2))
+    h = rng.uniform(0.1, 0.5, size=(n_boxes, 2))
+    yaw = rng.uniform(0.0, np.pi, size=n_boxes)
+    return np.column_stack([c, np.cos(yaw), np.sin(yaw), h, np.zeros(n_boxes), np.full(n_boxes, 0.2)])
+
+
+def _wrap_2pi(a):
+    """angleWrap (mcsimplugin/MCSimulator.h:56-65) for arrays: [0, 2 pi]."""
+    a = np.where(a < 0, a + 2 * np.pi, a)
+    a = np.where(a < 0, a + 2 * np.pi, a)
+    a = np.where(a > 2 * np.pi, a - 2 * np.pi, a)
+    return np.where(a > 2 * np.pi, a - 2 * np.pi, a)
+
+
+def synthetic_plans(seed, n_plans, T, boxes, reach=0.4724, clear=0.05, step=0.15, room=40.0, persistence=0.9):
+    """8-connected lattice walks (step 0.15 m, heading in {0, pi/2, pi, 3pi/2}: the discretisation of
+    hw2_astar.py:122-123) whose nominal poses keep the robot's bounding circle `clear` metres away from
+    every box's bounding circle; odometry by inverseOdometry (MCSimulator.h:434-449).
+    Returns (trajectories [n_plans, 3, T], odometry [n_plans, 3, T-1])."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    bc, brad = boxes[:, :2], np.hypot(boxes[:, 4], boxes[:, 5])
+    lim = (reach + brad + clear) ** 2
+
+    def ok(p):
+        d2 = ((p[:, None, :] - bc[None, :, :]) ** 2).sum(-1)
+        inside = (np.abs(p) < room / 2 - 1.0).all(-1)
+        return (d2 > lim[None, :]).all(-1) & inside
+
+    dirs = np.array([[1, 0], [1, 1], [0, 1], [-1, 1], [-1, 0], [-1, -1], [0, -1], [1, -1]], dtype=np.float64) * step
+    pos = np.zeros((n_plans, 2))
+    todo = np.ones(n_plans, dtype=bool)
+    while todo.any():
+        cand = rng.uniform(-room / 2 + 2, room / 2 - 2, size=(int(todo.sum()), 2))
+        good = ok(cand)
+        idx = np.nonzero(todo)[0]
+        pos[idx[good]] = cand[good]
+        todo[idx[good]] = False
+    d = rng.integers(0, 8, size=n_plans)
+    traj = np.zeros((n_plans, 3, T))
+    heading = (np.round(d / 2.0).astype(int) % 4) * (np.pi / 2)
+    traj[:, 0, 0], traj[:, 1, 0], traj[:, 2, 0] = pos[:, 0], pos[:, 1], heading
+    for t in range(1, T):
+        change = rng.random(n_plans) > persistence
+        d = np.where(change, rng.integers(0, 8, size=n_plans), d)
+        moved = np.zeros(n_plans, dtype=bool)
+        newpos = pos.copy()
+        for attempt in range(8):
+            trial = (d + np.where(moved, 0, attempt * rng.choice([1, -1], size=n_plans))) % 8
+            cand = pos + dirs[trial]
+            good = ok(cand) & ~moved
+            newpos[good] = cand[good]
+            d = np.where(good, trial, d)
+            moved |= good
+        pos = newpos
+        heading = (np.round(d / 2.0).astype(int) % 4) * (np.pi / 2)
+        traj[:, 0, t], traj[:, 1, t], traj[:, 2, t] = pos[:, 0], pos[:, 1], heading
+    dx, dy = np.diff(traj[:, 0, :], axis=1), np.diff(traj[:, 1, :], axis=1)
+    rot1 = _wrap_2pi(np.arctan2(dy, dx) - traj[:, 2, :-1])
+    trans = np.hypot(dx, dy)
+    rot2 = _wrap_2pi(traj[:, 2, 1:] - traj[:, 2, :-1] - rot1)
+    return traj, np.stack([rot1, trans, rot2], axis=1)

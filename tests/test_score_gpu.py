@@ -1,0 +1,59 @@
+"""GPU tests of batched plan scoring (BASELINE config 4), through the C ABI (mcsim_cuda_score_*).
+
+The per-rollout law is the MC Philox law, whose parity with the reference is established in
+tests/test_mc_gpu.py; here: (1) a batch of one plan reproduces mcsim_cuda_mc_run on the same Philox
+counters, (2) the broad phase is exact (same hits as testing every live pair at every step),
+(3) results do not depend on how plans are split over calls (the multi-GPU sharding)."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _hulls():
+    from conftest import golden
+    return golden("scene_pr2test2.npz")["hulls"]
+
+
+def test_single_plan_batch_equals_mc_run(ctx, plan, scenes):
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    for name in ("pr2test2", "pr2custom"):
+        ctx.set_scene(scenes[name]["boxes"], scenes[name]["hulls"])
+        N = 100001
+        p, keep = abi.make_mc_params(plan, n_rollouts=N, mode=abi.MODE_PHILOX, early_exit=False)
+        mc = ctx.mc_run(p)
+        for margin in (-1.0, 0.3):
+            sc = ctx.score_plans(plan, plan["trajectory"][None], plan["odometry"][None], N, margin=margin)
+            # same counters and arithmetic except the SAT grouping (rounding at contact): |d hits| tiny
+            assert abs(int(sc["hits"][0]) - mc["hits"]) <= 5e-4 * N, (name, margin, sc["hits"], mc["hits"])
+            assert sc["executed_steps"] == N * plan["trajectory"].shape[1]
+        ee = ctx.score_plans(plan, plan["trajectory"][None], plan["odometry"][None], N, margin=0.3, early_exit=True)
+        assert ee["hits"][0] == sc["hits"][0] and ee["executed_steps"] < sc["executed_steps"]
+
+
+def test_broad_phase_is_exact_and_split_invariant(ctx, plan):
+    import pcoll_b200
+    inp = pcoll_b200.inputs
+    boxes = inp.synthetic_obstacle_field()
+    ctx.set_scene(boxes, _hulls())
+    # clear = -0.15: nominal paths graze the obstacles, so P spans (0, 1)
+    tr, od = inp.synthetic_plans(7, 24, 120, boxes, clear=-0.15)
+    R = 4096 + 37
+    full = ctx.score_plans(plan, tr, od, R, margin=-1.0)
+    cull = ctx.score_plans(plan, tr, od, R, margin=1.5)
+    tight = ctx.score_plans(plan, tr, od, R, margin=0.02)   # most warps fall back to the exhaustive test
+    np.testing.assert_array_equal(cull["hits"], full["hits"])
+    np.testing.assert_array_equal(tight["hits"], full["hits"])
+    print("pair tests per rollout-step: exhaustive %.1f, margin 1.5 m %.2f, margin 0.02 m %.1f" % tuple(o["pair_tests"] / o["executed_steps"] for o in (full, cull, tight)))
+    assert cull["pair_tests"] < 0.1 * full["pair_tests"] and full["pair_tests"] == full["executed_steps"] * 256
+    assert cull["pair_tests"] < tight["pair_tests"] <= full["pair_tests"]
+    assert 0 < (full["P"] > 0.01).sum() and (full["P"] < 0.99).sum() > 0
+    print("P per plan:", np.round(full["P"], 3))
+    # plans split over calls (what the multi-GPU sharding does)
+    parts = [ctx.score_plans(plan, tr[a:b], od[a:b], R, plan_offset=a, margin=1.5)["hits"] for a, b in ((0, 5), (5, 24))]
+    np.testing.assert_array_equal(np.concatenate(parts), full["hits"])
+    # device-resident form
+    ctx.score_prepare(plan, tr, od, R, margin=1.5)
+    ctx.score_launch()
+    np.testing.assert_array_equal(ctx.score_collect()["hits"], full["hits"])
