@@ -287,7 +287,7 @@ def main():
         "clocks": clocks, "gpu_launches": launches, "e2e": e2e,
         "roofline": {
             "bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,
-            "traffic": None, "kernel": "mc_rollout_kernel<PHILOX, no audit, no early exit, reference estimator, L=8>",
+            "traffic": None, "kernel": "mc_philox2_kernel<no early exit, reference estimator, L=8> (two rollouts per thread, packed FP32 pairs)",
             "kernel_ms_per_launch": kernel_ms / a.steps,
             "algorithmic": "%d flops per Philox rollout-step + %d per SAT pair test x %.1f live pair tests per step" % (
                 F_PHILOX_STEP, F_SAT, tot["pair_tests"] / job_steps),
@@ -297,6 +297,10 @@ def main():
     }
     if rank == 0 and not a.no_extras:
         line["extras"] = extras(a, ctx, abi, plan, T, stream, torch)
+        try:
+            line["extras"].update(extras_scoring_em(ctx, abi, plan, sc, fp32_peak))
+        except Exception as exc:  # reported, never silently dropped
+            line["extras"]["scoring_em_error"] = repr(exc)
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
         import oracle_ref
         if oracle_ref.available():
@@ -381,6 +385,78 @@ def extras(a, ctx, abi, plan, T, stream, torch):
         except Exception as exc:
             out["gmm_error"] = repr(exc)
     return out
+
+
+def extras_scoring_em(ctx, abi, plan, sc, fp32_peak):
+    """BASELINE configs 4 and 5 as side measurements on rank 0 (subsets stated in each record)."""
+    import pcoll_b200
+    inp = pcoll_b200.inputs
+    out = {}
+    peaks = read_measured_peaks() or {}
+    # ---- config 4: batched plan scoring, 128 of the 4,096 plans x 65,536 rollouts x 500 waypoints, 256 boxes
+    boxes = inp.synthetic_obstacle_field(4096, 256)
+    n_plans, T4, R = 128, 500, 65536
+    tr, od = inp.synthetic_plans(4096, n_plans, T4, boxes)
+    ctx.set_scene(boxes, sc["hulls"])
+    for name, margin, plans, rollouts in (("score_config4_broad_phase", 1.5, n_plans, R), ("score_config4_exhaustive", -1.0, 16, 16384)):
+        ctx.score_prepare(plan, tr[:plans], od[:plans], rollouts, margin=margin)
+        ctx.score_launch()
+        ctx.score_collect()
+        ev = [cuda_event(ctx) for _ in range(2)]
+        ev[0].record()
+        ctx.score_launch()
+        ev[1].record()
+        r = ctx.score_collect()
+        ms = ev[0].elapsed_ms(ev[1])
+        flops = r["executed_steps"] * F_PHILOX_STEP + r["pair_tests"] * F_SAT
+        out[name] = {
+            "subset": "%d plans x %d rollouts x %d waypoints, 256-box field, margin %s" % (plans, rollouts, T4, margin),
+            "nominal_rollout_steps_per_s": plans * rollouts * T4 / (ms * 1e-3), "kernel_ms": ms,
+            "pair_tests_per_rollout_step": r["pair_tests"] / max(r["executed_steps"], 1),
+            "algorithmic_tflops": flops / (ms * 1e-3) / 1e12, "frac_of_fp32_peak": flops / (ms * 1e-3) / 1e12 / fp32_peak,
+            "P_mean": float(r["P"].mean()), "P_max": float(r["P"].max())}
+    ctx.set_scene(sc["boxes"], sc["hulls"])
+    # ---- config 5: EM sweep, 56 waypoint buffers x 10^6 FP32 samples (672 MB resident), 10 iterations
+    F, n, iters = 56, 10 ** 6, 10
+    traj = plan["trajectory"]
+    base = [inp.synthetic_em_problem(9000 + f, n, 16, centre=(0.0, 0.0, 0.0)) for f in range(8)]
+    probs = []  # 56 distinct buffers: 8 seeded mixtures, each moved to 7 different trajectory poses
+    for f in range(F):
+        b, ctr = base[f % 8], traj[:, f % traj.shape[1]]
+        probs.append(((b[0] + ctr.astype(np.float32)[:, None]).astype(np.float32), b[1], b[2] + ctr[None, :], b[3]))
+    x = np.stack([q[0] for q in probs])
+    first = True
+    for K in (1, 2, 3, 4, 8, 16):
+        h = np.stack([np.full(K, 1.0 / K) for q in probs]); m = np.stack([q[2][:K] for q in probs]); c = np.stack([q[3][:K] for q in probs])
+        ctx.em_fit(x if first else None, h, m, c, 2)
+        first = False
+        r = ctx.em_fit(None, h, m, c, iters)
+        sec = r["kernel_ms"] * 1e-3
+        gbs = 12.0 * n * F * iters / sec / 1e9
+        out["em_config5_K%d" % K] = {
+            "fits": F, "samples_per_fit": n, "iterations": iters, "kernel_ms": r["kernel_ms"],
+            "sample_iterations_per_s": n * F * iters / sec, "algorithmic_GBps": gbs,
+            "frac_of_hbm_peak": gbs / peaks["hbm_gbs"] if peaks.get("hbm_gbs") else None,
+            "algorithmic_tflops": 61.0 * K * n * F * iters / sec / 1e12,
+            "frac_of_fp32_peak": 61.0 * K * n * F * iters / sec / 1e12 / fp32_peak,
+            "avg_log_p_last": float(np.nanmean(r["avg_log_p"][:, -1]))}
+    return out
+
+
+class cuda_event:
+    """CUDA event on the library's own stream (torch.cuda.Event sees only torch's current stream)."""
+    def __init__(self, ctx):
+        import torch
+        self._torch = torch
+        self._stream = torch.cuda.ExternalStream(ctx.stream, device=ctx.device)
+        self._ev = torch.cuda.Event(enable_timing=True)
+
+    def record(self):
+        self._ev.record(self._stream)
+
+    def elapsed_ms(self, other):
+        other._ev.synchronize()
+        return self._ev.elapsed_time(other._ev)
 
 
 if __name__ == "__main__":

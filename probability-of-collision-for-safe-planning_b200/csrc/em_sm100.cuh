@@ -66,45 +66,69 @@ __global__ void __launch_bounds__(256) em_estep_kernel(const EmLaunch a) {
         for (int k = 0; k < EM_NSTAT; ++k) acc[g][k] = 0.f;
     float lsum = 0.f;
 
+    // U samples per pass, the next pass's 3 U loads issued before this pass's arithmetic: enough bytes
+    // in flight per SM to stream from HBM while the FP32 pipe works on the previous samples
+    constexpr int U = K <= 4 ? 4 : (K <= 8 ? 2 : 1);
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
-        const float x = __ldg(xs + i), y = __ldg(ys + i), t = __ldg(ts + i);
-        float ll[K];
-        float m = -FLT_MAX;
+    unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    float bx[U], by[U], bt[U];
 #pragma unroll
-        for (int g = 0; g < K; ++g) {
-            const float* c = s_c + g * EM_COMP_STRIDE;
-            const float d0 = x - c[0], d1 = y - c[1], d2 = t - c[2];
-            // -1/2 d^T A d + cst with b = -1/2 A (off-diagonals doubled)
-            const float q0 = fmaf(c[3], d0, fmaf(c[4], d1, c[5] * d2));
-            const float q1 = fmaf(c[6], d1, c[7] * d2);
-            ll[g] = fmaf(d0, q0, fmaf(d1, q1, fmaf(c[8] * d2, d2, c[9])));
-            m = fmaxf(m, ll[g]);
+    for (int u = 0; u < U; ++u) {
+        const unsigned long long k = i + u * stride;
+        const bool ok = k < a.n;
+        bx[u] = ok ? __ldg(xs + k) : 0.f; by[u] = ok ? __ldg(ys + k) : 0.f; bt[u] = ok ? __ldg(ts + k) : 0.f;
+    }
+    for (; i < a.n; i += U * stride) {
+        float cx[U], cy[U], ct[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) { cx[u] = bx[u]; cy[u] = by[u]; ct[u] = bt[u]; }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const unsigned long long k = i + (U + u) * stride;
+            const bool ok = k < a.n;
+            bx[u] = ok ? __ldg(xs + k) : 0.f; by[u] = ok ? __ldg(ys + k) : 0.f; bt[u] = ok ? __ldg(ts + k) : 0.f;
         }
-        float s = 0.f;
 #pragma unroll
-        for (int g = 0; g < K; ++g) {
-            ll[g] = exp2f((ll[g] - m) * 1.4426950408889634f);
-            s += ll[g];
-        }
-        if (G0 == 0) lsum += m + __logf(s);
-        const float inv = __frcp_rn(s);
+        for (int u = 0; u < U; ++u) {
+            if (i + u * stride >= a.n) break;
+            const float x = cx[u], y = cy[u], t = ct[u];
+            float ll[K];
+            float m = -FLT_MAX;
 #pragma unroll
-        for (int gg = 0; gg < KG; ++gg) {
-            const float* c = s_c + (G0 + gg) * EM_COMP_STRIDE;
-            const float r = ll[G0 + gg] * inv;
-            const float d0 = x - c[0], d1 = y - c[1], d2 = t - c[2];
-            const float r0 = r * d0, r1 = r * d1, r2 = r * d2;
-            acc[gg][0] += r;
-            acc[gg][1] += r0;
-            acc[gg][2] += r1;
-            acc[gg][3] += r2;
-            acc[gg][4] = fmaf(r0, d0, acc[gg][4]);
-            acc[gg][5] = fmaf(r0, d1, acc[gg][5]);
-            acc[gg][6] = fmaf(r0, d2, acc[gg][6]);
-            acc[gg][7] = fmaf(r1, d1, acc[gg][7]);
-            acc[gg][8] = fmaf(r1, d2, acc[gg][8]);
-            acc[gg][9] = fmaf(r2, d2, acc[gg][9]);
+            for (int g = 0; g < K; ++g) {
+                const float* c = s_c + g * EM_COMP_STRIDE;
+                const float d0 = x - c[0], d1 = y - c[1], d2 = t - c[2];
+                // -1/2 d^T A d + cst with b = -1/2 A (off-diagonals doubled)
+                const float q0 = fmaf(c[3], d0, fmaf(c[4], d1, c[5] * d2));
+                const float q1 = fmaf(c[6], d1, c[7] * d2);
+                ll[g] = fmaf(d0, q0, fmaf(d1, q1, fmaf(c[8] * d2, d2, c[9])));
+                m = fmaxf(m, ll[g]);
+            }
+            float s = 0.f;
+#pragma unroll
+            for (int g = 0; g < K; ++g) {
+                ll[g] = exp2f((ll[g] - m) * 1.4426950408889634f);
+                s += ll[g];
+            }
+            if (G0 == 0) lsum += m + __logf(s);
+            const float inv = __frcp_rn(s);
+#pragma unroll
+            for (int gg = 0; gg < KG; ++gg) {
+                const float* c = s_c + (G0 + gg) * EM_COMP_STRIDE;
+                const float r = ll[G0 + gg] * inv;
+                const float d0 = x - c[0], d1 = y - c[1], d2 = t - c[2];
+                const float r0 = r * d0, r1 = r * d1, r2 = r * d2;
+                acc[gg][0] += r;
+                acc[gg][1] += r0;
+                acc[gg][2] += r1;
+                acc[gg][3] += r2;
+                acc[gg][4] = fmaf(r0, d0, acc[gg][4]);
+                acc[gg][5] = fmaf(r0, d1, acc[gg][5]);
+                acc[gg][6] = fmaf(r0, d2, acc[gg][6]);
+                acc[gg][7] = fmaf(r1, d1, acc[gg][7]);
+                acc[gg][8] = fmaf(r1, d2, acc[gg][8]);
+                acc[gg][9] = fmaf(r2, d2, acc[gg][9]);
+            }
         }
     }
 

@@ -238,6 +238,12 @@ class Context:
         return lib().mcsim_cuda_stream(self._h)
 
     @property
+    def torch_stream(self):
+        """The context's CUDA stream as a torch stream (collectives are issued on it, behind the kernels)."""
+        import torch
+        return torch.cuda.ExternalStream(self.stream, device=self.device)
+
+    @property
     def launch_count(self):
         return int(lib().mcsim_cuda_launch_count(self._h))
 
