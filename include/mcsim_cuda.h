@@ -308,6 +308,15 @@ int mcsim_cuda_score_prepare(mcsim_cuda_ctx* ctx, const mcsim_score_params* p);
 int mcsim_cuda_score_launch(mcsim_cuda_ctx* ctx);
 int mcsim_cuda_score_collect(mcsim_cuda_ctx* ctx, mcsim_score_result* r);
 
+/* ---- analytic linear-constraint truncation (host, FP64) ------------------------ */
+/* Truncates N(mean, cov) (3-D, cov row-major) against n half-spaces A[k] . x <= b[k]: per constraint the
+ * 1-D marginal along A[k] is truncated and the moment changes are propagated through the conditional;
+ * the changes of all constraints are computed from the untruncated belief and summed.  p_violation[k]
+ * (optional) = mass of the belief violating constraint k.  The reference holds only a predicate stub
+ * for this (linConstraint.py:15-30, gaussprop.py:58-73): parity unpinned. */
+int mcsim_truncate_linear(const double mean[3], const double cov[9], int n, const double* A, const double* b,
+                          double mean_out[3], double cov_out[9], double* p_violation);
+
 /* bytes the last *_run call copied host->device and device->host (bench.py's e2e accounting) */
 void mcsim_cuda_io_bytes(mcsim_cuda_ctx* ctx, uint64_t* h2d, uint64_t* d2h);
 

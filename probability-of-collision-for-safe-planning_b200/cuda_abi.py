@@ -136,6 +136,7 @@ def lib():
         L.mcsim_host_normals.argtypes = [C.c_uint64, C.c_uint32, C.c_int, C.c_int, _dp]
         L.mcsim_cuda_gmm_truncate.argtypes = [vp, C.POINTER(GmmTruncateParams), C.POINTER(GmmTruncateResult)]
         L.mcsim_cuda_gmm_run.argtypes = [vp, C.POINTER(McParams), C.POINTER(GmmRunParams), C.POINTER(GmmRunResult)]
+        L.mcsim_truncate_linear.argtypes = [_dp, _dp, C.c_int, _dp, _dp, _dp, _dp, _dp]
         L.mcsim_cuda_score_plans.argtypes = [vp, C.POINTER(ScoreParams), C.POINTER(ScoreResult)]
         L.mcsim_cuda_score_prepare.argtypes = [vp, C.POINTER(ScoreParams)]
         L.mcsim_cuda_score_launch.argtypes = [vp]
@@ -198,6 +199,18 @@ def make_mc_params(plan, n_rollouts=0, mode=MODE_PHILOX, estimator=EST_REFERENCE
     p.near_eps = float(near_eps)
     p.precise = int(bool(precise))
     return p, keep
+
+
+def truncate_linear(mean, cov, A, b):
+    """Analytic truncation of N(mean, cov) against the half-spaces A[k] . x <= b[k].
+    Returns (mean', cov', p_violation[k])."""
+    m = np.ascontiguousarray(mean, dtype=np.float64).reshape(3)
+    cv = np.ascontiguousarray(cov, dtype=np.float64).reshape(9)
+    Aa = np.ascontiguousarray(A, dtype=np.float64).reshape(-1, 3)
+    bb = np.ascontiguousarray(b, dtype=np.float64).reshape(-1)
+    mo, co, pv = np.zeros(3), np.zeros(9), np.zeros(Aa.shape[0])
+    check(lib().mcsim_truncate_linear(dptr(m), dptr(cv), Aa.shape[0], dptr(Aa), dptr(bb), dptr(mo), dptr(co), dptr(pv)))
+    return mo, co.reshape(3, 3), pv
 
 
 def host_thread(plan, normals):

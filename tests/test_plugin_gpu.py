@@ -99,3 +99,20 @@ def test_run_without_parameters_is_an_error():
     with pytest.raises(pcoll_b200.McsimError, match="setAlphas"):
         mod.SendCommand("runSimulation")
     mod.close()
+
+
+def test_py3_driver_twin_mc_and_gmm(tmp_path):
+    """tools/mc_simulation.py: the reference driver's loop and report files (MCSimulation.py:100-270)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("mc_simulation", os.path.join(ROOT, "tools", "mc_simulation.py"))
+    drv = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(drv)
+    for opt, prefix in (("MC", "simReport_"), ("GMM", "GMMsimReport_")):
+        out = drv.main([opt, "--num-simulations", "3", "--num-particles", "2000", "--outdir", str(tmp_path), "--seed", "5"])
+        assert len(out["proportions"]) == 3 and all(0.5 < p <= 1.0 for p in out["proportions"])
+        text = open(out["report"]).read()
+        assert os.path.basename(out["report"]).startswith(prefix)
+        for key in ("Environment: ", "Num Landmarks: 8", "NumSimulations: 3", "Average Prob Collision: ", "Trajectory: ", "Odometry: "):
+            assert key in text
+        ck = open(out["checkpoint"]).read()
+        assert ck.count("collProp: ") == 3 and "Simulation: 2" in ck
