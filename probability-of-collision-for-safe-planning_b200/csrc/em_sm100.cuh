@@ -48,7 +48,7 @@ template <int K, int G0>
 __global__ void __launch_bounds__(256) em_estep_kernel(const EmLaunch a) {
     constexpr int KG = (K - G0) < 8 ? (K - G0) : 8;
     constexpr int NACC = KG * EM_NSTAT + 1;
-    __shared__ float s_c[K * EM_COMP_STRIDE];
+    __shared__ __align__(16) float s_c[K * EM_COMP_STRIDE];
     __shared__ double s_acc[NACC];
     const int fit = blockIdx.y;
     if (a.done[fit]) return;
@@ -69,39 +69,42 @@ __global__ void __launch_bounds__(256) em_estep_kernel(const EmLaunch a) {
     // U samples per pass, the next pass's 3 U loads issued before this pass's arithmetic: enough bytes
     // in flight per SM to stream from HBM while the FP32 pipe works on the previous samples
     constexpr int U = K <= 4 ? 4 : (K <= 8 ? 2 : 1);
-    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    // 32-bit sample indices (mcsim_cuda_em_prepare rejects n >= 2^31 per fit and shard)
+    const unsigned n = unsigned(a.n);
+    const unsigned stride = gridDim.x * blockDim.x;
+    unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
     float bx[U], by[U], bt[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-        const unsigned long long k = i + u * stride;
-        const bool ok = k < a.n;
+        const unsigned k = i + u * stride;
+        const bool ok = k < n;
         bx[u] = ok ? __ldg(xs + k) : 0.f; by[u] = ok ? __ldg(ys + k) : 0.f; bt[u] = ok ? __ldg(ts + k) : 0.f;
     }
-    for (; i < a.n; i += U * stride) {
+    for (; i < n; i += U * stride) {
         float cx[U], cy[U], ct[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) { cx[u] = bx[u]; cy[u] = by[u]; ct[u] = bt[u]; }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            const unsigned long long k = i + (U + u) * stride;
-            const bool ok = k < a.n;
+            const unsigned k = i + (U + u) * stride;
+            const bool ok = k < n;
             bx[u] = ok ? __ldg(xs + k) : 0.f; by[u] = ok ? __ldg(ys + k) : 0.f; bt[u] = ok ? __ldg(ts + k) : 0.f;
         }
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-            if (i + u * stride >= a.n) break;
+            if (i + u * stride >= n) break;
             const float x = cx[u], y = cy[u], t = ct[u];
             float ll[K];
             float m = -FLT_MAX;
 #pragma unroll
             for (int g = 0; g < K; ++g) {
-                const float* c = s_c + g * EM_COMP_STRIDE;
-                const float d0 = x - c[0], d1 = y - c[1], d2 = t - c[2];
+                const float4* c4 = reinterpret_cast<const float4*>(s_c + g * EM_COMP_STRIDE);  // 3 LDS.128
+                const float4 ca = c4[0], cb = c4[1], cc = c4[2];   // mu0 mu1 mu2 b00 | b01 b02 b11 b12 | b22 cst - -
+                const float d0 = x - ca.x, d1 = y - ca.y, d2 = t - ca.z;
                 // -1/2 d^T A d + cst with b = -1/2 A (off-diagonals doubled)
-                const float q0 = fmaf(c[3], d0, fmaf(c[4], d1, c[5] * d2));
-                const float q1 = fmaf(c[6], d1, c[7] * d2);
-                ll[g] = fmaf(d0, q0, fmaf(d1, q1, fmaf(c[8] * d2, d2, c[9])));
+                const float q0 = fmaf(ca.w, d0, fmaf(cb.x, d1, cb.y * d2));
+                const float q1 = fmaf(cb.z, d1, cb.w * d2);
+                ll[g] = fmaf(d0, q0, fmaf(d1, q1, fmaf(cc.x * d2, d2, cc.y)));
                 m = fmaxf(m, ll[g]);
             }
             float s = 0.f;
@@ -114,9 +117,9 @@ __global__ void __launch_bounds__(256) em_estep_kernel(const EmLaunch a) {
             const float inv = __frcp_rn(s);
 #pragma unroll
             for (int gg = 0; gg < KG; ++gg) {
-                const float* c = s_c + (G0 + gg) * EM_COMP_STRIDE;
+                const float4 ca = *reinterpret_cast<const float4*>(s_c + (G0 + gg) * EM_COMP_STRIDE);
                 const float r = ll[G0 + gg] * inv;
-                const float d0 = x - c[0], d1 = y - c[1], d2 = t - c[2];
+                const float d0 = x - ca.x, d1 = y - ca.y, d2 = t - ca.z;
                 const float r0 = r * d0, r1 = r * d1, r2 = r * d2;
                 acc[gg][0] += r;
                 acc[gg][1] += r0;

@@ -156,23 +156,21 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a) {
     }
     __syncthreads();
 
-    double acc[GMM_STAT];
-#pragma unroll
-    for (int k = 0; k < GMM_STAT; ++k) acc[k] = 0.0;
-    int gcur = 0;
-    auto flush = [&](int g) {
-#pragma unroll
-        for (int k = 0; k < GMM_STAT; ++k) {
-            if (acc[k] != 0.0) atomicAdd(&s_stat[g][k], acc[k]);
-            acc[k] = 0.0;
-        }
-    };
+    // Block-uniform trip count; every pass ends with a warp-level reduction of the pass's contributions
+    // (segmented by component: samples are grouped by component, so a warp almost always holds one),
+    // then ONE shared-memory atomic per statistic and warp.  (Per-thread FP64 shared atomics are CAS
+    // loops: with every thread of the grid flushing 11 of them onto K x 11 addresses they serialised the
+    // whole kernel.)
+    int g = 0;
     const unsigned long long n = s_prefix[K] < a.n ? s_prefix[K] : a.n;
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        int g = gcur;
+    for (unsigned long long base = (unsigned long long)blockIdx.x * blockDim.x; base < n; base += stride) {
+        const unsigned long long i = base + threadIdx.x;
+        const bool valid = i < n;
+        bool hit = false;
+        double d0 = 0.0, d1 = 0.0, d2 = 0.0;
+        if (valid) {
         while (g < K - 1 && i >= s_prefix[g + 1]) ++g;  // i only grows: the component index is monotone
-        if (g != gcur) { flush(gcur); gcur = g; }
         double z0, z1, z2;
         if (MODE == MCSIM_MODE_REPLAY) {
             z0 = a.normals[3 * i]; z1 = a.normals[3 * i + 1]; z2 = a.normals[3 * i + 2];
@@ -187,11 +185,10 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a) {
         const double* cp = s_comp[g];
         const double* Lc = cp + 13;
         // d = L z in the summation order of a 3x3 times 3x1 product (left to right), no contraction
-        const double d0 = __dmul_rn(Lc[0], z0);
-        const double d1 = __dadd_rn(__dmul_rn(Lc[1], z0), __dmul_rn(Lc[2], z1));
-        const double d2 = __dadd_rn(__dadd_rn(__dmul_rn(Lc[3], z0), __dmul_rn(Lc[4], z1)), __dmul_rn(Lc[5], z2));
+        d0 = __dmul_rn(Lc[0], z0);
+        d1 = __dadd_rn(__dmul_rn(Lc[1], z0), __dmul_rn(Lc[2], z1));
+        d2 = __dadd_rn(__dadd_rn(__dmul_rn(Lc[3], z0), __dmul_rn(Lc[4], z1)), __dmul_rn(Lc[5], z2));
         const double x = __dadd_rn(d0, cp[1]), y = __dadd_rn(d1, cp[2]), th = __dadd_rn(d2, cp[3]);
-        bool hit;
         if (MODE == MCSIM_MODE_REPLAY) {
             hit = clearance_d(a.hulls_d, a.pairs_d, a.n_hulls, x, y, th) <= 0.0;
         } else {
@@ -204,16 +201,34 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a) {
             unsigned nt = 0;
             hit = robot_hits(float(x), float(y), cs, sn, nt);
         }
-        if (hit) {
-            acc[1] += 1.0;
-        } else {
-            acc[0] += 1.0;
-            acc[2] += d0; acc[3] += d1; acc[4] += d2;
-            acc[5] += d0 * d0; acc[6] += d0 * d1; acc[7] += d0 * d2;
-            acc[8] += d1 * d1; acc[9] += d1 * d2; acc[10] += d2 * d2;
+        }  // valid
+        const int gmin = __reduce_min_sync(0xffffffffu, valid ? g : 0x7fffffff);
+        const int gmax = __reduce_max_sync(0xffffffffu, valid ? g : -1);
+        for (int gg = gmin; gg <= gmax; ++gg) {  // warp-uniform
+            const bool sel = valid && g == gg;
+            const unsigned nf = __reduce_add_sync(0xffffffffu, unsigned(sel && !hit));
+            const unsigned nc = __reduce_add_sync(0xffffffffu, unsigned(sel && hit));
+            double v[9];
+            const bool use = sel && !hit;
+            v[0] = use ? d0 : 0.0; v[1] = use ? d1 : 0.0; v[2] = use ? d2 : 0.0;
+            v[3] = use ? d0 * d0 : 0.0; v[4] = use ? d0 * d1 : 0.0; v[5] = use ? d0 * d2 : 0.0;
+            v[6] = use ? d1 * d1 : 0.0; v[7] = use ? d1 * d2 : 0.0; v[8] = use ? d2 * d2 : 0.0;
+            if (nf) {
+#pragma unroll
+                for (int k = 0; k < 9; ++k)
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+            }
+            if ((threadIdx.x & 31) == 0) {
+                if (nf) {
+                    atomicAdd(&s_stat[gg][0], double(nf));
+#pragma unroll
+                    for (int k = 0; k < 9; ++k) atomicAdd(&s_stat[gg][2 + k], v[k]);
+                }
+                if (nc) atomicAdd(&s_stat[gg][1], double(nc));
+            }
         }
     }
-    flush(gcur);
     __syncthreads();
     for (int i = threadIdx.x; i < K * GMM_STAT; i += blockDim.x) {
         const double v = s_stat[i / GMM_STAT][i % GMM_STAT];

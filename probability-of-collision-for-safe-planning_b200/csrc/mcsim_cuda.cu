@@ -554,7 +554,8 @@ static void gmm_fill_launch(mcsim_cuda_ctx* c, GmmLaunch& a, int K, int T, int L
 
 // the three launches of one waypoint
 static int gmm_launch_waypoint(mcsim_cuda_ctx* c, const GmmLaunch& a, int mode) {
-    const int block = 256;
+    // small sample counts (the reference's N = 10^4): 64-thread CTAs so that every SM gets work
+    const int block = a.n < (unsigned long long)c->n_sm * 256 ? 64 : 256;
     unsigned long long want = (a.n + block - 1) / block;
     const unsigned long long cap = (unsigned long long)c->n_sm * 8;
     const unsigned grid = unsigned(want < cap ? (want ? want : 1) : cap);
@@ -776,6 +777,7 @@ extern "C" int mcsim_cuda_em_prepare(mcsim_cuda_ctx* c, const mcsim_em_params* p
     if (p->K < 1 || p->K > MCSIM_MAX_GAUSSIANS) return fail(MCSIM_ERR_ARG, "em: K=%d out of range 1..%d", p->K, MCSIM_MAX_GAUSSIANS);
     if (p->n_fits < 1 || p->n_fits > 65535) return fail(MCSIM_ERR_ARG, "em: n_fits=%d out of range 1..65535", p->n_fits);
     if (p->iters < 0) return fail(MCSIM_ERR_ARG, "em: negative iteration count");
+    if (p->n >= (1ull << 31) - (1ull << 24)) return fail(MCSIM_ERR_ARG, "em: more than 2^31 samples per fit and shard");
     if (!p->hefts || !p->means || !p->fcovs) return fail(MCSIM_ERR_ARG, "em: initial parameters are NULL (seed mode is keep_existing)");
     if (!p->x && !(c->em_x_valid && c->em_x_n == p->n && c->em_x_fits == p->n_fits))
         return fail(MCSIM_ERR_ARG, "em: x is NULL and no resident samples of this shape");
