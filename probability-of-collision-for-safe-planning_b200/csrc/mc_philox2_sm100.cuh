@@ -25,6 +25,9 @@
 // per-step plan record in __constant__ memory (uniform loads, operands broadcast from uniform
 // registers): x*_t (3), u*_t (3), M_t (3) = generateM_EKF(u*_t), M_0 + M_2
 #define MC_PLAN2_STRIDE 12
+#ifndef MC_P2_CTAS_PER_SM
+#define MC_P2_CTAS_PER_SM 5  // resident 128-thread CTAs per SM the register budget is set for
+#endif
 #define MC_PLAN2_MAX_T 256
 __constant__ float c_plan2[MC_PLAN2_MAX_T * MC_PLAN2_STRIDE];
 
@@ -231,7 +234,7 @@ __device__ __forceinline__ void step2(Rollout2& st, const float* r, int t, unsig
 }
 
 template <bool EARLY_EXIT, int EST, int NL>
-__global__ void __launch_bounds__(128, 4) mc_philox2_kernel(const McLaunch a) {
+__global__ void __launch_bounds__(128, MC_P2_CTAS_PER_SM) mc_philox2_kernel(const McLaunch a) {
     extern __shared__ __align__(16) float4 s_tab[];
     __shared__ unsigned s_cnt[2];
     __shared__ unsigned s_hist[MCSIM_MAX_WAYPOINTS];

@@ -421,8 +421,8 @@ static int mc_launch_impl(mcsim_cuda_ctx* c, uint64_t n, uint64_t offset, const 
     const int block = packed ? 128 : 256;
     const size_t smem = packed ? sizeof(float4) * size_t(c->sat2_n) : sizeof(float) * size_t(c->mc_T) * MC_PHILOX_STRIDE;
     unsigned long long want = packed ? ((n + 1) / 2 + block - 1) / block : (n + block - 1) / block;
-    // persistent: whole waves of resident CTAs (packed: 4 x 128 threads per SM at <= 128 registers)
-    const unsigned long long cap = (unsigned long long)c->n_sm * (packed ? 4 : 8);
+    // persistent: whole waves of resident CTAs
+    const unsigned long long cap = (unsigned long long)c->n_sm * (packed ? MC_P2_CTAS_PER_SM : 8);
     const unsigned grid = unsigned(want < cap ? (want ? want : 1) : cap);
     if (smem > 40 * 1024) CK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     k<<<grid, block, smem, c->stream>>>(a);
