@@ -382,6 +382,15 @@ def extras(a, ctx, abi, plan, T, stream, torch):
                 dt = (time.perf_counter() - t0) / reps
                 out["gmm_K%d_N%d" % (K, ns)] = {"trajectories_per_s": 1.0 / dt, "sample_checks_per_s": T * ns / dt,
                                                 "kernel_ms": g["kernel_ms"], "P": g["P"]}
+            for ns, B in ((10000, 256), (10000, 1024)):
+                ctx.gmm_run_batch(plan, 3, ns, B)
+                t0 = time.perf_counter()
+                g = ctx.gmm_run_batch(plan, 3, ns, B, stream0=B)
+                dt = time.perf_counter() - t0
+                out["gmm_K3_N%d_batch%d" % (ns, B)] = {
+                    "trajectories_per_s": B / dt, "trajectories_per_s_kernel_only": B / (g["kernel_ms"] * 1e-3),
+                    "sample_checks_per_s": B * T * ns / dt, "kernel_ms": g["kernel_ms"],
+                    "P_mean": float(g["P"].mean()), "P_std": float(g["P"].std())}
         except Exception as exc:
             out["gmm_error"] = repr(exc)
     return out

@@ -220,6 +220,30 @@ typedef struct {
 int mcsim_cuda_gmm_run(mcsim_cuda_ctx* ctx, const mcsim_mc_params* mc, const mcsim_gmm_run_params* g,
                        mcsim_gmm_run_result* r);
 
+/* Batched form (Philox mode): n_traj independent runGMMEstimation runs in the same launches -- the
+ * driver's 200-run loop (MCSimulation.py:226-246) or many candidate plans at once.  One run is a chain
+ * of T dependent sample -> refit steps that leaves most of the GPU idle at the reference's N = 10^4;
+ * the batch fills it.  Member b is exactly mcsim_cuda_gmm_run with rollout_offset = stream0 + b (and
+ * plan b when trajectories / odometry are given). */
+typedef struct {
+    int K;
+    uint64_t n_samples;
+    int n_traj;
+    const double* trajectories;  /* [n_traj][3][T] or NULL: every member runs mc->trajectory */
+    const double* odometry;      /* [n_traj][3][T-1] or NULL */
+    uint64_t stream0;
+} mcsim_gmm_batch_params;
+
+typedef struct {
+    double* P;                   /* [n_traj] */
+    double* probabilities;       /* [n_traj][T] optional */
+    int degenerate;              /* summed over the batch */
+    float kernel_ms;
+} mcsim_gmm_batch_result;
+
+int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* ctx, const mcsim_mc_params* mc, const mcsim_gmm_batch_params* g,
+                             mcsim_gmm_batch_result* r);
+
 /* ---- EM fit of full-covariance 3-D mixtures (BASELINE.json config 5) ------------------------ */
 /* Replaces arma::gmm_full::learn(X, K, dist, keep_existing, km_iter = 0, em_iter, var_floor)
  * (armadillo-8.400.0/include/armadillo_bits/gmm_full_meat.hpp:764-890): em_iterate :2390-2484,

@@ -68,7 +68,24 @@ struct GmmLaunch {
     unsigned long long* n_out;    // [2K] n_coll, n_free of this truncation (optional)
     int* degenerate;              // count of (waypoint, component) refits with < 2 free samples
     int do_ekf;                   // refit kernel: propagate to waypoint t+1 (0 for the single-shot API)
+    int B;                        // batch: independent trajectories in the same launches (Philox mode; 0/1 = single)
 };
+
+// Batch member b (blockIdx.y of the count / sample kernels, blockIdx.x of the refit kernel): same plan-independent
+// fields, its own mixture, statistics, counts, step table, per-waypoint probabilities and Philox subsequence.
+__device__ __forceinline__ GmmLaunch gmm_member(const GmmLaunch& in, int b) {
+    GmmLaunch a = in;
+    if (b > 0) {
+        a.comps += size_t(b) * MCSIM_MAX_GAUSSIANS * GMM_COMP;
+        a.stats += size_t(b) * MCSIM_MAX_GAUSSIANS * GMM_STAT;
+        a.hist += size_t(b) * MCSIM_MAX_GAUSSIANS;
+        a.steps += size_t(b) * (in.T > 1 ? in.T - 1 : 1);
+        a.probabilities += size_t(b) * in.T;
+        a.degenerate += b;
+        a.stream_id += unsigned(b);
+    }
+    return a;
+}
 
 // ---- FP64 SAT, statement order of oracle/sat_cpu.h (no contraction: _rn intrinsics) --------------------------
 __device__ __forceinline__ double gap_d(double hcx, double hcy, double ch, double sh, double hhx, double hhy, const PairD& b) {
@@ -107,7 +124,8 @@ __device__ __forceinline__ double clearance_d(const HullD* hulls, const PairD* p
 }
 
 // ---- multinomial counts (Philox mode): inverse CDF on one uniform per sample -----------------------------------
-__global__ void __launch_bounds__(256) gmm_count_kernel(const GmmLaunch a) {
+__global__ void __launch_bounds__(256) gmm_count_kernel(const GmmLaunch a_in) {
+    const GmmLaunch a = gmm_member(a_in, blockIdx.y);
     __shared__ float s_cdf[MCSIM_MAX_GAUSSIANS];
     __shared__ unsigned s_hist[MCSIM_MAX_GAUSSIANS];
     if (threadIdx.x < MCSIM_MAX_GAUSSIANS) s_hist[threadIdx.x] = 0;
@@ -139,7 +157,8 @@ __global__ void __launch_bounds__(256) gmm_count_kernel(const GmmLaunch a) {
 
 // ---- sample -> collide -> moments -------------------------------------------------------------------------------
 template <int MODE>
-__global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a) {
+__global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
+    const GmmLaunch a = gmm_member(a_in, blockIdx.y);
     __shared__ double s_comp[MCSIM_MAX_GAUSSIANS][GMM_COMP];
     __shared__ double s_stat[MCSIM_MAX_GAUSSIANS][GMM_STAT];
     __shared__ unsigned long long s_prefix[MCSIM_MAX_GAUSSIANS + 1];
@@ -252,7 +271,8 @@ __host__ __device__ inline bool gmm_chol3(const double* A, double* Lo) {
 }
 
 // ---- refit + propagate: one thread per component ------------------------------------------------------------------
-__global__ void __launch_bounds__(32) gmm_refit_kernel(const GmmLaunch a) {
+__global__ void __launch_bounds__(32) gmm_refit_kernel(const GmmLaunch a_in) {
+    const GmmLaunch a = gmm_member(a_in, blockIdx.x);
     using namespace mcsim_math;
     __shared__ double s_free[MCSIM_MAX_GAUSSIANS], s_coll[MCSIM_MAX_GAUSSIANS];
     const int g = threadIdx.x;

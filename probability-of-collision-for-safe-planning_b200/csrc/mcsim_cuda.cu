@@ -519,20 +519,20 @@ static void host_normals(uint64_t seed, unsigned stream_id, int T, int per_step,
     if (!out.empty()) mcsim_host_normals(seed, stream_id, T, per_step, out.data());
 }
 
-static int gmm_reserve(mcsim_cuda_ctx* c, int T, int K) {
-    CK(c->gmm_comps.reserve(sizeof(double) * MCSIM_MAX_GAUSSIANS * GMM_COMP));
-    CK(c->gmm_stats.reserve(sizeof(double) * MCSIM_MAX_GAUSSIANS * GMM_STAT));
-    CK(c->gmm_hist.reserve(sizeof(unsigned) * MCSIM_MAX_GAUSSIANS));
-    CK(c->gmm_prob.reserve(sizeof(double) * T));
+static int gmm_reserve(mcsim_cuda_ctx* c, int T, int K, int B = 1) {
+    CK(c->gmm_comps.reserve(sizeof(double) * MCSIM_MAX_GAUSSIANS * GMM_COMP * B));
+    CK(c->gmm_stats.reserve(sizeof(double) * MCSIM_MAX_GAUSSIANS * GMM_STAT * B));
+    CK(c->gmm_hist.reserve(sizeof(unsigned) * MCSIM_MAX_GAUSSIANS * B));
+    CK(c->gmm_prob.reserve(sizeof(double) * T * B));
     CK(c->gmm_pre.reserve(sizeof(double) * size_t(T) * K * GMM_REC));
     CK(c->gmm_post.reserve(sizeof(double) * K * GMM_REC));
     CK(c->gmm_trunc.reserve(sizeof(double) * K * GMM_REC));
     CK(c->gmm_nout.reserve(sizeof(unsigned long long) * 2 * MCSIM_MAX_GAUSSIANS));
-    CK(c->gmm_deg.reserve(sizeof(int)));
-    CK(c->gmm_steps.reserve(sizeof(GmmStepTable) * (T > 1 ? T - 1 : 1)));
-    CK(cudaMemsetAsync(c->gmm_stats.p, 0, sizeof(double) * MCSIM_MAX_GAUSSIANS * GMM_STAT, c->stream));
-    CK(cudaMemsetAsync(c->gmm_hist.p, 0, sizeof(unsigned) * MCSIM_MAX_GAUSSIANS, c->stream));
-    CK(cudaMemsetAsync(c->gmm_deg.p, 0, sizeof(int), c->stream));
+    CK(c->gmm_deg.reserve(sizeof(int) * B));
+    CK(c->gmm_steps.reserve(sizeof(GmmStepTable) * (T > 1 ? T - 1 : 1) * B));
+    CK(cudaMemsetAsync(c->gmm_stats.p, 0, sizeof(double) * MCSIM_MAX_GAUSSIANS * GMM_STAT * B, c->stream));
+    CK(cudaMemsetAsync(c->gmm_hist.p, 0, sizeof(unsigned) * MCSIM_MAX_GAUSSIANS * B, c->stream));
+    CK(cudaMemsetAsync(c->gmm_deg.p, 0, sizeof(int) * B, c->stream));
     return MCSIM_OK;
 }
 
@@ -558,7 +558,8 @@ static int gmm_launch_waypoint(mcsim_cuda_ctx* c, const GmmLaunch& a, int mode) 
     const int block = a.n < (unsigned long long)c->n_sm * 256 ? 64 : 256;
     unsigned long long want = (a.n + block - 1) / block;
     const unsigned long long cap = (unsigned long long)c->n_sm * 8;
-    const unsigned grid = unsigned(want < cap ? (want ? want : 1) : cap);
+    const unsigned B = a.B > 1 ? unsigned(a.B) : 1u;
+    const dim3 grid(unsigned(want < cap ? (want ? want : 1) : cap), B);
     if (mode == MCSIM_MODE_PHILOX) {
         gmm_count_kernel<<<grid, block, 0, c->stream>>>(a);
         gmm_sample_kernel<MCSIM_MODE_PHILOX><<<grid, block, 0, c->stream>>>(a);
@@ -567,7 +568,7 @@ static int gmm_launch_waypoint(mcsim_cuda_ctx* c, const GmmLaunch& a, int mode) 
         gmm_sample_kernel<MCSIM_MODE_REPLAY><<<grid, block, 0, c->stream>>>(a);
         c->launches += 1;
     }
-    gmm_refit_kernel<<<1, 32, 0, c->stream>>>(a);
+    gmm_refit_kernel<<<B, 32, 0, c->stream>>>(a);
     c->launches += 1;
     CK(cudaGetLastError());
     return MCSIM_OK;
@@ -1017,5 +1018,86 @@ extern "C" int mcsim_cuda_score_plans(mcsim_cuda_ctx* c, const mcsim_score_param
     CK(cudaEventRecord(c->ev1, c->stream));
     if ((rc = mcsim_cuda_score_collect(c, r))) return rc;
     CK(cudaEventElapsedTime(&r->kernel_ms, c->ev0, c->ev1));
+    return MCSIM_OK;
+}
+
+// ---- batched GMM mode: n_traj independent runGMMEstimation runs in the same launches ----------------
+extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, const mcsim_gmm_batch_params* g,
+                                        mcsim_gmm_batch_result* r) {
+    if (!c || !mc || !g || !r || !r->P) return fail(MCSIM_ERR_ARG, "gmm_run_batch: NULL argument");
+    if (!c->scene_set) return fail(MCSIM_ERR_ARG, "gmm_run_batch: mcsim_cuda_set_scene has not been called");
+    if (mc->mode != MCSIM_MODE_PHILOX) return fail(MCSIM_ERR_ARG, "gmm_run_batch: Philox mode only");
+    const int T = mc->T, K = g->K, L = mc->n_landmarks, B = g->n_traj;
+    const uint64_t N = g->n_samples;
+    if (T < 1 || T > MCSIM_MAX_WAYPOINTS || !mc->trajectory || (T > 1 && !mc->odometry)) return fail(MCSIM_ERR_ARG, "gmm_run_batch: bad plan");
+    if (K < 1 || K > MCSIM_MAX_GAUSSIANS || N < 1 || B < 1 || B > 65535) return fail(MCSIM_ERR_ARG, "gmm_run_batch: bad K / n_samples / n_traj");
+    if (L < 0 || L > MCSIM_MAX_LANDMARKS || (L && !mc->landmarks)) return fail(MCSIM_ERR_ARG, "gmm_run_batch: bad landmarks");
+    if ((g->trajectories == nullptr) != (g->odometry == nullptr)) return fail(MCSIM_ERR_ARG, "gmm_run_batch: trajectories and odometry go together");
+    CK(cudaSetDevice(c->device));
+    const int per_step = 3 + L, TS = T > 1 ? T - 1 : 1;
+    std::vector<GmmStepTable> steps(size_t(B) * TS);
+    std::vector<double> comps(size_t(B) * MCSIM_MAX_GAUSSIANS * GMM_COMP, 0.0);
+    std::vector<double> hn, applied(size_t(3) * TS), obs(size_t(TS) * (L ? L : 1));
+    mcsim_math::NoiseModel<double> nmd;
+    for (int k = 0; k < 4; ++k) nmd.alpha[k] = mc->alphas[k];
+    double Lo[6];
+    if (!gmm_chol3(mc->cov0, Lo)) return fail(MCSIM_ERR_ARG, "gmm_run_batch: initial covariance is not positive definite");
+    for (int b = 0; b < B; ++b) {
+        mcsim_mc_params pb = *mc;
+        if (g->trajectories) { pb.trajectory = g->trajectories + size_t(b) * 3 * T; pb.odometry = g->odometry + size_t(b) * 3 * (T - 1); }
+        // the member's shared real-robot thread (host, FP64), its own Philox subsequence
+        host_normals(mc->seed, unsigned(g->stream0 + b), T, per_step, hn);
+        if (T > 1) {
+            int rc = mcsim_host_thread(&pb, hn.data(), hn.size(), nullptr, applied.data(), nullptr, nullptr, nullptr, obs.data());
+            if (rc) return fail(rc, "gmm_run_batch: host thread of member %d failed (%d)", b, rc);
+        }
+        for (int t = 0; t < T - 1; ++t) {
+            GmmStepTable& s = steps[size_t(b) * TS + t];
+            double us[3];
+            for (int k = 0; k < 3; ++k) { us[k] = pb.odometry[k * (T - 1) + t]; s.u[k] = applied[k * (T - 1) + t]; }
+            mcsim_math::motion_noise(nmd, us, s.M);
+            for (int l = 0; l < L; ++l) s.z[l] = obs[size_t(t) * L + l];
+        }
+        for (int k = 0; k < K; ++k) {
+            double* cp = &comps[(size_t(b) * MCSIM_MAX_GAUSSIANS + k) * GMM_COMP];
+            cp[0] = 1.0 / K;
+            for (int i = 0; i < 3; ++i) cp[1 + i] = pb.trajectory[i * T];
+            for (int i = 0; i < 9; ++i) cp[4 + i] = mc->cov0[i];
+            for (int i = 0; i < 6; ++i) cp[13 + i] = Lo[i];
+        }
+    }
+    int rc = gmm_reserve(c, T, K, B);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(c->gmm_comps.p, comps.data(), sizeof(double) * comps.size(), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->gmm_steps.p, steps.data(), sizeof(GmmStepTable) * steps.size(), cudaMemcpyHostToDevice, c->stream));
+    c->h2d_bytes = sizeof(double) * comps.size() + sizeof(GmmStepTable) * steps.size();
+    GmmLaunch a;
+    gmm_fill_launch(c, a, K, T, L, N, mc->seed, unsigned(g->stream0));
+    a.Q = mc->Q;
+    for (int l = 0; l < L; ++l) { a.lx[l] = mc->landmarks[l]; a.ly[l] = mc->landmarks[L + l]; }
+    a.do_ekf = 1;
+    a.B = B;
+    CK(cudaEventRecord(c->ev0, c->stream));
+    for (int t = 0; t < T; ++t) {
+        a.t = t;
+        rc = gmm_launch_waypoint(c, a, MCSIM_MODE_PHILOX);
+        if (rc) return rc;
+    }
+    CK(cudaEventRecord(c->ev1, c->stream));
+    std::vector<double> prob(size_t(B) * T);
+    std::vector<int> deg(B);
+    CK(cudaMemcpyAsync(prob.data(), c->gmm_prob.p, sizeof(double) * prob.size(), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(deg.data(), c->gmm_deg.p, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->d2h_bytes = sizeof(double) * prob.size() + sizeof(int) * B;
+    CK(cudaEventElapsedTime(&r->kernel_ms, c->ev0, c->ev1));
+    r->degenerate = 0;
+    for (int b = 0; b < B; ++b) {
+        double free_all = 1.0;  // P = 1 - prod_t (1 - p_t)  (MCSimulator.h:848-856)
+        for (int t = 0; t < T; ++t) free_all *= (1.0 - prob[size_t(b) * T + t]);
+        r->P[b] = 1.0 - free_all;
+        r->degenerate += deg[b];
+    }
+    if (r->probabilities) memcpy(r->probabilities, prob.data(), sizeof(double) * prob.size());
     return MCSIM_OK;
 }

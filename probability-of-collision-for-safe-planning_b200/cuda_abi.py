@@ -55,6 +55,15 @@ class EmResult(C.Structure):
     ]
 
 
+class GmmBatchParams(C.Structure):
+    _fields_ = [("K", C.c_int), ("n_samples", C.c_uint64), ("n_traj", C.c_int), ("trajectories", _dp), ("odometry", _dp),
+                ("stream0", C.c_uint64)]
+
+
+class GmmBatchResult(C.Structure):
+    _fields_ = [("P", _dp), ("probabilities", _dp), ("degenerate", C.c_int), ("kernel_ms", C.c_float)]
+
+
 class ScoreParams(C.Structure):
     _fields_ = [
         ("T", C.c_int), ("n_plans", C.c_int), ("trajectories", _dp), ("odometry", _dp),
@@ -136,6 +145,7 @@ def lib():
         L.mcsim_host_normals.argtypes = [C.c_uint64, C.c_uint32, C.c_int, C.c_int, _dp]
         L.mcsim_cuda_gmm_truncate.argtypes = [vp, C.POINTER(GmmTruncateParams), C.POINTER(GmmTruncateResult)]
         L.mcsim_cuda_gmm_run.argtypes = [vp, C.POINTER(McParams), C.POINTER(GmmRunParams), C.POINTER(GmmRunResult)]
+        L.mcsim_cuda_gmm_run_batch.argtypes = [vp, C.POINTER(McParams), C.POINTER(GmmBatchParams), C.POINTER(GmmBatchResult)]
         L.mcsim_truncate_linear.argtypes = [_dp, _dp, C.c_int, _dp, _dp, _dp, _dp, _dp]
         L.mcsim_cuda_score_plans.argtypes = [vp, C.POINTER(ScoreParams), C.POINTER(ScoreResult)]
         L.mcsim_cuda_score_prepare.argtypes = [vp, C.POINTER(ScoreParams)]
@@ -473,6 +483,26 @@ class Context:
         raw = _Raw()
         raw.__cuda_array_interface__ = dict(shape=(int(n.value),), typestr="<f8", version=2, data=(int(ptr), False))
         return torch.as_tensor(raw, device="cuda:%d" % self.device)
+
+    def gmm_run_batch(self, plan, K, n_samples, n_traj, trajectories=None, odometry=None, seed=0x5AFEC0DE, stream0=0):
+        """n_traj independent runGMMEstimation runs in the same launches (Philox mode); member b ==
+        gmm_run(..., stream_id=stream0 + b) on plan b (trajectories [n_traj, 3, T]) or on `plan`."""
+        p, keep = make_mc_params(plan, mode=MODE_PHILOX, seed=seed)
+        T = int(p.T)
+        g = GmmBatchParams()
+        g.K, g.n_samples, g.n_traj, g.stream0 = int(K), int(n_samples), int(n_traj), int(stream0)
+        if trajectories is not None:
+            tr = np.ascontiguousarray(trajectories, dtype=np.float64)
+            od = np.ascontiguousarray(odometry, dtype=np.float64)
+            assert tr.shape == (n_traj, 3, T) and od.shape == (n_traj, 3, T - 1)
+            keep += [tr, od]
+            g.trajectories, g.odometry = dptr(tr), dptr(od)
+        out = dict(P=np.zeros(n_traj), probabilities=np.zeros((n_traj, T)))
+        r = GmmBatchResult()
+        r.P, r.probabilities = dptr(out["P"]), dptr(out["probabilities"])
+        check(lib().mcsim_cuda_gmm_run_batch(self._h, C.byref(p), C.byref(g), C.byref(r)))
+        out.update(degenerate=int(r.degenerate), kernel_ms=float(r.kernel_ms))
+        return out
 
     def gmm_truncate(self, weights, means, covs, n_samples, mode=MODE_PHILOX, counts=None, normals=None,
                      seed=0x5AFEC0DE, stream_id=0):

@@ -111,3 +111,24 @@ def test_gmm_philox_statistics(ctx, plan, scenes):
     print("GMM philox: ours mean %.4f (std %.4f), reference mean %.4f (std %.4f), 99%% half-width %.4f" %
           (ours.mean(), ours.std(ddof=1), ref.mean(), ref.std(ddof=1), half))
     assert abs(ours.mean() - ref.mean()) < half
+
+
+def test_gmm_batch_members_equal_single_runs(ctx, plan, scenes):
+    """mcsim_cuda_gmm_run_batch: member b == mcsim_cuda_gmm_run on Philox subsequence stream0 + b (the FP64
+    sums are accumulated in a different order: agreement to 1e-9, not bit-exact)."""
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    ctx.set_scene(scenes["pr2test2"]["boxes"], scenes["pr2test2"]["hulls"])
+    batch = ctx.gmm_run_batch(plan, 3, 5000, 7, stream0=11)
+    for b in range(7):
+        one = ctx.gmm_run(plan, 3, 5000, mode=abi.MODE_PHILOX, stream_id=11 + b)
+        np.testing.assert_allclose(batch["probabilities"][b], one["probabilities"], rtol=1e-9, atol=1e-12)
+        np.testing.assert_allclose(batch["P"][b], one["P"], rtol=1e-9)
+    assert len(set(np.round(batch["P"], 6))) > 1     # different subsequences, different runs
+    # different plans in one batch: plan 0 = the committed plan, plan 1 = the same plan driven backwards in time is
+    # not a valid plan, so use a shifted copy (same odometry, start moved 5 cm)
+    tr = np.stack([plan["trajectory"], plan["trajectory"] + np.array([[0.05], [0.0], [0.0]])])
+    od = np.stack([plan["odometry"], plan["odometry"]])
+    two = ctx.gmm_run_batch(plan, 3, 5000, 2, trajectories=tr, odometry=od, stream0=11)
+    np.testing.assert_allclose(two["P"][0], batch["P"][0], rtol=1e-9)
+    assert two["P"][1] != two["P"][0]
