@@ -55,6 +55,7 @@ const MCModule::Command MCModule::kCommands[] = {
     {"setNumGMMSamples", &MCModule::setNumGMMSamples, "This is to set number of samples for GMM collision estimation"},
     {"help", &MCModule::help, "display this message."},
     // additions
+    {"runGMMEstimationBatch", &MCModule::runGMMEstimationBatch, "runGMMEstimationBatch <n>: the next n runGMMEstimation runs in the same launches; n probabilities"},
     {"setSeed", &MCModule::setSeed, "setSeed <u64>: Philox key; restarts the run counter"},
     {"setMode", &MCModule::setMode, "setMode shared|philox|deterministic: how the draws of a run are produced"},
     {"setDrawsFile", &MCModule::setDrawsFile, "setDrawsFile <path>: float64 little-endian standard normals in the reference's consumption order"},

@@ -62,6 +62,7 @@ class MCModule {
     bool runSimulation(std::ostream&, std::istream&);
     bool setNumGaussians(std::ostream&, std::istream&);
     bool runGMMEstimation(std::ostream&, std::istream&);
+    bool runGMMEstimationBatch(std::ostream&, std::istream&);
     bool setNumGMMSamples(std::ostream&, std::istream&);
     bool help(std::ostream&, std::istream&);
     // -- additions (never required by the reference driver)

@@ -137,6 +137,37 @@ bool MCModule::runGMMEstimation(std::ostream& sout, std::istream&) {
     return true;
 }
 
+// runGMMEstimationBatch <n>: the next n runs of runGMMEstimation (the driver's loop, MCSimulation.py:226-246) in the
+// same launches; returns the n probabilities separated by spaces.  Run k of the batch is bit-for-bit the run that
+// the (run_index + k)-th runGMMEstimation call would have been up to the summation order of the FP64 moments.
+bool MCModule::runGMMEstimationBatch(std::ostream& sout, std::istream& sinput) {
+    int n = 0;
+    if (!(sinput >> n) || n < 1 || n > 65535) throw std::runtime_error("runGMMEstimationBatch: a run count 1..65535 expected");
+    if (mode_ == Mode::kDeterministic) throw std::runtime_error("runGMMEstimationBatch: not available in deterministic mode (one injected draw stream = one run)");
+    mcsim_mc_params p;
+    fill_params(p);
+    if (num_gaussians_ < 1) throw std::runtime_error("setNumGaussians has not been sent");
+    if (num_gmm_samples_ < 1) throw std::runtime_error("setNumGMMSamples has not been sent");
+    p.mode = MCSIM_MODE_PHILOX;
+    mcsim_gmm_batch_params g;
+    std::memset(&g, 0, sizeof(g));
+    g.K = num_gaussians_;
+    g.n_samples = uint64_t(num_gmm_samples_);
+    g.n_traj = n;
+    g.stream0 = rollout_offset_ + run_index_;
+    std::vector<double> P(size_t(n), 0.0);
+    mcsim_gmm_batch_result r;
+    std::memset(&r, 0, sizeof(r));
+    r.P = P.data();
+    cuda_check(mcsim_cuda_gmm_run_batch(ctx_, &p, &g, &r), "mcsim_cuda_gmm_run_batch");
+    run_index_ += uint64_t(n);
+    last_kernel_ms_ = r.kernel_ms;
+    last_degenerate_ = r.degenerate;
+    last_n_ = g.n_samples * uint64_t(n); last_hits_ = 0; last_steps_ = uint64_t(p.T) * g.n_samples * uint64_t(n); last_tests_ = 0;
+    for (int k = 0; k < n; ++k) sout << (k ? " " : "") << P[size_t(k)];
+    return true;
+}
+
 // ---- additions ---------------------------------------------------------------------------------------------------
 bool MCModule::setSeed(std::ostream&, std::istream& sinput) {
     unsigned long long s;

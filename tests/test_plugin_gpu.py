@@ -116,3 +116,21 @@ def test_py3_driver_twin_mc_and_gmm(tmp_path):
             assert key in text
         ck = open(out["checkpoint"]).read()
         assert ck.count("collProp: ") == 3 and "Simulation: 2" in ck
+
+
+def test_run_gmm_estimation_batch_command_equals_the_loop():
+    """runGMMEstimationBatch <n> == the next n runGMMEstimation calls (MCSimulation.py:226-246 in one launch chain)."""
+    import pcoll_b200
+    plan = pcoll_b200.load_plan_json(os.path.join(GOLD, "plan_committed.json"))
+    outs = []
+    for batched in (False, True):
+        mod = pcoll_b200.MCModule(os.path.join(ROOT, "data", "scenes", "pr2test2.env.xml"), device=0)
+        pcoll_b200.push_parameters(mod, plan, num_particles=4000, num_gaussians=3, num_gmm_samples=4000)
+        mod.SendCommand("setSeed 9")
+        if batched:
+            outs.append([float(v) for v in mod.SendCommand("runGMMEstimationBatch 5").split()])
+        else:
+            outs.append([float(mod.SendCommand("runGMMEstimation")) for _ in range(5)])
+        mod.close()
+    np.testing.assert_allclose(outs[0], outs[1], rtol=1e-5)   # text round trip: 6 significant digits
+    assert len(set(outs[1])) > 1

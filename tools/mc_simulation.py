@@ -63,6 +63,9 @@ def main(argv=None):
     ap.add_argument("--seed", type=int, default=None)
     ap.add_argument("--device", type=int, default=0)
     ap.add_argument("--outdir", default=".")
+    ap.add_argument("--batch", action="store_true",
+                    help="GMM only: the whole run loop as ONE runGMMEstimationBatch command (same runs, same files; "
+                         "simTime of each run = batch time / runs)")
     a = ap.parse_args(argv)
 
     plan = pcoll_b200.plan_from_pickles(a.trajectory, a.odometry)
@@ -82,10 +85,15 @@ def main(argv=None):
     sim_times, proportions = [], []
     ck = os.path.join(a.outdir, ("GMMcheckpoint_" if gmm else "checkpoint_") + st + ".txt")
     with open(ck, "w") as f2:
+        batch = None
+        if gmm and a.batch:
+            start = time.perf_counter()
+            batch = [float(v) for v in mod.SendCommand("runGMMEstimationBatch %d" % a.num_simulations).split()]
+            batch_time = (time.perf_counter() - start) / a.num_simulations
         for i in range(a.num_simulations):
             start = time.perf_counter()
-            collprop = float(mod.SendCommand("runGMMEstimation" if gmm else "runSimulation"))
-            sim_time = time.perf_counter() - start
+            collprop = batch[i] if batch else float(mod.SendCommand("runGMMEstimation" if gmm else "runSimulation"))
+            sim_time = batch_time if batch else time.perf_counter() - start
             print("Python got collision proportion: ", collprop)
             print("Python Simulation Time: ", sim_time)
             sim_times.append(sim_time)
