@@ -17,6 +17,7 @@
 
 #include <float.h>
 
+#include "f32x2.cuh"
 #include "mcsim_cuda.h"
 
 #define EM_COMP_STRIDE 12  // floats per component: mu[3], b00 b01 b02 b11 b12 b22, cst, pad[2]
@@ -155,6 +156,125 @@ __global__ void __launch_bounds__(256) em_estep_kernel(const EmLaunch a) {
     double* st = a.stats + (size_t)fit * (K * EM_NSTAT + 1);
     for (int i = threadIdx.x; i < KG * EM_NSTAT; i += blockDim.x) atomicAdd(&st[G0 * EM_NSTAT + i], s_acc[i]);
     if (G0 == 0 && threadIdx.x == 0) atomicAdd(&st[K * EM_NSTAT], s_acc[NACC - 1]);
+}
+
+// ---- E-step, packed: two samples per thread in the lanes of FFMA2 / FMUL2 / FADD2 (K <= 4) ----------------
+// The E-step is almost pure FP32 arithmetic (no compares / selects to speak of), which is where packed
+// pairs pay on sm_100a (tools/pipe_probe.cu): half the FMA-pipe issue slots per sample.  Same arithmetic
+// per lane as em_estep_kernel; MUFU (ex2, lg2, rcp) and the running maximum stay per lane.
+template <int K>
+__global__ void __launch_bounds__(256) em_estep2_kernel(const EmLaunch a) {
+    constexpr int NACC = K * EM_NSTAT + 1;
+    __shared__ __align__(16) float s_c[K * EM_COMP_STRIDE];
+    __shared__ double s_acc[NACC];
+    const int fit = blockIdx.y;
+    if (a.done[fit]) return;
+    for (int i = threadIdx.x; i < K * EM_COMP_STRIDE; i += blockDim.x) s_c[i] = a.comps[(size_t)fit * K * EM_COMP_STRIDE + i];
+    for (int i = threadIdx.x; i < NACC; i += blockDim.x) s_acc[i] = 0.0;
+    __syncthreads();
+    const float* xs = a.x + (size_t)fit * 3 * a.n;
+    const float* ys = xs + a.n;
+    const float* ts = ys + a.n;
+    f2 acc[K][EM_NSTAT];
+#pragma unroll
+    for (int g = 0; g < K; ++g)
+#pragma unroll
+        for (int k = 0; k < EM_NSTAT; ++k) acc[g][k] = bc(0.f);
+    f2 lsum = bc(0.f);
+
+    constexpr int U = 2;  // pairs per pass: 4 samples, 12 loads in flight while the previous 4 are processed
+    const unsigned n = unsigned(a.n);
+    const unsigned stride = gridDim.x * blockDim.x;
+    unsigned i = blockIdx.x * blockDim.x + threadIdx.x;   // lane 0 of pair u: i + 2 u stride, lane 1: i + (2 u + 1) stride
+    float bx[2 * U], by[2 * U], bt[2 * U];
+#pragma unroll
+    for (int u = 0; u < 2 * U; ++u) {
+        const unsigned k = i + u * stride;
+        const bool ok = k < n;
+        bx[u] = ok ? __ldg(xs + k) : 0.f; by[u] = ok ? __ldg(ys + k) : 0.f; bt[u] = ok ? __ldg(ts + k) : 0.f;
+    }
+    for (; i < n; i += 2 * U * stride) {
+        float cx[2 * U], cy[2 * U], ct[2 * U];
+#pragma unroll
+        for (int u = 0; u < 2 * U; ++u) { cx[u] = bx[u]; cy[u] = by[u]; ct[u] = bt[u]; }
+#pragma unroll
+        for (int u = 0; u < 2 * U; ++u) {
+            const unsigned k = i + (2 * U + u) * stride;
+            const bool ok = k < n;
+            bx[u] = ok ? __ldg(xs + k) : 0.f; by[u] = ok ? __ldg(ys + k) : 0.f; bt[u] = ok ? __ldg(ts + k) : 0.f;
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            if (i + 2 * u * stride >= n) break;
+            const float v1 = (i + (2 * u + 1) * stride < n) ? 1.f : 0.f;   // lane 1 may be past the end
+            const f2 x = mk2(cx[2 * u], cx[2 * u + 1]), y = mk2(cy[2 * u], cy[2 * u + 1]), t = mk2(ct[2 * u], ct[2 * u + 1]);
+            f2 ll[K];
+            float m0 = -FLT_MAX, m1 = -FLT_MAX;
+#pragma unroll
+            for (int g = 0; g < K; ++g) {
+                const float4* c4 = reinterpret_cast<const float4*>(s_c + g * EM_COMP_STRIDE);
+                const float4 ca = c4[0], cb = c4[1], cc = c4[2];
+                const f2 d0 = add2(x, -ca.x), d1 = add2(y, -ca.y), d2 = add2(t, -ca.z);
+                const f2 q0 = fma2(d0, ca.w, fma2(d1, cb.x, mul2(d2, cb.y)));
+                const f2 q1 = fma2(d1, cb.z, mul2(d2, cb.w));
+                ll[g] = fma2(d0, q0, fma2(d1, q1, fma2(mul2(d2, cc.x), d2, cc.y)));
+                m0 = fmaxf(m0, lo(ll[g]));
+                m1 = fmaxf(m1, hi(ll[g]));
+            }
+            const f2 mm = mk2(m0, m1);
+            const f2 ms = mul2(mm, -1.4426950408889634f);
+            f2 s = bc(0.f);
+#pragma unroll
+            for (int g = 0; g < K; ++g) {
+                const f2 e = fma2(ll[g], 1.4426950408889634f, ms);
+                float e0, e1;
+                un2(e, e0, e1);
+                asm("ex2.approx.ftz.f32 %0, %0;" : "+f"(e0));
+                asm("ex2.approx.ftz.f32 %0, %0;" : "+f"(e1));
+                ll[g] = mk2(e0, e1);
+                s = add2(s, ll[g]);
+            }
+            const f2 lg = mk2(mufu_lg2(lo(s)), mufu_lg2(hi(s)));
+            const f2 valid = mk2(1.f, v1);
+            lsum = fma2(fma2(lg, 0.6931471805599453f, mm), valid, lsum);   // (m + ln s) per valid lane
+            const f2 inv = mul2(rcp2(s), valid);
+#pragma unroll
+            for (int g = 0; g < K; ++g) {
+                const float4 ca = *reinterpret_cast<const float4*>(s_c + g * EM_COMP_STRIDE);
+                const f2 r = mul2(ll[g], inv);
+                const f2 d0 = add2(x, -ca.x), d1 = add2(y, -ca.y), d2 = add2(t, -ca.z);
+                const f2 r0 = mul2(r, d0), r1 = mul2(r, d1), r2 = mul2(r, d2);
+                acc[g][0] = add2(acc[g][0], r);
+                acc[g][1] = add2(acc[g][1], r0);
+                acc[g][2] = add2(acc[g][2], r1);
+                acc[g][3] = add2(acc[g][3], r2);
+                acc[g][4] = fma2(r0, d0, acc[g][4]);
+                acc[g][5] = fma2(r0, d1, acc[g][5]);
+                acc[g][6] = fma2(r0, d2, acc[g][6]);
+                acc[g][7] = fma2(r1, d1, acc[g][7]);
+                acc[g][8] = fma2(r1, d2, acc[g][8]);
+                acc[g][9] = fma2(r2, d2, acc[g][9]);
+            }
+        }
+    }
+#pragma unroll
+    for (int g = 0; g < K; ++g)
+#pragma unroll
+        for (int k = 0; k < EM_NSTAT; ++k) {
+            double v = double(lo(acc[g][k])) + double(hi(acc[g][k]));
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if ((threadIdx.x & 31) == 0) atomicAdd(&s_acc[g * EM_NSTAT + k], v);
+        }
+    {
+        double v = double(lo(lsum)) + double(hi(lsum));
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) atomicAdd(&s_acc[NACC - 1], v);
+    }
+    __syncthreads();
+    double* st = a.stats + (size_t)fit * NACC;
+    for (int k = threadIdx.x; k < NACC; k += blockDim.x) atomicAdd(&st[k], s_acc[k]);
 }
 
 // ---- M-step, parameter sanitising, convergence test and the next iteration's constants (FP64) --------

@@ -757,6 +757,7 @@ template <int K>
 static void em_pick(em_kernel_t& k0, em_kernel_t& k1) {
     k0 = em_estep_kernel<K, 0>;
     k1 = nullptr;
+    if constexpr (K <= 4) k0 = em_estep2_kernel<K>;  // packed: two samples per thread
     if constexpr (K > 8) k1 = em_estep_kernel<K, 8>;
 }
 static bool em_kernels(int K, em_kernel_t& k0, em_kernel_t& k1) {
