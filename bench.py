@@ -287,7 +287,10 @@ def main():
         "clocks": clocks, "gpu_launches": launches, "e2e": e2e,
         "roofline": {
             "bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,
-            "traffic": None, "kernel": "mc_philox2_kernel<no early exit, reference estimator, L=8> (two rollouts per thread, packed FP32 pairs)",
+            "traffic": None,
+            "traffic_note": "no HBM input: tables in __constant__ / shared memory, state in registers; ncu capture of a 4e6-rollout "
+                            "launch: dram__bytes_read 52 KB, dram__bytes_write 0 (profiles/r01_philox2_grouped_ncu_summary.csv)",
+            "kernel": "mc_philox2_kernel<no early exit, reference estimator, L=8> (two rollouts per thread, packed FP32 pairs)",
             "kernel_ms_per_launch": kernel_ms / a.steps,
             "algorithmic": "%d flops per Philox rollout-step + %d per SAT pair test x %.1f live pair tests per step" % (
                 F_PHILOX_STEP, F_SAT, tot["pair_tests"] / job_steps),
@@ -301,6 +304,12 @@ def main():
             line["extras"].update(extras_scoring_em(ctx, abi, plan, sc, fp32_peak))
         except Exception as exc:  # reported, never silently dropped
             line["extras"]["scoring_em_error"] = repr(exc)
+    if rank == 0 and "extras" in line and "gmm_K3_N10000_batch1024" in line["extras"]:
+        g = line["extras"]["gmm_K3_N10000_batch1024"]
+        line["secondary"] = {"metric": "gmm_pcoll_trajectories_per_s", "value": g["trajectories_per_s"], "unit": "trajectories/s",
+                             "config": "runGMMEstimation, K = 3, 10^4 samples per waypoint, 56 waypoints, 1,024 runs per batch, "
+                                       "host buffers in and out (BASELINE configs[1])",
+                             "single_run_value": line["extras"].get("gmm_K3_N10000", {}).get("trajectories_per_s")}
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
         import oracle_ref
         if oracle_ref.available():

@@ -69,6 +69,7 @@ struct GmmLaunch {
     int* degenerate;              // count of (waypoint, component) refits with < 2 free samples
     int do_ekf;                   // refit kernel: propagate to waypoint t+1 (0 for the single-shot API)
     int B;                        // batch: independent trajectories in the same launches (Philox mode; 0/1 = single)
+    const float4* sat2;           // orientation-grouped FP32 pair table (Philox mode SAT)
 };
 
 // Batch member b (blockIdx.y of the count / sample kernels, blockIdx.x of the refit kernel): same plan-independent
@@ -189,37 +190,36 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
         bool hit = false;
         double d0 = 0.0, d1 = 0.0, d2 = 0.0;
         if (valid) {
-        while (g < K - 1 && i >= s_prefix[g + 1]) ++g;  // i only grows: the component index is monotone
-        double z0, z1, z2;
-        if (MODE == MCSIM_MODE_REPLAY) {
-            z0 = a.normals[3 * i]; z1 = a.normals[3 * i + 1]; z2 = a.normals[3 * i + 2];
-        } else {
-            mcsim_rng::u32x4 c = {unsigned(i), a.stream_id, unsigned(2 * a.t) | unsigned((i >> 32) << 16), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
-            c = mcsim_rng::philox4x32_10(c, a.k0, a.k1);
-            float f0, f1, f2, f3;
-            mcsim_rng::box_muller(c.x, c.y, f0, f1);
-            mcsim_rng::box_muller(c.z, c.w, f2, f3);
-            z0 = f0; z1 = f1; z2 = f2;
-        }
-        const double* cp = s_comp[g];
-        const double* Lc = cp + 13;
-        // d = L z in the summation order of a 3x3 times 3x1 product (left to right), no contraction
-        d0 = __dmul_rn(Lc[0], z0);
-        d1 = __dadd_rn(__dmul_rn(Lc[1], z0), __dmul_rn(Lc[2], z1));
-        d2 = __dadd_rn(__dadd_rn(__dmul_rn(Lc[3], z0), __dmul_rn(Lc[4], z1)), __dmul_rn(Lc[5], z2));
-        const double x = __dadd_rn(d0, cp[1]), y = __dadd_rn(d1, cp[2]), th = __dadd_rn(d2, cp[3]);
-        if (MODE == MCSIM_MODE_REPLAY) {
-            hit = clearance_d(a.hulls_d, a.pairs_d, a.n_hulls, x, y, th) <= 0.0;
-        } else {
-            float sn, cs;
-            // theta of a sample is mu_theta + O(sigma): reduce to [-pi, pi] before the FP32 sincos
-            double tr = th;
-            if (tr > MCSIM_PI) tr -= 2 * MCSIM_PI;
-            if (tr < -MCSIM_PI) tr += 2 * MCSIM_PI;
-            sincosf(float(tr), &sn, &cs);
-            unsigned nt = 0;
-            hit = robot_hits(float(x), float(y), cs, sn, nt);
-        }
+            while (g < K - 1 && i >= s_prefix[g + 1]) ++g;  // i only grows: the component index is monotone
+            double z0, z1, z2;
+            if (MODE == MCSIM_MODE_REPLAY) {
+                z0 = a.normals[3 * i]; z1 = a.normals[3 * i + 1]; z2 = a.normals[3 * i + 2];
+            } else {
+                mcsim_rng::u32x4 c = {unsigned(i), a.stream_id, unsigned(2 * a.t) | unsigned((i >> 32) << 16), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
+                c = mcsim_rng::philox4x32_10(c, a.k0, a.k1);
+                float f0, f1, f2, f3;
+                mcsim_rng::box_muller(c.x, c.y, f0, f1);
+                mcsim_rng::box_muller(c.z, c.w, f2, f3);
+                z0 = f0; z1 = f1; z2 = f2;
+            }
+            const double* cp = s_comp[g];
+            const double* Lc = cp + 13;
+            // d = L z in the summation order of a 3x3 times 3x1 product (left to right), no contraction
+            d0 = __dmul_rn(Lc[0], z0);
+            d1 = __dadd_rn(__dmul_rn(Lc[1], z0), __dmul_rn(Lc[2], z1));
+            d2 = __dadd_rn(__dadd_rn(__dmul_rn(Lc[3], z0), __dmul_rn(Lc[4], z1)), __dmul_rn(Lc[5], z2));
+            const double x = __dadd_rn(d0, cp[1]), y = __dadd_rn(d1, cp[2]), th = __dadd_rn(d2, cp[3]);
+            if (MODE == MCSIM_MODE_REPLAY) {
+                hit = clearance_d(a.hulls_d, a.pairs_d, a.n_hulls, x, y, th) <= 0.0;
+            } else {
+                float sn, cs;
+                // theta of a sample is mu_theta + O(sigma): reduce to [-pi, pi] before the FP32 sincos
+                double tr = th;
+                if (tr > MCSIM_PI) tr -= 2 * MCSIM_PI;
+                if (tr < -MCSIM_PI) tr += 2 * MCSIM_PI;
+                sincosf(float(tr), &sn, &cs);
+                hit = robot_hits_grouped(a.sat2, float(x), float(y), cs, sn);
+            }
         }  // valid
         const int gmin = __reduce_min_sync(0xffffffffu, valid ? g : 0x7fffffff);
         const int gmax = __reduce_max_sync(0xffffffffu, valid ? g : -1);

@@ -9,6 +9,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <atomic>
+#include <thread>
 #include <vector>
 
 #include "mc_rollout_sm100.cuh"
@@ -550,6 +552,7 @@ static void gmm_fill_launch(mcsim_cuda_ctx* c, GmmLaunch& a, int K, int T, int L
     a.steps = (const GmmStepTable*)c->gmm_steps.p;
     a.probabilities = (double*)c->gmm_prob.p;
     a.degenerate = (int*)c->gmm_deg.p;
+    a.sat2 = (const float4*)c->sat2.p;
 }
 
 // the three launches of one waypoint
@@ -1038,35 +1041,45 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
     const int per_step = 3 + L, TS = T > 1 ? T - 1 : 1;
     std::vector<GmmStepTable> steps(size_t(B) * TS);
     std::vector<double> comps(size_t(B) * MCSIM_MAX_GAUSSIANS * GMM_COMP, 0.0);
-    std::vector<double> hn, applied(size_t(3) * TS), obs(size_t(TS) * (L ? L : 1));
     mcsim_math::NoiseModel<double> nmd;
     for (int k = 0; k < 4; ++k) nmd.alpha[k] = mc->alphas[k];
     double Lo[6];
     if (!gmm_chol3(mc->cov0, Lo)) return fail(MCSIM_ERR_ARG, "gmm_run_batch: initial covariance is not positive definite");
-    for (int b = 0; b < B; ++b) {
-        mcsim_mc_params pb = *mc;
-        if (g->trajectories) { pb.trajectory = g->trajectories + size_t(b) * 3 * T; pb.odometry = g->odometry + size_t(b) * 3 * (T - 1); }
-        // the member's shared real-robot thread (host, FP64), its own Philox subsequence
-        host_normals(mc->seed, unsigned(g->stream0 + b), T, per_step, hn);
-        if (T > 1) {
-            int rc = mcsim_host_thread(&pb, hn.data(), hn.size(), nullptr, applied.data(), nullptr, nullptr, nullptr, obs.data());
-            if (rc) return fail(rc, "gmm_run_batch: host thread of member %d failed (%d)", b, rc);
+    // the members' shared real-robot threads (host, FP64, O(T) each) are independent: spread them over host threads
+    std::atomic<int> next(0), bad(0);
+    auto work = [&]() {
+        std::vector<double> hn, applied(size_t(3) * TS), obs(size_t(TS) * (L ? L : 1));
+        for (int b = next.fetch_add(1); b < B; b = next.fetch_add(1)) {
+            mcsim_mc_params pb = *mc;
+            if (g->trajectories) { pb.trajectory = g->trajectories + size_t(b) * 3 * T; pb.odometry = g->odometry + size_t(b) * 3 * (T - 1); }
+            host_normals(mc->seed, unsigned(g->stream0 + b), T, per_step, hn);  // its own Philox subsequence
+            if (T > 1 && mcsim_host_thread(&pb, hn.data(), hn.size(), nullptr, applied.data(), nullptr, nullptr, nullptr, obs.data())) { bad = 1; return; }
+            for (int t = 0; t < T - 1; ++t) {
+                GmmStepTable& s = steps[size_t(b) * TS + t];
+                double us[3];
+                for (int k = 0; k < 3; ++k) { us[k] = pb.odometry[k * (T - 1) + t]; s.u[k] = applied[k * (T - 1) + t]; }
+                mcsim_math::motion_noise(nmd, us, s.M);
+                for (int l = 0; l < L; ++l) s.z[l] = obs[size_t(t) * L + l];
+            }
+            for (int k = 0; k < K; ++k) {
+                double* cp = &comps[(size_t(b) * MCSIM_MAX_GAUSSIANS + k) * GMM_COMP];
+                cp[0] = 1.0 / K;
+                for (int i = 0; i < 3; ++i) cp[1 + i] = pb.trajectory[i * T];
+                for (int i = 0; i < 9; ++i) cp[4 + i] = mc->cov0[i];
+                for (int i = 0; i < 6; ++i) cp[13 + i] = Lo[i];
+            }
         }
-        for (int t = 0; t < T - 1; ++t) {
-            GmmStepTable& s = steps[size_t(b) * TS + t];
-            double us[3];
-            for (int k = 0; k < 3; ++k) { us[k] = pb.odometry[k * (T - 1) + t]; s.u[k] = applied[k * (T - 1) + t]; }
-            mcsim_math::motion_noise(nmd, us, s.M);
-            for (int l = 0; l < L; ++l) s.z[l] = obs[size_t(t) * L + l];
-        }
-        for (int k = 0; k < K; ++k) {
-            double* cp = &comps[(size_t(b) * MCSIM_MAX_GAUSSIANS + k) * GMM_COMP];
-            cp[0] = 1.0 / K;
-            for (int i = 0; i < 3; ++i) cp[1 + i] = pb.trajectory[i * T];
-            for (int i = 0; i < 9; ++i) cp[4 + i] = mc->cov0[i];
-            for (int i = 0; i < 6; ++i) cp[13 + i] = Lo[i];
-        }
+    };
+    {
+        unsigned nt = std::thread::hardware_concurrency();
+        nt = nt < 1 ? 1 : (nt > 16 ? 16 : nt);
+        if (unsigned(B) < 4 * nt) nt = 1;
+        std::vector<std::thread> pool;
+        for (unsigned i = 1; i < nt; ++i) pool.emplace_back(work);
+        work();
+        for (auto& th : pool) th.join();
     }
+    if (bad) return fail(MCSIM_ERR_ARG, "gmm_run_batch: host thread of a member failed");
     int rc = gmm_reserve(c, T, K, B);
     if (rc) return rc;
     CK(cudaMemcpyAsync(c->gmm_comps.p, comps.data(), sizeof(double) * comps.size(), cudaMemcpyHostToDevice, c->stream));

@@ -97,6 +97,49 @@ __device__ __forceinline__ bool robot_hits(float x, float y, float ct, float st,
     return hit;
 }
 
+// The same exhaustive test on the orientation-grouped table (built by mcsim_cuda_set_scene; layout and the
+// algebra are described at robot_hits2 in mc_philox2_sm100.cuh): per class of boxes sharing an axis direction
+// mod 90 degrees the relative rotation, the hull centre in the class frame and the hull's radii on the class
+// axes are computed once, which leaves 12 FP32 operations + 4 compares per pair instead of 20 + 4.
+// tab: global (read through the read-only path; every thread reads the same addresses) or shared memory.
+__device__ __forceinline__ bool robot_hits_grouped(const float4* __restrict__ tab, float x, float y, float ct, float st) {
+    bool hit = false;
+    for (int hI = 0; hI < c_scene.n_hulls; ++hI) {
+        const HullRec& hr = c_scene.hulls[hI];
+        const float hcx = fmaf(ct, hr.ox, fmaf(-st, hr.oy, x));
+        const float hcy = fmaf(st, hr.ox, fmaf(ct, hr.oy, y));
+        const float ch = fmaf(ct, hr.cp, -st * hr.sp);
+        const float sh = fmaf(st, hr.cp, ct * hr.sp);
+        const float nph = -fmaf(ch, hcx, sh * hcy);
+        const float nqh = -fmaf(ch, hcy, -sh * hcx);
+        const float hhx = hr.hx, hhy = hr.hy;
+        const float4* g = tab + hr.g_first;
+        for (int gi = 0; gi < hr.n_groups; ++gi) {
+            const float4 head = __ldg(g);
+            const int cnt = __float_as_int(head.z);
+            const float c = fabsf(fmaf(ch, head.x, sh * head.y));
+            const float s = fabsf(fmaf(sh, head.x, -ch * head.y));
+            const float gx = fmaf(hcx, head.x, hcy * head.y);
+            const float gy = fmaf(hcy, head.x, -hcx * head.y);
+            const float rbx = fmaf(c, hhx, s * hhy);
+            const float rby = fmaf(s, hhx, c * hhy);
+            ++g;
+#pragma unroll 4
+            for (int b = 0; b < cnt; ++b) {
+                const float4 A = __ldg(g + 2 * b);                                        // cx, cy, hx, hy
+                const float2 B = __ldg(reinterpret_cast<const float2*>(g + 2 * b + 1));   // -p, -q
+                const float drx = fmaf(ch, A.x, fmaf(sh, A.y, nph));
+                const float dry = fmaf(ch, A.y, fmaf(-sh, A.x, nqh));
+                const float r0 = fmaf(c, A.z, fmaf(s, A.w, hhx));
+                const float r1 = fmaf(s, A.z, fmaf(c, A.w, hhy));
+                if ((fabsf(drx) <= r0) & (fabsf(dry) <= r1) & (fabsf(gx + B.x) <= rbx + A.z) & (fabsf(gy + B.y) <= rby + A.w)) hit = true;
+            }
+            g += 2 * cnt;
+        }
+    }
+    return hit;
+}
+
 // Signed clearance: min over live pairs of the pair gap (+FLT_MAX when there is no pair).
 __device__ __forceinline__ float robot_clearance(float x, float y, float ct, float st) {
     float best = 3.402823466e+38f;
