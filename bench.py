@@ -320,6 +320,14 @@ def main():
                           "waypoints, 1 thread (the reference is single-threaded), CPU SAT on the same geometry; %.1f s"
                           % (a.ref_particles, T, r["wall_s"]),
                 "P_mean": r["P_mean"]}
+            # the GMM mode of the reference on the same core: runGMMEstimation, K = 3, 10^4 samples per waypoint
+            plan_c, sc_c = load_inputs(a.scene)
+            t0 = time.perf_counter()
+            gp = [oracle_ref.gmm_run(plan_c, sc_c["boxes"], sc_c["hulls"], 3, 10000, mt_seed=s_, multinomial_seed=s_ + 1, record=False)["P"] for s_ in range(8)]
+            dt = time.perf_counter() - t0
+            line["cpu_baseline"]["gmm"] = {"value": 8 / dt, "unit": "trajectories/s", "cores": 1, "kind": "reference",
+                                           "sample": "8 x runGMMEstimation() of the reference estimator headers, K = 3, 10^4 samples x 56 waypoints, 1 thread; %.1f s" % dt,
+                                           "P_mean": float(np.mean(gp))}
         else:
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
     if rank == 0:

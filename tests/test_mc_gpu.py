@@ -172,3 +172,41 @@ def test_philox_packed_kernel_matches_precise_kernel(ctx, plan, scenes, name, es
     np.testing.assert_array_equal(ee["counts"], (a["counts"] > 0).astype(np.uint32))
     assert ee["hits"] == a["hits"] and ee["executed_steps"] < a["executed_steps"]
     np.testing.assert_array_equal(ee["first_hit_hist"], a["first_hit_hist"])
+
+
+def test_philox_edge_cases_empty_scene_single_waypoint_other_landmark_counts(ctx, plan, scenes):
+    """Empty obstacle set (no live pair): no rollout ever hits; T = 1: only the start poses are tested;
+    a landmark count other than 8 or a plan longer than the packed kernel's table falls back to the scalar
+    kernel and must agree with the packed one statistically."""
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    hulls = scenes["pr2test2"]["hulls"]
+    ctx.set_scene(np.zeros((0, 8)), hulls)
+    p, keep = abi.make_mc_params(plan, n_rollouts=5001, mode=abi.MODE_PHILOX, early_exit=False)
+    out = ctx.mc_run(p, want_counts=True)
+    assert out["hits"] == 0 and out["pair_tests"] == 0 and out["executed_steps"] == 5001 * plan["trajectory"].shape[1]
+    ctx.set_scene(scenes["pr2test2"]["boxes"], hulls)
+    one = dict(plan)
+    one["trajectory"] = np.ascontiguousarray(plan["trajectory"][:, :1])
+    one["odometry"] = np.zeros((3, 0))
+    p, keep = abi.make_mc_params(one, n_rollouts=4097, mode=abi.MODE_PHILOX, early_exit=False)
+    out = ctx.mc_run(p)
+    assert out["executed_steps"] == 4097 and out["hits"] <= 4097
+    # 6 landmarks -> scalar kernel (NL generic); compare P with the 8-landmark packed run loosely (different filter)
+    six = dict(plan)
+    six["landmarks"] = np.ascontiguousarray(plan["landmarks"][:, :6])
+    p6, keep6 = abi.make_mc_params(six, n_rollouts=100000, mode=abi.MODE_PHILOX)
+    p8, keep8 = abi.make_mc_params(plan, n_rollouts=100000, mode=abi.MODE_PHILOX)
+    P6, P8 = ctx.mc_run(p6)["P"], ctx.mc_run(p8)["P"]
+    assert 0.5 < P6 <= 1.0 and abs(P6 - P8) < 0.1
+    # T = 300 > 256 waypoints: plan repeated back and forth is not needed, a long straight plan will do
+    T = 300
+    long_plan = dict(plan)
+    tr = np.zeros((3, T)); tr[0] = -3.0 + 0.01 * np.arange(T); tr[1] = 1.3
+    od = np.zeros((3, T - 1)); od[1] = 0.01
+    long_plan["trajectory"], long_plan["odometry"] = tr, od
+    pl, keepl = abi.make_mc_params(long_plan, n_rollouts=20000, mode=abi.MODE_PHILOX, early_exit=False)
+    out = ctx.mc_run(pl)
+    assert out["executed_steps"] == 20000 * T
+    sc = ctx.score_plans(long_plan, tr[None], od[None], 20000, margin=-1.0)   # packed law, plan table in shared memory
+    assert abs(sc["P"][0] - out["P"]) < 0.02, (sc["P"][0], out["P"])
