@@ -328,6 +328,13 @@ def main():
             line["cpu_baseline"]["gmm"] = {"value": 8 / dt, "unit": "trajectories/s", "cores": 1, "kind": "reference",
                                            "sample": "8 x runGMMEstimation() of the reference estimator headers, K = 3, 10^4 samples x 56 waypoints, 1 thread; %.1f s" % dt,
                                            "P_mean": float(np.mean(gp))}
+            # the vendored Armadillo EM (gmm_full::learn, keep_existing) on one core: K = 3, 2 x 10^5 samples, 10 iterations
+            xe, he, me, ce = pcoll_b200.inputs.synthetic_em_problem(9000, 200000, 3)
+            t0 = time.perf_counter()
+            oracle_ref.em_fit(xe.T.astype(np.float64), me, ce.reshape(3, 9), he, 10)
+            dt = time.perf_counter() - t0
+            line["cpu_baseline"]["em"] = {"value": 200000 * 10 / dt, "unit": "sample-iterations/s", "cores": 1, "kind": "reference",
+                                          "sample": "arma::gmm_full::learn(keep_existing, em_iter = 10), K = 3, 2 x 10^5 samples, 1 thread; %.1f s" % dt}
         else:
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
     if rank == 0:
