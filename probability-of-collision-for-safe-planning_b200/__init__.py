@@ -9,6 +9,7 @@ from . import cuda_abi  # noqa: F401
 from . import plugin  # noqa: F401
 from . import inputs  # noqa: F401
 from . import sharding  # noqa: F401
+from . import planner  # noqa: F401
 from .inputs import default_params, load_plan_json, plan_from_pickles, py2_str  # noqa: F401
 from .plugin import MCModule, McsimError, push_parameters  # noqa: F401
 

@@ -57,3 +57,19 @@ def test_broad_phase_is_exact_and_split_invariant(ctx, plan):
     ctx.score_prepare(plan, tr, od, R, margin=1.5)
     ctx.score_launch()
     np.testing.assert_array_equal(ctx.score_collect()["hits"], full["hits"])
+
+
+def test_planner_to_scorer_loop(tmp_path):
+    """tools/plan_and_score.py: candidates planned on the lattice, scored in one launch, safest one written as
+    trajectory.dat / odometry.dat; a wider berth must not be less safe than grazing the obstacles."""
+    import importlib.util
+    import os
+    from conftest import ROOT
+    spec = importlib.util.spec_from_file_location("plan_and_score", os.path.join(ROOT, "tools", "plan_and_score.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    out = mod.main(["--rollouts", "16384", "--outdir", str(tmp_path)])
+    P = [c["P_collision"] for c in out["candidates"]]
+    assert len(P) >= 3 and all(0.0 <= p <= 1.0 for p in P)
+    assert P[-1] <= P[0] + 0.02 and out["chosen"] == int(np.argmin(P))
+    assert os.path.isfile(out["files"][0]) and os.path.isfile(out["files"][1])
