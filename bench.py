@@ -57,6 +57,7 @@ def parse():
     ap.add_argument("--e2e-rollouts", type=int, default=10 ** 7, help="rollouts per GPU per e2e step")
     ap.add_argument("--ref-particles", type=int, default=10000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exhaustive", action="store_true", help="time the rollout kernel with its broad phase off (every live pair at every step)")
     ap.add_argument("--no-extras", action="store_true", help="skip the GMM / early-exit / pr2custom side measurements")
     return ap.parse_args()
 
@@ -181,6 +182,9 @@ def workload_config(a, per_gpu):
                     "Philox mode, reference estimator law, no early exit; %s rollouts per GPU per step" % (
                         "%d" % per_gpu if per_gpu else "reference arm: bounded sample of the same plan"),
         "scene": a.scene, "waypoints": 56, "rollouts_per_gpu_per_step": per_gpu,
+        "collision_query": "every live (hull, box) pair at every step" if getattr(a, "exhaustive", False) else
+                           "exact broad phase: identical per-rollout counts to testing every live pair (tests/test_mc_gpu.py::"
+                           "test_philox_broad_phase_is_exact); executed pair tests are counted and are what the roofline is charged with",
         "l2": "kernel reads no HBM input (2 KB plan table in shared memory, geometry in __constant__); a 512 MiB buffer "
               "is overwritten between timed steps anyway",
     }
@@ -217,7 +221,7 @@ def main():
 
     fp32_peak, mufu_peak = ctx.measure_peaks(150.0)
 
-    p, keep = abi.make_mc_params(plan, n_rollouts=n, rollout_offset=rank * n, mode=abi.MODE_PHILOX, early_exit=False)
+    p, keep = abi.make_mc_params(plan, n_rollouts=n, rollout_offset=rank * n, mode=abi.MODE_PHILOX, early_exit=False, exhaustive=a.exhaustive)
     ctx.mc_prepare(p)
 
     def barrier():
@@ -271,6 +275,33 @@ def main():
     achieved = flops_job / world / (kernel_ms * 1e-3) / 1e12  # per GPU, TFLOP/s
     P = tot["hits"] / (a.steps * world * n)
 
+    # ---- the same kernel with the broad phase off (every live pair tested at every step, as CheckCollision does):
+    # its arithmetic rate under the full SAT load, reported inside `roofline` next to the product configuration
+    every_pair = None
+    if not a.exhaustive:
+        pe, keep_e = abi.make_mc_params(plan, n_rollouts=n, rollout_offset=rank * n, mode=abi.MODE_PHILOX, early_exit=False, exhaustive=True)
+        ctx.mc_prepare(pe)
+        ev_e = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        with torch.cuda.stream(stream):
+            ctx.mc_launch(n, rank * n)
+            counters.zero_()
+            flush.zero_()
+            ev_e[0].record(stream)
+            ctx.mc_launch(n, rank * n)
+            ev_e[1].record(stream)
+        stream.synchronize()
+        ce = counters.cpu().numpy().astype(np.uint64)
+        with torch.cuda.stream(stream):
+            counters.zero_()
+        stream.synchronize()
+        ms_e = ev_e[0].elapsed_time(ev_e[1])
+        fl_e = int(ce[2]) * F_PHILOX_STEP + int(ce[3]) * F_SAT
+        every_pair = {"rollout_steps_per_s_per_gpu": int(ce[2]) / (ms_e * 1e-3), "pair_tests_per_step": int(ce[3]) / max(int(ce[2]), 1),
+                      "achieved": fl_e / (ms_e * 1e-3) / 1e12, "frac": fl_e / (ms_e * 1e-3) / 1e12 / fp32_peak,
+                      "hits_equal_product_run": int(ce[0]) * a.steps * world == tot["hits"] if world == 1 else None,
+                      "note": "one launch, rank %d, broad phase off (mcsim_mc_params.exhaustive = 1)" % rank}
+        ctx.mc_prepare(p)
+
     # ---- e2e: the plugin command interface with host buffers, every step: parameters + plan pushed as command
     # strings are parsed once; runSimulation uploads the plan table, runs, and returns P as text
     e2e = None
@@ -296,6 +327,7 @@ def main():
                 F_PHILOX_STEP, F_SAT, tot["pair_tests"] / job_steps),
             "peak_source": "FFMA-chain microbenchmark (csrc/peaks_sm100.cuh) measured in this process; MUFU peak %.3f Top/s" % mufu_peak,
             "file_peaks": read_measured_peaks(),
+            "every_pair_tested": every_pair,
         },
     }
     if rank == 0 and not a.no_extras:

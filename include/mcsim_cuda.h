@@ -110,6 +110,11 @@ typedef struct {
                                     approximations (mc_philox2_sm100.cuh); 1: scalar kernel with IEEE
                                     division / sqrt / libm trigonometry (same Philox counters and draw
                                     order; audit launches always use it) */
+    int exhaustive;              /* packed kernel only.  0: exact broad phase -- per waypoint the pairs within
+                                    reach of the nominal pose are listed on the host, a warp whose rollouts
+                                    are all near x*_t tests only those (same flags and counts, fewer pair
+                                    tests; result.pair_tests counts the executed ones); 1: every live
+                                    (hull, box) pair is tested at every step, as CheckCollision does */
 } mcsim_mc_params;
 
 enum { MCSIM_MODE_REPLAY = 0, MCSIM_MODE_PHILOX = 1 };

@@ -63,6 +63,7 @@ const MCModule::Command MCModule::kCommands[] = {
     {"setGMMCountsFile", &MCModule::setGMMCountsFile, "setGMMCountsFile <path>: int32 little-endian multinomial counts [T x K] (deterministic GMM mode)"},
     {"setGMMCounts", &MCModule::setGMMCounts, "setGMMCounts <n> <c_0> ...: the same, inline"},
     {"setEarlyExit", &MCModule::setEarlyExit, "setEarlyExit 0|1: stop a rollout at its first hit (the returned P does not change)"},
+    {"setBroadPhase", &MCModule::setBroadPhase, "setBroadPhase 0|1: 1 (default) tests only the obstacles within reach of each waypoint, 0 every obstacle at every step (the returned P does not change)"},
     {"setEstimator", &MCModule::setEstimator, "setEstimator reference|closedloop: collision tested on the particle (reference) or on the real state"},
     {"setRolloutOffset", &MCModule::setRolloutOffset, "setRolloutOffset <u64>: global id of this module's first rollout (multi-GPU shards)"},
     {"setGeometry", &MCModule::setGeometry, "setGeometry <n_boxes> <n_hulls> <8 numbers per prism ...>: replace the collision geometry"},

@@ -73,6 +73,7 @@ class MCModule {
     bool setGMMCountsFile(std::ostream&, std::istream&);
     bool setGMMCounts(std::ostream&, std::istream&);
     bool setEarlyExit(std::ostream&, std::istream&);
+    bool setBroadPhase(std::ostream&, std::istream&);
     bool setEstimator(std::ostream&, std::istream&);
     bool setRolloutOffset(std::ostream&, std::istream&);
     bool setGeometry(std::ostream&, std::istream&);
@@ -107,6 +108,7 @@ class MCModule {
     uint64_t run_index_ = 0;
     uint64_t rollout_offset_ = 0;
     int early_exit_ = 1;
+    int exhaustive_ = 0;
     int estimator_ = MCSIM_EST_REFERENCE;
     std::vector<double> draws_;
     std::vector<int> gmm_counts_;

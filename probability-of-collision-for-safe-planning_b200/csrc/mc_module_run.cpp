@@ -47,6 +47,7 @@ void MCModule::fill_params(mcsim_mc_params& p) const {
     std::memcpy(p.cov0, cov0_, sizeof(cov0_));
     p.estimator = estimator_;
     p.early_exit = early_exit_;
+    p.exhaustive = exhaustive_;
     p.seed = seed_;
     p.near_eps = 1e-4;
 }
@@ -221,6 +222,13 @@ bool MCModule::setEarlyExit(std::ostream&, std::istream& sinput) {
     int v;
     if (!(sinput >> v)) throw std::runtime_error("setEarlyExit: 0 or 1 expected");
     early_exit_ = v != 0;
+    return true;
+}
+
+bool MCModule::setBroadPhase(std::ostream&, std::istream& sinput) {
+    int v;
+    if (!(sinput >> v)) throw std::runtime_error("setBroadPhase: 0 or 1 expected");
+    exhaustive_ = v == 0;
     return true;
 }
 

@@ -64,47 +64,119 @@ __device__ __forceinline__ Philox2 philox_pair(unsigned long long id0, unsigned 
 // leaves 8 FFMA2 + 4 FADD2 and 8 FSETP.  Every live pair is still tested at every step.
 // Table records (float4, shared memory): class header (cos, sin, count, -), then per pair
 // (cx, cy, hx, hy), (-p, -q, -, -) with p = cb cx + sb cy, q = cb cy - sb cx.
+struct ClassFrame2 {
+    f2 c, s, gx, gy, rbx, rby;
+};
+// per orientation class: |relative rotation|, hull centre in the class frame, hull radii on the class axes
+__device__ __forceinline__ ClassFrame2 class_frame2(const float4 head, f2 ch, f2 sh, f2 hcx, f2 hcy, f2 hhx, f2 hhy) {
+    ClassFrame2 k;
+    k.c = abs2(fma2(ch, head.x, mul2(sh, head.y)));
+    k.s = abs2(fma2(sh, head.x, mul2(neg2(ch), head.y)));
+    k.gx = fma2(hcx, head.x, mul2(hcy, head.y));
+    k.gy = fma2(hcy, head.x, mul2(neg2(hcx), head.y));
+    k.rbx = fma2(k.c, hhx, mul2(k.s, hhy));
+    k.rby = fma2(k.s, hhx, mul2(k.c, hhy));
+    return k;
+}
+// one pair of a class, both lanes: A = (cx, cy, hx, hy), B = (-p, -q)
+__device__ __forceinline__ void class_pair_test2(const ClassFrame2& k, f2 ch, f2 sh, f2 nph, f2 nqh, f2 hhx, f2 hhy, const float4 A, const float2 B, bool& hit0, bool& hit1) {
+    const f2 drx = fma2(ch, A.x, fma2(sh, A.y, nph));
+    const f2 dry = fma2(ch, A.y, fma2(neg2(sh), A.x, nqh));
+    const f2 r0 = fma2(k.c, A.z, fma2(k.s, A.w, hhx));
+    const f2 r1 = fma2(k.s, A.z, fma2(k.c, A.w, hhy));
+    const f2 dbx = add2(k.gx, B.x);
+    const f2 dby = add2(k.gy, B.y);
+    const f2 r2 = add2(k.rbx, A.z);
+    const f2 r3 = add2(k.rby, A.w);
+    if ((fabsf(lo(drx)) <= lo(r0)) & (fabsf(lo(dry)) <= lo(r1)) & (fabsf(lo(dbx)) <= lo(r2)) & (fabsf(lo(dby)) <= lo(r3))) hit0 = true;
+    if ((fabsf(hi(drx)) <= hi(r0)) & (fabsf(hi(dry)) <= hi(r1)) & (fabsf(hi(dbx)) <= hi(r2)) & (fabsf(hi(dby)) <= hi(r3))) hit1 = true;
+}
+
+struct HullFrame2 {
+    f2 hcx, hcy, ch, sh, nph, nqh, hhx, hhy;
+};
+__device__ __forceinline__ HullFrame2 hull_frame2(const HullRec& hr, f2 x, f2 y, f2 ct, f2 st) {
+    HullFrame2 h;
+    h.hcx = fma2(ct, hr.ox, fma2(neg2(st), hr.oy, x));
+    h.hcy = fma2(st, hr.ox, fma2(ct, hr.oy, y));
+    h.ch = fma2(ct, hr.cp, mul2(neg2(st), hr.sp));
+    h.sh = fma2(st, hr.cp, mul2(ct, hr.sp));
+    h.nph = neg2(fma2(h.ch, h.hcx, mul2(h.sh, h.hcy)));
+    h.nqh = neg2(fma2(h.ch, h.hcy, mul2(neg2(h.sh), h.hcx)));
+    h.hhx = bc(hr.hx);
+    h.hhy = bc(hr.hy);
+    return h;
+}
+
 __device__ __forceinline__ void robot_hits2(const float4* __restrict__ tab, f2 x, f2 y, f2 ct, f2 st, bool& hit0, bool& hit1) {
     const int nh = c_scene.n_hulls;
     for (int hI = 0; hI < nh; ++hI) {
         const HullRec& hr = c_scene.hulls[hI];
-        const f2 hcx = fma2(ct, hr.ox, fma2(neg2(st), hr.oy, x));
-        const f2 hcy = fma2(st, hr.ox, fma2(ct, hr.oy, y));
-        const f2 ch = fma2(ct, hr.cp, mul2(neg2(st), hr.sp));
-        const f2 sh = fma2(st, hr.cp, mul2(ct, hr.sp));
-        const f2 nph = neg2(fma2(ch, hcx, mul2(sh, hcy)));
-        const f2 nqh = neg2(fma2(ch, hcy, mul2(neg2(sh), hcx)));
-        const f2 hhx = bc(hr.hx), hhy = bc(hr.hy);
+        const HullFrame2 h = hull_frame2(hr, x, y, ct, st);
         const float4* g = tab + hr.g_first;
         for (int gi = 0; gi < hr.n_groups; ++gi) {
             const float4 head = g[0];
             const int cnt = __float_as_int(head.z);
-            const f2 c = abs2(fma2(ch, head.x, mul2(sh, head.y)));
-            const f2 s = abs2(fma2(sh, head.x, mul2(neg2(ch), head.y)));
-            const f2 gx = fma2(hcx, head.x, mul2(hcy, head.y));
-            const f2 gy = fma2(hcy, head.x, mul2(neg2(hcx), head.y));
-            const f2 rbx = fma2(c, hhx, mul2(s, hhy));
-            const f2 rby = fma2(s, hhx, mul2(c, hhy));
+            const ClassFrame2 k = class_frame2(head, h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
             ++g;
 #pragma unroll 4
-            for (int b = 0; b < cnt; ++b) {
-                const float4 A = g[2 * b];                                           // cx, cy, hx, hy
-                const float2 B = *reinterpret_cast<const float2*>(g + 2 * b + 1);    // -p, -q
-                const f2 drx = fma2(ch, A.x, fma2(sh, A.y, nph));
-                const f2 dry = fma2(ch, A.y, fma2(neg2(sh), A.x, nqh));
-                const f2 r0 = fma2(c, A.z, fma2(s, A.w, hhx));
-                const f2 r1 = fma2(s, A.z, fma2(c, A.w, hhy));
-                const f2 dbx = add2(gx, B.x);
-                const f2 dby = add2(gy, B.y);
-                const f2 r2 = add2(rbx, A.z);
-                const f2 r3 = add2(rby, A.w);
-                if ((fabsf(lo(drx)) <= lo(r0)) & (fabsf(lo(dry)) <= lo(r1)) & (fabsf(lo(dbx)) <= lo(r2)) & (fabsf(lo(dby)) <= lo(r3))) hit0 = true;
-                if ((fabsf(hi(drx)) <= hi(r0)) & (fabsf(hi(dry)) <= hi(r1)) & (fabsf(hi(dbx)) <= hi(r2)) & (fabsf(hi(dby)) <= hi(r3))) hit1 = true;
-            }
+            for (int b = 0; b < cnt; ++b)
+                class_pair_test2(k, h.ch, h.sh, h.nph, h.nqh, h.hhx, h.hhy, g[2 * b], *reinterpret_cast<const float2*>(g + 2 * b + 1), hit0, hit1);
             g += 2 * cnt;
         }
     }
 }
+
+struct HullPose2 {
+    f2 hcx, hcy, ch, sh, nph, nqh;
+    float hhx, hhy;
+};
+
+__device__ __forceinline__ HullPose2 place_hull2(const HullRec& hr, f2 x, f2 y, f2 ct, f2 st) {
+    HullPose2 h;
+    h.hcx = fma2(ct, hr.ox, fma2(neg2(st), hr.oy, x));
+    h.hcy = fma2(st, hr.ox, fma2(ct, hr.oy, y));
+    h.ch = fma2(ct, hr.cp, mul2(neg2(st), hr.sp));
+    h.sh = fma2(st, hr.cp, mul2(ct, hr.sp));
+    h.nph = neg2(fma2(h.ch, h.hcx, mul2(h.sh, h.hcy)));
+    h.nqh = neg2(fma2(h.ch, h.hcy, mul2(neg2(h.sh), h.hcx)));
+    h.hhx = hr.hx;
+    h.hhy = hr.hy;
+    return h;
+}
+
+// pair_hit (sat_device.cuh) for both lanes: 20 packed FP32 instructions + 8 FSETP
+__device__ __forceinline__ void pair_test2(const HullPose2& h, const float4 lo4, const float4 hi4, bool& hit0, bool& hit1) {
+    const f2 c = abs2(fma2(h.ch, lo4.z, mul2(h.sh, lo4.w)));
+    const f2 s = abs2(fma2(h.sh, lo4.z, mul2(neg2(h.ch), lo4.w)));
+    const f2 drx = fma2(h.ch, lo4.x, fma2(h.sh, lo4.y, h.nph));
+    const f2 dry = fma2(h.ch, lo4.y, fma2(neg2(h.sh), lo4.x, h.nqh));
+    const f2 dbx = fma2(h.hcx, lo4.z, fma2(h.hcy, lo4.w, hi4.z));
+    const f2 dby = fma2(h.hcy, lo4.z, fma2(neg2(h.hcx), lo4.w, hi4.w));
+    const f2 r0 = fma2(c, hi4.x, fma2(s, hi4.y, h.hhx));
+    const f2 r1 = fma2(s, hi4.x, fma2(c, hi4.y, h.hhy));
+    const f2 r2 = fma2(c, h.hhx, fma2(s, h.hhy, hi4.x));
+    const f2 r3 = fma2(s, h.hhx, fma2(c, h.hhy, hi4.y));
+    if ((fabsf(lo(drx)) <= lo(r0)) & (fabsf(lo(dry)) <= lo(r1)) & (fabsf(lo(dbx)) <= lo(r2)) & (fabsf(lo(dby)) <= lo(r3))) hit0 = true;
+    if ((fabsf(hi(drx)) <= hi(r0)) & (fabsf(hi(dry)) <= hi(r1)) & (fabsf(hi(dbx)) <= hi(r2)) & (fabsf(hi(dby)) <= hi(r3))) hit1 = true;
+}
+
+// ---- exact broad phase ----------------------------------------------------------------------------
+// Host side (mcsim_cuda_mc_prepare) lists, per waypoint t and hull h, the pairs whose box footprint lies within
+// reach_h + m of the nominal position x*_t, sorted by the smallest such m, and how many of them are needed for
+// m = MC_CULL_M0 * 2^k, k < MC_CULL_LEVELS.  A hull whose centre pose is within m of x*_t cannot touch any
+// other box (every hull point is within reach_h of the pose), so a warp whose 64 rollouts are all within
+// m_k of x*_t tests the first cnt[t][h][k] listed pairs; a warp with a rollout further out than the last
+// level (or a list longer than MC_CULL_CAP) tests every live pair.  Hit flags and counts are identical to
+// the exhaustive test's (tests/test_mc_gpu.py); executed pair tests are counted.
+// Table (32-bit words): cnt[T][n_hulls][MC_CULL_LEVELS] bytes (255 = list too long), padded to 4 bytes,
+// then idx[T][n_hulls][MC_CULL_CAP][2] 16-bit offsets into the orientation-grouped table: the pair's record
+// and its class header -- the listed pairs go through the SAME arithmetic as the exhaustive loop (class_frame2 +
+// class_pair_test2), which is what makes the two modes bit-identical at poses within rounding of contact.
+#define MC_CULL_LEVELS 4
+#define MC_CULL_CAP 16
+#define MC_CULL_M0 0.1f
+#define MC_CULL_OVERFLOW 255
 
 // prediction (:413-431) on a packed pose
 __device__ __forceinline__ void move2(f2 p[3], const f2 u[3]) {
@@ -239,12 +311,21 @@ __global__ void __launch_bounds__(128, MC_P2_CTAS_PER_SM) mc_philox2_kernel(cons
     __shared__ unsigned s_cnt[2];
     __shared__ unsigned s_hist[MCSIM_MAX_WAYPOINTS];
     const int T = c_mc.T;
+    const int nh = c_scene.n_hulls;
+    const bool cull = a.cull != nullptr;
+    // dynamic shared memory: grouped table | candidate lists (with cull only)
+    unsigned* s_cull = reinterpret_cast<unsigned*>(s_tab + a.sat2_n);
     for (int i = threadIdx.x; i < a.sat2_n; i += blockDim.x) s_tab[i] = a.sat2[i];
+    if (cull)
+        for (int i = threadIdx.x; i < a.cull_words; i += blockDim.x) s_cull[i] = a.cull[i];
+    const unsigned char* s_ccnt = reinterpret_cast<const unsigned char*>(s_cull);
+    const unsigned short* s_cidx = reinterpret_cast<const unsigned short*>(s_cull + (T * nh * MC_CULL_LEVELS + 3) / 4);
     for (int i = threadIdx.x; i < T; i += blockDim.x) s_hist[i] = 0;
     if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
     __syncthreads();
 
-    unsigned my_hits = 0, my_steps = 0;
+    unsigned my_hits = 0;
+    unsigned long long my_steps = 0, my_tests = 0;
     const unsigned n_pairs = c_scene.n_pairs;
     const unsigned long long n_thr = (a.n + 1) >> 1;
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
@@ -260,7 +341,7 @@ __global__ void __launch_bounds__(128, MC_P2_CTAS_PER_SM) mc_philox2_kernel(cons
         Rollout2 st;
         init2<EST>(st, c_mc.mu0, id0, id1, a.k0, a.k1);
 
-        unsigned cnt0 = 0, cnt1 = 0;
+        unsigned cnt0 = 0, cnt1 = 0, pass_steps = 0, pass_tests = 0;
         int first0 = -1, first1 = -1;
         for (int t = 0; t < T; ++t) {
             // ---- collision test at waypoint t
@@ -268,10 +349,38 @@ __global__ void __launch_bounds__(128, MC_P2_CTAS_PER_SM) mc_philox2_kernel(cons
             f2 sn, cs;
             sincos2(q[2], sn, cs);
             bool h0 = false, h1 = false;
-            robot_hits2(s_tab, q[0], q[1], cs, sn, h0, h1);
-            if (EARLY_EXIT) {
-                my_steps += (valid0 && cnt0 == 0) + (valid1 && cnt1 == 0);
+            const unsigned live = EARLY_EXIT ? unsigned(valid0 && cnt0 == 0) + unsigned(valid1 && cnt1 == 0) : unsigned(valid0) + unsigned(valid1);
+            int lev = MC_CULL_LEVELS;
+            if (cull) {
+                // squared distance of the tested poses from x*_t, max over the warp's live lanes
+                const float* r = c_plan2 + t * MC_PLAN2_STRIDE;
+                const f2 ex = add2(q[0], -r[0]), ey = add2(q[1], -r[1]);
+                const f2 d2 = fma2(ex, ex, mul2(ey, ey));
+                const unsigned u0 = valid0 ? __float_as_uint(lo(d2)) : 0u, u1 = valid1 ? __float_as_uint(hi(d2)) : 0u;
+                const float dm = __uint_as_float(__reduce_max_sync(0xffffffffu, u0 > u1 ? u0 : u1));  // NaN orders above every finite value
+                lev = dm <= MC_CULL_M0 * MC_CULL_M0 ? 0 : (dm <= 4.f * MC_CULL_M0 * MC_CULL_M0 ? 1 : (dm <= 16.f * MC_CULL_M0 * MC_CULL_M0 ? 2 : (dm <= 64.f * MC_CULL_M0 * MC_CULL_M0 ? 3 : MC_CULL_LEVELS)));
+                if (lev < MC_CULL_LEVELS && s_ccnt[t * nh * MC_CULL_LEVELS + lev] == MC_CULL_OVERFLOW) lev = MC_CULL_LEVELS;
             }
+            if (lev < MC_CULL_LEVELS) {
+                unsigned tested = 0;
+                for (int hI = 0; hI < nh; ++hI) {
+                    const int n = s_ccnt[(t * nh + hI) * MC_CULL_LEVELS + lev];
+                    if (n == 0) continue;
+                    const HullFrame2 h = hull_frame2(c_scene.hulls[hI], q[0], q[1], cs, sn);
+                    const ushort2* ci = reinterpret_cast<const ushort2*>(s_cidx) + (t * nh + hI) * MC_CULL_CAP;
+                    for (int k = 0; k < n; ++k) {
+                        const ushort2 o = ci[k];  // x: pair record, y: class header
+                        const ClassFrame2 cf = class_frame2(s_tab[o.y], h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
+                        class_pair_test2(cf, h.ch, h.sh, h.nph, h.nqh, h.hhx, h.hhy, s_tab[o.x], *reinterpret_cast<const float2*>(s_tab + o.x + 1), h0, h1);
+                    }
+                    tested += n;
+                }
+                pass_tests += live * tested;
+            } else {
+                robot_hits2(s_tab, q[0], q[1], cs, sn, h0, h1);
+                pass_tests += live * n_pairs;
+            }
+            pass_steps += live;
             if (h0) { if (first0 < 0) first0 = t; ++cnt0; }
             if (h1) { if (first1 < 0) first1 = t; ++cnt1; }
             if (EARLY_EXIT && __all_sync(0xffffffffu, (cnt0 || !valid0) && (cnt1 || !valid1))) break;
@@ -279,7 +388,8 @@ __global__ void __launch_bounds__(128, MC_P2_CTAS_PER_SM) mc_philox2_kernel(cons
 
             step2<EST, NL>(st, c_plan2 + t * MC_PLAN2_STRIDE, t, id0, id1, a.k0, a.k1);
         }
-        if (!EARLY_EXIT) my_steps += (unsigned(valid0) + unsigned(valid1)) * unsigned(T);
+        my_steps += pass_steps;
+        my_tests += pass_tests;
         if (cnt0 && valid0) { ++my_hits; atomicAdd(&s_hist[first0], 1u); }
         if (cnt1 && valid1) { ++my_hits; atomicAdd(&s_hist[first1], 1u); }
         if (a.counts) {
@@ -290,13 +400,15 @@ __global__ void __launch_bounds__(128, MC_P2_CTAS_PER_SM) mc_philox2_kernel(cons
 
     // ---- aggregation: warp reduce -> shared -> one 64-bit atomic per counter per block
     my_hits = __reduce_add_sync(0xffffffffu, my_hits);
-    unsigned long long w_steps = my_steps;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) w_steps += __shfl_xor_sync(0xffffffffu, w_steps, o);
+    for (int o = 16; o > 0; o >>= 1) {
+        my_steps += __shfl_xor_sync(0xffffffffu, my_steps, o);
+        my_tests += __shfl_xor_sync(0xffffffffu, my_tests, o);
+    }
     if ((threadIdx.x & 31) == 0) {
         atomicAdd(&s_cnt[0], my_hits);
-        atomicAdd(&a.counters[CNT_STEPS], w_steps);
-        atomicAdd(&a.counters[CNT_TESTS], w_steps * n_pairs);  // exhaustive: every live pair at every executed step
+        atomicAdd(&a.counters[CNT_STEPS], my_steps);
+        atomicAdd(&a.counters[CNT_TESTS], my_tests);  // executed pair tests
     }
     __syncthreads();
     if (threadIdx.x == 0 && s_cnt[0]) atomicAdd(&a.counters[CNT_HITS], (unsigned long long)s_cnt[0]);

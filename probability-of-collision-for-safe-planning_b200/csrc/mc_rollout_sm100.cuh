@@ -46,6 +46,9 @@ struct McLaunch {
     float near_eps;
     const float4* sat2;           // orientation-grouped pair table (packed kernel), sat2_n float4 records
     int sat2_n;
+    // exact broad phase of the packed kernel (mc_philox2_sm100.cuh); cull == nullptr: every live pair at every step
+    const unsigned* cull;         // per-waypoint candidate lists, cull_words 32-bit words
+    int cull_words;
 };
 
 // FP64 angle in [0, 4 pi] -> FP32 angle in [-pi, pi] (rounding error <= 1.2e-7 rad, not accumulated)

@@ -11,6 +11,8 @@
 
 #include <atomic>
 #include <thread>
+#include <algorithm>
+#include <utility>
 #include <vector>
 
 #include "mc_rollout_sm100.cuh"
@@ -68,6 +70,13 @@ struct mcsim_cuda_ctx {
     // orientation-grouped FP32 pair table of the packed Philox kernel (staged into shared memory)
     DevBuf sat2;
     int sat2_n = 0;  // float4 records
+    // exact broad phase of the packed Philox kernel: host copy of the live pairs, per-plan candidate lists
+    std::vector<double> h_pairgeom;  // per pair: cx, cy, cos, sin, hx, hy
+    std::vector<int> h_pair_hull;    // per pair: hull index
+    std::vector<unsigned> h_pair_sat2;  // per pair: record offset | class header offset << 16 in the grouped table
+    double h_reach[MCSIM_MAX_HULLS] = {0};
+    DevBuf mc_cull;
+    int mc_cull_words = 0;           // 0: no lists for the prepared plan (every live pair is tested)
     // GMM state
     DevBuf gmm_comps, gmm_stats, gmm_hist, gmm_counts, gmm_normals, gmm_steps, gmm_prob, gmm_pre, gmm_post, gmm_trunc, gmm_nout, gmm_deg;
     double* h_gmm = nullptr;  // pinned staging
@@ -122,7 +131,7 @@ extern "C" void mcsim_cuda_destroy(mcsim_cuda_ctx* c) {
     cudaStreamSynchronize(c->stream);
     c->plan.release(); c->z0.release(); c->counters.release(); c->counts.release();
     c->poses.release(); c->clearance.release();
-    c->hulls_d.release(); c->pairs_d.release(); c->sat2.release();
+    c->hulls_d.release(); c->pairs_d.release(); c->sat2.release(); c->mc_cull.release();
     c->pairs_f.release(); c->sc_plans.release(); c->sc_hits.release(); c->sc_counters.release();
     c->em_x.release(); c->em_comps.release(); c->em_hefts.release(); c->em_means.release(); c->em_fcovs.release();
     c->em_stats.release(); c->em_old.release(); c->em_done.release(); c->em_iters.release(); c->em_trace.release();
@@ -195,6 +204,10 @@ extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int 
     std::vector<HullD> hd(n_hulls);
     std::vector<PairD> pd;
     sc.n_hulls = n_hulls;
+    c->h_pairgeom.clear();
+    c->h_pair_hull.clear();
+    c->h_pair_sat2.clear();
+    c->mc_prepared = false;  // candidate lists of a prepared plan refer to the old scene
     for (int h = 0; h < n_hulls; ++h) {
         const double* hu = hulls + h * MCSIM_PRISM_STRIDE;
         HullRec& r = sc.hulls[h];
@@ -209,6 +222,8 @@ extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int 
             pairs.push_back(make_float4(float(bx[0]), float(bx[1]), float(bx[2]), float(bx[3])));
             pairs.push_back(make_float4(float(bx[4]), float(bx[5]), -float(p), -float(q)));
             pd.push_back(PairD{bx[0], bx[1], bx[2], bx[3], bx[4], bx[5]});
+            for (int k = 0; k < 6; ++k) c->h_pairgeom.push_back(bx[k]);
+            c->h_pair_hull.push_back(h);
         }
         r.count = int(pairs.size() / 2) - r.first;
         // ---- the same live pairs grouped by orientation class.  A box (phi, hx, hy) is the box
@@ -233,6 +248,7 @@ extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int 
         r.g_first = int(sat2.size());
         r.n_groups = 0;
         std::vector<char> done(live.size(), 0);
+        c->h_pair_sat2.resize(size_t(r.first) + live.size(), 0u);  // live[j] is pair r.first + j
         for (size_t i = 0; i < live.size(); ++i) {
             if (done[i]) continue;
             const size_t header = sat2.size();
@@ -243,6 +259,7 @@ extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int 
                 done[j] = 1;
                 const Canon& q = live[j];
                 const double pp = live[i].cb * q.cx + live[i].sb * q.cy, qq = live[i].cb * q.cy - live[i].sb * q.cx;
+                c->h_pair_sat2[size_t(r.first) + j] = unsigned(sat2.size()) | (unsigned(header) << 16);
                 sat2.push_back(make_float4(float(q.cx), float(q.cy), float(q.hx), float(q.hy)));
                 sat2.push_back(make_float4(-float(pp), -float(qq), 0.f, 0.f));
                 ++cnt;
@@ -253,6 +270,7 @@ extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int 
         hd[h] = HullD{hu[0], hu[1], hu[2], hu[3], hu[4], hu[5], r.first, r.count};
         const float reach = float(sqrt(hu[0] * hu[0] + hu[1] * hu[1]) + sqrt(hu[4] * hu[4] + hu[5] * hu[5]));
         if (reach > sc.reach) sc.reach = reach;
+        c->h_reach[h] = sqrt(hu[0] * hu[0] + hu[1] * hu[1]) + sqrt(hu[4] * hu[4] + hu[5] * hu[5]);
     }
     sc.n_pairs = int(pairs.size() / 2);
     if (sc.n_pairs > MCSIM_MAX_PAIRS)
@@ -336,6 +354,44 @@ static int mc_check(const mcsim_cuda_ctx* c, const mcsim_mc_params* p) {
     return MCSIM_OK;
 }
 
+// Candidate lists of the packed kernel's broad phase (layout and exactness argument: mc_philox2_sm100.cuh).
+// need(pair) = distance from x*_t to the box footprint - reach of the pair's hull - 1 mm of slack for the FP32
+// plan record and the FP32 deviation test of the kernel.
+static void build_cull_lists(const mcsim_cuda_ctx* c, const double* trajectory, int T, std::vector<unsigned>& words) {
+    const int nh = c->n_hulls, np = int(c->h_pair_hull.size());
+    const size_t cnt_words = (size_t(T) * nh * MC_CULL_LEVELS + 3) / 4, idx_words = size_t(T) * nh * MC_CULL_CAP;
+    words.assign(cnt_words + idx_words, 0u);
+    unsigned char* cnt = reinterpret_cast<unsigned char*>(words.data());
+    unsigned* idx = words.data() + cnt_words;  // ushort2 (record, header)
+    std::vector<std::pair<double, int>> need;
+    for (int t = 0; t < T; ++t) {
+        const double px = trajectory[t], py = trajectory[T + t];
+        bool overflow[MC_CULL_LEVELS] = {false};
+        for (int h = 0; h < nh; ++h) {
+            need.clear();
+            for (int b = 0; b < np; ++b) {
+                if (c->h_pair_hull[b] != h) continue;
+                const double* g = &c->h_pairgeom[size_t(b) * 6];
+                const double dx = px - g[0], dy = py - g[1];
+                const double lx = fabs(g[2] * dx + g[3] * dy) - g[4], ly = fabs(g[2] * dy - g[3] * dx) - g[5];
+                const double dist = hypot(lx > 0 ? lx : 0, ly > 0 ? ly : 0);
+                need.emplace_back(dist - c->h_reach[h] - 1e-3, b);
+            }
+            std::sort(need.begin(), need.end());
+            double m = MC_CULL_M0;
+            for (int k = 0; k < MC_CULL_LEVELS; ++k, m *= 2) {
+                size_t n = 0;
+                while (n < need.size() && need[n].first <= m) ++n;
+                if (n > MC_CULL_CAP) overflow[k] = true;
+                cnt[(size_t(t) * nh + h) * MC_CULL_LEVELS + k] = (unsigned char)(n > MC_CULL_CAP ? MC_CULL_CAP : n);
+            }
+            for (size_t k = 0; k < need.size() && k < MC_CULL_CAP; ++k) idx[(size_t(t) * nh + h) * MC_CULL_CAP + k] = c->h_pair_sat2[need[k].second];
+        }
+        for (int k = 0; k < MC_CULL_LEVELS; ++k)
+            if (overflow[k]) for (int h = 0; h < nh; ++h) cnt[(size_t(t) * nh + h) * MC_CULL_LEVELS + k] = MC_CULL_OVERFLOW;
+    }
+}
+
 // Uploads the plan table + constants; zeroes the counters.
 extern "C" int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* c, const mcsim_mc_params* p) {
     int rc = mc_check(c, p);
@@ -384,11 +440,18 @@ extern "C" int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* c, const mcsim_mc_params* p
             w[9] = r[6] + r[8];
         }
     }
+    std::vector<unsigned> cull;
+    if (!plan2.empty() && !p->exhaustive && L == 8 && c->sat2_n < 65536) build_cull_lists(c, p->trajectory, T, cull);
+    // the lists ride in shared memory next to the pair table; too large a plan x scene goes without them
+    if ((cull.size() * sizeof(unsigned) + sizeof(float4) * size_t(c->sat2_n)) * MC_P2_CTAS_PER_SM > 200 * 1024) cull.clear();
+    c->mc_cull_words = int(cull.size());
+    if (!cull.empty()) CK(c->mc_cull.reserve(cull.size() * sizeof(unsigned)));
     CK(c->plan.reserve(plan.size() * sizeof(float)));
     CK(c->counters.reserve(sizeof(unsigned long long) * (4 + MCSIM_MAX_WAYPOINTS)));
     CK(cudaStreamSynchronize(c->stream));
     CK(cudaMemcpyToSymbolAsync(c_mc, &pc, sizeof(pc), 0, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemcpyAsync(c->plan.p, plan.data(), plan.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    if (!cull.empty()) CK(cudaMemcpyAsync(c->mc_cull.p, cull.data(), cull.size() * sizeof(unsigned), cudaMemcpyHostToDevice, c->stream));
     if (!plan2.empty()) CK(cudaMemcpyToSymbolAsync(c_plan2, plan2.data(), plan2.size() * sizeof(float), 0, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * (4 + T), c->stream));
     CK(cudaStreamSynchronize(c->stream));  // plan is a stack vector
@@ -420,8 +483,12 @@ static int mc_launch_impl(mcsim_cuda_ctx* c, uint64_t n, uint64_t offset, const 
     a.near_eps = float(p.near_eps);
     a.sat2 = (const float4*)c->sat2.p;
     a.sat2_n = c->sat2_n;
+    const bool cull = packed && c->mc_cull_words > 0;
+    a.cull = cull ? (const unsigned*)c->mc_cull.p : nullptr;
+    a.cull_words = cull ? c->mc_cull_words : 0;
     const int block = packed ? 128 : 256;
-    const size_t smem = packed ? sizeof(float4) * size_t(c->sat2_n) : sizeof(float) * size_t(c->mc_T) * MC_PHILOX_STRIDE;
+    const size_t smem = packed ? sizeof(float4) * size_t(c->sat2_n) + (cull ? sizeof(unsigned) * size_t(c->mc_cull_words) : 0)
+                               : sizeof(float) * size_t(c->mc_T) * MC_PHILOX_STRIDE;
     unsigned long long want = packed ? ((n + 1) / 2 + block - 1) / block : (n + block - 1) / block;
     // persistent: whole waves of resident CTAs
     const unsigned long long cap = (unsigned long long)c->n_sm * (packed ? MC_P2_CTAS_PER_SM : 8);
@@ -462,7 +529,8 @@ extern "C" int mcsim_cuda_mc_run(mcsim_cuda_ctx* c, const mcsim_mc_params* p, mc
     int rc = mcsim_cuda_mc_prepare(c, p);
     if (rc) return rc;
     c->h2d_bytes = sizeof(McPlanConst) + sizeof(float) * size_t(p->T) * MC_PHILOX_STRIDE +
-                   ((p->mode == MCSIM_MODE_PHILOX && p->T <= MC_PLAN2_MAX_T) ? sizeof(float) * size_t(p->T) * MC_PLAN2_STRIDE : 0);
+                   ((p->mode == MCSIM_MODE_PHILOX && p->T <= MC_PLAN2_MAX_T) ? sizeof(float) * size_t(p->T) * MC_PLAN2_STRIDE : 0) +
+                   sizeof(unsigned) * size_t(c->mc_cull_words);
     c->d2h_bytes = sizeof(unsigned long long) * (4 + p->T);
     const uint64_t n = p->n_rollouts;
     const int T = p->T;

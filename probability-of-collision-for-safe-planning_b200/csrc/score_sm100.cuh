@@ -34,40 +34,6 @@ struct ScoreLaunch {
     unsigned long long* counters;  // [2]: executed rollout-steps, executed pair tests
 };
 
-struct HullPose2 {
-    f2 hcx, hcy, ch, sh, nph, nqh;
-    float hhx, hhy;
-};
-
-__device__ __forceinline__ HullPose2 place_hull2(const HullRec& hr, f2 x, f2 y, f2 ct, f2 st) {
-    HullPose2 h;
-    h.hcx = fma2(ct, hr.ox, fma2(neg2(st), hr.oy, x));
-    h.hcy = fma2(st, hr.ox, fma2(ct, hr.oy, y));
-    h.ch = fma2(ct, hr.cp, mul2(neg2(st), hr.sp));
-    h.sh = fma2(st, hr.cp, mul2(ct, hr.sp));
-    h.nph = neg2(fma2(h.ch, h.hcx, mul2(h.sh, h.hcy)));
-    h.nqh = neg2(fma2(h.ch, h.hcy, mul2(neg2(h.sh), h.hcx)));
-    h.hhx = hr.hx;
-    h.hhy = hr.hy;
-    return h;
-}
-
-// pair_hit (sat_device.cuh) for both lanes: 20 packed FP32 instructions + 8 FSETP
-__device__ __forceinline__ void pair_test2(const HullPose2& h, const float4 lo4, const float4 hi4, bool& hit0, bool& hit1) {
-    const f2 c = abs2(fma2(h.ch, lo4.z, mul2(h.sh, lo4.w)));
-    const f2 s = abs2(fma2(h.sh, lo4.z, mul2(neg2(h.ch), lo4.w)));
-    const f2 drx = fma2(h.ch, lo4.x, fma2(h.sh, lo4.y, h.nph));
-    const f2 dry = fma2(h.ch, lo4.y, fma2(neg2(h.sh), lo4.x, h.nqh));
-    const f2 dbx = fma2(h.hcx, lo4.z, fma2(h.hcy, lo4.w, hi4.z));
-    const f2 dby = fma2(h.hcy, lo4.z, fma2(neg2(h.hcx), lo4.w, hi4.w));
-    const f2 r0 = fma2(c, hi4.x, fma2(s, hi4.y, h.hhx));
-    const f2 r1 = fma2(s, hi4.x, fma2(c, hi4.y, h.hhy));
-    const f2 r2 = fma2(c, h.hhx, fma2(s, h.hhy, hi4.x));
-    const f2 r3 = fma2(s, h.hhx, fma2(c, h.hhy, hi4.y));
-    if ((fabsf(lo(drx)) <= lo(r0)) & (fabsf(lo(dry)) <= lo(r1)) & (fabsf(lo(dbx)) <= lo(r2)) & (fabsf(lo(dby)) <= lo(r3))) hit0 = true;
-    if ((fabsf(hi(drx)) <= hi(r0)) & (fabsf(hi(dry)) <= hi(r1)) & (fabsf(hi(dbx)) <= hi(r2)) & (fabsf(hi(dby)) <= hi(r3))) hit1 = true;
-}
-
 template <int EST, int NL, bool EARLY_EXIT>
 __global__ void __launch_bounds__(128, 4) score_plans_kernel(const ScoreLaunch a) {
     extern __shared__ __align__(16) unsigned char s_raw[];

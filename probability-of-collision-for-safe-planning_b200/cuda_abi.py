@@ -28,7 +28,7 @@ class McParams(C.Structure):
         ("n_landmarks", C.c_int), ("landmarks", _dp), ("cov0", C.c_double * 9),
         ("n_rollouts", C.c_uint64), ("rollout_offset", C.c_uint64),
         ("mode", C.c_int), ("estimator", C.c_int), ("early_exit", C.c_int), ("seed", C.c_uint64),
-        ("applied", _dp), ("z0", _dp), ("near_eps", C.c_double), ("precise", C.c_int),
+        ("applied", _dp), ("z0", _dp), ("near_eps", C.c_double), ("precise", C.c_int), ("exhaustive", C.c_int),
     ]
 
 
@@ -182,7 +182,7 @@ def dptr(a):
 
 
 def make_mc_params(plan, n_rollouts=0, mode=MODE_PHILOX, estimator=EST_REFERENCE, early_exit=True,
-                   seed=0x5AFEC0DE, rollout_offset=0, applied=None, z0=None, near_eps=1e-4, precise=False):
+                   seed=0x5AFEC0DE, rollout_offset=0, applied=None, z0=None, near_eps=1e-4, precise=False, exhaustive=False):
     """plan: dict(trajectory[3,T], odometry[3,T-1], alphas[4], Q, landmarks[2,L], cov0[3,3]).
     Returns (McParams, keepalive list of the arrays its pointers refer to)."""
     tr = np.ascontiguousarray(plan["trajectory"], dtype=np.float64)
@@ -208,6 +208,7 @@ def make_mc_params(plan, n_rollouts=0, mode=MODE_PHILOX, estimator=EST_REFERENCE
         p.z0 = dptr(zz)
     p.near_eps = float(near_eps)
     p.precise = int(bool(precise))
+    p.exhaustive = int(bool(exhaustive))
     return p, keep
 
 
@@ -286,6 +287,8 @@ class Context:
         b = np.ascontiguousarray(boxes, dtype=np.float64).reshape(-1, 8)
         h = np.ascontiguousarray(hulls, dtype=np.float64).reshape(-1, 8)
         check(lib().mcsim_cuda_set_scene(self._h, dptr(b), b.shape[0], dptr(h), h.shape[0]))
+        # live (hull, box) pairs: z-intervals overlap (the same rule as mcsim_cuda_set_scene)
+        self.n_pairs = int(sum(((hh[6] < b[:, 7]) & (b[:, 6] < hh[7])).sum() for hh in h))
 
     def mc_run(self, params, want_counts=False, want_hist=False, audit=False):
         """Runs params.n_rollouts rollouts; returns a dict."""

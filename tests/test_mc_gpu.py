@@ -164,7 +164,7 @@ def test_philox_packed_kernel_matches_precise_kernel(ctx, plan, scenes, name, es
     assert same >= 0.99 and flags >= 0.999
     assert abs(a["P"] - b["P"]) <= 2e-3
     assert a["executed_steps"] == b["executed_steps"] == N * plan["trajectory"].shape[1]
-    assert a["pair_tests"] == b["pair_tests"]
+    assert a["pair_tests"] <= b["pair_tests"]     # packed kernel: broad phase on by default
     assert int(a["first_hit_hist"].sum()) == a["hits"] == int((a["counts"] > 0).sum())
     # early exit on the packed kernel: same flags as its own exhaustive run
     p, keep = abi.make_mc_params(plan, n_rollouts=N, mode=abi.MODE_PHILOX, estimator=e, early_exit=True, rollout_offset=12345)
@@ -172,6 +172,41 @@ def test_philox_packed_kernel_matches_precise_kernel(ctx, plan, scenes, name, es
     np.testing.assert_array_equal(ee["counts"], (a["counts"] > 0).astype(np.uint32))
     assert ee["hits"] == a["hits"] and ee["executed_steps"] < a["executed_steps"]
     np.testing.assert_array_equal(ee["first_hit_hist"], a["first_hit_hist"])
+
+
+@pytest.mark.parametrize("est", ["reference", "closedloop"])
+@pytest.mark.parametrize("name", ["pr2test2", "pr2custom"])
+def test_philox_broad_phase_is_exact(ctx, plan, scenes, name, est):
+    """The packed kernel's broad phase (per-waypoint candidate lists chosen by the warp's largest deviation from
+    x*_t, exhaustive fallback) must give the SAME per-rollout collision counts, first-hit histogram and executed
+    steps as testing every live pair at every step -- bit-exact, with and without early exit; only the executed
+    pair tests shrink.  A second plan with a 36 x larger initial covariance (sigma = 0.19 m) drives warps through every level
+    and into the exhaustive fallback."""
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    ctx.set_scene(scenes[name]["boxes"], scenes[name]["hulls"])
+    e = abi.EST_REFERENCE if est == "reference" else abi.EST_CLOSEDLOOP
+    N = 150001
+    wide = dict(plan)
+    wide["cov0"] = np.asarray(plan["cov0"]) * np.array([[36.0], [36.0], [25.0]])
+    for label, pl in (("committed", plan), ("wide start", wide)):
+        for ee in (False, True):
+            outs = {}
+            for exhaustive in (False, True):
+                p, keep = abi.make_mc_params(pl, n_rollouts=N, mode=abi.MODE_PHILOX, estimator=e, early_exit=ee,
+                                             exhaustive=exhaustive, rollout_offset=777)
+                outs[exhaustive] = ctx.mc_run(p, want_counts=True, want_hist=True)
+            a, b = outs[False], outs[True]
+            np.testing.assert_array_equal(a["counts"], b["counts"])
+            np.testing.assert_array_equal(a["first_hit_hist"], b["first_hit_hist"])
+            assert a["hits"] == b["hits"] and a["executed_steps"] == b["executed_steps"]
+            assert b["pair_tests"] == b["executed_steps"] * ctx.n_pairs
+            print("%s/%s/%s ee=%d: P=%.4f pair tests per step %.2f (exhaustive %d)" % (
+                name, est, label, ee, a["P"], a["pair_tests"] / a["executed_steps"], ctx.n_pairs))
+            if label == "committed":
+                assert a["pair_tests"] < 0.25 * b["pair_tests"]
+            else:
+                assert a["pair_tests"] < b["pair_tests"]
 
 
 def test_philox_edge_cases_empty_scene_single_waypoint_other_landmark_counts(ctx, plan, scenes):
