@@ -282,7 +282,7 @@ __device__ __forceinline__ void step2(Rollout2& st, const float* r, int t, unsig
         const float lx = c_mc.nm.lx[l], ly = c_mc.nm.ly[l];
         const f2 ex = add2(real[0], -lx), ey = add2(real[1], -ly);
         const f2 eq = fma2(ex, ex, mul2(ey, ey));
-        const f2 z = fma2(zn[3 + l], c_mc.sqrtQ, mul2(eq, rsqrt2(eq)));
+        const f2 z = fma2(zn[3 + l], c_mc.sqrtQ, sqrt2(eq));
         const f2 dx = add2(mu[0], -lx), dy = add2(mu[1], -ly);
         const f2 qq = fma2(dx, dx, mul2(dy, dy));
         const f2 rs = rsqrt2(qq);
@@ -368,9 +368,14 @@ __global__ void __launch_bounds__(128, MC_P2_CTAS_PER_SM) mc_philox2_kernel(cons
                     if (n == 0) continue;
                     const HullFrame2 h = hull_frame2(c_scene.hulls[hI], q[0], q[1], cs, sn);
                     const ushort2* ci = reinterpret_cast<const ushort2*>(s_cidx) + (t * nh + hI) * MC_CULL_CAP;
+                    ClassFrame2 cf;
+                    unsigned cls = 0xffffffffu;
                     for (int k = 0; k < n; ++k) {
                         const ushort2 o = ci[k];  // x: pair record, y: class header
-                        const ClassFrame2 cf = class_frame2(s_tab[o.y], h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
+                        if (o.y != cls) {         // consecutive candidates mostly share their class (axis-aligned scenes)
+                            cls = o.y;
+                            cf = class_frame2(s_tab[o.y], h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
+                        }
                         class_pair_test2(cf, h.ch, h.sh, h.nph, h.nqh, h.hhx, h.hhy, s_tab[o.x], *reinterpret_cast<const float2*>(s_tab + o.x + 1), h0, h1);
                     }
                     tested += n;
