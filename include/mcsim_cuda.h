@@ -217,6 +217,7 @@ typedef struct {
     double* gmm_post;            /* [K x 13] optional: mixture after the last truncation */
     int degenerate;
     float kernel_ms;             /* summed device time of the truncation kernels */
+    uint64_t pair_tests;         /* Philox mode: SAT pair tests executed (broad phase as in mcsim_mc_params.exhaustive) */
 } mcsim_gmm_run_result;
 
 /* Whole GMM branch of EKF_GaussProp for one plan; plan / noise parameters come from mc (its
@@ -244,6 +245,7 @@ typedef struct {
     double* probabilities;       /* [n_traj][T] optional */
     int degenerate;              /* summed over the batch */
     float kernel_ms;
+    uint64_t pair_tests;         /* SAT pair tests executed by the whole batch */
 } mcsim_gmm_batch_result;
 
 int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* ctx, const mcsim_mc_params* mc, const mcsim_gmm_batch_params* g,

@@ -70,6 +70,10 @@ struct GmmLaunch {
     int do_ekf;                   // refit kernel: propagate to waypoint t+1 (0 for the single-shot API)
     int B;                        // batch: independent trajectories in the same launches (Philox mode; 0/1 = single)
     const float4* sat2;           // orientation-grouped FP32 pair table (Philox mode SAT)
+    const unsigned* cull;         // Philox mode: the plan's candidate lists (sat_device.cuh), NULL = every pair
+    int cull_stride;              // batch: 32-bit words between the members' lists (0: one plan for all)
+    const float2* nominal;        // [T] (x*_t, y*_t), the centres of the lists; batch: [B][T] when cull_stride != 0
+    unsigned long long* tests;    // optional: executed pair tests (all members)
 };
 
 // Batch member b (blockIdx.y of the count / sample kernels, blockIdx.x of the refit kernel): same plan-independent
@@ -84,6 +88,7 @@ __device__ __forceinline__ GmmLaunch gmm_member(const GmmLaunch& in, int b) {
         a.probabilities += size_t(b) * in.T;
         a.degenerate += b;
         a.stream_id += unsigned(b);
+        if (in.cull && in.cull_stride) { a.cull += size_t(b) * in.cull_stride; a.nominal += size_t(b) * in.T; }
     }
     return a;
 }
@@ -141,16 +146,27 @@ __global__ void __launch_bounds__(256) gmm_count_kernel(const GmmLaunch a_in) {
         s_cdf[last] = 2.0f;  // u in (0,1]: the last live component absorbs rounding
     }
     __syncthreads();
+    // one Philox block serves 4 consecutive samples (block index i / 4, word i % 4): one thread per block,
+    // block-uniform trip count, per-component ballots instead of per-sample shared atomics
+    const unsigned long long n4 = (a.n + 3) >> 2;
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
-        // one Philox block serves 4 consecutive samples: block index i/4, word i%4
-        mcsim_rng::u32x4 c = {unsigned(i >> 2), a.stream_id, unsigned(2 * a.t + 1) | unsigned((i >> 34) << 16), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
+    const int K = a.K;
+    for (unsigned long long base = (unsigned long long)blockIdx.x * blockDim.x; base < n4; base += stride) {
+        const unsigned long long j = base + threadIdx.x;
+        mcsim_rng::u32x4 c = {unsigned(j), a.stream_id, unsigned(2 * a.t + 1) | unsigned((j >> 32) << 16), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
         c = mcsim_rng::philox4x32_10(c, a.k0, a.k1);
-        const unsigned w = (i & 3) == 0 ? c.x : (i & 3) == 1 ? c.y : (i & 3) == 2 ? c.z : c.w;
-        const float u = mcsim_rng::u01(w);
-        int g = 0;
-        while (g < a.K - 1 && u > s_cdf[g]) ++g;
-        atomicAdd(&s_hist[g], 1u);
+        const unsigned w[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const bool valid = j < n4 && 4 * j + q < a.n;
+            const float u = mcsim_rng::u01(w[q]);
+            int g = 0;
+            while (g < K - 1 && u > s_cdf[g]) ++g;
+            for (int gg = 0; gg < K; ++gg) {
+                const unsigned m = __ballot_sync(0xffffffffu, valid && g == gg);
+                if (m && (threadIdx.x & 31) == 0) atomicAdd(&s_hist[gg], unsigned(__popc(m)));
+            }
+        }
     }
     __syncthreads();
     if (threadIdx.x < a.K && s_hist[threadIdx.x]) atomicAdd(&a.hist[threadIdx.x], s_hist[threadIdx.x]);
@@ -163,7 +179,17 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
     __shared__ double s_comp[MCSIM_MAX_GAUSSIANS][GMM_COMP];
     __shared__ double s_stat[MCSIM_MAX_GAUSSIANS][GMM_STAT];
     __shared__ unsigned long long s_prefix[MCSIM_MAX_GAUSSIANS + 1];
+    __shared__ unsigned char s_ccnt[MCSIM_MAX_HULLS * MC_CULL_LEVELS];
+    __shared__ ushort2 s_cidx[MCSIM_MAX_HULLS * MC_CULL_CAP];
     const int K = a.K;
+    if (MODE != MCSIM_MODE_REPLAY && a.cull) {
+        const int nh = c_scene.n_hulls;
+        const unsigned char* gc = reinterpret_cast<const unsigned char*>(a.cull) + size_t(a.t) * nh * MC_CULL_LEVELS;
+        const ushort2* gi = reinterpret_cast<const ushort2*>(a.cull + (size_t(a.T) * nh * MC_CULL_LEVELS + 3) / 4) + size_t(a.t) * nh * MC_CULL_CAP;
+        for (int i = threadIdx.x; i < nh * MC_CULL_LEVELS; i += blockDim.x) s_ccnt[i] = gc[i];
+        for (int i = threadIdx.x; i < nh * MC_CULL_CAP; i += blockDim.x) s_cidx[i] = gi[i];
+    }
+    unsigned long long my_tests = 0;
     for (int i = threadIdx.x; i < K * GMM_COMP; i += blockDim.x) s_comp[i / GMM_COMP][i % GMM_COMP] = a.comps[i];
     for (int i = threadIdx.x; i < K * GMM_STAT; i += blockDim.x) s_stat[i / GMM_STAT][i % GMM_STAT] = 0.0;
     if (threadIdx.x == 0) {
@@ -176,12 +202,44 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
     }
     __syncthreads();
 
-    // Block-uniform trip count; every pass ends with a warp-level reduction of the pass's contributions
-    // (segmented by component: samples are grouped by component, so a warp almost always holds one),
-    // then ONE shared-memory atomic per statistic and warp.  (Per-thread FP64 shared atomics are CAS
-    // loops: with every thread of the grid flushing 11 of them onto K x 11 addresses they serialised the
-    // whole kernel.)
-    int g = 0;
+    // Block-uniform trip count.  Every thread keeps the sums of its free samples in registers for the component
+    // its samples currently belong to (samples are grouped by component and a thread's sample index only grows, so
+    // that component changes at most K - 1 times); when any lane of the warp moves on to another component -- and
+    // after the last pass -- the warp reduces its lanes' sums, segmented by component, into ONE shared-memory atomic
+    // per statistic and warp.  (Per-thread FP64 shared atomics are CAS loops: with every thread of the grid
+    // flushing 11 of them onto K x 11 addresses they serialised the whole kernel; a reduction after every pass
+    // costs 90 shuffles per sample.)
+    int g = 0, g_acc = -1;
+    unsigned nf = 0, nc = 0;
+    double acc[9] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    auto flush = [&]() {
+        const int gmin = __reduce_min_sync(0xffffffffu, g_acc >= 0 ? g_acc : 0x7fffffff);
+        const int gmax = __reduce_max_sync(0xffffffffu, g_acc);
+        for (int gg = gmin; gg <= gmax; ++gg) {  // warp-uniform
+            const bool sel = g_acc == gg;
+            const unsigned wf = __reduce_add_sync(0xffffffffu, sel ? nf : 0u);
+            const unsigned wc = __reduce_add_sync(0xffffffffu, sel ? nc : 0u);
+            if (wf) {
+                double v[9];
+#pragma unroll
+                for (int k = 0; k < 9; ++k) {
+                    v[k] = sel ? acc[k] : 0.0;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+                }
+                if ((threadIdx.x & 31) == 0) {
+                    atomicAdd(&s_stat[gg][0], double(wf));
+#pragma unroll
+                    for (int k = 0; k < 9; ++k) atomicAdd(&s_stat[gg][2 + k], v[k]);
+                }
+            }
+            if (wc && (threadIdx.x & 31) == 0) atomicAdd(&s_stat[gg][1], double(wc));
+        }
+        g_acc = -1;
+        nf = nc = 0;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) acc[k] = 0.0;
+    };
     const unsigned long long n = s_prefix[K] < a.n ? s_prefix[K] : a.n;
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
     for (unsigned long long base = (unsigned long long)blockIdx.x * blockDim.x; base < n; base += stride) {
@@ -189,6 +247,7 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
         const bool valid = i < n;
         bool hit = false;
         double d0 = 0.0, d1 = 0.0, d2 = 0.0;
+        float xf = 0.f, yf = 0.f, sn = 0.f, cs = 1.f;
         if (valid) {
             while (g < K - 1 && i >= s_prefix[g + 1]) ++g;  // i only grows: the component index is monotone
             double z0, z1, z2;
@@ -212,46 +271,204 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
             if (MODE == MCSIM_MODE_REPLAY) {
                 hit = clearance_d(a.hulls_d, a.pairs_d, a.n_hulls, x, y, th) <= 0.0;
             } else {
-                float sn, cs;
                 // theta of a sample is mu_theta + O(sigma): reduce to [-pi, pi] before the FP32 sincos
                 double tr = th;
                 if (tr > MCSIM_PI) tr -= 2 * MCSIM_PI;
                 if (tr < -MCSIM_PI) tr += 2 * MCSIM_PI;
                 sincosf(float(tr), &sn, &cs);
-                hit = robot_hits_grouped(a.sat2, float(x), float(y), cs, sn);
+                xf = float(x);
+                yf = float(y);
             }
         }  // valid
-        const int gmin = __reduce_min_sync(0xffffffffu, valid ? g : 0x7fffffff);
-        const int gmax = __reduce_max_sync(0xffffffffu, valid ? g : -1);
-        for (int gg = gmin; gg <= gmax; ++gg) {  // warp-uniform
-            const bool sel = valid && g == gg;
-            const unsigned nf = __reduce_add_sync(0xffffffffu, unsigned(sel && !hit));
-            const unsigned nc = __reduce_add_sync(0xffffffffu, unsigned(sel && hit));
-            double v[9];
-            const bool use = sel && !hit;
-            v[0] = use ? d0 : 0.0; v[1] = use ? d1 : 0.0; v[2] = use ? d2 : 0.0;
-            v[3] = use ? d0 * d0 : 0.0; v[4] = use ? d0 * d1 : 0.0; v[5] = use ? d0 * d2 : 0.0;
-            v[6] = use ? d1 * d1 : 0.0; v[7] = use ? d1 * d2 : 0.0; v[8] = use ? d2 * d2 : 0.0;
-            if (nf) {
-#pragma unroll
-                for (int k = 0; k < 9; ++k)
-#pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+        if (MODE != MCSIM_MODE_REPLAY) {
+            // warp-uniform choice of the candidate list by the warp's largest deviation from x*_t (exact: sat_device.cuh)
+            int lev = MC_CULL_LEVELS;
+            if (a.cull) {
+                const float2 nom = __ldg(a.nominal + a.t);
+                const float ex = xf - nom.x, ey = yf - nom.y;
+                const float dm = __uint_as_float(__reduce_max_sync(0xffffffffu, valid ? __float_as_uint(fmaf(ex, ex, ey * ey)) : 0u));
+                lev = cull_level(dm);
+                if (lev < MC_CULL_LEVELS && s_ccnt[lev] == MC_CULL_OVERFLOW) lev = MC_CULL_LEVELS;
             }
-            if ((threadIdx.x & 31) == 0) {
-                if (nf) {
-                    atomicAdd(&s_stat[gg][0], double(nf));
-#pragma unroll
-                    for (int k = 0; k < 9; ++k) atomicAdd(&s_stat[gg][2 + k], v[k]);
-                }
-                if (nc) atomicAdd(&s_stat[gg][1], double(nc));
+            unsigned tested = 0;
+            if (lev < MC_CULL_LEVELS) {
+                hit = robot_hits_listed(a.sat2, s_ccnt, s_cidx, lev, xf, yf, cs, sn, tested);
+            } else {
+                hit = robot_hits_grouped(a.sat2, xf, yf, cs, sn);
+                tested = c_scene.n_pairs;
+            }
+            if (valid) my_tests += tested;
+        }
+        if (__any_sync(0xffffffffu, valid && g_acc >= 0 && g != g_acc)) flush();
+        if (valid) {
+            g_acc = g;
+            if (hit) {
+                ++nc;
+            } else {
+                ++nf;
+                acc[0] += d0; acc[1] += d1; acc[2] += d2;
+                acc[3] += d0 * d0; acc[4] += d0 * d1; acc[5] += d0 * d2;
+                acc[6] += d1 * d1; acc[7] += d1 * d2; acc[8] += d2 * d2;
             }
         }
     }
+    flush();
     __syncthreads();
     for (int i = threadIdx.x; i < K * GMM_STAT; i += blockDim.x) {
         const double v = s_stat[i / GMM_STAT][i % GMM_STAT];
         if (v != 0.0) atomicAdd(&a.stats[i], v);
+    }
+    if (MODE != MCSIM_MODE_REPLAY && a.tests) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) my_tests += __shfl_xor_sync(0xffffffffu, my_tests, o);
+        if ((threadIdx.x & 31) == 0 && my_tests) atomicAdd(a.tests, my_tests);
+    }
+}
+
+// ---- Philox mode: the same step in FP32 ----------------------------------------------------------------------------
+// Same Philox counters, draws and sample -> component assignment as gmm_sample_kernel<PHILOX>; what changes is
+// the arithmetic: x = mu_g + L_g z, the angle reduction and sin / cos in FP32 (MUFU), 32-bit sample indices, the
+// sums of the free samples' d = L_g z still in FP64.  There is no bit-exact bar in this mode (the bar is the
+// reference's run-to-run distribution, tests/test_gmm_gpu.py); replay mode keeps the FP64 kernel above.
+
+// per-thread sums of the free samples of the component the thread's samples currently belong to (see
+// gmm_sample_kernel); flush = warp reduction segmented by component, one shared atomic per statistic and warp
+struct GmmAcc {
+    int g_acc = -1;
+    unsigned nf = 0, nc = 0;
+    double acc[9] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    __device__ __forceinline__ void add(int g, bool hit, float d0, float d1, float d2) {
+        g_acc = g;
+        if (hit) {
+            ++nc;
+        } else {
+            ++nf;
+            const double e0 = d0, e1 = d1, e2 = d2;
+            acc[0] += e0; acc[1] += e1; acc[2] += e2;
+            acc[3] = fma(e0, e0, acc[3]); acc[4] = fma(e0, e1, acc[4]); acc[5] = fma(e0, e2, acc[5]);
+            acc[6] = fma(e1, e1, acc[6]); acc[7] = fma(e1, e2, acc[7]); acc[8] = fma(e2, e2, acc[8]);
+        }
+    }
+    __device__ __forceinline__ void flush(double (*s_stat)[GMM_STAT]) {
+        const int gmin = __reduce_min_sync(0xffffffffu, g_acc >= 0 ? g_acc : 0x7fffffff);
+        const int gmax = __reduce_max_sync(0xffffffffu, g_acc);
+        for (int gg = gmin; gg <= gmax; ++gg) {  // warp-uniform
+            const bool sel = g_acc == gg;
+            const unsigned wf = __reduce_add_sync(0xffffffffu, sel ? nf : 0u);
+            const unsigned wc = __reduce_add_sync(0xffffffffu, sel ? nc : 0u);
+            if (wf) {
+                double v[9];
+#pragma unroll
+                for (int k = 0; k < 9; ++k) {
+                    v[k] = sel ? acc[k] : 0.0;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+                }
+                if ((threadIdx.x & 31) == 0) {
+                    atomicAdd(&s_stat[gg][0], double(wf));
+#pragma unroll
+                    for (int k = 0; k < 9; ++k) atomicAdd(&s_stat[gg][2 + k], v[k]);
+                }
+            }
+            if (wc && (threadIdx.x & 31) == 0) atomicAdd(&s_stat[gg][1], double(wc));
+        }
+        g_acc = -1;
+        nf = nc = 0;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) acc[k] = 0.0;
+    }
+};
+
+// one pass of the sample loop: samples base + threadIdx.x of waypoint a.t; every thread of the warp calls it
+template <bool SMEM>
+__device__ __forceinline__ void gmm_philox_pass(const GmmLaunch& a, unsigned i, unsigned n, int K, int& g, const unsigned* s_prefix,
+                                                const float (*s_mu)[3], const float (*s_L)[6], double (*s_stat)[GMM_STAT],
+                                                const float4* tab, const unsigned char* ccnt, const ushort2* cidx, bool cull, float2 nom,
+                                                GmmAcc& acc, unsigned& my_tests) {
+    const bool valid = i < n;
+    while (valid && g < K - 1 && i >= s_prefix[g + 1]) ++g;  // i only grows: the component index is monotone
+    mcsim_rng::u32x4 c = {i, a.stream_id, unsigned(2 * a.t), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
+    c = mcsim_rng::philox4x32_10(c, a.k0, a.k1);
+    float z0, z1, z2, z3;
+    mcsim_rng::box_muller(c.x, c.y, z0, z1);
+    mcsim_rng::box_muller(c.z, c.w, z2, z3);
+    const float* Lc = s_L[g];
+    const float d0 = Lc[0] * z0;
+    const float d1 = fmaf(Lc[2], z1, Lc[1] * z0);
+    const float d2 = fmaf(Lc[5], z2, fmaf(Lc[4], z1, Lc[3] * z0));
+    const float x = s_mu[g][0] + d0, y = s_mu[g][1] + d1;
+    float th = s_mu[g][2] + d2;
+    th -= 6.283185307179586f * rintf(th * 0.15915494309189535f);  // into [-pi, pi] for the MUFU sin / cos
+    float sn, cs;
+    __sincosf(th, &sn, &cs);
+    // warp-uniform choice of the candidate list by the warp's largest deviation from x*_t (exact: sat_device.cuh)
+    int lev = MC_CULL_LEVELS;
+    if (cull) {
+        const float ex = x - nom.x, ey = y - nom.y;
+        const float dm = __uint_as_float(__reduce_max_sync(0xffffffffu, valid ? __float_as_uint(fmaf(ex, ex, ey * ey)) : 0u));
+        lev = cull_level(dm);
+        if (lev < MC_CULL_LEVELS && ccnt[lev] == MC_CULL_OVERFLOW) lev = MC_CULL_LEVELS;
+    }
+    unsigned tested = 0;
+    bool hit;
+    if (lev < MC_CULL_LEVELS) {
+        hit = robot_hits_listed<SMEM>(tab, ccnt, cidx, lev, x, y, cs, sn, tested);
+    } else {
+        hit = robot_hits_grouped<SMEM>(tab, x, y, cs, sn);
+        tested = c_scene.n_pairs;
+    }
+    if (__any_sync(0xffffffffu, valid && acc.g_acc >= 0 && g != acc.g_acc)) acc.flush(s_stat);
+    if (valid) {
+        my_tests += tested;
+        acc.add(g, hit, d0, d1, d2);
+    }
+}
+
+__global__ void __launch_bounds__(256) gmm_sample_philox_kernel(const GmmLaunch a_in) {
+    const GmmLaunch a = gmm_member(a_in, blockIdx.y);
+    __shared__ float s_mu[MCSIM_MAX_GAUSSIANS][3];
+    __shared__ float s_L[MCSIM_MAX_GAUSSIANS][6];
+    __shared__ double s_stat[MCSIM_MAX_GAUSSIANS][GMM_STAT];
+    __shared__ unsigned s_prefix[MCSIM_MAX_GAUSSIANS + 1];
+    __shared__ unsigned char s_ccnt[MCSIM_MAX_HULLS * MC_CULL_LEVELS];
+    __shared__ ushort2 s_cidx[MCSIM_MAX_HULLS * MC_CULL_CAP];
+    const int K = a.K;
+    if (a.cull) {
+        const int nh = c_scene.n_hulls;
+        const unsigned char* gc = reinterpret_cast<const unsigned char*>(a.cull) + size_t(a.t) * nh * MC_CULL_LEVELS;
+        const ushort2* gi = reinterpret_cast<const ushort2*>(a.cull + (size_t(a.T) * nh * MC_CULL_LEVELS + 3) / 4) + size_t(a.t) * nh * MC_CULL_CAP;
+        for (int i = threadIdx.x; i < nh * MC_CULL_LEVELS; i += blockDim.x) s_ccnt[i] = gc[i];
+        for (int i = threadIdx.x; i < nh * MC_CULL_CAP; i += blockDim.x) s_cidx[i] = gi[i];
+    }
+    for (int i = threadIdx.x; i < K * 3; i += blockDim.x) s_mu[i / 3][i % 3] = float(a.comps[(i / 3) * GMM_COMP + 1 + i % 3]);
+    for (int i = threadIdx.x; i < K * 6; i += blockDim.x) s_L[i / 6][i % 6] = float(a.comps[(i / 6) * GMM_COMP + 13 + i % 6]);
+    for (int i = threadIdx.x; i < K * GMM_STAT; i += blockDim.x) s_stat[i / GMM_STAT][i % GMM_STAT] = 0.0;
+    if (threadIdx.x == 0) {
+        unsigned acc = 0;
+        for (int g = 0; g < K; ++g) { s_prefix[g] = acc; acc += a.hist[g]; }
+        s_prefix[K] = acc;
+    }
+    __syncthreads();
+
+    int g = 0;
+    unsigned my_tests = 0;
+    GmmAcc acc;
+    const unsigned n = unsigned(s_prefix[K] < a.n ? s_prefix[K] : a.n);  // Philox mode: n <= 2^31 (checked on the host)
+    const unsigned stride = gridDim.x * blockDim.x;
+    const float2 nom = a.cull ? __ldg(a.nominal + a.t) : make_float2(0.f, 0.f);
+    for (unsigned base = blockIdx.x * blockDim.x; base < n; base += stride)
+        gmm_philox_pass<false>(a, base + threadIdx.x, n, K, g, s_prefix, s_mu, s_L, s_stat, a.sat2, s_ccnt, s_cidx, a.cull != nullptr, nom, acc, my_tests);
+    acc.flush(s_stat);
+    __syncthreads();
+    for (int i = threadIdx.x; i < K * GMM_STAT; i += blockDim.x) {
+        const double v = s_stat[i / GMM_STAT][i % GMM_STAT];
+        if (v != 0.0) atomicAdd(&a.stats[i], v);
+    }
+    if (a.tests) {
+        unsigned long long t64 = my_tests;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t64 += __shfl_xor_sync(0xffffffffu, t64, o);
+        if ((threadIdx.x & 31) == 0 && t64) atomicAdd(a.tests, t64);
     }
 }
 
@@ -271,65 +488,253 @@ __host__ __device__ inline bool gmm_chol3(const double* A, double* Lo) {
 }
 
 // ---- refit + propagate: one thread per component ------------------------------------------------------------------
+// cp: the component's record (GMM_COMP doubles), st: its statistics; both may live in global or shared memory.
+// Part 1: truncated moments of the free samples; returns (n_free, n_coll).
+__device__ __forceinline__ void gmm_refit_moments(double* cp, const double* st, int* degenerate, double& nf, double& nc) {
+    nf = st[0];
+    nc = st[1];
+    if (nf >= 2.0) {
+        // mean(free) = mu + sum d / n;  cov = (sum d d^T - (sum d)(sum d)^T / n) / (n - 1)   (unbiased)
+        const double m0 = st[2] / nf, m1 = st[3] / nf, m2 = st[4] / nf;
+        const double inv = 1.0 / (nf - 1.0);
+        const double cxx = (st[5] - st[2] * m0) * inv, cxy = (st[6] - st[2] * m1) * inv, cxz = (st[7] - st[2] * m2) * inv;
+        const double cyy = (st[8] - st[3] * m1) * inv, cyz = (st[9] - st[3] * m2) * inv, czz = (st[10] - st[4] * m2) * inv;
+        cp[1] += m0; cp[2] += m1; cp[3] += m2;
+        cp[4] = cxx; cp[5] = cxy; cp[6] = cxz;
+        cp[7] = cxy; cp[8] = cyy; cp[9] = cyz;
+        cp[10] = cxz; cp[11] = cyz; cp[12] = czz;
+    } else {
+        // reference: mean of a 3x0 matrix -> exception / undefined behaviour.  Here: moments kept, counted.
+        atomicAdd(degenerate, 1);
+    }
+}
+// Part 2 (after every component's part 1): weight, p_t, records, EKFpredict + EKFupdate to waypoint t+1, Cholesky.
+__device__ __forceinline__ void gmm_refit_finish(const GmmLaunch& a, int g, double* cp, const double* s_free, const double* s_coll) {
+    using namespace mcsim_math;
+    const int K = a.K;
+    double tf = 0, tc = 0;
+    for (int k = 0; k < K; ++k) { tf += s_free[k]; tc += s_coll[k]; }
+    // normalise(collisionCounts, 1, 1).row(1): divides by the row's 1-norm, or by 1 if that is 0
+    cp[0] = s_free[g] / (tf > 0 ? tf : 1.0);
+    if (g == 0) a.probabilities[a.t] = tc / double(a.n);
+    if (a.n_out) { a.n_out[g] = (unsigned long long)s_coll[g]; a.n_out[K + g] = (unsigned long long)s_free[g]; }
+    if (a.trunc_out) for (int k = 0; k < GMM_REC; ++k) a.trunc_out[g * GMM_REC + k] = cp[k];
+    if (a.t == a.T - 1 && a.rec_post) for (int k = 0; k < GMM_REC; ++k) a.rec_post[g * GMM_REC + k] = cp[k];
+    // ---- move the component to waypoint t+1: EKFpredict (:766-772) then EKFupdate (:804-812)
+    if (a.do_ekf && a.t < a.T - 1) {
+        const GmmStepTable& s = a.steps[a.t];
+        NoiseModel<double> nm;
+        nm.Q = a.Q; nm.L = a.L;
+        for (int l = 0; l < a.L; ++l) { nm.lx[l] = a.lx[l]; nm.ly[l] = a.ly[l]; }
+        double pmu[3], pS[9];
+        ekf_predict(cp + 1, cp + 4, s.u, s.M, pmu, pS);
+        ekf_update(nm, pmu, pS, s.z, a.L);
+        for (int k = 0; k < 3; ++k) cp[1 + k] = pmu[k];
+        for (int k = 0; k < 9; ++k) cp[4 + k] = pS[k];
+        if (a.rec_pre) for (int k = 0; k < GMM_REC; ++k) a.rec_pre[(size_t(a.t + 1) * K + g) * GMM_REC + k] = cp[k];
+    }
+    if (!gmm_chol3(cp + 4, cp + 13)) {
+        // not SPD (the reference falls back to an eigen-decomposition, glue_mvnrnd_meat.hpp:98-132):
+        // sample from the diagonal instead and count the event
+        atomicAdd(a.degenerate, 1);
+        cp[13] = sqrt(fmax(cp[4], 0.0)); cp[14] = 0; cp[15] = sqrt(fmax(cp[8], 0.0));
+        cp[16] = 0; cp[17] = 0; cp[18] = sqrt(fmax(cp[12], 0.0));
+    }
+}
+
 __global__ void __launch_bounds__(32) gmm_refit_kernel(const GmmLaunch a_in) {
     const GmmLaunch a = gmm_member(a_in, blockIdx.x);
-    using namespace mcsim_math;
     __shared__ double s_free[MCSIM_MAX_GAUSSIANS], s_coll[MCSIM_MAX_GAUSSIANS];
     const int g = threadIdx.x;
     const int K = a.K;
     double* cp = a.comps + g * GMM_COMP;
-    if (g < K) {
-        const double* st = a.stats + g * GMM_STAT;
-        const double nf = st[0], nc = st[1];
-        s_free[g] = nf; s_coll[g] = nc;
-        if (nf >= 2.0) {
-            // mean(free) = mu + sum d / n;  cov = (sum d d^T - (sum d)(sum d)^T / n) / (n - 1)   (unbiased)
-            const double m0 = st[2] / nf, m1 = st[3] / nf, m2 = st[4] / nf;
-            const double inv = 1.0 / (nf - 1.0);
-            const double cxx = (st[5] - st[2] * m0) * inv, cxy = (st[6] - st[2] * m1) * inv, cxz = (st[7] - st[2] * m2) * inv;
-            const double cyy = (st[8] - st[3] * m1) * inv, cyz = (st[9] - st[3] * m2) * inv, czz = (st[10] - st[4] * m2) * inv;
-            cp[1] += m0; cp[2] += m1; cp[3] += m2;
-            cp[4] = cxx; cp[5] = cxy; cp[6] = cxz;
-            cp[7] = cxy; cp[8] = cyy; cp[9] = cyz;
-            cp[10] = cxz; cp[11] = cyz; cp[12] = czz;
-        } else {
-            // reference: mean of a 3x0 matrix -> exception / undefined behaviour.  Here: moments kept, counted.
-            atomicAdd(a.degenerate, 1);
-        }
-    }
+    if (g < K) gmm_refit_moments(cp, a.stats + g * GMM_STAT, a.degenerate, s_free[g], s_coll[g]);
     __syncthreads();
     if (g < K) {
-        double tf = 0, tc = 0;
-        for (int k = 0; k < K; ++k) { tf += s_free[k]; tc += s_coll[k]; }
-        // normalise(collisionCounts, 1, 1).row(1): divides by the row's 1-norm, or by 1 if that is 0
-        cp[0] = s_free[g] / (tf > 0 ? tf : 1.0);
-        if (g == 0) a.probabilities[a.t] = tc / double(a.n);
-        if (a.n_out) { a.n_out[g] = (unsigned long long)s_coll[g]; a.n_out[K + g] = (unsigned long long)s_free[g]; }
-        if (a.trunc_out) for (int k = 0; k < GMM_REC; ++k) a.trunc_out[g * GMM_REC + k] = cp[k];
-        if (a.t == a.T - 1 && a.rec_post) for (int k = 0; k < GMM_REC; ++k) a.rec_post[g * GMM_REC + k] = cp[k];
-        // ---- move the component to waypoint t+1: EKFpredict (:766-772) then EKFupdate (:804-812)
-        if (a.do_ekf && a.t < a.T - 1) {
-            const GmmStepTable& s = a.steps[a.t];
-            NoiseModel<double> nm;
-            nm.Q = a.Q; nm.L = a.L;
-            for (int l = 0; l < a.L; ++l) { nm.lx[l] = a.lx[l]; nm.ly[l] = a.ly[l]; }
-            double pmu[3], pS[9];
-            ekf_predict(cp + 1, cp + 4, s.u, s.M, pmu, pS);
-            ekf_update(nm, pmu, pS, s.z, a.L);
-            for (int k = 0; k < 3; ++k) cp[1 + k] = pmu[k];
-            for (int k = 0; k < 9; ++k) cp[4 + k] = pS[k];
-            if (a.rec_pre) for (int k = 0; k < GMM_REC; ++k) a.rec_pre[(size_t(a.t + 1) * K + g) * GMM_REC + k] = cp[k];
-        }
-        if (!gmm_chol3(cp + 4, cp + 13)) {
-            // not SPD (the reference falls back to an eigen-decomposition, glue_mvnrnd_meat.hpp:98-132):
-            // sample from the diagonal instead and count the event
-            atomicAdd(a.degenerate, 1);
-            cp[13] = sqrt(fmax(cp[4], 0.0)); cp[14] = 0; cp[15] = sqrt(fmax(cp[8], 0.0));
-            cp[16] = 0; cp[17] = 0; cp[18] = sqrt(fmax(cp[12], 0.0));
-        }
+        gmm_refit_finish(a, g, cp, s_free, s_coll);
         for (int k = 0; k < GMM_STAT; ++k) a.stats[g * GMM_STAT + k] = 0.0;
         a.hist[g] = 0;
     }
 }
 
+// ---- batch: ONE CTA runs ONE member's whole runGMMEstimation (all T waypoints) ---------------------------------------
+// The three kernels per waypoint above keep a single run's 10^4 samples spread over the GPU; a batch fills the GPU
+// with members instead, and then a member's mixture, statistics, counts, the pair table and the plan's candidate
+// lists can live in shared memory for the whole run: no global atomics, no per-waypoint prologue, one launch instead
+// of 3 T.  Same draws, same component assignment, same refit code as the per-waypoint kernels (member b ==
+// mcsim_cuda_gmm_run on Philox subsequence stream0 + b up to the order of the FP64 sums).
+// Dynamic shared memory: pair table (a.sat2, sat2_n float4) | candidate lists (cull_words 32-bit words).
+__global__ void __launch_bounds__(256, 3) gmm_member_run_kernel(const GmmLaunch a_in, int sat2_n, int cull_words) {
+    extern __shared__ __align__(16) float4 s_tab[];
+    __shared__ double s_comp[MCSIM_MAX_GAUSSIANS][GMM_COMP];
+    __shared__ double s_stat[MCSIM_MAX_GAUSSIANS][GMM_STAT];
+    __shared__ double s_free[MCSIM_MAX_GAUSSIANS], s_coll[MCSIM_MAX_GAUSSIANS];
+    __shared__ float s_mu[MCSIM_MAX_GAUSSIANS][3];
+    __shared__ float s_L[MCSIM_MAX_GAUSSIANS][6];
+    __shared__ float s_cdf[MCSIM_MAX_GAUSSIANS];
+    __shared__ unsigned s_hist[MCSIM_MAX_GAUSSIANS];
+    __shared__ unsigned s_prefix[MCSIM_MAX_GAUSSIANS + 1];
+    GmmLaunch a = gmm_member(a_in, blockIdx.x);
+    const int K = a.K, T = a.T, nh = c_scene.n_hulls;
+    const bool cull = a.cull != nullptr;
+    unsigned* s_cull = reinterpret_cast<unsigned*>(s_tab + sat2_n);
+    for (int i = threadIdx.x; i < sat2_n; i += blockDim.x) s_tab[i] = a.sat2[i];
+    if (cull) for (int i = threadIdx.x; i < cull_words; i += blockDim.x) s_cull[i] = a.cull[i];
+    for (int i = threadIdx.x; i < K * GMM_COMP; i += blockDim.x) s_comp[i / GMM_COMP][i % GMM_COMP] = a.comps[i];
+    for (int i = threadIdx.x; i < K * GMM_STAT; i += blockDim.x) s_stat[i / GMM_STAT][i % GMM_STAT] = 0.0;
+    if (threadIdx.x < MCSIM_MAX_GAUSSIANS) s_hist[threadIdx.x] = 0;
+    const unsigned char* s_ccnt = reinterpret_cast<const unsigned char*>(s_cull);
+    const ushort2* s_cidx = reinterpret_cast<const ushort2*>(s_cull + (T * nh * MC_CULL_LEVELS + 3) / 4);
+    unsigned my_tests = 0;
+    __syncthreads();
+
+    for (int t = 0; t < T; ++t) {
+        a.t = t;
+        // ---- multinomial counts of this waypoint (gmm_count_kernel)
+        if (threadIdx.x == 0) {
+            double acc = 0, tot = 0;
+            for (int g = 0; g < K; ++g) tot += s_comp[g][0];
+            for (int g = 0; g < K; ++g) { acc += s_comp[g][0]; s_cdf[g] = float(acc / tot); }
+            for (int g = K - 1; g >= 0 && !(s_comp[g][0] > 0); --g) s_cdf[g] = 2.0f;
+            int last = K - 1;
+            while (last > 0 && !(s_comp[last][0] > 0)) --last;
+            s_cdf[last] = 2.0f;
+        }
+        for (int i = threadIdx.x; i < K * 3; i += blockDim.x) s_mu[i / 3][i % 3] = float(s_comp[i / 3][1 + i % 3]);
+        for (int i = threadIdx.x; i < K * 6; i += blockDim.x) s_L[i / 6][i % 6] = float(s_comp[i / 6][13 + i % 6]);
+        __syncthreads();
+        const unsigned n4 = unsigned((a.n + 3) >> 2);
+        for (unsigned base = 0; base < n4; base += blockDim.x) {
+            const unsigned j = base + threadIdx.x;
+            mcsim_rng::u32x4 c = {j, a.stream_id, unsigned(2 * t + 1), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
+            c = mcsim_rng::philox4x32_10(c, a.k0, a.k1);
+            const unsigned w[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const bool valid = j < n4 && 4ull * j + q < a.n;
+                const float u = mcsim_rng::u01(w[q]);
+                int g = 0;
+                while (g < K - 1 && u > s_cdf[g]) ++g;
+                for (int gg = 0; gg < K; ++gg) {
+                    const unsigned m = __ballot_sync(0xffffffffu, valid && g == gg);
+                    if (m && (threadIdx.x & 31) == 0) atomicAdd(&s_hist[gg], unsigned(__popc(m)));
+                }
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned acc = 0;
+            for (int g = 0; g < K; ++g) { s_prefix[g] = acc; acc += s_hist[g]; }
+            s_prefix[K] = acc;
+        }
+        __syncthreads();
+        // ---- sample -> collide -> moments (gmm_sample_philox_kernel)
+        {
+            int g = 0;
+            GmmAcc acc;
+            const unsigned n = unsigned(s_prefix[K] < a.n ? s_prefix[K] : a.n);
+            const float2 nom = cull ? __ldg(a.nominal + t) : make_float2(0.f, 0.f);
+            const unsigned char* cc = s_ccnt + t * nh * MC_CULL_LEVELS;
+            const ushort2* ci = s_cidx + t * nh * MC_CULL_CAP;
+            for (unsigned base = 0; base < n; base += blockDim.x)
+                gmm_philox_pass<true>(a, base + threadIdx.x, n, K, g, s_prefix, s_mu, s_L, s_stat, s_tab, cc, ci, cull, nom, acc, my_tests);
+            acc.flush(s_stat);
+        }
+        __syncthreads();
+        // ---- refit + propagate (gmm_refit_kernel)
+        const int g = threadIdx.x;
+        if (g < K) gmm_refit_moments(s_comp[g], s_stat[g], a.degenerate, s_free[g], s_coll[g]);
+        __syncthreads();
+        if (g < K) {
+            gmm_refit_finish(a, g, s_comp[g], s_free, s_coll);
+            for (int k = 0; k < GMM_STAT; ++k) s_stat[g][k] = 0.0;
+            s_hist[g] = 0;
+        }
+        __syncthreads();
+    }
+    if (a.tests) {
+        unsigned long long t64 = my_tests;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t64 += __shfl_xor_sync(0xffffffffu, t64, o);
+        if ((threadIdx.x & 31) == 0 && t64) atomicAdd(a.tests, t64);
+    }
+}
+
+// ---- batch: the members' shared real-robot threads on the device -------------------------------------------------------
+// host_thread.cpp (one closed-loop real robot per run, FP64: MCSimulator.h:692-830 without the particles) for every
+// member of a batch at once: one warp per member.  The 32 lanes draw the member's (T-1) x (3 + L) standard normals
+// (the counters, the FP64 Box-Muller and the order of mcsim_host_normals), lane 0 then walks the plan -- the chain
+// is sequential in t -- and writes the member's step table (applied command, motion noise, observations) and its
+// initial mixture straight into device memory: nothing per member crosses PCIe.
+struct RobotThreadLaunch {
+    int B, T, L, K;
+    unsigned k0, k1, stream0;
+    double alphas[4], Q, cov0[9], chol0[6];
+    double lx[MCSIM_MAX_LANDMARKS], ly[MCSIM_MAX_LANDMARKS];
+    const double* trajectories;   // [3][T] (per_member: [B][3][T])
+    const double* odometry;       // [3][T-1]
+    int per_member;
+    double* normals;              // scratch [B][T-1][3 + L]
+    GmmStepTable* steps;          // [B][T-1]
+    double* comps;                // [B][MCSIM_MAX_GAUSSIANS][GMM_COMP]
+};
+
+__global__ void __launch_bounds__(32) gmm_robot_thread_kernel(const RobotThreadLaunch a) {
+    using namespace mcsim_math;
+    const int b = blockIdx.x, T = a.T, L = a.L, TS = T > 1 ? T - 1 : 1, per_step = 3 + L, blocks = (per_step + 3) / 4;
+    double* zn = a.normals + size_t(b) * TS * per_step;
+    for (int q = threadIdx.x; q < (T - 1) * blocks; q += 32) {
+        const int t = q / blocks, j = q - t * blocks;
+        mcsim_rng::u32x4 c = {unsigned(t), a.stream0 + unsigned(b), unsigned(j), unsigned(mcsim_rng::PURPOSE_GMM_HOST)};
+        c = mcsim_rng::philox4x32_10(c, a.k0, a.k1);
+        const unsigned w[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const double u1 = (double(w[2 * h]) + 0.5) * (1.0 / 4294967296.0);
+            const double u2 = (double(w[2 * h + 1]) + 0.5) * (1.0 / 4294967296.0);
+            const double r = sqrt(-2.0 * log(u1));
+            double sn, cs;
+            sincos(2 * MCSIM_PI * u2, &sn, &cs);
+            if (4 * j + 2 * h < per_step) zn[size_t(t) * per_step + 4 * j + 2 * h] = r * cs;
+            if (4 * j + 2 * h + 1 < per_step) zn[size_t(t) * per_step + 4 * j + 2 * h + 1] = r * sn;
+        }
+    }
+    __syncwarp();
+    const double* tr = a.trajectories + (a.per_member ? size_t(b) * 3 * T : 0);
+    const double* od = a.odometry + (a.per_member ? size_t(b) * 3 * (T - 1) : 0);
+    // initial mixture: K copies of N(x*_0, Sigma_0), weights 1/K (GM_Model::initModel, GM_Model.h:57-77)
+    for (int q = threadIdx.x; q < a.K * GMM_COMP; q += 32) {
+        const int k = q / GMM_COMP, f = q - k * GMM_COMP;
+        a.comps[(size_t(b) * MCSIM_MAX_GAUSSIANS + k) * GMM_COMP + f] =
+            f == 0 ? 1.0 / a.K : (f < 4 ? tr[(f - 1) * T] : (f < 13 ? a.cov0[f - 4] : a.chol0[f - 13]));
+    }
+    if (threadIdx.x != 0) return;
+    NoiseModel<double> nm;
+    for (int i = 0; i < 4; ++i) nm.alpha[i] = a.alphas[i];
+    nm.Q = a.Q;
+    nm.L = L;
+    for (int l = 0; l < L; ++l) { nm.lx[l] = a.lx[l]; nm.ly[l] = a.ly[l]; }
+    double mu[3] = {tr[0], tr[T], tr[2 * T]}, S[9], real[3] = {tr[0], tr[T], tr[2 * T]};
+    for (int i = 0; i < 9; ++i) S[i] = a.cov0[i];
+    const double sq = sqrt(nm.Q);
+    for (int t = 0; t < T - 1; ++t) {
+        const double* z = zn + size_t(t) * per_step;
+        GmmStepTable& st = a.steps[size_t(b) * TS + t];
+        const double ustar[3] = {od[t], od[(T - 1) + t], od[2 * (T - 1) + t]};
+        const double xs[3] = {tr[t], tr[T + t], tr[2 * T + t]};
+        const double xg[3] = {tr[t + 1], tr[T + t + 1], tr[2 * T + t + 1]};
+        double M[3], u[3], pmu[3], pS[9], un[3], nxt[3], zobs[MCSIM_MAX_LANDMARKS];
+        motion_noise(nm, ustar, M);
+        applied_control(xs, mu, xg, ustar, u);
+        ekf_predict(mu, S, u, M, pmu, pS);
+        sample_odometry(nm, u, z, un);
+        predict_pose(real, un, nxt);
+        for (int k = 0; k < 3; ++k) real[k] = nxt[k];
+        for (int l = 0; l < L; ++l) zobs[l] = range_to(nm, real, l) + z[3 + l] * sq;
+        ekf_update(nm, pmu, pS, zobs, L);
+        for (int k = 0; k < 3; ++k) { mu[k] = pmu[k]; st.u[k] = u[k]; st.M[k] = M[k]; }
+        for (int k = 0; k < 9; ++k) S[k] = pS[k];
+        for (int l = 0; l < L; ++l) st.z[l] = zobs[l];
+    }
+}
 #endif

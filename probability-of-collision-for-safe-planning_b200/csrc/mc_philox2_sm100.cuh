@@ -161,22 +161,7 @@ __device__ __forceinline__ void pair_test2(const HullPose2& h, const float4 lo4,
     if ((fabsf(hi(drx)) <= hi(r0)) & (fabsf(hi(dry)) <= hi(r1)) & (fabsf(hi(dbx)) <= hi(r2)) & (fabsf(hi(dby)) <= hi(r3))) hit1 = true;
 }
 
-// ---- exact broad phase ----------------------------------------------------------------------------
-// Host side (mcsim_cuda_mc_prepare) lists, per waypoint t and hull h, the pairs whose box footprint lies within
-// reach_h + m of the nominal position x*_t, sorted by the smallest such m, and how many of them are needed for
-// m = MC_CULL_M0 * 2^k, k < MC_CULL_LEVELS.  A hull whose centre pose is within m of x*_t cannot touch any
-// other box (every hull point is within reach_h of the pose), so a warp whose 64 rollouts are all within
-// m_k of x*_t tests the first cnt[t][h][k] listed pairs; a warp with a rollout further out than the last
-// level (or a list longer than MC_CULL_CAP) tests every live pair.  Hit flags and counts are identical to
-// the exhaustive test's (tests/test_mc_gpu.py); executed pair tests are counted.
-// Table (32-bit words): cnt[T][n_hulls][MC_CULL_LEVELS] bytes (255 = list too long), padded to 4 bytes,
-// then idx[T][n_hulls][MC_CULL_CAP][2] 16-bit offsets into the orientation-grouped table: the pair's record
-// and its class header -- the listed pairs go through the SAME arithmetic as the exhaustive loop (class_frame2 +
-// class_pair_test2), which is what makes the two modes bit-identical at poses within rounding of contact.
-#define MC_CULL_LEVELS 4
-#define MC_CULL_CAP 16
-#define MC_CULL_M0 0.1f
-#define MC_CULL_OVERFLOW 255
+// (exact broad phase: table layout, levels and the exactness argument are in sat_device.cuh)
 
 // prediction (:413-431) on a packed pose
 __device__ __forceinline__ void move2(f2 p[3], const f2 u[3]) {
@@ -358,7 +343,7 @@ __global__ void __launch_bounds__(128, MC_P2_CTAS_PER_SM) mc_philox2_kernel(cons
                 const f2 d2 = fma2(ex, ex, mul2(ey, ey));
                 const unsigned u0 = valid0 ? __float_as_uint(lo(d2)) : 0u, u1 = valid1 ? __float_as_uint(hi(d2)) : 0u;
                 const float dm = __uint_as_float(__reduce_max_sync(0xffffffffu, u0 > u1 ? u0 : u1));  // NaN orders above every finite value
-                lev = dm <= MC_CULL_M0 * MC_CULL_M0 ? 0 : (dm <= 4.f * MC_CULL_M0 * MC_CULL_M0 ? 1 : (dm <= 16.f * MC_CULL_M0 * MC_CULL_M0 ? 2 : (dm <= 64.f * MC_CULL_M0 * MC_CULL_M0 ? 3 : MC_CULL_LEVELS)));
+                lev = cull_level(dm);
                 if (lev < MC_CULL_LEVELS && s_ccnt[t * nh * MC_CULL_LEVELS + lev] == MC_CULL_OVERFLOW) lev = MC_CULL_LEVELS;
             }
             if (lev < MC_CULL_LEVELS) {

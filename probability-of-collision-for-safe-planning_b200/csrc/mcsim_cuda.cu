@@ -12,6 +12,7 @@
 #include <atomic>
 #include <thread>
 #include <algorithm>
+#include <chrono>
 #include <utility>
 #include <vector>
 
@@ -76,6 +77,9 @@ struct mcsim_cuda_ctx {
     std::vector<unsigned> h_pair_sat2;  // per pair: record offset | class header offset << 16 in the grouped table
     double h_reach[MCSIM_MAX_HULLS] = {0};
     DevBuf mc_cull;
+    int gmm_cull_words = 0;  // words of ONE plan's lists
+    DevBuf gmm_plans, gmm_robot_normals;      // batch: the plan(s) and the scratch normals of the device robot threads
+    DevBuf gmm_cull, gmm_nominal, gmm_tests;  // GMM Philox mode: the plan's (or every batch member's) lists
     int mc_cull_words = 0;           // 0: no lists for the prepared plan (every live pair is tested)
     // GMM state
     DevBuf gmm_comps, gmm_stats, gmm_hist, gmm_counts, gmm_normals, gmm_steps, gmm_prob, gmm_pre, gmm_post, gmm_trunc, gmm_nout, gmm_deg;
@@ -131,7 +135,7 @@ extern "C" void mcsim_cuda_destroy(mcsim_cuda_ctx* c) {
     cudaStreamSynchronize(c->stream);
     c->plan.release(); c->z0.release(); c->counters.release(); c->counts.release();
     c->poses.release(); c->clearance.release();
-    c->hulls_d.release(); c->pairs_d.release(); c->sat2.release(); c->mc_cull.release();
+    c->hulls_d.release(); c->pairs_d.release(); c->sat2.release(); c->mc_cull.release(); c->gmm_cull.release(); c->gmm_nominal.release(); c->gmm_tests.release(); c->gmm_plans.release(); c->gmm_robot_normals.release();
     c->pairs_f.release(); c->sc_plans.release(); c->sc_hits.release(); c->sc_counters.release();
     c->em_x.release(); c->em_comps.release(); c->em_hefts.release(); c->em_means.release(); c->em_fcovs.release();
     c->em_stats.release(); c->em_old.release(); c->em_done.release(); c->em_iters.release(); c->em_trace.release();
@@ -623,17 +627,70 @@ static void gmm_fill_launch(mcsim_cuda_ctx* c, GmmLaunch& a, int K, int T, int L
     a.sat2 = (const float4*)c->sat2.p;
 }
 
+// GMM Philox mode: candidate lists + list centres of n_plans plans (plan b = trajectories + b * 3 * T), uploaded
+// to gmm_cull / gmm_nominal; the executed-pair-test counter is zeroed.  Returns the words per plan (0: no lists).
+static int gmm_upload_cull(mcsim_cuda_ctx* c, GmmLaunch& a, const double* trajectories, int n_plans, int T, bool exhaustive) {
+    CK(c->gmm_tests.reserve(sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(c->gmm_tests.p, 0, sizeof(unsigned long long), c->stream));
+    a.tests = (unsigned long long*)c->gmm_tests.p;
+    a.cull = nullptr;
+    a.cull_stride = 0;
+    c->gmm_cull_words = 0;
+    if (exhaustive || c->sat2_n >= 65536 || c->n_pairs == 0) return MCSIM_OK;
+    if (size_t(n_plans) * T * c->n_hulls * (MC_CULL_CAP + 1) > (size_t(64) << 20)) return MCSIM_OK;  // 256 MB of lists: go without
+    std::vector<unsigned> all, one;
+    std::vector<float2> nominal(size_t(n_plans) * T);
+    for (int b = 0; b < n_plans; ++b) {
+        const double* tr = trajectories + size_t(b) * 3 * T;
+        build_cull_lists(c, tr, T, one);
+        all.insert(all.end(), one.begin(), one.end());
+        for (int t = 0; t < T; ++t) nominal[size_t(b) * T + t] = make_float2(float(tr[t]), float(tr[T + t]));
+    }
+    CK(c->gmm_cull.reserve(all.size() * sizeof(unsigned)));
+    CK(c->gmm_nominal.reserve(nominal.size() * sizeof(float2)));
+    CK(cudaMemcpyAsync(c->gmm_cull.p, all.data(), all.size() * sizeof(unsigned), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->gmm_nominal.p, nominal.data(), nominal.size() * sizeof(float2), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));  // stack vectors
+    c->h2d_bytes += all.size() * sizeof(unsigned) + nominal.size() * sizeof(float2);
+    a.cull = (const unsigned*)c->gmm_cull.p;
+    a.nominal = (const float2*)c->gmm_nominal.p;
+    a.cull_stride = n_plans > 1 ? int(one.size()) : 0;
+    c->gmm_cull_words = int(one.size());
+    return MCSIM_OK;
+}
+
 // the three launches of one waypoint
 static int gmm_launch_waypoint(mcsim_cuda_ctx* c, const GmmLaunch& a, int mode) {
-    // small sample counts (the reference's N = 10^4): 64-thread CTAs so that every SM gets work
-    const int block = a.n < (unsigned long long)c->n_sm * 256 ? 64 : 256;
-    unsigned long long want = (a.n + block - 1) / block;
-    const unsigned long long cap = (unsigned long long)c->n_sm * 8;
     const unsigned B = a.B > 1 ? unsigned(a.B) : 1u;
-    const dim3 grid(unsigned(want < cap ? (want ? want : 1) : cap), B);
+    int block;
+    unsigned gx;
+    if (B == 1) {
+        // one run, small sample counts (the reference's N = 10^4): 64-thread CTAs so that every SM gets work
+        block = a.n < (unsigned long long)c->n_sm * 256 ? 64 : 256;
+        const unsigned long long want = (a.n + block - 1) / block, cap = (unsigned long long)c->n_sm * 8;
+        gx = unsigned(want < cap ? (want ? want : 1) : cap);
+    } else {
+        // a batch fills the GPU by its members: few 256-thread CTAs per member, many samples per thread (the CTA
+        // prologue / epilogue and the warp reductions are per CTA and per component change, not per sample);
+        // two waves of resident CTAs in total, the count per member chosen for the fewest idle lanes in the last pass
+        block = 256;
+        const unsigned long long want = (a.n + block - 1) / block;
+        unsigned g0 = unsigned((2ull * c->n_sm * 8 + B - 1) / B);
+        if (g0 < 1) g0 = 1;
+        unsigned best = g0;
+        unsigned long long best_waste = ~0ull;
+        for (unsigned cand = g0; cand <= 2 * g0; ++cand) {
+            const unsigned long long per = (unsigned long long)cand * block, passes = (a.n + per - 1) / per;
+            const unsigned long long waste = passes * per - a.n;
+            if (waste < best_waste) { best_waste = waste; best = cand; }
+        }
+        gx = unsigned(best < want ? best : (want ? want : 1));
+    }
+    const dim3 grid(gx, B);
+    if (mode == MCSIM_MODE_PHILOX && a.n > (1ull << 31)) return fail(MCSIM_ERR_ARG, "gmm: Philox mode takes at most 2^31 samples per waypoint");
     if (mode == MCSIM_MODE_PHILOX) {
         gmm_count_kernel<<<grid, block, 0, c->stream>>>(a);
-        gmm_sample_kernel<MCSIM_MODE_PHILOX><<<grid, block, 0, c->stream>>>(a);
+        gmm_sample_philox_kernel<<<grid, block, 0, c->stream>>>(a);
         c->launches += 2;
     } else {
         gmm_sample_kernel<MCSIM_MODE_REPLAY><<<grid, block, 0, c->stream>>>(a);
@@ -729,6 +786,7 @@ extern "C" int mcsim_cuda_gmm_run(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, 
     a.rec_post = (double*)c->gmm_post.p;
     a.do_ekf = 1;
     a.counts_replay = (const int*)c->gmm_counts.p;
+    if (mode == MCSIM_MODE_PHILOX) { rc = gmm_upload_cull(c, a, mc->trajectory, 1, T, mc->exhaustive != 0); if (rc) return rc; }
     CK(cudaEventRecord(c->ev0, c->stream));
     for (int t = 0; t < T; ++t) {
         a.t = t;
@@ -742,6 +800,8 @@ extern "C" int mcsim_cuda_gmm_run(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, 
     CK(cudaMemcpyAsync(prob.data(), c->gmm_prob.p, sizeof(double) * T, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaMemcpyAsync(&deg, c->gmm_deg.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     c->d2h_bytes += sizeof(double) * T + sizeof(int);
+    unsigned long long tests = 0;
+    if (a.tests) { CK(cudaMemcpyAsync(&tests, a.tests, sizeof(tests), cudaMemcpyDeviceToHost, c->stream)); c->d2h_bytes += sizeof(tests); }
     if (r->gmm_pre) { CK(cudaMemcpyAsync(r->gmm_pre, c->gmm_pre.p, sizeof(double) * size_t(T) * K * GMM_REC, cudaMemcpyDeviceToHost, c->stream)); c->d2h_bytes += sizeof(double) * size_t(T) * K * GMM_REC; }
     if (r->gmm_post) { CK(cudaMemcpyAsync(r->gmm_post, c->gmm_post.p, sizeof(double) * K * GMM_REC, cudaMemcpyDeviceToHost, c->stream)); c->d2h_bytes += sizeof(double) * K * GMM_REC; }
     CK(cudaStreamSynchronize(c->stream));
@@ -751,6 +811,7 @@ extern "C" int mcsim_cuda_gmm_run(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, 
     for (int t = 0; t < T; ++t) free_all *= (1.0 - prob[t]);
     r->P = 1.0 - free_all;
     r->degenerate = deg;
+    r->pair_tests = tests;
     if (r->probabilities) memcpy(r->probabilities, prob.data(), sizeof(double) * T);
     return MCSIM_OK;
 }
@@ -1106,72 +1167,84 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
     if (L < 0 || L > MCSIM_MAX_LANDMARKS || (L && !mc->landmarks)) return fail(MCSIM_ERR_ARG, "gmm_run_batch: bad landmarks");
     if ((g->trajectories == nullptr) != (g->odometry == nullptr)) return fail(MCSIM_ERR_ARG, "gmm_run_batch: trajectories and odometry go together");
     CK(cudaSetDevice(c->device));
+    const bool trace = getenv("MCSIM_TRACE") != nullptr;
+    auto now = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t_0 = now();
     const int per_step = 3 + L, TS = T > 1 ? T - 1 : 1;
-    std::vector<GmmStepTable> steps(size_t(B) * TS);
-    std::vector<double> comps(size_t(B) * MCSIM_MAX_GAUSSIANS * GMM_COMP, 0.0);
-    mcsim_math::NoiseModel<double> nmd;
-    for (int k = 0; k < 4; ++k) nmd.alpha[k] = mc->alphas[k];
     double Lo[6];
     if (!gmm_chol3(mc->cov0, Lo)) return fail(MCSIM_ERR_ARG, "gmm_run_batch: initial covariance is not positive definite");
-    // the members' shared real-robot threads (host, FP64, O(T) each) are independent: spread them over host threads
-    std::atomic<int> next(0), bad(0);
-    auto work = [&]() {
-        std::vector<double> hn, applied(size_t(3) * TS), obs(size_t(TS) * (L ? L : 1));
-        for (int b = next.fetch_add(1); b < B; b = next.fetch_add(1)) {
-            mcsim_mc_params pb = *mc;
-            if (g->trajectories) { pb.trajectory = g->trajectories + size_t(b) * 3 * T; pb.odometry = g->odometry + size_t(b) * 3 * (T - 1); }
-            host_normals(mc->seed, unsigned(g->stream0 + b), T, per_step, hn);  // its own Philox subsequence
-            if (T > 1 && mcsim_host_thread(&pb, hn.data(), hn.size(), nullptr, applied.data(), nullptr, nullptr, nullptr, obs.data())) { bad = 1; return; }
-            for (int t = 0; t < T - 1; ++t) {
-                GmmStepTable& s = steps[size_t(b) * TS + t];
-                double us[3];
-                for (int k = 0; k < 3; ++k) { us[k] = pb.odometry[k * (T - 1) + t]; s.u[k] = applied[k * (T - 1) + t]; }
-                mcsim_math::motion_noise(nmd, us, s.M);
-                for (int l = 0; l < L; ++l) s.z[l] = obs[size_t(t) * L + l];
-            }
-            for (int k = 0; k < K; ++k) {
-                double* cp = &comps[(size_t(b) * MCSIM_MAX_GAUSSIANS + k) * GMM_COMP];
-                cp[0] = 1.0 / K;
-                for (int i = 0; i < 3; ++i) cp[1 + i] = pb.trajectory[i * T];
-                for (int i = 0; i < 9; ++i) cp[4 + i] = mc->cov0[i];
-                for (int i = 0; i < 6; ++i) cp[13 + i] = Lo[i];
-            }
-        }
-    };
-    {
-        unsigned nt = std::thread::hardware_concurrency();
-        nt = nt < 1 ? 1 : (nt > 16 ? 16 : nt);
-        if (unsigned(B) < 4 * nt) nt = 1;
-        std::vector<std::thread> pool;
-        for (unsigned i = 1; i < nt; ++i) pool.emplace_back(work);
-        work();
-        for (auto& th : pool) th.join();
-    }
-    if (bad) return fail(MCSIM_ERR_ARG, "gmm_run_batch: host thread of a member failed");
     int rc = gmm_reserve(c, T, K, B);
     if (rc) return rc;
-    CK(cudaMemcpyAsync(c->gmm_comps.p, comps.data(), sizeof(double) * comps.size(), cudaMemcpyHostToDevice, c->stream));
-    CK(cudaMemcpyAsync(c->gmm_steps.p, steps.data(), sizeof(GmmStepTable) * steps.size(), cudaMemcpyHostToDevice, c->stream));
-    c->h2d_bytes = sizeof(double) * comps.size() + sizeof(GmmStepTable) * steps.size();
+    // ---- the members' shared real-robot threads (FP64, O(T) each, independent) run on the device, one warp per
+    // member (gmm_robot_thread_kernel): only the plan(s) cross PCIe, the step tables and initial mixtures are
+    // written where the run reads them
+    const size_t n_plans = g->trajectories ? size_t(B) : 1, tr_n = size_t(3) * T, od_n = size_t(3) * (T > 1 ? T - 1 : 0);
+    CK(c->gmm_plans.reserve(sizeof(double) * n_plans * (tr_n + od_n + 1)));
+    CK(c->gmm_robot_normals.reserve(sizeof(double) * size_t(B) * TS * per_step));
+    double* d_tr = (double*)c->gmm_plans.p;
+    double* d_od = d_tr + n_plans * tr_n;
+    CK(cudaMemcpyAsync(d_tr, g->trajectories ? g->trajectories : mc->trajectory, sizeof(double) * n_plans * tr_n, cudaMemcpyHostToDevice, c->stream));
+    if (od_n) CK(cudaMemcpyAsync(d_od, g->odometry ? g->odometry : mc->odometry, sizeof(double) * n_plans * od_n, cudaMemcpyHostToDevice, c->stream));
+    c->h2d_bytes = sizeof(double) * n_plans * (tr_n + od_n);
+    {
+        RobotThreadLaunch rt;
+        memset(&rt, 0, sizeof(rt));
+        rt.B = B; rt.T = T; rt.L = L; rt.K = K;
+        rt.k0 = unsigned(mc->seed); rt.k1 = unsigned(mc->seed >> 32); rt.stream0 = unsigned(g->stream0);
+        for (int k = 0; k < 4; ++k) rt.alphas[k] = mc->alphas[k];
+        rt.Q = mc->Q;
+        for (int k = 0; k < 9; ++k) rt.cov0[k] = mc->cov0[k];
+        for (int k = 0; k < 6; ++k) rt.chol0[k] = Lo[k];
+        for (int l = 0; l < L; ++l) { rt.lx[l] = mc->landmarks[l]; rt.ly[l] = mc->landmarks[L + l]; }
+        rt.trajectories = d_tr; rt.odometry = d_od; rt.per_member = g->trajectories ? 1 : 0;
+        rt.normals = (double*)c->gmm_robot_normals.p;
+        rt.steps = (GmmStepTable*)c->gmm_steps.p;
+        rt.comps = (double*)c->gmm_comps.p;
+        gmm_robot_thread_kernel<<<B, 32, 0, c->stream>>>(rt);
+        ++c->launches;
+        CK(cudaGetLastError());
+    }
+    const double t_1 = now();
     GmmLaunch a;
     gmm_fill_launch(c, a, K, T, L, N, mc->seed, unsigned(g->stream0));
     a.Q = mc->Q;
     for (int l = 0; l < L; ++l) { a.lx[l] = mc->landmarks[l]; a.ly[l] = mc->landmarks[L + l]; }
     a.do_ekf = 1;
     a.B = B;
+    rc = g->trajectories ? gmm_upload_cull(c, a, g->trajectories, B, T, mc->exhaustive != 0)
+                         : gmm_upload_cull(c, a, mc->trajectory, 1, T, mc->exhaustive != 0);
+    if (rc) return rc;
+    const double t_2 = now();
+    if (N > (1ull << 31)) return fail(MCSIM_ERR_ARG, "gmm_run_batch: at most 2^31 samples per waypoint");
+    // enough members to fill the GPU by themselves: one CTA per member for the whole run (gmm_member_run_kernel);
+    // fewer: the per-waypoint kernels, several CTAs per member
+    const size_t fused_smem = sizeof(float4) * size_t(c->sat2_n) + sizeof(unsigned) * size_t(c->gmm_cull_words);
+    const bool fused = B >= 64 && fused_smem <= 64 * 1024;
     CK(cudaEventRecord(c->ev0, c->stream));
-    for (int t = 0; t < T; ++t) {
-        a.t = t;
-        rc = gmm_launch_waypoint(c, a, MCSIM_MODE_PHILOX);
-        if (rc) return rc;
+    if (fused) {
+        if (fused_smem > 40 * 1024) CK(cudaFuncSetAttribute((const void*)gmm_member_run_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(fused_smem)));
+        gmm_member_run_kernel<<<B, 256, fused_smem, c->stream>>>(a, c->sat2_n, c->gmm_cull_words);
+        ++c->launches;
+        CK(cudaGetLastError());
+    } else {
+        for (int t = 0; t < T; ++t) {
+            a.t = t;
+            rc = gmm_launch_waypoint(c, a, MCSIM_MODE_PHILOX);
+            if (rc) return rc;
+        }
     }
     CK(cudaEventRecord(c->ev1, c->stream));
+    const double t_3 = now();
     std::vector<double> prob(size_t(B) * T);
     std::vector<int> deg(B);
     CK(cudaMemcpyAsync(prob.data(), c->gmm_prob.p, sizeof(double) * prob.size(), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaMemcpyAsync(deg.data(), c->gmm_deg.p, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
+    unsigned long long tests = 0;
+    CK(cudaMemcpyAsync(&tests, a.tests, sizeof(tests), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
-    c->d2h_bytes = sizeof(double) * prob.size() + sizeof(int) * B;
+    if (trace) fprintf(stderr, "[mcsim] gmm_run_batch B=%d: plans + robot-thread launch %.3f ms, lists %.3f ms, launch %.3f ms, wait + download %.3f ms\n", B, t_1 - t_0, t_2 - t_1, t_3 - t_2, now() - t_3);
+    r->pair_tests = tests;
+    c->d2h_bytes = sizeof(double) * prob.size() + sizeof(int) * B + sizeof(tests);
     CK(cudaEventElapsedTime(&r->kernel_ms, c->ev0, c->ev1));
     r->degenerate = 0;
     for (int b = 0; b < B; ++b) {

@@ -102,40 +102,100 @@ __device__ __forceinline__ bool robot_hits(float x, float y, float ct, float st,
 // mod 90 degrees the relative rotation, the hull centre in the class frame and the hull's radii on the class
 // axes are computed once, which leaves 12 FP32 operations + 4 compares per pair instead of 20 + 4.
 // tab: global (read through the read-only path; every thread reads the same addresses) or shared memory.
+struct HullFrame1 { float hcx, hcy, ch, sh, nph, nqh, hhx, hhy; };
+struct ClassFrame1 { float c, s, gx, gy, rbx, rby; };
+__device__ __forceinline__ HullFrame1 hull_frame1(const HullRec& hr, float x, float y, float ct, float st) {
+    HullFrame1 h;
+    h.hcx = fmaf(ct, hr.ox, fmaf(-st, hr.oy, x));
+    h.hcy = fmaf(st, hr.ox, fmaf(ct, hr.oy, y));
+    h.ch = fmaf(ct, hr.cp, -st * hr.sp);
+    h.sh = fmaf(st, hr.cp, ct * hr.sp);
+    h.nph = -fmaf(h.ch, h.hcx, h.sh * h.hcy);
+    h.nqh = -fmaf(h.ch, h.hcy, -h.sh * h.hcx);
+    h.hhx = hr.hx;
+    h.hhy = hr.hy;
+    return h;
+}
+__device__ __forceinline__ ClassFrame1 class_frame1(const HullFrame1& h, const float4 head) {
+    ClassFrame1 k;
+    k.c = fabsf(fmaf(h.ch, head.x, h.sh * head.y));
+    k.s = fabsf(fmaf(h.sh, head.x, -h.ch * head.y));
+    k.gx = fmaf(h.hcx, head.x, h.hcy * head.y);
+    k.gy = fmaf(h.hcy, head.x, -h.hcx * head.y);
+    k.rbx = fmaf(k.c, h.hhx, k.s * h.hhy);
+    k.rby = fmaf(k.s, h.hhx, k.c * h.hhy);
+    return k;
+}
+__device__ __forceinline__ bool class_pair_hit1(const HullFrame1& h, const ClassFrame1& k, const float4 A, const float2 B) {
+    const float drx = fmaf(h.ch, A.x, fmaf(h.sh, A.y, h.nph));
+    const float dry = fmaf(h.ch, A.y, fmaf(-h.sh, A.x, h.nqh));
+    const float r0 = fmaf(k.c, A.z, fmaf(k.s, A.w, h.hhx));
+    const float r1 = fmaf(k.s, A.z, fmaf(k.c, A.w, h.hhy));
+    return (fabsf(drx) <= r0) & (fabsf(dry) <= r1) & (fabsf(k.gx + B.x) <= k.rbx + A.z) & (fabsf(k.gy + B.y) <= k.rby + A.w);
+}
+
+// SMEM = true: tab points into shared memory (plain loads); false: global memory through the read-only path
+template <bool SMEM>
+__device__ __forceinline__ float4 tab_ld4(const float4* p) { return SMEM ? *p : __ldg(p); }
+template <bool SMEM>
+__device__ __forceinline__ float2 tab_ld2(const float4* p) { return SMEM ? *reinterpret_cast<const float2*>(p) : __ldg(reinterpret_cast<const float2*>(p)); }
+
+template <bool SMEM = false>
 __device__ __forceinline__ bool robot_hits_grouped(const float4* __restrict__ tab, float x, float y, float ct, float st) {
     bool hit = false;
     for (int hI = 0; hI < c_scene.n_hulls; ++hI) {
         const HullRec& hr = c_scene.hulls[hI];
-        const float hcx = fmaf(ct, hr.ox, fmaf(-st, hr.oy, x));
-        const float hcy = fmaf(st, hr.ox, fmaf(ct, hr.oy, y));
-        const float ch = fmaf(ct, hr.cp, -st * hr.sp);
-        const float sh = fmaf(st, hr.cp, ct * hr.sp);
-        const float nph = -fmaf(ch, hcx, sh * hcy);
-        const float nqh = -fmaf(ch, hcy, -sh * hcx);
-        const float hhx = hr.hx, hhy = hr.hy;
+        const HullFrame1 h = hull_frame1(hr, x, y, ct, st);
         const float4* g = tab + hr.g_first;
         for (int gi = 0; gi < hr.n_groups; ++gi) {
-            const float4 head = __ldg(g);
+            const float4 head = tab_ld4<SMEM>(g);
             const int cnt = __float_as_int(head.z);
-            const float c = fabsf(fmaf(ch, head.x, sh * head.y));
-            const float s = fabsf(fmaf(sh, head.x, -ch * head.y));
-            const float gx = fmaf(hcx, head.x, hcy * head.y);
-            const float gy = fmaf(hcy, head.x, -hcx * head.y);
-            const float rbx = fmaf(c, hhx, s * hhy);
-            const float rby = fmaf(s, hhx, c * hhy);
+            const ClassFrame1 k = class_frame1(h, head);
             ++g;
 #pragma unroll 4
-            for (int b = 0; b < cnt; ++b) {
-                const float4 A = __ldg(g + 2 * b);                                        // cx, cy, hx, hy
-                const float2 B = __ldg(reinterpret_cast<const float2*>(g + 2 * b + 1));   // -p, -q
-                const float drx = fmaf(ch, A.x, fmaf(sh, A.y, nph));
-                const float dry = fmaf(ch, A.y, fmaf(-sh, A.x, nqh));
-                const float r0 = fmaf(c, A.z, fmaf(s, A.w, hhx));
-                const float r1 = fmaf(s, A.z, fmaf(c, A.w, hhy));
-                if ((fabsf(drx) <= r0) & (fabsf(dry) <= r1) & (fabsf(gx + B.x) <= rbx + A.z) & (fabsf(gy + B.y) <= rby + A.w)) hit = true;
-            }
+            for (int b = 0; b < cnt; ++b)
+                if (class_pair_hit1(h, k, tab_ld4<SMEM>(g + 2 * b), tab_ld2<SMEM>(g + 2 * b + 1))) hit = true;
             g += 2 * cnt;
         }
+    }
+    return hit;
+}
+
+// ---- exact broad phase (candidate lists built on the host per plan waypoint: mcsim_cuda.cu build_cull_lists) -------
+// Per waypoint t and hull h the pairs whose box footprint lies within reach_h + m of the nominal position x*_t,
+// sorted by the smallest such m, and how many of them are needed for m = MC_CULL_M0 * 2^k, k < MC_CULL_LEVELS.
+// A hull whose robot pose is within m of x*_t cannot touch any other box (every hull point is within reach_h of
+// the pose), so a warp whose poses are all within m_k of x*_t tests the first cnt[t][h][k] listed pairs; a warp
+// with a pose further out than the last level (or a list longer than MC_CULL_CAP) tests every live pair.  The
+// listed pairs go through the SAME arithmetic as the exhaustive loop (class frame + pair test on the grouped
+// table), so flags and counts are bit-identical to the exhaustive test's; executed pair tests are counted.
+// Table (32-bit words): cnt[T][n_hulls][MC_CULL_LEVELS] bytes (255 = list too long), padded to 4 bytes, then
+// idx[T][n_hulls][MC_CULL_CAP] x (16-bit pair record offset, 16-bit class header offset) into the grouped table.
+#define MC_CULL_LEVELS 4
+#define MC_CULL_CAP 16
+#define MC_CULL_M0 0.1f
+#define MC_CULL_OVERFLOW 255
+
+// level of a squared deviation (NaN -> exhaustive)
+__device__ __forceinline__ int cull_level(float d2max) {
+    return d2max <= MC_CULL_M0 * MC_CULL_M0 ? 0 : (d2max <= 4.f * MC_CULL_M0 * MC_CULL_M0 ? 1 : (d2max <= 16.f * MC_CULL_M0 * MC_CULL_M0 ? 2 : (d2max <= 64.f * MC_CULL_M0 * MC_CULL_M0 ? 3 : MC_CULL_LEVELS)));
+}
+
+// listed pairs of waypoint t at level lev; cnt / idx point at the waypoint's slices ([n_hulls][LEVELS], [n_hulls][CAP])
+template <bool SMEM = false>
+__device__ __forceinline__ bool robot_hits_listed(const float4* __restrict__ tab, const unsigned char* cnt, const ushort2* idx, int lev,
+                                                  float x, float y, float ct, float st, unsigned& tested) {
+    bool hit = false;
+    for (int hI = 0; hI < c_scene.n_hulls; ++hI) {
+        const int n = cnt[hI * MC_CULL_LEVELS + lev];
+        if (n == 0) continue;
+        const HullFrame1 h = hull_frame1(c_scene.hulls[hI], x, y, ct, st);
+        for (int k = 0; k < n; ++k) {
+            const ushort2 o = idx[hI * MC_CULL_CAP + k];
+            const ClassFrame1 cf = class_frame1(h, tab_ld4<SMEM>(tab + o.y));
+            if (class_pair_hit1(h, cf, tab_ld4<SMEM>(tab + o.x), tab_ld2<SMEM>(tab + o.x + 1))) hit = true;
+        }
+        tested += n;
     }
     return hit;
 }

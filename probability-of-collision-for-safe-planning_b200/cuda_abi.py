@@ -61,7 +61,7 @@ class GmmBatchParams(C.Structure):
 
 
 class GmmBatchResult(C.Structure):
-    _fields_ = [("P", _dp), ("probabilities", _dp), ("degenerate", C.c_int), ("kernel_ms", C.c_float)]
+    _fields_ = [("P", _dp), ("probabilities", _dp), ("degenerate", C.c_int), ("kernel_ms", C.c_float), ("pair_tests", C.c_uint64)]
 
 
 class ScoreParams(C.Structure):
@@ -107,7 +107,7 @@ class GmmRunParams(C.Structure):
 class GmmRunResult(C.Structure):
     _fields_ = [
         ("P", C.c_double), ("probabilities", _dp), ("gmm_pre", _dp), ("gmm_post", _dp),
-        ("degenerate", C.c_int), ("kernel_ms", C.c_float),
+        ("degenerate", C.c_int), ("kernel_ms", C.c_float), ("pair_tests", C.c_uint64),
     ]
 
 
@@ -348,10 +348,10 @@ class Context:
         return int(a.value), int(b.value)
 
     def gmm_run(self, plan, K, n_samples, mode=MODE_PHILOX, seed=0x5AFEC0DE, stream_id=0, draws=None, counts=None,
-                record=False):
+                record=False, exhaustive=False):
         """runGMMEstimation of one plan (MCSimulator.h:354-358 -> the GMM branch of EKF_GaussProp).
         Replay mode: draws = the reference's normal stream of the run, counts[T, K] = multinomial counts."""
-        p, keep = make_mc_params(plan, mode=mode, seed=seed, rollout_offset=stream_id)
+        p, keep = make_mc_params(plan, mode=mode, seed=seed, rollout_offset=stream_id, exhaustive=exhaustive)
         T = int(p.T)
         g = GmmRunParams()
         g.K, g.n_samples = int(K), int(n_samples)
@@ -371,7 +371,7 @@ class Context:
             out["gmm_post"] = np.zeros((int(K), 13))
             r.gmm_pre, r.gmm_post = dptr(out["gmm_pre"]), dptr(out["gmm_post"])
         check(lib().mcsim_cuda_gmm_run(self._h, C.byref(p), C.byref(g), C.byref(r)))
-        out.update(P=float(r.P), degenerate=int(r.degenerate), kernel_ms=float(r.kernel_ms))
+        out.update(P=float(r.P), degenerate=int(r.degenerate), kernel_ms=float(r.kernel_ms), pair_tests=int(r.pair_tests))
         return out
 
     # ---- batched plan scoring (BASELINE config 4)
@@ -487,10 +487,11 @@ class Context:
         raw.__cuda_array_interface__ = dict(shape=(int(n.value),), typestr="<f8", version=2, data=(int(ptr), False))
         return torch.as_tensor(raw, device="cuda:%d" % self.device)
 
-    def gmm_run_batch(self, plan, K, n_samples, n_traj, trajectories=None, odometry=None, seed=0x5AFEC0DE, stream0=0):
+    def gmm_run_batch(self, plan, K, n_samples, n_traj, trajectories=None, odometry=None, seed=0x5AFEC0DE, stream0=0,
+                      exhaustive=False):
         """n_traj independent runGMMEstimation runs in the same launches (Philox mode); member b ==
         gmm_run(..., stream_id=stream0 + b) on plan b (trajectories [n_traj, 3, T]) or on `plan`."""
-        p, keep = make_mc_params(plan, mode=MODE_PHILOX, seed=seed)
+        p, keep = make_mc_params(plan, mode=MODE_PHILOX, seed=seed, exhaustive=exhaustive)
         T = int(p.T)
         g = GmmBatchParams()
         g.K, g.n_samples, g.n_traj, g.stream0 = int(K), int(n_samples), int(n_traj), int(stream0)
@@ -504,7 +505,7 @@ class Context:
         r = GmmBatchResult()
         r.P, r.probabilities = dptr(out["P"]), dptr(out["probabilities"])
         check(lib().mcsim_cuda_gmm_run_batch(self._h, C.byref(p), C.byref(g), C.byref(r)))
-        out.update(degenerate=int(r.degenerate), kernel_ms=float(r.kernel_ms))
+        out.update(degenerate=int(r.degenerate), kernel_ms=float(r.kernel_ms), pair_tests=int(r.pair_tests))
         return out
 
     def gmm_truncate(self, weights, means, covs, n_samples, mode=MODE_PHILOX, counts=None, normals=None,

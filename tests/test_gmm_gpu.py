@@ -132,3 +132,60 @@ def test_gmm_batch_members_equal_single_runs(ctx, plan, scenes):
     two = ctx.gmm_run_batch(plan, 3, 5000, 2, trajectories=tr, odometry=od, stream0=11)
     np.testing.assert_allclose(two["P"][0], batch["P"][0], rtol=1e-9)
     assert two["P"][1] != two["P"][0]
+
+
+def test_gmm_broad_phase_is_exact(ctx, plan, scenes):
+    """Philox-mode GMM sampling with the candidate lists (default) against testing every live pair: the collision
+    flag of every sample is the same (same SAT arithmetic on the listed pairs), so the per-waypoint colliding
+    fractions -- ratios of integer counts -- and P are identical, the refitted mixtures agree to the order of the
+    FP64 atomics.  Single runs on both scenes, and a batch whose members have different plans
+    (their own lists)."""
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    T = plan["trajectory"].shape[1]
+    for name in ("pr2test2", "pr2custom"):
+        ctx.set_scene(scenes[name]["boxes"], scenes[name]["hulls"])
+        a = ctx.gmm_run(plan, 3, 20000, mode=abi.MODE_PHILOX, stream_id=5, record=True)
+        b = ctx.gmm_run(plan, 3, 20000, mode=abi.MODE_PHILOX, stream_id=5, record=True, exhaustive=True)
+        np.testing.assert_array_equal(a["probabilities"], b["probabilities"])
+        np.testing.assert_allclose(a["gmm_post"], b["gmm_post"], rtol=1e-9, atol=1e-15)   # FP64 atomics: order varies
+        assert abs(a["P"] - b["P"]) <= 1e-12
+        assert b["pair_tests"] == 20000 * T * ctx.n_pairs
+        print("%s: P = %.5f, pair tests per sample %.2f (every pair: %d)" % (name, a["P"], a["pair_tests"] / (20000 * T), ctx.n_pairs))
+        assert a["pair_tests"] < 0.3 * b["pair_tests"]
+    tr = np.stack([plan["trajectory"], plan["trajectory"] + np.array([[0.05], [0.0], [0.0]]), plan["trajectory"] + np.array([[0.0], [-0.08], [0.0]])])
+    od = np.stack([plan["odometry"]] * 3)
+    a = ctx.gmm_run_batch(plan, 3, 5000, 3, trajectories=tr, odometry=od, stream0=11)
+    b = ctx.gmm_run_batch(plan, 3, 5000, 3, trajectories=tr, odometry=od, stream0=11, exhaustive=True)
+    np.testing.assert_array_equal(a["probabilities"], b["probabilities"])
+    assert a["pair_tests"] < b["pair_tests"] == 3 * 5000 * T * ctx.n_pairs
+
+
+def test_gmm_batch_fused_kernel_members_equal_single_runs(ctx, plan, scenes):
+    """Batches of >= 64 members run as one CTA per member for the whole plan (gmm_member_run_kernel): a member must
+    still equal the single run on its Philox subsequence (same draws, same refit code; FP64 sums in another order),
+    with and without the broad phase, and with members on different plans."""
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    T = plan["trajectory"].shape[1]
+    ctx.set_scene(scenes["pr2test2"]["boxes"], scenes["pr2test2"]["hulls"])
+    B = 80
+    batch = ctx.gmm_run_batch(plan, 3, 5000, B, stream0=300)
+    every = ctx.gmm_run_batch(plan, 3, 5000, B, stream0=300, exhaustive=True)
+    np.testing.assert_array_equal(batch["probabilities"], every["probabilities"])
+    assert every["pair_tests"] == B * 5000 * T * ctx.n_pairs and batch["pair_tests"] < 0.3 * every["pair_tests"]
+    for b in (0, 1, 41, 79):
+        one = ctx.gmm_run(plan, 3, 5000, mode=abi.MODE_PHILOX, stream_id=300 + b)
+        np.testing.assert_allclose(batch["probabilities"][b], one["probabilities"], rtol=1e-9, atol=1e-12)
+        np.testing.assert_allclose(batch["P"][b], one["P"], rtol=1e-9)
+    shift = np.zeros((B, 3, 1))
+    shift[:, 0, 0] = np.linspace(-0.04, 0.04, B)
+    tr = plan["trajectory"][None] + shift
+    od = np.repeat(plan["odometry"][None], B, axis=0)
+    many = ctx.gmm_run_batch(plan, 2, 4000, B, trajectories=tr, odometry=od, stream0=7)
+    few = ctx.gmm_run_batch(plan, 2, 4000, 3, trajectories=tr[[0, 17, 79]], odometry=od[:3], stream0=7)
+    # members 17 and 79 of `many` use subsequences 24 and 86; re-run them alone through the per-waypoint kernels
+    np.testing.assert_allclose(many["P"][0], few["P"][0], rtol=1e-9)
+    for b in (17, 79):
+        alone = ctx.gmm_run_batch(plan, 2, 4000, 1, trajectories=tr[[b]], odometry=od[:1], stream0=7 + b)
+        np.testing.assert_allclose(many["probabilities"][b], alone["probabilities"][0], rtol=1e-9, atol=1e-12)
