@@ -27,6 +27,7 @@
 #include "estimator_math.h"
 #include "philox.h"
 #include "sat_device.cuh"
+#include "mc_philox2_sm100.cuh"   // packed FP32 pairs: box_muller2, hull_frame2, class_frame2, class_pair_test2, robot_hits2
 
 #define GMM_STAT 11        // n_free, n_coll, sum d[3], sum d d^T [6: xx xy xz yy yz zz]
 #define GMM_COMP 19        // w, mu[3], S[9] row-major, L[6] lower Cholesky (l00 l10 l11 l20 l21 l22)
@@ -74,6 +75,7 @@ struct GmmLaunch {
     int cull_stride;              // batch: 32-bit words between the members' lists (0: one plan for all)
     const float2* nominal;        // [T] (x*_t, y*_t), the centres of the lists; batch: [B][T] when cull_stride != 0
     unsigned long long* tests;    // optional: executed pair tests (all members)
+    int spread;                   // Philox sample kernel: one sample per thread instead of two (small n, single run)
 };
 
 // Batch member b (blockIdx.y of the count / sample kernels, blockIdx.x of the refit kernel): same plan-independent
@@ -379,49 +381,77 @@ struct GmmAcc {
     }
 };
 
-// one pass of the sample loop: samples base + threadIdx.x of waypoint a.t; every thread of the warp calls it
-template <bool SMEM>
-__device__ __forceinline__ void gmm_philox_pass(const GmmLaunch& a, unsigned i, unsigned n, int K, int& g, const unsigned* s_prefix,
-                                                const float (*s_mu)[3], const float (*s_L)[6], double (*s_stat)[GMM_STAT],
-                                                const float4* tab, const unsigned char* ccnt, const ushort2* cidx, bool cull, float2 nom,
-                                                GmmAcc& acc, unsigned& my_tests) {
-    const bool valid = i < n;
-    while (valid && g < K - 1 && i >= s_prefix[g + 1]) ++g;  // i only grows: the component index is monotone
-    mcsim_rng::u32x4 c = {i, a.stream_id, unsigned(2 * a.t), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
-    c = mcsim_rng::philox4x32_10(c, a.k0, a.k1);
-    float z0, z1, z2, z3;
-    mcsim_rng::box_muller(c.x, c.y, z0, z1);
-    mcsim_rng::box_muller(c.z, c.w, z2, z3);
-    const float* Lc = s_L[g];
-    const float d0 = Lc[0] * z0;
-    const float d1 = fmaf(Lc[2], z1, Lc[1] * z0);
-    const float d2 = fmaf(Lc[5], z2, fmaf(Lc[4], z1, Lc[3] * z0));
-    const float x = s_mu[g][0] + d0, y = s_mu[g][1] + d1;
-    float th = s_mu[g][2] + d2;
-    th -= 6.283185307179586f * rintf(th * 0.15915494309189535f);  // into [-pi, pi] for the MUFU sin / cos
-    float sn, cs;
-    __sincosf(th, &sn, &cs);
+// one pass of the sample loop: every thread draws and tests TWO samples, i0 = 2 j and i0 + 1, in the two lanes of
+// packed FP32 pairs (f32x2.cuh; the SAT is the packed kernel's, mc_philox2_sm100.cuh: same arithmetic for listed and
+// exhaustive tests); every thread of the warp calls it.  tab / ccnt / cidx: global or shared memory.
+__device__ __forceinline__ void gmm_philox_pass2(unsigned stream_id, unsigned ctr2, unsigned k0, unsigned k1, unsigned i0, unsigned i1, unsigned n, int K, int& g,
+                                                 const unsigned* s_prefix, const float (*s_mu)[3], const float (*s_L)[6], double (*s_stat)[GMM_STAT],
+                                                 const float4* tab, const unsigned char* ccnt, const ushort2* cidx, bool cull, float2 nom,
+                                                 GmmAcc& acc, unsigned& my_tests) {
+    const bool valid0 = i0 < n, valid1 = i1 < n;   // i1 = i0 + 1, or >= n when the launch spreads one sample per thread
+    while (valid0 && g < K - 1 && i0 >= s_prefix[g + 1]) ++g;  // i0 only grows: the component index is monotone
+    int g1 = g;
+    while (valid1 && g1 < K - 1 && i1 >= s_prefix[g1 + 1]) ++g1;
+    const mcsim_rng::u32x4 ca = mcsim_rng::philox4x32_10(mcsim_rng::u32x4{i0, stream_id, ctr2, unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)}, k0, k1);
+    const mcsim_rng::u32x4 cb = mcsim_rng::philox4x32_10(mcsim_rng::u32x4{i1, stream_id, ctr2, unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)}, k0, k1);
+    f2 z0, z1, z2, z3;
+    box_muller2(ca.x, ca.y, cb.x, cb.y, z0, z1);
+    box_muller2(ca.z, ca.w, cb.z, cb.w, z2, z3);
+    // component records per lane (the two samples share the component except across a boundary)
+    float La[6], Lb[6], ma[3], mb[3];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) La[k] = Lb[k] = s_L[g][k];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) ma[k] = mb[k] = s_mu[g][k];
+    if (g1 != g) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) Lb[k] = s_L[g1][k];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) mb[k] = s_mu[g1][k];
+    }
+    const f2 d0 = mul2(mk2(La[0], Lb[0]), z0);
+    const f2 d1 = fma2(mk2(La[2], Lb[2]), z1, mul2(mk2(La[1], Lb[1]), z0));
+    const f2 d2 = fma2(mk2(La[5], Lb[5]), z2, fma2(mk2(La[4], Lb[4]), z1, mul2(mk2(La[3], Lb[3]), z0)));
+    const f2 x = add2(mk2(ma[0], mb[0]), d0), y = add2(mk2(ma[1], mb[1]), d1), th = add2(mk2(ma[2], mb[2]), d2);
+    f2 sn, cs;
+    sincos2(th, sn, cs);   // |theta| < 3 pi: mu_theta in [0, 2 pi] + O(sigma)
     // warp-uniform choice of the candidate list by the warp's largest deviation from x*_t (exact: sat_device.cuh)
     int lev = MC_CULL_LEVELS;
     if (cull) {
-        const float ex = x - nom.x, ey = y - nom.y;
-        const float dm = __uint_as_float(__reduce_max_sync(0xffffffffu, valid ? __float_as_uint(fmaf(ex, ex, ey * ey)) : 0u));
-        lev = cull_level(dm);
+        const f2 ex = add2(x, -nom.x), ey = add2(y, -nom.y);
+        const f2 e2 = fma2(ex, ex, mul2(ey, ey));
+        const unsigned u0 = valid0 ? __float_as_uint(lo(e2)) : 0u, u1 = valid1 ? __float_as_uint(hi(e2)) : 0u;
+        lev = cull_level(__uint_as_float(__reduce_max_sync(0xffffffffu, u0 > u1 ? u0 : u1)));
         if (lev < MC_CULL_LEVELS && ccnt[lev] == MC_CULL_OVERFLOW) lev = MC_CULL_LEVELS;
     }
     unsigned tested = 0;
-    bool hit;
+    bool hit0 = false, hit1 = false;
     if (lev < MC_CULL_LEVELS) {
-        hit = robot_hits_listed<SMEM>(tab, ccnt, cidx, lev, x, y, cs, sn, tested);
+        for (int hI = 0; hI < c_scene.n_hulls; ++hI) {
+            const int nc = ccnt[hI * MC_CULL_LEVELS + lev];
+            if (nc == 0) continue;
+            const HullFrame2 h = hull_frame2(c_scene.hulls[hI], x, y, cs, sn);
+            ClassFrame2 cf;
+            unsigned cls = 0xffffffffu;
+            for (int k = 0; k < nc; ++k) {
+                const ushort2 o = cidx[hI * MC_CULL_CAP + k];  // x: pair record, y: class header
+                if (o.y != cls) {
+                    cls = o.y;
+                    cf = class_frame2(tab[o.y], h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
+                }
+                class_pair_test2(cf, h.ch, h.sh, h.nph, h.nqh, h.hhx, h.hhy, tab[o.x], *reinterpret_cast<const float2*>(tab + o.x + 1), hit0, hit1);
+            }
+            tested += nc;
+        }
     } else {
-        hit = robot_hits_grouped<SMEM>(tab, x, y, cs, sn);
+        robot_hits2(tab, x, y, cs, sn, hit0, hit1);
         tested = c_scene.n_pairs;
     }
-    if (__any_sync(0xffffffffu, valid && acc.g_acc >= 0 && g != acc.g_acc)) acc.flush(s_stat);
-    if (valid) {
-        my_tests += tested;
-        acc.add(g, hit, d0, d1, d2);
-    }
+    if (__any_sync(0xffffffffu, valid0 && acc.g_acc >= 0 && g != acc.g_acc)) acc.flush(s_stat);
+    if (valid0) acc.add(g, hit0, lo(d0), lo(d1), lo(d2));
+    if (__any_sync(0xffffffffu, valid1 && acc.g_acc >= 0 && g1 != acc.g_acc)) acc.flush(s_stat);
+    if (valid1) acc.add(g1, hit1, hi(d0), hi(d1), hi(d2));
+    my_tests += tested * (unsigned(valid0) + unsigned(valid1));
 }
 
 __global__ void __launch_bounds__(256) gmm_sample_philox_kernel(const GmmLaunch a_in) {
@@ -456,8 +486,11 @@ __global__ void __launch_bounds__(256) gmm_sample_philox_kernel(const GmmLaunch 
     const unsigned n = unsigned(s_prefix[K] < a.n ? s_prefix[K] : a.n);  // Philox mode: n <= 2^31 (checked on the host)
     const unsigned stride = gridDim.x * blockDim.x;
     const float2 nom = a.cull ? __ldg(a.nominal + a.t) : make_float2(0.f, 0.f);
-    for (unsigned base = blockIdx.x * blockDim.x; base < n; base += stride)
-        gmm_philox_pass<false>(a, base + threadIdx.x, n, K, g, s_prefix, s_mu, s_L, s_stat, a.sat2, s_ccnt, s_cidx, a.cull != nullptr, nom, acc, my_tests);
+    // two samples per thread and pass; a.spread (small sample counts, one run): one per thread, the second lane idle,
+    // so that twice as many warps share the waypoint's latency
+    const unsigned per = a.spread ? 1u : 2u;
+    for (unsigned base = per * blockIdx.x * blockDim.x; base < n; base += per * stride)
+        gmm_philox_pass2(a.stream_id, unsigned(2 * a.t), a.k0, a.k1, base + per * threadIdx.x, a.spread ? 0xffffffffu : base + per * threadIdx.x + 1, n, K, g, s_prefix, s_mu, s_L, s_stat, a.sat2, s_ccnt, s_cidx, a.cull != nullptr, nom, acc, my_tests);
     acc.flush(s_stat);
     __syncthreads();
     for (int i = threadIdx.x; i < K * GMM_STAT; i += blockDim.x) {
@@ -509,20 +542,20 @@ __device__ __forceinline__ void gmm_refit_moments(double* cp, const double* st, 
     }
 }
 // Part 2 (after every component's part 1): weight, p_t, records, EKFpredict + EKFupdate to waypoint t+1, Cholesky.
-__device__ __forceinline__ void gmm_refit_finish(const GmmLaunch& a, int g, double* cp, const double* s_free, const double* s_coll) {
+__device__ __forceinline__ void gmm_refit_finish(const GmmLaunch& a, int t, int g, double* cp, const double* s_free, const double* s_coll) {
     using namespace mcsim_math;
     const int K = a.K;
     double tf = 0, tc = 0;
     for (int k = 0; k < K; ++k) { tf += s_free[k]; tc += s_coll[k]; }
     // normalise(collisionCounts, 1, 1).row(1): divides by the row's 1-norm, or by 1 if that is 0
     cp[0] = s_free[g] / (tf > 0 ? tf : 1.0);
-    if (g == 0) a.probabilities[a.t] = tc / double(a.n);
+    if (g == 0) a.probabilities[t] = tc / double(a.n);
     if (a.n_out) { a.n_out[g] = (unsigned long long)s_coll[g]; a.n_out[K + g] = (unsigned long long)s_free[g]; }
     if (a.trunc_out) for (int k = 0; k < GMM_REC; ++k) a.trunc_out[g * GMM_REC + k] = cp[k];
-    if (a.t == a.T - 1 && a.rec_post) for (int k = 0; k < GMM_REC; ++k) a.rec_post[g * GMM_REC + k] = cp[k];
+    if (t == a.T - 1 && a.rec_post) for (int k = 0; k < GMM_REC; ++k) a.rec_post[g * GMM_REC + k] = cp[k];
     // ---- move the component to waypoint t+1: EKFpredict (:766-772) then EKFupdate (:804-812)
-    if (a.do_ekf && a.t < a.T - 1) {
-        const GmmStepTable& s = a.steps[a.t];
+    if (a.do_ekf && t < a.T - 1) {
+        const GmmStepTable& s = a.steps[t];
         NoiseModel<double> nm;
         nm.Q = a.Q; nm.L = a.L;
         for (int l = 0; l < a.L; ++l) { nm.lx[l] = a.lx[l]; nm.ly[l] = a.ly[l]; }
@@ -531,7 +564,7 @@ __device__ __forceinline__ void gmm_refit_finish(const GmmLaunch& a, int g, doub
         ekf_update(nm, pmu, pS, s.z, a.L);
         for (int k = 0; k < 3; ++k) cp[1 + k] = pmu[k];
         for (int k = 0; k < 9; ++k) cp[4 + k] = pS[k];
-        if (a.rec_pre) for (int k = 0; k < GMM_REC; ++k) a.rec_pre[(size_t(a.t + 1) * K + g) * GMM_REC + k] = cp[k];
+        if (a.rec_pre) for (int k = 0; k < GMM_REC; ++k) a.rec_pre[(size_t(t + 1) * K + g) * GMM_REC + k] = cp[k];
     }
     if (!gmm_chol3(cp + 4, cp + 13)) {
         // not SPD (the reference falls back to an eigen-decomposition, glue_mvnrnd_meat.hpp:98-132):
@@ -551,7 +584,7 @@ __global__ void __launch_bounds__(32) gmm_refit_kernel(const GmmLaunch a_in) {
     if (g < K) gmm_refit_moments(cp, a.stats + g * GMM_STAT, a.degenerate, s_free[g], s_coll[g]);
     __syncthreads();
     if (g < K) {
-        gmm_refit_finish(a, g, cp, s_free, s_coll);
+        gmm_refit_finish(a, a.t, g, cp, s_free, s_coll);
         for (int k = 0; k < GMM_STAT; ++k) a.stats[g * GMM_STAT + k] = 0.0;
         a.hist[g] = 0;
     }
@@ -564,7 +597,10 @@ __global__ void __launch_bounds__(32) gmm_refit_kernel(const GmmLaunch a_in) {
 // of 3 T.  Same draws, same component assignment, same refit code as the per-waypoint kernels (member b ==
 // mcsim_cuda_gmm_run on Philox subsequence stream0 + b up to the order of the FP64 sums).
 // Dynamic shared memory: pair table (a.sat2, sat2_n float4) | candidate lists (cull_words 32-bit words).
-__global__ void __launch_bounds__(256, 3) gmm_member_run_kernel(const GmmLaunch a_in, int sat2_n, int cull_words) {
+#ifndef GMM_FUSED_CTAS
+#define GMM_FUSED_CTAS 3   // resident 256-thread CTAs per SM the fused kernel's register budget is set for
+#endif
+__global__ void __launch_bounds__(256, GMM_FUSED_CTAS) gmm_member_run_kernel(const GmmLaunch a_in, int sat2_n, int cull_words) {
     extern __shared__ __align__(16) float4 s_tab[];
     __shared__ double s_comp[MCSIM_MAX_GAUSSIANS][GMM_COMP];
     __shared__ double s_stat[MCSIM_MAX_GAUSSIANS][GMM_STAT];
@@ -574,8 +610,9 @@ __global__ void __launch_bounds__(256, 3) gmm_member_run_kernel(const GmmLaunch 
     __shared__ float s_cdf[MCSIM_MAX_GAUSSIANS];
     __shared__ unsigned s_hist[MCSIM_MAX_GAUSSIANS];
     __shared__ unsigned s_prefix[MCSIM_MAX_GAUSSIANS + 1];
-    GmmLaunch a = gmm_member(a_in, blockIdx.x);
+    const GmmLaunch a = gmm_member(a_in, blockIdx.x);
     const int K = a.K, T = a.T, nh = c_scene.n_hulls;
+    const unsigned stream_id = a.stream_id, k0 = a.k0, k1 = a.k1, n_all = unsigned(a.n);
     const bool cull = a.cull != nullptr;
     unsigned* s_cull = reinterpret_cast<unsigned*>(s_tab + sat2_n);
     for (int i = threadIdx.x; i < sat2_n; i += blockDim.x) s_tab[i] = a.sat2[i];
@@ -589,7 +626,6 @@ __global__ void __launch_bounds__(256, 3) gmm_member_run_kernel(const GmmLaunch 
     __syncthreads();
 
     for (int t = 0; t < T; ++t) {
-        a.t = t;
         // ---- multinomial counts of this waypoint (gmm_count_kernel)
         if (threadIdx.x == 0) {
             double acc = 0, tot = 0;
@@ -603,24 +639,41 @@ __global__ void __launch_bounds__(256, 3) gmm_member_run_kernel(const GmmLaunch 
         for (int i = threadIdx.x; i < K * 3; i += blockDim.x) s_mu[i / 3][i % 3] = float(s_comp[i / 3][1 + i % 3]);
         for (int i = threadIdx.x; i < K * 6; i += blockDim.x) s_L[i / 6][i % 6] = float(s_comp[i / 6][13 + i % 6]);
         __syncthreads();
-        const unsigned n4 = unsigned((a.n + 3) >> 2);
+        // per-thread counts in four registers of four 8-bit fields (component g: field g % 4 of register g / 4),
+        // flushed by warp sums before a field can overflow and after the last pass
+        const unsigned n4 = (n_all + 3) >> 2;
+        unsigned cnt[4] = {0u, 0u, 0u, 0u};
+        unsigned held = 0;
+        auto flush_counts = [&]() {
+            for (int gg = 0; gg < K; ++gg) {
+                const unsigned r = gg < 4 ? cnt[0] : (gg < 8 ? cnt[1] : (gg < 12 ? cnt[2] : cnt[3]));
+                const unsigned v = __reduce_add_sync(0xffffffffu, (r >> (8 * (gg & 3))) & 0xffu);
+                if (v && (threadIdx.x & 31) == 0) atomicAdd(&s_hist[gg], v);
+            }
+            cnt[0] = cnt[1] = cnt[2] = cnt[3] = 0u;
+            held = 0;
+        };
         for (unsigned base = 0; base < n4; base += blockDim.x) {
             const unsigned j = base + threadIdx.x;
-            mcsim_rng::u32x4 c = {j, a.stream_id, unsigned(2 * t + 1), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
-            c = mcsim_rng::philox4x32_10(c, a.k0, a.k1);
+            mcsim_rng::u32x4 c = {j, stream_id, unsigned(2 * t + 1), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
+            c = mcsim_rng::philox4x32_10(c, k0, k1);
             const unsigned w[4] = {c.x, c.y, c.z, c.w};
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                const bool valid = j < n4 && 4ull * j + q < a.n;
+                const bool valid = j < n4 && 4 * j + q < n_all;   // n <= 2^31: no overflow
                 const float u = mcsim_rng::u01(w[q]);
                 int g = 0;
-                while (g < K - 1 && u > s_cdf[g]) ++g;
-                for (int gg = 0; gg < K; ++gg) {
-                    const unsigned m = __ballot_sync(0xffffffffu, valid && g == gg);
-                    if (m && (threadIdx.x & 31) == 0) atomicAdd(&s_hist[gg], unsigned(__popc(m)));
-                }
+                for (int k = 0; k < K - 1; ++k) g += u > s_cdf[k];   // the cdf is non-decreasing: first k with u <= cdf[k]
+                const unsigned inc = valid ? 1u << (8 * (g & 3)) : 0u;
+                cnt[0] += g < 4 ? inc : 0u;
+                cnt[1] += (g >= 4 && g < 8) ? inc : 0u;
+                cnt[2] += (g >= 8 && g < 12) ? inc : 0u;
+                cnt[3] += g >= 12 ? inc : 0u;
             }
+            held += 4;
+            if (held > 248) flush_counts();   // warp-uniform
         }
+        flush_counts();
         __syncthreads();
         if (threadIdx.x == 0) {
             unsigned acc = 0;
@@ -632,12 +685,12 @@ __global__ void __launch_bounds__(256, 3) gmm_member_run_kernel(const GmmLaunch 
         {
             int g = 0;
             GmmAcc acc;
-            const unsigned n = unsigned(s_prefix[K] < a.n ? s_prefix[K] : a.n);
+            const unsigned n = s_prefix[K] < n_all ? s_prefix[K] : n_all;
             const float2 nom = cull ? __ldg(a.nominal + t) : make_float2(0.f, 0.f);
             const unsigned char* cc = s_ccnt + t * nh * MC_CULL_LEVELS;
             const ushort2* ci = s_cidx + t * nh * MC_CULL_CAP;
-            for (unsigned base = 0; base < n; base += blockDim.x)
-                gmm_philox_pass<true>(a, base + threadIdx.x, n, K, g, s_prefix, s_mu, s_L, s_stat, s_tab, cc, ci, cull, nom, acc, my_tests);
+            for (unsigned base = 0; base < n; base += 2 * blockDim.x)   // two samples per thread and pass
+                gmm_philox_pass2(stream_id, unsigned(2 * t), k0, k1, base + 2 * threadIdx.x, base + 2 * threadIdx.x + 1, n, K, g, s_prefix, s_mu, s_L, s_stat, s_tab, cc, ci, cull, nom, acc, my_tests);
             acc.flush(s_stat);
         }
         __syncthreads();
@@ -646,7 +699,7 @@ __global__ void __launch_bounds__(256, 3) gmm_member_run_kernel(const GmmLaunch 
         if (g < K) gmm_refit_moments(s_comp[g], s_stat[g], a.degenerate, s_free[g], s_coll[g]);
         __syncthreads();
         if (g < K) {
-            gmm_refit_finish(a, g, s_comp[g], s_free, s_coll);
+            gmm_refit_finish(a, t, g, s_comp[g], s_free, s_coll);
             for (int k = 0; k < GMM_STAT; ++k) s_stat[g][k] = 0.0;
             s_hist[g] = 0;
         }

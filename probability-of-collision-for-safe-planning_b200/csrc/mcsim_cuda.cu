@@ -77,7 +77,12 @@ struct mcsim_cuda_ctx {
     std::vector<unsigned> h_pair_sat2;  // per pair: record offset | class header offset << 16 in the grouped table
     double h_reach[MCSIM_MAX_HULLS] = {0};
     DevBuf mc_cull;
-    int gmm_cull_words = 0;  // words of ONE plan's lists
+    int gmm_cull_words = 0, gmm_cull_words_cached = 0;  // words of ONE plan's lists (this run / on the device)
+    // the lists depend on (scene, trajectory) only: repeated runs of one plan (the reference's 200-run loop) reuse them
+    uint64_t scene_epoch = 0;
+    std::vector<double> mc_cull_key, gmm_cull_key;   // scene epoch, T, trajectory x / y of the lists on the device
+    std::vector<unsigned> mc_cull_host;
+    bool mc_cull_uploaded = false;   // by the last mc_prepare (h2d byte accounting)
     DevBuf gmm_plans, gmm_robot_normals;      // batch: the plan(s) and the scratch normals of the device robot threads
     DevBuf gmm_cull, gmm_nominal, gmm_tests;  // GMM Philox mode: the plan's (or every batch member's) lists
     int mc_cull_words = 0;           // 0: no lists for the prepared plan (every live pair is tested)
@@ -211,6 +216,7 @@ extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int 
     c->h_pairgeom.clear();
     c->h_pair_hull.clear();
     c->h_pair_sat2.clear();
+    ++c->scene_epoch;
     c->mc_prepared = false;  // candidate lists of a prepared plan refer to the old scene
     for (int h = 0; h < n_hulls; ++h) {
         const double* hu = hulls + h * MCSIM_PRISM_STRIDE;
@@ -358,6 +364,12 @@ static int mc_check(const mcsim_cuda_ctx* c, const mcsim_mc_params* p) {
     return MCSIM_OK;
 }
 
+static void cull_key(const mcsim_cuda_ctx* c, const double* trajectory, int n_plans, int T, std::vector<double>& key) {
+    key.assign(3 + size_t(n_plans) * 2 * T, 0.0);
+    key[0] = double(c->scene_epoch); key[1] = double(T); key[2] = double(n_plans);
+    for (int b = 0; b < n_plans; ++b) memcpy(&key[3 + size_t(b) * 2 * T], trajectory + size_t(b) * 3 * T, sizeof(double) * 2 * T);  // x and y rows
+}
+
 // Candidate lists of the packed kernel's broad phase (layout and exactness argument: mc_philox2_sm100.cuh).
 // need(pair) = distance from x*_t to the box footprint - reach of the pair's hull - 1 mm of slack for the FP32
 // plan record and the FP32 deviation test of the kernel.
@@ -445,7 +457,19 @@ extern "C" int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* c, const mcsim_mc_params* p
         }
     }
     std::vector<unsigned> cull;
-    if (!plan2.empty() && !p->exhaustive && L == 8 && c->sat2_n < 65536) build_cull_lists(c, p->trajectory, T, cull);
+    bool cull_cached = false;
+    if (!plan2.empty() && !p->exhaustive && L == 8 && c->sat2_n < 65536) {
+        std::vector<double> key;
+        cull_key(c, p->trajectory, 1, T, key);
+        if (key == c->mc_cull_key) {
+            cull = c->mc_cull_host;
+            cull_cached = true;
+        } else {
+            build_cull_lists(c, p->trajectory, T, cull);
+            c->mc_cull_key.swap(key);
+            c->mc_cull_host = cull;
+        }
+    }
     // the lists ride in shared memory next to the pair table; too large a plan x scene goes without them
     if ((cull.size() * sizeof(unsigned) + sizeof(float4) * size_t(c->sat2_n)) * MC_P2_CTAS_PER_SM > 200 * 1024) cull.clear();
     c->mc_cull_words = int(cull.size());
@@ -455,7 +479,8 @@ extern "C" int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* c, const mcsim_mc_params* p
     CK(cudaStreamSynchronize(c->stream));
     CK(cudaMemcpyToSymbolAsync(c_mc, &pc, sizeof(pc), 0, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemcpyAsync(c->plan.p, plan.data(), plan.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
-    if (!cull.empty()) CK(cudaMemcpyAsync(c->mc_cull.p, cull.data(), cull.size() * sizeof(unsigned), cudaMemcpyHostToDevice, c->stream));
+    c->mc_cull_uploaded = !cull.empty() && !cull_cached;
+    if (!cull.empty() && !cull_cached) CK(cudaMemcpyAsync(c->mc_cull.p, cull.data(), cull.size() * sizeof(unsigned), cudaMemcpyHostToDevice, c->stream));
     if (!plan2.empty()) CK(cudaMemcpyToSymbolAsync(c_plan2, plan2.data(), plan2.size() * sizeof(float), 0, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * (4 + T), c->stream));
     CK(cudaStreamSynchronize(c->stream));  // plan is a stack vector
@@ -534,7 +559,7 @@ extern "C" int mcsim_cuda_mc_run(mcsim_cuda_ctx* c, const mcsim_mc_params* p, mc
     if (rc) return rc;
     c->h2d_bytes = sizeof(McPlanConst) + sizeof(float) * size_t(p->T) * MC_PHILOX_STRIDE +
                    ((p->mode == MCSIM_MODE_PHILOX && p->T <= MC_PLAN2_MAX_T) ? sizeof(float) * size_t(p->T) * MC_PLAN2_STRIDE : 0) +
-                   sizeof(unsigned) * size_t(c->mc_cull_words);
+                   (c->mc_cull_uploaded ? sizeof(unsigned) * size_t(c->mc_cull_words) : 0);
     c->d2h_bytes = sizeof(unsigned long long) * (4 + p->T);
     const uint64_t n = p->n_rollouts;
     const int T = p->T;
@@ -638,6 +663,15 @@ static int gmm_upload_cull(mcsim_cuda_ctx* c, GmmLaunch& a, const double* trajec
     c->gmm_cull_words = 0;
     if (exhaustive || c->sat2_n >= 65536 || c->n_pairs == 0) return MCSIM_OK;
     if (size_t(n_plans) * T * c->n_hulls * (MC_CULL_CAP + 1) > (size_t(64) << 20)) return MCSIM_OK;  // 256 MB of lists: go without
+    std::vector<double> key;
+    cull_key(c, trajectories, n_plans, T, key);
+    if (key == c->gmm_cull_key && c->gmm_cull_words_cached > 0) {   // same scene, same plan(s): the lists are on the device
+        a.cull = (const unsigned*)c->gmm_cull.p;
+        a.nominal = (const float2*)c->gmm_nominal.p;
+        a.cull_stride = n_plans > 1 ? c->gmm_cull_words_cached : 0;
+        c->gmm_cull_words = c->gmm_cull_words_cached;
+        return MCSIM_OK;
+    }
     std::vector<unsigned> all, one;
     std::vector<float2> nominal(size_t(n_plans) * T);
     for (int b = 0; b < n_plans; ++b) {
@@ -655,32 +689,39 @@ static int gmm_upload_cull(mcsim_cuda_ctx* c, GmmLaunch& a, const double* trajec
     a.cull = (const unsigned*)c->gmm_cull.p;
     a.nominal = (const float2*)c->gmm_nominal.p;
     a.cull_stride = n_plans > 1 ? int(one.size()) : 0;
-    c->gmm_cull_words = int(one.size());
+    c->gmm_cull_words = c->gmm_cull_words_cached = int(one.size());
+    c->gmm_cull_key.swap(key);
     return MCSIM_OK;
 }
 
 // the three launches of one waypoint
-static int gmm_launch_waypoint(mcsim_cuda_ctx* c, const GmmLaunch& a, int mode) {
+static int gmm_launch_waypoint(mcsim_cuda_ctx* c, const GmmLaunch& a_in, int mode) {
+    GmmLaunch a = a_in;
     const unsigned B = a.B > 1 ? unsigned(a.B) : 1u;
-    int block;
+    int block, spread_flag = 0;
     unsigned gx;
     if (B == 1) {
         // one run, small sample counts (the reference's N = 10^4): 64-thread CTAs so that every SM gets work
-        block = a.n < (unsigned long long)c->n_sm * 256 ? 64 : 256;
-        const unsigned long long want = (a.n + block - 1) / block, cap = (unsigned long long)c->n_sm * 8;
+        // (the Philox-mode sample kernel takes two samples per thread and pass unless that leaves SMs without work)
+        const bool spread = mode == MCSIM_MODE_PHILOX && a.n < (unsigned long long)c->n_sm * 256;
+        spread_flag = spread ? 1 : 0;
+        const unsigned per_thread = mode == MCSIM_MODE_PHILOX && !spread ? 2 : 1;
+        block = a.n < (unsigned long long)c->n_sm * 256 * per_thread ? 64 : 256;
+        const unsigned long long want = (a.n + block * per_thread - 1) / (block * per_thread), cap = (unsigned long long)c->n_sm * 8;
         gx = unsigned(want < cap ? (want ? want : 1) : cap);
     } else {
         // a batch fills the GPU by its members: few 256-thread CTAs per member, many samples per thread (the CTA
         // prologue / epilogue and the warp reductions are per CTA and per component change, not per sample);
         // two waves of resident CTAs in total, the count per member chosen for the fewest idle lanes in the last pass
         block = 256;
-        const unsigned long long want = (a.n + block - 1) / block;
+        const unsigned per_thread = mode == MCSIM_MODE_PHILOX ? 2 : 1;
+        const unsigned long long want = (a.n + block * per_thread - 1) / (block * per_thread);
         unsigned g0 = unsigned((2ull * c->n_sm * 8 + B - 1) / B);
         if (g0 < 1) g0 = 1;
         unsigned best = g0;
         unsigned long long best_waste = ~0ull;
         for (unsigned cand = g0; cand <= 2 * g0; ++cand) {
-            const unsigned long long per = (unsigned long long)cand * block, passes = (a.n + per - 1) / per;
+            const unsigned long long per = (unsigned long long)cand * block * per_thread, passes = (a.n + per - 1) / per;
             const unsigned long long waste = passes * per - a.n;
             if (waste < best_waste) { best_waste = waste; best = cand; }
         }
@@ -688,6 +729,7 @@ static int gmm_launch_waypoint(mcsim_cuda_ctx* c, const GmmLaunch& a, int mode) 
     }
     const dim3 grid(gx, B);
     if (mode == MCSIM_MODE_PHILOX && a.n > (1ull << 31)) return fail(MCSIM_ERR_ARG, "gmm: Philox mode takes at most 2^31 samples per waypoint");
+    a.spread = spread_flag;
     if (mode == MCSIM_MODE_PHILOX) {
         gmm_count_kernel<<<grid, block, 0, c->stream>>>(a);
         gmm_sample_philox_kernel<<<grid, block, 0, c->stream>>>(a);
