@@ -152,41 +152,45 @@ MCSIM_HD T range_to(const NoiseModel<T>& nm, const T s[3], int l) {
 
 // EKFupdate (:883-929): L sequential scalar range updates, in place; H row from makeHRow (:470-492);
 // K = Sigma H^T * (1/S); Sigma <- (I - K H) Sigma (non-Joseph); no angle wrap afterwards.
+// One landmark (the loop body); callers with a compile-time landmark count unroll it themselves.
+template <typename T>
+MCSIM_HD void ekf_update_one(const T lx, const T ly, const T Q, T mu[3], T S[9], const T zl) {
+    const T dx = mu[0] - lx, dy = mu[1] - ly;
+    const T q = dx * dx + dy * dy;
+    const T rq = sqrt_t(q);
+    const T h0 = dx / rq, h1 = dy / rq;
+    // H Sigma (1x3), then S = H Sigma H^T + Q
+    const T hs0 = h0 * S[0] + h1 * S[3];
+    const T hs1 = h0 * S[1] + h1 * S[4];
+    const T s = hs0 * h0 + hs1 * h1 + Q;
+    const T inv = T(1) / s;
+    // K = Sigma H^T / S
+    const T k0 = (S[0] * h0 + S[1] * h1) * inv;
+    const T k1 = (S[3] * h0 + S[4] * h1) * inv;
+    const T k2 = (S[6] * h0 + S[7] * h1) * inv;
+    const T innov = zl - rq;
+    mu[0] += k0 * innov;
+    mu[1] += k1 * innov;
+    mu[2] += k2 * innov;
+    // A = I - K H (third column of H is 0), Sigma <- A Sigma
+    const T a00 = T(1) - k0 * h0, a01 = -k0 * h1;
+    const T a10 = -k1 * h0, a11 = T(1) - k1 * h1;
+    const T a20 = -k2 * h0, a21 = -k2 * h1;
+    T N[9];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        N[0 + j] = a00 * S[0 + j] + a01 * S[3 + j];
+        N[3 + j] = a10 * S[0 + j] + a11 * S[3 + j];
+        N[6 + j] = a20 * S[0 + j] + a21 * S[3 + j] + S[6 + j];
+    }
+#pragma unroll
+    for (int j = 0; j < 9; ++j) S[j] = N[j];
+}
+
 template <typename T>
 MCSIM_HD void ekf_update(const NoiseModel<T>& nm, T mu[3], T S[9], const T* z, const int L) {
 #pragma unroll
-    for (int l = 0; l < L; ++l) {
-        const T dx = mu[0] - nm.lx[l], dy = mu[1] - nm.ly[l];
-        const T q = dx * dx + dy * dy;
-        const T rq = sqrt_t(q);
-        const T h0 = dx / rq, h1 = dy / rq;
-        // H Sigma (1x3), then S = H Sigma H^T + Q
-        const T hs0 = h0 * S[0] + h1 * S[3];
-        const T hs1 = h0 * S[1] + h1 * S[4];
-        const T s = hs0 * h0 + hs1 * h1 + nm.Q;
-        const T inv = T(1) / s;
-        // K = Sigma H^T / S
-        const T k0 = (S[0] * h0 + S[1] * h1) * inv;
-        const T k1 = (S[3] * h0 + S[4] * h1) * inv;
-        const T k2 = (S[6] * h0 + S[7] * h1) * inv;
-        const T innov = z[l] - rq;
-        mu[0] += k0 * innov;
-        mu[1] += k1 * innov;
-        mu[2] += k2 * innov;
-        // A = I - K H (third column of H is 0), Sigma <- A Sigma
-        const T a00 = T(1) - k0 * h0, a01 = -k0 * h1;
-        const T a10 = -k1 * h0, a11 = T(1) - k1 * h1;
-        const T a20 = -k2 * h0, a21 = -k2 * h1;
-        T N[9];
-#pragma unroll
-        for (int j = 0; j < 3; ++j) {
-            N[0 + j] = a00 * S[0 + j] + a01 * S[3 + j];
-            N[3 + j] = a10 * S[0 + j] + a11 * S[3 + j];
-            N[6 + j] = a20 * S[0 + j] + a21 * S[3 + j] + S[6 + j];
-        }
-#pragma unroll
-        for (int j = 0; j < 9; ++j) S[j] = N[j];
-    }
+    for (int l = 0; l < L; ++l) ekf_update_one(nm.lx[l], nm.ly[l], nm.Q, mu, S, z[l]);
 }
 
 }  // namespace mcsim_math
