@@ -208,6 +208,30 @@ __global__ void __launch_bounds__(256) em_estep2_kernel(const EmLaunch a) {
             if (i + 2 * u * stride >= n) break;
             const float v1 = (i + (2 * u + 1) * stride < n) ? 1.f : 0.f;   // lane 1 may be past the end
             const f2 x = mk2(cx[2 * u], cx[2 * u + 1]), y = mk2(cy[2 * u], cy[2 * u + 1]), t = mk2(ct[2 * u], ct[2 * u + 1]);
+            if (K == 1) {
+                // one component: the responsibility is 1 and the log-sum-exp is the log-likelihood itself; the general
+                // path below computes the same up to the rounding of its ex2 / rcp (1e-7), with 6 MUFU per pair more
+                const float4* c4 = reinterpret_cast<const float4*>(s_c);
+                const float4 ca = c4[0], cb = c4[1], cc = c4[2];
+                const f2 valid = mk2(1.f, v1);
+                const f2 d0 = add2(x, -ca.x), d1 = add2(y, -ca.y), d2 = add2(t, -ca.z);
+                const f2 q0 = fma2(d0, ca.w, fma2(d1, cb.x, mul2(d2, cb.y)));
+                const f2 q1 = fma2(d1, cb.z, mul2(d2, cb.w));
+                const f2 l1 = fma2(d0, q0, fma2(d1, q1, fma2(mul2(d2, cc.x), d2, cc.y)));
+                lsum = fma2(l1, valid, lsum);
+                const f2 r0 = mul2(valid, d0), r1 = mul2(valid, d1), r2 = mul2(valid, d2);
+                acc[0][0] = add2(acc[0][0], valid);
+                acc[0][1] = add2(acc[0][1], r0);
+                acc[0][2] = add2(acc[0][2], r1);
+                acc[0][3] = add2(acc[0][3], r2);
+                acc[0][4] = fma2(r0, d0, acc[0][4]);
+                acc[0][5] = fma2(r0, d1, acc[0][5]);
+                acc[0][6] = fma2(r0, d2, acc[0][6]);
+                acc[0][7] = fma2(r1, d1, acc[0][7]);
+                acc[0][8] = fma2(r1, d2, acc[0][8]);
+                acc[0][9] = fma2(r2, d2, acc[0][9]);
+                continue;
+            }
             f2 ll[K];
             float m0 = -FLT_MAX, m1 = -FLT_MAX;
 #pragma unroll

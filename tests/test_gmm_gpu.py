@@ -189,3 +189,23 @@ def test_gmm_batch_fused_kernel_members_equal_single_runs(ctx, plan, scenes):
     for b in (17, 79):
         alone = ctx.gmm_run_batch(plan, 2, 4000, 1, trajectories=tr[[b]], odometry=od[:1], stream0=7 + b)
         np.testing.assert_allclose(many["probabilities"][b], alone["probabilities"][0], rtol=1e-9, atol=1e-12)
+
+
+@pytest.mark.parametrize("K,N", [(1, 3000), (16, 4000), (3, 40)])
+def test_gmm_batch_fused_kernel_edge_cases(ctx, plan, scenes, K, N):
+    """One-CTA-per-run kernel against the per-waypoint kernels (the same members run as a batch of 2, below the
+    64-run threshold): one component, the maximum component count, and so few samples that components starve
+    (degenerate refits are counted, not fatal); a two-waypoint plan."""
+    ctx.set_scene(scenes["pr2custom"]["boxes"], scenes["pr2custom"]["hulls"])
+    B = 64
+    fused = ctx.gmm_run_batch(plan, K, N, B, stream0=1000)
+    for b0 in (0, 62):
+        pair = ctx.gmm_run_batch(plan, K, N, 2, stream0=1000 + b0)
+        np.testing.assert_allclose(fused["probabilities"][b0:b0 + 2], pair["probabilities"], rtol=1e-9, atol=1e-12)
+    assert np.all((fused["P"] >= 0) & (fused["P"] <= 1))
+    short = dict(plan)
+    short["trajectory"] = plan["trajectory"][:, :2]
+    short["odometry"] = plan["odometry"][:, :1]
+    f2 = ctx.gmm_run_batch(short, K, N, B, stream0=5)
+    p2 = ctx.gmm_run_batch(short, K, N, 2, stream0=5)
+    np.testing.assert_allclose(f2["probabilities"][:2], p2["probabilities"], rtol=1e-9, atol=1e-12)
