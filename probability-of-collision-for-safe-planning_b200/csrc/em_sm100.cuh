@@ -162,8 +162,87 @@ __global__ void __launch_bounds__(256) em_estep_kernel(const EmLaunch a) {
 // The E-step is almost pure FP32 arithmetic (no compares / selects to speak of), which is where packed
 // pairs pay on sm_100a (tools/pipe_probe.cu): half the FMA-pipe issue slots per sample.  Same arithmetic
 // per lane as em_estep_kernel; MUFU (ex2, lg2, rcp) and the running maximum stay per lane.
+// one pair of samples (the two lanes of x, y, t) against the K components in s_c; v1 = 0 masks lane 1
 template <int K>
-__global__ void __launch_bounds__(256) em_estep2_kernel(const EmLaunch a) {
+__device__ __forceinline__ void em_pair2(const float* s_c, f2 x, f2 y, f2 t, float v1, f2 (&acc)[K][EM_NSTAT], f2& lsum) {
+    if (K == 1) {
+        // one component: the responsibility is 1 and the log-sum-exp is the log-likelihood itself; the general
+        // path below computes the same up to the rounding of its ex2 / rcp (1e-7), with 6 MUFU per pair more
+        const float4* c4 = reinterpret_cast<const float4*>(s_c);
+        const float4 ca = c4[0], cb = c4[1], cc = c4[2];
+        const f2 valid = mk2(1.f, v1);
+        const f2 d0 = add2(x, -ca.x), d1 = add2(y, -ca.y), d2 = add2(t, -ca.z);
+        const f2 q0 = fma2(d0, ca.w, fma2(d1, cb.x, mul2(d2, cb.y)));
+        const f2 q1 = fma2(d1, cb.z, mul2(d2, cb.w));
+        const f2 l1 = fma2(d0, q0, fma2(d1, q1, fma2(mul2(d2, cc.x), d2, cc.y)));
+        lsum = fma2(l1, valid, lsum);
+        const f2 r0 = mul2(valid, d0), r1 = mul2(valid, d1), r2 = mul2(valid, d2);
+        acc[0][0] = add2(acc[0][0], valid);
+        acc[0][1] = add2(acc[0][1], r0);
+        acc[0][2] = add2(acc[0][2], r1);
+        acc[0][3] = add2(acc[0][3], r2);
+        acc[0][4] = fma2(r0, d0, acc[0][4]);
+        acc[0][5] = fma2(r0, d1, acc[0][5]);
+        acc[0][6] = fma2(r0, d2, acc[0][6]);
+        acc[0][7] = fma2(r1, d1, acc[0][7]);
+        acc[0][8] = fma2(r1, d2, acc[0][8]);
+        acc[0][9] = fma2(r2, d2, acc[0][9]);
+        return;
+    }
+    f2 ll[K];
+    float m0 = -FLT_MAX, m1 = -FLT_MAX;
+#pragma unroll
+    for (int g = 0; g < K; ++g) {
+        const float4* c4 = reinterpret_cast<const float4*>(s_c + g * EM_COMP_STRIDE);
+        const float4 ca = c4[0], cb = c4[1], cc = c4[2];
+        const f2 d0 = add2(x, -ca.x), d1 = add2(y, -ca.y), d2 = add2(t, -ca.z);
+        const f2 q0 = fma2(d0, ca.w, fma2(d1, cb.x, mul2(d2, cb.y)));
+        const f2 q1 = fma2(d1, cb.z, mul2(d2, cb.w));
+        ll[g] = fma2(d0, q0, fma2(d1, q1, fma2(mul2(d2, cc.x), d2, cc.y)));
+        m0 = fmaxf(m0, lo(ll[g]));
+        m1 = fmaxf(m1, hi(ll[g]));
+    }
+    const f2 mm = mk2(m0, m1);
+    const f2 ms = mul2(mm, -1.4426950408889634f);
+    f2 s = bc(0.f);
+#pragma unroll
+    for (int g = 0; g < K; ++g) {
+        const f2 e = fma2(ll[g], 1.4426950408889634f, ms);
+        float e0, e1;
+        un2(e, e0, e1);
+        asm("ex2.approx.ftz.f32 %0, %0;" : "+f"(e0));
+        asm("ex2.approx.ftz.f32 %0, %0;" : "+f"(e1));
+        ll[g] = mk2(e0, e1);
+        s = add2(s, ll[g]);
+    }
+    const f2 lg = mk2(mufu_lg2(lo(s)), mufu_lg2(hi(s)));
+    const f2 valid = mk2(1.f, v1);
+    lsum = fma2(fma2(lg, 0.6931471805599453f, mm), valid, lsum);   // (m + ln s) per valid lane
+    const f2 inv = mul2(rcp2(s), valid);
+#pragma unroll
+    for (int g = 0; g < K; ++g) {
+        const float4 ca = *reinterpret_cast<const float4*>(s_c + g * EM_COMP_STRIDE);
+        const f2 r = mul2(ll[g], inv);
+        const f2 d0 = add2(x, -ca.x), d1 = add2(y, -ca.y), d2 = add2(t, -ca.z);
+        const f2 r0 = mul2(r, d0), r1 = mul2(r, d1), r2 = mul2(r, d2);
+        acc[g][0] = add2(acc[g][0], r);
+        acc[g][1] = add2(acc[g][1], r0);
+        acc[g][2] = add2(acc[g][2], r1);
+        acc[g][3] = add2(acc[g][3], r2);
+        acc[g][4] = fma2(r0, d0, acc[g][4]);
+        acc[g][5] = fma2(r0, d1, acc[g][5]);
+        acc[g][6] = fma2(r0, d2, acc[g][6]);
+        acc[g][7] = fma2(r1, d1, acc[g][7]);
+        acc[g][8] = fma2(r1, d2, acc[g][8]);
+        acc[g][9] = fma2(r2, d2, acc[g][9]);
+    }
+}
+
+// VEC: the sample count is a multiple of 4, so every row of x is 16-byte aligned: one LDG.128 per row brings 4
+// consecutive samples (two pairs) per thread, two such triples in flight while the previous one is processed
+// (96 B per thread) -- the K <= 2 fits are HBM-bound and need the bytes in flight.
+template <int K, bool VEC>
+__global__ void __launch_bounds__(256, (VEC && K == 1) ? 3 : ((VEC && K == 2) ? 2 : 1)) em_estep2_kernel(const EmLaunch a) {
     constexpr int NACC = K * EM_NSTAT + 1;
     __shared__ __align__(16) float s_c[K * EM_COMP_STRIDE];
     __shared__ double s_acc[NACC];
@@ -181,105 +260,178 @@ __global__ void __launch_bounds__(256) em_estep2_kernel(const EmLaunch a) {
 #pragma unroll
         for (int k = 0; k < EM_NSTAT; ++k) acc[g][k] = bc(0.f);
     f2 lsum = bc(0.f);
-
-    constexpr int U = 2;  // pairs per pass: 4 samples, 12 loads in flight while the previous 4 are processed
     const unsigned n = unsigned(a.n);
     const unsigned stride = gridDim.x * blockDim.x;
-    unsigned i = blockIdx.x * blockDim.x + threadIdx.x;   // lane 0 of pair u: i + 2 u stride, lane 1: i + (2 u + 1) stride
-    float bx[2 * U], by[2 * U], bt[2 * U];
+
+    if (VEC) {
+        const float4* x4 = reinterpret_cast<const float4*>(xs);
+        const float4* y4 = reinterpret_cast<const float4*>(ys);
+        const float4* t4 = reinterpret_cast<const float4*>(ts);
+        const unsigned n4 = n >> 2;
+        const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
+        unsigned j = blockIdx.x * blockDim.x + threadIdx.x;
+        float4 bx[2], by[2], bt[2];
 #pragma unroll
-    for (int u = 0; u < 2 * U; ++u) {
-        const unsigned k = i + u * stride;
-        const bool ok = k < n;
-        bx[u] = ok ? __ldg(xs + k) : 0.f; by[u] = ok ? __ldg(ys + k) : 0.f; bt[u] = ok ? __ldg(ts + k) : 0.f;
-    }
-    for (; i < n; i += 2 * U * stride) {
-        float cx[2 * U], cy[2 * U], ct[2 * U];
+        for (int u = 0; u < 2; ++u) {
+            const unsigned k = j + u * stride;
+            const bool ok = k < n4;
+            bx[u] = ok ? __ldg(x4 + k) : zero; by[u] = ok ? __ldg(y4 + k) : zero; bt[u] = ok ? __ldg(t4 + k) : zero;
+        }
+        for (; j < n4; j += 2 * stride) {
+            float4 cx[2], cy[2], ct[2];
 #pragma unroll
-        for (int u = 0; u < 2 * U; ++u) { cx[u] = bx[u]; cy[u] = by[u]; ct[u] = bt[u]; }
+            for (int u = 0; u < 2; ++u) { cx[u] = bx[u]; cy[u] = by[u]; ct[u] = bt[u]; }
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                const unsigned k = j + (2 + u) * stride;
+                const bool ok = k < n4;
+                bx[u] = ok ? __ldg(x4 + k) : zero; by[u] = ok ? __ldg(y4 + k) : zero; bt[u] = ok ? __ldg(t4 + k) : zero;
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                if (j + u * stride >= n4) break;
+                em_pair2<K>(s_c, mk2(cx[u].x, cx[u].y), mk2(cy[u].x, cy[u].y), mk2(ct[u].x, ct[u].y), 1.f, acc, lsum);
+                em_pair2<K>(s_c, mk2(cx[u].z, cx[u].w), mk2(cy[u].z, cy[u].w), mk2(ct[u].z, ct[u].w), 1.f, acc, lsum);
+            }
+        }
+    } else {
+        constexpr int U = 2;  // pairs per pass: 4 samples, 12 loads in flight while the previous 4 are processed
+        unsigned i = blockIdx.x * blockDim.x + threadIdx.x;   // lane 0 of pair u: i + 2 u stride, lane 1: i + (2 u + 1) stride
+        float bx[2 * U], by[2 * U], bt[2 * U];
 #pragma unroll
         for (int u = 0; u < 2 * U; ++u) {
-            const unsigned k = i + (2 * U + u) * stride;
+            const unsigned k = i + u * stride;
             const bool ok = k < n;
             bx[u] = ok ? __ldg(xs + k) : 0.f; by[u] = ok ? __ldg(ys + k) : 0.f; bt[u] = ok ? __ldg(ts + k) : 0.f;
         }
+        for (; i < n; i += 2 * U * stride) {
+            float cx[2 * U], cy[2 * U], ct[2 * U];
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            if (i + 2 * u * stride >= n) break;
-            const float v1 = (i + (2 * u + 1) * stride < n) ? 1.f : 0.f;   // lane 1 may be past the end
-            const f2 x = mk2(cx[2 * u], cx[2 * u + 1]), y = mk2(cy[2 * u], cy[2 * u + 1]), t = mk2(ct[2 * u], ct[2 * u + 1]);
-            if (K == 1) {
-                // one component: the responsibility is 1 and the log-sum-exp is the log-likelihood itself; the general
-                // path below computes the same up to the rounding of its ex2 / rcp (1e-7), with 6 MUFU per pair more
-                const float4* c4 = reinterpret_cast<const float4*>(s_c);
-                const float4 ca = c4[0], cb = c4[1], cc = c4[2];
-                const f2 valid = mk2(1.f, v1);
-                const f2 d0 = add2(x, -ca.x), d1 = add2(y, -ca.y), d2 = add2(t, -ca.z);
-                const f2 q0 = fma2(d0, ca.w, fma2(d1, cb.x, mul2(d2, cb.y)));
-                const f2 q1 = fma2(d1, cb.z, mul2(d2, cb.w));
-                const f2 l1 = fma2(d0, q0, fma2(d1, q1, fma2(mul2(d2, cc.x), d2, cc.y)));
-                lsum = fma2(l1, valid, lsum);
-                const f2 r0 = mul2(valid, d0), r1 = mul2(valid, d1), r2 = mul2(valid, d2);
-                acc[0][0] = add2(acc[0][0], valid);
-                acc[0][1] = add2(acc[0][1], r0);
-                acc[0][2] = add2(acc[0][2], r1);
-                acc[0][3] = add2(acc[0][3], r2);
-                acc[0][4] = fma2(r0, d0, acc[0][4]);
-                acc[0][5] = fma2(r0, d1, acc[0][5]);
-                acc[0][6] = fma2(r0, d2, acc[0][6]);
-                acc[0][7] = fma2(r1, d1, acc[0][7]);
-                acc[0][8] = fma2(r1, d2, acc[0][8]);
-                acc[0][9] = fma2(r2, d2, acc[0][9]);
-                continue;
+            for (int u = 0; u < 2 * U; ++u) { cx[u] = bx[u]; cy[u] = by[u]; ct[u] = bt[u]; }
+#pragma unroll
+            for (int u = 0; u < 2 * U; ++u) {
+                const unsigned k = i + (2 * U + u) * stride;
+                const bool ok = k < n;
+                bx[u] = ok ? __ldg(xs + k) : 0.f; by[u] = ok ? __ldg(ys + k) : 0.f; bt[u] = ok ? __ldg(ts + k) : 0.f;
             }
-            f2 ll[K];
-            float m0 = -FLT_MAX, m1 = -FLT_MAX;
 #pragma unroll
-            for (int g = 0; g < K; ++g) {
-                const float4* c4 = reinterpret_cast<const float4*>(s_c + g * EM_COMP_STRIDE);
-                const float4 ca = c4[0], cb = c4[1], cc = c4[2];
-                const f2 d0 = add2(x, -ca.x), d1 = add2(y, -ca.y), d2 = add2(t, -ca.z);
-                const f2 q0 = fma2(d0, ca.w, fma2(d1, cb.x, mul2(d2, cb.y)));
-                const f2 q1 = fma2(d1, cb.z, mul2(d2, cb.w));
-                ll[g] = fma2(d0, q0, fma2(d1, q1, fma2(mul2(d2, cc.x), d2, cc.y)));
-                m0 = fmaxf(m0, lo(ll[g]));
-                m1 = fmaxf(m1, hi(ll[g]));
-            }
-            const f2 mm = mk2(m0, m1);
-            const f2 ms = mul2(mm, -1.4426950408889634f);
-            f2 s = bc(0.f);
-#pragma unroll
-            for (int g = 0; g < K; ++g) {
-                const f2 e = fma2(ll[g], 1.4426950408889634f, ms);
-                float e0, e1;
-                un2(e, e0, e1);
-                asm("ex2.approx.ftz.f32 %0, %0;" : "+f"(e0));
-                asm("ex2.approx.ftz.f32 %0, %0;" : "+f"(e1));
-                ll[g] = mk2(e0, e1);
-                s = add2(s, ll[g]);
-            }
-            const f2 lg = mk2(mufu_lg2(lo(s)), mufu_lg2(hi(s)));
-            const f2 valid = mk2(1.f, v1);
-            lsum = fma2(fma2(lg, 0.6931471805599453f, mm), valid, lsum);   // (m + ln s) per valid lane
-            const f2 inv = mul2(rcp2(s), valid);
-#pragma unroll
-            for (int g = 0; g < K; ++g) {
-                const float4 ca = *reinterpret_cast<const float4*>(s_c + g * EM_COMP_STRIDE);
-                const f2 r = mul2(ll[g], inv);
-                const f2 d0 = add2(x, -ca.x), d1 = add2(y, -ca.y), d2 = add2(t, -ca.z);
-                const f2 r0 = mul2(r, d0), r1 = mul2(r, d1), r2 = mul2(r, d2);
-                acc[g][0] = add2(acc[g][0], r);
-                acc[g][1] = add2(acc[g][1], r0);
-                acc[g][2] = add2(acc[g][2], r1);
-                acc[g][3] = add2(acc[g][3], r2);
-                acc[g][4] = fma2(r0, d0, acc[g][4]);
-                acc[g][5] = fma2(r0, d1, acc[g][5]);
-                acc[g][6] = fma2(r0, d2, acc[g][6]);
-                acc[g][7] = fma2(r1, d1, acc[g][7]);
-                acc[g][8] = fma2(r1, d2, acc[g][8]);
-                acc[g][9] = fma2(r2, d2, acc[g][9]);
+            for (int u = 0; u < U; ++u) {
+                if (i + 2 * u * stride >= n) break;
+                const float v1 = (i + (2 * u + 1) * stride < n) ? 1.f : 0.f;   // lane 1 may be past the end
+                em_pair2<K>(s_c, mk2(cx[2 * u], cx[2 * u + 1]), mk2(cy[2 * u], cy[2 * u + 1]), mk2(ct[2 * u], ct[2 * u + 1]), v1, acc, lsum);
             }
         }
+    }
+#pragma unroll
+    for (int g = 0; g < K; ++g)
+#pragma unroll
+        for (int k = 0; k < EM_NSTAT; ++k) {
+            double v = double(lo(acc[g][k])) + double(hi(acc[g][k]));
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if ((threadIdx.x & 31) == 0) atomicAdd(&s_acc[g * EM_NSTAT + k], v);
+        }
+    {
+        double v = double(lo(lsum)) + double(hi(lsum));
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) == 0) atomicAdd(&s_acc[NACC - 1], v);
+    }
+    __syncthreads();
+    double* st = a.stats + (size_t)fit * NACC;
+    for (int k = threadIdx.x; k < NACC; k += blockDim.x) atomicAdd(&st[k], s_acc[k]);
+}
+
+// ---- the same E-step fed by the bulk-copy engine (K <= 2: the HBM-bound fits) ---------------------------------------
+// Rows of x are contiguous 1-D arrays, so no tensor map is needed: one elected thread issues three
+// cp.async.bulk (global -> shared, completion counted in bytes on an mbarrier) per tile of EM_TMA_TILE samples,
+// EM_TMA_STAGES tiles ahead; the 256 threads wait on the stage's barrier, read their samples with LDS.128 and
+// hand the stage back with one __syncthreads.  Nothing of the stream sits in registers, so three CTAs per SM keep
+// up to 216 KB of loads in flight per SM (the register-prefetch kernel above: 74 KB).  Needs n % 4 == 0 (16-byte
+// aligned rows and tile sizes).
+#define EM_TMA_TILE 2048
+#define EM_TMA_STAGES 3
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return unsigned(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "EM_WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra EM_DONE_%=;\n"
+        "bra EM_WAIT_%=;\n"
+        "EM_DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+template <int K>
+__global__ void __launch_bounds__(256, K == 1 ? 3 : (K <= 3 ? 2 : 1)) em_estep_tma_kernel(const EmLaunch a) {
+    constexpr int NACC = K * EM_NSTAT + 1;
+    extern __shared__ __align__(128) float s_tile[];   // [EM_TMA_STAGES][3][EM_TMA_TILE]
+    __shared__ __align__(8) unsigned long long s_bar[EM_TMA_STAGES];
+    __shared__ __align__(16) float s_c[K * EM_COMP_STRIDE];
+    __shared__ double s_acc[NACC];
+    const int fit = blockIdx.y;
+    if (a.done[fit]) return;
+    const unsigned n = unsigned(a.n);
+    const unsigned n_tiles = (n + EM_TMA_TILE - 1) / EM_TMA_TILE;
+    const float* xs = a.x + (size_t)fit * 3 * a.n;
+    // this CTA's tiles: blockIdx.x, blockIdx.x + gridDim.x, ...
+    const unsigned my_tiles = blockIdx.x < n_tiles ? (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    auto issue = [&](unsigned i) {   // tile number i of this CTA into stage i % STAGES (one thread)
+        const unsigned tile = blockIdx.x + i * gridDim.x, first = tile * EM_TMA_TILE;
+        const unsigned count = n - first < EM_TMA_TILE ? n - first : EM_TMA_TILE, bytes = count * 4u;
+        unsigned long long* bar = &s_bar[i % EM_TMA_STAGES];
+        float* dst = s_tile + (i % EM_TMA_STAGES) * 3 * EM_TMA_TILE;
+        mbar_expect_tx(bar, 3 * bytes);
+        bulk_g2s(dst, xs + first, bytes, bar);
+        bulk_g2s(dst + EM_TMA_TILE, xs + a.n + first, bytes, bar);
+        bulk_g2s(dst + 2 * EM_TMA_TILE, xs + 2 * a.n + first, bytes, bar);
+    };
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < EM_TMA_STAGES; ++s) mbar_init(&s_bar[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        for (unsigned i = 0; i < EM_TMA_STAGES && i < my_tiles; ++i) issue(i);
+    }
+    for (int i = threadIdx.x; i < K * EM_COMP_STRIDE; i += blockDim.x) s_c[i] = a.comps[(size_t)fit * K * EM_COMP_STRIDE + i];
+    for (int i = threadIdx.x; i < NACC; i += blockDim.x) s_acc[i] = 0.0;
+    __syncthreads();
+    f2 acc[K][EM_NSTAT];
+#pragma unroll
+    for (int g = 0; g < K; ++g)
+#pragma unroll
+        for (int k = 0; k < EM_NSTAT; ++k) acc[g][k] = bc(0.f);
+    f2 lsum = bc(0.f);
+
+    for (unsigned i = 0; i < my_tiles; ++i) {
+        const unsigned stage = i % EM_TMA_STAGES;
+        const unsigned first = (blockIdx.x + i * gridDim.x) * EM_TMA_TILE;
+        const unsigned count = n - first < EM_TMA_TILE ? n - first : EM_TMA_TILE;
+        mbar_wait(&s_bar[stage], (i / EM_TMA_STAGES) & 1u);
+        const float4* tx = reinterpret_cast<const float4*>(s_tile + stage * 3 * EM_TMA_TILE);
+        const float4* ty = tx + EM_TMA_TILE / 4;
+        const float4* tt = ty + EM_TMA_TILE / 4;
+#pragma unroll 1
+        for (unsigned q = threadIdx.x; 4 * q < count; q += 256) {
+            const float4 vx = tx[q], vy = ty[q], vt = tt[q];
+            em_pair2<K>(s_c, mk2(vx.x, vx.y), mk2(vy.x, vy.y), mk2(vt.x, vt.y), 1.f, acc, lsum);
+            em_pair2<K>(s_c, mk2(vx.z, vx.w), mk2(vy.z, vy.w), mk2(vt.z, vt.w), 1.f, acc, lsum);
+        }
+        // every thread is done reading the stage before the bulk-copy engine may overwrite it
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        if (threadIdx.x == 0 && i + EM_TMA_STAGES < my_tiles) issue(i + EM_TMA_STAGES);
     }
 #pragma unroll
     for (int g = 0; g < K; ++g)

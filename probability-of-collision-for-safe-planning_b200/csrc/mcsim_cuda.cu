@@ -927,23 +927,30 @@ extern "C" void mcsim_cuda_io_bytes(mcsim_cuda_ctx* c, uint64_t* h2d, uint64_t* 
 
 // ---- EM fit (BASELINE config 5) ---------------------------------------------------------------------
 typedef void (*em_kernel_t)(const EmLaunch);
+#ifndef EM_TMA_MAX_K
+#define EM_TMA_MAX_K 4   // fits with at most this many components stream through the bulk-copy kernel (packed pairs)
+#endif
 template <int K>
-static void em_pick(em_kernel_t& k0, em_kernel_t& k1) {
+static void em_pick(em_kernel_t& k0, em_kernel_t& k1, bool vec, size_t& smem) {
     k0 = em_estep_kernel<K, 0>;
     k1 = nullptr;
-    if constexpr (K <= 4) k0 = em_estep2_kernel<K>;  // packed: two samples per thread
+    smem = 0;
+    if constexpr (K <= 4) k0 = em_estep2_kernel<K, false>;  // packed: two samples per thread
+    if constexpr (K <= EM_TMA_MAX_K) {  // fed by the bulk-copy engine: K = 1 is HBM-bound; K = 2..4 gain the prefetch registers back
+        if (vec) { k0 = em_estep_tma_kernel<K>; smem = sizeof(float) * EM_TMA_STAGES * 3 * EM_TMA_TILE; }
+    }
     if constexpr (K > 8) k1 = em_estep_kernel<K, 8>;
 }
-static bool em_kernels(int K, em_kernel_t& k0, em_kernel_t& k1) {
+static bool em_kernels(int K, em_kernel_t& k0, em_kernel_t& k1, bool vec, size_t& smem) {
     switch (K) {
-        case 1: em_pick<1>(k0, k1); return true;    case 2: em_pick<2>(k0, k1); return true;
-        case 3: em_pick<3>(k0, k1); return true;    case 4: em_pick<4>(k0, k1); return true;
-        case 5: em_pick<5>(k0, k1); return true;    case 6: em_pick<6>(k0, k1); return true;
-        case 7: em_pick<7>(k0, k1); return true;    case 8: em_pick<8>(k0, k1); return true;
-        case 9: em_pick<9>(k0, k1); return true;    case 10: em_pick<10>(k0, k1); return true;
-        case 11: em_pick<11>(k0, k1); return true;  case 12: em_pick<12>(k0, k1); return true;
-        case 13: em_pick<13>(k0, k1); return true;  case 14: em_pick<14>(k0, k1); return true;
-        case 15: em_pick<15>(k0, k1); return true;  case 16: em_pick<16>(k0, k1); return true;
+        case 1: em_pick<1>(k0, k1, vec, smem); return true;    case 2: em_pick<2>(k0, k1, vec, smem); return true;
+        case 3: em_pick<3>(k0, k1, vec, smem); return true;    case 4: em_pick<4>(k0, k1, vec, smem); return true;
+        case 5: em_pick<5>(k0, k1, vec, smem); return true;    case 6: em_pick<6>(k0, k1, vec, smem); return true;
+        case 7: em_pick<7>(k0, k1, vec, smem); return true;    case 8: em_pick<8>(k0, k1, vec, smem); return true;
+        case 9: em_pick<9>(k0, k1, vec, smem); return true;    case 10: em_pick<10>(k0, k1, vec, smem); return true;
+        case 11: em_pick<11>(k0, k1, vec, smem); return true;  case 12: em_pick<12>(k0, k1, vec, smem); return true;
+        case 13: em_pick<13>(k0, k1, vec, smem); return true;  case 14: em_pick<14>(k0, k1, vec, smem); return true;
+        case 15: em_pick<15>(k0, k1, vec, smem); return true;  case 16: em_pick<16>(k0, k1, vec, smem); return true;
     }
     return false;
 }
@@ -1011,16 +1018,32 @@ extern "C" int mcsim_cuda_em_estep(mcsim_cuda_ctx* c) {
     if (!c || !c->em_prepared) return fail(MCSIM_ERR_ARG, "em_estep: mcsim_cuda_em_prepare has not been called");
     CK(cudaSetDevice(c->device));
     em_kernel_t k0, k1;
-    if (!em_kernels(c->em.K, k0, k1)) return fail(MCSIM_ERR_ARG, "em_estep: bad K");
-    // chunks per fit: fill the machine with whole waves (4 CTAs of 256 threads per SM), but keep at
-    // least ~8 samples per thread so the per-CTA reduction stays small next to the streaming loop
-    const unsigned long long per_cta = 256ull * 8;
-    unsigned long long chunks = (c->em.n + per_cta - 1) / per_cta;
-    const unsigned long long cap = (unsigned long long)(c->n_sm * 4 + c->em.n_fits - 1) / c->em.n_fits;
-    if (chunks > cap) chunks = cap;
-    if (chunks < 1) chunks = 1;
+    // 128-bit loads when every row of every fit is 16-byte aligned
+    const bool vec = (c->em.n % 4) == 0 && c->em.n >= 4;
+    size_t smem = 0;
+    if (!em_kernels(c->em.K, k0, k1, vec, smem)) return fail(MCSIM_ERR_ARG, "em_estep: bad K");
+    if (smem > 48 * 1024) CK(cudaFuncSetAttribute((const void*)k0, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    // chunks per fit: whole waves of resident CTAs with as little tail as possible (616 CTAs on 444 resident slots
+    // ran at 70 % of what 392 do), at least ~8 samples per thread so the per-CTA reduction stays small
+    int occ = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)k0, 256, smem));
+    if (k1) { int o1 = 0; CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, (const void*)k1, 256, 0)); if (o1 < occ) occ = o1; }
+    if (occ < 1) occ = 1;
+    const unsigned long long resident = (unsigned long long)c->n_sm * occ, F = (unsigned long long)c->em.n_fits;
+    const unsigned long long per_cta = smem ? EM_TMA_TILE : 256ull * 8;
+    const unsigned long long most = (c->em.n + per_cta - 1) / per_cta ? (c->em.n + per_cta - 1) / per_cta : 1;
+    unsigned long long chunks = 1;
+    double best = -1.0;
+    for (unsigned long long w = 1; w <= 4; ++w) {
+        unsigned long long ch = w * resident / F;
+        if (ch < 1) ch = 1;
+        if (ch > most) ch = most;
+        const unsigned long long ctas = ch * F, waves = (ctas + resident - 1) / resident;
+        const double eff = double(ctas) / double(waves * resident);
+        if (eff > best + 0.02) { best = eff; chunks = ch; }
+    }
     const dim3 grid((unsigned)chunks, (unsigned)c->em.n_fits);
-    k0<<<grid, 256, 0, c->stream>>>(c->em);
+    k0<<<grid, 256, smem, c->stream>>>(c->em);
     ++c->launches;
     if (k1) { k1<<<grid, 256, 0, c->stream>>>(c->em); ++c->launches; }
     CK(cudaGetLastError());

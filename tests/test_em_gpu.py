@@ -102,3 +102,24 @@ def test_em_split_api_two_shards_equal_whole(ctx):
     np.testing.assert_allclose(ra["means"], whole["means"], rtol=1e-6)
     np.testing.assert_allclose(ra["fcovs"], whole["fcovs"], rtol=1e-4, atol=1e-9)
     np.testing.assert_allclose(ra["hefts"], whole["hefts"], rtol=1e-5)
+
+
+def test_em_bulk_copy_path_vs_live_reference(ctx):
+    """K <= 4 with n % 4 == 0 streams through em_estep_tma_kernel (cp.async.bulk + mbarrier pipeline, 2,048-sample
+    tiles, 3 stages): many tiles per CTA, a ragged last tile, several fits per launch, against Armadillo run here;
+    and the same fit one sample shorter (n % 4 != 0: the register-prefetch kernel) must agree with it closely."""
+    import oracle_ref
+    import pcoll_b200
+    if not oracle_ref.available():
+        pytest.skip("oracle/_ref not built")
+    for K, n in ((1, 40004), (2, 123460), (2, 2048 * 9), (4, 50000)):
+        probs = [pcoll_b200.inputs.synthetic_em_problem(50 + f, n, K, centre=(0.3 * f, 1.0, 0.2)) for f in range(3)]
+        x = np.stack([p[0] for p in probs]); h = np.stack([p[1] for p in probs])
+        m = np.stack([p[2] for p in probs]); c = np.stack([p[3] for p in probs])
+        out = ctx.em_fit(x, h, m, c, 4)
+        for f in range(3):
+            rm, rc, rh, rl = oracle_ref.em_fit(x[f].T.astype(np.float64), m[f], c[f].reshape(K, 9), h[f], 4)
+            eh, em, ec = _errors(out, rh, rm, rc.reshape(K, 3, 3), f)
+            assert max(eh, em, ec) < RTOL, (K, n, f, eh, em, ec)
+        shorter = ctx.em_fit(np.ascontiguousarray(x[:, :, :n - 1]), h, m, c, 4)
+        np.testing.assert_allclose(shorter["means"], out["means"], rtol=1e-3, atol=1e-4)
