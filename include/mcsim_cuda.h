@@ -169,6 +169,12 @@ int mcsim_host_thread(const mcsim_mc_params* p, const double* normals, size_t n_
  * Philox GMM mode). */
 int mcsim_host_normals(uint64_t seed, uint32_t stream_id, int T, int per_step, double* out);
 
+/* The 12 standard normals one Philox-mode rollout draws for the step t -> t+1 (3 odometry, then the
+ * observations), recomputed on the host in FP64 from the same bits the kernels use: two Philox4x32-10
+ * blocks, counter = (rollout id lo, hi, 8 t + {0, 1}, PURPOSE_STEP), key = seed, six Box-Muller pairs at
+ * 24 radius + 16 angle bits (csrc/philox.h, "step draws").  For audits of the Philox mode; no GPU. */
+int mcsim_step_normals(uint64_t seed, uint64_t rollout_id, int t, double out[12]);
+
 /* ---- GMM truncation (moment matching) ---------------------------------------------------- */
 typedef struct {
     int K;                       /* components (setNumGaussians) */

@@ -44,6 +44,34 @@ __device__ __forceinline__ void box_muller2(unsigned a0, unsigned b0, unsigned a
     n1 = mul2(r, s);
 }
 
+// the same from the 24 radius + 16 angle bits of one step pair per lane (philox.h: step draws).
+// MC_ANGLE_PRMT = 1 (default; 3.637 vs 3.628e10 rollout-steps/s): the 16-bit halves become floats on the ALU pipe (one PRMT each: 0x4B000000 | a =
+// 2^23 + a, and the 2^23 leaves in a packed add); 0: plain conversion, for which ptxas picks I2F.U16
+// (one instruction, but on the XU pipe next to the MUFUs).
+#ifndef MC_ANGLE_PRMT
+#define MC_ANGLE_PRMT 1
+#endif
+__device__ __forceinline__ float half16f(unsigned w, int h) {
+#if MC_ANGLE_PRMT
+    return __uint_as_float(__byte_perm(w, 0x4B000000u, h ? 0x7632u : 0x7610u));
+#else
+    return float(h ? (w >> 16) : (w & 0xffffu));
+#endif
+}
+__device__ __forceinline__ void box_muller2_bits(unsigned r0, float a0, unsigned r1, float a1, f2& n0, f2& n1) {
+    const f2 ua = fma2(mk2(float(r0), float(r1)), MCSIM_U24_SCALE, MCSIM_U24_HALF);
+#if MC_ANGLE_PRMT
+    const f2 th = fma2(add2(mk2(a0, a1), -8388608.0f), MCSIM_A16_SCALE, MCSIM_A16_HALF);
+#else
+    const f2 th = fma2(mk2(a0, a1), MCSIM_A16_SCALE, MCSIM_A16_HALF);
+#endif
+    const f2 r = sqrt2(mul2(mk2(mufu_lg2(lo(ua)), mufu_lg2(hi(ua))), -1.3862943611198906f));
+    f2 s, c;
+    sincos2(th, s, c);
+    n0 = mul2(r, c);
+    n1 = mul2(r, s);
+}
+
 struct Philox2 {
     mcsim_rng::u32x4 a, b;
 };
@@ -207,13 +235,19 @@ __device__ __forceinline__ void step2(Rollout2& st, const float* r, int t, unsig
     f2 (&mu)[3] = st.mu;
     f2 (&S)[6] = st.S;
     // ---- step t -> t+1 of this rollout's own real robot + EKF
-    // noise: block 0 = (rot1, trans, rot2, obs 0), block 1 = obs 1..4, block 2 = obs 5..7
-    f2 zn[4 * ((3 + NL + 3) / 4)];
+    // noise: (rot1, trans, rot2, obs 0 .. NL-1), 12 normals per two Philox blocks (philox.h: step draws)
+    f2 zn[12 * ((3 + NL + 11) / 12)];
 #pragma unroll
-    for (int jb = 0; jb < (3 + NL + 3) / 4; ++jb) {
-        const Philox2 w = philox_pair(id0, id1, unsigned(t * 8 + jb), unsigned(mcsim_rng::PURPOSE_STEP), k0, k1);
-        box_muller2(w.a.x, w.a.y, w.b.x, w.b.y, zn[4 * jb], zn[4 * jb + 1]);
-        box_muller2(w.a.z, w.a.w, w.b.z, w.b.w, zn[4 * jb + 2], zn[4 * jb + 3]);
+    for (int g = 0; g < (3 + NL + 11) / 12; ++g) {
+        const Philox2 wa = philox_pair(id0, id1, unsigned(t * 8 + 2 * g), unsigned(mcsim_rng::PURPOSE_STEP), k0, k1);
+        const Philox2 wb = philox_pair(id0, id1, unsigned(t * 8 + 2 * g + 1), unsigned(mcsim_rng::PURPOSE_STEP), k0, k1);
+        unsigned rad0[6], ang0[6], rad1[6], ang1[6];
+        mcsim_rng::step_bits(wa.a, wb.a, rad0, ang0);  // (the integer angle halves are dead code here)
+        mcsim_rng::step_bits(wa.b, wb.b, rad1, ang1);
+        const unsigned aw0[3] = {wb.a.y, wb.a.z, wb.a.w}, aw1[3] = {wb.b.y, wb.b.z, wb.b.w};
+#pragma unroll
+        for (int j = 0; j < 6; ++j)
+            box_muller2_bits(rad0[j], half16f(aw0[j >> 1], j & 1), rad1[j], half16f(aw1[j >> 1], j & 1), zn[12 * g + 2 * j], zn[12 * g + 2 * j + 1]);
     }
     // applied control (generateL + :719-726): u = u_req = inverseOdometry(mu, x*_{t+1}); u*_0 at t = 0
     f2 u[3];

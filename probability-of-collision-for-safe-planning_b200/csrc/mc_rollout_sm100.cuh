@@ -168,14 +168,16 @@ __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
                 const float xg[3] = {r[STRIDE], r[STRIDE + 1], r[STRIDE + 2]};
                 const int L = NL > 0 ? NL : c_mc.nm.L;
                 // noise draws of this step: 3 odometry + L observation normals
-                float zn[NL > 0 ? 4 * ((3 + NL + 3) / 4) : 4 * ((3 + MCSIM_MAX_LANDMARKS + 3) / 4)];
-                const int nblk = (3 + L + 3) >> 2;
+                float zn[NL > 0 ? 12 * ((3 + NL + 11) / 12) : 12 * ((3 + MCSIM_MAX_LANDMARKS + 11) / 12)];
+                const int ngrp = (3 + L + 11) / 12;  // 12 normals per two Philox blocks (philox.h: step draws)
 #pragma unroll
-                for (int j = 0; j < nblk; ++j) {
-                    mcsim_rng::u32x4 c = {unsigned(id), unsigned(id >> 32), unsigned(t * 8 + j), unsigned(mcsim_rng::PURPOSE_STEP)};
-                    c = mcsim_rng::philox4x32_10(c, a.k0, a.k1);
-                    mcsim_rng::box_muller(c.x, c.y, zn[4 * j], zn[4 * j + 1]);
-                    mcsim_rng::box_muller(c.z, c.w, zn[4 * j + 2], zn[4 * j + 3]);
+                for (int g = 0; g < ngrp; ++g) {
+                    const mcsim_rng::u32x4 ca = {unsigned(id), unsigned(id >> 32), unsigned(t * 8 + 2 * g), unsigned(mcsim_rng::PURPOSE_STEP)};
+                    const mcsim_rng::u32x4 cb = {unsigned(id), unsigned(id >> 32), unsigned(t * 8 + 2 * g + 1), unsigned(mcsim_rng::PURPOSE_STEP)};
+                    unsigned rad[6], ang[6];
+                    mcsim_rng::step_bits(mcsim_rng::philox4x32_10(ca, a.k0, a.k1), mcsim_rng::philox4x32_10(cb, a.k0, a.k1), rad, ang);
+#pragma unroll
+                    for (int j = 0; j < 6; ++j) mcsim_rng::box_muller_bits(rad[j], ang[j], zn[12 * g + 2 * j], zn[12 * g + 2 * j + 1]);
                 }
                 float u[3], pmu[3], pS[9], un[3], nx[3];
                 applied_control(xs, mu, xg, us, u);

@@ -592,6 +592,23 @@ extern "C" int mcsim_cuda_mc_run(mcsim_cuda_ctx* c, const mcsim_mc_params* p, mc
     return MCSIM_OK;
 }
 
+// the step draws of one Philox-mode rollout, host FP64 (csrc/philox.h: step draws)
+extern "C" int mcsim_step_normals(uint64_t seed, uint64_t rollout_id, int t, double out[12]) {
+    if (!out || t < 0) return MCSIM_ERR_ARG;
+    const unsigned k0 = unsigned(seed), k1 = unsigned(seed >> 32);
+    const mcsim_rng::u32x4 ca = {unsigned(rollout_id), unsigned(rollout_id >> 32), unsigned(t * 8), unsigned(mcsim_rng::PURPOSE_STEP)};
+    const mcsim_rng::u32x4 cb = {unsigned(rollout_id), unsigned(rollout_id >> 32), unsigned(t * 8 + 1), unsigned(mcsim_rng::PURPOSE_STEP)};
+    uint32_t rad[6], ang[6];
+    mcsim_rng::step_bits(mcsim_rng::philox4x32_10(ca, k0, k1), mcsim_rng::philox4x32_10(cb, k0, k1), rad, ang);
+    for (int j = 0; j < 6; ++j) {
+        const double u = (double(rad[j]) + 0.5) / 16777216.0, th = 2 * MCSIM_PI * (double(ang[j]) + 0.5) / 65536.0;
+        const double r = sqrt(-2.0 * log(u));
+        out[2 * j] = r * cos(th);
+        out[2 * j + 1] = r * sin(th);
+    }
+    return MCSIM_OK;
+}
+
 // ---- GMM mode -----------------------------------------------------------------------------------
 // two standard normals from one Philox block, host side (the host thread of a Philox-mode GMM run)
 extern "C" int mcsim_host_normals(uint64_t seed, uint32_t stream_id, int T, int per_step, double* out) {

@@ -143,6 +143,8 @@ def lib():
         L.mcsim_cuda_mc_counters.restype = vp
         L.mcsim_host_thread.argtypes = [C.POINTER(McParams), _dp, C.c_size_t, _dp, _dp, _dp, _dp, _dp, _dp]
         L.mcsim_host_normals.argtypes = [C.c_uint64, C.c_uint32, C.c_int, C.c_int, _dp]
+        L.mcsim_step_normals.argtypes = [C.c_uint64, C.c_uint64, C.c_int, _dp]
+        L.mcsim_step_normals.restype = C.c_int
         L.mcsim_cuda_gmm_truncate.argtypes = [vp, C.POINTER(GmmTruncateParams), C.POINTER(GmmTruncateResult)]
         L.mcsim_cuda_gmm_run.argtypes = [vp, C.POINTER(McParams), C.POINTER(GmmRunParams), C.POINTER(GmmRunResult)]
         L.mcsim_cuda_gmm_run_batch.argtypes = [vp, C.POINTER(McParams), C.POINTER(GmmBatchParams), C.POINTER(GmmBatchResult)]
