@@ -1172,12 +1172,38 @@ extern "C" int mcsim_cuda_score_prepare(mcsim_cuda_ctx* c, const mcsim_score_par
     a.plans = (const float*)c->sc_plans.p;
     a.pairs = (const float4*)c->pairs_f.p;
     a.T = T; a.n_plans = NP; a.n_pairs = c->n_pairs;
-    // whole waves of resident CTAs: one CTA per plan when there are enough plans, else split the rollouts
-    const int want = c->n_sm * 4;
-    int chunks = (want + NP - 1) / NP;
-    const unsigned long long max_chunks = (p->rollouts + 255) / 256;
-    if ((unsigned long long)chunks > max_chunks) chunks = int(max_chunks ? max_chunks : 1);
-    a.chunks = chunks < 1 ? 1 : chunks;
+    // CTAs = plans x chunks of a plan's rollouts, in whole waves of resident CTAs: every CTA of a launch runs
+    // the same number of rollout-steps, so n CTAs on s resident slots take ceil(n / s) CTA lifetimes and a
+    // launch of 1.08 waves (128 plans x 5 chunks on 592 slots) runs at 54 % of the machine.  Take the chunk
+    // count with the fullest last wave; a chunk keeps >= 512 rollouts (two passes of a CTA) when the plan has
+    // them, so that the per-CTA prologue (tables + candidate lists) stays below 1 % of its work.  Rollout ids
+    // do not depend on the split (plan id << 32 | rollout), so the hits do not either.
+    {
+        score_kernel_t k = pick_score(p->estimator, p->early_exit != 0);
+        const size_t smem = sizeof(float4) * 2 * size_t(a.n_pairs) + sizeof(float) * size_t(T) * MC_PLAN2_STRIDE +
+                            sizeof(unsigned short) * size_t(T) * SCORE_CAND_CAP + size_t(T) + 16;
+        int per_sm = 4;
+        if (smem <= 200 * 1024) {
+            if (smem > 40 * 1024) CK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+            CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void*)k, 128, smem));
+            if (per_sm < 1) per_sm = 1;
+        }
+        const unsigned long long slots = (unsigned long long)c->n_sm * per_sm;
+        unsigned long long max_chunks = p->rollouts / 512;
+        if (max_chunks < 1) max_chunks = (p->rollouts + 255) / 256;
+        if (max_chunks < 1) max_chunks = 1;
+        if (max_chunks > 4096) max_chunks = 4096;
+        unsigned long long best_ch = 1;
+        double best = -1.0;
+        for (unsigned long long ch = 1; ch <= max_chunks; ++ch) {
+            const unsigned long long n = (unsigned long long)NP * ch, waves = (n + slots - 1) / slots;
+            // rollouts of a chunk are rounded up to whole passes of 256: count the padding as lost work too
+            const unsigned long long per = (p->rollouts + ch - 1) / ch, passes = (per + 255) / 256;
+            const double eff = double(p->rollouts) * NP / (double(waves) * slots * passes * 256.0);
+            if (eff > best + 0.005) { best = eff; best_ch = ch; }
+        }
+        a.chunks = int(best_ch);
+    }
     a.rollouts = p->rollouts;
     a.plan_offset = p->plan_offset;
     a.k0 = unsigned(p->seed); a.k1 = unsigned(p->seed >> 32);
