@@ -394,8 +394,8 @@ static void build_cull_lists(const mcsim_cuda_ctx* c, const double* trajectory, 
                 need.emplace_back(dist - c->h_reach[h] - 1e-3, b);
             }
             std::sort(need.begin(), need.end());
-            double m = MC_CULL_M0;
-            for (int k = 0; k < MC_CULL_LEVELS; ++k, m *= 2) {
+            for (int k = 0; k < MC_CULL_LEVELS; ++k) {
+                const double m = sqrt(mc_cull_margin_sq(k));
                 size_t n = 0;
                 while (n < need.size() && need[n].first <= m) ++n;
                 if (n > MC_CULL_CAP) overflow[k] = true;

@@ -163,7 +163,7 @@ __device__ __forceinline__ bool robot_hits_grouped(const float4* __restrict__ ta
 
 // ---- exact broad phase (candidate lists built on the host per plan waypoint: mcsim_cuda.cu build_cull_lists) -------
 // Per waypoint t and hull h the pairs whose box footprint lies within reach_h + m of the nominal position x*_t,
-// sorted by the smallest such m, and how many of them are needed for m = MC_CULL_M0 * 2^k, k < MC_CULL_LEVELS.
+// sorted by the smallest such m, and how many of them are needed for the margins m_k of the MC_CULL_LEVELS levels (mc_cull_margin_sq below).
 // A hull whose robot pose is within m of x*_t cannot touch any other box (every hull point is within reach_h of
 // the pose), so a warp whose poses are all within m_k of x*_t tests the first cnt[t][h][k] listed pairs; a warp
 // with a pose further out than the last level (or a list longer than MC_CULL_CAP) tests every live pair.  The
@@ -171,14 +171,25 @@ __device__ __forceinline__ bool robot_hits_grouped(const float4* __restrict__ ta
 // table), so flags and counts are bit-identical to the exhaustive test's; executed pair tests are counted.
 // Table (32-bit words): cnt[T][n_hulls][MC_CULL_LEVELS] bytes (255 = list too long), padded to 4 bytes, then
 // idx[T][n_hulls][MC_CULL_CAP] x (16-bit pair record offset, 16-bit class header offset) into the grouped table.
-#define MC_CULL_LEVELS 4
+#ifndef MC_CULL_SUB
+#define MC_CULL_SUB 2  // mantissa bits of the squared deviation that enter the level (2^SUB levels per octave of d^2)
+#endif
+#define MC_CULL_LEVELS (8 << MC_CULL_SUB)
 #define MC_CULL_CAP 16
-#define MC_CULL_M0 0.1f
 #define MC_CULL_OVERFLOW 255
+// squared margin of level k = (1 + (k mod 2^SUB) / 2^SUB) * 2^(k / 2^SUB - 7) m^2: the float whose bit pattern is
+// (MC_CULL_B0 + k) << (23 - SUB).  SUB = 2: 32 levels, m = 0.088, 0.099, 0.108, 0.117, 0.125, ... 1.0, 1.12, 1.22, 1.32 m
+#define MC_CULL_B0 (120u << MC_CULL_SUB)
+static inline double mc_cull_margin_sq(int k) { return ldexp(1.0 + double(k & ((1 << MC_CULL_SUB) - 1)) / double(1 << MC_CULL_SUB), (k >> MC_CULL_SUB) - 7); }
 
-// level of a squared deviation (NaN -> exhaustive)
+// level of a squared deviation = smallest k with d2max <= margin_sq(k), read off the exponent and leading mantissa
+// bits (exact: no rounding between this test and the host's margins); beyond the last level, NaN and negative
+// patterns -> exhaustive
 __device__ __forceinline__ int cull_level(float d2max) {
-    return d2max <= MC_CULL_M0 * MC_CULL_M0 ? 0 : (d2max <= 4.f * MC_CULL_M0 * MC_CULL_M0 ? 1 : (d2max <= 16.f * MC_CULL_M0 * MC_CULL_M0 ? 2 : (d2max <= 64.f * MC_CULL_M0 * MC_CULL_M0 ? 3 : MC_CULL_LEVELS)));
+    const unsigned b = __float_as_uint(d2max);
+    const unsigned u = ((b ? b : 1u) - 1u) >> (23 - MC_CULL_SUB);  // patterns in ((B0 + k - 1) << s, (B0 + k) << s] -> B0 + k - 1
+    const unsigned k = u >= MC_CULL_B0 ? u - (MC_CULL_B0 - 1u) : 0u;
+    return k < unsigned(MC_CULL_LEVELS) ? int(k) : MC_CULL_LEVELS;
 }
 
 // listed pairs of waypoint t at level lev; cnt / idx point at the waypoint's slices ([n_hulls][LEVELS], [n_hulls][CAP])

@@ -20,5 +20,6 @@ ctx.set_scene(sc["boxes"], sc["hulls"])
 p, keep = abi.make_mc_params(plan, n_rollouts=N, mode=abi.MODE_PHILOX, early_exit=False, precise=precise)
 for _ in range(2):
     out = ctx.mc_run(p)
-print("N=%d P=%.5f kernel %.3f ms  %.3e rollout-steps/s" % (N, out["P"], out["kernel_ms"], out["executed_steps"] / out["kernel_ms"] * 1e3))
+print("N=%d P=%.5f hits=%d kernel %.3f ms  %.3e rollout-steps/s  %.3f pair tests per step" %
+      (N, out["P"], out["hits"], out["kernel_ms"], out["executed_steps"] / out["kernel_ms"] * 1e3, out["pair_tests"] / max(out["executed_steps"], 1)))
 ctx.close()
