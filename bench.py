@@ -474,7 +474,7 @@ def extras_scoring_em(ctx, abi, plan, sc, fp32_peak):
     n_plans, T4, R = 128, 500, 65536
     tr, od = inp.synthetic_plans(4096, n_plans, T4, boxes)
     ctx.set_scene(boxes, sc["hulls"])
-    for name, margin, plans, rollouts in (("score_config4_broad_phase", 1.5, n_plans, R), ("score_config4_exhaustive", -1.0, 16, 16384)):
+    for name, margin, plans, rollouts in (("score_config4_broad_phase", 3.0, n_plans, R), ("score_config4_exhaustive", -1.0, 16, 16384)):
         ctx.score_prepare(plan, tr[:plans], od[:plans], rollouts, margin=margin)
         ctx.score_launch()
         ctx.score_collect()

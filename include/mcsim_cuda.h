@@ -325,8 +325,10 @@ typedef struct {
     int estimator;               /* MCSIM_EST_* */
     int early_exit;
     uint64_t seed;
-    double margin;               /* broad phase: rollouts within `margin` metres of the nominal waypoint
-                                    test only the boxes within reach of it (exact, see score_sm100.cuh);
+    double margin;               /* broad phase: largest deviation from the nominal waypoint served by the
+                                    candidate lists (8 levels, margin * 2^((k - 7) / 2) metres; a warp tests
+                                    the boxes within reach at the level of its furthest rollout -- exact, see
+                                    score_sm100.cuh; 3.0 is the measured optimum of BASELINE config 4);
                                     < 0: every live pair at every step */
 } mcsim_score_params;
 

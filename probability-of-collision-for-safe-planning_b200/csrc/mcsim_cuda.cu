@@ -1180,8 +1180,7 @@ extern "C" int mcsim_cuda_score_prepare(mcsim_cuda_ctx* c, const mcsim_score_par
     // do not depend on the split (plan id << 32 | rollout), so the hits do not either.
     {
         score_kernel_t k = pick_score(p->estimator, p->early_exit != 0);
-        const size_t smem = sizeof(float4) * 2 * size_t(a.n_pairs) + sizeof(float) * size_t(T) * MC_PLAN2_STRIDE +
-                            sizeof(unsigned short) * size_t(T) * SCORE_CAND_CAP + size_t(T) + 16;
+        const size_t smem = score_smem_bytes(T, a.n_pairs, c->n_hulls);
         int per_sm = 4;
         if (smem <= 200 * 1024) {
             if (smem > 40 * 1024) CK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
@@ -1220,8 +1219,7 @@ extern "C" int mcsim_cuda_score_launch(mcsim_cuda_ctx* c) {
     CK(cudaSetDevice(c->device));
     const ScoreLaunch& a = c->sc;
     score_kernel_t k = pick_score(c->sc_est, c->sc_ee != 0);
-    const size_t smem = sizeof(float4) * 2 * size_t(a.n_pairs) + sizeof(float) * size_t(a.T) * MC_PLAN2_STRIDE +
-                        sizeof(unsigned short) * size_t(a.T) * SCORE_CAND_CAP + size_t(a.T) + 16;
+    const size_t smem = score_smem_bytes(a.T, a.n_pairs, c->n_hulls);
     if (smem > 200 * 1024) return fail(MCSIM_ERR_ARG, "score: %zu bytes of shared memory needed (T=%d, %d pairs)", smem, a.T, a.n_pairs);
     if (smem > 40 * 1024) CK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     k<<<unsigned(a.n_plans) * unsigned(a.chunks), 128, smem, c->stream>>>(a);

@@ -399,7 +399,7 @@ class Context:
         return r, out
 
     def score_plans(self, model, trajectories, odometry, rollouts, plan_offset=0, estimator=EST_REFERENCE,
-                    early_exit=False, seed=0x5AFEC0DE, margin=1.5):
+                    early_exit=False, seed=0x5AFEC0DE, margin=3.0):
         """model: dict(alphas, Q, landmarks[2, 8], cov0); trajectories [n, 3, T], odometry [n, 3, T-1]."""
         p, keep = self._score_params(model, trajectories, odometry, rollouts, plan_offset, estimator, early_exit, seed, margin)
         r, out = self._score_result(int(p.n_plans))
@@ -410,7 +410,7 @@ class Context:
     def score_prepare(self, model, trajectories, odometry, rollouts, **kw):
         p, keep = self._score_params(model, trajectories, odometry, rollouts, kw.get("plan_offset", 0),
                                      kw.get("estimator", EST_REFERENCE), kw.get("early_exit", False),
-                                     kw.get("seed", 0x5AFEC0DE), kw.get("margin", 1.5))
+                                     kw.get("seed", 0x5AFEC0DE), kw.get("margin", 3.0))
         self._score_n = int(p.n_plans)
         check(lib().mcsim_cuda_score_prepare(self._h, C.byref(p)))
 

@@ -73,3 +73,25 @@ def test_planner_to_scorer_loop(tmp_path):
     assert len(P) >= 3 and all(0.0 <= p <= 1.0 for p in P)
     assert P[-1] <= P[0] + 0.02 and out["chosen"] == int(np.argmin(P))
     assert os.path.isfile(out["files"][0]) and os.path.isfile(out["files"][1])
+
+
+def test_broad_phase_levels_with_overflowing_lists(ctx, plan):
+    """1,000 boxes: at wide margins the 16 list entries of a waypoint do not hold every pair, so the upper levels
+    fall back to the exhaustive test while the lower ones keep their lists -- hits must not change."""
+    import pcoll_b200
+    inp = pcoll_b200.inputs
+    boxes = inp.synthetic_obstacle_field(11, 1000)
+    ctx.set_scene(boxes, _hulls())
+    tr, od = inp.synthetic_plans(11, 6, 80, boxes, clear=-0.25)
+    R = 2048 + 5
+    full = ctx.score_plans(plan, tr, od, R, margin=-1.0)
+    assert full["pair_tests"] == full["executed_steps"] * 1000
+    tests = []
+    for m in (0.5, 3.0, 8.0, 40.0):
+        o = ctx.score_plans(plan, tr, od, R, margin=m)
+        np.testing.assert_array_equal(o["hits"], full["hits"])
+        tests.append(o["pair_tests"] / o["executed_steps"])
+    print("pair tests per rollout-step at margins 0.5 / 3 / 8 / 40 m: %.1f %.1f %.1f %.1f (exhaustive 1000)" % tuple(tests))
+    assert tests[1] < 100
+    print("P per plan:", np.round(full["P"], 3))
+    assert full["hits"].sum() > 0
