@@ -43,6 +43,8 @@ import numpy as np  # noqa: E402
 
 GOLD = os.path.join(ROOT, "tests", "golden")
 F_PHILOX_STEP, F_SAT, F_GMM_SAMPLE = 647, 40, 35  # algorithmic flops (DESIGN.md "Algorithmic work")
+# algorithmic MUFU operations of one Philox rollout-step: 2 moves x 2 + 11 normals x 2.5 + controller 6 + 8 updates x 2
+SFU_PHILOX_STEP = 2 * 2 + 11 * 2.5 + 6 + 8 * 2
 METRIC, UNIT = "mc_rollout_steps_per_s", "rollout-steps/s"
 
 
@@ -320,11 +322,14 @@ def main():
             "bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,
             "traffic": None,
             "traffic_note": "no HBM input: tables in __constant__ / shared memory, state in registers; ncu capture of a 4e6-rollout "
-                            "launch: dram__bytes_read 52 KB, dram__bytes_write 0 (profiles/r01_philox2_grouped_ncu_summary.csv)",
+                            "launch: dram__bytes_read 52 KB, dram__bytes_write 0 (profiles/r01_philox2_ladder_ncu_summary.csv)",
             "kernel": "mc_philox2_kernel<no early exit, reference estimator, L=8> (two rollouts per thread, packed FP32 pairs)",
             "kernel_ms_per_launch": kernel_ms / a.steps,
             "algorithmic": "%d flops per Philox rollout-step + %d per SAT pair test x %.1f live pair tests per step" % (
                 F_PHILOX_STEP, F_SAT, tot["pair_tests"] / job_steps),
+            "sfu": {"achieved": job_steps * SFU_PHILOX_STEP / world / (kernel_ms * 1e-3) / 1e12, "peak": mufu_peak, "unit": "Top/s",
+                    "frac": job_steps * SFU_PHILOX_STEP / world / (kernel_ms * 1e-3) / 1e12 / mufu_peak,
+                    "algorithmic": "%.1f MUFU operations per Philox rollout-step; the FP32 and SFU pipes run side by side, the fractions do not add" % SFU_PHILOX_STEP},
             "peak_source": "FFMA-chain microbenchmark (csrc/peaks_sm100.cuh) measured in this process; MUFU peak %.3f Top/s" % mufu_peak,
             "file_peaks": read_measured_peaks(),
             "every_pair_tested": every_pair,
