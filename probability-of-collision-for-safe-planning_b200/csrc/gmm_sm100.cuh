@@ -24,6 +24,8 @@
 #ifndef MCSIM_GMM_CUH
 #define MCSIM_GMM_CUH
 
+#include <cooperative_groups.h>
+
 #include "estimator_math.h"
 #include "philox.h"
 #include "sat_device.cuh"
@@ -542,7 +544,8 @@ __device__ __forceinline__ void gmm_refit_moments(double* cp, const double* st, 
     }
 }
 // Part 2 (after every component's part 1): weight, p_t, records, EKFpredict + EKFupdate to waypoint t+1, Cholesky.
-__device__ __forceinline__ void gmm_refit_finish(const GmmLaunch& a, int t, int g, double* cp, const double* s_free, const double* s_coll) {
+__device__ __forceinline__ void gmm_refit_finish(const GmmLaunch& a, int t, int g, double* cp, const double* s_free, const double* s_coll,
+                                                 const GmmStepTable* staged_step = nullptr) {
     using namespace mcsim_math;
     const int K = a.K;
     double tf = 0, tc = 0;
@@ -555,7 +558,7 @@ __device__ __forceinline__ void gmm_refit_finish(const GmmLaunch& a, int t, int 
     if (t == a.T - 1 && a.rec_post) for (int k = 0; k < GMM_REC; ++k) a.rec_post[g * GMM_REC + k] = cp[k];
     // ---- move the component to waypoint t+1: EKFpredict (:766-772) then EKFupdate (:804-812)
     if (a.do_ekf && t < a.T - 1) {
-        const GmmStepTable& s = a.steps[t];
+        const GmmStepTable& s = staged_step ? *staged_step : a.steps[t];
         NoiseModel<double> nm;
         nm.Q = a.Q; nm.L = a.L;
         for (int l = 0; l < a.L; ++l) { nm.lx[l] = a.lx[l]; nm.ly[l] = a.ly[l]; }
@@ -575,19 +578,32 @@ __device__ __forceinline__ void gmm_refit_finish(const GmmLaunch& a, int t, int 
     }
 }
 
+// The mixture, the statistics and the step record are staged in shared memory first: the refit is one long dependent
+// FP64 chain per component, and every read-modify-write of the record in global memory was a round trip to L2 on it.
 __global__ void __launch_bounds__(32) gmm_refit_kernel(const GmmLaunch a_in) {
     const GmmLaunch a = gmm_member(a_in, blockIdx.x);
     __shared__ double s_free[MCSIM_MAX_GAUSSIANS], s_coll[MCSIM_MAX_GAUSSIANS];
+    __shared__ double s_cp[MCSIM_MAX_GAUSSIANS * GMM_COMP], s_st[MCSIM_MAX_GAUSSIANS * GMM_STAT];
+    __shared__ GmmStepTable s_step;
     const int g = threadIdx.x;
     const int K = a.K;
-    double* cp = a.comps + g * GMM_COMP;
-    if (g < K) gmm_refit_moments(cp, a.stats + g * GMM_STAT, a.degenerate, s_free[g], s_coll[g]);
-    __syncthreads();
-    if (g < K) {
-        gmm_refit_finish(a, a.t, g, cp, s_free, s_coll);
-        for (int k = 0; k < GMM_STAT; ++k) a.stats[g * GMM_STAT + k] = 0.0;
-        a.hist[g] = 0;
+    const bool ekf = a.do_ekf && a.t < a.T - 1;
+    for (int i = g; i < K * GMM_COMP; i += 32) s_cp[i] = a.comps[i];
+    for (int i = g; i < K * GMM_STAT; i += 32) s_st[i] = a.stats[i];
+    if (ekf) {
+        const double* src = reinterpret_cast<const double*>(a.steps + a.t);
+        double* dst = reinterpret_cast<double*>(&s_step);
+        for (int i = g; i < int(sizeof(GmmStepTable) / sizeof(double)); i += 32) dst[i] = src[i];
     }
+    __syncthreads();
+    double* cp = s_cp + g * GMM_COMP;
+    if (g < K) gmm_refit_moments(cp, s_st + g * GMM_STAT, a.degenerate, s_free[g], s_coll[g]);
+    __syncthreads();
+    if (g < K) gmm_refit_finish(a, a.t, g, cp, s_free, s_coll, ekf ? &s_step : nullptr);
+    __syncthreads();
+    for (int i = g; i < K * GMM_COMP; i += 32) a.comps[i] = s_cp[i];
+    for (int i = g; i < K * GMM_STAT; i += 32) a.stats[i] = 0.0;
+    if (g < K) a.hist[g] = 0;
 }
 
 // ---- batch: ONE CTA runs ONE member's whole runGMMEstimation (all T waypoints) ---------------------------------------
@@ -711,6 +727,153 @@ __global__ void __launch_bounds__(256, GMM_FUSED_CTAS) gmm_member_run_kernel(con
         for (int o = 16; o > 0; o >>= 1) t64 += __shfl_xor_sync(0xffffffffu, t64, o);
         if ((threadIdx.x & 31) == 0 && t64) atomicAdd(a.tests, t64);
     }
+}
+
+// ---- few runs (one runGMMEstimation at a time, small batches): ONE THREAD-BLOCK CLUSTER runs one whole run -----------
+// A single run's 10^4 samples per waypoint are one pass of a cluster of 16 x 512 threads (two samples per thread); what the per-waypoint
+// kernels pay for instead is three dependent launches per waypoint (6 + 9 + 11 us of mostly launch and tail latency,
+// 168 launches per run).  Here the CTAs of a cluster split the samples of a waypoint (same Philox counters: sample
+// index -> draws, so the samples are the per-waypoint kernels' own), keep their partial multinomial counts and
+// sufficient statistics in their own shared memory, and after a cluster barrier every CTA adds up all partials
+// through distributed shared memory in the same order -- every CTA holds bit-identical totals, so each runs the (serial,
+// FP64) refit + EKF step redundantly on its own copy of the mixture and nothing has to be sent back.  Counts and
+// statistics are double-buffered by waypoint parity: a buffer is cleared one barrier after its last remote read,
+// which leaves two cluster barriers per waypoint.  Outputs (p_t, recorded mixtures) are written by every CTA with
+// identical values; the degenerate-refit counter only by rank 0.
+#define GMM_CLUSTER 8          // CTAs per cluster for small batches; single runs take 16 (non-portable size)
+#define GMM_CLUSTER_THREADS 512
+__global__ void __launch_bounds__(GMM_CLUSTER_THREADS, 1) gmm_cluster_run_kernel(const GmmLaunch a_in, int sat2_n, int cull_words) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cl = cg::this_cluster();
+    const unsigned rank = cl.block_rank(), CL = cl.num_blocks();
+    extern __shared__ __align__(16) float4 s_tab[];
+    __shared__ double s_comp[MCSIM_MAX_GAUSSIANS][GMM_COMP];
+    __shared__ double s_stat[2][MCSIM_MAX_GAUSSIANS][GMM_STAT];
+    __shared__ double s_tot[MCSIM_MAX_GAUSSIANS][GMM_STAT];
+    __shared__ double s_free[MCSIM_MAX_GAUSSIANS], s_coll[MCSIM_MAX_GAUSSIANS];
+    __shared__ float s_mu[MCSIM_MAX_GAUSSIANS][3];
+    __shared__ float s_L[MCSIM_MAX_GAUSSIANS][6];
+    __shared__ float s_cdf[MCSIM_MAX_GAUSSIANS];
+    __shared__ unsigned s_hist[2][MCSIM_MAX_GAUSSIANS];
+    __shared__ unsigned s_prefix[MCSIM_MAX_GAUSSIANS + 1];
+    __shared__ int s_sink;
+    GmmLaunch a = gmm_member(a_in, blockIdx.x / CL);
+    if (rank) a.degenerate = &s_sink;
+    const int K = a.K, T = a.T, nh = c_scene.n_hulls;
+    const unsigned stream_id = a.stream_id, k0 = a.k0, k1 = a.k1, n_all = unsigned(a.n);
+    const bool cull = a.cull != nullptr;
+    unsigned* s_cull = reinterpret_cast<unsigned*>(s_tab + sat2_n);
+    for (int i = threadIdx.x; i < sat2_n; i += blockDim.x) s_tab[i] = a.sat2[i];
+    if (cull) for (int i = threadIdx.x; i < cull_words; i += blockDim.x) s_cull[i] = a.cull[i];
+    for (int i = threadIdx.x; i < K * GMM_COMP; i += blockDim.x) s_comp[i / GMM_COMP][i % GMM_COMP] = a.comps[i];
+    for (int i = threadIdx.x; i < 2 * MCSIM_MAX_GAUSSIANS * GMM_STAT; i += blockDim.x) (&s_stat[0][0][0])[i] = 0.0;
+    if (threadIdx.x < 2 * MCSIM_MAX_GAUSSIANS) (&s_hist[0][0])[threadIdx.x] = 0;
+    const unsigned char* s_ccnt = reinterpret_cast<const unsigned char*>(s_cull);
+    const ushort2* s_cidx = reinterpret_cast<const ushort2*>(s_cull + (T * nh * MC_CULL_LEVELS + 3) / 4);
+    unsigned my_tests = 0;
+    __syncthreads();
+    cl.sync();   // every CTA's buffers are cleared before anyone reads them
+
+    for (int t = 0; t < T; ++t) {
+        const int cur = t & 1;
+        // ---- multinomial counts of this waypoint: this CTA's share of the Philox blocks
+        if (threadIdx.x == 0) {
+            double acc = 0, tot = 0;
+            for (int g = 0; g < K; ++g) tot += s_comp[g][0];
+            for (int g = 0; g < K; ++g) { acc += s_comp[g][0]; s_cdf[g] = float(acc / tot); }
+            for (int g = K - 1; g >= 0 && !(s_comp[g][0] > 0); --g) s_cdf[g] = 2.0f;
+            int last = K - 1;
+            while (last > 0 && !(s_comp[last][0] > 0)) --last;
+            s_cdf[last] = 2.0f;
+        }
+        for (int i = threadIdx.x; i < K * 3; i += blockDim.x) s_mu[i / 3][i % 3] = float(s_comp[i / 3][1 + i % 3]);
+        for (int i = threadIdx.x; i < K * 6; i += blockDim.x) s_L[i / 6][i % 6] = float(s_comp[i / 6][13 + i % 6]);
+        __syncthreads();
+        const unsigned n4 = (n_all + 3) >> 2;
+        unsigned cnt[4] = {0u, 0u, 0u, 0u};
+        unsigned held = 0;
+        auto flush_counts = [&]() {
+            for (int gg = 0; gg < K; ++gg) {
+                const unsigned r = gg < 4 ? cnt[0] : (gg < 8 ? cnt[1] : (gg < 12 ? cnt[2] : cnt[3]));
+                const unsigned v = __reduce_add_sync(0xffffffffu, (r >> (8 * (gg & 3))) & 0xffu);
+                if (v && (threadIdx.x & 31) == 0) atomicAdd(&s_hist[cur][gg], v);
+            }
+            cnt[0] = cnt[1] = cnt[2] = cnt[3] = 0u;
+            held = 0;
+        };
+        for (unsigned base = rank * blockDim.x; base < n4; base += CL * blockDim.x) {
+            const unsigned j = base + threadIdx.x;
+            mcsim_rng::u32x4 c = {j, stream_id, unsigned(2 * t + 1), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
+            c = mcsim_rng::philox4x32_10(c, k0, k1);
+            const unsigned w[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const bool valid = j < n4 && 4 * j + q < n_all;
+                const float u = mcsim_rng::u01(w[q]);
+                int g = 0;
+                for (int k = 0; k < K - 1; ++k) g += u > s_cdf[k];
+                const unsigned inc = valid ? 1u << (8 * (g & 3)) : 0u;
+                cnt[0] += g < 4 ? inc : 0u;
+                cnt[1] += (g >= 4 && g < 8) ? inc : 0u;
+                cnt[2] += (g >= 8 && g < 12) ? inc : 0u;
+                cnt[3] += g >= 12 ? inc : 0u;
+            }
+            held += 4;
+            if (held > 248) flush_counts();
+        }
+        flush_counts();
+        __syncthreads();
+        cl.sync();   // barrier 1: every CTA's partial counts of waypoint t are complete
+        if (threadIdx.x < 32) {   // lane r reads rank r's partial counts: the remote loads of a component go out together
+            unsigned acc = 0;
+            for (int g = 0; g < K; ++g) {
+                const unsigned part = threadIdx.x < CL ? *cl.map_shared_rank(&s_hist[cur][g], threadIdx.x) : 0u;
+                if (threadIdx.x == 0) s_prefix[g] = acc;
+                acc += __reduce_add_sync(0xffffffffu, part);
+            }
+            if (threadIdx.x == 0) s_prefix[K] = acc;
+        }
+        // the other parity's buffers were last read (remotely) before barrier 1: clear them for waypoint t + 1
+        for (int i = threadIdx.x; i < MCSIM_MAX_GAUSSIANS * GMM_STAT; i += blockDim.x) (&s_stat[cur ^ 1][0][0])[i] = 0.0;
+        if (threadIdx.x < MCSIM_MAX_GAUSSIANS) s_hist[cur ^ 1][threadIdx.x] = 0;
+        __syncthreads();
+        // ---- sample -> collide -> moments: this CTA's share of the sample pairs
+        {
+            int g = 0;
+            GmmAcc acc;
+            const unsigned n = s_prefix[K] < n_all ? s_prefix[K] : n_all;
+            const float2 nom = cull ? __ldg(a.nominal + t) : make_float2(0.f, 0.f);
+            const unsigned char* cc = s_ccnt + t * nh * MC_CULL_LEVELS;
+            const ushort2* ci = s_cidx + t * nh * MC_CULL_CAP;
+            for (unsigned base = 2 * blockDim.x * rank; base < n; base += 2 * blockDim.x * CL)
+                gmm_philox_pass2(stream_id, unsigned(2 * t), k0, k1, base + 2 * threadIdx.x, base + 2 * threadIdx.x + 1, n, K, g, s_prefix, s_mu, s_L, s_stat[cur], s_tab, cc, ci, cull, nom, acc, my_tests);
+            acc.flush(s_stat[cur]);
+        }
+        __syncthreads();
+        cl.sync();   // barrier 2: every CTA's partial statistics of waypoint t are complete
+        // CL consecutive lanes read one statistic from the CL ranks (one round of remote loads), then add up by a
+        // butterfly: the same order in every CTA, so the totals are bit-identical across the cluster (CL = 8 or 16)
+        for (int base = 0; base < K * GMM_STAT * int(CL); base += blockDim.x) {
+            const int idx = base + threadIdx.x, i = idx / int(CL);
+            double v = i < K * GMM_STAT ? *cl.map_shared_rank(&s_stat[cur][0][0] + i, unsigned(idx) % CL) : 0.0;
+            for (unsigned o = CL >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (i < K * GMM_STAT && unsigned(idx) % CL == 0) (&s_tot[0][0])[i] = v;
+        }
+        __syncthreads();
+        // ---- refit + propagate, redundantly in every CTA
+        const int g = threadIdx.x;
+        if (g < K) gmm_refit_moments(s_comp[g], s_tot[g], a.degenerate, s_free[g], s_coll[g]);
+        __syncthreads();
+        if (g < K) gmm_refit_finish(a, t, g, s_comp[g], s_free, s_coll);
+        __syncthreads();
+    }
+    if (a.tests) {
+        unsigned long long t64 = my_tests;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t64 += __shfl_xor_sync(0xffffffffu, t64, o);
+        if ((threadIdx.x & 31) == 0 && t64) atomicAdd(a.tests, t64);
+    }
+    cl.sync();   // no CTA leaves while a peer may still read its shared memory
 }
 
 // ---- batch: the members' shared real-robot threads on the device -------------------------------------------------------

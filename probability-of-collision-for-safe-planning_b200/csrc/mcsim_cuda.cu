@@ -761,6 +761,47 @@ static int gmm_launch_waypoint(mcsim_cuda_ctx* c, const GmmLaunch& a_in, int mod
     return MCSIM_OK;
 }
 
+// one thread-block cluster per run for the whole plan (gmm_cluster_run_kernel): single runs and small batches in
+// Philox mode whose samples per waypoint are a few passes of a cluster; larger sample counts keep the per-waypoint
+// kernels (the whole GPU per waypoint), batches that fill the GPU by themselves the one-CTA-per-member kernel
+#define GMM_CLUSTER_MAX_SAMPLES 32768ull
+static bool gmm_cluster_fits(const mcsim_cuda_ctx* c, uint64_t n_samples, int n_runs) {
+    if (getenv("MCSIM_GMM_NO_CLUSTER")) return false;
+    const size_t smem = sizeof(float4) * size_t(c->sat2_n) + sizeof(unsigned) * size_t(c->gmm_cull_words);
+    return n_samples <= GMM_CLUSTER_MAX_SAMPLES && smem <= 64 * 1024 && n_runs >= 1 && n_runs < 64;
+}
+static int gmm_launch_cluster(mcsim_cuda_ctx* c, const GmmLaunch& a, int n_runs) {
+    const size_t smem = sizeof(float4) * size_t(c->sat2_n) + sizeof(unsigned) * size_t(c->gmm_cull_words);
+    if (smem > 32 * 1024) CK(cudaFuncSetAttribute((const void*)gmm_cluster_run_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    // up to 8 runs: 16 CTAs per cluster (one pass over 10^4 samples; a GPC holds one such cluster), else 8
+    int cl = n_runs <= 8 ? 16 : GMM_CLUSTER;
+    if (cl > 8) CK(cudaFuncSetAttribute((const void*)gmm_cluster_run_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[1];
+    for (;;) {
+        memset(&cfg, 0, sizeof(cfg));
+        cfg.gridDim = dim3(unsigned(n_runs) * unsigned(cl));
+        cfg.blockDim = dim3(GMM_CLUSTER_THREADS);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = c->stream;
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = unsigned(cl);
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        int fit = 0;
+        const cudaError_t q = cudaOccupancyMaxActiveClusters(&fit, gmm_cluster_run_kernel, &cfg);
+        if (q == cudaSuccess && fit >= 1) break;
+        (void)cudaGetLastError();
+        if (cl == GMM_CLUSTER) return fail(MCSIM_ERR_CUDA, "gmm: a cluster of %d x %d threads does not fit this device", cl, GMM_CLUSTER_THREADS);
+        cl = GMM_CLUSTER;
+    }
+    CK(cudaLaunchKernelEx(&cfg, gmm_cluster_run_kernel, a, c->sat2_n, c->gmm_cull_words));
+    ++c->launches;
+    return MCSIM_OK;
+}
+
 extern "C" int mcsim_cuda_gmm_run(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, const mcsim_gmm_run_params* g,
                                   mcsim_gmm_run_result* r) {
     if (!c || !mc || !g || !r) return fail(MCSIM_ERR_ARG, "gmm_run: NULL argument");
@@ -847,11 +888,17 @@ extern "C" int mcsim_cuda_gmm_run(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, 
     a.counts_replay = (const int*)c->gmm_counts.p;
     if (mode == MCSIM_MODE_PHILOX) { rc = gmm_upload_cull(c, a, mc->trajectory, 1, T, mc->exhaustive != 0); if (rc) return rc; }
     CK(cudaEventRecord(c->ev0, c->stream));
-    for (int t = 0; t < T; ++t) {
-        a.t = t;
-        a.normals = mode == MCSIM_MODE_REPLAY ? (const double*)c->gmm_normals.p + size_t(t) * 3 * N : nullptr;
-        rc = gmm_launch_waypoint(c, a, mode);
+    if (mode == MCSIM_MODE_PHILOX && gmm_cluster_fits(c, N, 1)) {
+        a.t = 0;
+        rc = gmm_launch_cluster(c, a, 1);
         if (rc) return rc;
+    } else {
+        for (int t = 0; t < T; ++t) {
+            a.t = t;
+            a.normals = mode == MCSIM_MODE_REPLAY ? (const double*)c->gmm_normals.p + size_t(t) * 3 * N : nullptr;
+            rc = gmm_launch_waypoint(c, a, mode);
+            if (rc) return rc;
+        }
     }
     CK(cudaEventRecord(c->ev1, c->stream));
     std::vector<double> prob(T);
@@ -1332,6 +1379,10 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
         gmm_member_run_kernel<<<B, 256, fused_smem, c->stream>>>(a, c->sat2_n, c->gmm_cull_words);
         ++c->launches;
         CK(cudaGetLastError());
+    } else if (gmm_cluster_fits(c, N, B)) {
+        a.t = 0;
+        rc = gmm_launch_cluster(c, a, B);
+        if (rc) return rc;
     } else {
         for (int t = 0; t < T; ++t) {
             a.t = t;
