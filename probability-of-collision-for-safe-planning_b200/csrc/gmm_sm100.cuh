@@ -730,17 +730,21 @@ __global__ void __launch_bounds__(256, GMM_FUSED_CTAS) gmm_member_run_kernel(con
 }
 
 // ---- few runs (one runGMMEstimation at a time, small batches): ONE THREAD-BLOCK CLUSTER runs one whole run -----------
-// A single run's 10^4 samples per waypoint are one pass of a cluster of 16 x 512 threads (two samples per thread); what the per-waypoint
-// kernels pay for instead is three dependent launches per waypoint (6 + 9 + 11 us of mostly launch and tail latency,
-// 168 launches per run).  Here the CTAs of a cluster split the samples of a waypoint (same Philox counters: sample
-// index -> draws, so the samples are the per-waypoint kernels' own), keep their partial multinomial counts and
-// sufficient statistics in their own shared memory, and after a cluster barrier every CTA adds up all partials
-// through distributed shared memory in the same order -- every CTA holds bit-identical totals, so each runs the (serial,
-// FP64) refit + EKF step redundantly on its own copy of the mixture and nothing has to be sent back.  Counts and
-// statistics are double-buffered by waypoint parity: a buffer is cleared one barrier after its last remote read,
-// which leaves two cluster barriers per waypoint.  Outputs (p_t, recorded mixtures) are written by every CTA with
-// identical values; the degenerate-refit counter only by rank 0.
+// A single run's 10^4 samples per waypoint are one pass of a cluster of 16 x 512 threads (two samples per thread); what
+// the per-waypoint kernels pay for instead is three dependent launches per waypoint (6 + 9 + 11 us of mostly launch and
+// tail latency, 168 launches per run).  Here the CTAs of a cluster split the samples of a waypoint (same Philox
+// counters: sample index -> draws, so the samples are the per-waypoint kernels' own), and exchange their partial
+// multinomial counts and sufficient statistics through distributed shared memory: every CTA stores its partials into
+// slot [its rank] of EVERY peer (remote stores, nobody waits for them), a cluster barrier makes them visible, and every
+// CTA adds up the slots in rank order -- bit-identical totals everywhere, so each CTA runs the (serial, FP64) refit +
+// EKF step redundantly on its own copy of the mixture and nothing has to be sent back.  A slot is rewritten only after
+// the next barrier, which every CTA reaches after it has read the slot: two cluster barriers per waypoint, no double
+// buffers.  The EKF chain of the refit occupies one warp for ~ 5 us; the other warps draw the NEXT waypoint's
+// multinomial counts meanwhile (they need the new weights only, which the moments give before the EKF step).
+// Outputs (p_t, recorded mixtures) are written by every CTA with identical values; the degenerate-refit counter only
+// by rank 0.
 #define GMM_CLUSTER 8          // CTAs per cluster for small batches; single runs take 16 (non-portable size)
+#define GMM_CLUSTER_MAX 16
 #define GMM_CLUSTER_THREADS 512
 __global__ void __launch_bounds__(GMM_CLUSTER_THREADS, 1) gmm_cluster_run_kernel(const GmmLaunch a_in, int sat2_n, int cull_words) {
     namespace cg = cooperative_groups;
@@ -748,13 +752,15 @@ __global__ void __launch_bounds__(GMM_CLUSTER_THREADS, 1) gmm_cluster_run_kernel
     const unsigned rank = cl.block_rank(), CL = cl.num_blocks();
     extern __shared__ __align__(16) float4 s_tab[];
     __shared__ double s_comp[MCSIM_MAX_GAUSSIANS][GMM_COMP];
-    __shared__ double s_stat[2][MCSIM_MAX_GAUSSIANS][GMM_STAT];
+    __shared__ double s_stat[MCSIM_MAX_GAUSSIANS][GMM_STAT];                      // this CTA's partial statistics
+    __shared__ double s_part[GMM_CLUSTER_MAX][MCSIM_MAX_GAUSSIANS * GMM_STAT];   // slot r: rank r's partials (written remotely)
     __shared__ double s_tot[MCSIM_MAX_GAUSSIANS][GMM_STAT];
     __shared__ double s_free[MCSIM_MAX_GAUSSIANS], s_coll[MCSIM_MAX_GAUSSIANS];
     __shared__ float s_mu[MCSIM_MAX_GAUSSIANS][3];
     __shared__ float s_L[MCSIM_MAX_GAUSSIANS][6];
     __shared__ float s_cdf[MCSIM_MAX_GAUSSIANS];
-    __shared__ unsigned s_hist[2][MCSIM_MAX_GAUSSIANS];
+    __shared__ unsigned s_hist[MCSIM_MAX_GAUSSIANS];                              // this CTA's partial counts
+    __shared__ unsigned s_hpart[GMM_CLUSTER_MAX][MCSIM_MAX_GAUSSIANS];           // slot r: rank r's counts (written remotely)
     __shared__ unsigned s_prefix[MCSIM_MAX_GAUSSIANS + 1];
     __shared__ int s_sink;
     GmmLaunch a = gmm_member(a_in, blockIdx.x / CL);
@@ -766,29 +772,36 @@ __global__ void __launch_bounds__(GMM_CLUSTER_THREADS, 1) gmm_cluster_run_kernel
     for (int i = threadIdx.x; i < sat2_n; i += blockDim.x) s_tab[i] = a.sat2[i];
     if (cull) for (int i = threadIdx.x; i < cull_words; i += blockDim.x) s_cull[i] = a.cull[i];
     for (int i = threadIdx.x; i < K * GMM_COMP; i += blockDim.x) s_comp[i / GMM_COMP][i % GMM_COMP] = a.comps[i];
-    for (int i = threadIdx.x; i < 2 * MCSIM_MAX_GAUSSIANS * GMM_STAT; i += blockDim.x) (&s_stat[0][0][0])[i] = 0.0;
-    if (threadIdx.x < 2 * MCSIM_MAX_GAUSSIANS) (&s_hist[0][0])[threadIdx.x] = 0;
+    for (int i = threadIdx.x; i < MCSIM_MAX_GAUSSIANS * GMM_STAT; i += blockDim.x) (&s_stat[0][0])[i] = 0.0;
+    if (threadIdx.x < MCSIM_MAX_GAUSSIANS) s_hist[threadIdx.x] = 0;
     const unsigned char* s_ccnt = reinterpret_cast<const unsigned char*>(s_cull);
     const ushort2* s_cidx = reinterpret_cast<const ushort2*>(s_cull + (T * nh * MC_CULL_LEVELS + 3) / 4);
     unsigned my_tests = 0;
     __syncthreads();
-    cl.sync();   // every CTA's buffers are cleared before anyone reads them
+    if (threadIdx.x < K) s_free[threadIdx.x] = s_comp[threadIdx.x][0];   // the initial weights play the free counts' part
+    __syncthreads();
+    cl.sync();   // every CTA is resident and initialised before anyone stores into it
 
-    for (int t = 0; t < T; ++t) {
-        const int cur = t & 1;
-        // ---- multinomial counts of this waypoint: this CTA's share of the Philox blocks
-        if (threadIdx.x == 0) {
+    // multinomial counts of waypoint t from weights proportional to s_free[] (= the weights the refit of waypoint t - 1
+    // stores: n_free,g / sum n_free); run by warps 1.. of the CTA only, warp 0 is busy with the EKF chain meanwhile
+    const unsigned cw = blockDim.x - 32;   // counting threads per CTA
+    auto count_waypoint = [&](int t) {
+        const unsigned tid = threadIdx.x - 32;
+        if (tid == 0) {
+            // the weights exactly as gmm_refit_finish stores them (t = 0: the initial weights, already in s_free)
+            double tf = 0;
+            for (int g = 0; g < K; ++g) tf += s_free[g];
+            const double den = t == 0 ? 1.0 : (tf > 0 ? tf : 1.0);
             double acc = 0, tot = 0;
-            for (int g = 0; g < K; ++g) tot += s_comp[g][0];
-            for (int g = 0; g < K; ++g) { acc += s_comp[g][0]; s_cdf[g] = float(acc / tot); }
-            for (int g = K - 1; g >= 0 && !(s_comp[g][0] > 0); --g) s_cdf[g] = 2.0f;
+            for (int g = 0; g < K; ++g) tot += s_free[g] / den;
+            for (int g = 0; g < K; ++g) { acc += s_free[g] / den; s_cdf[g] = float(acc / tot); }
+            for (int g = K - 1; g >= 0 && !(s_free[g] > 0); --g) s_cdf[g] = 2.0f;
             int last = K - 1;
-            while (last > 0 && !(s_comp[last][0] > 0)) --last;
+            while (last > 0 && !(s_free[last] > 0)) --last;
             s_cdf[last] = 2.0f;
         }
-        for (int i = threadIdx.x; i < K * 3; i += blockDim.x) s_mu[i / 3][i % 3] = float(s_comp[i / 3][1 + i % 3]);
-        for (int i = threadIdx.x; i < K * 6; i += blockDim.x) s_L[i / 6][i % 6] = float(s_comp[i / 6][13 + i % 6]);
-        __syncthreads();
+        asm volatile("bar.sync 1, %0;" ::"r"(cw) : "memory");
+        // per-thread counts in four registers of four 8-bit fields, flushed by warp sums before a field can overflow
         const unsigned n4 = (n_all + 3) >> 2;
         unsigned cnt[4] = {0u, 0u, 0u, 0u};
         unsigned held = 0;
@@ -796,13 +809,13 @@ __global__ void __launch_bounds__(GMM_CLUSTER_THREADS, 1) gmm_cluster_run_kernel
             for (int gg = 0; gg < K; ++gg) {
                 const unsigned r = gg < 4 ? cnt[0] : (gg < 8 ? cnt[1] : (gg < 12 ? cnt[2] : cnt[3]));
                 const unsigned v = __reduce_add_sync(0xffffffffu, (r >> (8 * (gg & 3))) & 0xffu);
-                if (v && (threadIdx.x & 31) == 0) atomicAdd(&s_hist[cur][gg], v);
+                if (v && (threadIdx.x & 31) == 0) atomicAdd(&s_hist[gg], v);
             }
             cnt[0] = cnt[1] = cnt[2] = cnt[3] = 0u;
             held = 0;
         };
-        for (unsigned base = rank * blockDim.x; base < n4; base += CL * blockDim.x) {
-            const unsigned j = base + threadIdx.x;
+        for (unsigned base = rank * cw; base < n4; base += CL * cw) {
+            const unsigned j = base + tid;
             mcsim_rng::u32x4 c = {j, stream_id, unsigned(2 * t + 1), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
             c = mcsim_rng::philox4x32_10(c, k0, k1);
             const unsigned w[4] = {c.x, c.y, c.z, c.w};
@@ -822,20 +835,28 @@ __global__ void __launch_bounds__(GMM_CLUSTER_THREADS, 1) gmm_cluster_run_kernel
             if (held > 248) flush_counts();
         }
         flush_counts();
-        __syncthreads();
-        cl.sync();   // barrier 1: every CTA's partial counts of waypoint t are complete
-        if (threadIdx.x < 32) {   // lane r reads rank r's partial counts: the remote loads of a component go out together
+    };
+    if (threadIdx.x >= 32) count_waypoint(0);
+
+    for (int t = 0; t < T; ++t) {
+        __syncthreads();   // counts of waypoint t (warps 1..) and the refit of waypoint t - 1 (warp 0) are done
+        // ---- partial counts -> slot [rank] of every CTA
+        for (unsigned i = threadIdx.x; i < unsigned(K) * CL; i += blockDim.x) {
+            const unsigned g = i / CL, r = i % CL;
+            *cl.map_shared_rank(&s_hpart[rank][g], r) = s_hist[g];
+        }
+        for (int i = threadIdx.x; i < K * 3; i += blockDim.x) s_mu[i / 3][i % 3] = float(s_comp[i / 3][1 + i % 3]);
+        for (int i = threadIdx.x; i < K * 6; i += blockDim.x) s_L[i / 6][i % 6] = float(s_comp[i / 6][13 + i % 6]);
+        cl.sync();   // barrier 1: every CTA's counts of waypoint t have arrived
+        if (threadIdx.x == 0) {
             unsigned acc = 0;
             for (int g = 0; g < K; ++g) {
-                const unsigned part = threadIdx.x < CL ? *cl.map_shared_rank(&s_hist[cur][g], threadIdx.x) : 0u;
-                if (threadIdx.x == 0) s_prefix[g] = acc;
-                acc += __reduce_add_sync(0xffffffffu, part);
+                s_prefix[g] = acc;
+                for (unsigned r = 0; r < CL; ++r) acc += s_hpart[r][g];
             }
-            if (threadIdx.x == 0) s_prefix[K] = acc;
+            s_prefix[K] = acc;
         }
-        // the other parity's buffers were last read (remotely) before barrier 1: clear them for waypoint t + 1
-        for (int i = threadIdx.x; i < MCSIM_MAX_GAUSSIANS * GMM_STAT; i += blockDim.x) (&s_stat[cur ^ 1][0][0])[i] = 0.0;
-        if (threadIdx.x < MCSIM_MAX_GAUSSIANS) s_hist[cur ^ 1][threadIdx.x] = 0;
+        if (threadIdx.x < MCSIM_MAX_GAUSSIANS) s_hist[threadIdx.x] = 0;
         __syncthreads();
         // ---- sample -> collide -> moments: this CTA's share of the sample pairs
         {
@@ -846,26 +867,33 @@ __global__ void __launch_bounds__(GMM_CLUSTER_THREADS, 1) gmm_cluster_run_kernel
             const unsigned char* cc = s_ccnt + t * nh * MC_CULL_LEVELS;
             const ushort2* ci = s_cidx + t * nh * MC_CULL_CAP;
             for (unsigned base = 2 * blockDim.x * rank; base < n; base += 2 * blockDim.x * CL)
-                gmm_philox_pass2(stream_id, unsigned(2 * t), k0, k1, base + 2 * threadIdx.x, base + 2 * threadIdx.x + 1, n, K, g, s_prefix, s_mu, s_L, s_stat[cur], s_tab, cc, ci, cull, nom, acc, my_tests);
-            acc.flush(s_stat[cur]);
+                gmm_philox_pass2(stream_id, unsigned(2 * t), k0, k1, base + 2 * threadIdx.x, base + 2 * threadIdx.x + 1, n, K, g, s_prefix, s_mu, s_L, s_stat, s_tab, cc, ci, cull, nom, acc, my_tests);
+            acc.flush(s_stat);
         }
         __syncthreads();
-        cl.sync();   // barrier 2: every CTA's partial statistics of waypoint t are complete
-        // CL consecutive lanes read one statistic from the CL ranks (one round of remote loads), then add up by a
-        // butterfly: the same order in every CTA, so the totals are bit-identical across the cluster (CL = 8 or 16)
-        for (int base = 0; base < K * GMM_STAT * int(CL); base += blockDim.x) {
-            const int idx = base + threadIdx.x, i = idx / int(CL);
-            double v = i < K * GMM_STAT ? *cl.map_shared_rank(&s_stat[cur][0][0] + i, unsigned(idx) % CL) : 0.0;
-            for (unsigned o = CL >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            if (i < K * GMM_STAT && unsigned(idx) % CL == 0) (&s_tot[0][0])[i] = v;
+        // ---- partial statistics -> slot [rank] of every CTA
+        for (unsigned i = threadIdx.x; i < unsigned(K * GMM_STAT) * CL; i += blockDim.x) {
+            const unsigned v = i / CL, r = i % CL;
+            *cl.map_shared_rank(&s_part[rank][v], r) = (&s_stat[0][0])[v];
+        }
+        cl.sync();   // barrier 2: every CTA's statistics of waypoint t have arrived
+        for (int i = threadIdx.x; i < K * GMM_STAT; i += blockDim.x) {
+            double v = 0.0;
+            for (unsigned r = 0; r < CL; ++r) v += s_part[r][i];   // rank order: bit-identical in every CTA
+            (&s_tot[0][0])[i] = v;
+            (&s_stat[0][0])[i] = 0.0;
         }
         __syncthreads();
-        // ---- refit + propagate, redundantly in every CTA
+        // ---- refit, redundantly in every CTA: moments and weights first ...
         const int g = threadIdx.x;
         if (g < K) gmm_refit_moments(s_comp[g], s_tot[g], a.degenerate, s_free[g], s_coll[g]);
         __syncthreads();
-        if (g < K) gmm_refit_finish(a, t, g, s_comp[g], s_free, s_coll);
-        __syncthreads();
+        // ... then warp 0 walks the EKF chain to waypoint t + 1 while the other warps draw that waypoint's counts
+        if (threadIdx.x < 32) {
+            if (g < K) gmm_refit_finish(a, t, g, s_comp[g], s_free, s_coll);
+        } else if (t + 1 < T) {
+            count_waypoint(t + 1);
+        }
     }
     if (a.tests) {
         unsigned long long t64 = my_tests;
@@ -873,7 +901,7 @@ __global__ void __launch_bounds__(GMM_CLUSTER_THREADS, 1) gmm_cluster_run_kernel
         for (int o = 16; o > 0; o >>= 1) t64 += __shfl_xor_sync(0xffffffffu, t64, o);
         if ((threadIdx.x & 31) == 0 && t64) atomicAdd(a.tests, t64);
     }
-    cl.sync();   // no CTA leaves while a peer may still read its shared memory
+    cl.sync();   // no CTA leaves while a peer may still store into its shared memory
 }
 
 // ---- batch: the members' shared real-robot threads on the device -------------------------------------------------------
