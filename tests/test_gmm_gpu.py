@@ -209,3 +209,34 @@ def test_gmm_batch_fused_kernel_edge_cases(ctx, plan, scenes, K, N):
     f2 = ctx.gmm_run_batch(short, K, N, B, stream0=5)
     p2 = ctx.gmm_run_batch(short, K, N, 2, stream0=5)
     np.testing.assert_allclose(f2["probabilities"][:2], p2["probabilities"], rtol=1e-9, atol=1e-12)
+
+
+@pytest.mark.parametrize("K,N", [(3, 10000), (1, 10001), (16, 3000), (2, 100), (3, 32768)])
+def test_gmm_cluster_kernel_equals_per_waypoint_kernels(ctx, plan, scenes, K, N, monkeypatch):
+    """One-cluster-per-run kernel (single runs and batches below 64 in Philox mode, N <= 32,768) against the
+    per-waypoint kernels (MCSIM_GMM_NO_CLUSTER=1 keeps them): same Philox draws per sample index, FP64 sums in a
+    different order -> per-waypoint fractions, recorded mixtures and P to 1e-9.  Cases: the reference's default, a
+    sample count that is no multiple of 4, the maximum component count, so few samples that most CTAs of the cluster
+    idle and components starve, the largest routed sample count; a two-waypoint plan; a batch on 8-CTA clusters."""
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    ctx.set_scene(scenes["pr2test2"]["boxes"], scenes["pr2test2"]["hulls"])
+    short = dict(plan)
+    short["trajectory"] = plan["trajectory"][:, :2]
+    short["odometry"] = plan["odometry"][:, :1]
+    for pl in (plan, short):
+        monkeypatch.delenv("MCSIM_GMM_NO_CLUSTER", raising=False)
+        a = ctx.gmm_run(pl, K, N, mode=abi.MODE_PHILOX, stream_id=21, record=True)
+        monkeypatch.setenv("MCSIM_GMM_NO_CLUSTER", "1")
+        b = ctx.gmm_run(pl, K, N, mode=abi.MODE_PHILOX, stream_id=21, record=True)
+        np.testing.assert_allclose(a["probabilities"], b["probabilities"], rtol=1e-9, atol=1e-12)
+        np.testing.assert_allclose(a["P"], b["P"], rtol=1e-9)
+        np.testing.assert_allclose(a["gmm_pre"], b["gmm_pre"], rtol=1e-7, atol=1e-12)
+        np.testing.assert_allclose(a["gmm_post"], b["gmm_post"], rtol=1e-7, atol=1e-12)
+        assert a["degenerate"] == b["degenerate"]
+    monkeypatch.delenv("MCSIM_GMM_NO_CLUSTER", raising=False)
+    batch = ctx.gmm_run_batch(plan, K, N, 12, stream0=40)       # 12 runs: 8 CTAs per cluster
+    monkeypatch.setenv("MCSIM_GMM_NO_CLUSTER", "1")
+    for b in (0, 11):
+        one = ctx.gmm_run(plan, K, N, mode=abi.MODE_PHILOX, stream_id=40 + b)
+        np.testing.assert_allclose(batch["probabilities"][b], one["probabilities"], rtol=1e-9, atol=1e-12)
