@@ -794,7 +794,7 @@ static int gmm_launch_cluster(mcsim_cuda_ctx* c, const GmmLaunch& a, int n_runs)
         const cudaError_t q = cudaOccupancyMaxActiveClusters(&fit, gmm_cluster_run_kernel, &cfg);
         if (q == cudaSuccess && fit >= 1) break;
         (void)cudaGetLastError();
-        if (cl == GMM_CLUSTER) return fail(MCSIM_ERR_CUDA, "gmm: a cluster of %d x %d threads does not fit this device", cl, GMM_CLUSTER_THREADS);
+        if (cl == GMM_CLUSTER) return -1;   // no cluster shape fits (e.g. a partitioned device): the caller keeps the per-waypoint kernels
         cl = GMM_CLUSTER;
     }
     CK(cudaLaunchKernelEx(&cfg, gmm_cluster_run_kernel, a, c->sat2_n, c->gmm_cull_words));
@@ -888,11 +888,13 @@ extern "C" int mcsim_cuda_gmm_run(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, 
     a.counts_replay = (const int*)c->gmm_counts.p;
     if (mode == MCSIM_MODE_PHILOX) { rc = gmm_upload_cull(c, a, mc->trajectory, 1, T, mc->exhaustive != 0); if (rc) return rc; }
     CK(cudaEventRecord(c->ev0, c->stream));
+    rc = -1;
     if (mode == MCSIM_MODE_PHILOX && gmm_cluster_fits(c, N, 1)) {
         a.t = 0;
         rc = gmm_launch_cluster(c, a, 1);
-        if (rc) return rc;
-    } else {
+        if (rc > 0) return rc;
+    }
+    if (rc < 0) {
         for (int t = 0; t < T; ++t) {
             a.t = t;
             a.normals = mode == MCSIM_MODE_REPLAY ? (const double*)c->gmm_normals.p + size_t(t) * 3 * N : nullptr;
@@ -1379,15 +1381,17 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
         gmm_member_run_kernel<<<B, 256, fused_smem, c->stream>>>(a, c->sat2_n, c->gmm_cull_words);
         ++c->launches;
         CK(cudaGetLastError());
-    } else if (gmm_cluster_fits(c, N, B)) {
-        a.t = 0;
-        rc = gmm_launch_cluster(c, a, B);
-        if (rc) return rc;
     } else {
-        for (int t = 0; t < T; ++t) {
+        rc = -1;
+        if (gmm_cluster_fits(c, N, B)) {
+            a.t = 0;
+            rc = gmm_launch_cluster(c, a, B);
+            if (rc > 0) return rc;
+        }
+        for (int t = 0; rc < 0 && t < T; ++t) {
             a.t = t;
-            rc = gmm_launch_waypoint(c, a, MCSIM_MODE_PHILOX);
-            if (rc) return rc;
+            const int rw = gmm_launch_waypoint(c, a, MCSIM_MODE_PHILOX);
+            if (rw) return rw;
         }
     }
     CK(cudaEventRecord(c->ev1, c->stream));
