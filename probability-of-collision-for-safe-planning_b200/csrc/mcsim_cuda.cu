@@ -772,7 +772,8 @@ static bool gmm_cluster_fits(const mcsim_cuda_ctx* c, uint64_t n_samples, int n_
 }
 static int gmm_launch_cluster(mcsim_cuda_ctx* c, const GmmLaunch& a, int n_runs) {
     const size_t smem = sizeof(float4) * size_t(c->sat2_n) + sizeof(unsigned) * size_t(c->gmm_cull_words);
-    if (smem > 32 * 1024) CK(cudaFuncSetAttribute((const void*)gmm_cluster_run_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    // the kernel holds ~30 KB of static shared memory (the peers' slots): static + dynamic pass 48 KB early
+    if (smem > 12 * 1024) CK(cudaFuncSetAttribute((const void*)gmm_cluster_run_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     // up to 8 runs: 16 CTAs per cluster (one pass over 10^4 samples; a GPC holds one such cluster), else 8
     int cl = n_runs <= 8 ? 16 : GMM_CLUSTER;
     if (cl > 8) CK(cudaFuncSetAttribute((const void*)gmm_cluster_run_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));

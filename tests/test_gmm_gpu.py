@@ -240,3 +240,22 @@ def test_gmm_cluster_kernel_equals_per_waypoint_kernels(ctx, plan, scenes, K, N,
     for b in (0, 11):
         one = ctx.gmm_run(plan, K, N, mode=abi.MODE_PHILOX, stream_id=40 + b)
         np.testing.assert_allclose(batch["probabilities"][b], one["probabilities"], rtol=1e-9, atol=1e-12)
+
+
+@pytest.mark.parametrize("T", [120, 250])
+def test_gmm_cluster_kernel_long_plans(ctx, plan, scenes, T, monkeypatch):
+    """Plans whose candidate lists make static + dynamic shared memory of the cluster kernel pass 48 KB (T = 120: 23 KB of
+    lists beside 30 KB of static slots; T = 250: 48 KB of lists): same results as the per-waypoint kernels."""
+    import pcoll_b200
+    abi, inp = pcoll_b200.cuda_abi, pcoll_b200.inputs
+    boxes = inp.synthetic_obstacle_field(5, 64)
+    ctx.set_scene(boxes, scenes["pr2test2"]["hulls"])
+    tr, od = inp.synthetic_plans(5, 1, T, boxes, clear=-0.1)
+    long_plan = dict(plan)
+    long_plan["trajectory"], long_plan["odometry"] = tr[0], od[0]
+    monkeypatch.delenv("MCSIM_GMM_NO_CLUSTER", raising=False)
+    a = ctx.gmm_run(long_plan, 3, 4000, mode=abi.MODE_PHILOX, stream_id=3)
+    monkeypatch.setenv("MCSIM_GMM_NO_CLUSTER", "1")
+    b = ctx.gmm_run(long_plan, 3, 4000, mode=abi.MODE_PHILOX, stream_id=3)
+    np.testing.assert_allclose(a["probabilities"], b["probabilities"], rtol=1e-9, atol=1e-12)
+    assert a["kernel_ms"] < b["kernel_ms"]
