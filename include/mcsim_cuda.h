@@ -175,6 +175,11 @@ int mcsim_host_normals(uint64_t seed, uint32_t stream_id, int T, int per_step, d
  * 24 radius + 16 angle bits (csrc/philox.h, "step draws").  For audits of the Philox mode; no GPU. */
 int mcsim_step_normals(uint64_t seed, uint64_t rollout_id, int t, double out[12]);
 
+/* The same 12 draws for rollouts id0 .. id0 + n - 1 as the packed rollout kernel computes them ON THE DEVICE (FP32,
+ * MUFU lg2 / sqrt / sin / cos; the device function mc_philox2_kernel itself calls): out = [n][12] floats on the host.
+ * For distribution tests of the Philox-mode noise (Kolmogorov-Smirnov, tail mass) and audits against mcsim_step_normals. */
+int mcsim_cuda_step_normals(mcsim_cuda_ctx* ctx, uint64_t seed, uint64_t id0, uint64_t n, int t, float* out);
+
 /* ---- GMM truncation (moment matching) ---------------------------------------------------- */
 typedef struct {
     int K;                       /* components (setNumGaussians) */

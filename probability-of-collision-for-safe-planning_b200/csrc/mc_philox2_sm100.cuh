@@ -84,6 +84,24 @@ __device__ __forceinline__ Philox2 philox_pair(unsigned long long id0, unsigned 
     return o;
 }
 
+// the 3 + NL standard normals of step t -> t+1 for both rollouts of a thread: 12 per two Philox blocks
+// (philox.h: step draws); also what mcsim_cuda_step_normals dumps for the distribution tests
+template <int NL>
+__device__ __forceinline__ void step_normals2(f2* zn, int t, unsigned long long id0, unsigned long long id1, unsigned k0, unsigned k1) {
+#pragma unroll
+    for (int g = 0; g < (3 + NL + 11) / 12; ++g) {
+        const Philox2 wa = philox_pair(id0, id1, unsigned(t * 8 + 2 * g), unsigned(mcsim_rng::PURPOSE_STEP), k0, k1);
+        const Philox2 wb = philox_pair(id0, id1, unsigned(t * 8 + 2 * g + 1), unsigned(mcsim_rng::PURPOSE_STEP), k0, k1);
+        unsigned rad0[6], ang0[6], rad1[6], ang1[6];
+        mcsim_rng::step_bits(wa.a, wb.a, rad0, ang0);  // (the integer angle halves are dead code here)
+        mcsim_rng::step_bits(wa.b, wb.b, rad1, ang1);
+        const unsigned aw0[3] = {wb.a.y, wb.a.z, wb.a.w}, aw1[3] = {wb.b.y, wb.b.z, wb.b.w};
+#pragma unroll
+        for (int j = 0; j < 6; ++j)
+            box_muller2_bits(rad0[j], half16f(aw0[j >> 1], j & 1), rad1[j], half16f(aw1[j >> 1], j & 1), zn[12 * g + 2 * j], zn[12 * g + 2 * j + 1]);
+    }
+}
+
 // ---- packed SAT: both lanes against every live pair ------------------------------------------------
 // The same separating-axis test as pair_hit (sat_device.cuh) on the orientation-grouped table
 // (mcsim_cuda_set_scene): per class of boxes sharing an axis direction (mod 90 degrees) the relative
@@ -237,18 +255,7 @@ __device__ __forceinline__ void step2(Rollout2& st, const float* r, int t, unsig
     // ---- step t -> t+1 of this rollout's own real robot + EKF
     // noise: (rot1, trans, rot2, obs 0 .. NL-1), 12 normals per two Philox blocks (philox.h: step draws)
     f2 zn[12 * ((3 + NL + 11) / 12)];
-#pragma unroll
-    for (int g = 0; g < (3 + NL + 11) / 12; ++g) {
-        const Philox2 wa = philox_pair(id0, id1, unsigned(t * 8 + 2 * g), unsigned(mcsim_rng::PURPOSE_STEP), k0, k1);
-        const Philox2 wb = philox_pair(id0, id1, unsigned(t * 8 + 2 * g + 1), unsigned(mcsim_rng::PURPOSE_STEP), k0, k1);
-        unsigned rad0[6], ang0[6], rad1[6], ang1[6];
-        mcsim_rng::step_bits(wa.a, wb.a, rad0, ang0);  // (the integer angle halves are dead code here)
-        mcsim_rng::step_bits(wa.b, wb.b, rad1, ang1);
-        const unsigned aw0[3] = {wb.a.y, wb.a.z, wb.a.w}, aw1[3] = {wb.b.y, wb.b.z, wb.b.w};
-#pragma unroll
-        for (int j = 0; j < 6; ++j)
-            box_muller2_bits(rad0[j], half16f(aw0[j >> 1], j & 1), rad1[j], half16f(aw1[j >> 1], j & 1), zn[12 * g + 2 * j], zn[12 * g + 2 * j + 1]);
-    }
+    step_normals2<NL>(zn, t, id0, id1, k0, k1);
     // applied control (generateL + :719-726): u = u_req = inverseOdometry(mu, x*_{t+1}); u*_0 at t = 0
     f2 u[3];
     if (t == 0) {
@@ -438,6 +445,21 @@ __global__ void __launch_bounds__(128, MC_P2_CTAS_PER_SM) mc_philox2_kernel(cons
     if (threadIdx.x == 0 && s_cnt[0]) atomicAdd(&a.counters[CNT_HITS], (unsigned long long)s_cnt[0]);
     for (int t = threadIdx.x; t < T; t += blockDim.x)
         if (s_hist[t]) atomicAdd(&a.counters[CNT_HIST + t], (unsigned long long)s_hist[t]);
+}
+
+// test hook (mcsim_cuda_step_normals): the 12 step normals of rollouts id0 .. id0 + n - 1 at step t exactly as
+// mc_philox2_kernel draws them (same device function: MUFU lg2 / sqrt / sin / cos on 24 + 16 bits)
+__global__ void mc_step_normals_kernel(unsigned long long id0, unsigned long long n, int t, unsigned k0, unsigned k1, float* __restrict__ out) {
+    const unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned long long i0 = 2 * j, i1 = 2 * j + 1;
+    if (i0 >= n) return;
+    f2 zn[12];
+    step_normals2<8>(zn, t, id0 + i0, id0 + i1, k0, k1);
+#pragma unroll
+    for (int k = 0; k < 12; ++k) {
+        out[i0 * 12 + k] = lo(zn[k]);
+        if (i1 < n) out[i1 * 12 + k] = hi(zn[k]);
+    }
 }
 
 #endif

@@ -609,6 +609,23 @@ extern "C" int mcsim_step_normals(uint64_t seed, uint64_t rollout_id, int t, dou
     return MCSIM_OK;
 }
 
+// the same draws as the packed kernel computes them on the device (FP32, MUFU): [n][12] floats to the host
+extern "C" int mcsim_cuda_step_normals(mcsim_cuda_ctx* c, uint64_t seed, uint64_t id0, uint64_t n, int t, float* out) {
+    if (!c || !out || t < 0 || n == 0 || n > (1ull << 28)) return fail(MCSIM_ERR_ARG, "step_normals: bad arguments");
+    CK(cudaSetDevice(c->device));
+    DevBuf buf;
+    CK(buf.reserve(sizeof(float) * 12 * n));
+    const unsigned long long thr = (n + 1) / 2;
+    mc_step_normals_kernel<<<unsigned((thr + 255) / 256), 256, 0, c->stream>>>(id0, n, t, unsigned(seed), unsigned(seed >> 32), (float*)buf.p);
+    ++c->launches;
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, buf.p, sizeof(float) * 12 * n, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    buf.release();
+    if (e != cudaSuccess) return fail(MCSIM_ERR_CUDA, "step_normals: %s", cudaGetErrorString(e));
+    return MCSIM_OK;
+}
+
 // ---- GMM mode -----------------------------------------------------------------------------------
 // two standard normals from one Philox block, host side (the host thread of a Philox-mode GMM run)
 extern "C" int mcsim_host_normals(uint64_t seed, uint32_t stream_id, int T, int per_step, double* out) {

@@ -145,6 +145,7 @@ def lib():
         L.mcsim_host_normals.argtypes = [C.c_uint64, C.c_uint32, C.c_int, C.c_int, _dp]
         L.mcsim_step_normals.argtypes = [C.c_uint64, C.c_uint64, C.c_int, _dp]
         L.mcsim_step_normals.restype = C.c_int
+        L.mcsim_cuda_step_normals.argtypes = [vp, C.c_uint64, C.c_uint64, C.c_uint64, C.c_int, _fp]
         L.mcsim_cuda_gmm_truncate.argtypes = [vp, C.POINTER(GmmTruncateParams), C.POINTER(GmmTruncateResult)]
         L.mcsim_cuda_gmm_run.argtypes = [vp, C.POINTER(McParams), C.POINTER(GmmRunParams), C.POINTER(GmmRunResult)]
         L.mcsim_cuda_gmm_run_batch.argtypes = [vp, C.POINTER(McParams), C.POINTER(GmmBatchParams), C.POINTER(GmmBatchResult)]
@@ -312,6 +313,13 @@ class Context:
         out.update(hits=int(r.hits), near_contact=int(r.near_contact), executed_steps=int(r.executed_steps),
                    pair_tests=int(r.pair_tests), kernel_ms=float(r.kernel_ms),
                    P=(r.hits / n if n else 0.0))
+        return out
+
+    def step_normals(self, n, t=0, id0=0, seed=0x5AFEC0DE):
+        """[n, 12] float32: the step draws of rollouts id0 .. id0 + n - 1 at step t, computed on the device by the
+        packed kernel's own device function."""
+        out = np.zeros((int(n), 12), dtype=np.float32)
+        check(lib().mcsim_cuda_step_normals(self._h, int(seed), int(id0), int(n), int(t), out.ctypes.data_as(_fp)))
         return out
 
     def mc_prepare(self, params):

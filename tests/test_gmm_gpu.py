@@ -60,6 +60,33 @@ def test_gmm_replay_vs_live_reference(ctx, plan, scenes):
         _assert_mixture_close(out["gmm_pre"], ref["gmm_pre"], "pre-truncation mixtures K=%d" % K)
 
 
+def test_gmm_replay_config2_size_vs_live_reference(ctx, plan, scenes):
+    """BASELINE config 2 at its real size: K = 3 components, N = 10,000 samples per waypoint (MCSimulation.py:204-205),
+    all 56 waypoints, deterministic mode against the reference's own runGMMEstimation() run live on the same 1.68 M
+    injected normals and its multinomial counts (MCSimulator.h:570-642): per-waypoint colliding fractions exact,
+    every pre-truncation mixture, the final mixture and P within 1e-4 relative."""
+    import oracle_ref
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    if not oracle_ref.available():
+        pytest.skip("oracle/_ref not built")
+    T = plan["trajectory"].shape[1]
+    sc = scenes["pr2test2"]
+    ctx.set_scene(sc["boxes"], sc["hulls"])
+    K, N = 3, 10000
+    for seed in (2018, 2019):
+        draws = np.random.Generator(np.random.PCG64(seed)).standard_normal(3 * N * T + 11 * (T - 1))
+        ref = oracle_ref.gmm_run(plan, sc["boxes"], sc["hulls"], K, N, draws=draws, multinomial_seed=seed)
+        out = ctx.gmm_run(plan, K, N, mode=abi.MODE_REPLAY, draws=draws, counts=ref["gmm_counts"], record=True)
+        assert out["degenerate"] == 0
+        np.testing.assert_array_equal(out["probabilities"], ref["probabilities"])
+        assert abs(out["P"] - ref["P"]) <= RTOL * ref["P"]
+        _assert_mixture_close(out["gmm_pre"], ref["gmm_pre"], "pre-truncation mixtures, N = 10,000")
+        _assert_mixture_close(out["gmm_post"], ref["gmm_post"], "final mixture, N = 10,000")
+        print("config 2 (K=3, N=10,000) seed %d: P gpu %.6f reference %.6f, colliding samples %d" %
+              (seed, out["P"], ref["P"], int(round(ref["probabilities"].sum() * N))))
+
+
 def test_gmm_truncate_single_shot_matches_first_waypoint(ctx, plan, scenes):
     import pcoll_b200
     abi = pcoll_b200.cuda_abi

@@ -110,13 +110,58 @@ def test_philox_inside_reference_confidence_interval(ctx, plan, scenes):
     N = 1 << 20
     p, keep = abi.make_mc_params(plan, n_rollouts=N, mode=abi.MODE_PHILOX, early_exit=True)
     out = ctx.mc_run(p)
-    print("philox P=%.5f reference mean=%.5f +- %.5f (99%% CI)" % (out["P"], dist["mean"], half))
+    print("philox P=%.5f reference mean=%.5f +- %.5f (99%% CI, %d reference runs)" % (out["P"], dist["mean"], half, dist["runs"]))
+    assert half < 0.003      # 2,000 reference runs (tests/golden/make_round2.py)
     assert abs(out["P"] - dist["mean"]) < half
     # early exit does not change the estimate
     p2, keep2 = abi.make_mc_params(plan, n_rollouts=N, mode=abi.MODE_PHILOX, early_exit=False)
     out2 = ctx.mc_run(p2, want_counts=True)
     assert out2["hits"] == out["hits"]
     assert out2["executed_steps"] == N * plan["trajectory"].shape[1]
+
+
+def test_philox_step_normals_distribution(ctx):
+    """The packed kernel's step draws (24 radius + 16 angle bits per Box-Muller pair, MUFU lg2 / sqrt / sin / cos,
+    csrc/philox.h) dumped from the device function the kernel itself calls: 10^7 draws against N(0, 1) --
+    Kolmogorov-Smirnov distance below the 1 % critical value 1.628 / sqrt(n), tail masses beyond 3, 4 and 5 sigma
+    inside 4.5-sigma Poisson bounds, moments and pair correlation per draw slot -- and against the FP64 host
+    recomputation of the same bits (mcsim_step_normals)."""
+    import ctypes as C
+    from scipy import stats
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    n_roll = 833_334                       # x 12 = 10,000,008 draws
+    z = ctx.step_normals(n_roll, t=17, id0=5_000_000_000)   # ids beyond 2^32: the high counter word is in play
+    assert z.shape == (n_roll, 12) and np.isfinite(z).all()
+    flat = z.astype(np.float64).ravel()
+    n = flat.size
+    d, pval = stats.kstest(flat, "norm")
+    print("KS distance %.3e (1%% critical %.3e), max |z| %.3f" % (d, 1.628 / np.sqrt(n), np.abs(flat).max()))
+    assert d < 1.628 / np.sqrt(n)
+    for k, p_tail in ((3.0, 2.6997960632601866e-3), (4.0, 6.334248366623973e-5), (5.0, 5.733031437583878e-7)):
+        got, want = int((np.abs(flat) > k).sum()), n * p_tail
+        print("|z| > %.0f: %d draws, expected %.1f" % (k, got, want))
+        assert abs(got - want) < 4.5 * np.sqrt(want) + 1
+    assert np.abs(flat).max() < 5.9       # sqrt(2 * 25 ln 2) = 5.887: the 24-bit radius cap
+    # per slot: mean, variance, kurtosis, correlation with the partner of its Box-Muller pair
+    for j in range(12):
+        col = z[:, j].astype(np.float64)
+        assert abs(col.mean()) < 4.5 / np.sqrt(n_roll)
+        assert abs(col.var() - 1.0) < 4.5 * np.sqrt(2.0 / n_roll)
+        assert abs((col ** 4).mean() - 3.0) < 4.5 * np.sqrt(96.0 / n_roll)
+    for j in range(0, 12, 2):
+        r = np.corrcoef(z[:, j], z[:, j + 1])[0, 1]
+        assert abs(r) < 4.5 / np.sqrt(n_roll)
+    r = np.corrcoef(z[:, 0], z[:, 2])[0, 1]
+    assert abs(r) < 4.5 / np.sqrt(n_roll)
+    # FP64 recomputation from the same Philox bits on the host
+    host = np.zeros(12)
+    worst = 0.0
+    for i in (0, 1, 2, 3, 77, 4096, n_roll - 1):
+        assert abi.lib().mcsim_step_normals(0x5AFEC0DE, 5_000_000_000 + i, 17, host.ctypes.data_as(C.POINTER(C.c_double))) == 0
+        worst = max(worst, float(np.abs(z[i] - host).max()))
+    print("device FP32 / MUFU draws vs FP64 host recomputation: max |diff| %.2e" % worst)
+    assert worst < 2e-5
 
 
 def test_philox_shard_invariance(ctx, plan, scenes):

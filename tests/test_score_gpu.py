@@ -32,6 +32,34 @@ def test_single_plan_batch_equals_mc_run(ctx, plan, scenes):
         assert ee["hits"][0] == sc["hits"][0] and ee["executed_steps"] < sc["executed_steps"]
 
 
+def test_scoring_inside_reference_confidence_interval(ctx, plan):
+    """Batched scoring against the ORACLE, not against another CUDA path: 3 plans of the config-4 generator on its
+    256-box field; the reference's own runSimulation() (oracle/_ref, MCSimulator.h:649-864) was run 256 x 1,000
+    particles per plan with the same boxes (tests/golden/score_oracle.json, made by tests/golden/make_round2.py).
+    score_plans' P (65,536 rollouts per plan, Philox law = the expectation of the reference's per-run estimate)
+    must fall inside the 99 % confidence interval of the reference's run-to-run mean; with the broad phase and
+    with every pair tested."""
+    import json
+    import os
+    import pcoll_b200
+    from conftest import GOLD
+    inp = pcoll_b200.inputs
+    ref = json.load(open(os.path.join(GOLD, "score_oracle.json")))
+    boxes = inp.synthetic_obstacle_field()
+    tr, od = inp.synthetic_plans(ref["seed"], len(ref["plans"]), ref["T"], boxes, clear=ref["clear"])
+    for q, r in enumerate(ref["plans"]):
+        np.testing.assert_allclose(tr[q, :, 0], r["start"], rtol=0, atol=1e-12)   # same plans as the oracle saw
+    ctx.set_scene(boxes, _hulls())
+    R = 65536
+    for margin in (3.0, -1.0):
+        out = ctx.score_plans(plan, tr, od, R, margin=margin)
+        for q, r in enumerate(ref["plans"]):
+            half = 2.576 * np.sqrt(r["std"] ** 2 / ref["runs"] + out["P"][q] * (1 - out["P"][q]) / R)
+            print("plan %d margin %.0f: P %.4f, reference %.4f +- %.4f" % (q, margin, out["P"][q], r["mean"], half))
+            assert abs(out["P"][q] - r["mean"]) < half, (q, margin, out["P"][q], r["mean"], half)
+    assert min(r["mean"] for r in ref["plans"]) < 0.9     # the anchor is informative (not all plans at P = 1)
+
+
 def test_broad_phase_is_exact_and_split_invariant(ctx, plan):
     import pcoll_b200
     inp = pcoll_b200.inputs
