@@ -115,6 +115,11 @@ typedef struct {
                                     are all near x*_t tests only those (same flags and counts, fewer pair
                                     tests; result.pair_tests counts the executed ones); 1: every live
                                     (hull, box) pair is tested at every step, as CheckCollision does */
+    int no_compaction;           /* packed kernel with early_exit only.  0: runs of >= 2^18 rollouts are cut into segments
+                                    of 4 waypoints, the survivors of a segment are compacted in device memory and the
+                                    next launch runs full warps of them (same flags, hits and histogram; executed
+                                    rollout-steps drop to the free ones); 1: one launch, a warp leaves when all its
+                                    rollouts have hit */
 } mcsim_mc_params;
 
 enum { MCSIM_MODE_REPLAY = 0, MCSIM_MODE_PHILOX = 1 };

@@ -73,7 +73,7 @@ __device__ __forceinline__ void sincos2(f2 a, f2& s, f2& c) {
 
 // a mod 2 pi into [0, 2 pi] (angleWrap, MCSimulator.h:56-65; both ends kept) without branches:
 // k = rint(a / 2 pi - 1/2) by the 1.5 * 2^23 trick, a - 2 pi k in two FMAs (hi + lo of 2 pi).
-__device__ __forceinline__ f2 wrap2(f2 a) {
+__device__ __forceinline__ f2 wrap2(f2 a) {  // @phase wrap
     const float M = 12582912.0f;
     const f2 t = fma2(a, 0.15915494309189535f, -0.5f);
     const f2 k = add2(add2(t, M), -M);
@@ -82,7 +82,7 @@ __device__ __forceinline__ f2 wrap2(f2 a) {
 
 // atan2(y, x) per lane pair: octant reduction + odd minimax polynomial of degree 17
 // (Abramowitz & Stegun 4.4.49, |error| <= 1e-7 in FP32), result in [-pi, pi].
-__device__ __forceinline__ f2 atan2_2(f2 y, f2 x) {
+__device__ __forceinline__ f2 atan2_2(f2 y, f2 x) {  // @phase atan2
     float x0, x1, y0, y1;
     un2(x, x0, x1);
     un2(y, y0, y1);

@@ -77,6 +77,7 @@ struct mcsim_cuda_ctx {
     std::vector<unsigned> h_pair_sat2;  // per pair: record offset | class header offset << 16 in the grouped table
     double h_reach[MCSIM_MAX_HULLS] = {0};
     DevBuf mc_cull;
+    DevBuf seg_state[2], seg_alive;  // early exit with survivor compaction: double-buffered state of the survivors, counts per segment
     int gmm_cull_words = 0, gmm_cull_words_cached = 0;  // words of ONE plan's lists (this run / on the device)
     // the lists depend on (scene, trajectory) only: repeated runs of one plan (the reference's 200-run loop) reuse them
     uint64_t scene_epoch = 0;
@@ -140,6 +141,7 @@ extern "C" void mcsim_cuda_destroy(mcsim_cuda_ctx* c) {
     cudaStreamSynchronize(c->stream);
     c->plan.release(); c->z0.release(); c->counters.release(); c->counts.release();
     c->poses.release(); c->clearance.release();
+    c->seg_state[0].release(); c->seg_state[1].release(); c->seg_alive.release();
     c->hulls_d.release(); c->pairs_d.release(); c->sat2.release(); c->mc_cull.release(); c->gmm_cull.release(); c->gmm_nominal.release(); c->gmm_tests.release(); c->gmm_plans.release(); c->gmm_robot_normals.release();
     c->pairs_f.release(); c->sc_plans.release(); c->sc_hits.release(); c->sc_counters.release();
     c->em_x.release(); c->em_comps.release(); c->em_hefts.release(); c->em_means.release(); c->em_fcovs.release();
@@ -454,6 +456,7 @@ extern "C" int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* c, const mcsim_mc_params* p
             float* w = &plan2[size_t(t) * MC_PLAN2_STRIDE];
             for (int k = 0; k < 9; ++k) w[k] = r[k];
             w[9] = r[6] + r[8];
+            w[10] = float(mcsim_math::angle_wrap(p->trajectory[2 * T + t]));
         }
     }
     std::vector<unsigned> cull;
@@ -491,6 +494,47 @@ extern "C" int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* c, const mcsim_mc_params* p
     return MCSIM_OK;
 }
 
+typedef void (*mc_seg_kernel_t)(const McSegLaunch);
+// Early exit with survivor compaction (mc_philox2_segment_kernel): chunks of at most MC_SEG_CHUNK rollouts, one launch
+// per MC_SEG waypoints; everything is queued on the context's stream, the survivor counts stay on the device.
+#define MC_SEG_CHUNK (1ull << 24)
+#define MC_SEG_MIN_ROLLOUTS (1ull << 18)   // below this the plain early-exit kernel is as fast (launch overheads)
+static int mc_launch_segmented(mcsim_cuda_ctx* c, const McLaunch& a0, uint64_t n, uint64_t offset, unsigned* d_counts, int block, size_t smem, unsigned grid_cap) {
+    const int T = c->mc_T;
+    const int n_seg = (T + MC_SEG - 1) / MC_SEG;
+    const uint64_t chunk = n < MC_SEG_CHUNK ? ((n + 1) & ~1ull) : MC_SEG_CHUNK;
+    CK(c->seg_state[0].reserve(sizeof(float) * MC_STATE_WORDS * chunk));
+    CK(c->seg_state[1].reserve(sizeof(float) * MC_STATE_WORDS * chunk));
+    CK(c->seg_alive.reserve(sizeof(unsigned) * (size_t(n_seg) + 1)));
+    mc_seg_kernel_t k = c->mc.estimator == MCSIM_EST_CLOSEDLOOP ? mc_philox2_segment_kernel<MCSIM_EST_CLOSEDLOOP, 8> : mc_philox2_segment_kernel<MCSIM_EST_REFERENCE, 8>;
+    if (smem > 40 * 1024) CK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    if (d_counts) CK(cudaMemsetAsync(d_counts, 0, sizeof(unsigned) * n, c->stream));
+    for (uint64_t done = 0; done < n; done += chunk) {
+        const uint64_t m = n - done < chunk ? n - done : chunk;
+        CK(cudaMemsetAsync(c->seg_alive.p, 0, sizeof(unsigned) * (size_t(n_seg) + 1), c->stream));
+        for (int sg = 0; sg < n_seg; ++sg) {
+            McSegLaunch g;
+            g.base = a0;
+            g.base.n = m;
+            g.base.offset = offset + done;
+            g.base.counts = d_counts ? d_counts + done : nullptr;
+            g.t0 = sg * MC_SEG;
+            g.t1 = (sg + 1) * MC_SEG < T ? (sg + 1) * MC_SEG : T;
+            g.in = sg == 0 ? nullptr : (const float*)c->seg_state[(sg - 1) & 1].p;
+            g.out = g.t1 < T ? (float*)c->seg_state[sg & 1].p : nullptr;
+            g.n_in = (const unsigned*)c->seg_alive.p + sg;
+            g.n_out = (unsigned*)c->seg_alive.p + sg + 1;
+            g.cap = unsigned(chunk);
+            const unsigned long long want = ((m + 1) / 2 + block - 1) / block;
+            const unsigned grid = unsigned(want < grid_cap ? (want ? want : 1) : grid_cap);
+            k<<<grid, block, smem, c->stream>>>(g);
+            ++c->launches;
+        }
+        CK(cudaGetLastError());
+    }
+    return MCSIM_OK;
+}
+
 static int mc_launch_impl(mcsim_cuda_ctx* c, uint64_t n, uint64_t offset, const double* d_z0, unsigned* d_counts,
                           float* d_poses, float* d_clear) {
     const mcsim_mc_params& p = c->mc;
@@ -522,6 +566,8 @@ static int mc_launch_impl(mcsim_cuda_ctx* c, uint64_t n, uint64_t offset, const 
     // persistent: whole waves of resident CTAs
     const unsigned long long cap = (unsigned long long)c->n_sm * (packed ? MC_P2_CTAS_PER_SM : 8);
     const unsigned grid = unsigned(want < cap ? (want ? want : 1) : cap);
+    if (packed && p.early_exit && n >= MC_SEG_MIN_ROLLOUTS && c->mc_T > MC_SEG && !p.no_compaction)
+        return mc_launch_segmented(c, a, n, offset, d_counts, block, smem, unsigned(cap));
     if (smem > 40 * 1024) CK(cudaFuncSetAttribute((const void*)k, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     k<<<grid, block, smem, c->stream>>>(a);
     ++c->launches;
@@ -1215,6 +1261,7 @@ extern "C" int mcsim_cuda_score_prepare(mcsim_cuda_ctx* c, const mcsim_score_par
         for (int t = 0; t < T; ++t) {
             float* w = &tab[(size_t(q) * T + t) * MC_PLAN2_STRIDE];
             for (int k = 0; k < 3; ++k) w[k] = float(tr[k * T + t]);
+            w[10] = float(mcsim_math::angle_wrap(tr[2 * T + t]));
             if (t < T - 1) {
                 double us[3], M[3];
                 for (int k = 0; k < 3; ++k) { us[k] = od[k * (T - 1) + t]; w[3 + k] = float(us[k]); }

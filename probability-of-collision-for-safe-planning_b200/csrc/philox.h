@@ -20,7 +20,7 @@ namespace mcsim_rng {
 
 struct u32x4 { uint32_t x, y, z, w; };
 
-MCSIM_PHD void mulhilo(uint32_t a, uint32_t b, uint32_t& hi, uint32_t& lo) {
+MCSIM_PHD void mulhilo(uint32_t a, uint32_t b, uint32_t& hi, uint32_t& lo) {  // @phase philox
 #ifdef __CUDA_ARCH__
     lo = a * b;
     hi = __umulhi(a, b);
@@ -31,7 +31,7 @@ MCSIM_PHD void mulhilo(uint32_t a, uint32_t b, uint32_t& hi, uint32_t& lo) {
 #endif
 }
 
-MCSIM_PHD u32x4 philox4x32_10(u32x4 c, uint32_t k0, uint32_t k1) {
+MCSIM_PHD u32x4 philox4x32_10(u32x4 c, uint32_t k0, uint32_t k1) {  // @phase philox
 #pragma unroll
     for (int r = 0; r < 10; ++r) {
         uint32_t hi0, lo0, hi1, lo1;
@@ -64,7 +64,7 @@ MCSIM_PHD float u01(uint32_t x) { return float(x) * 2.3283064365386963e-10f + 1.
 // kernel, the scalar audit kernel and the scoring kernel, so their rollouts are the same experiments):
 //   radius of pair j = 0..3: a.{x,y,z,w} >> 8;  pair 4: b.x >> 8;  pair 5: low bytes of a.x, a.y, a.z
 //   angle  of pair j: half (j & 1) of b.{y,z,w}[j >> 1]
-MCSIM_PHD void step_bits(const u32x4& a, const u32x4& b, uint32_t rad[6], uint32_t ang[6]) {
+MCSIM_PHD void step_bits(const u32x4& a, const u32x4& b, uint32_t rad[6], uint32_t ang[6]) {  // @phase draw_bits
     rad[0] = a.x >> 8; rad[1] = a.y >> 8; rad[2] = a.z >> 8; rad[3] = a.w >> 8; rad[4] = b.x >> 8;
 #ifdef __CUDA_ARCH__
     rad[5] = __byte_perm(__byte_perm(a.x, a.y, 0x0400), a.z, 0x4210) >> 8;

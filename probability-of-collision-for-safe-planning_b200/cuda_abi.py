@@ -29,6 +29,7 @@ class McParams(C.Structure):
         ("n_rollouts", C.c_uint64), ("rollout_offset", C.c_uint64),
         ("mode", C.c_int), ("estimator", C.c_int), ("early_exit", C.c_int), ("seed", C.c_uint64),
         ("applied", _dp), ("z0", _dp), ("near_eps", C.c_double), ("precise", C.c_int), ("exhaustive", C.c_int),
+        ("no_compaction", C.c_int),
     ]
 
 
@@ -185,7 +186,7 @@ def dptr(a):
 
 
 def make_mc_params(plan, n_rollouts=0, mode=MODE_PHILOX, estimator=EST_REFERENCE, early_exit=True,
-                   seed=0x5AFEC0DE, rollout_offset=0, applied=None, z0=None, near_eps=1e-4, precise=False, exhaustive=False):
+                   seed=0x5AFEC0DE, rollout_offset=0, applied=None, z0=None, near_eps=1e-4, precise=False, exhaustive=False, no_compaction=False):
     """plan: dict(trajectory[3,T], odometry[3,T-1], alphas[4], Q, landmarks[2,L], cov0[3,3]).
     Returns (McParams, keepalive list of the arrays its pointers refer to)."""
     tr = np.ascontiguousarray(plan["trajectory"], dtype=np.float64)
@@ -212,6 +213,7 @@ def make_mc_params(plan, n_rollouts=0, mode=MODE_PHILOX, estimator=EST_REFERENCE
     p.near_eps = float(near_eps)
     p.precise = int(bool(precise))
     p.exhaustive = int(bool(exhaustive))
+    p.no_compaction = int(bool(no_compaction))
     return p, keep
 
 

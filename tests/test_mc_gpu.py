@@ -254,6 +254,56 @@ def test_philox_broad_phase_is_exact(ctx, plan, scenes, name, est):
                 assert a["pair_tests"] < b["pair_tests"]
 
 
+@pytest.mark.parametrize("est", ["reference", "closedloop"])
+@pytest.mark.parametrize("name", ["pr2test2", "pr2custom"])
+def test_early_exit_survivor_compaction_is_exact(ctx, plan, scenes, name, est):
+    """Early exit with survivor compaction (runs of >= 2^18 rollouts: one launch per 4 waypoints, the survivors' state
+    goes through a compacted buffer in device memory) against the one-launch early-exit kernel and against the full
+    per-rollout counts: identical flags for every rollout, identical hit total and first-hit histogram; executed
+    rollout-steps = the free ones (sum over waypoints of rollouts without a hit so far) in both early-exit forms -- the
+    compacted launches just no longer carry the dead lanes along.  Odd N: masked lane."""
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    ctx.set_scene(scenes[name]["boxes"], scenes[name]["hulls"])
+    e = abi.EST_REFERENCE if est == "reference" else abi.EST_CLOSEDLOOP
+    N = (1 << 18) + 4097
+    T = plan["trajectory"].shape[1]
+    outs = {}
+    for key, kw in (("full", dict(early_exit=False)), ("ee", dict(early_exit=True, no_compaction=True)), ("seg", dict(early_exit=True))):
+        p, keep = abi.make_mc_params(plan, n_rollouts=N, mode=abi.MODE_PHILOX, estimator=e, rollout_offset=(1 << 33) + 5, **kw)
+        outs[key] = ctx.mc_run(p, want_counts=True, want_hist=True)
+    flags = (outs["full"]["counts"] > 0).astype(np.uint32)
+    for key in ("ee", "seg"):
+        np.testing.assert_array_equal(outs[key]["counts"], flags)
+        np.testing.assert_array_equal(outs[key]["first_hit_hist"], outs["full"]["first_hit_hist"])
+        assert outs[key]["hits"] == outs["full"]["hits"] == int(flags.sum())
+    # free rollout-steps: a rollout is tested at waypoints 0 .. first hit
+    hist = outs["full"]["first_hit_hist"].astype(np.int64)
+    free_steps = int((hist * (np.arange(T) + 1)).sum() + (N - hist.sum()) * T)
+    assert outs["seg"]["executed_steps"] == outs["ee"]["executed_steps"] == free_steps
+    # (pair tests differ a little either way: compacted warps hold other rollouts, so the warp-wide list level differs)
+    print("%s/%s: P=%.4f free steps %.3f of nominal; kernel ms: full %.3f, one-launch early exit %.3f, compaction %.3f" % (
+        name, est, outs["full"]["P"], free_steps / (N * T), outs["full"]["kernel_ms"], outs["ee"]["kernel_ms"], outs["seg"]["kernel_ms"]))
+
+
+def test_early_exit_compaction_across_chunks(ctx, plan, scenes):
+    """More than one chunk of 2^24 rollouts (the survivor buffers are reused chunk after chunk) and a plan whose length is
+    no multiple of the segment length: hit total and histogram equal to the one-launch kernel's."""
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    ctx.set_scene(scenes["pr2test2"]["boxes"], scenes["pr2test2"]["hulls"])
+    short = dict(plan)
+    short["trajectory"] = np.ascontiguousarray(plan["trajectory"][:, :30])
+    short["odometry"] = np.ascontiguousarray(plan["odometry"][:, :29])
+    N = (1 << 24) + 70001
+    outs = []
+    for nc in (True, False):
+        p, keep = abi.make_mc_params(short, n_rollouts=N, mode=abi.MODE_PHILOX, early_exit=True, no_compaction=nc)
+        outs.append(ctx.mc_run(p, want_hist=True))
+    assert outs[0]["hits"] == outs[1]["hits"] and outs[0]["executed_steps"] == outs[1]["executed_steps"]
+    np.testing.assert_array_equal(outs[0]["first_hit_hist"], outs[1]["first_hit_hist"])
+
+
 def test_philox_edge_cases_empty_scene_single_waypoint_other_landmark_counts(ctx, plan, scenes):
     """Empty obstacle set (no live pair): no rollout ever hits; T = 1: only the start poses are tested;
     a landmark count other than 8 or a plan longer than the packed kernel's table falls back to the scalar
