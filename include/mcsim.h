@@ -43,6 +43,11 @@ mcsim_handle* mcsim_create_from_arrays(const double* boxes, int n_boxes, const d
  * mcsim_last_error(h). */
 int mcsim_send_command(mcsim_handle* h, const char* cmd, char* out, size_t out_cap, size_t* out_len);
 
+/* The reply of the last successful command again (NUL-terminated, truncated to out_cap - 1 characters); returns its
+ * full length.  For replies longer than the buffer given to mcsim_send_command -- fetching them must not re-run the
+ * command (runGMMEstimationBatch 10000 returns ~90 KB and advances the run counter). */
+size_t mcsim_last_output(mcsim_handle* h, char* out, size_t out_cap);
+
 const char* mcsim_last_error(mcsim_handle* h);
 
 /* The extracted geometry (so a caller can check or reuse it).  Copies up to cap rows of 8 doubles; returns the

@@ -44,7 +44,8 @@ enum {
     MCSIM_ERR_ARG = 2,        /* bad argument / limits exceeded */
     MCSIM_ERR_NODEVICE = 3,   /* no sm_100 device visible: there is NO CPU fallback */
     MCSIM_ERR_DRAWS = 4,      /* injected draws buffer too short */
-    MCSIM_ERR_DEGENERATE = 5  /* GMM component with < 2 collision-free samples (reference: UB) */
+    MCSIM_ERR_DEGENERATE = 5, /* GMM component with < 2 collision-free samples (reference: UB) */
+    MCSIM_ERR_NCCL = 6        /* a multi-device group needs libnccl.so.2 and it failed (message has the NCCL error) */
 };
 
 /* ---- context ---------------------------------------------------------------------------- */
@@ -55,6 +56,8 @@ void mcsim_cuda_destroy(mcsim_cuda_ctx* ctx);
 const char* mcsim_cuda_last_error(void);
 /* cudaStream_t of the context as an opaque pointer (so a caller can record CUDA events on it). */
 void* mcsim_cuda_stream(mcsim_cuda_ctx* ctx);
+/* CUDA ordinal the context was created on (-1 for NULL). */
+int mcsim_cuda_ctx_device(const mcsim_cuda_ctx* ctx);
 /* number of kernels this context has launched so far (bench.py's gpu_launches). */
 uint64_t mcsim_cuda_launch_count(mcsim_cuda_ctx* ctx);
 
@@ -286,6 +289,8 @@ typedef struct {
     const double* fcovs;         /* [n_fits][K][9] symmetric */
     int iters;                   /* em_iter */
     double var_floor;            /* <= 0: DBL_MIN, as learn() does (:868) */
+    uint64_t x_row_stride;       /* floats between the starts of consecutive rows of x; 0 means n (rows are contiguous).
+                                    Larger: x points at a column slice of wider rows (a shard of a sharded fit) */
 } mcsim_em_params;
 
 typedef struct {
@@ -365,6 +370,34 @@ int mcsim_cuda_score_collect(mcsim_cuda_ctx* ctx, mcsim_score_result* r);
  * for this (linConstraint.py:15-30, gaussprop.py:58-73): parity unpinned. */
 int mcsim_truncate_linear(const double mean[3], const double cov[9], int n, const double* A, const double* b,
                           double mean_out[3], double cov_out[9], double* p_violation);
+
+/* ---- several devices behind one handle ---------------------------------------------------------------------------- */
+/* What lets the C++ plugin run `setNumParticles 100000000` + `runSimulation` (mcsimplugin.cpp:75-81) on every GPU of a
+ * box: one context per listed device and -- for more than one device -- one NCCL communicator per device
+ * (ncclCommInitAll, single process), all owned by the group.  libnccl.so.2 is resolved at run time (dlopen; a copy
+ * already in the process is shared), so single-device use needs no NCCL at all.
+ *   group_mc_run          rollout ids split into contiguous ranges; one ncclAllReduce(sum, uint64) of the counter block per
+ *                         run on the devices' streams; the result is the job's: identical for 1, 2, 4, 8 devices
+ *   group_em_fit          samples split (x is ONE host array [n_fits][3][n]); one ncclAllReduce(sum, float64) of the
+ *                         statistics per iteration, identical M-step on every device
+ *   group_score_plans     plans split; no exchange (results land in disjoint slices of the caller's arrays)
+ *   group_gmm_run_batch   batch members split (independent replicas); no exchange
+ * A group of one device is the plain single-device path. */
+typedef struct mcsim_cuda_group mcsim_cuda_group;
+int mcsim_cuda_device_count(void);
+int mcsim_cuda_group_create(const int* devices, int n_devices, mcsim_cuda_group** out);
+void mcsim_cuda_group_destroy(mcsim_cuda_group* g);
+int mcsim_cuda_group_size(const mcsim_cuda_group* g);
+mcsim_cuda_ctx* mcsim_cuda_group_ctx(mcsim_cuda_group* g, int i);
+int mcsim_cuda_group_set_scene(mcsim_cuda_group* g, const double* boxes, int n_boxes, const double* hulls, int n_hulls);
+int mcsim_cuda_group_mc_run(mcsim_cuda_group* g, const mcsim_mc_params* p, mcsim_mc_result* r);
+int mcsim_cuda_group_em_fit(mcsim_cuda_group* g, const mcsim_em_params* p, mcsim_em_result* r);
+int mcsim_cuda_group_score_plans(mcsim_cuda_group* g, const mcsim_score_params* p, mcsim_score_result* r);
+int mcsim_cuda_group_gmm_run_batch(mcsim_cuda_group* g, const mcsim_mc_params* mc, const mcsim_gmm_batch_params* gp,
+                                   mcsim_gmm_batch_result* r);
+/* device time of the collective(s) of the last group call that had one (ms, max over devices; for EM the last
+ * iteration's) and the number of collectives issued so far */
+void mcsim_cuda_group_stats(const mcsim_cuda_group* g, float* collective_ms, uint64_t* collectives);
 
 /* bytes the last *_run call copied host->device and device->host (bench.py's e2e accounting) */
 void mcsim_cuda_io_bytes(mcsim_cuda_ctx* ctx, uint64_t* h2d, uint64_t* d2h);

@@ -65,7 +65,10 @@ const MCModule::Command MCModule::kCommands[] = {
     {"setEarlyExit", &MCModule::setEarlyExit, "setEarlyExit 0|1: stop a rollout at its first hit (the returned P does not change)"},
     {"setBroadPhase", &MCModule::setBroadPhase, "setBroadPhase 0|1: 1 (default) tests only the obstacles within reach of each waypoint, 0 every obstacle at every step (the returned P does not change)"},
     {"setEstimator", &MCModule::setEstimator, "setEstimator reference|closedloop: collision tested on the particle (reference) or on the real state"},
-    {"setRolloutOffset", &MCModule::setRolloutOffset, "setRolloutOffset <u64>: global id of this module's first rollout (multi-GPU shards)"},
+    {"setRolloutOffset", &MCModule::setRolloutOffset, "setRolloutOffset <u64>: global id of this module's first rollout (shards of one job over several modules / processes)"},
+    {"setDevices", &MCModule::setDevices, "setDevices all | <ordinal> [<ordinal> ...]: the CUDA devices this module runs on; runSimulation splits its rollouts over them (one NCCL all-reduce of the counters), runGMMEstimationBatch its runs"},
+    {"getDevices", &MCModule::getDevices, "the CUDA ordinals in use"},
+    {"describeRun", &MCModule::describeRun, "describeRun [k]: Philox key, first rollout id and rollout count of the k-th runSimulation from now (default 0 = the next one), then key and stream id of the k-th runGMMEstimation"},
     {"setGeometry", &MCModule::setGeometry, "setGeometry <n_boxes> <n_hulls> <8 numbers per prism ...>: replace the collision geometry"},
     {"setScene", &MCModule::setScene, "setScene <env.xml> [fixture_dir ...]: extract the collision geometry from an OpenRAVE env XML"},
     {"getWaypointProbabilities", &MCModule::getWaypointProbabilities, "per-waypoint colliding fraction of the last runGMMEstimation"},
@@ -78,20 +81,32 @@ MCModule::MCModule(const Scene& scene, int device) : scene_(scene) {
     std::random_device rd;  // the reference seeds from the clock / random device (MCSimulator.h:141 set_seed_random)
     seed_ = (uint64_t(rd()) << 32) ^ uint64_t(rd());
     if (device < 0) return;  // parse-only module: setters and queries work, run* / geometry uploads fail loudly
-    cuda_check(mcsim_cuda_create(device, &ctx_), "mcsim_cuda_create");
+    open_devices(std::vector<int>{device});
+}
+
+MCModule::~MCModule() { mcsim_cuda_group_destroy(group_); }
+
+// (re)creates the device group and gives every device the scene
+void MCModule::open_devices(const std::vector<int>& devices) {
+    mcsim_cuda_group* g = nullptr;
+    cuda_check(mcsim_cuda_group_create(devices.data(), int(devices.size()), &g), "mcsim_cuda_group_create");
+    mcsim_cuda_group* old = group_;
+    group_ = g;
+    ctx_ = mcsim_cuda_group_ctx(g, 0);
     try {
         if (scene_.n_hulls() > 0) upload_scene();
     } catch (...) {
-        mcsim_cuda_destroy(ctx_);
+        mcsim_cuda_group_destroy(g);
+        group_ = old;
+        ctx_ = old ? mcsim_cuda_group_ctx(old, 0) : nullptr;
         throw;
     }
+    mcsim_cuda_group_destroy(old);
 }
 
-MCModule::~MCModule() { mcsim_cuda_destroy(ctx_); }
-
 void MCModule::upload_scene() {
-    if (!ctx_) return;  // parse-only module
-    cuda_check(mcsim_cuda_set_scene(ctx_, scene_.boxes.data(), scene_.n_boxes(), scene_.hulls.data(), scene_.n_hulls()), "mcsim_cuda_set_scene");
+    if (!group_) return;  // parse-only module
+    cuda_check(mcsim_cuda_group_set_scene(group_, scene_.boxes.data(), scene_.n_boxes(), scene_.hulls.data(), scene_.n_hulls()), "mcsim_cuda_set_scene");
 }
 
 void MCModule::io_bytes(uint64_t* h2d, uint64_t* d2h) const { mcsim_cuda_io_bytes(ctx_, h2d, d2h); }

@@ -76,6 +76,9 @@ class MCModule {
     bool setBroadPhase(std::ostream&, std::istream&);
     bool setEstimator(std::ostream&, std::istream&);
     bool setRolloutOffset(std::ostream&, std::istream&);
+    bool setDevices(std::ostream&, std::istream&);
+    bool getDevices(std::ostream&, std::istream&);
+    bool describeRun(std::ostream&, std::istream&);
     bool setGeometry(std::ostream&, std::istream&);
     bool setScene(std::ostream&, std::istream&);
     bool getWaypointProbabilities(std::ostream&, std::istream&);
@@ -85,9 +88,18 @@ class MCModule {
 
     void fill_params(mcsim_mc_params& p) const;  // throws when a parameter is missing
     void upload_scene();
+    void open_devices(const std::vector<int>& devices);
+    // Philox key of run number `run` of this module: the seed for run 0, seed ^ splitmix64(run) afterwards.  The run
+    // number lives in the KEY and the shard offset (setRolloutOffset) in the COUNTER, so R runs on W shards draw W x R
+    // disjoint (key, id) blocks whatever the offsets are.
+    uint64_t run_key(uint64_t run) const;
+    // Philox key of the GMM runs of this module: the seed, salted with the shard offset (a replica id for GMM mode:
+    // one run does not shard); the run number is the stream id in the counter, as a batch numbers its members.
+    uint64_t gmm_key() const;
 
     Scene scene_;
-    mcsim_cuda_ctx* ctx_ = nullptr;
+    mcsim_cuda_group* group_ = nullptr;   // one context per device (setDevices) + the NCCL communicators; owned
+    mcsim_cuda_ctx* ctx_ = nullptr;       // the group's first context (single-run GMM, queries)
     std::string err_;
     // parameters, as the setters leave them
     std::vector<double> alphas_;

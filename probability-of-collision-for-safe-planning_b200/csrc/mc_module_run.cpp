@@ -26,7 +26,17 @@ std::vector<T> read_binary(const std::string& path) {
     return v;
 }
 
+uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+
 }  // namespace
+
+uint64_t MCModule::run_key(uint64_t run) const { return run ? seed_ ^ splitmix64(run) : seed_; }
+uint64_t MCModule::gmm_key() const { return rollout_offset_ ? seed_ ^ splitmix64(~rollout_offset_) : seed_; }
 
 void MCModule::fill_params(mcsim_mc_params& p) const {
     if (!ctx_) throw std::runtime_error("this module was created without a CUDA device (device < 0): run commands are unavailable, there is no CPU fallback");
@@ -60,9 +70,10 @@ bool MCModule::runSimulation(std::ostream& sout, std::istream&) {
     const uint64_t N = uint64_t(num_particles_);
     p.n_rollouts = N;
     std::vector<double> applied_noisy(size_t(3) * (T > 1 ? T - 1 : 1));
+    p.seed = run_key(run_index_);      // the run number is in the key, the shard offset in the counter (see run_key)
+    p.rollout_offset = rollout_offset_;
     if (mode_ == Mode::kPhilox) {
         p.mode = MCSIM_MODE_PHILOX;
-        p.rollout_offset = rollout_offset_ + run_index_ * N;
     } else {
         // one shared real-robot thread on the host (FP64), replayed by every rollout
         const size_t per_step = size_t(3 + L), need_host = per_step * size_t(T - 1);
@@ -73,12 +84,10 @@ bool MCModule::runSimulation(std::ostream& sout, std::istream&) {
                 throw std::runtime_error("runSimulation: deterministic mode needs " + std::to_string(3 * N + need_host) + " draws, " + std::to_string(draws_.size()) + " loaded");
             p.z0 = draws_.data();            // 3N particle normals first (initParticles), then 3 + L per step
             host_normals = draws_.data() + 3 * N;
-            p.rollout_offset = rollout_offset_;
         } else {
             hn.resize(need_host ? need_host : 1);
             if (T > 1) cuda_check(mcsim_host_normals(seed_, uint32_t(run_index_), T, int(per_step), hn.data()), "mcsim_host_normals");
-            host_normals = hn.data();
-            p.rollout_offset = rollout_offset_ + run_index_ * N;  // fresh particles every run
+            host_normals = hn.data();   // (the particles' start poses: per-rollout Philox blocks under this run's key)
         }
         if (T > 1) {
             const int rc = mcsim_host_thread(&p, host_normals, need_host, applied_noisy.data(), nullptr, nullptr, nullptr, nullptr, nullptr);
@@ -91,7 +100,7 @@ bool MCModule::runSimulation(std::ostream& sout, std::istream&) {
     std::memset(&r, 0, sizeof(r));
     first_hit_hist_.assign(size_t(T), 0);
     r.first_hit_hist = first_hit_hist_.data();
-    cuda_check(mcsim_cuda_mc_run(ctx_, &p, &r), "mcsim_cuda_mc_run");
+    cuda_check(mcsim_cuda_group_mc_run(group_, &p, &r), "mcsim_cuda_mc_run");   // all devices of the module; one device: the plain path
     ++run_index_;
     last_hits_ = r.hits; last_n_ = N; last_steps_ = r.executed_steps; last_tests_ = r.pair_tests; last_kernel_ms_ = r.kernel_ms;
     last_degenerate_ = 0;
@@ -120,7 +129,8 @@ bool MCModule::runGMMEstimation(std::ostream& sout, std::istream&) {
         g.counts = gmm_counts_.data();
     } else {
         p.mode = MCSIM_MODE_PHILOX;
-        p.rollout_offset = rollout_offset_ + run_index_;  // Philox subsequence of this run
+        p.seed = gmm_key();
+        p.rollout_offset = run_index_;  // Philox subsequence (stream id) of this run
     }
     probabilities_.assign(size_t(T), 0.0);
     gmm_post_.assign(size_t(K) * 13, 0.0);
@@ -150,17 +160,18 @@ bool MCModule::runGMMEstimationBatch(std::ostream& sout, std::istream& sinput) {
     if (num_gaussians_ < 1) throw std::runtime_error("setNumGaussians has not been sent");
     if (num_gmm_samples_ < 1) throw std::runtime_error("setNumGMMSamples has not been sent");
     p.mode = MCSIM_MODE_PHILOX;
+    p.seed = gmm_key();
     mcsim_gmm_batch_params g;
     std::memset(&g, 0, sizeof(g));
     g.K = num_gaussians_;
     g.n_samples = uint64_t(num_gmm_samples_);
     g.n_traj = n;
-    g.stream0 = rollout_offset_ + run_index_;
+    g.stream0 = run_index_;
     std::vector<double> P(size_t(n), 0.0);
     mcsim_gmm_batch_result r;
     std::memset(&r, 0, sizeof(r));
     r.P = P.data();
-    cuda_check(mcsim_cuda_gmm_run_batch(ctx_, &p, &g, &r), "mcsim_cuda_gmm_run_batch");
+    cuda_check(mcsim_cuda_group_gmm_run_batch(group_, &p, &g, &r), "mcsim_cuda_gmm_run_batch");   // members split over the module's devices
     run_index_ += uint64_t(n);
     last_kernel_ms_ = r.kernel_ms;
     last_degenerate_ = r.degenerate;
@@ -245,6 +256,46 @@ bool MCModule::setRolloutOffset(std::ostream&, std::istream& sinput) {
     unsigned long long v;
     if (!(sinput >> v)) throw std::runtime_error("setRolloutOffset: an unsigned integer expected");
     rollout_offset_ = v;
+    return true;
+}
+
+// setDevices all | <ordinal> [<ordinal> ...] (commas are accepted as separators)
+bool MCModule::setDevices(std::ostream&, std::istream& sinput) {
+    std::string rest, tok;
+    std::getline(sinput, rest);
+    for (auto& ch : rest) if (ch == ',') ch = ' ';
+    std::istringstream in(rest);
+    std::vector<int> devs;
+    while (in >> tok) {
+        if (tok == "all") {
+            const int n = mcsim_cuda_device_count();
+            if (n < 1) throw std::runtime_error("setDevices: no CUDA device (there is no CPU path)");
+            devs.clear();
+            for (int d = 0; d < n; ++d) devs.push_back(d);
+            break;
+        }
+        size_t used = 0;
+        int v = -1;
+        try { v = std::stoi(tok, &used); } catch (...) { used = 0; }
+        if (used != tok.size() || v < 0) throw std::runtime_error("setDevices: device ordinals or 'all' expected, got '" + tok + "'");
+        devs.push_back(v);
+    }
+    if (devs.empty()) throw std::runtime_error("setDevices: at least one device expected");
+    open_devices(devs);
+    return true;
+}
+
+bool MCModule::getDevices(std::ostream& sout, std::istream&) {
+    const int n = mcsim_cuda_group_size(group_);
+    for (int i = 0; i < n; ++i) sout << (i ? " " : "") << mcsim_cuda_ctx_device(mcsim_cuda_group_ctx(group_, i));
+    return true;
+}
+
+bool MCModule::describeRun(std::ostream& sout, std::istream& sinput) {
+    unsigned long long k = 0;
+    sinput >> k;
+    const uint64_t run = run_index_ + k;
+    sout << "mc " << run_key(run) << " " << rollout_offset_ << " " << num_particles_ << " gmm " << gmm_key() << " " << run;
     return true;
 }
 

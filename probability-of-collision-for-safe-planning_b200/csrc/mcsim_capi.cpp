@@ -11,6 +11,7 @@
 struct mcsim_handle {
     std::unique_ptr<mcsim::MCModule> mod;
     std::string err;
+    std::string last;   // reply of the last successful command (mcsim_last_output)
 };
 
 static thread_local std::string g_create_err;
@@ -58,6 +59,7 @@ extern "C" int mcsim_send_command(mcsim_handle* h, const char* cmd, char* out, s
     const bool ok = h->mod->SendCommand(std::string(cmd), text);
     if (!ok) { h->err = h->mod->last_error(); return 1; }
     h->err.clear();
+    h->last = text;
     if (out_len) *out_len = text.size();
     if (out && out_cap) {
         const size_t n = text.size() < out_cap - 1 ? text.size() : out_cap - 1;
@@ -65,6 +67,16 @@ extern "C" int mcsim_send_command(mcsim_handle* h, const char* cmd, char* out, s
         out[n] = '\0';
     }
     return 0;
+}
+
+extern "C" size_t mcsim_last_output(mcsim_handle* h, char* out, size_t out_cap) {
+    if (!h) return 0;
+    if (out && out_cap) {
+        const size_t n = h->last.size() < out_cap - 1 ? h->last.size() : out_cap - 1;
+        std::memcpy(out, h->last.data(), n);
+        out[n] = '\0';
+    }
+    return h->last.size();
 }
 
 extern "C" const char* mcsim_last_error(mcsim_handle* h) { return h ? h->err.c_str() : g_create_err.c_str(); }

@@ -10,9 +10,11 @@
 #include <string.h>
 
 #include <atomic>
+#include <mutex>
 #include <thread>
 #include <algorithm>
 #include <chrono>
+#include <string>
 #include <utility>
 #include <vector>
 
@@ -51,8 +53,33 @@ struct DevBuf {
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
 };
 
+// ---- ownership of the __constant__ tables ---------------------------------------------------------------------------
+// c_scene / c_pairs (scene) and c_mc / c_plan2 (prepared plan) are one set of symbols per DEVICE, while every context
+// (and every MCModule) has its own scene and plan.  Each context keeps host copies of what it wants in the symbols and a
+// tag per table; the per-device registry remembers whose data the symbols hold.  A launch path takes the registry lock,
+// re-uploads when the tags differ (after a device-wide synchronise: a kernel of the previous owner may still be reading
+// them) and keeps the lock across its launches, so contexts sharing a device -- also from different host threads --
+// cannot run on each other's tables.
+struct DeviceSymbols {
+    std::mutex m;
+    uint64_t scene_tag = 0, plan_tag = 0;
+    uint64_t owner = 0;            // context id of the last writer (its own stream orders its own re-uploads)
+};
+static DeviceSymbols g_symbols[64];
+static std::atomic<uint64_t> g_next_tag{1};
+struct PlanSymbols {           // what a prepare call wants in c_mc / c_plan2
+    McPlanConst pc;
+    std::vector<float> plan2;
+    uint64_t tag = 0;
+};
+
 struct mcsim_cuda_ctx {
     int device = 0;
+    uint64_t id = g_next_tag++;
+    SceneConst h_scene;                 // host copies of this context's symbol contents
+    std::vector<float4> h_pairs;
+    uint64_t scene_tag = 0;
+    PlanSymbols mc_sym, sc_sym;         // prepared MC plan / prepared scoring batch
     int n_sm = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -104,6 +131,32 @@ struct mcsim_cuda_ctx {
     int em_x_fits = 0;
     uint64_t h2d_bytes = 0, d2h_bytes = 0;  // bytes copied by the last run call
 };
+
+// Makes the device's symbols hold this context's scene (and, when `plan` is given, that plan) and returns holding the
+// device's registry lock; the caller launches its kernels and lets the lock go.
+struct SymbolLock {
+    std::unique_lock<std::mutex> lk;
+};
+static int bind_symbols(mcsim_cuda_ctx* c, const PlanSymbols* plan, SymbolLock& out) {
+    DeviceSymbols& d = g_symbols[c->device & 63];
+    out.lk = std::unique_lock<std::mutex>(d.m);
+    const bool scene_stale = d.scene_tag != c->scene_tag, plan_stale = plan && d.plan_tag != plan->tag;
+    if (!scene_stale && !plan_stale) return MCSIM_OK;
+    if (d.owner == c->id) CK(cudaStreamSynchronize(c->stream));   // only this context's kernels can be reading them
+    else CK(cudaDeviceSynchronize());
+    d.owner = c->id;
+    if (scene_stale) {
+        CK(cudaMemcpyToSymbol(c_scene, &c->h_scene, sizeof(SceneConst)));
+        if (!c->h_pairs.empty()) CK(cudaMemcpyToSymbol(c_pairs, c->h_pairs.data(), c->h_pairs.size() * sizeof(float4)));
+        d.scene_tag = c->scene_tag;
+    }
+    if (plan_stale) {
+        CK(cudaMemcpyToSymbol(c_mc, &plan->pc, sizeof(McPlanConst)));
+        if (!plan->plan2.empty()) CK(cudaMemcpyToSymbol(c_plan2, plan->plan2.data(), plan->plan2.size() * sizeof(float)));
+        d.plan_tag = plan->tag;
+    }
+    return MCSIM_OK;
+}
 
 extern "C" const char* mcsim_cuda_last_error(void) { return g_err; }
 
@@ -158,6 +211,7 @@ extern "C" void mcsim_cuda_destroy(mcsim_cuda_ctx* c) {
 }
 
 extern "C" void* mcsim_cuda_stream(mcsim_cuda_ctx* c) { return c ? (void*)c->stream : nullptr; }
+extern "C" int mcsim_cuda_ctx_device(const mcsim_cuda_ctx* c) { return c ? c->device : -1; }
 extern "C" uint64_t mcsim_cuda_launch_count(mcsim_cuda_ctx* c) { return c ? c->launches : 0; }
 
 // ---- peaks ----------------------------------------------------------------------------------
@@ -288,8 +342,10 @@ extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int 
     if (sc.n_pairs > MCSIM_MAX_PAIRS)
         return fail(MCSIM_ERR_ARG, "set_scene: %d live (hull, box) pairs exceed MCSIM_MAX_PAIRS=%d", sc.n_pairs, MCSIM_MAX_PAIRS);
     CK(cudaStreamSynchronize(c->stream));
-    CK(cudaMemcpyToSymbol(c_scene, &sc, sizeof(sc)));
-    if (!pairs.empty()) CK(cudaMemcpyToSymbol(c_pairs, pairs.data(), pairs.size() * sizeof(float4)));
+    c->h_scene = sc;                       // uploaded to c_scene / c_pairs by the next launch of this context (bind_symbols)
+    c->h_pairs = pairs;
+    c->scene_tag = g_next_tag++;
+    c->sc_prepared = false;                // a prepared scoring batch points at the old pair table
     CK(c->hulls_d.reserve(sizeof(HullD) * hd.size()));
     CK(cudaMemcpy(c->hulls_d.p, hd.data(), sizeof(HullD) * hd.size(), cudaMemcpyHostToDevice));
     CK(c->pairs_d.reserve(sizeof(PairD) * (pd.size() ? pd.size() : 1)));
@@ -480,11 +536,12 @@ extern "C" int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* c, const mcsim_mc_params* p
     CK(c->plan.reserve(plan.size() * sizeof(float)));
     CK(c->counters.reserve(sizeof(unsigned long long) * (4 + MCSIM_MAX_WAYPOINTS)));
     CK(cudaStreamSynchronize(c->stream));
-    CK(cudaMemcpyToSymbolAsync(c_mc, &pc, sizeof(pc), 0, cudaMemcpyHostToDevice, c->stream));
+    c->mc_sym.pc = pc;                     // uploaded to c_mc / c_plan2 by the launch (bind_symbols)
+    c->mc_sym.plan2 = plan2;
+    c->mc_sym.tag = g_next_tag++;
     CK(cudaMemcpyAsync(c->plan.p, plan.data(), plan.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
     c->mc_cull_uploaded = !cull.empty() && !cull_cached;
     if (!cull.empty() && !cull_cached) CK(cudaMemcpyAsync(c->mc_cull.p, cull.data(), cull.size() * sizeof(unsigned), cudaMemcpyHostToDevice, c->stream));
-    if (!plan2.empty()) CK(cudaMemcpyToSymbolAsync(c_plan2, plan2.data(), plan2.size() * sizeof(float), 0, cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * (4 + T), c->stream));
     CK(cudaStreamSynchronize(c->stream));  // plan is a stack vector
     c->mc = *p;
@@ -538,6 +595,8 @@ static int mc_launch_segmented(mcsim_cuda_ctx* c, const McLaunch& a0, uint64_t n
 static int mc_launch_impl(mcsim_cuda_ctx* c, uint64_t n, uint64_t offset, const double* d_z0, unsigned* d_counts,
                           float* d_poses, float* d_clear) {
     const mcsim_mc_params& p = c->mc;
+    SymbolLock sym;
+    { const int rb = bind_symbols(c, &c->mc_sym, sym); if (rb) return rb; }
     const bool audit = d_poses || d_clear;
     const bool packed = p.mode == MCSIM_MODE_PHILOX && !audit && !p.precise && p.n_landmarks == 8 && c->mc_T <= MC_PLAN2_MAX_T;
     mc_kernel_t k = packed ? pick_packed(p.early_exit != 0, p.estimator)
@@ -599,7 +658,9 @@ extern "C" int mcsim_cuda_mc_collect(mcsim_cuda_ctx* c, mcsim_mc_result* r) {
     return MCSIM_OK;
 }
 
-extern "C" int mcsim_cuda_mc_run(mcsim_cuda_ctx* c, const mcsim_mc_params* p, mcsim_mc_result* r) {
+// mc_run in two halves, so that several devices can be in flight at once (mcsim_group.cuh): begin = prepare, upload,
+// launch, queue the per-rollout downloads; end = collect the counters (synchronises) and read the kernel time.
+static int mc_run_begin(mcsim_cuda_ctx* c, const mcsim_mc_params* p, mcsim_mc_result* r) {
     if (!r) return fail(MCSIM_ERR_ARG, "mc_run: result is NULL");
     int rc = mcsim_cuda_mc_prepare(c, p);
     if (rc) return rc;
@@ -632,10 +693,18 @@ extern "C" int mcsim_cuda_mc_run(mcsim_cuda_ctx* c, const mcsim_mc_params* p, mc
     if (d_counts) { CK(cudaMemcpyAsync(r->counts, d_counts, sizeof(unsigned) * n, cudaMemcpyDeviceToHost, c->stream)); c->d2h_bytes += sizeof(unsigned) * n; }
     if (d_poses && r->poses) CK(cudaMemcpyAsync(r->poses, d_poses, sizeof(float) * 3 * T * n, cudaMemcpyDeviceToHost, c->stream));
     if (d_clear && r->clearance) CK(cudaMemcpyAsync(r->clearance, d_clear, sizeof(float) * T * n, cudaMemcpyDeviceToHost, c->stream));
-    rc = mcsim_cuda_mc_collect(c, r);
+    return MCSIM_OK;
+}
+static int mc_run_end(mcsim_cuda_ctx* c, mcsim_mc_result* r) {
+    const int rc = mcsim_cuda_mc_collect(c, r);
     if (rc) return rc;
     CK(cudaEventElapsedTime(&r->kernel_ms, c->ev0, c->ev1));
     return MCSIM_OK;
+}
+
+extern "C" int mcsim_cuda_mc_run(mcsim_cuda_ctx* c, const mcsim_mc_params* p, mcsim_mc_result* r) {
+    const int rc = mc_run_begin(c, p, r);
+    return rc ? rc : mc_run_end(c, r);
 }
 
 // the step draws of one Philox-mode rollout, host FP64 (csrc/philox.h: step draws)
@@ -777,6 +846,8 @@ static int gmm_upload_cull(mcsim_cuda_ctx* c, GmmLaunch& a, const double* trajec
 // the three launches of one waypoint
 static int gmm_launch_waypoint(mcsim_cuda_ctx* c, const GmmLaunch& a_in, int mode) {
     GmmLaunch a = a_in;
+    SymbolLock sym;
+    { const int rb = bind_symbols(c, nullptr, sym); if (rb) return rb; }
     const unsigned B = a.B > 1 ? unsigned(a.B) : 1u;
     int block, spread_flag = 0;
     unsigned gx;
@@ -834,6 +905,8 @@ static bool gmm_cluster_fits(const mcsim_cuda_ctx* c, uint64_t n_samples, int n_
     return n_samples <= GMM_CLUSTER_MAX_SAMPLES && smem <= 64 * 1024 && n_runs >= 1 && n_runs < 64;
 }
 static int gmm_launch_cluster(mcsim_cuda_ctx* c, const GmmLaunch& a, int n_runs) {
+    SymbolLock sym;
+    { const int rb = bind_symbols(c, nullptr, sym); if (rb) return rb; }
     const size_t smem = sizeof(float4) * size_t(c->sat2_n) + sizeof(unsigned) * size_t(c->gmm_cull_words);
     // the kernel holds ~30 KB of static shared memory (the peers' slots): static + dynamic pass 48 KB early
     if (smem > 12 * 1024) CK(cudaFuncSetAttribute((const void*)gmm_cluster_run_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
@@ -1100,7 +1173,10 @@ extern "C" int mcsim_cuda_em_prepare(mcsim_cuda_ctx* c, const mcsim_em_params* p
     c->h2d_bytes = sizeof(double) * size_t(F) * K * 13;
     if (p->x) {
         CK(c->em_x.reserve(sizeof(float) * (nx ? nx : 1)));
-        if (nx) CK(cudaMemcpyAsync(c->em_x.p, p->x, sizeof(float) * nx, cudaMemcpyHostToDevice, c->stream));
+        if (nx && p->x_row_stride && p->x_row_stride != p->n) {   // a column slice of wider rows (one shard of a sharded fit)
+            if (p->x_row_stride < p->n) return fail(MCSIM_ERR_ARG, "em: x_row_stride smaller than n");
+            CK(cudaMemcpy2DAsync(c->em_x.p, sizeof(float) * p->n, p->x, sizeof(float) * p->x_row_stride, sizeof(float) * p->n, size_t(F) * 3, cudaMemcpyHostToDevice, c->stream));
+        } else if (nx) CK(cudaMemcpyAsync(c->em_x.p, p->x, sizeof(float) * nx, cudaMemcpyHostToDevice, c->stream));
         c->em_x_valid = true; c->em_x_n = p->n; c->em_x_fits = F;
         c->h2d_bytes += sizeof(float) * nx;
     }
@@ -1275,13 +1351,14 @@ extern "C" int mcsim_cuda_score_prepare(mcsim_cuda_ctx* c, const mcsim_score_par
     CK(c->sc_hits.reserve(sizeof(unsigned long long) * NP));
     CK(c->sc_counters.reserve(sizeof(unsigned long long) * 2));
     CK(cudaStreamSynchronize(c->stream));
-    CK(cudaMemcpyToSymbolAsync(c_mc, &pc, sizeof(pc), 0, cudaMemcpyHostToDevice, c->stream));
+    c->sc_sym.pc = pc;                     // uploaded to c_mc by score_launch (bind_symbols); c_plan2 is not used by scoring
+    c->sc_sym.plan2.clear();
+    c->sc_sym.tag = g_next_tag++;
     CK(cudaMemcpyAsync(c->sc_plans.p, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemsetAsync(c->sc_hits.p, 0, sizeof(unsigned long long) * NP, c->stream));
     CK(cudaMemsetAsync(c->sc_counters.p, 0, sizeof(unsigned long long) * 2, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     c->h2d_bytes = sizeof(pc) + tab.size() * sizeof(float);
-    c->mc_prepared = false;  // c_mc now holds this batch's noise model
     ScoreLaunch& a = c->sc;
     a.plans = (const float*)c->sc_plans.p;
     a.pairs = (const float4*)c->pairs_f.p;
@@ -1332,6 +1409,8 @@ extern "C" int mcsim_cuda_score_launch(mcsim_cuda_ctx* c) {
     if (!c || !c->sc_prepared) return fail(MCSIM_ERR_ARG, "score_launch: mcsim_cuda_score_prepare has not been called");
     CK(cudaSetDevice(c->device));
     const ScoreLaunch& a = c->sc;
+    SymbolLock sym;
+    { const int rb = bind_symbols(c, &c->sc_sym, sym); if (rb) return rb; }
     score_kernel_t k = pick_score(c->sc_est, c->sc_ee != 0);
     const size_t smem = score_smem_bytes(a.T, a.n_pairs, c->n_hulls);
     if (smem > 200 * 1024) return fail(MCSIM_ERR_ARG, "score: %zu bytes of shared memory needed (T=%d, %d pairs)", smem, a.T, a.n_pairs);
@@ -1442,6 +1521,8 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
     const bool fused = B >= 64 && fused_smem <= 64 * 1024;
     CK(cudaEventRecord(c->ev0, c->stream));
     if (fused) {
+        SymbolLock sym;
+        { const int rb = bind_symbols(c, nullptr, sym); if (rb) return rb; }
         if (fused_smem > 40 * 1024) CK(cudaFuncSetAttribute((const void*)gmm_member_run_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(fused_smem)));
         gmm_member_run_kernel<<<B, 256, fused_smem, c->stream>>>(a, c->sat2_n, c->gmm_cull_words);
         ++c->launches;
@@ -1482,3 +1563,5 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
     if (r->probabilities) memcpy(r->probabilities, prob.data(), sizeof(double) * prob.size());
     return MCSIM_OK;
 }
+
+#include "mcsim_group.cuh"

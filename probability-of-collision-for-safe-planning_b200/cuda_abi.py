@@ -46,6 +46,7 @@ class EmParams(C.Structure):
     _fields_ = [
         ("K", C.c_int), ("n_fits", C.c_int), ("n", C.c_uint64), ("n_total", C.c_uint64),
         ("x", _fp), ("hefts", _dp), ("means", _dp), ("fcovs", _dp), ("iters", C.c_int), ("var_floor", C.c_double),
+        ("x_row_stride", C.c_uint64),
     ]
 
 
@@ -164,6 +165,21 @@ def lib():
         L.mcsim_cuda_em_stats.restype = vp
         L.mcsim_cuda_io_bytes.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.mcsim_cuda_io_bytes.restype = None
+        L.mcsim_cuda_device_count.restype = C.c_int
+        L.mcsim_cuda_ctx_device.argtypes = [vp]
+        L.mcsim_cuda_group_create.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(vp)]
+        L.mcsim_cuda_group_destroy.argtypes = [vp]
+        L.mcsim_cuda_group_destroy.restype = None
+        L.mcsim_cuda_group_size.argtypes = [vp]
+        L.mcsim_cuda_group_ctx.argtypes = [vp, C.c_int]
+        L.mcsim_cuda_group_ctx.restype = vp
+        L.mcsim_cuda_group_set_scene.argtypes = [vp, _dp, C.c_int, _dp, C.c_int]
+        L.mcsim_cuda_group_mc_run.argtypes = [vp, C.POINTER(McParams), C.POINTER(McResult)]
+        L.mcsim_cuda_group_em_fit.argtypes = [vp, C.POINTER(EmParams), C.POINTER(EmResult)]
+        L.mcsim_cuda_group_score_plans.argtypes = [vp, C.POINTER(ScoreParams), C.POINTER(ScoreResult)]
+        L.mcsim_cuda_group_gmm_run_batch.argtypes = [vp, C.POINTER(McParams), C.POINTER(GmmBatchParams), C.POINTER(GmmBatchResult)]
+        L.mcsim_cuda_group_stats.argtypes = [vp, _fp, C.POINTER(C.c_uint64)]
+        L.mcsim_cuda_group_stats.restype = None
         _lib = L
     return _lib
 
@@ -256,6 +272,14 @@ class Context:
             lib().mcsim_cuda_destroy(self._h)
             self._h = C.c_void_p()
 
+    # set_scene / mc_run / score_plans / em_fit / gmm_run_batch exist per context and per device group (class Group)
+    def _entry(self, name):
+        return getattr(lib(), "mcsim_cuda_" + name)
+
+    @property
+    def _target(self):
+        return self._h
+
     def __del__(self):
         try:
             self.close()
@@ -291,7 +315,7 @@ class Context:
     def set_scene(self, boxes, hulls):
         b = np.ascontiguousarray(boxes, dtype=np.float64).reshape(-1, 8)
         h = np.ascontiguousarray(hulls, dtype=np.float64).reshape(-1, 8)
-        check(lib().mcsim_cuda_set_scene(self._h, dptr(b), b.shape[0], dptr(h), h.shape[0]))
+        check(self._entry("set_scene")(self._target, dptr(b), b.shape[0], dptr(h), h.shape[0]))
         # live (hull, box) pairs: z-intervals overlap (the same rule as mcsim_cuda_set_scene)
         self.n_pairs = int(sum(((hh[6] < b[:, 7]) & (b[:, 6] < hh[7])).sum() for hh in h))
 
@@ -311,7 +335,7 @@ class Context:
             out["clearance"] = np.zeros((T, n), dtype=np.float32)
             r.poses = out["poses"].ctypes.data_as(_fp)
             r.clearance = out["clearance"].ctypes.data_as(_fp)
-        check(lib().mcsim_cuda_mc_run(self._h, C.byref(params), C.byref(r)))
+        check(self._entry("mc_run")(self._target, C.byref(params), C.byref(r)))
         out.update(hits=int(r.hits), near_contact=int(r.near_contact), executed_steps=int(r.executed_steps),
                    pair_tests=int(r.pair_tests), kernel_ms=float(r.kernel_ms),
                    P=(r.hits / n if n else 0.0))
@@ -413,7 +437,7 @@ class Context:
         """model: dict(alphas, Q, landmarks[2, 8], cov0); trajectories [n, 3, T], odometry [n, 3, T-1]."""
         p, keep = self._score_params(model, trajectories, odometry, rollouts, plan_offset, estimator, early_exit, seed, margin)
         r, out = self._score_result(int(p.n_plans))
-        check(lib().mcsim_cuda_score_plans(self._h, C.byref(p), C.byref(r)))
+        check(self._entry("score_plans")(self._target, C.byref(p), C.byref(r)))
         out.update(executed_steps=int(r.executed_steps), pair_tests=int(r.pair_tests), kernel_ms=float(r.kernel_ms))
         return out
 
@@ -466,7 +490,7 @@ class Context:
         hefts [F, K], means [F, K, 3], fcovs [F, K, 3, 3]: initial parameters.  Returns a dict."""
         p, keep, (F, K) = self._em_params(x, hefts, means, fcovs, iters, var_floor, 0)
         r, out = self._em_result(F, K, iters)
-        check(lib().mcsim_cuda_em_fit(self._h, C.byref(p), C.byref(r)))
+        check(self._entry("em_fit")(self._target, C.byref(p), C.byref(r)))
         out["kernel_ms"] = float(r.kernel_ms)
         return out
 
@@ -516,7 +540,7 @@ class Context:
         out = dict(P=np.zeros(n_traj), probabilities=np.zeros((n_traj, T)))
         r = GmmBatchResult()
         r.P, r.probabilities = dptr(out["P"]), dptr(out["probabilities"])
-        check(lib().mcsim_cuda_gmm_run_batch(self._h, C.byref(p), C.byref(g), C.byref(r)))
+        check(self._entry("gmm_run_batch")(self._target, C.byref(p), C.byref(g), C.byref(r)))
         out.update(degenerate=int(r.degenerate), kernel_ms=float(r.kernel_ms), pair_tests=int(r.pair_tests))
         return out
 
@@ -545,3 +569,39 @@ class Context:
                     covs=np.array(r.covs[:9 * K]).reshape(K, 3, 3), n_coll=np.array(r.n_coll[:K], dtype=np.uint64),
                     n_free=np.array(r.n_free[:K], dtype=np.uint64), p_collision=float(r.p_collision),
                     degenerate=int(r.degenerate))
+
+
+class Group(Context):
+    """Several devices behind one handle (mcsim_cuda_group_*): one context per device, the NCCL communicators owned by the
+    group.  set_scene / mc_run / score_plans / em_fit / gmm_run_batch run on all devices (rollout ids / plans / samples /
+    batch members split, counters and EM statistics all-reduced over NCCL); every other method addresses device 0's
+    context.  No torch, no torch.distributed: this is what a C++ host gets."""
+
+    def __init__(self, devices):
+        devices = [int(d) for d in devices]
+        arr = (C.c_int * len(devices))(*devices)
+        self._g = C.c_void_p()
+        self._h = C.c_void_p()
+        check(lib().mcsim_cuda_group_create(arr, len(devices), C.byref(self._g)))
+        self._h = C.c_void_p(lib().mcsim_cuda_group_ctx(self._g, 0))
+        self.devices = devices
+        self.device = devices[0]
+
+    def close(self):
+        if getattr(self, "_g", None):
+            lib().mcsim_cuda_group_destroy(self._g)
+            self._g = C.c_void_p()
+            self._h = C.c_void_p()
+
+    def _entry(self, name):
+        return getattr(lib(), "mcsim_cuda_group_" + name)
+
+    @property
+    def _target(self):
+        return self._g
+
+    def collective_stats(self):
+        """(device time of the last call's collective in ms, collectives issued so far)"""
+        ms, n = C.c_float(), C.c_uint64()
+        lib().mcsim_cuda_group_stats(self._g, C.byref(ms), C.byref(n))
+        return float(ms.value), int(n.value)

@@ -38,6 +38,8 @@ def lib():
         L.mcsim_create_from_arrays.argtypes = [_dp, C.c_int, _dp, C.c_int, C.c_int]
         L.mcsim_create_from_arrays.restype = vp
         L.mcsim_send_command.argtypes = [vp, C.c_char_p, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]
+        L.mcsim_last_output.argtypes = [vp, C.c_char_p, C.c_size_t]
+        L.mcsim_last_output.restype = C.c_size_t
         L.mcsim_last_error.argtypes = [vp]
         L.mcsim_last_error.restype = C.c_char_p
         L.mcsim_get_boxes.argtypes = [vp, _dp, C.c_int]
@@ -74,9 +76,9 @@ class MCModule:
         n = C.c_size_t()
         data = cmd.encode()
         rc = L.mcsim_send_command(self._h, data, self._buf, len(self._buf), C.byref(n))
-        if rc == 0 and n.value >= len(self._buf):  # output longer than the buffer: grow and resend is not
-            self._buf = C.create_string_buffer(n.value + 1)  # idempotent for run*, so only queries get here
-            rc = L.mcsim_send_command(self._h, data, self._buf, len(self._buf), C.byref(n))
+        if rc == 0 and n.value >= len(self._buf):  # reply longer than the buffer: fetch it again, do NOT re-send
+            self._buf = C.create_string_buffer(n.value + 1)  # (run* commands are not idempotent)
+            L.mcsim_last_output(self._h, self._buf, len(self._buf))
         if rc != 0:
             raise McsimError("%s: %s" % (cmd.split(" ", 1)[0], L.mcsim_last_error(self._h).decode()))
         return self._buf.value.decode()

@@ -134,3 +134,93 @@ def test_run_gmm_estimation_batch_command_equals_the_loop():
         mod.close()
     np.testing.assert_allclose(outs[0], outs[1], rtol=1e-5)   # text round trip: 6 significant digits
     assert len(set(outs[1])) > 1
+
+
+def test_two_modules_with_different_scenes_share_one_device(plan):
+    """Two MCModules (pr2test2 and pr2custom) on cuda:0, run alternately: the __constant__ scene / plan tables are per
+    device, each module must get its own back at every launch (per-device ownership registry in mcsim_cuda.cu).
+    Every alternating result must equal what the module returns when it has the device to itself."""
+    import pcoll_b200
+    alone = {}
+    for name in ("pr2test2", "pr2custom"):
+        mod = _module(plan, name, 50000, num_gaussians=2, num_gmm_samples=3000)
+        mod.SendCommand("setSeed 77")
+        mod.SendCommand("setMode philox")
+        alone[name] = [mod.SendCommand("runSimulation"), mod.SendCommand("runSimulation"), mod.SendCommand("runGMMEstimation")]
+        mod.close()
+    assert alone["pr2test2"][0] != alone["pr2custom"][0]
+    mods = {name: _module(plan, name, 50000, num_gaussians=2, num_gmm_samples=3000) for name in alone}
+    for m in mods.values():
+        m.SendCommand("setSeed 77")
+        m.SendCommand("setMode philox")
+    got = {name: [] for name in alone}
+    for cmd in ("runSimulation", "runSimulation", "runGMMEstimation"):
+        for name in ("pr2test2", "pr2custom"):
+            got[name].append(mods[name].SendCommand(cmd))
+    for m in mods.values():
+        m.close()
+    assert got == alone
+
+
+def test_long_reply_is_not_resent():
+    """A reply longer than the 64 KB buffer is fetched with mcsim_last_output, not by running the command again."""
+    import pcoll_b200
+    plan = pcoll_b200.load_plan_json(os.path.join(GOLD, "plan_committed.json"))
+    short = dict(plan)
+    short["trajectory"] = plan["trajectory"][:, :3]
+    short["odometry"] = plan["odometry"][:, :2]
+    mod = pcoll_b200.MCModule(os.path.join(ROOT, "data", "scenes", "pr2test2.env.xml"), device=0)
+    pcoll_b200.push_parameters(mod, short, num_particles=64, num_gaussians=1, num_gmm_samples=64)
+    mod.SendCommand("setSeed 3")
+    n = 9000
+    reply = mod.SendCommand("runGMMEstimationBatch %d" % n)
+    assert len(reply) > (1 << 16) and len(reply.split()) == n
+    assert mod.SendCommand("describeRun").split()[-1] == str(n)      # the run counter advanced by n, not 2 n
+    mod.close()
+
+
+def _n_gpus():
+    import pcoll_b200
+    return pcoll_b200.cuda_abi.lib().mcsim_cuda_device_count()
+
+
+def test_set_devices_single_device_equals_default(plan):
+    import pcoll_b200
+    outs = []
+    for use in (False, True):
+        mod = _module(plan, "pr2test2", 200000)
+        if use:
+            mod.SendCommand("setDevices 0")
+            assert mod.SendCommand("getDevices") == "0"
+        mod.SendCommand("setSeed 5")
+        mod.SendCommand("setMode philox")
+        outs.append((mod.SendCommand("runSimulation"), mod.SendCommand("getStats").split()[0], mod.SendCommand("getFirstHitHistogram")))
+        mod.close()
+    assert outs[0] == outs[1]
+
+
+def test_multi_device_run_simulation_equals_one_device(plan):
+    """setDevices all: the C++ plugin host drives every GPU of the box through the C ABI alone (no Python-side
+    distribution): rollout ids split over the devices, counters all-reduced by the NCCL communicator the handle owns;
+    hits, histogram and the returned text equal the one-device run (BASELINE config 3's invariance)."""
+    import pcoll_b200
+    if _n_gpus() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    outs = []
+    for devs in ("0", "all"):
+        mod = _module(plan, "pr2test2", 3000001, num_gaussians=3, num_gmm_samples=5000)
+        mod.SendCommand("setDevices " + devs)
+        mod.SendCommand("setSeed 5")
+        mod.SendCommand("setMode philox")
+        res = []
+        for ee in (1, 0):
+            mod.SendCommand("setEarlyExit %d" % ee)
+            res.append((mod.SendCommand("runSimulation"), mod.SendCommand("getStats").split()[:3], mod.SendCommand("getFirstHitHistogram")))
+        res.append(mod.SendCommand("runGMMEstimationBatch 70"))
+        mod.SendCommand("setMode shared")
+        res.append(mod.SendCommand("runSimulation"))
+        outs.append(res)
+        mod.close()
+    assert outs[0][0] == outs[1][0] and outs[0][1] == outs[1][1]
+    np.testing.assert_allclose([float(v) for v in outs[0][2].split()], [float(v) for v in outs[1][2].split()], rtol=1e-5)
+    assert outs[0][3] == outs[1][3]

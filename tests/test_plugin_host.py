@@ -123,6 +123,47 @@ def test_command_grammar_parse_only(plan, scenes):
     mod.close()
 
 
+def test_run_ids_of_shards_and_runs_are_disjoint(plan, scenes):
+    """Two shards (setRolloutOffset 0 / N, common seed) x three runs: the run number lives in the Philox KEY, the shard
+    offset in the COUNTER, so the W x R blocks of (key, rollout id) are pairwise disjoint -- in round 1 run r + 1 of
+    shard s reused the ids of run r of shard s + 1.  describeRun reports what the next runs will use (no GPU needed)."""
+    import pcoll_b200
+    N = 1000
+    blocks = []
+    gmm = []
+    for shard in range(2):
+        mod = pcoll_b200.MCModule(scenes["pr2test2"], device=-1)
+        pcoll_b200.push_parameters(mod, plan, num_particles=N, num_gaussians=3)
+        mod.SendCommand("setSeed 12345")
+        mod.SendCommand("setRolloutOffset %d" % (shard * N))
+        for run in range(3):
+            f = mod.SendCommand("describeRun %d" % run).split()
+            assert f[0] == "mc" and f[4] == "gmm"
+            blocks.append((int(f[1]), int(f[2]), int(f[3])))
+            gmm.append((int(f[5]), int(f[6])))
+        mod.close()
+    assert blocks[0] == (12345, 0, N)                      # run 0 of shard 0: the seed itself, ids from 0
+    keys = {b[0] for b in blocks}
+    assert len(keys) == 3                                  # one key per run number, the same on both shards
+    seen = set()
+    for key, first, count in blocks:
+        for other_key, lo, hi in seen:
+            assert key != other_key or first + count <= lo or hi <= first, "overlapping (key, id) blocks"
+        seen.add((key, first, first + count))
+    assert len(set(gmm)) == 6                              # GMM runs: (key salted by the shard, stream = run number)
+
+
+def test_set_devices_needs_a_device_and_is_parsed(scenes):
+    import pcoll_b200
+    mod = pcoll_b200.MCModule(scenes["pr2test2"], device=-1)
+    with pytest.raises(pcoll_b200.McsimError, match="ordinals or 'all'"):
+        mod.SendCommand("setDevices zero")
+    with pytest.raises(pcoll_b200.McsimError):     # no CUDA device in the CPU test environment: loud, no fallback
+        mod.SendCommand("setDevices 0,1")
+    assert mod.SendCommand("getDevices") == ""
+    mod.close()
+
+
 def test_arma_command_writes_arma_ascii(tmp_path, scenes, monkeypatch):
     import pcoll_b200
     monkeypatch.chdir(tmp_path)
