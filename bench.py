@@ -10,8 +10,10 @@ plan (tests/golden/plan_committed.json = trajectory.dat / odometry.dat as MCSimu
 reference's noise parameters, Philox mode (every rollout owns its real-robot/EKF thread and its particle,
 SURVEY.md A0), NO early exit (the reference moves and tests every particle at every waypoint,
 MCSimulator.h:333-347), so executed rollout-steps == nominal rollout-steps.  One step = one runSimulation of
-`--rollouts` rollouts PER GPU (weak scaling: rank r owns rollout ids [r*n, (r+1)*n), a disjoint Philox
-subsequence per id) followed by the NCCL all-reduce of the hit counters on the same stream.
+`--rollouts` rollouts IN TOTAL (`--scaling strong`, the default: configs[2] is a fixed job of 10^8 rollouts "sharded across
+1/2/4/8 B200"; rank r owns rollout ids [r*N/G, (r+1)*N/G), Philox counters come from the global id, so hits and
+P_collision are the same at every N) or PER GPU (`--scaling weak`), followed by the NCCL all-reduce of the hit
+counters on the same stream.
 
 metric  = MC rollout-steps/s (a rollout-step = one pose update + one robot-vs-scene collision query).
 value   = device-resident: plan uploaded once, timed region = K x (rollout kernel + all-reduce), CUDA events on
@@ -55,8 +57,11 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scene", default="pr2test2", choices=["pr2test2", "pr2custom"])
-    ap.add_argument("--rollouts", type=int, default=10 ** 8, help="rollouts per GPU per step")
-    ap.add_argument("--e2e-rollouts", type=int, default=10 ** 7, help="rollouts per GPU per e2e step")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                    help="strong: --rollouts is the whole job, split over the GPUs (BASELINE configs[2]); weak: --rollouts per GPU")
+    ap.add_argument("--rollouts", type=int, default=10 ** 8, help="rollouts per step: of the whole job (strong) or per GPU (weak)")
+    ap.add_argument("--e2e-rollouts", type=int, default=8 * 10 ** 7, help="rollouts per e2e step: whole job (strong) or x GPUs (weak: this / 8 per GPU)")
+    ap.add_argument("--group-e2e-child", type=int, default=0, help=argparse.SUPPRESS)
     ap.add_argument("--ref-particles", type=int, default=10000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--exhaustive", action="store_true", help="time the rollout kernel with its broad phase off (every live pair at every step)")
@@ -178,12 +183,13 @@ def reference_arm(a):
     return 0
 
 
-def workload_config(a, per_gpu):
+def workload_config(a, per_gpu, job=None):
     return {
         "workload": "BASELINE configs[2]: MC convergence run of the committed trajectory.dat/odometry.dat plan (T=56), "
-                    "Philox mode, reference estimator law, no early exit; %s rollouts per GPU per step" % (
-                        "%d" % per_gpu if per_gpu else "reference arm: bounded sample of the same plan"),
-        "scene": a.scene, "waypoints": 56, "rollouts_per_gpu_per_step": per_gpu,
+                    "Philox mode, reference estimator law, no early exit; %s" % (
+                        ("%d rollouts per step in total, %s scaling (%d per GPU)" % (job, a.scaling, per_gpu)) if per_gpu
+                        else "reference arm: bounded sample of the same plan"),
+        "scene": a.scene, "waypoints": 56, "rollouts_per_gpu_per_step": per_gpu, "rollouts_per_step": job,
         "collision_query": "every live (hull, box) pair at every step" if getattr(a, "exhaustive", False) else
                            "exact broad phase: identical per-rollout counts to testing every live pair (tests/test_mc_gpu.py::"
                            "test_philox_broad_phase_is_exact); executed pair tests are counted and are what the roofline is charged with",
@@ -197,11 +203,14 @@ def main():
     a = parse()
     if a.impl == "reference":
         return reference_arm(a)
+    if a.group_e2e_child:
+        return group_e2e_child(a)
 
     import torch
     import torch.distributed as dist
     import pcoll_b200
     abi = pcoll_b200.cuda_abi
+    from pcoll_b200.sharding import shard_range
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -216,14 +225,17 @@ def main():
     ctx = abi.Context(local)
     ctx.set_scene(sc["boxes"], sc["hulls"])
     stream = torch.cuda.ExternalStream(ctx.stream, device=local)
-    n = a.rollouts
+    # strong scaling: one fixed job, rollout ids [lo, hi) per rank; weak: --rollouts per rank
+    n_job = a.rollouts if a.scaling == "strong" else a.rollouts * world
+    lo, hi = shard_range(n_job, rank, world)
+    n = hi - lo
     counters = ctx.mc_counters_tensor(T)  # torch view of the device counter block (u64 as int64)
     total = torch.zeros_like(counters)
     flush = torch.empty(512 << 20, dtype=torch.uint8, device="cuda")
 
     fp32_peak, mufu_peak = ctx.measure_peaks(150.0)
 
-    p, keep = abi.make_mc_params(plan, n_rollouts=n, rollout_offset=rank * n, mode=abi.MODE_PHILOX, early_exit=False, exhaustive=a.exhaustive)
+    p, keep = abi.make_mc_params(plan, n_rollouts=n, rollout_offset=lo, mode=abi.MODE_PHILOX, early_exit=False, exhaustive=a.exhaustive)
     ctx.mc_prepare(p)
 
     def barrier():
@@ -236,7 +248,7 @@ def main():
             flush.zero_()  # L2 flush, outside the event pair
             if ev:
                 ev[0].record(stream)
-            ctx.mc_launch(n, rank * n)
+            ctx.mc_launch(n, lo)
             if ev:
                 ev[1].record(stream)
             if world > 1:
@@ -271,25 +283,53 @@ def main():
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
     step_ms, kernel_ms = float(tmax[0]), float(tmax[1])
     job_steps = tot["executed_steps"]          # whole job, K steps
-    assert job_steps == a.steps * world * n * T, (job_steps, a.steps, world, n, T)
+    assert job_steps == a.steps * n_job * T, (job_steps, a.steps, n_job, T)
     value = job_steps / (step_ms * 1e-3)
     flops_job = job_steps * F_PHILOX_STEP + tot["pair_tests"] * F_SAT
     achieved = flops_job / world / (kernel_ms * 1e-3) / 1e12  # per GPU, TFLOP/s
-    P = tot["hits"] / (a.steps * world * n)
+    assert tot["hits"] % a.steps == 0           # every step is the same job: the same hits
+    hits_per_step = tot["hits"] // a.steps
+    P = hits_per_step / n_job
+
+    # ---- BASELINE configs[2]'s invariant, checked inside the bench: the sharded job's hit total and first-hit histogram equal
+    # one GPU's on the same rollout ids (a 2^22-rollout job, so that rank 0 can run all of it alone in milliseconds)
+    invariance = None
+    if world > 1:
+        n_small = 1 << 22
+        slo, shi = shard_range(n_small, rank, world)
+        ps, keep_s = abi.make_mc_params(plan, n_rollouts=shi - slo, rollout_offset=slo, mode=abi.MODE_PHILOX, early_exit=False)
+        ctx.mc_prepare(ps)
+        with torch.cuda.stream(stream):
+            counters.zero_()
+            ctx.mc_launch(shi - slo, slo)
+            dist.all_reduce(counters)
+        stream.synchronize()
+        sharded = counters.cpu().numpy().astype(np.uint64)
+        with torch.cuda.stream(stream):
+            counters.zero_()
+        if rank == 0:
+            pa, keep_a = abi.make_mc_params(plan, n_rollouts=n_small, rollout_offset=0, mode=abi.MODE_PHILOX, early_exit=False)
+            alone = ctx.mc_run(pa, want_hist=True)
+            same = int(sharded[0]) == alone["hits"] and np.array_equal(sharded[4:4 + T], alone["first_hit_hist"])
+            invariance = {"rollouts": n_small, "hits_sharded": int(sharded[0]), "hits_one_gpu": alone["hits"], "histogram_equal": bool(same)}
+            assert same, invariance
+        ctx.mc_prepare(p)
+        barrier()
 
     # ---- the same kernel with the broad phase off (every live pair tested at every step, as CheckCollision does):
     # its arithmetic rate under the full SAT load, reported inside `roofline` next to the product configuration
     every_pair = None
     if not a.exhaustive:
-        pe, keep_e = abi.make_mc_params(plan, n_rollouts=n, rollout_offset=rank * n, mode=abi.MODE_PHILOX, early_exit=False, exhaustive=True)
+        ne = min(n, 25 * 10 ** 6)
+        pe, keep_e = abi.make_mc_params(plan, n_rollouts=ne, rollout_offset=lo, mode=abi.MODE_PHILOX, early_exit=False, exhaustive=True)
         ctx.mc_prepare(pe)
         ev_e = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
         with torch.cuda.stream(stream):
-            ctx.mc_launch(n, rank * n)
+            ctx.mc_launch(ne, lo)
             counters.zero_()
             flush.zero_()
             ev_e[0].record(stream)
-            ctx.mc_launch(n, rank * n)
+            ctx.mc_launch(ne, lo)
             ev_e[1].record(stream)
         stream.synchronize()
         ce = counters.cpu().numpy().astype(np.uint64)
@@ -300,8 +340,7 @@ def main():
         fl_e = int(ce[2]) * F_PHILOX_STEP + int(ce[3]) * F_SAT
         every_pair = {"rollout_steps_per_s_per_gpu": int(ce[2]) / (ms_e * 1e-3), "pair_tests_per_step": int(ce[3]) / max(int(ce[2]), 1),
                       "achieved": fl_e / (ms_e * 1e-3) / 1e12, "frac": fl_e / (ms_e * 1e-3) / 1e12 / fp32_peak,
-                      "hits_equal_product_run": int(ce[0]) * a.steps * world == tot["hits"] if world == 1 else None,
-                      "note": "one launch, rank %d, broad phase off (mcsim_mc_params.exhaustive = 1)" % rank}
+                      "note": "one launch of %d rollouts, rank %d, broad phase off (mcsim_mc_params.exhaustive = 1)" % (ne, rank)}
         ctx.mc_prepare(p)
 
     # ---- e2e: the plugin command interface with host buffers, every step: parameters + plan pushed as command
@@ -314,9 +353,10 @@ def main():
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
-        "ms_per_step": step_ms / a.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic", "config": workload_config(a, n),
-        "P_collision": P, "wall_ms_per_step_incl_flush": 1e3 * t_wall / a.steps,
+        "ms_per_step": step_ms / a.steps, "higher_is_better": True, "scaling": a.scaling, "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(a, n, n_job),
+        "P_collision": P, "hits_per_step": hits_per_step, "hits_invariance": invariance,
+        "wall_ms_per_step_incl_flush": 1e3 * t_wall / a.steps,
         "clocks": clocks, "gpu_launches": launches, "e2e": e2e,
         "roofline": {
             "bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak,
@@ -325,7 +365,7 @@ def main():
                             "launch: dram__bytes_read 52 KB, dram__bytes_write 0 (profiles/r01_philox2_ladder_ncu_summary.csv)",
             "kernel": "mc_philox2_kernel<no early exit, reference estimator, L=8> (two rollouts per thread, packed FP32 pairs)",
             "kernel_ms_per_launch": kernel_ms / a.steps,
-            "algorithmic": "%d flops per Philox rollout-step + %d per SAT pair test x %.1f live pair tests per step" % (
+            "algorithmic": "%d flops per Philox rollout-step + %d per SAT pair test x %.2f executed pair tests per step" % (
                 F_PHILOX_STEP, F_SAT, tot["pair_tests"] / job_steps),
             "sfu": {"achieved": job_steps * SFU_PHILOX_STEP / world / (kernel_ms * 1e-3) / 1e12, "peak": mufu_peak, "unit": "Top/s",
                     "frac": job_steps * SFU_PHILOX_STEP / world / (kernel_ms * 1e-3) / 1e12 / mufu_peak,
@@ -335,20 +375,32 @@ def main():
             "every_pair_tested": every_pair,
         },
     }
-    if rank == 0 and not a.no_extras:
-        line["extras"] = extras(a, ctx, abi, plan, T, stream, torch)
+    if not a.no_extras:
+        # legs every rank takes part in (GMM replicas, sharded EM); rank 0 keeps the records
         try:
-            line["extras"].update(extras_scoring_em(ctx, abi, plan, sc, fp32_peak))
-        except Exception as exc:  # reported, never silently dropped
-            line["extras"]["scoring_em_error"] = repr(exc)
-    if rank == 0 and "extras" in line and line["extras"].get("gmm_batch_main") in line["extras"]:
-        key = line["extras"]["gmm_batch_main"]
-        g = line["extras"][key]
-        line["secondary"] = {"metric": "gmm_pcoll_trajectories_per_s", "value": g["trajectories_per_s"], "unit": "trajectories/s",
-                             "config": "runGMMEstimation, K = 3, 10^4 samples per waypoint, 56 waypoints, %s runs per batch "
-                                       "(mcsim_cuda_gmm_run_batch), host buffers in and out (BASELINE configs[1])" % key.split("batch")[-1],
+            multi = extras_all_ranks(a, ctx, abi, plan, T, torch, dist, world, rank, barrier, fp32_peak)
+        except Exception as exc:
+            multi = {"all_ranks_error": repr(exc)}
+        if rank == 0:
+            line["extras"] = extras(a, ctx, abi, plan, T, stream, torch)
+            line["extras"].update(multi)
+            try:
+                line["extras"].update(extras_scoring_em(ctx, abi, plan, sc, fp32_peak))
+            except Exception as exc:  # reported, never silently dropped
+                line["extras"]["scoring_em_error"] = repr(exc)
+            try:
+                line["extras"]["config1_shared_mode"] = config1_leg(a, plan, sc, local)
+            except Exception as exc:
+                line["extras"]["config1_error"] = repr(exc)
+    if rank == 0 and "extras" in line and "gmm_replicas" in line["extras"]:
+        g = line["extras"]["gmm_replicas"]
+        line["secondary"] = {"metric": "gmm_pcoll_trajectories_per_s", "value": g["trajectories_per_s"], "unit": "trajectories/s", "n_gpus": world,
+                             "config": "runGMMEstimation, K = 3, 10^4 samples per waypoint, 56 waypoints, %d runs per batch and GPU "
+                                       "(mcsim_cuda_gmm_run_batch; replicas: every GPU its own batch, no collective), host buffers in and out "
+                                       "(BASELINE configs[1])" % g["runs_per_gpu"],
                              "kernel_only": g["trajectories_per_s_kernel_only"],
-                             "single_run_value": line["extras"].get("gmm_K3_N10000", {}).get("trajectories_per_s")}
+                             "single_run_value": line["extras"].get("gmm_K3_N10000", {}).get("trajectories_per_s"),
+                             "roofline": g["roofline"]}
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
         import oracle_ref
         if oracle_ref.available():
@@ -376,12 +428,177 @@ def main():
                                           "sample": "arma::gmm_full::learn(keep_existing, em_iter = 10), K = 3, 2 x 10^5 samples, 1 thread; %.1f s" % dt}
         else:
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": "oracle/_ref not built"}
+    ctx.close()
+    del counters, total, flush
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+        if rank != 0:
+            return 0
+        # ---- e2e at N GPUs through the C ABI alone: ONE plugin module, `setDevices 0 .. N-1` (NCCL communicators owned
+        # by the handle), driven from a torch-free child process once the other ranks have left their GPUs
+        torch.cuda.synchronize()
+        line["e2e"] = group_e2e_parent(a, world, line["e2e"])
     if rank == 0:
         print(json.dumps(line))
-    ctx.close()
-    if world > 1:
-        dist.destroy_process_group()
     return 0
+
+
+def group_e2e_parent(a, world, per_rank):
+    import subprocess as sp
+    time.sleep(1.0)
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "GROUP_RANK",
+                                                            "ROLE_RANK", "ROLE_WORLD_SIZE", "LOCAL_WORLD_SIZE", "TORCHELASTIC_RUN_ID")}
+    cmd = [sys.executable, os.path.abspath(__file__), "--group-e2e-child", str(world), "--steps", str(a.steps), "--warmup", str(a.warmup),
+           "--scene", a.scene, "--e2e-rollouts", str(a.e2e_rollouts), "--scaling", a.scaling]
+    try:
+        out = sp.run(cmd, env=env, capture_output=True, text=True, timeout=240)
+        rec = json.loads(out.stdout.strip().splitlines()[-1])
+        rec["per_rank_modules"] = per_rank    # the same job as N processes x one module each (torch.distributed around them)
+        return rec
+    except Exception as exc:
+        per_rank = dict(per_rank or {})
+        per_rank["single_process_group_error"] = repr(exc)
+        return per_rank
+
+
+def group_e2e_child(a):
+    """Torch-free: one MCModule over `--group-e2e-child` devices; runSimulation of the whole e2e job, host wall clock."""
+    import pcoll_b200
+    G = a.group_e2e_child
+    plan, sc = load_inputs(a.scene)
+    T = plan["trajectory"].shape[1]
+    n_job = a.e2e_rollouts if a.scaling == "strong" else (a.e2e_rollouts // 8) * G
+    mod = pcoll_b200.MCModule(scene=sc, device=0)
+    mod.SendCommand("setDevices " + " ".join(str(d) for d in range(G)))
+    pcoll_b200.push_parameters(mod, plan, num_particles=n_job)
+    mod.SendCommand("setMode philox")
+    mod.SendCommand("setEarlyExit 0")
+    mod.SendCommand("setSeed %d" % 0x5AFEC0DE)
+    for _ in range(max(1, a.warmup)):
+        mod.SendCommand("runSimulation")
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        float(mod.SendCommand("runSimulation"))
+    dt = time.perf_counter() - t0
+    io = mod.io_bytes()
+    hits = int(mod.SendCommand("getStats").split()[0])
+    mod.close()
+    print(json.dumps({"value": a.steps * n_job * T / dt, "unit": UNIT, "h2d_bytes_per_step": io[0] * G, "d2h_bytes_per_step": io[1] * G,
+                      "rollouts_per_step": n_job, "n_gpus": G, "hits_last_step": hits,
+                      "api": "ONE MCModule, SendCommand('setDevices 0..%d') + SendCommand('runSimulation') -> libmcsim.so -> mcsim_cuda_group_mc_run "
+                             "(rollout ids split over the devices, ncclAllReduce of the counters on the handle's communicators); no torch in this process" % (G - 1),
+                      "timing": "host wall clock around K synchronous calls"}))
+    return 0
+
+
+def config1_leg(a, plan, sc, local):
+    """BASELINE configs[0] as the reference driver runs it: runSimulation in the plugin's default `shared` mode (one
+    closed-loop real robot per run, MCSimulator.h:754-761) at N = 1,000 (BASELINE) and 10,000 (MCSimulation.py:164):
+    microseconds per call through SendCommand, beside the reference estimator on one host core."""
+    import pcoll_b200
+    out = {}
+    for N in (1000, 10000):
+        mod = pcoll_b200.MCModule(scene=sc, device=local)
+        pcoll_b200.push_parameters(mod, plan, num_particles=N)
+        mod.SendCommand("setSeed 1")
+        for _ in range(20):
+            mod.SendCommand("runSimulation")
+        reps = 200
+        t0 = time.perf_counter()
+        Ps = [float(mod.SendCommand("runSimulation")) for _ in range(reps)]
+        dt = (time.perf_counter() - t0) / reps
+        kernel_ms = float(mod.SendCommand("getStats").split()[4])
+        mod.close()
+        rec = {"us_per_call": dt * 1e6, "kernel_us": kernel_ms * 1e3, "P_mean_of_200_runs": float(np.mean(Ps)), "P_std": float(np.std(Ps, ddof=1)),
+               "rollout_steps_per_s": N * plan["trajectory"].shape[1] / dt}
+        try:
+            import oracle_ref
+            if oracle_ref.available():
+                t0 = time.perf_counter()
+                k = 3 if N > 1000 else 10
+                for s_ in range(k):
+                    oracle_ref.mc_run(plan, sc["boxes"], sc["hulls"], N, mt_seed=s_, record=False)
+                rec["reference_us_per_call_one_core"] = (time.perf_counter() - t0) / k * 1e6
+        except Exception:
+            pass
+        out["N%d" % N] = rec
+    return out
+
+
+def extras_all_ranks(a, ctx, abi, plan, T, torch, dist, world, rank, barrier, fp32_peak):
+    """The legs of BASELINE.json's metric that need every rank: GMM trajectories/s as replicas (each GPU its own batch of
+    runs, no collective -- one run is a chain of 56 dependent waypoints and does not shard) and the EM fit
+    with its samples sharded (one all-reduce of the K 10 + 1 statistics per fit and iteration)."""
+    from pcoll_b200.sharding import em_fit_sharded, shard_range
+    import pcoll_b200
+    out = {}
+    n_sm = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
+    B, ns = 9 * n_sm, 10000
+    ctx.gmm_run_batch(plan, 3, ns, B, stream0=rank * 100000)
+    best, rec = None, None
+    for rep in range(3):
+        barrier()
+        t0 = time.perf_counter()
+        g = ctx.gmm_run_batch(plan, 3, ns, B, stream0=rank * 100000 + B * (rep + 1))
+        dt = time.perf_counter() - t0
+        t = torch.tensor([dt, g["kernel_ms"] * 1e-3], dtype=torch.float64, device="cuda")
+        tests = torch.tensor([float(g["pair_tests"])], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(tests)
+        if best is None or float(t[0]) < best:
+            best, rec = float(t[0]), (float(t[1]), float(tests[0]), g)
+    ksec, tests, g = rec
+    checks = world * B * T * ns
+    flops = checks * F_GMM_SAMPLE + tests * F_SAT
+    out["gmm_replicas"] = {
+        "trajectories_per_s": world * B / best, "trajectories_per_s_kernel_only": world * B / ksec, "runs_per_gpu": B, "n_gpus": world,
+        "sample_checks_per_s": checks / best, "pair_tests_per_sample": tests / checks, "P_mean": float(g["P"].mean()), "P_std": float(g["P"].std()),
+        "timing": "best of 3 barrier-aligned calls, host wall clock, max over ranks",
+        "roofline": {"bound": "fp32", "achieved": flops / world / ksec / 1e12, "peak": fp32_peak, "unit": "TFLOP/s", "frac": flops / world / ksec / 1e12 / fp32_peak,
+                     "kernel": "gmm_member_run_kernel (one CTA per run for the whole plan)",
+                     "algorithmic": "%d flops per sample (draw, L z, pose, moment sums) + %d per executed SAT pair test x %.2f tests per sample" % (
+                         F_GMM_SAMPLE, F_SAT, tests / checks)}}
+    # ---- EM, samples sharded: BASELINE config 5's 56 waypoint buffers x 10^6 samples, K = 1, 3, 16, 10 iterations
+    F, n_tot, iters = 56, 10 ** 6, 10
+    lo, hi = shard_range(n_tot, rank, world)
+    lo, hi = lo & ~3, (hi & ~3) if rank + 1 < world else n_tot
+    xf, m16, c16 = config5_buffers(plan, n_tot, F)
+    x = np.ascontiguousarray(xf[:, :, lo:hi])
+    del xf
+    first = True
+    for K in (1, 3, 16):
+        h = np.full((F, K), 1.0 / K); m = np.ascontiguousarray(m16[:, :K]); c = np.ascontiguousarray(c16[:, :K])
+        em_fit_sharded(ctx, x if first else None, n_tot, h, m, c, 2)
+        first = False
+        times = []
+        for with_collective in (True, False):   # the same loop with and without the all-reduce: its share of the iteration
+            ctx.em_prepare(None, h, m, c, iters, n_total=n_tot)
+            barrier()
+            evs = [cuda_event(ctx) for _ in range(2)]
+            evs[0].record()
+            for _ in range(iters):
+                ctx.em_estep()
+                if with_collective and world > 1:
+                    with torch.cuda.stream(ctx.torch_stream):
+                        dist.all_reduce(ctx.em_stats_tensor())
+                ctx.em_mstep()
+            evs[1].record()
+            times.append(evs[0].elapsed_ms(evs[1]))
+            if with_collective:
+                r = ctx.em_collect()
+        ms, ms_local = times
+        t = torch.tensor([ms, ms_local], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, ms_local = float(t[0]), float(t[1])
+        out["em_sharded_K%d" % K] = {
+            "fits": F, "samples_per_fit": n_tot, "iterations": iters, "n_gpus": world, "ms": ms, "ms_without_all_reduce": ms_local,
+            "all_reduce_share": max(0.0, 1.0 - ms_local / ms) if ms > 0 else None,
+            "sample_iterations_per_s": F * n_tot * iters / (ms * 1e-3), "iters_run_min_max": [int(r["iters_run"].min()), int(r["iters_run"].max())],
+            "collective": "all_reduce(sum, float64) of %d doubles per iteration (NCCL, on the library's stream)" % (F * (K * 10 + 1))}
+    return out
 
 
 def read_measured_peaks():
@@ -397,13 +614,17 @@ def e2e_leg(a, plan, sc, local, rank, world, barrier):
     """rollout-steps/s through the reference-facing command interface (MCModule.SendCommand), host buffers."""
     import torch
     import pcoll_b200
+    from pcoll_b200.sharding import shard_range
     T = plan["trajectory"].shape[1]
-    n = a.e2e_rollouts
+    n_job = a.e2e_rollouts if a.scaling == "strong" else (a.e2e_rollouts // 8) * world
+    lo, hi = shard_range(n_job, rank, world)
+    n = hi - lo
     mod = pcoll_b200.MCModule(scene=sc, device=local)
     pcoll_b200.push_parameters(mod, plan, num_particles=n)
     mod.SendCommand("setMode philox")
     mod.SendCommand("setEarlyExit 0")
-    mod.SendCommand("setRolloutOffset %d" % (rank * n))
+    mod.SendCommand("setSeed %d" % 0x5AFEC0DE)
+    mod.SendCommand("setRolloutOffset %d" % lo)
     for _ in range(max(1, a.warmup)):
         mod.SendCommand("runSimulation")
     barrier()
@@ -419,8 +640,8 @@ def e2e_leg(a, plan, sc, local, rank, world, barrier):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     io = mod.io_bytes()
     mod.close()
-    return {"value": a.steps * world * n * T / float(t[0]), "unit": UNIT, "h2d_bytes_per_step": io[0], "d2h_bytes_per_step": io[1],
-            "rollouts_per_gpu_per_step": n, "api": "MCModule.SendCommand('runSimulation') -> libmcsim.so -> libmcsim_cuda.so",
+    return {"value": a.steps * n_job * T / float(t[0]), "unit": UNIT, "h2d_bytes_per_step": io[0] * world, "d2h_bytes_per_step": io[1] * world,
+            "rollouts_per_step": n_job, "rollouts_per_gpu_per_step": n, "api": "MCModule.SendCommand('runSimulation') -> libmcsim.so -> libmcsim_cuda.so",
             "timing": "host wall clock around K synchronous calls, max over ranks"}
 
 
@@ -433,7 +654,14 @@ def extras(a, ctx, abi, plan, T, stream, torch):
     r = ctx.mc_run(p)
     out["mc_early_exit"] = {"nominal_rollout_steps_per_s": n * T / (r["kernel_ms"] * 1e-3),
                             "executed_rollout_steps_per_s": r["executed_steps"] / (r["kernel_ms"] * 1e-3),
-                            "rollouts": n, "P": r["P"]}
+                            "executed_fraction": r["executed_steps"] / (n * T), "rollouts": n, "P": r["P"], "hits": r["hits"],
+                            "how": "survivor compaction: one launch per 4 waypoints, the rollouts still free are compacted in device memory "
+                                   "(mc_philox2_segment_kernel); hits identical to the no-exit run"}
+    pn, keep_n = abi.make_mc_params(plan, n_rollouts=n, mode=abi.MODE_PHILOX, early_exit=True, no_compaction=True)
+    ctx.mc_run(pn)
+    rn = ctx.mc_run(pn)
+    out["mc_early_exit"]["one_launch_nominal_rollout_steps_per_s"] = n * T / (rn["kernel_ms"] * 1e-3)
+    assert rn["hits"] == r["hits"]
     if hasattr(ctx, "gmm_run"):
         try:
             for K, ns in ((3, 10000), (3, 1000000)):
@@ -445,10 +673,7 @@ def extras(a, ctx, abi, plan, T, stream, torch):
                 dt = (time.perf_counter() - t0) / reps
                 out["gmm_K%d_N%d" % (K, ns)] = {"trajectories_per_s": 1.0 / dt, "sample_checks_per_s": T * ns / dt,
                                                 "kernel_ms": g["kernel_ms"], "P": g["P"]}
-            # batches: 256 runs, 1,024 runs, and 9 x the SM count (three full waves of the one-CTA-per-run kernel at
-            # its three resident CTAs per SM: 1,332 on a 148-SM B200) -- the last is the `secondary` metric
-            n_sm = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
-            for ns, B in ((10000, 256), (10000, 1024), (10000, 9 * n_sm)):
+            for ns, B in ((10000, 256), (10000, 1024)):
                 ctx.gmm_run_batch(plan, 3, ns, B)
                 best = None
                 for rep in range(3):
@@ -456,13 +681,9 @@ def extras(a, ctx, abi, plan, T, stream, torch):
                     g = ctx.gmm_run_batch(plan, 3, ns, B, stream0=B * (rep + 1))
                     dt = time.perf_counter() - t0
                     best = dt if best is None or dt < best else best
-                dt = best
                 out["gmm_K3_N%d_batch%d" % (ns, B)] = {
-                    "trajectories_per_s": B / dt, "trajectories_per_s_kernel_only": B / (g["kernel_ms"] * 1e-3),
-                    "sample_checks_per_s": B * T * ns / dt, "kernel_ms": g["kernel_ms"],
-                    "pair_tests_per_sample": g["pair_tests"] / (B * T * ns),
-                    "P_mean": float(g["P"].mean()), "P_std": float(g["P"].std()), "timing": "best of 3 calls, host wall clock"}
-                out["gmm_batch_main"] = "gmm_K3_N%d_batch%d" % (ns, B)
+                    "trajectories_per_s": B / best, "trajectories_per_s_kernel_only": B / (g["kernel_ms"] * 1e-3), "kernel_ms": g["kernel_ms"],
+                    "pair_tests_per_sample": g["pair_tests"] / (B * T * ns), "timing": "best of 3 calls, host wall clock"}
         except Exception as exc:
             out["gmm_error"] = repr(exc)
     return out
@@ -499,29 +720,44 @@ def extras_scoring_em(ctx, abi, plan, sc, fp32_peak):
     ctx.set_scene(sc["boxes"], sc["hulls"])
     # ---- config 5: EM sweep, 56 waypoint buffers x 10^6 FP32 samples (672 MB resident), 10 iterations
     F, n, iters = 56, 10 ** 6, 10
-    traj = plan["trajectory"]
-    base = [inp.synthetic_em_problem(9000 + f, n, 16, centre=(0.0, 0.0, 0.0)) for f in range(8)]
-    probs = []  # 56 distinct buffers: 8 seeded mixtures, each moved to 7 different trajectory poses
-    for f in range(F):
-        b, ctr = base[f % 8], traj[:, f % traj.shape[1]]
-        probs.append(((b[0] + ctr.astype(np.float32)[:, None]).astype(np.float32), b[1], b[2] + ctr[None, :], b[3]))
-    x = np.stack([q[0] for q in probs])
+    x, m16, c16 = config5_buffers(plan, n, F)
     first = True
     for K in (1, 2, 3, 4, 8, 16):
-        h = np.stack([np.full(K, 1.0 / K) for q in probs]); m = np.stack([q[2][:K] for q in probs]); c = np.stack([q[3][:K] for q in probs])
+        h = np.full((F, K), 1.0 / K); m = np.ascontiguousarray(m16[:, :K]); c = np.ascontiguousarray(c16[:, :K])
         ctx.em_fit(x if first else None, h, m, c, 2)
         first = False
         r = ctx.em_fit(None, h, m, c, iters)
         sec = r["kernel_ms"] * 1e-3
-        gbs = 12.0 * n * F * iters / sec / 1e9
+        done_it = int(r["iters_run"].astype(np.int64).sum())      # executed fit-iterations (= F * iters unless a fit converged early)
+        gbs = 12.0 * n * done_it / sec / 1e9
         out["em_config5_K%d" % K] = {
             "fits": F, "samples_per_fit": n, "iterations": iters, "kernel_ms": r["kernel_ms"],
-            "sample_iterations_per_s": n * F * iters / sec, "algorithmic_GBps": gbs,
+            "sample_iterations_per_s": n * done_it / sec, "algorithmic_GBps": gbs,
             "frac_of_hbm_peak": gbs / peaks["hbm_gbs"] if peaks.get("hbm_gbs") else None,
-            "algorithmic_tflops": 61.0 * K * n * F * iters / sec / 1e12,
-            "frac_of_fp32_peak": 61.0 * K * n * F * iters / sec / 1e12 / fp32_peak,
+            "algorithmic_tflops": 61.0 * K * n * done_it / sec / 1e12,
+            "frac_of_fp32_peak": 61.0 * K * n * done_it / sec / 1e12 / fp32_peak,
+            "iters_run_min_max": [int(r["iters_run"].min()), int(r["iters_run"].max())],
+            "executed_sample_iterations": int(r["iters_run"].astype(np.int64).sum()) * n,
+            "note": "rates are charged with the EXECUTED sample-iterations (a fit that converges stops; iters_run says whether any did)",
             "avg_log_p_last": float(np.nanmean(r["avg_log_p"][:, -1]))}
     return out
+
+
+def config5_buffers(plan, n=10 ** 6, F=56):
+    """BASELINE config 5: F distinct waypoint buffers of n FP32 samples (672 MB at 56 x 10^6, so an iteration streams from
+    HBM, not L2): 8 seeded 3-component mixtures, each moved to 7 trajectory poses.  Returns x [F, 3, n] and the
+    keep_existing starting points for up to 16 components."""
+    import pcoll_b200
+    traj = plan["trajectory"]
+    base = [pcoll_b200.inputs.synthetic_em_problem(9000 + f, n, 16, centre=(0.0, 0.0, 0.0)) for f in range(8)]
+    x = np.empty((F, 3, n), dtype=np.float32)
+    means, fcovs = [], []
+    for f in range(F):
+        b, ctr = base[f % 8], traj[:, f % traj.shape[1]]
+        x[f] = b[0] + ctr.astype(np.float32)[:, None]
+        means.append(b[2] + ctr[None, :])
+        fcovs.append(b[3])
+    return x, np.stack(means), np.stack(fcovs)
 
 
 class cuda_event:

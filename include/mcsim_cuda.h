@@ -227,7 +227,16 @@ typedef struct {
     const double* normals;
     size_t n_normals;
     const int* counts;           /* [T x K] multinomial counts per waypoint (replay) */
+    int kernel;                  /* MCSIM_GMM_KERNEL_*: which launch shape runs a Philox-mode plan (results agree to the
+                                    order of the FP64 sums; for tests and for measuring the switch-over) */
 } mcsim_gmm_run_params;
+
+enum {
+    MCSIM_GMM_KERNEL_AUTO = 0,          /* one thread-block cluster for the whole plan up to 98,304 samples per waypoint
+                                           (batches of >= 64 runs: one CTA per run), else three kernels per waypoint */
+    MCSIM_GMM_KERNEL_PER_WAYPOINT = 1,  /* count / sample / refit launches per waypoint, the whole GPU per waypoint */
+    MCSIM_GMM_KERNEL_CLUSTER = 2        /* the cluster kernel at any sample count */
+};
 
 typedef struct {
     double P;                    /* 1 - prod_t (1 - p_t)  (MCSimulator.h:848-856) */
@@ -257,6 +266,7 @@ typedef struct {
     const double* trajectories;  /* [n_traj][3][T] or NULL: every member runs mc->trajectory */
     const double* odometry;      /* [n_traj][3][T-1] or NULL */
     uint64_t stream0;
+    int kernel;                  /* MCSIM_GMM_KERNEL_* (AUTO: batches of >= 64 runs take the one-CTA-per-run kernel) */
 } mcsim_gmm_batch_params;
 
 typedef struct {

@@ -80,21 +80,35 @@ struct GmmLaunch {
     int spread;                   // Philox sample kernel: one sample per thread instead of two (small n, single run)
 };
 
-// Batch member b (blockIdx.y of the count / sample kernels, blockIdx.x of the refit kernel): same plan-independent
-// fields, its own mixture, statistics, counts, step table, per-waypoint probabilities and Philox subsequence.
-__device__ __forceinline__ GmmLaunch gmm_member(const GmmLaunch& in, int b) {
-    GmmLaunch a = in;
-    if (b > 0) {
-        a.comps += size_t(b) * MCSIM_MAX_GAUSSIANS * GMM_COMP;
-        a.stats += size_t(b) * MCSIM_MAX_GAUSSIANS * GMM_STAT;
-        a.hist += size_t(b) * MCSIM_MAX_GAUSSIANS;
-        a.steps += size_t(b) * (in.T > 1 ? in.T - 1 : 1);
-        a.probabilities += size_t(b) * in.T;
-        a.degenerate += b;
-        a.stream_id += unsigned(b);
-        if (in.cull && in.cull_stride) { a.cull += size_t(b) * in.cull_stride; a.nominal += size_t(b) * in.T; }
-    }
-    return a;
+// Batch member b (blockIdx.y of the count / sample kernels, blockIdx.x of the refit kernel): its own mixture, statistics,
+// counts, step table, per-waypoint probabilities, lists and Philox subsequence.  Only these few pointers are per member;
+// everything else is read from the launch struct where it lies (the kernel parameter, constant bank).  (A by-value copy
+// of the whole GmmLaunch with adjusted pointers -- round 1 -- put 824 bytes on every thread's stack: its landmark
+// arrays are indexed at run time.)
+struct GmmMember {
+    double* comps;
+    double* stats;
+    unsigned* hist;
+    const GmmStepTable* steps;
+    double* probabilities;
+    int* degenerate;
+    const unsigned* cull;
+    const float2* nominal;
+    unsigned stream_id;
+};
+__device__ __forceinline__ GmmMember gmm_member(const GmmLaunch& in, int b) {
+    GmmMember m;
+    m.comps = in.comps + size_t(b) * MCSIM_MAX_GAUSSIANS * GMM_COMP;
+    m.stats = in.stats + size_t(b) * MCSIM_MAX_GAUSSIANS * GMM_STAT;
+    m.hist = in.hist + size_t(b) * MCSIM_MAX_GAUSSIANS;
+    m.steps = in.steps + size_t(b) * (in.T > 1 ? in.T - 1 : 1);
+    m.probabilities = in.probabilities + size_t(b) * in.T;
+    m.degenerate = in.degenerate + b;
+    m.stream_id = in.stream_id + unsigned(b);
+    const bool own = in.cull && in.cull_stride;
+    m.cull = own ? in.cull + size_t(b) * in.cull_stride : in.cull;
+    m.nominal = own ? in.nominal + size_t(b) * in.T : in.nominal;
+    return m;
 }
 
 // ---- FP64 SAT, statement order of oracle/sat_cpu.h (no contraction: _rn intrinsics) --------------------------
@@ -135,18 +149,19 @@ __device__ __forceinline__ double clearance_d(const HullD* hulls, const PairD* p
 
 // ---- multinomial counts (Philox mode): inverse CDF on one uniform per sample -----------------------------------
 __global__ void __launch_bounds__(256) gmm_count_kernel(const GmmLaunch a_in) {
-    const GmmLaunch a = gmm_member(a_in, blockIdx.y);
+    const GmmLaunch& a = a_in;
+    const GmmMember m = gmm_member(a_in, blockIdx.y);
     __shared__ float s_cdf[MCSIM_MAX_GAUSSIANS];
     __shared__ unsigned s_hist[MCSIM_MAX_GAUSSIANS];
     if (threadIdx.x < MCSIM_MAX_GAUSSIANS) s_hist[threadIdx.x] = 0;
     if (threadIdx.x == 0) {
         double acc = 0, tot = 0;
-        for (int g = 0; g < a.K; ++g) tot += a.comps[g * GMM_COMP];
-        for (int g = 0; g < a.K; ++g) { acc += a.comps[g * GMM_COMP]; s_cdf[g] = float(acc / tot); }
+        for (int g = 0; g < a.K; ++g) tot += m.comps[g * GMM_COMP];
+        for (int g = 0; g < a.K; ++g) { acc += m.comps[g * GMM_COMP]; s_cdf[g] = float(acc / tot); }
         // components after the last one with positive weight can never be drawn
-        for (int g = a.K - 1; g >= 0 && !(a.comps[g * GMM_COMP] > 0); --g) s_cdf[g] = 2.0f;
+        for (int g = a.K - 1; g >= 0 && !(m.comps[g * GMM_COMP] > 0); --g) s_cdf[g] = 2.0f;
         int last = a.K - 1;
-        while (last > 0 && !(a.comps[last * GMM_COMP] > 0)) --last;
+        while (last > 0 && !(m.comps[last * GMM_COMP] > 0)) --last;
         s_cdf[last] = 2.0f;  // u in (0,1]: the last live component absorbs rounding
     }
     __syncthreads();
@@ -157,7 +172,7 @@ __global__ void __launch_bounds__(256) gmm_count_kernel(const GmmLaunch a_in) {
     const int K = a.K;
     for (unsigned long long base = (unsigned long long)blockIdx.x * blockDim.x; base < n4; base += stride) {
         const unsigned long long j = base + threadIdx.x;
-        mcsim_rng::u32x4 c = {unsigned(j), a.stream_id, unsigned(2 * a.t + 1) | unsigned((j >> 32) << 16), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
+        mcsim_rng::u32x4 c = {unsigned(j), m.stream_id, unsigned(2 * a.t + 1) | unsigned((j >> 32) << 16), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
         c = mcsim_rng::philox4x32_10(c, a.k0, a.k1);
         const unsigned w[4] = {c.x, c.y, c.z, c.w};
 #pragma unroll
@@ -173,34 +188,35 @@ __global__ void __launch_bounds__(256) gmm_count_kernel(const GmmLaunch a_in) {
         }
     }
     __syncthreads();
-    if (threadIdx.x < a.K && s_hist[threadIdx.x]) atomicAdd(&a.hist[threadIdx.x], s_hist[threadIdx.x]);
+    if (threadIdx.x < a.K && s_hist[threadIdx.x]) atomicAdd(&m.hist[threadIdx.x], s_hist[threadIdx.x]);
 }
 
 // ---- sample -> collide -> moments -------------------------------------------------------------------------------
 template <int MODE>
 __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
-    const GmmLaunch a = gmm_member(a_in, blockIdx.y);
+    const GmmLaunch& a = a_in;
+    const GmmMember m = gmm_member(a_in, blockIdx.y);
     __shared__ double s_comp[MCSIM_MAX_GAUSSIANS][GMM_COMP];
     __shared__ double s_stat[MCSIM_MAX_GAUSSIANS][GMM_STAT];
     __shared__ unsigned long long s_prefix[MCSIM_MAX_GAUSSIANS + 1];
     __shared__ unsigned char s_ccnt[MCSIM_MAX_HULLS * MC_CULL_LEVELS];
     __shared__ ushort2 s_cidx[MCSIM_MAX_HULLS * MC_CULL_CAP];
     const int K = a.K;
-    if (MODE != MCSIM_MODE_REPLAY && a.cull) {
+    if (MODE != MCSIM_MODE_REPLAY && m.cull) {
         const int nh = c_scene.n_hulls;
-        const unsigned char* gc = reinterpret_cast<const unsigned char*>(a.cull) + size_t(a.t) * nh * MC_CULL_LEVELS;
-        const ushort2* gi = reinterpret_cast<const ushort2*>(a.cull + (size_t(a.T) * nh * MC_CULL_LEVELS + 3) / 4) + size_t(a.t) * nh * MC_CULL_CAP;
+        const unsigned char* gc = reinterpret_cast<const unsigned char*>(m.cull) + size_t(a.t) * nh * MC_CULL_LEVELS;
+        const ushort2* gi = reinterpret_cast<const ushort2*>(m.cull + (size_t(a.T) * nh * MC_CULL_LEVELS + 3) / 4) + size_t(a.t) * nh * MC_CULL_CAP;
         for (int i = threadIdx.x; i < nh * MC_CULL_LEVELS; i += blockDim.x) s_ccnt[i] = gc[i];
         for (int i = threadIdx.x; i < nh * MC_CULL_CAP; i += blockDim.x) s_cidx[i] = gi[i];
     }
     unsigned long long my_tests = 0;
-    for (int i = threadIdx.x; i < K * GMM_COMP; i += blockDim.x) s_comp[i / GMM_COMP][i % GMM_COMP] = a.comps[i];
+    for (int i = threadIdx.x; i < K * GMM_COMP; i += blockDim.x) s_comp[i / GMM_COMP][i % GMM_COMP] = m.comps[i];
     for (int i = threadIdx.x; i < K * GMM_STAT; i += blockDim.x) s_stat[i / GMM_STAT][i % GMM_STAT] = 0.0;
     if (threadIdx.x == 0) {
         unsigned long long acc = 0;
         for (int g = 0; g < K; ++g) {
             s_prefix[g] = acc;
-            acc += (MODE == MCSIM_MODE_REPLAY) ? (unsigned long long)a.counts_replay[a.t * K + g] : (unsigned long long)a.hist[g];
+            acc += (MODE == MCSIM_MODE_REPLAY) ? (unsigned long long)a.counts_replay[a.t * K + g] : (unsigned long long)m.hist[g];
         }
         s_prefix[K] = acc;
     }
@@ -258,7 +274,7 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
             if (MODE == MCSIM_MODE_REPLAY) {
                 z0 = a.normals[3 * i]; z1 = a.normals[3 * i + 1]; z2 = a.normals[3 * i + 2];
             } else {
-                mcsim_rng::u32x4 c = {unsigned(i), a.stream_id, unsigned(2 * a.t) | unsigned((i >> 32) << 16), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
+                mcsim_rng::u32x4 c = {unsigned(i), m.stream_id, unsigned(2 * a.t) | unsigned((i >> 32) << 16), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
                 c = mcsim_rng::philox4x32_10(c, a.k0, a.k1);
                 float f0, f1, f2, f3;
                 mcsim_rng::box_muller(c.x, c.y, f0, f1);
@@ -287,8 +303,8 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
         if (MODE != MCSIM_MODE_REPLAY) {
             // warp-uniform choice of the candidate list by the warp's largest deviation from x*_t (exact: sat_device.cuh)
             int lev = MC_CULL_LEVELS;
-            if (a.cull) {
-                const float2 nom = __ldg(a.nominal + a.t);
+            if (m.cull) {
+                const float2 nom = __ldg(m.nominal + a.t);
                 const float ex = xf - nom.x, ey = yf - nom.y;
                 const float dm = __uint_as_float(__reduce_max_sync(0xffffffffu, valid ? __float_as_uint(fmaf(ex, ex, ey * ey)) : 0u));
                 lev = cull_level(dm);
@@ -320,7 +336,7 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
     __syncthreads();
     for (int i = threadIdx.x; i < K * GMM_STAT; i += blockDim.x) {
         const double v = s_stat[i / GMM_STAT][i % GMM_STAT];
-        if (v != 0.0) atomicAdd(&a.stats[i], v);
+        if (v != 0.0) atomicAdd(&m.stats[i], v);
     }
     if (MODE != MCSIM_MODE_REPLAY && a.tests) {
 #pragma unroll
@@ -457,7 +473,8 @@ __device__ __forceinline__ void gmm_philox_pass2(unsigned stream_id, unsigned ct
 }
 
 __global__ void __launch_bounds__(256) gmm_sample_philox_kernel(const GmmLaunch a_in) {
-    const GmmLaunch a = gmm_member(a_in, blockIdx.y);
+    const GmmLaunch& a = a_in;
+    const GmmMember m = gmm_member(a_in, blockIdx.y);
     __shared__ float s_mu[MCSIM_MAX_GAUSSIANS][3];
     __shared__ float s_L[MCSIM_MAX_GAUSSIANS][6];
     __shared__ double s_stat[MCSIM_MAX_GAUSSIANS][GMM_STAT];
@@ -465,19 +482,19 @@ __global__ void __launch_bounds__(256) gmm_sample_philox_kernel(const GmmLaunch 
     __shared__ unsigned char s_ccnt[MCSIM_MAX_HULLS * MC_CULL_LEVELS];
     __shared__ ushort2 s_cidx[MCSIM_MAX_HULLS * MC_CULL_CAP];
     const int K = a.K;
-    if (a.cull) {
+    if (m.cull) {
         const int nh = c_scene.n_hulls;
-        const unsigned char* gc = reinterpret_cast<const unsigned char*>(a.cull) + size_t(a.t) * nh * MC_CULL_LEVELS;
-        const ushort2* gi = reinterpret_cast<const ushort2*>(a.cull + (size_t(a.T) * nh * MC_CULL_LEVELS + 3) / 4) + size_t(a.t) * nh * MC_CULL_CAP;
+        const unsigned char* gc = reinterpret_cast<const unsigned char*>(m.cull) + size_t(a.t) * nh * MC_CULL_LEVELS;
+        const ushort2* gi = reinterpret_cast<const ushort2*>(m.cull + (size_t(a.T) * nh * MC_CULL_LEVELS + 3) / 4) + size_t(a.t) * nh * MC_CULL_CAP;
         for (int i = threadIdx.x; i < nh * MC_CULL_LEVELS; i += blockDim.x) s_ccnt[i] = gc[i];
         for (int i = threadIdx.x; i < nh * MC_CULL_CAP; i += blockDim.x) s_cidx[i] = gi[i];
     }
-    for (int i = threadIdx.x; i < K * 3; i += blockDim.x) s_mu[i / 3][i % 3] = float(a.comps[(i / 3) * GMM_COMP + 1 + i % 3]);
-    for (int i = threadIdx.x; i < K * 6; i += blockDim.x) s_L[i / 6][i % 6] = float(a.comps[(i / 6) * GMM_COMP + 13 + i % 6]);
+    for (int i = threadIdx.x; i < K * 3; i += blockDim.x) s_mu[i / 3][i % 3] = float(m.comps[(i / 3) * GMM_COMP + 1 + i % 3]);
+    for (int i = threadIdx.x; i < K * 6; i += blockDim.x) s_L[i / 6][i % 6] = float(m.comps[(i / 6) * GMM_COMP + 13 + i % 6]);
     for (int i = threadIdx.x; i < K * GMM_STAT; i += blockDim.x) s_stat[i / GMM_STAT][i % GMM_STAT] = 0.0;
     if (threadIdx.x == 0) {
         unsigned acc = 0;
-        for (int g = 0; g < K; ++g) { s_prefix[g] = acc; acc += a.hist[g]; }
+        for (int g = 0; g < K; ++g) { s_prefix[g] = acc; acc += m.hist[g]; }
         s_prefix[K] = acc;
     }
     __syncthreads();
@@ -487,17 +504,17 @@ __global__ void __launch_bounds__(256) gmm_sample_philox_kernel(const GmmLaunch 
     GmmAcc acc;
     const unsigned n = unsigned(s_prefix[K] < a.n ? s_prefix[K] : a.n);  // Philox mode: n <= 2^31 (checked on the host)
     const unsigned stride = gridDim.x * blockDim.x;
-    const float2 nom = a.cull ? __ldg(a.nominal + a.t) : make_float2(0.f, 0.f);
+    const float2 nom = m.cull ? __ldg(m.nominal + a.t) : make_float2(0.f, 0.f);
     // two samples per thread and pass; a.spread (small sample counts, one run): one per thread, the second lane idle,
     // so that twice as many warps share the waypoint's latency
     const unsigned per = a.spread ? 1u : 2u;
     for (unsigned base = per * blockIdx.x * blockDim.x; base < n; base += per * stride)
-        gmm_philox_pass2(a.stream_id, unsigned(2 * a.t), a.k0, a.k1, base + per * threadIdx.x, a.spread ? 0xffffffffu : base + per * threadIdx.x + 1, n, K, g, s_prefix, s_mu, s_L, s_stat, a.sat2, s_ccnt, s_cidx, a.cull != nullptr, nom, acc, my_tests);
+        gmm_philox_pass2(m.stream_id, unsigned(2 * a.t), a.k0, a.k1, base + per * threadIdx.x, a.spread ? 0xffffffffu : base + per * threadIdx.x + 1, n, K, g, s_prefix, s_mu, s_L, s_stat, a.sat2, s_ccnt, s_cidx, m.cull != nullptr, nom, acc, my_tests);
     acc.flush(s_stat);
     __syncthreads();
     for (int i = threadIdx.x; i < K * GMM_STAT; i += blockDim.x) {
         const double v = s_stat[i / GMM_STAT][i % GMM_STAT];
-        if (v != 0.0) atomicAdd(&a.stats[i], v);
+        if (v != 0.0) atomicAdd(&m.stats[i], v);
     }
     if (a.tests) {
         unsigned long long t64 = my_tests;
@@ -544,7 +561,7 @@ __device__ __forceinline__ void gmm_refit_moments(double* cp, const double* st, 
     }
 }
 // Part 2 (after every component's part 1): weight, p_t, records, EKFpredict + EKFupdate to waypoint t+1, Cholesky.
-__device__ __forceinline__ void gmm_refit_finish(const GmmLaunch& a, int t, int g, double* cp, const double* s_free, const double* s_coll,
+__device__ __forceinline__ void gmm_refit_finish(const GmmLaunch& a, const GmmMember& m, int t, int g, double* cp, const double* s_free, const double* s_coll,
                                                  const GmmStepTable* staged_step = nullptr) {
     using namespace mcsim_math;
     const int K = a.K;
@@ -552,19 +569,16 @@ __device__ __forceinline__ void gmm_refit_finish(const GmmLaunch& a, int t, int 
     for (int k = 0; k < K; ++k) { tf += s_free[k]; tc += s_coll[k]; }
     // normalise(collisionCounts, 1, 1).row(1): divides by the row's 1-norm, or by 1 if that is 0
     cp[0] = s_free[g] / (tf > 0 ? tf : 1.0);
-    if (g == 0) a.probabilities[t] = tc / double(a.n);
+    if (g == 0) m.probabilities[t] = tc / double(a.n);
     if (a.n_out) { a.n_out[g] = (unsigned long long)s_coll[g]; a.n_out[K + g] = (unsigned long long)s_free[g]; }
     if (a.trunc_out) for (int k = 0; k < GMM_REC; ++k) a.trunc_out[g * GMM_REC + k] = cp[k];
     if (t == a.T - 1 && a.rec_post) for (int k = 0; k < GMM_REC; ++k) a.rec_post[g * GMM_REC + k] = cp[k];
     // ---- move the component to waypoint t+1: EKFpredict (:766-772) then EKFupdate (:804-812)
     if (a.do_ekf && t < a.T - 1) {
-        const GmmStepTable& s = staged_step ? *staged_step : a.steps[t];
-        NoiseModel<double> nm;
-        nm.Q = a.Q; nm.L = a.L;
-        for (int l = 0; l < a.L; ++l) { nm.lx[l] = a.lx[l]; nm.ly[l] = a.ly[l]; }
+        const GmmStepTable& s = staged_step ? *staged_step : m.steps[t];
         double pmu[3], pS[9];
         ekf_predict(cp + 1, cp + 4, s.u, s.M, pmu, pS);
-        ekf_update(nm, pmu, pS, s.z, a.L);
+        for (int l = 0; l < a.L; ++l) ekf_update_one(a.lx[l], a.ly[l], a.Q, pmu, pS, s.z[l]);   // landmarks straight from the launch struct
         for (int k = 0; k < 3; ++k) cp[1 + k] = pmu[k];
         for (int k = 0; k < 9; ++k) cp[4 + k] = pS[k];
         if (a.rec_pre) for (int k = 0; k < GMM_REC; ++k) a.rec_pre[(size_t(t + 1) * K + g) * GMM_REC + k] = cp[k];
@@ -572,7 +586,7 @@ __device__ __forceinline__ void gmm_refit_finish(const GmmLaunch& a, int t, int 
     if (!gmm_chol3(cp + 4, cp + 13)) {
         // not SPD (the reference falls back to an eigen-decomposition, glue_mvnrnd_meat.hpp:98-132):
         // sample from the diagonal instead and count the event
-        atomicAdd(a.degenerate, 1);
+        atomicAdd(m.degenerate, 1);
         cp[13] = sqrt(fmax(cp[4], 0.0)); cp[14] = 0; cp[15] = sqrt(fmax(cp[8], 0.0));
         cp[16] = 0; cp[17] = 0; cp[18] = sqrt(fmax(cp[12], 0.0));
     }
@@ -581,29 +595,30 @@ __device__ __forceinline__ void gmm_refit_finish(const GmmLaunch& a, int t, int 
 // The mixture, the statistics and the step record are staged in shared memory first: the refit is one long dependent
 // FP64 chain per component, and every read-modify-write of the record in global memory was a round trip to L2 on it.
 __global__ void __launch_bounds__(32) gmm_refit_kernel(const GmmLaunch a_in) {
-    const GmmLaunch a = gmm_member(a_in, blockIdx.x);
+    const GmmLaunch& a = a_in;
+    const GmmMember m = gmm_member(a_in, blockIdx.x);
     __shared__ double s_free[MCSIM_MAX_GAUSSIANS], s_coll[MCSIM_MAX_GAUSSIANS];
     __shared__ double s_cp[MCSIM_MAX_GAUSSIANS * GMM_COMP], s_st[MCSIM_MAX_GAUSSIANS * GMM_STAT];
     __shared__ GmmStepTable s_step;
     const int g = threadIdx.x;
     const int K = a.K;
     const bool ekf = a.do_ekf && a.t < a.T - 1;
-    for (int i = g; i < K * GMM_COMP; i += 32) s_cp[i] = a.comps[i];
-    for (int i = g; i < K * GMM_STAT; i += 32) s_st[i] = a.stats[i];
+    for (int i = g; i < K * GMM_COMP; i += 32) s_cp[i] = m.comps[i];
+    for (int i = g; i < K * GMM_STAT; i += 32) s_st[i] = m.stats[i];
     if (ekf) {
-        const double* src = reinterpret_cast<const double*>(a.steps + a.t);
+        const double* src = reinterpret_cast<const double*>(m.steps + a.t);
         double* dst = reinterpret_cast<double*>(&s_step);
         for (int i = g; i < int(sizeof(GmmStepTable) / sizeof(double)); i += 32) dst[i] = src[i];
     }
     __syncthreads();
     double* cp = s_cp + g * GMM_COMP;
-    if (g < K) gmm_refit_moments(cp, s_st + g * GMM_STAT, a.degenerate, s_free[g], s_coll[g]);
+    if (g < K) gmm_refit_moments(cp, s_st + g * GMM_STAT, m.degenerate, s_free[g], s_coll[g]);
     __syncthreads();
-    if (g < K) gmm_refit_finish(a, a.t, g, cp, s_free, s_coll, ekf ? &s_step : nullptr);
+    if (g < K) gmm_refit_finish(a, m, a.t, g, cp, s_free, s_coll, ekf ? &s_step : nullptr);
     __syncthreads();
-    for (int i = g; i < K * GMM_COMP; i += 32) a.comps[i] = s_cp[i];
-    for (int i = g; i < K * GMM_STAT; i += 32) a.stats[i] = 0.0;
-    if (g < K) a.hist[g] = 0;
+    for (int i = g; i < K * GMM_COMP; i += 32) m.comps[i] = s_cp[i];
+    for (int i = g; i < K * GMM_STAT; i += 32) m.stats[i] = 0.0;
+    if (g < K) m.hist[g] = 0;
 }
 
 // ---- batch: ONE CTA runs ONE member's whole runGMMEstimation (all T waypoints) ---------------------------------------
@@ -626,14 +641,15 @@ __global__ void __launch_bounds__(256, GMM_FUSED_CTAS) gmm_member_run_kernel(con
     __shared__ float s_cdf[MCSIM_MAX_GAUSSIANS];
     __shared__ unsigned s_hist[MCSIM_MAX_GAUSSIANS];
     __shared__ unsigned s_prefix[MCSIM_MAX_GAUSSIANS + 1];
-    const GmmLaunch a = gmm_member(a_in, blockIdx.x);
+    const GmmLaunch& a = a_in;
+    const GmmMember m = gmm_member(a_in, blockIdx.x);
     const int K = a.K, T = a.T, nh = c_scene.n_hulls;
-    const unsigned stream_id = a.stream_id, k0 = a.k0, k1 = a.k1, n_all = unsigned(a.n);
-    const bool cull = a.cull != nullptr;
+    const unsigned stream_id = m.stream_id, k0 = a.k0, k1 = a.k1, n_all = unsigned(a.n);
+    const bool cull = m.cull != nullptr;
     unsigned* s_cull = reinterpret_cast<unsigned*>(s_tab + sat2_n);
     for (int i = threadIdx.x; i < sat2_n; i += blockDim.x) s_tab[i] = a.sat2[i];
-    if (cull) for (int i = threadIdx.x; i < cull_words; i += blockDim.x) s_cull[i] = a.cull[i];
-    for (int i = threadIdx.x; i < K * GMM_COMP; i += blockDim.x) s_comp[i / GMM_COMP][i % GMM_COMP] = a.comps[i];
+    if (cull) for (int i = threadIdx.x; i < cull_words; i += blockDim.x) s_cull[i] = m.cull[i];
+    for (int i = threadIdx.x; i < K * GMM_COMP; i += blockDim.x) s_comp[i / GMM_COMP][i % GMM_COMP] = m.comps[i];
     for (int i = threadIdx.x; i < K * GMM_STAT; i += blockDim.x) s_stat[i / GMM_STAT][i % GMM_STAT] = 0.0;
     if (threadIdx.x < MCSIM_MAX_GAUSSIANS) s_hist[threadIdx.x] = 0;
     const unsigned char* s_ccnt = reinterpret_cast<const unsigned char*>(s_cull);
@@ -702,7 +718,7 @@ __global__ void __launch_bounds__(256, GMM_FUSED_CTAS) gmm_member_run_kernel(con
             int g = 0;
             GmmAcc acc;
             const unsigned n = s_prefix[K] < n_all ? s_prefix[K] : n_all;
-            const float2 nom = cull ? __ldg(a.nominal + t) : make_float2(0.f, 0.f);
+            const float2 nom = cull ? __ldg(m.nominal + t) : make_float2(0.f, 0.f);
             const unsigned char* cc = s_ccnt + t * nh * MC_CULL_LEVELS;
             const ushort2* ci = s_cidx + t * nh * MC_CULL_CAP;
             for (unsigned base = 0; base < n; base += 2 * blockDim.x)   // two samples per thread and pass
@@ -712,10 +728,10 @@ __global__ void __launch_bounds__(256, GMM_FUSED_CTAS) gmm_member_run_kernel(con
         __syncthreads();
         // ---- refit + propagate (gmm_refit_kernel)
         const int g = threadIdx.x;
-        if (g < K) gmm_refit_moments(s_comp[g], s_stat[g], a.degenerate, s_free[g], s_coll[g]);
+        if (g < K) gmm_refit_moments(s_comp[g], s_stat[g], m.degenerate, s_free[g], s_coll[g]);
         __syncthreads();
         if (g < K) {
-            gmm_refit_finish(a, t, g, s_comp[g], s_free, s_coll);
+            gmm_refit_finish(a, m, t, g, s_comp[g], s_free, s_coll);
             for (int k = 0; k < GMM_STAT; ++k) s_stat[g][k] = 0.0;
             s_hist[g] = 0;
         }
@@ -763,15 +779,16 @@ __global__ void __launch_bounds__(GMM_CLUSTER_THREADS, 1) gmm_cluster_run_kernel
     __shared__ unsigned s_hpart[GMM_CLUSTER_MAX][MCSIM_MAX_GAUSSIANS];           // slot r: rank r's counts (written remotely)
     __shared__ unsigned s_prefix[MCSIM_MAX_GAUSSIANS + 1];
     __shared__ int s_sink;
-    GmmLaunch a = gmm_member(a_in, blockIdx.x / CL);
-    if (rank) a.degenerate = &s_sink;
+    const GmmLaunch& a = a_in;
+    GmmMember m = gmm_member(a_in, blockIdx.x / CL);
+    if (rank) m.degenerate = &s_sink;
     const int K = a.K, T = a.T, nh = c_scene.n_hulls;
-    const unsigned stream_id = a.stream_id, k0 = a.k0, k1 = a.k1, n_all = unsigned(a.n);
-    const bool cull = a.cull != nullptr;
+    const unsigned stream_id = m.stream_id, k0 = a.k0, k1 = a.k1, n_all = unsigned(a.n);
+    const bool cull = m.cull != nullptr;
     unsigned* s_cull = reinterpret_cast<unsigned*>(s_tab + sat2_n);
     for (int i = threadIdx.x; i < sat2_n; i += blockDim.x) s_tab[i] = a.sat2[i];
-    if (cull) for (int i = threadIdx.x; i < cull_words; i += blockDim.x) s_cull[i] = a.cull[i];
-    for (int i = threadIdx.x; i < K * GMM_COMP; i += blockDim.x) s_comp[i / GMM_COMP][i % GMM_COMP] = a.comps[i];
+    if (cull) for (int i = threadIdx.x; i < cull_words; i += blockDim.x) s_cull[i] = m.cull[i];
+    for (int i = threadIdx.x; i < K * GMM_COMP; i += blockDim.x) s_comp[i / GMM_COMP][i % GMM_COMP] = m.comps[i];
     for (int i = threadIdx.x; i < MCSIM_MAX_GAUSSIANS * GMM_STAT; i += blockDim.x) (&s_stat[0][0])[i] = 0.0;
     if (threadIdx.x < MCSIM_MAX_GAUSSIANS) s_hist[threadIdx.x] = 0;
     const unsigned char* s_ccnt = reinterpret_cast<const unsigned char*>(s_cull);
@@ -863,7 +880,7 @@ __global__ void __launch_bounds__(GMM_CLUSTER_THREADS, 1) gmm_cluster_run_kernel
             int g = 0;
             GmmAcc acc;
             const unsigned n = s_prefix[K] < n_all ? s_prefix[K] : n_all;
-            const float2 nom = cull ? __ldg(a.nominal + t) : make_float2(0.f, 0.f);
+            const float2 nom = cull ? __ldg(m.nominal + t) : make_float2(0.f, 0.f);
             const unsigned char* cc = s_ccnt + t * nh * MC_CULL_LEVELS;
             const ushort2* ci = s_cidx + t * nh * MC_CULL_CAP;
             for (unsigned base = 2 * blockDim.x * rank; base < n; base += 2 * blockDim.x * CL)
@@ -886,11 +903,11 @@ __global__ void __launch_bounds__(GMM_CLUSTER_THREADS, 1) gmm_cluster_run_kernel
         __syncthreads();
         // ---- refit, redundantly in every CTA: moments and weights first ...
         const int g = threadIdx.x;
-        if (g < K) gmm_refit_moments(s_comp[g], s_tot[g], a.degenerate, s_free[g], s_coll[g]);
+        if (g < K) gmm_refit_moments(s_comp[g], s_tot[g], m.degenerate, s_free[g], s_coll[g]);
         __syncthreads();
         // ... then warp 0 walks the EKF chain to waypoint t + 1 while the other warps draw that waypoint's counts
         if (threadIdx.x < 32) {
-            if (g < K) gmm_refit_finish(a, t, g, s_comp[g], s_free, s_coll);
+            if (g < K) gmm_refit_finish(a, m, t, g, s_comp[g], s_free, s_coll);
         } else if (t + 1 < T) {
             count_waypoint(t + 1);
         }

@@ -898,11 +898,12 @@ static int gmm_launch_waypoint(mcsim_cuda_ctx* c, const GmmLaunch& a_in, int mod
 // one thread-block cluster per run for the whole plan (gmm_cluster_run_kernel): single runs and small batches in
 // Philox mode whose samples per waypoint are a few passes of a cluster; larger sample counts keep the per-waypoint
 // kernels (the whole GPU per waypoint), batches that fill the GPU by themselves the one-CTA-per-member kernel
-#define GMM_CLUSTER_MAX_SAMPLES 32768ull
-static bool gmm_cluster_fits(const mcsim_cuda_ctx* c, uint64_t n_samples, int n_runs) {
-    if (getenv("MCSIM_GMM_NO_CLUSTER")) return false;
+#define GMM_CLUSTER_MAX_SAMPLES 98304ull   // measured switch-over (tools/gmm_quick.py sweep, B200): 65,536: 1.18 vs 1.41 ms; 131,072: 1.62 vs 1.46 ms
+static bool gmm_cluster_fits(const mcsim_cuda_ctx* c, uint64_t n_samples, int n_runs, int kernel_choice) {
+    if (kernel_choice == MCSIM_GMM_KERNEL_PER_WAYPOINT) return false;
     const size_t smem = sizeof(float4) * size_t(c->sat2_n) + sizeof(unsigned) * size_t(c->gmm_cull_words);
-    return n_samples <= GMM_CLUSTER_MAX_SAMPLES && smem <= 64 * 1024 && n_runs >= 1 && n_runs < 64;
+    const uint64_t most = kernel_choice == MCSIM_GMM_KERNEL_CLUSTER ? (1ull << 31) : GMM_CLUSTER_MAX_SAMPLES;   // forced: any size
+    return n_samples <= most && smem <= 64 * 1024 && n_runs >= 1 && n_runs < 64;
 }
 static int gmm_launch_cluster(mcsim_cuda_ctx* c, const GmmLaunch& a, int n_runs) {
     SymbolLock sym;
@@ -1026,7 +1027,7 @@ extern "C" int mcsim_cuda_gmm_run(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, 
     if (mode == MCSIM_MODE_PHILOX) { rc = gmm_upload_cull(c, a, mc->trajectory, 1, T, mc->exhaustive != 0); if (rc) return rc; }
     CK(cudaEventRecord(c->ev0, c->stream));
     rc = -1;
-    if (mode == MCSIM_MODE_PHILOX && gmm_cluster_fits(c, N, 1)) {
+    if (mode == MCSIM_MODE_PHILOX && gmm_cluster_fits(c, N, 1, g->kernel)) {
         a.t = 0;
         rc = gmm_launch_cluster(c, a, 1);
         if (rc > 0) return rc;
@@ -1466,9 +1467,6 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
     if (L < 0 || L > MCSIM_MAX_LANDMARKS || (L && !mc->landmarks)) return fail(MCSIM_ERR_ARG, "gmm_run_batch: bad landmarks");
     if ((g->trajectories == nullptr) != (g->odometry == nullptr)) return fail(MCSIM_ERR_ARG, "gmm_run_batch: trajectories and odometry go together");
     CK(cudaSetDevice(c->device));
-    const bool trace = getenv("MCSIM_TRACE") != nullptr;
-    auto now = []() { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
-    const double t_0 = now();
     const int per_step = 3 + L, TS = T > 1 ? T - 1 : 1;
     double Lo[6];
     if (!gmm_chol3(mc->cov0, Lo)) return fail(MCSIM_ERR_ARG, "gmm_run_batch: initial covariance is not positive definite");
@@ -1503,7 +1501,6 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
         ++c->launches;
         CK(cudaGetLastError());
     }
-    const double t_1 = now();
     GmmLaunch a;
     gmm_fill_launch(c, a, K, T, L, N, mc->seed, unsigned(g->stream0));
     a.Q = mc->Q;
@@ -1513,12 +1510,11 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
     rc = g->trajectories ? gmm_upload_cull(c, a, g->trajectories, B, T, mc->exhaustive != 0)
                          : gmm_upload_cull(c, a, mc->trajectory, 1, T, mc->exhaustive != 0);
     if (rc) return rc;
-    const double t_2 = now();
     if (N > (1ull << 31)) return fail(MCSIM_ERR_ARG, "gmm_run_batch: at most 2^31 samples per waypoint");
     // enough members to fill the GPU by themselves: one CTA per member for the whole run (gmm_member_run_kernel);
     // fewer: the per-waypoint kernels, several CTAs per member
     const size_t fused_smem = sizeof(float4) * size_t(c->sat2_n) + sizeof(unsigned) * size_t(c->gmm_cull_words);
-    const bool fused = B >= 64 && fused_smem <= 64 * 1024;
+    const bool fused = B >= 64 && fused_smem <= 64 * 1024 && g->kernel == MCSIM_GMM_KERNEL_AUTO;
     CK(cudaEventRecord(c->ev0, c->stream));
     if (fused) {
         SymbolLock sym;
@@ -1529,7 +1525,7 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
         CK(cudaGetLastError());
     } else {
         rc = -1;
-        if (gmm_cluster_fits(c, N, B)) {
+        if (gmm_cluster_fits(c, N, B, g->kernel)) {
             a.t = 0;
             rc = gmm_launch_cluster(c, a, B);
             if (rc > 0) return rc;
@@ -1541,7 +1537,6 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
         }
     }
     CK(cudaEventRecord(c->ev1, c->stream));
-    const double t_3 = now();
     std::vector<double> prob(size_t(B) * T);
     std::vector<int> deg(B);
     CK(cudaMemcpyAsync(prob.data(), c->gmm_prob.p, sizeof(double) * prob.size(), cudaMemcpyDeviceToHost, c->stream));
@@ -1549,7 +1544,6 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
     unsigned long long tests = 0;
     CK(cudaMemcpyAsync(&tests, a.tests, sizeof(tests), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
-    if (trace) fprintf(stderr, "[mcsim] gmm_run_batch B=%d: plans + robot-thread launch %.3f ms, lists %.3f ms, launch %.3f ms, wait + download %.3f ms\n", B, t_1 - t_0, t_2 - t_1, t_3 - t_2, now() - t_3);
     r->pair_tests = tests;
     c->d2h_bytes = sizeof(double) * prob.size() + sizeof(int) * B + sizeof(tests);
     CK(cudaEventElapsedTime(&r->kernel_ms, c->ev0, c->ev1));

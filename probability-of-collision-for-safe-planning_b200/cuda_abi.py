@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libmcsim_cuda.so")
 MAX_GAUSSIANS = 16
 MAX_WAYPOINTS = 1024
 MODE_REPLAY, MODE_PHILOX = 0, 1
+GMM_KERNEL_AUTO, GMM_KERNEL_PER_WAYPOINT, GMM_KERNEL_CLUSTER = 0, 1, 2
 EST_REFERENCE, EST_CLOSEDLOOP = 0, 1
 
 _dp = C.POINTER(C.c_double)
@@ -59,7 +60,7 @@ class EmResult(C.Structure):
 
 class GmmBatchParams(C.Structure):
     _fields_ = [("K", C.c_int), ("n_samples", C.c_uint64), ("n_traj", C.c_int), ("trajectories", _dp), ("odometry", _dp),
-                ("stream0", C.c_uint64)]
+                ("stream0", C.c_uint64), ("kernel", C.c_int)]
 
 
 class GmmBatchResult(C.Structure):
@@ -102,7 +103,7 @@ class GmmTruncateResult(C.Structure):
 class GmmRunParams(C.Structure):
     _fields_ = [
         ("K", C.c_int), ("n_samples", C.c_uint64), ("normals", _dp), ("n_normals", C.c_size_t),
-        ("counts", C.POINTER(C.c_int)),
+        ("counts", C.POINTER(C.c_int)), ("kernel", C.c_int),
     ]
 
 
@@ -384,13 +385,13 @@ class Context:
         return int(a.value), int(b.value)
 
     def gmm_run(self, plan, K, n_samples, mode=MODE_PHILOX, seed=0x5AFEC0DE, stream_id=0, draws=None, counts=None,
-                record=False, exhaustive=False):
+                record=False, exhaustive=False, kernel=GMM_KERNEL_AUTO):
         """runGMMEstimation of one plan (MCSimulator.h:354-358 -> the GMM branch of EKF_GaussProp).
         Replay mode: draws = the reference's normal stream of the run, counts[T, K] = multinomial counts."""
         p, keep = make_mc_params(plan, mode=mode, seed=seed, rollout_offset=stream_id, exhaustive=exhaustive)
         T = int(p.T)
         g = GmmRunParams()
-        g.K, g.n_samples = int(K), int(n_samples)
+        g.K, g.n_samples, g.kernel = int(K), int(n_samples), int(kernel)
         if draws is not None:
             dr = np.ascontiguousarray(draws, dtype=np.float64)
             keep.append(dr)
@@ -524,13 +525,13 @@ class Context:
         return torch.as_tensor(raw, device="cuda:%d" % self.device)
 
     def gmm_run_batch(self, plan, K, n_samples, n_traj, trajectories=None, odometry=None, seed=0x5AFEC0DE, stream0=0,
-                      exhaustive=False):
+                      exhaustive=False, kernel=GMM_KERNEL_AUTO):
         """n_traj independent runGMMEstimation runs in the same launches (Philox mode); member b ==
         gmm_run(..., stream_id=stream0 + b) on plan b (trajectories [n_traj, 3, T]) or on `plan`."""
         p, keep = make_mc_params(plan, mode=MODE_PHILOX, seed=seed, exhaustive=exhaustive)
         T = int(p.T)
         g = GmmBatchParams()
-        g.K, g.n_samples, g.n_traj, g.stream0 = int(K), int(n_samples), int(n_traj), int(stream0)
+        g.K, g.n_samples, g.n_traj, g.stream0, g.kernel = int(K), int(n_samples), int(n_traj), int(stream0), int(kernel)
         if trajectories is not None:
             tr = np.ascontiguousarray(trajectories, dtype=np.float64)
             od = np.ascontiguousarray(odometry, dtype=np.float64)

@@ -241,7 +241,7 @@ def test_gmm_batch_fused_kernel_edge_cases(ctx, plan, scenes, K, N):
 @pytest.mark.parametrize("K,N", [(3, 10000), (1, 10001), (16, 3000), (2, 100), (3, 32768)])
 def test_gmm_cluster_kernel_equals_per_waypoint_kernels(ctx, plan, scenes, K, N, monkeypatch):
     """One-cluster-per-run kernel (single runs and batches below 64 in Philox mode, N <= 32,768) against the
-    per-waypoint kernels (MCSIM_GMM_NO_CLUSTER=1 keeps them): same Philox draws per sample index, FP64 sums in a
+    per-waypoint kernels (mcsim_gmm_run_params.kernel = MCSIM_GMM_KERNEL_PER_WAYPOINT keeps them): same Philox draws per sample index, FP64 sums in a
     different order -> per-waypoint fractions, recorded mixtures and P to 1e-9.  Cases: the reference's default, a
     sample count that is no multiple of 4, the maximum component count, so few samples that most CTAs of the cluster
     idle and components starve, the largest routed sample count; a two-waypoint plan; a batch on 8-CTA clusters."""
@@ -252,20 +252,16 @@ def test_gmm_cluster_kernel_equals_per_waypoint_kernels(ctx, plan, scenes, K, N,
     short["trajectory"] = plan["trajectory"][:, :2]
     short["odometry"] = plan["odometry"][:, :1]
     for pl in (plan, short):
-        monkeypatch.delenv("MCSIM_GMM_NO_CLUSTER", raising=False)
         a = ctx.gmm_run(pl, K, N, mode=abi.MODE_PHILOX, stream_id=21, record=True)
-        monkeypatch.setenv("MCSIM_GMM_NO_CLUSTER", "1")
-        b = ctx.gmm_run(pl, K, N, mode=abi.MODE_PHILOX, stream_id=21, record=True)
+        b = ctx.gmm_run(pl, K, N, mode=abi.MODE_PHILOX, stream_id=21, record=True, kernel=abi.GMM_KERNEL_PER_WAYPOINT)
         np.testing.assert_allclose(a["probabilities"], b["probabilities"], rtol=1e-9, atol=1e-12)
         np.testing.assert_allclose(a["P"], b["P"], rtol=1e-9)
         np.testing.assert_allclose(a["gmm_pre"], b["gmm_pre"], rtol=1e-7, atol=1e-12)
         np.testing.assert_allclose(a["gmm_post"], b["gmm_post"], rtol=1e-7, atol=1e-12)
         assert a["degenerate"] == b["degenerate"]
-    monkeypatch.delenv("MCSIM_GMM_NO_CLUSTER", raising=False)
     batch = ctx.gmm_run_batch(plan, K, N, 12, stream0=40)       # 12 runs: 8 CTAs per cluster
-    monkeypatch.setenv("MCSIM_GMM_NO_CLUSTER", "1")
     for b in (0, 11):
-        one = ctx.gmm_run(plan, K, N, mode=abi.MODE_PHILOX, stream_id=40 + b)
+        one = ctx.gmm_run(plan, K, N, mode=abi.MODE_PHILOX, stream_id=40 + b, kernel=abi.GMM_KERNEL_PER_WAYPOINT)
         np.testing.assert_allclose(batch["probabilities"][b], one["probabilities"], rtol=1e-9, atol=1e-12)
 
 
@@ -280,9 +276,7 @@ def test_gmm_cluster_kernel_long_plans(ctx, plan, scenes, T, monkeypatch):
     tr, od = inp.synthetic_plans(5, 1, T, boxes, clear=-0.1)
     long_plan = dict(plan)
     long_plan["trajectory"], long_plan["odometry"] = tr[0], od[0]
-    monkeypatch.delenv("MCSIM_GMM_NO_CLUSTER", raising=False)
     a = ctx.gmm_run(long_plan, 3, 4000, mode=abi.MODE_PHILOX, stream_id=3)
-    monkeypatch.setenv("MCSIM_GMM_NO_CLUSTER", "1")
-    b = ctx.gmm_run(long_plan, 3, 4000, mode=abi.MODE_PHILOX, stream_id=3)
+    b = ctx.gmm_run(long_plan, 3, 4000, mode=abi.MODE_PHILOX, stream_id=3, kernel=abi.GMM_KERNEL_PER_WAYPOINT)
     np.testing.assert_allclose(a["probabilities"], b["probabilities"], rtol=1e-9, atol=1e-12)
     assert a["kernel_ms"] < b["kernel_ms"]
