@@ -158,6 +158,153 @@ __global__ void __launch_bounds__(256) em_estep_kernel(const EmLaunch a) {
     if (G0 == 0 && threadIdx.x == 0) atomicAdd(&st[K * EM_NSTAT], s_acc[NACC - 1]);
 }
 
+// ---- E-step, components split over the warps of a group (K >= 5) ----------------------------------------------------
+// One thread of em_estep_kernel carries 10 accumulators per component: 80 for K = 8 (227 registers, two warps per
+// scheduler), and K = 16 needed a second launch that recomputed all 16 log-likelihoods.  Here S consecutive warps form a
+// group that walks the SAME samples (lane l of every member holds sample l of the group's tile); member w owns the
+// components g = w, w + S, w + 2 S, ... -- their quadratic forms, exponentials and 10 accumulators each.  What the
+// members owe each other is the normaliser of the responsibilities: each writes its partial (max, sum of exponentials)
+// per sample to shared memory, a named barrier over the S warps (bar.sync id, 32 S) makes them visible, and everyone
+// combines them to the log-sum-exp of all K components (gmm_full_meat.hpp:2707-2723).  Per sample and member that is one
+// STS.64, S - 1 LDS.64, S + 1 MUFU and a barrier shared by U samples; the accumulators per thread drop to 10 ceil(K / S),
+// one launch covers any K <= 16, and twice to four times the warps are resident.  Member 0 also sums the log-likelihood.
+template <int K, int S>
+__global__ void __launch_bounds__(256, (K + S - 1) / S <= 2 ? 3 : 2) em_estep_split_kernel(const EmLaunch a) {
+    constexpr int KG = (K + S - 1) / S;   // components per member (strided: counts differ by at most one)
+    constexpr int NG = 8 / S;             // groups per CTA
+    constexpr int U = KG > 6 ? 1 : 2;     // samples per thread between two barriers
+    constexpr int NACC = K * EM_NSTAT + 1;
+    constexpr float LOG2E = 1.4426950408889634f;
+    __shared__ __align__(16) float s_c[K * EM_COMP_STRIDE];
+    __shared__ double s_acc[NACC];
+    __shared__ float2 s_ex[2][8][U][32];  // [round parity][warp][sample of the round][lane]: partial (max, sum)
+    const int fit = blockIdx.y;
+    if (a.done[fit]) return;
+    for (int i = threadIdx.x; i < K * EM_COMP_STRIDE; i += blockDim.x) s_c[i] = a.comps[(size_t)fit * K * EM_COMP_STRIDE + i];
+    for (int i = threadIdx.x; i < NACC; i += blockDim.x) s_acc[i] = 0.0;
+    __syncthreads();
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, grp = warp / S, w = warp % S;
+    const float* xs = a.x + (size_t)fit * 3 * a.n;
+    const float* ys = xs + a.n;
+    const float* ts = ys + a.n;
+    float acc[KG][EM_NSTAT];
+#pragma unroll
+    for (int g = 0; g < KG; ++g)
+#pragma unroll
+        for (int k = 0; k < EM_NSTAT; ++k) acc[g][k] = 0.f;
+    float lsum = 0.f;
+    const unsigned n = unsigned(a.n);
+    const unsigned stride = gridDim.x * NG * 32u;                 // samples per round of the whole grid, per u
+    unsigned i = (blockIdx.x * NG + grp) * 32u + lane;            // sample u of this round: i + u * stride
+    float bx[U], by[U], bt[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        const unsigned k = i + u * stride;
+        const bool ok = k < n;
+        bx[u] = ok ? __ldg(xs + k) : 0.f; by[u] = ok ? __ldg(ys + k) : 0.f; bt[u] = ok ? __ldg(ts + k) : 0.f;
+    }
+    unsigned par = 0;
+    // group-uniform trip count: the first lane of the group decides (all members run the same rounds and barriers)
+    for (unsigned base = (blockIdx.x * NG + grp) * 32u; base < n; base += U * stride, i += U * stride, par ^= 1u) {
+        float cx[U], cy[U], ct[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) { cx[u] = bx[u]; cy[u] = by[u]; ct[u] = bt[u]; }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const unsigned k = i + (U + u) * stride;
+            const bool ok = k < n;
+            bx[u] = ok ? __ldg(xs + k) : 0.f; by[u] = ok ? __ldg(ys + k) : 0.f; bt[u] = ok ? __ldg(ts + k) : 0.f;
+        }
+        float e[U][KG], m[U], sm[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            m[u] = -FLT_MAX;
+#pragma unroll
+            for (int gg = 0; gg < KG; ++gg) {
+                const int g = int(w) + gg * S;
+                if (g < K) {
+                    const float4* c4 = reinterpret_cast<const float4*>(s_c + g * EM_COMP_STRIDE);
+                    const float4 ca = c4[0], cb = c4[1], cc = c4[2];
+                    const float d0 = cx[u] - ca.x, d1 = cy[u] - ca.y, d2 = ct[u] - ca.z;
+                    const float q0 = fmaf(ca.w, d0, fmaf(cb.x, d1, cb.y * d2));
+                    const float q1 = fmaf(cb.z, d1, cb.w * d2);
+                    e[u][gg] = fmaf(d0, q0, fmaf(d1, q1, fmaf(cc.x * d2, d2, cc.y)));
+                    m[u] = fmaxf(m[u], e[u][gg]);
+                } else {
+                    e[u][gg] = -FLT_MAX;
+                }
+            }
+            sm[u] = 0.f;
+#pragma unroll
+            for (int gg = 0; gg < KG; ++gg) {
+                e[u][gg] = exp2f((e[u][gg] - m[u]) * LOG2E);   // a member without component gg: exp2(-huge) = 0
+                sm[u] += e[u][gg];
+            }
+            s_ex[par][warp][u][lane] = make_float2(m[u], sm[u]);
+        }
+        asm volatile("bar.sync %0, %1;" ::"r"(1 + grp), "r"(S * 32) : "memory");
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            float om[S], os[S];
+            float M = m[u];
+#pragma unroll
+            for (int q = 0; q < S; ++q) {
+                const float2 v = s_ex[par][grp * S + q][u][lane];
+                om[q] = v.x; os[q] = v.y;
+                M = fmaxf(M, v.x);
+            }
+            float tot = 0.f;
+#pragma unroll
+            for (int q = 0; q < S; ++q) tot = fmaf(os[q], exp2f((om[q] - M) * LOG2E), tot);
+            const bool ok = i + u * stride < n;
+            const float scale = ok ? exp2f((m[u] - M) * LOG2E) * __frcp_rn(tot) : 0.f;
+            if (w == 0 && ok) lsum += M + __logf(tot);
+#pragma unroll
+            for (int gg = 0; gg < KG; ++gg) {
+                const int g = int(w) + gg * S;
+                if (g < K) {
+                    const float4 ca = *reinterpret_cast<const float4*>(s_c + g * EM_COMP_STRIDE);
+                    const float r = e[u][gg] * scale;
+                    const float d0 = cx[u] - ca.x, d1 = cy[u] - ca.y, d2 = ct[u] - ca.z;
+                    const float r0 = r * d0, r1 = r * d1, r2 = r * d2;
+                    acc[gg][0] += r;
+                    acc[gg][1] += r0;
+                    acc[gg][2] += r1;
+                    acc[gg][3] += r2;
+                    acc[gg][4] = fmaf(r0, d0, acc[gg][4]);
+                    acc[gg][5] = fmaf(r0, d1, acc[gg][5]);
+                    acc[gg][6] = fmaf(r0, d2, acc[gg][6]);
+                    acc[gg][7] = fmaf(r1, d1, acc[gg][7]);
+                    acc[gg][8] = fmaf(r1, d2, acc[gg][8]);
+                    acc[gg][9] = fmaf(r2, d2, acc[gg][9]);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int gg = 0; gg < KG; ++gg) {
+        const int g = int(w) + gg * S;
+        if (g < K) {
+#pragma unroll
+            for (int k = 0; k < EM_NSTAT; ++k) {
+                double v = acc[gg][k];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (lane == 0) atomicAdd(&s_acc[g * EM_NSTAT + k], v);
+            }
+        }
+    }
+    if (w == 0) {
+        double v = lsum;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) atomicAdd(&s_acc[NACC - 1], v);
+    }
+    __syncthreads();
+    double* st = a.stats + (size_t)fit * NACC;
+    for (int k = threadIdx.x; k < NACC; k += blockDim.x) atomicAdd(&st[k], s_acc[k]);
+}
+
 // ---- E-step, packed: two samples per thread in the lanes of FFMA2 / FMUL2 / FADD2 (K <= 4) ----------------
 // The E-step is almost pure FP32 arithmetic (no compares / selects to speak of), which is where packed
 // pairs pay on sm_100a (tools/pipe_probe.cu): half the FMA-pipe issue slots per sample.  Same arithmetic

@@ -1139,11 +1139,28 @@ static void em_pick(em_kernel_t& k0, em_kernel_t& k1, bool vec, size_t& smem) {
     k0 = em_estep_kernel<K, 0>;
     k1 = nullptr;
     smem = 0;
-    if constexpr (K <= 4) k0 = em_estep2_kernel<K, false>;  // packed: two samples per thread
+#ifndef EM_PACKED_MAX_K
+#define EM_PACKED_MAX_K 5   // packed pairs while the 10 K accumulator pairs fit the register file (K = 5: 230 registers, 1.61 vs 2.15 ms; K = 6 spills)
+#endif
+    if constexpr (K <= EM_PACKED_MAX_K) k0 = em_estep2_kernel<K, false>;  // packed: two samples per thread
     if constexpr (K <= EM_TMA_MAX_K) {  // fed by the bulk-copy engine: K = 1 is HBM-bound; K = 2..4 gain the prefetch registers back
         if (vec) { k0 = em_estep_tma_kernel<K>; smem = sizeof(float) * EM_TMA_STAGES * 3 * EM_TMA_TILE; }
     }
-    if constexpr (K > 8) k1 = em_estep_kernel<K, 8>;
+#ifndef EM_SPLIT_S_LOW
+#define EM_SPLIT_S_LOW 2    // warps per group for 5 <= K <= 8
+#endif
+#ifndef EM_SPLIT_S_HIGH
+#define EM_SPLIT_S_HIGH 2   // for K > 8 (measured: 16 components 8.08 ms in two launches, 6.07 ms with 4 warps per group, 5.38 ms with 2)
+#endif
+#ifndef EM_SPLIT_MIN_K
+#define EM_SPLIT_MIN_K 9    // 5 <= K <= 8: the one-warp kernel is still 5-15 % faster than a group of two
+#endif
+    // K >= 5: the components are split over the warps of a group (em_estep_split_kernel): one launch for any K <= 16
+    if constexpr (K >= EM_SPLIT_MIN_K && K <= 8) k0 = em_estep_split_kernel<K, EM_SPLIT_S_LOW>;
+    if constexpr (K > 8) {
+        if constexpr (EM_SPLIT_MIN_K <= 16) k0 = em_estep_split_kernel<K, EM_SPLIT_S_HIGH>;
+        else k1 = em_estep_kernel<K, 8>;
+    }
 }
 static bool em_kernels(int K, em_kernel_t& k0, em_kernel_t& k1, bool vec, size_t& smem) {
     switch (K) {
