@@ -201,7 +201,15 @@ typedef struct {
                                     0's samples first, sample-major (GM_Model.h:101-112) */
     uint64_t seed;               /* Philox key */
     uint64_t stream_id;          /* Philox subsequence (waypoint index / trajectory id) */
+    int refit;                   /* MCSIM_GMM_REFIT_MOMENTS: the reference's per-component moment matching (truncateGMM);
+                                    MCSIM_GMM_REFIT_EM: then em_iters EM iterations of the whole mixture on ALL
+                                    collision-free samples, started from the moment-matched mixture (the method variant
+                                    finalpaper/ajaay_paper.tex:901-903 lists as future work; oracle:
+                                    arma::gmm_full::learn(keep_existing) on the reference's free samples) */
+    int em_iters;
 } mcsim_gmm_truncate_params;
+
+enum { MCSIM_GMM_REFIT_MOMENTS = 0, MCSIM_GMM_REFIT_EM = 1 };
 
 typedef struct {
     double weights[MCSIM_MAX_GAUSSIANS];
@@ -229,6 +237,8 @@ typedef struct {
     const int* counts;           /* [T x K] multinomial counts per waypoint (replay) */
     int kernel;                  /* MCSIM_GMM_KERNEL_*: which launch shape runs a Philox-mode plan (results agree to the
                                     order of the FP64 sums; for tests and for measuring the switch-over) */
+    int refit;                   /* MCSIM_GMM_REFIT_*: see mcsim_gmm_truncate_params; EM runs the per-waypoint kernels */
+    int em_iters;
 } mcsim_gmm_run_params;
 
 enum {
@@ -371,6 +381,22 @@ int mcsim_cuda_score_plans(mcsim_cuda_ctx* ctx, const mcsim_score_params* p, mcs
 int mcsim_cuda_score_prepare(mcsim_cuda_ctx* ctx, const mcsim_score_params* p);
 int mcsim_cuda_score_launch(mcsim_cuda_ctx* ctx);
 int mcsim_cuda_score_collect(mcsim_cuda_ctx* ctx, mcsim_score_result* r);
+
+/* ---- method variant: belief propagation with the analytic linear-constraint truncation ------- */
+/* The GMM branch of EKF_GaussProp (MCSimulator.h:672-678, :766-772, :804-817, :843-856) with truncateGMM replaced by the
+ * closed form of mcsim_truncate_linear applied per component ON THE DEVICE (one launch per run): the free region is the
+ * intersection of the half-planes A[k] . (x, y, theta) <= b[k] -- the constraint list the reference only sketches
+ * (gaussprop.py:58-73, linConstraint.py:15-30).  No samples, no collision geometry.  Parity unpinned. */
+typedef struct {
+    int K;                       /* mixture components (all start as N(x*_0, Sigma_0), as initModel does) */
+    int n_constraints;
+    const double* A;             /* [n_constraints][3] */
+    const double* b;             /* [n_constraints] */
+    const double* normals;       /* optional: (T - 1) x (3 + L) standard normals of the shared real-robot thread in
+                                    consumption order; NULL: drawn from Philox (mc->seed, stream mc->rollout_offset) */
+    size_t n_normals;
+} mcsim_linear_params;
+int mcsim_cuda_linear_run(mcsim_cuda_ctx* ctx, const mcsim_mc_params* mc, const mcsim_linear_params* lp, mcsim_gmm_run_result* r);
 
 /* ---- analytic linear-constraint truncation (host, FP64) ------------------------ */
 /* Truncates N(mean, cov) (3-D, cov row-major) against n half-spaces A[k] . x <= b[k]: per constraint the

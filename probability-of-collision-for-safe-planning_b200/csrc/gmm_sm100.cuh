@@ -29,6 +29,7 @@
 #include "estimator_math.h"
 #include "philox.h"
 #include "sat_device.cuh"
+#include "linear_truncation.h"
 #include "mc_philox2_sm100.cuh"   // packed FP32 pairs: box_muller2, hull_frame2, class_frame2, class_pair_test2, robot_hits2
 
 #define GMM_STAT 11        // n_free, n_coll, sum d[3], sum d d^T [6: xx xy xz yy yz zz]
@@ -78,6 +79,11 @@ struct GmmLaunch {
     const float2* nominal;        // [T] (x*_t, y*_t), the centres of the lists; batch: [B][T] when cull_stride != 0
     unsigned long long* tests;    // optional: executed pair tests (all members)
     int spread;                   // Philox sample kernel: one sample per thread instead of two (small n, single run)
+    // EM-refit variant (8f-4): the collision-free samples of this waypoint, FP32, rows x | y | theta at stride free_cap,
+    // appended in no particular order (gmm_sample_kernel only); NULL: not kept
+    float* free_out;
+    unsigned* free_n;
+    unsigned free_cap;
 };
 
 // Batch member b (blockIdx.y of the count / sample kernels, blockIdx.x of the refit kernel): its own mixture, statistics,
@@ -268,6 +274,7 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
         bool hit = false;
         double d0 = 0.0, d1 = 0.0, d2 = 0.0;
         float xf = 0.f, yf = 0.f, sn = 0.f, cs = 1.f;
+        float px = 0.f, py = 0.f, pth = 0.f;   // the sample's pose (kept for the EM-refit variant)
         if (valid) {
             while (g < K - 1 && i >= s_prefix[g + 1]) ++g;  // i only grows: the component index is monotone
             double z0, z1, z2;
@@ -288,6 +295,7 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
             d1 = __dadd_rn(__dmul_rn(Lc[1], z0), __dmul_rn(Lc[2], z1));
             d2 = __dadd_rn(__dadd_rn(__dmul_rn(Lc[3], z0), __dmul_rn(Lc[4], z1)), __dmul_rn(Lc[5], z2));
             const double x = __dadd_rn(d0, cp[1]), y = __dadd_rn(d1, cp[2]), th = __dadd_rn(d2, cp[3]);
+            px = float(x); py = float(y); pth = float(th);
             if (MODE == MCSIM_MODE_REPLAY) {
                 hit = clearance_d(a.hulls_d, a.pairs_d, a.n_hulls, x, y, th) <= 0.0;
             } else {
@@ -318,6 +326,19 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
                 tested = c_scene.n_pairs;
             }
             if (valid) my_tests += tested;
+        }
+        if (a.free_out) {   // warp-aggregated append of the free samples
+            const unsigned keep = __ballot_sync(0xffffffffu, valid && !hit);
+            if (keep) {
+                unsigned at = 0;
+                if ((threadIdx.x & 31) == 0) at = atomicAdd(a.free_n, unsigned(__popc(keep)));
+                at = __shfl_sync(0xffffffffu, at, 0) + __popc(keep & ((1u << (threadIdx.x & 31)) - 1u));
+                if (valid && !hit && at < a.free_cap) {
+                    a.free_out[at] = px;
+                    a.free_out[size_t(a.free_cap) + at] = py;
+                    a.free_out[2 * size_t(a.free_cap) + at] = pth;
+                }
+            }
         }
         if (__any_sync(0xffffffffu, valid && g_acc >= 0 && g != g_acc)) flush();
         if (valid) {
@@ -619,6 +640,85 @@ __global__ void __launch_bounds__(32) gmm_refit_kernel(const GmmLaunch a_in) {
     for (int i = g; i < K * GMM_COMP; i += 32) m.comps[i] = s_cp[i];
     for (int i = g; i < K * GMM_STAT; i += 32) m.stats[i] = 0.0;
     if (g < K) m.hist[g] = 0;
+}
+
+// EM-refit variant: the mixture was refitted elsewhere (EM on the free samples); move it to waypoint t + 1 (EKFpredict +
+// EKFupdate), record it, and factor the covariances for the next sampling -- the second half of gmm_refit_finish.
+__global__ void __launch_bounds__(32) gmm_propagate_kernel(const GmmLaunch a_in) {
+    using namespace mcsim_math;
+    const GmmLaunch& a = a_in;
+    const GmmMember m = gmm_member(a_in, blockIdx.x);
+    const int g = threadIdx.x, K = a.K, t = a.t;
+    if (g >= K) return;
+    double* cp = m.comps + size_t(g) * GMM_COMP;
+    if (t == a.T - 1 && a.rec_post) for (int k = 0; k < GMM_REC; ++k) a.rec_post[g * GMM_REC + k] = cp[k];
+    if (a.do_ekf && t < a.T - 1) {
+        const GmmStepTable& s = m.steps[t];
+        double pmu[3], pS[9];
+        ekf_predict(cp + 1, cp + 4, s.u, s.M, pmu, pS);
+        for (int l = 0; l < a.L; ++l) ekf_update_one(a.lx[l], a.ly[l], a.Q, pmu, pS, s.z[l]);
+        for (int k = 0; k < 3; ++k) cp[1 + k] = pmu[k];
+        for (int k = 0; k < 9; ++k) cp[4 + k] = pS[k];
+        if (a.rec_pre) for (int k = 0; k < GMM_REC; ++k) a.rec_pre[(size_t(t + 1) * K + g) * GMM_REC + k] = cp[k];
+    }
+    if (!gmm_chol3(cp + 4, cp + 13)) {
+        atomicAdd(m.degenerate, 1);
+        cp[13] = sqrt(fmax(cp[4], 0.0)); cp[14] = 0; cp[15] = sqrt(fmax(cp[8], 0.0));
+        cp[16] = 0; cp[17] = 0; cp[18] = sqrt(fmax(cp[12], 0.0));
+    }
+}
+
+// ---- method variant: analytic linear-constraint (Patil) truncation instead of sampling --------
+// The same belief propagation as the GMM branch of EKF_GaussProp (:672-678, :766-772, :804-817, :843-856) with
+// truncateGMM replaced by the closed form of linear_truncation.h: at every waypoint each component is truncated against
+// the half-planes A x <= b (the constraint list of gaussprop.py:58-73, windows expanded into half-planes on the host),
+// its weight is multiplied by its collision-free mass, p_t = the mixture's lost mass, then EKFpredict + EKFupdate move
+// it to the next waypoint.  No samples, no collision geometry: one CTA walks the whole plan (one thread per component,
+// FP64), one launch per run; blockIdx.x = batch member.  Parity unpinned (no reference implementation).
+__global__ void __launch_bounds__(32) gmm_linear_run_kernel(const GmmLaunch a_in, const double* __restrict__ A, const double* __restrict__ b, int n_con) {
+    using namespace mcsim_math;
+    const GmmLaunch& a = a_in;
+    const GmmMember m = gmm_member(a_in, blockIdx.x);
+    __shared__ double s_free[MCSIM_MAX_GAUSSIANS], s_coll[MCSIM_MAX_GAUSSIANS];
+    __shared__ double s_cp[MCSIM_MAX_GAUSSIANS][GMM_COMP];
+    const int g = threadIdx.x, K = a.K, T = a.T;
+    for (int i = g; i < K * GMM_COMP; i += 32) s_cp[i / GMM_COMP][i % GMM_COMP] = m.comps[i];
+    __syncthreads();
+    for (int t = 0; t < T; ++t) {
+        if (g < K) {
+            double* cp = s_cp[g];
+            if (a.rec_pre) for (int k = 0; k < GMM_REC; ++k) a.rec_pre[(size_t(t) * K + g) * GMM_REC + k] = cp[k];
+            double mo[3], co[9], fm = 1.0;
+            const int rc = n_con ? mcsim_lt::truncate(cp + 1, cp + 4, n_con, A, b, mo, co, nullptr, &fm) : 0;
+            if (rc == 0 && n_con) {
+                for (int k = 0; k < 3; ++k) cp[1 + k] = mo[k];
+                for (int k = 0; k < 9; ++k) cp[4 + k] = co[k];
+            } else if (rc != 0) {       // no feasible mass (the whole component collides) or a degenerate covariance
+                atomicAdd(m.degenerate, 1);
+                fm = rc == 5 ? 0.0 : 1.0;
+            }
+            s_free[g] = cp[0] * fm;
+            s_coll[g] = cp[0] * (1.0 - fm);
+        }
+        __syncthreads();
+        if (g < K) {
+            double* cp = s_cp[g];
+            double tf = 0, tc = 0;
+            for (int k = 0; k < K; ++k) { tf += s_free[k]; tc += s_coll[k]; }
+            cp[0] = s_free[g] / (tf > 0 ? tf : 1.0);
+            if (g == 0) m.probabilities[t] = (tf + tc) > 0 ? tc / (tf + tc) : 0.0;
+            if (t == T - 1 && a.rec_post) for (int k = 0; k < GMM_REC; ++k) a.rec_post[g * GMM_REC + k] = cp[k];
+            if (t < T - 1) {
+                const GmmStepTable& s = m.steps[t];
+                double pmu[3], pS[9];
+                ekf_predict(cp + 1, cp + 4, s.u, s.M, pmu, pS);
+                for (int l = 0; l < a.L; ++l) ekf_update_one(a.lx[l], a.ly[l], a.Q, pmu, pS, s.z[l]);
+                for (int k = 0; k < 3; ++k) cp[1 + k] = pmu[k];
+                for (int k = 0; k < 9; ++k) cp[4 + k] = pS[k];
+            }
+        }
+        __syncthreads();
+    }
 }
 
 // ---- batch: ONE CTA runs ONE member's whole runGMMEstimation (all T waypoints) ---------------------------------------

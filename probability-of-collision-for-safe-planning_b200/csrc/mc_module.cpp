@@ -66,6 +66,9 @@ const MCModule::Command MCModule::kCommands[] = {
     {"setBroadPhase", &MCModule::setBroadPhase, "setBroadPhase 0|1: 1 (default) tests only the obstacles within reach of each waypoint, 0 every obstacle at every step (the returned P does not change)"},
     {"setEstimator", &MCModule::setEstimator, "setEstimator reference|closedloop: collision tested on the particle (reference) or on the real state"},
     {"setRolloutOffset", &MCModule::setRolloutOffset, "setRolloutOffset <u64>: global id of this module's first rollout (shards of one job over several modules / processes)"},
+    {"setRefit", &MCModule::setRefit, "setRefit moments | em [iterations]: runGMMEstimation refits each component by moment matching (the reference, default) or refits the whole mixture to the collision-free samples by EM started from the moment-matched one (default 5 iterations)"},
+    {"setConstraints", &MCModule::setConstraints, "setConstraints <n> then n x (ax ay b xmin xmax ymin ymax): the free space as linear constraints ax x + ay y <= b inside a window (linConstraint.py:4-11; 'inf' / '-inf' for an open side)"},
+    {"runLinearEstimation", &MCModule::runLinearEstimation, "P(collision) by propagating the mixture with the analytic (Patil) truncation against the constraints of setConstraints instead of sampling"},
     {"setDevices", &MCModule::setDevices, "setDevices all | <ordinal> [<ordinal> ...]: the CUDA devices this module runs on; runSimulation splits its rollouts over them (one NCCL all-reduce of the counters), runGMMEstimationBatch its runs"},
     {"getDevices", &MCModule::getDevices, "the CUDA ordinals in use"},
     {"describeRun", &MCModule::describeRun, "describeRun [k]: Philox key, first rollout id and rollout count of the k-th runSimulation from now (default 0 = the next one), then key and stream id of the k-th runGMMEstimation"},

@@ -76,6 +76,9 @@ class MCModule {
     bool setBroadPhase(std::ostream&, std::istream&);
     bool setEstimator(std::ostream&, std::istream&);
     bool setRolloutOffset(std::ostream&, std::istream&);
+    bool setRefit(std::ostream&, std::istream&);
+    bool setConstraints(std::ostream&, std::istream&);
+    bool runLinearEstimation(std::ostream&, std::istream&);
     bool setDevices(std::ostream&, std::istream&);
     bool getDevices(std::ostream&, std::istream&);
     bool describeRun(std::ostream&, std::istream&);
@@ -124,6 +127,9 @@ class MCModule {
     int estimator_ = MCSIM_EST_REFERENCE;
     std::vector<double> draws_;
     std::vector<int> gmm_counts_;
+    int refit_ = MCSIM_GMM_REFIT_MOMENTS;   // setRefit: how truncateGMM refits the mixture
+    int em_iters_ = 0;
+    std::vector<double> con_A_, con_b_;     // setConstraints, expanded into half-planes A (x, y, theta) <= b
     // results of the last run
     std::vector<double> probabilities_;
     std::vector<uint64_t> first_hit_hist_;

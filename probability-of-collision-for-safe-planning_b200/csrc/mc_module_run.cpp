@@ -121,6 +121,8 @@ bool MCModule::runGMMEstimation(std::ostream& sout, std::istream&) {
     std::memset(&g, 0, sizeof(g));
     g.K = K;
     g.n_samples = uint64_t(num_gmm_samples_);
+    g.refit = refit_;
+    g.em_iters = em_iters_;
     if (mode_ == Mode::kDeterministic) {
         if (gmm_counts_.size() != size_t(T) * K) throw std::runtime_error("runGMMEstimation: deterministic mode needs T x K multinomial counts (setGMMCounts / setGMMCountsFile)");
         p.mode = MCSIM_MODE_REPLAY;
@@ -256,6 +258,80 @@ bool MCModule::setRolloutOffset(std::ostream&, std::istream& sinput) {
     unsigned long long v;
     if (!(sinput >> v)) throw std::runtime_error("setRolloutOffset: an unsigned integer expected");
     rollout_offset_ = v;
+    return true;
+}
+
+bool MCModule::setRefit(std::ostream&, std::istream& sinput) {
+    std::string m;
+    sinput >> m;
+    if (m == "moments") { refit_ = MCSIM_GMM_REFIT_MOMENTS; em_iters_ = 0; return true; }
+    if (m != "em") throw std::runtime_error("setRefit: moments | em [iterations] expected, got '" + m + "'");
+    int it = 5;
+    if (sinput >> it) { if (it < 1 || it > 1000) throw std::runtime_error("setRefit: 1..1000 EM iterations expected"); }
+    refit_ = MCSIM_GMM_REFIT_EM;
+    em_iters_ = it;
+    return true;
+}
+
+// setConstraints <n> then n rows (ax ay b xmin xmax ymin ymax): linConstraint(A, b, xmin, xmax, ymin, ymax) of
+// linConstraint.py:4-11.  A state passes a constraint iff A . xy <= b AND it lies inside the window (:15-30), and collides
+// when any constraint fails (gaussprop.py:63-73): the free region is an intersection of half-planes, kept as such.
+bool MCModule::setConstraints(std::ostream&, std::istream& sinput) {
+    int n = -1;
+    if (!(sinput >> n) || n < 0 || n > 512) throw std::runtime_error("setConstraints: a constraint count 0..512 expected");
+    auto number = [&](double& v) {
+        std::string tok;
+        if (!(sinput >> tok)) return false;
+        if (tok == "inf" || tok == "+inf") { v = HUGE_VAL; return true; }
+        if (tok == "-inf") { v = -HUGE_VAL; return true; }
+        try { size_t used = 0; v = std::stod(tok, &used); return used == tok.size(); } catch (...) { return false; }
+    };
+    std::vector<double> A, b;
+    auto half_plane = [&](double ax, double ay, double bb) { A.push_back(ax); A.push_back(ay); A.push_back(0.0); b.push_back(bb); };
+    for (int k = 0; k < n; ++k) {
+        double v[7];
+        for (double& x : v) if (!number(x)) throw std::runtime_error("setConstraints: 7 numbers per constraint expected (ax ay b xmin xmax ymin ymax)");
+        if (v[0] != 0.0 || v[1] != 0.0) half_plane(v[0], v[1], v[2]);
+        if (std::isfinite(v[3])) half_plane(-1.0, 0.0, -v[3]);
+        if (std::isfinite(v[4])) half_plane(1.0, 0.0, v[4]);
+        if (std::isfinite(v[5])) half_plane(0.0, -1.0, -v[5]);
+        if (std::isfinite(v[6])) half_plane(0.0, 1.0, v[6]);
+    }
+    con_A_.swap(A);
+    con_b_.swap(b);
+    return true;
+}
+
+// the GMM branch with the analytic truncation (mcsim_cuda_linear_run); deterministic mode takes the real-robot thread's
+// draws from the draws file ((T - 1) x (3 + L) normals), the other modes from the module's Philox stream
+bool MCModule::runLinearEstimation(std::ostream& sout, std::istream&) {
+    mcsim_mc_params p;
+    fill_params(p);
+    if (num_gaussians_ < 1) throw std::runtime_error("setNumGaussians has not been sent");
+    const int T = p.T, K = num_gaussians_;
+    mcsim_linear_params lp;
+    std::memset(&lp, 0, sizeof(lp));
+    lp.K = K;
+    lp.n_constraints = int(con_b_.size());
+    lp.A = con_A_.data();
+    lp.b = con_b_.data();
+    if (mode_ == Mode::kDeterministic) { lp.normals = draws_.data(); lp.n_normals = draws_.size(); }
+    p.mode = MCSIM_MODE_PHILOX;
+    p.seed = gmm_key();
+    p.rollout_offset = run_index_;
+    probabilities_.assign(size_t(T), 0.0);
+    gmm_post_.assign(size_t(K) * 13, 0.0);
+    gmm_post_K_ = K;
+    mcsim_gmm_run_result r;
+    std::memset(&r, 0, sizeof(r));
+    r.probabilities = probabilities_.data();
+    r.gmm_post = gmm_post_.data();
+    cuda_check(mcsim_cuda_linear_run(ctx_, &p, &lp, &r), "mcsim_cuda_linear_run");
+    ++run_index_;
+    last_kernel_ms_ = r.kernel_ms;
+    last_degenerate_ = r.degenerate;
+    last_n_ = 0; last_hits_ = 0; last_steps_ = 0; last_tests_ = 0;
+    sout << r.P;
     return true;
 }
 

@@ -116,6 +116,7 @@ struct mcsim_cuda_ctx {
     int mc_cull_words = 0;           // 0: no lists for the prepared plan (every live pair is tested)
     // GMM state
     DevBuf gmm_comps, gmm_stats, gmm_hist, gmm_counts, gmm_normals, gmm_steps, gmm_prob, gmm_pre, gmm_post, gmm_trunc, gmm_nout, gmm_deg;
+    DevBuf gmm_free, gmm_free_n, lin_A, lin_b;   // EM-refit variant: free samples of a waypoint; linear variant: half-planes
     double* h_gmm = nullptr;  // pinned staging
     // scoring state
     DevBuf pairs_f, sc_plans, sc_hits, sc_counters;
@@ -202,6 +203,7 @@ extern "C" void mcsim_cuda_destroy(mcsim_cuda_ctx* c) {
     c->gmm_comps.release(); c->gmm_stats.release(); c->gmm_hist.release(); c->gmm_counts.release();
     c->gmm_normals.release(); c->gmm_steps.release(); c->gmm_prob.release(); c->gmm_pre.release();
     c->gmm_post.release(); c->gmm_trunc.release(); c->gmm_nout.release(); c->gmm_deg.release();
+    c->gmm_free.release(); c->gmm_free_n.release(); c->lin_A.release(); c->lin_b.release();
     if (c->h_counters) cudaFreeHost(c->h_counters);
     if (c->h_gmm) cudaFreeHost(c->h_gmm);
     cudaEventDestroy(c->ev0);
@@ -881,7 +883,11 @@ static int gmm_launch_waypoint(mcsim_cuda_ctx* c, const GmmLaunch& a_in, int mod
     const dim3 grid(gx, B);
     if (mode == MCSIM_MODE_PHILOX && a.n > (1ull << 31)) return fail(MCSIM_ERR_ARG, "gmm: Philox mode takes at most 2^31 samples per waypoint");
     a.spread = spread_flag;
-    if (mode == MCSIM_MODE_PHILOX) {
+    if (mode == MCSIM_MODE_PHILOX && a.free_out) {   // EM-refit variant: the kernel that can keep the free samples
+        gmm_count_kernel<<<grid, block, 0, c->stream>>>(a);
+        gmm_sample_kernel<MCSIM_MODE_PHILOX><<<grid, block, 0, c->stream>>>(a);
+        c->launches += 2;
+    } else if (mode == MCSIM_MODE_PHILOX) {
         gmm_count_kernel<<<grid, block, 0, c->stream>>>(a);
         gmm_sample_philox_kernel<<<grid, block, 0, c->stream>>>(a);
         c->launches += 2;
@@ -940,6 +946,146 @@ static int gmm_launch_cluster(mcsim_cuda_ctx* c, const GmmLaunch& a, int n_runs)
     return MCSIM_OK;
 }
 
+// ---- method variant: EM-refit truncation -------------------------------------------------------------
+// After the moment refit of truncateGMM (:592-629) the K-component mixture is refitted to ALL collision-free samples of
+// the waypoint by `iters` EM iterations started from the moment-matched mixture (arma::gmm_full::learn with
+// keep_existing: the EM operator of this library, em_sm100.cuh).  The free samples were kept by gmm_sample_kernel
+// (a.free_out, rows at stride N); they are packed into the EM sample buffer, the mixture makes one host round trip.
+// `mix` in / out: K x GMM_REC (w, mu[3], cov[9]).  Returns the number of free samples through n_free_out.
+static int gmm_em_refit(mcsim_cuda_ctx* c, int K, uint64_t N, int iters, double var_floor, double* mix, unsigned* n_free_out) {
+    unsigned n_free = 0;
+    CK(cudaMemcpyAsync(&n_free, c->gmm_free_n.p, sizeof(unsigned), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    if (n_free > N) n_free = unsigned(N);
+    if (n_free_out) *n_free_out = n_free;
+    if (n_free < 2 || iters < 1) return MCSIM_OK;
+    CK(c->em_x.reserve(sizeof(float) * 3 * size_t(n_free)));
+    for (int r = 0; r < 3; ++r)
+        CK(cudaMemcpyAsync((float*)c->em_x.p + size_t(r) * n_free, (const float*)c->gmm_free.p + size_t(r) * N, sizeof(float) * n_free, cudaMemcpyDeviceToDevice, c->stream));
+    c->em_x_valid = true; c->em_x_n = n_free; c->em_x_fits = 1;
+    std::vector<double> h(K), m(size_t(K) * 3), f(size_t(K) * 9);
+    for (int k = 0; k < K; ++k) {
+        h[k] = mix[size_t(k) * GMM_REC];
+        for (int i = 0; i < 3; ++i) m[size_t(k) * 3 + i] = mix[size_t(k) * GMM_REC + 1 + i];
+        for (int i = 0; i < 9; ++i) f[size_t(k) * 9 + i] = mix[size_t(k) * GMM_REC + 4 + i];
+    }
+    mcsim_em_params ep;
+    memset(&ep, 0, sizeof(ep));
+    ep.K = K; ep.n_fits = 1; ep.n = n_free; ep.x = nullptr;
+    ep.hefts = h.data(); ep.means = m.data(); ep.fcovs = f.data();
+    ep.iters = iters; ep.var_floor = var_floor;
+    mcsim_em_result er;
+    memset(&er, 0, sizeof(er));
+    er.hefts = h.data(); er.means = m.data(); er.fcovs = f.data();
+    const uint64_t h2d = c->h2d_bytes, d2h = c->d2h_bytes;
+    const int rc = mcsim_cuda_em_fit(c, &ep, &er);
+    c->h2d_bytes += h2d; c->d2h_bytes += d2h;
+    if (rc) return rc;
+    for (int k = 0; k < K; ++k) {
+        mix[size_t(k) * GMM_REC] = h[k];
+        for (int i = 0; i < 3; ++i) mix[size_t(k) * GMM_REC + 1 + i] = m[size_t(k) * 3 + i];
+        for (int i = 0; i < 9; ++i) mix[size_t(k) * GMM_REC + 4 + i] = f[size_t(k) * 9 + i];
+    }
+    return MCSIM_OK;
+}
+static int gmm_keep_free_samples(mcsim_cuda_ctx* c, GmmLaunch& a, uint64_t N) {
+    if (N >= (1ull << 31)) return fail(MCSIM_ERR_ARG, "gmm: the EM-refit variant takes fewer than 2^31 samples per waypoint");
+    CK(c->gmm_free.reserve(sizeof(float) * 3 * size_t(N)));
+    CK(c->gmm_free_n.reserve(sizeof(unsigned)));
+    a.free_out = (float*)c->gmm_free.p;
+    a.free_n = (unsigned*)c->gmm_free_n.p;
+    a.free_cap = unsigned(N);
+    return MCSIM_OK;
+}
+
+// the shared real-robot thread of a run (host, FP64): applied commands, motion noise and observations of every step.
+// hn: (T - 1) x (3 + L) standard normals in consumption order
+static int gmm_host_steps(const mcsim_mc_params* mc, const std::vector<double>& hn, std::vector<GmmStepTable>& steps) {
+    const int T = mc->T, L = mc->n_landmarks;
+    std::vector<double> applied(size_t(3) * (T > 1 ? T - 1 : 1)), obs(size_t(T > 1 ? T - 1 : 1) * (L ? L : 1));
+    if (T > 1) {
+        const int rc = mcsim_host_thread(mc, hn.data(), hn.size(), nullptr, applied.data(), nullptr, nullptr, nullptr, obs.data());
+        if (rc) return fail(rc, "host thread failed (%d)", rc);
+    }
+    steps.assign(T > 1 ? T - 1 : 1, GmmStepTable());
+    mcsim_math::NoiseModel<double> nmd;
+    for (int k = 0; k < 4; ++k) nmd.alpha[k] = mc->alphas[k];
+    for (int t = 0; t < T - 1; ++t) {
+        double us[3];
+        for (int k = 0; k < 3; ++k) { us[k] = mc->odometry[k * (T - 1) + t]; steps[t].u[k] = applied[k * (T - 1) + t]; }
+        mcsim_math::motion_noise(nmd, us, steps[t].M);
+        for (int l = 0; l < L; ++l) steps[t].z[l] = obs[size_t(t) * L + l];
+    }
+    return MCSIM_OK;
+}
+
+// ---- method variant: the GMM belief propagation with the analytic linear-constraint truncation
+extern "C" int mcsim_cuda_linear_run(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, const mcsim_linear_params* lp, mcsim_gmm_run_result* r) {
+    if (!c || !mc || !lp || !r) return fail(MCSIM_ERR_ARG, "linear_run: NULL argument");
+    const int T = mc->T, K = lp->K, L = mc->n_landmarks, n_con = lp->n_constraints;
+    if (T < 1 || T > MCSIM_MAX_WAYPOINTS || !mc->trajectory || (T > 1 && !mc->odometry)) return fail(MCSIM_ERR_ARG, "linear_run: bad plan");
+    if (K < 1 || K > MCSIM_MAX_GAUSSIANS) return fail(MCSIM_ERR_ARG, "linear_run: K=%d out of range 1..%d", K, MCSIM_MAX_GAUSSIANS);
+    if (L < 0 || L > MCSIM_MAX_LANDMARKS || (L && !mc->landmarks)) return fail(MCSIM_ERR_ARG, "linear_run: bad landmarks");
+    if (n_con < 0 || n_con > 4096 || (n_con && (!lp->A || !lp->b))) return fail(MCSIM_ERR_ARG, "linear_run: bad constraints");
+    CK(cudaSetDevice(c->device));
+    const int per_step = 3 + L;
+    std::vector<double> hn;
+    if (lp->normals) {
+        if (lp->n_normals < size_t(T > 1 ? T - 1 : 0) * per_step) return fail(MCSIM_ERR_DRAWS, "linear_run: %zu normals given, %zu needed", lp->n_normals, size_t(T - 1) * per_step);
+        hn.assign(lp->normals, lp->normals + size_t(T > 1 ? T - 1 : 0) * per_step);
+    } else {
+        host_normals(mc->seed, unsigned(mc->rollout_offset), T, per_step, hn);
+    }
+    std::vector<GmmStepTable> steps;
+    int rc = gmm_host_steps(mc, hn, steps);
+    if (rc) return rc;
+    rc = gmm_reserve(c, T, K);
+    if (rc) return rc;
+    std::vector<double> comps(size_t(K) * GMM_COMP, 0.0);
+    for (int k = 0; k < K; ++k) {   // K copies of N(x*_0, Sigma_0), weights 1 / K (GM_Model::initModel, GM_Model.h:57-77)
+        double* cp = &comps[size_t(k) * GMM_COMP];
+        cp[0] = 1.0 / K;
+        for (int i = 0; i < 3; ++i) cp[1 + i] = mc->trajectory[i * T];
+        for (int i = 0; i < 9; ++i) cp[4 + i] = mc->cov0[i];
+    }
+    CK(c->lin_A.reserve(sizeof(double) * 3 * size_t(n_con ? n_con : 1)));
+    CK(c->lin_b.reserve(sizeof(double) * size_t(n_con ? n_con : 1)));
+    CK(cudaMemcpyAsync(c->gmm_comps.p, comps.data(), sizeof(double) * comps.size(), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->gmm_steps.p, steps.data(), sizeof(GmmStepTable) * steps.size(), cudaMemcpyHostToDevice, c->stream));
+    if (n_con) {
+        CK(cudaMemcpyAsync(c->lin_A.p, lp->A, sizeof(double) * 3 * size_t(n_con), cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->lin_b.p, lp->b, sizeof(double) * size_t(n_con), cudaMemcpyHostToDevice, c->stream));
+    }
+    c->h2d_bytes = sizeof(double) * comps.size() + sizeof(GmmStepTable) * steps.size() + sizeof(double) * 4 * size_t(n_con);
+    GmmLaunch a;
+    gmm_fill_launch(c, a, K, T, L, 0, mc->seed, unsigned(mc->rollout_offset));
+    a.Q = mc->Q;
+    for (int l = 0; l < L; ++l) { a.lx[l] = mc->landmarks[l]; a.ly[l] = mc->landmarks[L + l]; }
+    a.rec_pre = r->gmm_pre ? (double*)c->gmm_pre.p : nullptr;
+    a.rec_post = (double*)c->gmm_post.p;
+    CK(cudaEventRecord(c->ev0, c->stream));
+    gmm_linear_run_kernel<<<1, 32, 0, c->stream>>>(a, (const double*)c->lin_A.p, (const double*)c->lin_b.p, n_con);
+    ++c->launches;
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(c->ev1, c->stream));
+    std::vector<double> prob(T);
+    int deg = 0;
+    CK(cudaMemcpyAsync(prob.data(), c->gmm_prob.p, sizeof(double) * T, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(&deg, c->gmm_deg.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    if (r->gmm_pre) CK(cudaMemcpyAsync(r->gmm_pre, c->gmm_pre.p, sizeof(double) * size_t(T) * K * GMM_REC, cudaMemcpyDeviceToHost, c->stream));
+    if (r->gmm_post) CK(cudaMemcpyAsync(r->gmm_post, c->gmm_post.p, sizeof(double) * K * GMM_REC, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    c->d2h_bytes = sizeof(double) * T + sizeof(int);
+    CK(cudaEventElapsedTime(&r->kernel_ms, c->ev0, c->ev1));
+    double free_all = 1.0;
+    for (int t = 0; t < T; ++t) free_all *= (1.0 - prob[t]);
+    r->P = 1.0 - free_all;
+    r->degenerate = deg;
+    r->pair_tests = 0;
+    if (r->probabilities) memcpy(r->probabilities, prob.data(), sizeof(double) * T);
+    return MCSIM_OK;
+}
+
 extern "C" int mcsim_cuda_gmm_run(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, const mcsim_gmm_run_params* g,
                                   mcsim_gmm_run_result* r) {
     if (!c || !mc || !g || !r) return fail(MCSIM_ERR_ARG, "gmm_run: NULL argument");
@@ -969,20 +1115,8 @@ extern "C" int mcsim_cuda_gmm_run(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, 
     } else {
         return fail(MCSIM_ERR_ARG, "gmm_run: unknown mode %d", mode);
     }
-    std::vector<double> applied(size_t(3) * (T > 1 ? T - 1 : 1)), obs(size_t(T > 1 ? T - 1 : 1) * (L ? L : 1));
-    if (T > 1) {
-        int rc = mcsim_host_thread(mc, hn.data(), hn.size(), nullptr, applied.data(), nullptr, nullptr, nullptr, obs.data());
-        if (rc) return fail(rc, "gmm_run: host thread failed (%d)", rc);
-    }
-    std::vector<GmmStepTable> steps(T > 1 ? T - 1 : 1);
-    mcsim_math::NoiseModel<double> nmd;
-    for (int k = 0; k < 4; ++k) nmd.alpha[k] = mc->alphas[k];
-    for (int t = 0; t < T - 1; ++t) {
-        double us[3];
-        for (int k = 0; k < 3; ++k) { us[k] = mc->odometry[k * (T - 1) + t]; steps[t].u[k] = applied[k * (T - 1) + t]; }
-        mcsim_math::motion_noise(nmd, us, steps[t].M);
-        for (int l = 0; l < L; ++l) steps[t].z[l] = obs[size_t(t) * L + l];
-    }
+    std::vector<GmmStepTable> steps;
+    { const int rs = gmm_host_steps(mc, hn, steps); if (rs) return rs; }
 
     int rc = gmm_reserve(c, T, K);
     if (rc) return rc;
@@ -1025,9 +1159,38 @@ extern "C" int mcsim_cuda_gmm_run(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, 
     a.do_ekf = 1;
     a.counts_replay = (const int*)c->gmm_counts.p;
     if (mode == MCSIM_MODE_PHILOX) { rc = gmm_upload_cull(c, a, mc->trajectory, 1, T, mc->exhaustive != 0); if (rc) return rc; }
+    const bool em_refit = g->refit == MCSIM_GMM_REFIT_EM;
+    if (g->refit != MCSIM_GMM_REFIT_MOMENTS && !em_refit) return fail(MCSIM_ERR_ARG, "gmm_run: unknown refit %d", g->refit);
+    if (em_refit) { rc = gmm_keep_free_samples(c, a, N); if (rc) return rc; }
     CK(cudaEventRecord(c->ev0, c->stream));
     rc = -1;
-    if (mode == MCSIM_MODE_PHILOX && gmm_cluster_fits(c, N, 1, g->kernel)) {
+    if (em_refit) {
+        // per waypoint: count / sample (free samples kept) / moment refit without the EKF step, EM on the free samples
+        // (one host round trip for the K x 13 mixture), then EKFpredict + EKFupdate + Cholesky of the refitted mixture
+        a.do_ekf = 0;
+        a.trunc_out = (double*)c->gmm_trunc.p;
+        std::vector<double> mix(size_t(K) * GMM_REC);
+        for (int t = 0; t < T; ++t) {
+            a.t = t;
+            a.normals = mode == MCSIM_MODE_REPLAY ? (const double*)c->gmm_normals.p + size_t(t) * 3 * N : nullptr;
+            CK(cudaMemsetAsync(c->gmm_free_n.p, 0, sizeof(unsigned), c->stream));
+            rc = gmm_launch_waypoint(c, a, mode);
+            if (rc) return rc;
+            CK(cudaMemcpyAsync(mix.data(), c->gmm_trunc.p, sizeof(double) * mix.size(), cudaMemcpyDeviceToHost, c->stream));
+            rc = gmm_em_refit(c, K, N, g->em_iters, 1e-10, mix.data(), nullptr);
+            if (rc) return rc;
+            std::vector<double> cps(size_t(K) * GMM_COMP, 0.0);
+            for (int k = 0; k < K; ++k) memcpy(&cps[size_t(k) * GMM_COMP], &mix[size_t(k) * GMM_REC], sizeof(double) * GMM_REC);
+            CK(cudaMemcpyAsync(c->gmm_comps.p, cps.data(), sizeof(double) * cps.size(), cudaMemcpyHostToDevice, c->stream));
+            GmmLaunch pa = a;
+            pa.do_ekf = 1;
+            gmm_propagate_kernel<<<1, 32, 0, c->stream>>>(pa);
+            ++c->launches;
+            CK(cudaGetLastError());
+            CK(cudaStreamSynchronize(c->stream));   // cps is a stack vector
+        }
+        rc = 0;
+    } else if (mode == MCSIM_MODE_PHILOX && gmm_cluster_fits(c, N, 1, g->kernel)) {
         a.t = 0;
         rc = gmm_launch_cluster(c, a, 1);
         if (rc > 0) return rc;
@@ -1099,6 +1262,13 @@ extern "C" int mcsim_cuda_gmm_truncate(mcsim_cuda_ctx* c, const mcsim_gmm_trunca
     a.trunc_out = (double*)c->gmm_trunc.p;
     a.n_out = (unsigned long long*)c->gmm_nout.p;
     a.do_ekf = 0;
+    const bool em_refit = p->refit == MCSIM_GMM_REFIT_EM;
+    if (p->refit != MCSIM_GMM_REFIT_MOMENTS && !em_refit) return fail(MCSIM_ERR_ARG, "gmm_truncate: unknown refit %d", p->refit);
+    if (em_refit) {
+        rc = gmm_keep_free_samples(c, a, N);
+        if (rc) return rc;
+        CK(cudaMemsetAsync(c->gmm_free_n.p, 0, sizeof(unsigned), c->stream));
+    }
     rc = gmm_launch_waypoint(c, a, p->mode);
     if (rc) return rc;
     std::vector<double> out(size_t(K) * GMM_REC);
@@ -1110,6 +1280,7 @@ extern "C" int mcsim_cuda_gmm_truncate(mcsim_cuda_ctx* c, const mcsim_gmm_trunca
     CK(cudaMemcpyAsync(&prob, c->gmm_prob.p, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaMemcpyAsync(&deg, c->gmm_deg.p, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
+    if (em_refit) { rc = gmm_em_refit(c, K, N, p->em_iters, 1e-10, out.data(), nullptr); if (rc) return rc; }
     memset(r, 0, sizeof(*r));
     for (int k = 0; k < K; ++k) {
         r->weights[k] = out[size_t(k) * GMM_REC];

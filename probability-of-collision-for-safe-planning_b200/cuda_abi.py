@@ -16,6 +16,7 @@ MAX_GAUSSIANS = 16
 MAX_WAYPOINTS = 1024
 MODE_REPLAY, MODE_PHILOX = 0, 1
 GMM_KERNEL_AUTO, GMM_KERNEL_PER_WAYPOINT, GMM_KERNEL_CLUSTER = 0, 1, 2
+GMM_REFIT_MOMENTS, GMM_REFIT_EM = 0, 1
 EST_REFERENCE, EST_CLOSEDLOOP = 0, 1
 
 _dp = C.POINTER(C.c_double)
@@ -87,7 +88,7 @@ class GmmTruncateParams(C.Structure):
     _fields_ = [
         ("K", C.c_int), ("weights", _dp), ("means", _dp), ("covs", _dp),
         ("n_samples", C.c_uint64), ("mode", C.c_int), ("counts", C.POINTER(C.c_int)),
-        ("normals", _dp), ("seed", C.c_uint64), ("stream_id", C.c_uint64),
+        ("normals", _dp), ("seed", C.c_uint64), ("stream_id", C.c_uint64), ("refit", C.c_int), ("em_iters", C.c_int),
     ]
 
 
@@ -103,8 +104,12 @@ class GmmTruncateResult(C.Structure):
 class GmmRunParams(C.Structure):
     _fields_ = [
         ("K", C.c_int), ("n_samples", C.c_uint64), ("normals", _dp), ("n_normals", C.c_size_t),
-        ("counts", C.POINTER(C.c_int)), ("kernel", C.c_int),
+        ("counts", C.POINTER(C.c_int)), ("kernel", C.c_int), ("refit", C.c_int), ("em_iters", C.c_int),
     ]
+
+
+class LinearParams(C.Structure):
+    _fields_ = [("K", C.c_int), ("n_constraints", C.c_int), ("A", _dp), ("b", _dp), ("normals", _dp), ("n_normals", C.c_size_t)]
 
 
 class GmmRunResult(C.Structure):
@@ -152,6 +157,7 @@ def lib():
         L.mcsim_cuda_gmm_truncate.argtypes = [vp, C.POINTER(GmmTruncateParams), C.POINTER(GmmTruncateResult)]
         L.mcsim_cuda_gmm_run.argtypes = [vp, C.POINTER(McParams), C.POINTER(GmmRunParams), C.POINTER(GmmRunResult)]
         L.mcsim_cuda_gmm_run_batch.argtypes = [vp, C.POINTER(McParams), C.POINTER(GmmBatchParams), C.POINTER(GmmBatchResult)]
+        L.mcsim_cuda_linear_run.argtypes = [vp, C.POINTER(McParams), C.POINTER(LinearParams), C.POINTER(GmmRunResult)]
         L.mcsim_truncate_linear.argtypes = [_dp, _dp, C.c_int, _dp, _dp, _dp, _dp, _dp]
         L.mcsim_cuda_score_plans.argtypes = [vp, C.POINTER(ScoreParams), C.POINTER(ScoreResult)]
         L.mcsim_cuda_score_prepare.argtypes = [vp, C.POINTER(ScoreParams)]
@@ -385,13 +391,13 @@ class Context:
         return int(a.value), int(b.value)
 
     def gmm_run(self, plan, K, n_samples, mode=MODE_PHILOX, seed=0x5AFEC0DE, stream_id=0, draws=None, counts=None,
-                record=False, exhaustive=False, kernel=GMM_KERNEL_AUTO):
+                record=False, exhaustive=False, kernel=GMM_KERNEL_AUTO, refit=GMM_REFIT_MOMENTS, em_iters=0):
         """runGMMEstimation of one plan (MCSimulator.h:354-358 -> the GMM branch of EKF_GaussProp).
         Replay mode: draws = the reference's normal stream of the run, counts[T, K] = multinomial counts."""
         p, keep = make_mc_params(plan, mode=mode, seed=seed, rollout_offset=stream_id, exhaustive=exhaustive)
         T = int(p.T)
         g = GmmRunParams()
-        g.K, g.n_samples, g.kernel = int(K), int(n_samples), int(kernel)
+        g.K, g.n_samples, g.kernel, g.refit, g.em_iters = int(K), int(n_samples), int(kernel), int(refit), int(em_iters)
         if draws is not None:
             dr = np.ascontiguousarray(draws, dtype=np.float64)
             keep.append(dr)
@@ -545,8 +551,31 @@ class Context:
         out.update(degenerate=int(r.degenerate), kernel_ms=float(r.kernel_ms), pair_tests=int(r.pair_tests))
         return out
 
+    def linear_run(self, plan, K, A, b, seed=0x5AFEC0DE, stream_id=0, normals=None, record=False):
+        """The GMM belief propagation with the analytic linear-constraint truncation (mcsim_cuda_linear_run):
+        free region = all x with A[k] . x <= b[k]."""
+        p, keep = make_mc_params(plan, mode=MODE_PHILOX, seed=seed, rollout_offset=stream_id)
+        T = int(p.T)
+        Aa = np.ascontiguousarray(A, dtype=np.float64).reshape(-1, 3)
+        bb = np.ascontiguousarray(b, dtype=np.float64).reshape(-1)
+        lp = LinearParams()
+        lp.K, lp.n_constraints, lp.A, lp.b = int(K), Aa.shape[0], dptr(Aa), dptr(bb)
+        if normals is not None:
+            nz = np.ascontiguousarray(normals, dtype=np.float64)
+            keep.append(nz)
+            lp.normals, lp.n_normals = dptr(nz), nz.size
+        r = GmmRunResult()
+        out = dict(probabilities=np.zeros(T), gmm_post=np.zeros((int(K), 13)))
+        r.probabilities, r.gmm_post = dptr(out["probabilities"]), dptr(out["gmm_post"])
+        if record:
+            out["gmm_pre"] = np.zeros((T, int(K), 13))
+            r.gmm_pre = dptr(out["gmm_pre"])
+        check(lib().mcsim_cuda_linear_run(self._h, C.byref(p), C.byref(lp), C.byref(r)))
+        out.update(P=float(r.P), degenerate=int(r.degenerate), kernel_ms=float(r.kernel_ms))
+        return out
+
     def gmm_truncate(self, weights, means, covs, n_samples, mode=MODE_PHILOX, counts=None, normals=None,
-                     seed=0x5AFEC0DE, stream_id=0):
+                     seed=0x5AFEC0DE, stream_id=0, refit=GMM_REFIT_MOMENTS, em_iters=0):
         """One truncateGMM (MCSimulator.h:570-642) of the mixture (weights[K], means[K,3], covs[K,3,3])."""
         w = np.ascontiguousarray(weights, dtype=np.float64)
         m = np.ascontiguousarray(means, dtype=np.float64).reshape(-1, 3)
@@ -555,6 +584,7 @@ class Context:
         p = GmmTruncateParams()
         p.K, p.weights, p.means, p.covs = K, dptr(w), dptr(m), dptr(cv)
         p.n_samples, p.mode, p.seed, p.stream_id = int(n_samples), int(mode), int(seed), int(stream_id)
+        p.refit, p.em_iters = int(refit), int(em_iters)
         keep = [w, m, cv]
         if counts is not None:
             cn = np.ascontiguousarray(counts, dtype=np.int32)

@@ -1,0 +1,204 @@
+"""Method variants wired into the estimator: EM-refit GMM truncation and the analytic linear-constraint
+(Patil) truncation as a third run* command.
+
+* EM refit: oracle = the reference's own free samples of a waypoint (runGMMEstimation run live through oracle/_ref, the
+  recorded poses and flags), moment-matched per component as truncateGMM does (MCSimulator.h:592-629), then
+  arma::gmm_full::learn(keep_existing) on them -- against mcsim_cuda_gmm_truncate(refit = EM) on the same injected draws.
+* Linear truncation: PARITY UNPINNED (the reference has a predicate stub only).  Checks: the device chain equals a NumPy
+  restatement of the EKF (MCSimulator.h:868-929) around mcsim_truncate_linear; and on a scene where both apply (point
+  robot, one half-plane wall) the analytic estimate agrees with the sampled truncation the reference implements."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLD, ROOT, golden
+
+pytestmark = pytest.mark.gpu
+
+
+def _moment_refit(samples_by_comp):
+    w = np.array([len(x) for x in samples_by_comp], dtype=np.float64)
+    means = np.array([x.mean(axis=0) for x in samples_by_comp])
+    covs = np.array([np.cov(x.T, ddof=1) for x in samples_by_comp])
+    return w / w.sum(), means, covs
+
+
+@pytest.mark.parametrize("iters", [1, 4])
+def test_em_refit_truncation_matches_armadillo_on_the_reference_free_samples(ctx, plan, scenes, iters):
+    import oracle_ref
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    if not oracle_ref.available():
+        pytest.skip("oracle/_ref not built")
+    g = golden("gmm_replay_pr2test2_K3.npz")
+    sc = scenes["pr2test2"]
+    K, N, T = 3, int(g["n_samples"]), plan["trajectory"].shape[1]
+    ref = oracle_ref.gmm_run(plan, sc["boxes"], sc["hulls"], K, N, draws=g["draws"], multinomial_seed=7)
+    np.testing.assert_array_equal(ref["gmm_counts"], g["gmm_counts"])
+    ctx.set_scene(sc["boxes"], sc["hulls"])
+    per_step = 11
+    checked = 0
+    for t in np.argsort(-ref["probabilities"])[:3]:           # the three waypoints that lose the most samples
+        t = int(t)
+        if not (0.02 < ref["probabilities"][t] < 0.98):
+            continue
+        counts = ref["gmm_counts"][t]
+        prefix = np.concatenate([[0], np.cumsum(counts)])
+        free = ref["flags"][t] == 0
+        by_comp = [ref["poses"][t][prefix[k]:prefix[k + 1]][free[prefix[k]:prefix[k + 1]]] for k in range(K)]
+        if min(len(x) for x in by_comp) < 10:
+            continue
+        w0, m0, c0 = _moment_refit(by_comp)
+        X = np.concatenate(by_comp)
+        rm, rc, rh, _ = oracle_ref.em_fit(X, m0, c0.reshape(K, 9), w0, iters)
+        off = 0 if t == 0 else 3 * N + (t - 1) * (per_step + 3 * N) + per_step
+        pre = ref["gmm_pre"][t]
+        out = ctx.gmm_truncate(pre[:, 0], pre[:, 1:4], pre[:, 4:].reshape(K, 3, 3), N, mode=abi.MODE_REPLAY, counts=counts,
+                               normals=g["draws"][off:off + 3 * N], refit=abi.GMM_REFIT_EM, em_iters=iters)
+        assert out["p_collision"] == ref["probabilities"][t]
+        np.testing.assert_array_equal(out["n_free"], [len(x) for x in by_comp])
+        np.testing.assert_allclose(out["weights"], rh, rtol=1e-4, atol=1e-6)
+        np.testing.assert_allclose(out["means"], rm, rtol=1e-4, atol=1e-5)
+        scale = np.abs(rc).max(axis=1, keepdims=True)
+        assert np.max(np.abs(out["covs"].reshape(K, 9) - rc) / scale) < 1e-4
+        # and it is not the moment refit any more
+        mom = ctx.gmm_truncate(pre[:, 0], pre[:, 1:4], pre[:, 4:].reshape(K, 3, 3), N, mode=abi.MODE_REPLAY, counts=counts,
+                               normals=g["draws"][off:off + 3 * N])
+        np.testing.assert_allclose(mom["weights"], w0, rtol=1e-12)
+        assert np.max(np.abs(mom["means"] - out["means"])) > 1e-6
+        print("waypoint %d: p_t %.4f, %d free samples; EM(%d) weights %s vs moments %s" % (
+            t, ref["probabilities"][t], len(X), iters, np.round(out["weights"], 4), np.round(w0, 4)))
+        checked += 1
+    assert checked >= 1
+
+
+def test_em_refit_full_run_and_plugin_command(ctx, plan, scenes):
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    ctx.set_scene(scenes["pr2test2"]["boxes"], scenes["pr2test2"]["hulls"])
+    mom = ctx.gmm_run(plan, 3, 10000, mode=abi.MODE_PHILOX, stream_id=4)
+    em = ctx.gmm_run(plan, 3, 10000, mode=abi.MODE_PHILOX, stream_id=4, refit=abi.GMM_REFIT_EM, em_iters=3, record=True)
+    again = ctx.gmm_run(plan, 3, 10000, mode=abi.MODE_PHILOX, stream_id=4, refit=abi.GMM_REFIT_EM, em_iters=3)
+    assert 0.0 < em["P"] <= 1.0 and abs(em["P"] - mom["P"]) < 0.15
+    np.testing.assert_allclose(again["probabilities"], em["probabilities"], rtol=1e-6, atol=1e-9)
+    np.testing.assert_allclose(em["gmm_post"][:, 0].sum(), 1.0, atol=1e-9)
+    assert np.all(np.isfinite(em["gmm_pre"]))
+    mod = pcoll_b200.MCModule(os.path.join(ROOT, "data", "scenes", "pr2test2.env.xml"), device=0)
+    pcoll_b200.push_parameters(mod, plan, num_particles=5000, num_gaussians=3, num_gmm_samples=5000)
+    mod.SendCommand("setSeed 11")
+    a = float(mod.SendCommand("runGMMEstimation"))
+    mod.SendCommand("setRefit em 3")
+    b = float(mod.SendCommand("runGMMEstimation"))
+    mod.SendCommand("setRefit moments")
+    assert 0.0 < b <= 1.0 and abs(a - b) < 0.2
+    with pytest.raises(pcoll_b200.McsimError):
+        mod.SendCommand("setRefit sometimes")
+    mod.close()
+
+
+# ---- NumPy restatement of the per-component EKF (MCSimulator.h:868-929) for the linear variant's chain ------------------
+def _wrap(a):
+    while a < 0:
+        a += 2 * np.pi
+    while a > 2 * np.pi:
+        a -= 2 * np.pi
+    return a
+
+
+def _ekf_step(mu, S, u, M, z, lm, Q):
+    sn, cs = np.sin(mu[2] + u[0]), np.cos(mu[2] + u[0])
+    G = np.eye(3); G[0, 2] = -u[1] * sn; G[1, 2] = u[1] * cs
+    V = np.array([[-u[1] * sn, cs, 0.0], [u[1] * cs, sn, 0.0], [1.0, 0.0, 1.0]])
+    mu = np.array([mu[0] + u[1] * cs, mu[1] + u[1] * sn, _wrap(mu[2] + u[0] + u[2])])
+    S = G @ S @ G.T + V @ np.diag(M) @ V.T
+    for l in range(lm.shape[1]):
+        dx, dy = mu[0] - lm[0, l], mu[1] - lm[1, l]
+        rq = np.sqrt(dx * dx + dy * dy)
+        H = np.array([[dx / rq, dy / rq, 0.0]])
+        s = float((H @ S @ H.T)[0, 0]) + Q
+        Kg = (S @ H.T) / s
+        mu = mu + Kg[:, 0] * (z[l] - rq)
+        S = (np.eye(3) - Kg @ H) @ S
+    return mu, S
+
+
+def test_linear_run_equals_numpy_chain(ctx, plan):
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    T, L = plan["trajectory"].shape[1], plan["landmarks"].shape[1]
+    normals = np.random.Generator(np.random.PCG64(9)).standard_normal((T - 1) * (3 + L))
+    ht = abi.host_thread(plan, normals)
+    A = np.array([[0.0, 1.0, 0.0], [1.0, 0.3, 0.0], [-1.0, 0.0, 0.0]])
+    b = np.array([1.08, 2.9, 3.6])
+    out = ctx.linear_run(plan, 2, A, b, normals=normals, record=True)
+    # restatement: K identical components stay identical, so one component carries the whole chain
+    alphas = np.asarray(plan["alphas"])
+    mu, S = plan["trajectory"][:, 0].copy(), np.asarray(plan["cov0"], dtype=np.float64).reshape(3, 3).copy()
+    probs = []
+    for t in range(T):
+        np.testing.assert_allclose(out["gmm_pre"][t, 0, 1:4], mu, rtol=1e-9, atol=1e-11)
+        m2, c2, pv = abi.truncate_linear(mu, S, A, b)
+        probs.append(1.0 - np.prod(1.0 - pv))
+        mu, S = m2, c2
+        if t < T - 1:
+            us = plan["odometry"][:, t]
+            r1, tr, r2 = us[0] ** 2, us[1] ** 2, us[2] ** 2
+            M = np.array([alphas[0] * r1 + alphas[1] * tr, alphas[2] * tr + alphas[3] * r1 + alphas[3] * r2, alphas[0] * r2 + alphas[1] * tr])
+            mu, S = _ekf_step(mu, S, ht["applied"][:, t], M, ht["obs"][t], plan["landmarks"], float(plan["Q"]))
+    np.testing.assert_allclose(out["probabilities"], probs, rtol=1e-8, atol=1e-12)
+    np.testing.assert_allclose(out["P"], 1.0 - np.prod(1.0 - np.array(probs)), rtol=1e-9)
+    np.testing.assert_allclose(out["gmm_post"][:, 0], [0.5, 0.5], rtol=1e-12)
+    assert 0.05 < out["P"] < 1.0
+    none = ctx.linear_run(plan, 3, np.zeros((0, 3)), np.zeros(0), normals=normals)
+    assert none["P"] == 0.0 and np.all(none["probabilities"] == 0.0)
+
+
+def test_linear_run_agrees_with_the_sampled_truncation_on_a_half_plane_scene(ctx, plan, scenes):
+    """A point robot (0.2 mm hull) and one wall y >= 1.08 (a 100 m x 10 m box): the reference's sampled truncation (K = 1:
+    the mean and covariance of the samples on the free side) and the analytic truncation against y <= 1.08 estimate the
+    same per-waypoint probabilities; same shared real-robot thread (same seed and stream) on both sides."""
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    y_wall = 1.08
+    boxes = np.array([[0.0, y_wall + 5.0, 1.0, 0.0, 50.0, 5.0, 0.0, 1.0]])
+    hulls = np.array([[0.0, 0.0, 1.0, 0.0, 1e-4, 1e-4, 0.0, 1.0]])
+    ctx.set_scene(boxes, hulls)
+    ps, pl = [], []
+    for stream in range(6):
+        s = ctx.gmm_run(plan, 1, 200000, mode=abi.MODE_PHILOX, stream_id=stream)
+        a = ctx.linear_run(plan, 1, [[0.0, 1.0, 0.0]], [y_wall - 1e-4], stream_id=stream)
+        ps.append(s["probabilities"]); pl.append(a["probabilities"])
+        assert abs(s["P"] - a["P"]) < 0.03, (stream, s["P"], a["P"])
+    ps, pl = np.array(ps), np.array(pl)
+    print("half-plane scene: P sampled %s, analytic %s" % (np.round(1 - np.prod(1 - ps, axis=1), 4), np.round(1 - np.prod(1 - pl, axis=1), 4)))
+    assert np.max(np.abs(ps - pl)) < 0.02
+    assert (1 - np.prod(1 - pl, axis=1)).max() > 0.05        # the wall is felt
+    ctx.set_scene(scenes["pr2test2"]["boxes"], scenes["pr2test2"]["hulls"])
+
+
+def test_run_linear_estimation_command(plan):
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    mod = pcoll_b200.MCModule(os.path.join(ROOT, "data", "scenes", "pr2test2.env.xml"), device=0)
+    pcoll_b200.push_parameters(mod, plan, num_particles=1000, num_gaussians=2, num_gmm_samples=1000)
+    mod.SendCommand("setSeed 21")
+    assert float(mod.SendCommand("runLinearEstimation")) == 0.0            # no constraints: nothing to hit
+    # the pr2test2 room as a window (the walls' inner faces minus the robot's half width) and the MidWall side of the door
+    mod.SendCommand("setConstraints 2  0 0 0 -3.45 3.45 -1.45 1.45   0 1 1.3 -inf inf -inf inf")
+    mod.SendCommand("setSeed 21")
+    P = float(mod.SendCommand("runLinearEstimation"))
+    probs = np.array(mod.SendCommand("getWaypointProbabilities").split(), dtype=np.float64)
+    assert 0.0 < P < 1.0 and probs.shape[0] == plan["trajectory"].shape[1]
+    assert abs((1 - np.prod(1 - probs)) - P) < 1e-5
+    ctx = abi.Context(0)
+    try:
+        A = [[-1, 0, 0], [1, 0, 0], [0, -1, 0], [0, 1, 0], [0, 1, 0]]
+        b = [3.45, 3.45, 1.45, 1.45, 1.3]
+        ref = ctx.linear_run(plan, 2, A, b, seed=21, stream_id=0)
+    finally:
+        ctx.close()
+    np.testing.assert_allclose(probs, ref["probabilities"], rtol=1e-12, atol=1e-15)
+    with pytest.raises(pcoll_b200.McsimError):
+        mod.SendCommand("setConstraints 1 0 1 2")
+    mod.close()
