@@ -54,6 +54,9 @@ const char* mcsim_last_error(mcsim_handle* h);
  * number of rows available. */
 int mcsim_get_boxes(mcsim_handle* h, double* out, int cap_rows);
 int mcsim_get_hulls(mcsim_handle* h, double* out, int cap_rows);
+/* convex-polygon robot hulls (<Geom type="prism"> of the robot file, or setRobotPolygons): rows of 19 doubles =
+ * n, zlo, zhi, x0, y0, ..., x7, y7 (counter-clockwise, robot frame) */
+int mcsim_get_poly_hulls(mcsim_handle* h, double* out, int cap_rows);
 /* x, y, yaw of the <Robot> element; returns 0 if the scene had none */
 int mcsim_get_robot_pose(mcsim_handle* h, double pose[3]);
 

@@ -30,6 +30,8 @@ extern "C" {
 
 #define MCSIM_PRISM_STRIDE 8      /* cx, cy, cos(phi), sin(phi), hx, hy, zlo, zhi */
 #define MCSIM_MAX_HULLS 8
+#define MCSIM_MAX_POLY_HULLS 4     /* convex-polygon robot hulls (mcsim_cuda_set_scene_ex) */
+#define MCSIM_POLY_STRIDE 19       /* n, zlo, zhi, x0, y0, ..., x7, y7: counter-clockwise, robot frame, at most 8 vertices */
 #define MCSIM_MAX_PAIRS 1024      /* live (hull, box) pairs held in __constant__ memory */
 #define MCSIM_MAX_LANDMARKS 16
 #define MCSIM_MAX_WAYPOINTS 1024
@@ -77,6 +79,14 @@ int mcsim_cuda_measure_peak(mcsim_cuda_ctx* ctx, int which, double ms, double* o
  * an FP32 table in __constant__ memory, grouped by hull. */
 int mcsim_cuda_set_scene(mcsim_cuda_ctx* ctx, const double* boxes, int n_boxes,
                          const double* hulls, int n_hulls);
+/* The same with robot hulls beyond boxes (the PR2 model the reference loads at pr2test2.env.xml:120 is
+ * not a set of boxes): poly_hulls = n_poly x MCSIM_POLY_STRIDE doubles, each a convex polygon in the robot frame
+ * extruded over [zlo, zhi].  n_hulls may then be 0.  Polygon hulls are tested by the scalar kernels (2.5-D SAT on the
+ * box's axes and the polygon's edge normals): MC replay / Philox (the precise kernel) and the per-waypoint GMM kernels
+ * in Philox mode; the packed kernels' tables hold box hulls only, so batched scoring, batched GMM runs and the GMM replay
+ * mode refuse a scene with polygon hulls (MCSIM_ERR_ARG). */
+int mcsim_cuda_set_scene_ex(mcsim_cuda_ctx* ctx, const double* boxes, int n_boxes, const double* hulls, int n_hulls,
+                            const double* poly_hulls, int n_poly);
 
 /* ---- Monte-Carlo rollouts --------------------------------------------------------------- */
 typedef struct {
@@ -426,6 +436,8 @@ void mcsim_cuda_group_destroy(mcsim_cuda_group* g);
 int mcsim_cuda_group_size(const mcsim_cuda_group* g);
 mcsim_cuda_ctx* mcsim_cuda_group_ctx(mcsim_cuda_group* g, int i);
 int mcsim_cuda_group_set_scene(mcsim_cuda_group* g, const double* boxes, int n_boxes, const double* hulls, int n_hulls);
+int mcsim_cuda_group_set_scene_ex(mcsim_cuda_group* g, const double* boxes, int n_boxes, const double* hulls, int n_hulls,
+                                  const double* poly_hulls, int n_poly);
 int mcsim_cuda_group_mc_run(mcsim_cuda_group* g, const mcsim_mc_params* p, mcsim_mc_result* r);
 int mcsim_cuda_group_em_fit(mcsim_cuda_group* g, const mcsim_em_params* p, mcsim_em_result* r);
 int mcsim_cuda_group_score_plans(mcsim_cuda_group* g, const mcsim_score_params* p, mcsim_score_result* r);

@@ -54,6 +54,8 @@ typedef struct {
     int n_boxes;
     const double* hulls;    // n_hulls x 8
     int n_hulls;
+    const double* poly_hulls;  // n_poly_hulls x 19 (sat_cpu.h), may be NULL
+    int n_poly_hulls;
 } ref_params;
 
 typedef struct {
@@ -200,6 +202,7 @@ int ref_mc_run(const ref_params* p, const double* draws, size_t n_draws, uint64_
         if (rec) ctx.rec = *rec;
         ctx.scene.boxes = p->boxes; ctx.scene.n_boxes = p->n_boxes;
         ctx.scene.hulls = p->hulls; ctx.scene.n_hulls = p->n_hulls;
+        ctx.scene.poly_hulls = p->poly_hulls; ctx.scene.n_poly_hulls = p->n_poly_hulls;
         ctx.calls = 0; ctx.group = size_t(p->n_particles); ctx.T = p->path_length; ctx.K = 0; ctx.gmm_mode = false;
         ctx.sim = nullptr;
         env->check = check_hook; env->check_ctx = &ctx;
@@ -239,6 +242,7 @@ int ref_gmm_run(const ref_params* p, const double* draws, size_t n_draws, uint64
         if (rec) ctx.rec = *rec;
         ctx.scene.boxes = p->boxes; ctx.scene.n_boxes = p->n_boxes;
         ctx.scene.hulls = p->hulls; ctx.scene.n_hulls = p->n_hulls;
+        ctx.scene.poly_hulls = p->poly_hulls; ctx.scene.n_poly_hulls = p->n_poly_hulls;
         ctx.calls = 0; ctx.group = size_t(p->n_gmm_samples); ctx.T = p->path_length; ctx.K = p->n_gaussians; ctx.gmm_mode = true;
         ctx.sim = nullptr;
         env->check = check_hook; env->check_ctx = &ctx;
@@ -320,6 +324,7 @@ void ref_cov(const double* A, int n_rows, int n_cols, double* out /* n_cols x n_
 double ref_clearance(const ref_params* p, const double pose[3]) {
     sat_scene sc;
     sc.boxes = p->boxes; sc.n_boxes = p->n_boxes; sc.hulls = p->hulls; sc.n_hulls = p->n_hulls;
+    sc.poly_hulls = p->poly_hulls; sc.n_poly_hulls = p->n_poly_hulls;
     return sat_clearance(&sc, pose);
 }
 

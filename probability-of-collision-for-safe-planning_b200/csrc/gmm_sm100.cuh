@@ -325,6 +325,7 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
                 hit = robot_hits_grouped(a.sat2, xf, yf, cs, sn);
                 tested = c_scene.n_pairs;
             }
+            if (c_scene.n_poly && poly_clearance(xf, yf, cs, sn, tested) <= 0.f) hit = true;   // polygon hulls: every live pair
             if (valid) my_tests += tested;
         }
         if (a.free_out) {   // warp-aggregated append of the free samples

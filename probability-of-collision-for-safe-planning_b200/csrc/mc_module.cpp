@@ -73,6 +73,7 @@ const MCModule::Command MCModule::kCommands[] = {
     {"getDevices", &MCModule::getDevices, "the CUDA ordinals in use"},
     {"describeRun", &MCModule::describeRun, "describeRun [k]: Philox key, first rollout id and rollout count of the k-th runSimulation from now (default 0 = the next one), then key and stream id of the k-th runGMMEstimation"},
     {"setGeometry", &MCModule::setGeometry, "setGeometry <n_boxes> <n_hulls> <8 numbers per prism ...>: replace the collision geometry"},
+    {"setRobotPolygons", &MCModule::setRobotPolygons, "setRobotPolygons <n> then per hull: zlo zhi m x0 y0 ... x(m-1) y(m-1): convex-polygon robot hulls (robot frame, 3..8 vertices) next to / instead of the box hulls"},
     {"setScene", &MCModule::setScene, "setScene <env.xml> [fixture_dir ...]: extract the collision geometry from an OpenRAVE env XML"},
     {"getWaypointProbabilities", &MCModule::getWaypointProbabilities, "per-waypoint colliding fraction of the last runGMMEstimation"},
     {"getFirstHitHistogram", &MCModule::getFirstHitHistogram, "rollouts whose first hit is at waypoint t, last runSimulation"},
@@ -97,7 +98,7 @@ void MCModule::open_devices(const std::vector<int>& devices) {
     group_ = g;
     ctx_ = mcsim_cuda_group_ctx(g, 0);
     try {
-        if (scene_.n_hulls() > 0) upload_scene();
+        if (scene_.n_hulls() + scene_.n_poly_hulls() > 0) upload_scene();
     } catch (...) {
         mcsim_cuda_group_destroy(g);
         group_ = old;
@@ -109,7 +110,8 @@ void MCModule::open_devices(const std::vector<int>& devices) {
 
 void MCModule::upload_scene() {
     if (!group_) return;  // parse-only module
-    cuda_check(mcsim_cuda_group_set_scene(group_, scene_.boxes.data(), scene_.n_boxes(), scene_.hulls.data(), scene_.n_hulls()), "mcsim_cuda_set_scene");
+    cuda_check(mcsim_cuda_group_set_scene_ex(group_, scene_.boxes.data(), scene_.n_boxes(), scene_.hulls.data(), scene_.n_hulls(),
+                                             scene_.poly_hulls.data(), scene_.n_poly_hulls()), "mcsim_cuda_set_scene");
 }
 
 void MCModule::io_bytes(uint64_t* h2d, uint64_t* d2h) const { mcsim_cuda_io_bytes(ctx_, h2d, d2h); }

@@ -45,7 +45,7 @@ void MCModule::fill_params(mcsim_mc_params& p) const {
     if (odometry_.size() != size_t(3) * (path_length_ - 1)) throw std::runtime_error("setOdometry has not been sent (or was sent before a different setPathLength)");
     if (landmarks_.size() != size_t(2) * num_landmarks_) throw std::runtime_error("setNumLandmarks / setLandmarks have not been sent");
     if (!cov0_set_) throw std::runtime_error("setInitialCovariance has not been sent");
-    if (scene_.n_hulls() < 1) throw std::runtime_error("no collision geometry: create the module with a scene, or send setScene / setGeometry");
+    if (scene_.n_hulls() + scene_.n_poly_hulls() < 1) throw std::runtime_error("no collision geometry: create the module with a scene, or send setScene / setGeometry");
     std::memset(&p, 0, sizeof(p));
     p.T = path_length_;
     p.trajectory = trajectory_.data();
@@ -388,13 +388,30 @@ bool MCModule::setGeometry(std::ostream&, std::istream& sinput) {
     return true;
 }
 
+bool MCModule::setRobotPolygons(std::ostream&, std::istream& sinput) {
+    int n = -1;
+    if (!(sinput >> n) || n < 0 || n > MCSIM_MAX_POLY_HULLS) throw std::runtime_error("setRobotPolygons: a hull count 0.." + std::to_string(MCSIM_MAX_POLY_HULLS) + " expected");
+    std::vector<double> rows;
+    for (int h = 0; h < n; ++h) {
+        double zlo, zhi;
+        int m;
+        if (!(sinput >> zlo >> zhi >> m) || m < 3 || m > 8 || !(zlo < zhi)) throw std::runtime_error("setRobotPolygons: zlo zhi m (3..8) expected for every hull");
+        double r[19] = {double(m), zlo, zhi};
+        for (int i = 0; i < 2 * m; ++i) if (!(sinput >> r[3 + i])) throw std::runtime_error("setRobotPolygons: too few vertex coordinates");
+        rows.insert(rows.end(), r, r + 19);
+    }
+    scene_.poly_hulls.swap(rows);
+    upload_scene();
+    return true;
+}
+
 bool MCModule::setScene(std::ostream&, std::istream& sinput) {
     std::string path, d;
     if (!(sinput >> path)) throw std::runtime_error("setScene: a path expected");
     std::vector<std::string> dirs;
     while (sinput >> d) dirs.push_back(d);
     scene_ = load_scene_xml(path, dirs);
-    if (scene_.n_hulls() < 1) throw std::runtime_error("setScene: " + path + " has no robot geometry");
+    if (scene_.n_hulls() + scene_.n_poly_hulls() < 1) throw std::runtime_error("setScene: " + path + " has no robot geometry");
     upload_scene();
     return true;
 }

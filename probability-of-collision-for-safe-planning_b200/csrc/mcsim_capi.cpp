@@ -88,6 +88,13 @@ static int copy_rows(const std::vector<double>& rows, double* out, int cap_rows)
 }
 extern "C" int mcsim_get_boxes(mcsim_handle* h, double* out, int cap_rows) { return h ? copy_rows(h->mod->scene().boxes, out, cap_rows) : 0; }
 extern "C" int mcsim_get_hulls(mcsim_handle* h, double* out, int cap_rows) { return h ? copy_rows(h->mod->scene().hulls, out, cap_rows) : 0; }
+extern "C" int mcsim_get_poly_hulls(mcsim_handle* h, double* out, int cap_rows) {
+    if (!h) return 0;
+    const std::vector<double>& rows = h->mod->scene().poly_hulls;
+    const int n = int(rows.size() / 19);
+    if (out && cap_rows > 0) std::memcpy(out, rows.data(), sizeof(double) * 19 * size_t(n < cap_rows ? n : cap_rows));
+    return n;
+}
 extern "C" int mcsim_get_robot_pose(mcsim_handle* h, double pose[3]) {
     if (!h || !h->mod->scene().has_robot) return 0;
     std::memcpy(pose, h->mod->scene().robot_pose, sizeof(double) * 3);

@@ -95,6 +95,7 @@ struct mcsim_cuda_ctx {
     // FP64 scene for the replay-mode GMM SAT
     DevBuf hulls_d, pairs_d;
     int n_hulls = 0;
+    int n_poly = 0;    // convex-polygon robot hulls (scalar kernels only)
     // orientation-grouped FP32 pair table of the packed Philox kernel (staged into shared memory)
     DevBuf sat2;
     int sat2_n = 0;  // float4 records
@@ -261,8 +262,14 @@ extern "C" int mcsim_cuda_measure_peaks(mcsim_cuda_ctx* c, double ms, double* fp
 static inline float __int_as_float_host(int v) { float f; memcpy(&f, &v, sizeof(f)); return f; }
 extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int n_boxes,
                                     const double* hulls, int n_hulls) {
-    if (!c || n_boxes < 0 || n_hulls < 1 || n_hulls > MCSIM_MAX_HULLS || !hulls || (n_boxes && !boxes))
-        return fail(MCSIM_ERR_ARG, "set_scene: bad arguments (n_boxes=%d n_hulls=%d)", n_boxes, n_hulls);
+    return mcsim_cuda_set_scene_ex(c, boxes, n_boxes, hulls, n_hulls, nullptr, 0);
+}
+
+extern "C" int mcsim_cuda_set_scene_ex(mcsim_cuda_ctx* c, const double* boxes, int n_boxes, const double* hulls, int n_hulls,
+                                       const double* poly_hulls, int n_poly) {
+    if (!c || n_boxes < 0 || n_hulls < 0 || n_hulls > MCSIM_MAX_HULLS || (n_hulls && !hulls) || (n_boxes && !boxes) ||
+        n_poly < 0 || n_poly > MCSIM_MAX_POLY_HULLS || (n_poly && !poly_hulls) || n_hulls + n_poly < 1)
+        return fail(MCSIM_ERR_ARG, "set_scene: bad arguments (n_boxes=%d n_hulls=%d n_poly=%d)", n_boxes, n_hulls, n_poly);
     CK(cudaSetDevice(c->device));
     SceneConst sc;
     memset(&sc, 0, sizeof(sc));
@@ -341,6 +348,42 @@ extern "C" int mcsim_cuda_set_scene(mcsim_cuda_ctx* c, const double* boxes, int 
         c->h_reach[h] = sqrt(hu[0] * hu[0] + hu[1] * hu[1]) + sqrt(hu[4] * hu[4] + hu[5] * hu[5]);
     }
     sc.n_pairs = int(pairs.size() / 2);
+    // ---- polygon hulls: records + their live pairs, appended behind the box hulls' pairs (scalar kernels only)
+    sc.n_poly = n_poly;
+    for (int h = 0; h < n_poly; ++h) {
+        const double* po = poly_hulls + size_t(h) * MCSIM_POLY_STRIDE;
+        const int nv = int(po[0]);
+        if (nv < 3 || nv > MCSIM_POLY_MAX_VERTICES) return fail(MCSIM_ERR_ARG, "set_scene: polygon hull %d has %d vertices (3..%d)", h, nv, MCSIM_POLY_MAX_VERTICES);
+        PolyHullRec& r = sc.poly[h];
+        r.n = nv;
+        double reach = 0;
+        for (int i = 0; i < nv; ++i) {
+            const int j = (i + 1) % nv, k = (i + 2) % nv;
+            const double ex = po[3 + 2 * j] - po[3 + 2 * i], ey = po[4 + 2 * j] - po[4 + 2 * i];
+            const double fx = po[3 + 2 * k] - po[3 + 2 * j], fy = po[4 + 2 * k] - po[4 + 2 * j];
+            const double len = sqrt(ex * ex + ey * ey);
+            if (!(len > 0) || ex * fy - ey * fx < -1e-12 * len) return fail(MCSIM_ERR_ARG, "set_scene: polygon hull %d is not convex and counter-clockwise at vertex %d", h, j);
+            const double nx = ey / len, ny = -ex / len;
+            double dmin = 1e300, dmax = -1e300;
+            for (int q = 0; q < nv; ++q) { const double d = nx * po[3 + 2 * q] + ny * po[4 + 2 * q]; dmin = d < dmin ? d : dmin; dmax = d > dmax ? d : dmax; }
+            r.vx[i] = float(po[3 + 2 * i]); r.vy[i] = float(po[4 + 2 * i]);
+            r.nx[i] = float(nx); r.ny[i] = float(ny); r.dmax[i] = float(dmax); r.dmin[i] = float(dmin);
+            reach = fmax(reach, hypot(po[3 + 2 * i], po[4 + 2 * i]));
+        }
+        if (float(reach) > sc.reach) sc.reach = float(reach);
+        r.first = int(pairs.size() / 2);
+        for (int b = 0; b < n_boxes; ++b) {
+            const double* bx = boxes + b * MCSIM_PRISM_STRIDE;
+            if (!((po[1] < bx[7]) && (bx[6] < po[2]))) continue;
+            const double p = bx[2] * bx[0] + bx[3] * bx[1], q = bx[2] * bx[1] - bx[3] * bx[0];
+            pairs.push_back(make_float4(float(bx[0]), float(bx[1]), float(bx[2]), float(bx[3])));
+            pairs.push_back(make_float4(float(bx[4]), float(bx[5]), -float(p), -float(q)));
+        }
+        r.count = int(pairs.size() / 2) - r.first;
+    }
+    c->n_poly = n_poly;
+    if (int(pairs.size() / 2) > MCSIM_MAX_PAIRS)
+        return fail(MCSIM_ERR_ARG, "set_scene: %d live (hull, box) pairs exceed MCSIM_MAX_PAIRS=%d", int(pairs.size() / 2), MCSIM_MAX_PAIRS);
     if (sc.n_pairs > MCSIM_MAX_PAIRS)
         return fail(MCSIM_ERR_ARG, "set_scene: %d live (hull, box) pairs exceed MCSIM_MAX_PAIRS=%d", sc.n_pairs, MCSIM_MAX_PAIRS);
     CK(cudaStreamSynchronize(c->stream));
@@ -600,7 +643,7 @@ static int mc_launch_impl(mcsim_cuda_ctx* c, uint64_t n, uint64_t offset, const 
     SymbolLock sym;
     { const int rb = bind_symbols(c, &c->mc_sym, sym); if (rb) return rb; }
     const bool audit = d_poses || d_clear;
-    const bool packed = p.mode == MCSIM_MODE_PHILOX && !audit && !p.precise && p.n_landmarks == 8 && c->mc_T <= MC_PLAN2_MAX_T;
+    const bool packed = p.mode == MCSIM_MODE_PHILOX && !audit && !p.precise && p.n_landmarks == 8 && c->mc_T <= MC_PLAN2_MAX_T && c->n_poly == 0;
     mc_kernel_t k = packed ? pick_packed(p.early_exit != 0, p.estimator)
                            : pick_kernel(p.mode, audit, p.early_exit != 0, p.estimator, p.n_landmarks);
     McLaunch a;
@@ -883,7 +926,7 @@ static int gmm_launch_waypoint(mcsim_cuda_ctx* c, const GmmLaunch& a_in, int mod
     const dim3 grid(gx, B);
     if (mode == MCSIM_MODE_PHILOX && a.n > (1ull << 31)) return fail(MCSIM_ERR_ARG, "gmm: Philox mode takes at most 2^31 samples per waypoint");
     a.spread = spread_flag;
-    if (mode == MCSIM_MODE_PHILOX && a.free_out) {   // EM-refit variant: the kernel that can keep the free samples
+    if (mode == MCSIM_MODE_PHILOX && (a.free_out || c->n_poly)) {   // EM-refit variant (keeps the free samples) / polygon hulls: the scalar kernel
         gmm_count_kernel<<<grid, block, 0, c->stream>>>(a);
         gmm_sample_kernel<MCSIM_MODE_PHILOX><<<grid, block, 0, c->stream>>>(a);
         c->launches += 2;
@@ -906,7 +949,7 @@ static int gmm_launch_waypoint(mcsim_cuda_ctx* c, const GmmLaunch& a_in, int mod
 // kernels (the whole GPU per waypoint), batches that fill the GPU by themselves the one-CTA-per-member kernel
 #define GMM_CLUSTER_MAX_SAMPLES 98304ull   // measured switch-over (tools/gmm_quick.py sweep, B200): 65,536: 1.18 vs 1.41 ms; 131,072: 1.62 vs 1.46 ms
 static bool gmm_cluster_fits(const mcsim_cuda_ctx* c, uint64_t n_samples, int n_runs, int kernel_choice) {
-    if (kernel_choice == MCSIM_GMM_KERNEL_PER_WAYPOINT) return false;
+    if (kernel_choice == MCSIM_GMM_KERNEL_PER_WAYPOINT || c->n_poly) return false;
     const size_t smem = sizeof(float4) * size_t(c->sat2_n) + sizeof(unsigned) * size_t(c->gmm_cull_words);
     const uint64_t most = kernel_choice == MCSIM_GMM_KERNEL_CLUSTER ? (1ull << 31) : GMM_CLUSTER_MAX_SAMPLES;   // forced: any size
     return n_samples <= most && smem <= 64 * 1024 && n_runs >= 1 && n_runs < 64;
@@ -1098,6 +1141,7 @@ extern "C" int mcsim_cuda_gmm_run(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, 
     if (N < 1) return fail(MCSIM_ERR_ARG, "gmm_run: n_samples must be positive");
     const int mode = mc->mode;
     const int per_step = 3 + L;
+    if (c->n_poly && mode == MCSIM_MODE_REPLAY) return fail(MCSIM_ERR_ARG, "gmm_run: the replay-mode (FP64) SAT holds box hulls only (the scene has %d polygon hulls)", c->n_poly);
     CK(cudaSetDevice(c->device));
     c->h2d_bytes = c->d2h_bytes = 0;
 
@@ -1501,6 +1545,7 @@ static score_kernel_t pick_score(int est, bool ee) {
 extern "C" int mcsim_cuda_score_prepare(mcsim_cuda_ctx* c, const mcsim_score_params* p) {
     if (!c || !p) return fail(MCSIM_ERR_ARG, "score: NULL context or params");
     if (!c->scene_set) return fail(MCSIM_ERR_ARG, "score: mcsim_cuda_set_scene has not been called");
+    if (c->n_poly) return fail(MCSIM_ERR_ARG, "score: batched scoring runs the packed kernel, whose tables hold box hulls only (the scene has %d polygon hulls)", c->n_poly);
     if (p->T < 2 || p->T > MCSIM_MAX_WAYPOINTS) return fail(MCSIM_ERR_ARG, "score: T=%d out of range 2..%d", p->T, MCSIM_MAX_WAYPOINTS);
     if (p->n_plans < 1 || !p->trajectories || !p->odometry) return fail(MCSIM_ERR_ARG, "score: no plans");
     if (p->n_landmarks != 8 || !p->landmarks) return fail(MCSIM_ERR_ARG, "score: this path is built for 8 landmarks (got %d)", p->n_landmarks);
@@ -1702,7 +1747,7 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
     // enough members to fill the GPU by themselves: one CTA per member for the whole run (gmm_member_run_kernel);
     // fewer: the per-waypoint kernels, several CTAs per member
     const size_t fused_smem = sizeof(float4) * size_t(c->sat2_n) + sizeof(unsigned) * size_t(c->gmm_cull_words);
-    const bool fused = B >= 64 && fused_smem <= 64 * 1024 && g->kernel == MCSIM_GMM_KERNEL_AUTO;
+    const bool fused = B >= 64 && fused_smem <= 64 * 1024 && g->kernel == MCSIM_GMM_KERNEL_AUTO && c->n_poly == 0;
     CK(cudaEventRecord(c->ev0, c->stream));
     if (fused) {
         SymbolLock sym;

@@ -79,10 +79,14 @@ extern "C" void mcsim_cuda_group_stats(const mcsim_cuda_group* g, float* collect
     if (collectives) *collectives = g ? g->collectives : 0;
 }
 
-extern "C" int mcsim_cuda_group_set_scene(mcsim_cuda_group* g, const double* boxes, int n_boxes, const double* hulls, int n_hulls) {
+extern "C" int mcsim_cuda_group_set_scene_ex(mcsim_cuda_group* g, const double* boxes, int n_boxes, const double* hulls, int n_hulls,
+                                             const double* poly_hulls, int n_poly) {
     if (!g) return fail(MCSIM_ERR_ARG, "group_set_scene: NULL group");
-    for (mcsim_cuda_ctx* c : g->ctx) { const int rc = mcsim_cuda_set_scene(c, boxes, n_boxes, hulls, n_hulls); if (rc) return rc; }
+    for (mcsim_cuda_ctx* c : g->ctx) { const int rc = mcsim_cuda_set_scene_ex(c, boxes, n_boxes, hulls, n_hulls, poly_hulls, n_poly); if (rc) return rc; }
     return MCSIM_OK;
+}
+extern "C" int mcsim_cuda_group_set_scene(mcsim_cuda_group* g, const double* boxes, int n_boxes, const double* hulls, int n_hulls) {
+    return mcsim_cuda_group_set_scene_ex(g, boxes, n_boxes, hulls, n_hulls, nullptr, 0);
 }
 
 // sum-all-reduce of one buffer per device, in place, on each device's stream (single thread: NCCL group call)

@@ -23,12 +23,26 @@ struct HullRec {
     int g_first, n_groups; // slice of the orientation-grouped table (float4 units; mc_philox2_sm100.cuh)
 };
 
+// Robot hulls beyond boxes: a convex polygon of up to 8 vertices in the robot frame, extruded in z.
+// Per edge the outward unit normal and the polygon's extent along it (max = the edge's own offset, min = the far side)
+// are folded on the host, so the device rotates 8 normals instead of projecting 8 x 8 vertices.
+#define MCSIM_POLY_MAX_VERTICES 8
+struct PolyHullRec {
+    int n;                 // vertices
+    int first, count;      // slice of c_pairs: the boxes whose z-range meets the hull's
+    int pad;
+    float vx[MCSIM_POLY_MAX_VERTICES], vy[MCSIM_POLY_MAX_VERTICES];
+    float nx[MCSIM_POLY_MAX_VERTICES], ny[MCSIM_POLY_MAX_VERTICES];      // outward edge normals (unit)
+    float dmax[MCSIM_POLY_MAX_VERTICES], dmin[MCSIM_POLY_MAX_VERTICES];  // extent of the polygon along each normal
+};
+
 struct SceneConst {
     int n_hulls;
-    int n_pairs;
+    int n_pairs;           // live (box hull, box) pairs: the packed kernels' tables cover exactly these
     float reach;           // max over hulls of |offset| + circumradius: robot bounding circle
-    float pad;
+    int n_poly;            // polygon hulls (scalar kernels only; their pairs follow the box hulls' in c_pairs)
     HullRec hulls[MCSIM_MAX_HULLS];
+    PolyHullRec poly[MCSIM_MAX_POLY_HULLS];
 };
 
 __constant__ SceneConst c_scene;
@@ -82,10 +96,42 @@ __device__ __forceinline__ bool pair_hit(const HullPose& h, const float4 lo, con
            (dbx <= fmaf(h.hx, c, fmaf(h.hy, s, hi.x))) & (dby <= fmaf(h.hx, s, fmaf(h.hy, c, hi.y)));
 }
 
+// gap of one (polygon hull, box) pair: max over the box's two axes and the polygon's edge normals of the separation of
+// the projection intervals (oracle/sat_cpu.h sat_poly_box_gap); lo / hi: the pair record of the box
+__device__ __forceinline__ float poly_pair_gap(const PolyHullRec& h, float x, float y, float ct, float st, const float4 lo, const float4 hi) {
+    float minx = 3.4e38f, maxx = -3.4e38f, miny = 3.4e38f, maxy = -3.4e38f;
+    for (int i = 0; i < h.n; ++i) {   // vertices in the box frame
+        const float wx = x + (ct * h.vx[i] - st * h.vy[i]) - lo.x, wy = y + (st * h.vx[i] + ct * h.vy[i]) - lo.y;
+        const float bx = fmaf(lo.z, wx, lo.w * wy), by = fmaf(lo.z, wy, -lo.w * wx);
+        minx = fminf(minx, bx); maxx = fmaxf(maxx, bx);
+        miny = fminf(miny, by); maxy = fmaxf(maxy, by);
+    }
+    float g = fmaxf(fmaxf(minx - hi.x, -hi.x - maxx), fmaxf(miny - hi.y, -hi.y - maxy));
+    const float rx = lo.x - x, ry = lo.y - y;   // box centre seen from the robot origin
+    for (int i = 0; i < h.n; ++i) {
+        const float nwx = ct * h.nx[i] - st * h.ny[i], nwy = st * h.nx[i] + ct * h.ny[i];   // normal in the world
+        const float cproj = fmaf(nwx, rx, nwy * ry);                                        // box centre along it, robot origin = 0
+        const float nbx = fmaf(lo.z, nwx, lo.w * nwy), nby = fmaf(lo.z, nwy, -lo.w * nwx);  // normal in the box frame
+        const float r = fmaf(hi.x, fabsf(nbx), hi.y * fabsf(nby));
+        g = fmaxf(g, fmaxf(h.dmin[i] - (cproj + r), (cproj - r) - h.dmax[i]));
+    }
+    return g;
+}
+__device__ __forceinline__ float poly_clearance(float x, float y, float ct, float st, unsigned& n_tests) {
+    float best = 3.402823466e+38f;
+    for (int hI = 0; hI < c_scene.n_poly; ++hI) {
+        const PolyHullRec& h = c_scene.poly[hI];
+        const int end = h.first + h.count;
+        for (int b = h.first; b < end; ++b) best = fminf(best, poly_pair_gap(h, x, y, ct, st, c_pairs[2 * b], c_pairs[2 * b + 1]));
+        n_tests += h.count;
+    }
+    return best;
+}
+
 // Exhaustive test of every live pair: the reference semantics (one CheckCollision = robot vs all
 // bodies).  Returns the collision flag; n_tests counts executed pair tests.
 __device__ __forceinline__ bool robot_hits(float x, float y, float ct, float st, unsigned& n_tests) {
-    bool hit = false;
+    bool hit = c_scene.n_poly ? poly_clearance(x, y, ct, st, n_tests) <= 0.f : false;
     for (int hI = 0; hI < c_scene.n_hulls; ++hI) {
         const HullRec& hr = c_scene.hulls[hI];
         const HullPose hp = place_hull(hr, x, y, ct, st);
@@ -213,7 +259,8 @@ __device__ __forceinline__ bool robot_hits_listed(const float4* __restrict__ tab
 
 // Signed clearance: min over live pairs of the pair gap (+FLT_MAX when there is no pair).
 __device__ __forceinline__ float robot_clearance(float x, float y, float ct, float st) {
-    float best = 3.402823466e+38f;
+    unsigned unused = 0;
+    float best = c_scene.n_poly ? poly_clearance(x, y, ct, st, unused) : 3.402823466e+38f;
     for (int hI = 0; hI < c_scene.n_hulls; ++hI) {
         const HullRec& hr = c_scene.hulls[hI];
         const HullPose hp = place_hull(hr, x, y, ct, st);

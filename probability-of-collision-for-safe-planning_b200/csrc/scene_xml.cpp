@@ -9,6 +9,9 @@
 //   frame of a sibling body; KinBody-level <Translation>/<RotationAxis> move the whole body; file="..." pulls
 //   geometry from another file, resolved next to the env file and then on the fixture path (ikeatable.kinbody.xml
 //   and the PR2 model are not in the reference repository); tag case varies (<translation>, pr2test2.env.xml:121).
+// Beyond the reference's files (robot hull sets that are not boxes): <Geom type="prism"> with
+//   <Vertices>x0 y0 x1 y1 ...</Vertices> (3..8 vertices of a convex polygon, either orientation) and <Height>zlo zhi
+//   </Height> in the geom's frame; accepted inside <Robot> only (obstacles stay boxes).
 // Output rows (8 doubles): cx, cy, cos(yaw), sin(yaw), hx, hy, zlo, zhi -- obstacles in the world frame, robot hulls
 // in the robot frame with absolute z (the robot's z offset from the env file applied).
 #include "scene_xml.h"
@@ -99,9 +102,10 @@ std::string resolve(const std::string& ref, const std::string& base_dir, const s
 }
 
 struct Prism { Frame f; double hx, hy, hz; };
+struct PolyPrism { Frame f; std::vector<double> xy; double zlo, zhi; };
 
 // every box geom of a <KinBody>/<Robot> element, in the frame `parent`
-void collect(const xml_lite::Node& kin, const Frame& parent, std::vector<Prism>& out) {
+void collect(const xml_lite::Node& kin, const Frame& parent, std::vector<Prism>& out, std::vector<PolyPrism>* polys = nullptr) {
     std::map<std::string, Frame> frames;
     for (const auto* body : kin.all("body")) {
         Frame f = local_frame(*body);
@@ -116,8 +120,18 @@ void collect(const xml_lite::Node& kin, const Frame& parent, std::vector<Prism>&
         if (const auto* nm = body->attr("name")) frames[*nm] = f;
         for (const auto* geom : body->all("geom")) {
             const auto* type = geom->attr("type");
+            if (type && xml_lite::lower(*type) == "prism" && polys) {
+                const auto* vt = geom->first("vertices");
+                const auto* ht = geom->first("height");
+                if (!vt || !ht) throw std::runtime_error("prism geom needs <Vertices> and <Height>");
+                const auto v = numbers(vt->text, "Vertices"), hz = numbers(ht->text, "Height");
+                if (v.size() < 6 || v.size() > 16 || v.size() % 2) throw std::runtime_error("<Vertices> needs 3..8 x y pairs");
+                if (hz.size() < 2 || !(hz[0] < hz[1])) throw std::runtime_error("<Height> needs zlo < zhi");
+                polys->push_back(PolyPrism{parent.then(f).then(local_frame(*geom)), v, hz[0], hz[1]});
+                continue;
+            }
             if (!type || xml_lite::lower(*type) != "box")
-                throw std::runtime_error("only box geoms are supported, got type='" + (type ? *type : std::string()) + "'");
+                throw std::runtime_error("only box geoms (and prism geoms in a <Robot>) are supported, got type='" + (type ? *type : std::string()) + "'");
             const auto* ext = geom->first("extents");
             if (!ext) throw std::runtime_error("box geom without <Extents>");
             const auto e = numbers(ext->text, "Extents");
@@ -125,6 +139,25 @@ void collect(const xml_lite::Node& kin, const Frame& parent, std::vector<Prism>&
             out.push_back(Prism{parent.then(f).then(local_frame(*geom)), e[0], e[1], e[2]});
         }
     }
+}
+
+// vertices into the parent frame, counter-clockwise
+void push_poly(std::vector<double>& rows, const PolyPrism& p) {
+    const size_t n = p.xy.size() / 2;
+    std::vector<double> w(2 * n);
+    const double c = std::cos(p.f.yaw), s = std::sin(p.f.yaw);
+    double area2 = 0;
+    for (size_t i = 0; i < n; ++i) {
+        w[2 * i] = p.f.x + c * p.xy[2 * i] - s * p.xy[2 * i + 1];
+        w[2 * i + 1] = p.f.y + s * p.xy[2 * i] + c * p.xy[2 * i + 1];
+    }
+    for (size_t i = 0; i < n; ++i) { const size_t j = (i + 1) % n; area2 += w[2 * i] * w[2 * j + 1] - w[2 * j] * w[2 * i + 1]; }
+    double r[19] = {double(n), p.f.z + p.zlo, p.f.z + p.zhi};
+    for (size_t i = 0; i < n; ++i) {
+        const size_t k = area2 >= 0 ? i : n - 1 - i;   // clockwise input: reversed
+        r[3 + 2 * i] = w[2 * k]; r[4 + 2 * i] = w[2 * k + 1];
+    }
+    rows.insert(rows.end(), r, r + 19);
 }
 
 void push_row(std::vector<double>& rows, const Prism& p) {
@@ -160,13 +193,15 @@ Scene load_scene_xml(const std::string& env_path, const std::vector<std::string>
         Frame zonly;
         zonly.z = top.z;  // hulls stay in the robot frame; only the robot's height is applied
         std::vector<Prism> prisms;
+        std::vector<PolyPrism> polys;
         if (const auto* file = rob->attr("file")) {
             const std::string sub = read_file(resolve(*file, base_dir, fixture_dirs));
-            collect(*xml_lite::parse(sub), zonly, prisms);
+            collect(*xml_lite::parse(sub), zonly, prisms, &polys);
         } else {
-            collect(*rob, zonly, prisms);
+            collect(*rob, zonly, prisms, &polys);
         }
         for (const auto& p : prisms) push_row(sc.hulls, p);
+        for (const auto& p : polys) push_poly(sc.poly_hulls, p);
     }
     return sc;
 }

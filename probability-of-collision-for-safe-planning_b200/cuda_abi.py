@@ -143,6 +143,8 @@ def lib():
         L.mcsim_cuda_measure_peaks.argtypes = [vp, C.c_double, _dp, _dp]
         L.mcsim_cuda_measure_peak.argtypes = [vp, C.c_int, C.c_double, _dp]
         L.mcsim_cuda_set_scene.argtypes = [vp, _dp, C.c_int, _dp, C.c_int]
+        L.mcsim_cuda_set_scene_ex.argtypes = [vp, _dp, C.c_int, _dp, C.c_int, _dp, C.c_int]
+        L.mcsim_cuda_group_set_scene_ex.argtypes = [vp, _dp, C.c_int, _dp, C.c_int, _dp, C.c_int]
         L.mcsim_cuda_mc_run.argtypes = [vp, C.POINTER(McParams), C.POINTER(McResult)]
         L.mcsim_cuda_mc_prepare.argtypes = [vp, C.POINTER(McParams)]
         L.mcsim_cuda_mc_launch.argtypes = [vp, C.c_uint64, C.c_uint64]
@@ -319,11 +321,14 @@ class Context:
         check(lib().mcsim_cuda_measure_peak(self._h, int(which), float(ms), C.byref(a)))
         return a.value
 
-    def set_scene(self, boxes, hulls):
+    def set_scene(self, boxes, hulls, poly_hulls=None):
+        """boxes [n, 8] (world), hulls [m, 8] (robot frame boxes, may be empty with polygons), poly_hulls [k, 19]:
+        convex-polygon robot hulls n, zlo, zhi, x0, y0, ... (counter-clockwise)."""
         b = np.ascontiguousarray(boxes, dtype=np.float64).reshape(-1, 8)
         h = np.ascontiguousarray(hulls, dtype=np.float64).reshape(-1, 8)
-        check(self._entry("set_scene")(self._target, dptr(b), b.shape[0], dptr(h), h.shape[0]))
-        # live (hull, box) pairs: z-intervals overlap (the same rule as mcsim_cuda_set_scene)
+        po = np.zeros((0, 19)) if poly_hulls is None else np.ascontiguousarray(poly_hulls, dtype=np.float64).reshape(-1, 19)
+        check(self._entry("set_scene_ex")(self._target, dptr(b), b.shape[0], dptr(h), h.shape[0], dptr(po), po.shape[0]))
+        # live (box hull, box) pairs: z-intervals overlap (the same rule as mcsim_cuda_set_scene)
         self.n_pairs = int(sum(((hh[6] < b[:, 7]) & (b[:, 6] < hh[7])).sum() for hh in h))
 
     def mc_run(self, params, want_counts=False, want_hist=False, audit=False):

@@ -44,6 +44,7 @@ def lib():
         L.mcsim_last_error.restype = C.c_char_p
         L.mcsim_get_boxes.argtypes = [vp, _dp, C.c_int]
         L.mcsim_get_hulls.argtypes = [vp, _dp, C.c_int]
+        L.mcsim_get_poly_hulls.argtypes = [vp, _dp, C.c_int]
         L.mcsim_get_robot_pose.argtypes = [vp, _dp]
         L.mcsim_io_bytes.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.mcsim_io_bytes.restype = None
@@ -90,7 +91,10 @@ class MCModule:
         L.mcsim_get_boxes(self._h, b.ctypes.data_as(_dp), nb)
         L.mcsim_get_hulls(self._h, h.ctypes.data_as(_dp), nh)
         has = L.mcsim_get_robot_pose(self._h, pose.ctypes.data_as(_dp))
-        return dict(boxes=b, hulls=h, robot_pose=pose if has else None)
+        npo = L.mcsim_get_poly_hulls(self._h, None, 0)
+        po = np.zeros((npo, 19))
+        L.mcsim_get_poly_hulls(self._h, po.ctypes.data_as(_dp), npo)
+        return dict(boxes=b, hulls=h, poly_hulls=po, robot_pose=pose if has else None)
 
     def io_bytes(self):
         a, b = C.c_uint64(), C.c_uint64()

@@ -57,6 +57,29 @@ d30 = 0.5 * (math.cos(math.radians(30)) + math.sin(math.radians(30)))
 add("rotated_pose_30_gap", [U], [box(1.2, 0)], [0, 0, math.pi / 6], False, 1.2 - 0.5 - d30,
     "hull rotated 30 deg reaches x = 0.5 (cos30 + sin30) = 0.68301; box left face x = 0.7 -> 0.016987; hull axes overlap (1.2 cos30 - 1.18301 < 0)")
 add("rotated_pose_30_overlap", [U], [box(1.18, 0)], [0, 0, math.pi / 6], True, 1.18 - 0.5 - d30, "box left face x = 0.68 < 0.68301")
+# ---- convex-polygon robot hulls: {n, zlo, zhi, x0, y0, ...} counter-clockwise, robot frame
+def poly(verts, z=(0.0, 1.0)):
+    flat = [c for v in verts for c in v] + [0.0] * (16 - 2 * len(verts))
+    return [len(verts), z[0], z[1]] + flat
+OCT = poly([(0.5 * math.cos(math.radians(45 * k)), 0.5 * math.sin(math.radians(45 * k))) for k in range(8)])
+TRI = poly([(0, 0), (1, 0), (0, 1)])
+apo = 0.5 * math.cos(math.radians(22.5))
+def addp(name, polys, boxes, pose, hit, gap, why, hulls=()):
+    cases.append(dict(name=name, hulls=[list(h) for h in hulls], poly_hulls=polys, boxes=boxes, pose=pose, hit=hit, gap=gap, why=why))
+addp("octagon_vertex_gap", [OCT], [box(1.01, 0)], [0, 0, 0], False, 0.01, "regular octagon, circumradius 0.5, a vertex at (0.5, 0); box face at x = 0.51: the box's x axis separates by 0.01")
+addp("octagon_vertex_overlap", [OCT], [box(0.99, 0)], [0, 0, 0], True, -0.01, "box face at x = 0.49")
+addp("octagon_edge_gap", [OCT], [box(0.77 * math.cos(math.radians(22.5)), 0.77 * math.sin(math.radians(22.5)), 0.3, 0.3, yaw=22.5)], [0, 0, 0], False, 0.77 - apo - 0.3,
+     "box face parallel to the octagon's edge between 0 and 45 deg (normal at 22.5 deg, apothem 0.5 cos 22.5 = 0.46194): 0.77 - 0.46194 - 0.3 = 0.0080602")
+addp("octagon_edge_overlap", [OCT], [box(0.75 * math.cos(math.radians(22.5)), 0.75 * math.sin(math.radians(22.5)), 0.3, 0.3, yaw=22.5)], [0, 0, 0], True, 0.75 - apo - 0.3, "0.75 - 0.76194 = -0.0119398")
+addp("triangle_hypotenuse_gap", [TRI], [box(0.8, 0.8, 0.2, 0.2)], [0, 0, 0], False, 0.2 / R2 * 1.0,
+     "right triangle (0,0) (1,0) (0,1): only its hypotenuse normal (1,1)/sqrt2 separates -- the box's axes overlap ([0.6, 1] inside [0, 1]); box corner (0.6, 0.6) projects to 0.848528, the hypotenuse to 0.707107: 0.141421")
+addp("triangle_hypotenuse_overlap", [TRI], [box(0.69, 0.69, 0.2, 0.2)], [0, 0, 0], True, 0.98 / R2 - 1 / R2, "box corner (0.49, 0.49) is 0.014142 inside the hypotenuse")
+addp("triangle_rotated_pose_gap", [TRI], [box(-0.8, 0.8, 0.2, 0.2)], [0, 0, math.pi / 2], False, 0.2 / R2, "the same triangle turned 90 deg by the robot pose: vertices (0,0) (0,1) (-1,0), mirror image of triangle_hypotenuse_gap")
+addp("polygon_z_disjoint", [poly([(0, 0), (1, 0), (0, 1)], z=(0.0, 0.3))], [box(0.2, 0.2, 0.2, 0.2, z=(0.3, 1.0))], [0, 0, 0], False, None, "z ranges touch only: no live pair")
+addp("box_and_polygon_hulls_gap", [poly([(0.4, -0.1), (0.7, -0.1), (0.7, 0.1), (0.4, 0.1)], z=(0.5, 0.9))], [box(1.0, 0, 0.25, 0.25, z=(0.5, 0.9))], [0, 0, 0], False, 0.05,
+     "a box hull (half 0.3, z 0..0.3) that cannot see the obstacle (z 0.5..0.9) and a polygon arm x in [0.4, 0.7] at z 0.5..0.9: obstacle face at x = 0.75", hulls=[[0, 0, 1, 0, 0.3, 0.3, 0.0, 0.3]])
+addp("box_and_polygon_hulls_arm_hits", [poly([(0.4, -0.1), (0.7, -0.1), (0.7, 0.1), (0.4, 0.1)], z=(0.5, 0.9))], [box(0.93, 0, 0.25, 0.25, z=(0.5, 0.9))], [0, 0, 0], True, -0.02,
+     "obstacle face at x = 0.68: 2 cm inside the arm; the base hull still cannot see it", hulls=[[0, 0, 1, 0, 0.3, 0.3, 0.0, 0.3]])
 json.dump(dict(note="hand-derived known answers for the 2.5-D SAT predicate (oracle/sat_cpu.h, csrc/sat_device.cuh); "
                "prisms are [cx, cy, cos, sin, hx, hy, zlo, zhi]; gap = expected signed SAT clearance (null: no live pair)",
                cases=cases), open("/root/repo/tests/golden/sat_cases.json", "w"), indent=1)

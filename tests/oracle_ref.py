@@ -17,6 +17,7 @@ class RefParams(C.Structure):
         ("n_particles", C.c_int), ("cov0", C.c_double * 9), ("path_length", C.c_int),
         ("trajectory", _dp), ("odometry", _dp), ("n_gaussians", C.c_int), ("n_gmm_samples", C.c_int),
         ("boxes", _dp), ("n_boxes", C.c_int), ("hulls", _dp), ("n_hulls", C.c_int),
+        ("poly_hulls", _dp), ("n_poly_hulls", C.c_int),
     ]
 
 
@@ -56,7 +57,7 @@ def _d(a):
     return a.ctypes.data_as(_dp)
 
 
-def make_params(plan, boxes, hulls, n_particles=1000, n_gaussians=3, n_gmm_samples=1000):
+def make_params(plan, boxes, hulls, n_particles=1000, n_gaussians=3, n_gmm_samples=1000, poly_hulls=None):
     keep = dict(
         tr=np.ascontiguousarray(plan["trajectory"], dtype=np.float64),
         od=np.ascontiguousarray(plan["odometry"], dtype=np.float64),
@@ -76,13 +77,16 @@ def make_params(plan, boxes, hulls, n_particles=1000, n_gaussians=3, n_gmm_sampl
     p.n_gaussians, p.n_gmm_samples = int(n_gaussians), int(n_gmm_samples)
     p.boxes, p.n_boxes = _d(keep["bx"]), keep["bx"].shape[0]
     p.hulls, p.n_hulls = _d(keep["hu"]), keep["hu"].shape[0]
+    if poly_hulls is not None:
+        keep["po"] = np.ascontiguousarray(poly_hulls, dtype=np.float64).reshape(-1, 19)
+        p.poly_hulls, p.n_poly_hulls = _d(keep["po"]), keep["po"].shape[0]
     return p, keep
 
 
-def mc_run(plan, boxes, hulls, n_particles, draws=None, mt_seed=0, record=True):
+def mc_run(plan, boxes, hulls, n_particles, draws=None, mt_seed=0, record=True, poly_hulls=None):
     """Runs the reference's runSimulation().  Returns dict(P, counts[N], final[N,3], and when
     record: poses[T,N,3], clearance[T,N], flags[T,N], mu_path[T,3], cov_path[T,9])."""
-    p, keep = make_params(plan, boxes, hulls, n_particles=n_particles)
+    p, keep = make_params(plan, boxes, hulls, n_particles=n_particles, poly_hulls=poly_hulls)
     T, N = p.path_length, int(n_particles)
     rec = RefRecord()
     out = {}

@@ -3,7 +3,7 @@
 The reference's own checker (ODE + the PR2 mesh) is not in its repository, so the GPU SAT (csrc/sat_device.cuh) and the
 oracle's CPU SAT (oracle/sat_cpu.h) are both restatements of one formula.  Two things here are NOT that formula:
 
-* tests/golden/sat_cases.json -- 30 hand-derived known answers (face contact counts as a hit, 45-degree corner-to-edge
+* tests/golden/sat_cases.json -- 40 hand-derived known answers (10 of them for convex-polygon robot hulls) (face contact counts as a hit, 45-degree corner-to-edge
   gaps that only the box's own axis separates, z-disjoint prisms, nesting, zero-extent boxes, hull yaw / offset / robot
   pose, the pr2custom spike tip at y = -1.133), each with its derivation; checked against sat_cpu.h (CPU) and against the
   device audit path (GPU).
@@ -30,7 +30,7 @@ def _boxes(case):
     return np.asarray(case["boxes"], dtype=np.float64).reshape(-1, 8)
 
 
-def _sat_cpu(boxes, hulls, pose):
+def _sat_cpu(boxes, hulls, pose, poly_hulls=None):
     """oracle/sat_cpu.h through oracle/_ref (ref_clearance)."""
     import oracle_ref
     b = np.ascontiguousarray(boxes, dtype=np.float64).reshape(-1, 8)
@@ -38,6 +38,9 @@ def _sat_cpu(boxes, hulls, pose):
     p = oracle_ref.RefParams()
     p.boxes, p.n_boxes = b.ctypes.data_as(oracle_ref._dp), b.shape[0]
     p.hulls, p.n_hulls = h.ctypes.data_as(oracle_ref._dp), h.shape[0]
+    if poly_hulls is not None and len(poly_hulls):
+        po = np.ascontiguousarray(poly_hulls, dtype=np.float64).reshape(-1, 19)
+        p.poly_hulls, p.n_poly_hulls = po.ctypes.data_as(oracle_ref._dp), po.shape[0]
     ps = (C.c_double * 3)(*[float(v) for v in pose])
     return oracle_ref.lib().ref_clearance(C.byref(p), ps)
 
@@ -47,7 +50,7 @@ def test_sat_cpu_known_answers(case):
     import oracle_ref
     if not oracle_ref.available():
         pytest.skip("oracle/_ref not built")
-    g = _sat_cpu(_boxes(case), case["hulls"], case["pose"])
+    g = _sat_cpu(_boxes(case), case["hulls"], case["pose"], case.get("poly_hulls"))
     if case["gap"] is None:
         assert g > 1e300 and not case["hit"]        # no live pair: +DBL_MAX
     else:
@@ -139,6 +142,27 @@ def test_second_algorithm_agrees_with_sat_cpu_on_random_pairs():
         bad.size, n, bad[:5], gaps[bad[0]])
 
 
+def test_polygon_path_equals_box_path_for_rectangles():
+    """A box hull handed over as a 4-vertex polygon: the polygon SAT (box axes + edge normals) must give the box SAT's gap."""
+    import oracle_ref
+    if not oracle_ref.available():
+        pytest.skip("oracle/_ref not built")
+    rng = np.random.Generator(np.random.PCG64(5))
+    for _ in range(2000):
+        ox, oy, psi = rng.uniform(-0.3, 0.3), rng.uniform(-0.3, 0.3), rng.uniform(0, 2 * np.pi)
+        hx, hy = rng.uniform(0.05, 0.6, 2)
+        box = [rng.normal(0, 0.8), rng.normal(0, 0.8), 0, 0, rng.uniform(0.02, 1.0), rng.uniform(0.02, 1.0), 0.0, 1.0]
+        phi = rng.uniform(0, 2 * np.pi)
+        box[2], box[3] = np.cos(phi), np.sin(phi)
+        pose = [rng.uniform(-1, 1), rng.uniform(-1, 1), rng.uniform(0, 2 * np.pi)]
+        c, s_ = np.cos(psi), np.sin(psi)
+        verts = [(ox + c * ux * hx - s_ * uy * hy, oy + s_ * ux * hx + c * uy * hy) for ux, uy in ((1, 1), (-1, 1), (-1, -1), (1, -1))]
+        po = [4, 0.0, 1.0] + [v for xy in verts for v in xy] + [0.0] * 8
+        a = _sat_cpu([box], [[ox, oy, c, s_, hx, hy, 0.0, 1.0]], pose)
+        b = _sat_cpu([box], np.zeros((0, 8)), pose, [po])
+        assert abs(a - b) < 1e-12, (a, b)
+
+
 @pytest.mark.gpu
 def test_device_sat_known_answers(ctx, plan):
     """The same known answers through the device: replay mode, one rollout, one waypoint, z0 = 0 (x0 = the pose),
@@ -149,7 +173,7 @@ def test_device_sat_known_answers(ctx, plan):
         one = dict(plan)
         one["trajectory"] = np.asarray(case["pose"], dtype=np.float64).reshape(3, 1)
         one["odometry"] = np.zeros((3, 0))
-        ctx.set_scene(_boxes(case), np.asarray(case["hulls"], dtype=np.float64))
+        ctx.set_scene(_boxes(case), np.asarray(case["hulls"], dtype=np.float64).reshape(-1, 8), case.get("poly_hulls"))
         p, keep = abi.make_mc_params(one, n_rollouts=1, mode=abi.MODE_REPLAY, z0=np.zeros(3), early_exit=False)
         aud = ctx.mc_run(p, want_counts=True, audit=True)
         run = ctx.mc_run(p, want_counts=True)
@@ -164,11 +188,18 @@ def test_device_sat_known_answers(ctx, plan):
             assert aud["near_contact"] == 0
         else:
             assert aud["near_contact"] == 1     # reported separately, as north_star asks
+        if case.get("poly_hulls") and abs(case["gap"]) >= NEAR:
+            # polygon hulls route Philox mode to the scalar kernel: every rollout sits at the pose (tiny start covariance)
+            tiny = dict(one)
+            tiny["cov0"] = np.eye(3) * 1e-16
+            pp, kk = abi.make_mc_params(tiny, n_rollouts=64, mode=abi.MODE_PHILOX, early_exit=False)
+            assert ctx.mc_run(pp)["hits"] == (64 if case["hit"] else 0), case["name"]
+            continue
         # the packed Philox kernel's SAT (orientation-grouped table, broad phase on and off) at the same pose:
         # a tiny start covariance puts every rollout at the pose
         tiny = dict(one)
         tiny["cov0"] = np.eye(3) * 1e-16
-        if abs(case["gap"]) >= NEAR:
+        if abs(case["gap"]) >= NEAR and not case.get("poly_hulls"):
             for ex in (False, True):
                 pp, kk = abi.make_mc_params(tiny, n_rollouts=64, mode=abi.MODE_PHILOX, early_exit=False, exhaustive=ex)
                 o = ctx.mc_run(pp)
