@@ -14,8 +14,25 @@
 #include <sstream>
 #include <stdexcept>
 
+// NVTX ranges, one per command (header-only NVTX 3: no-ops unless a profiler is attached)
+#if defined(__has_include)
+#if __has_include(<nvtx3/nvToolsExt.h>)
+#include <nvtx3/nvToolsExt.h>
+#define MCSIM_NVTX 1
+#endif
+#endif
+
 namespace mcsim {
 namespace {
+
+struct NvtxRange {
+#ifdef MCSIM_NVTX
+    explicit NvtxRange(const std::string& name) { nvtxRangePushA(("mcsim:" + name).c_str()); }
+    ~NvtxRange() { nvtxRangePop(); }
+#else
+    explicit NvtxRange(const std::string&) {}
+#endif
+};
 
 std::string lower(std::string s) {
     for (auto& ch : s) ch = char(std::tolower(static_cast<unsigned char>(ch)));
@@ -81,6 +98,12 @@ const MCModule::Command MCModule::kCommands[] = {
     {"getStats", &MCModule::getStats, "hits rollouts executed_steps pair_tests kernel_ms degenerate of the last run"},
 };
 
+std::vector<std::pair<std::string, std::string>> MCModule::command_list() {
+    std::vector<std::pair<std::string, std::string>> out;
+    for (const auto& c : kCommands) out.emplace_back(c.name, c.help);
+    return out;
+}
+
 MCModule::MCModule(const Scene& scene, int device) : scene_(scene) {
     std::random_device rd;  // the reference seeds from the clock / random device (MCSimulator.h:141 set_seed_random)
     seed_ = (uint64_t(rd()) << 32) ^ uint64_t(rd());
@@ -121,7 +144,10 @@ bool MCModule::SendCommand(std::ostream& sout, std::istream& sinput) {
     if (!(sinput >> name)) return false;
     const std::string key = lower(name);
     for (const auto& c : kCommands)
-        if (lower(c.name) == key) return (this->*c.fn)(sout, sinput);
+        if (lower(c.name) == key) {
+            NvtxRange range(c.name);
+            return (this->*c.fn)(sout, sinput);
+        }
     throw std::runtime_error("unknown command '" + name + "' (send 'help' for the list)");
 }
 

@@ -11,6 +11,7 @@
 #include <functional>
 #include <iosfwd>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "mcsim_cuda.h"
@@ -39,6 +40,8 @@ class MCModule {
     // Convenience for the C ABI: never throws; the message of a failure is kept in last_error().
     bool SendCommand(const std::string& line, std::string& out);
     const std::string& last_error() const { return err_; }
+    // every command name with its help string (what a front end registers: openrave_adapter.cpp)
+    static std::vector<std::pair<std::string, std::string>> command_list();
     const Scene& scene() const { return scene_; }
     void io_bytes(uint64_t* h2d, uint64_t* d2h) const;
 

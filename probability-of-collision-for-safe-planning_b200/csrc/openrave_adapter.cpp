@@ -80,15 +80,12 @@ class MCModuleAdapter : public ModuleBase {
             else if (tok.compare(0, 7, "device=") == 0) device = std::atoi(tok.c_str() + 7);
         }
         impl_.reset(new mcsim::MCModule(xml.empty() ? scene_from_environment(penv) : mcsim::load_scene_xml(xml, fixtures), device));
-        // the reference's 15 RegisterCommand names (mcsimplugin.cpp:13-44) plus this build's additions
-        std::istringstream names(
-            "MyCommand ArmaCommand setAlphas setQ setNumLandmarks setLandmarks setNumParticles setInitialCovariance "
-            "setPathLength setTrajectory setOdometry runSimulation setNumGaussians runGMMEstimation setNumGMMSamples "
-            "setSeed setMode setDrawsFile setDraws setGMMCountsFile setGMMCounts setEarlyExit setEstimator setRolloutOffset "
-            "setGeometry setScene getWaypointProbabilities getFirstHitHistogram getGMM getStats");
-        std::string name;
-        while (names >> name)
-            RegisterCommand(name, boost::bind(&MCModuleAdapter::Forward, this, name, _1, _2), "see INTEGRATION.md");
+        // every command of mcsim::MCModule -- the reference's 15 RegisterCommand names (mcsimplugin.cpp:13-44) and this
+        // build's additions -- straight from its table, so the two front ends cannot drift apart ("help" is OpenRAVE's own)
+        for (const auto& cmd : mcsim::MCModule::command_list()) {
+            if (cmd.first == "help") continue;
+            RegisterCommand(cmd.first, boost::bind(&MCModuleAdapter::Forward, this, cmd.first, _1, _2), cmd.second);
+        }
     }
     virtual ~MCModuleAdapter() {}
 

@@ -1,6 +1,6 @@
 // philox.h -- counter-based Philox4x32-10 (Salmon et al., "Parallel random numbers: as easy as
 // 1, 2, 3", SC'11) and the Box-Muller transform used for every noise draw of the Philox mode.
-// Host + device; the CPU oracle port (oracle/port/) has its own independent restatement.
+// Host + device.
 //
 // Replaces, for Philox mode, the reference's global Mersenne-Twister stream behind arma::randn()
 // (armadillo-8.400.0/include/armadillo_bits/arma_rng.hpp:320-436) with one independent subsequence
