@@ -49,6 +49,7 @@ struct McLaunch {
     // exact broad phase of the packed kernel (mc_philox2_sm100.cuh); cull == nullptr: every live pair at every step
     const unsigned* cull;         // per-waypoint candidate lists, cull_words 32-bit words
     int cull_words;
+    const float2* nominal;        // [T] (x*_t, y*_t): centres of the lists for the replay kernel (the packed kernels read c_plan2)
 };
 
 // FP64 angle in [0, 4 pi] -> FP32 angle in [-pi, pi] (rounding error <= 1.2e-7 rad, not accumulated)
@@ -73,9 +74,20 @@ __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
     if (threadIdx.x < 4) s_cnt[threadIdx.x] = 0;
     __syncthreads();
 
-    unsigned my_hits = 0, my_near = 0, my_steps = 0, my_tests = 0;
+    unsigned my_hits = 0, my_near = 0;
+    unsigned long long my_steps = 0, my_tests = 0;
     const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += stride) {
+    // exact broad phase of the replay mode (sat_device.cuh): the plan's candidate lists, chosen per warp and waypoint by
+    // the largest deviation of its live rollouts from x*_t -- the reference driver's default mode (one shared real robot,
+    // MCSimulation.py:238-247) spends its time in this kernel, 63 pair tests per pose without the lists
+    const bool listed = (MODE == MCSIM_MODE_REPLAY) && !AUDIT && a.cull != nullptr;
+    const int nh = c_scene.n_hulls;
+    const unsigned char* g_ccnt = reinterpret_cast<const unsigned char*>(a.cull);
+    const ushort2* g_cidx = reinterpret_cast<const ushort2*>(a.cull + (size_t(T) * nh * MC_CULL_LEVELS + 3) / 4);
+    // block-uniform trip count: lanes past the end are masked (the warp-wide reductions of the broad phase need every lane)
+    for (unsigned long long base = (unsigned long long)blockIdx.x * blockDim.x; base < a.n; base += stride) {
+        const unsigned long long i = base + threadIdx.x;
+        const bool valid = i < a.n;
         const unsigned long long id = a.offset + i;
         // ---- initial particle: x0 = mu0 + L z (initParticles, glue_mvnrnd_meat.hpp:89-147)
         // injected draws (replay with a z0 table) or the rollout's own Philox block (Philox mode, and the
@@ -93,9 +105,9 @@ __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
         double th = 0.0;  // replay mode keeps the heading in FP64 (see below)
         if (MODE == MCSIM_MODE_REPLAY) {
             // FP64 for the start pose only (3 FMAs): the injected draws are FP64
-            const double z0 = injected ? a.z0[3 * i] : double(z[0]);
-            const double z1 = injected ? a.z0[3 * i + 1] : double(z[1]);
-            const double z2 = injected ? a.z0[3 * i + 2] : double(z[2]);
+            const double z0 = (injected && valid) ? a.z0[3 * i] : double(z[0]);
+            const double z1 = (injected && valid) ? a.z0[3 * i + 1] : double(z[1]);
+            const double z2 = (injected && valid) ? a.z0[3 * i + 2] : double(z[2]);
             p[0] = float(c_mc.mu0d[0] + c_mc.chold[0] * z0);
             p[1] = float(c_mc.mu0d[1] + c_mc.chold[1] * z0 + c_mc.chold[2] * z1);
             th = c_mc.mu0d[2] + c_mc.chold[3] * z0 + c_mc.chold[4] * z1 + c_mc.chold[5] * z2;
@@ -123,6 +135,7 @@ __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
         // 55 steps (measured); x and y stay FP32.  Only the reduced angle is rounded to FP32.
         unsigned count = 0;
         int first = -1;
+        bool alive = valid;   // still being tested (early exit: until the first hit)
         for (int t = 0; t < T; ++t) {
             // ---- collision test at waypoint t (checkParticleCollisions)
             const float* q = (MODE == MCSIM_MODE_PHILOX && EST == MCSIM_EST_CLOSEDLOOP) ? real : p;
@@ -130,26 +143,42 @@ __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
             if (MODE == MCSIM_MODE_REPLAY) sincos_t(reduce_angle(th), sn, cs);
             else sincos_t(q[2], sn, cs);
             bool hit;
+            unsigned tested = 0;
             if (AUDIT) {
                 const float cl = robot_clearance(q[0], q[1], cs, sn);
                 hit = cl <= 0.0f;
-                my_near += (fabsf(cl) < a.near_eps);
-                my_tests += c_scene.n_pairs;
-                if (a.clearance) a.clearance[(size_t)t * a.n + i] = cl;
-                if (a.poses) {
-                    a.poses[((size_t)t * 3 + 0) * a.n + i] = q[0];
-                    a.poses[((size_t)t * 3 + 1) * a.n + i] = q[1];
-                    a.poses[((size_t)t * 3 + 2) * a.n + i] = (MODE == MCSIM_MODE_REPLAY) ? float(th) : q[2];
+                tested = c_scene.n_pairs;
+                if (valid) {
+                    my_near += (fabsf(cl) < a.near_eps);
+                    if (a.clearance) a.clearance[(size_t)t * a.n + i] = cl;
+                    if (a.poses) {
+                        a.poses[((size_t)t * 3 + 0) * a.n + i] = q[0];
+                        a.poses[((size_t)t * 3 + 1) * a.n + i] = q[1];
+                        a.poses[((size_t)t * 3 + 2) * a.n + i] = (MODE == MCSIM_MODE_REPLAY) ? float(th) : q[2];
+                    }
                 }
+            } else if (listed) {
+                const float2 nom = __ldg(a.nominal + t);
+                const float ex = q[0] - nom.x, ey = q[1] - nom.y;
+                const float dm = __uint_as_float(__reduce_max_sync(0xffffffffu, alive ? __float_as_uint(fmaf(ex, ex, ey * ey)) : 0u));
+                int lev = cull_level(dm);
+                const unsigned char* cc = g_ccnt + size_t(t) * nh * MC_CULL_LEVELS;
+                if (lev < MC_CULL_LEVELS && cc[lev] == MC_CULL_OVERFLOW) lev = MC_CULL_LEVELS;
+                if (lev < MC_CULL_LEVELS) hit = robot_hits_listed(a.sat2, cc, g_cidx + size_t(t) * nh * MC_CULL_CAP, lev, q[0], q[1], cs, sn, tested);
+                else hit = robot_hits(q[0], q[1], cs, sn, tested);
             } else {
-                hit = robot_hits(q[0], q[1], cs, sn, my_tests);
+                hit = robot_hits(q[0], q[1], cs, sn, tested);
             }
-            ++my_steps;
-            if (hit) {
-                if (first < 0) first = t;
-                ++count;
-                if (EARLY_EXIT) break;
+            if (alive) {
+                ++my_steps;
+                my_tests += tested;
+                if (hit) {
+                    if (first < 0) first = t;
+                    ++count;
+                    if (EARLY_EXIT) alive = false;
+                }
             }
+            if (EARLY_EXIT && !__any_sync(0xffffffffu, alive)) break;
             if (t == T - 1) break;
             // ---- move to waypoint t+1
             if (MODE == MCSIM_MODE_REPLAY) {
@@ -203,17 +232,18 @@ __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
             ++my_hits;
             atomicAdd(&s_hist[first], 1u);
         }
-        if (a.counts) a.counts[i] = count;
+        if (a.counts && valid) a.counts[i] = count;
     }
 
     // ---- aggregation: warp reduce -> shared -> one 64-bit atomic per counter per block
     my_hits = __reduce_add_sync(0xffffffffu, my_hits);
     my_near = __reduce_add_sync(0xffffffffu, my_near);
-    // steps / tests can exceed 2^32 per warp only for > 10^7 rollouts per thread: not reachable
-    const unsigned long long w_steps = __reduce_add_sync(0xffffffffu, my_steps);
-    unsigned long long w_tests = my_tests;
+    unsigned long long w_steps = my_steps, w_tests = my_tests;   // 64-bit: a 10^10-rollout precise run must not wrap
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) w_tests += __shfl_xor_sync(0xffffffffu, w_tests, o);
+    for (int o = 16; o > 0; o >>= 1) {
+        w_steps += __shfl_xor_sync(0xffffffffu, w_steps, o);
+        w_tests += __shfl_xor_sync(0xffffffffu, w_tests, o);
+    }
     if ((threadIdx.x & 31) == 0) {
         atomicAdd(&s_cnt[CNT_HITS], my_hits);
         atomicAdd(&s_cnt[CNT_NEAR], my_near);

@@ -104,7 +104,8 @@ struct mcsim_cuda_ctx {
     std::vector<int> h_pair_hull;    // per pair: hull index
     std::vector<unsigned> h_pair_sat2;  // per pair: record offset | class header offset << 16 in the grouped table
     double h_reach[MCSIM_MAX_HULLS] = {0};
-    DevBuf mc_cull;
+    DevBuf mc_cull, mc_nominal;
+    bool mc_cull_fits_smem = false;
     DevBuf seg_state[2], seg_alive;  // early exit with survivor compaction: double-buffered state of the survivors, counts per segment
     int gmm_cull_words = 0, gmm_cull_words_cached = 0;  // words of ONE plan's lists (this run / on the device)
     // the lists depend on (scene, trajectory) only: repeated runs of one plan (the reference's 200-run loop) reuse them
@@ -196,7 +197,7 @@ extern "C" void mcsim_cuda_destroy(mcsim_cuda_ctx* c) {
     cudaStreamSynchronize(c->stream);
     c->plan.release(); c->z0.release(); c->counters.release(); c->counts.release();
     c->poses.release(); c->clearance.release();
-    c->seg_state[0].release(); c->seg_state[1].release(); c->seg_alive.release();
+    c->seg_state[0].release(); c->seg_state[1].release(); c->seg_alive.release(); c->mc_nominal.release();
     c->hulls_d.release(); c->pairs_d.release(); c->sat2.release(); c->mc_cull.release(); c->gmm_cull.release(); c->gmm_nominal.release(); c->gmm_tests.release(); c->gmm_plans.release(); c->gmm_robot_normals.release();
     c->pairs_f.release(); c->sc_plans.release(); c->sc_hits.release(); c->sc_counters.release();
     c->em_x.release(); c->em_comps.release(); c->em_hefts.release(); c->em_means.release(); c->em_fcovs.release();
@@ -562,7 +563,11 @@ extern "C" int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* c, const mcsim_mc_params* p
     }
     std::vector<unsigned> cull;
     bool cull_cached = false;
-    if (!plan2.empty() && !p->exhaustive && L == 8 && c->sat2_n < 65536) {
+    // candidate lists of the exact broad phase: the packed Philox kernels (lists in shared memory) and the replay kernel
+    // (lists read from global memory); box hulls only
+    const bool lists_for_packed = !plan2.empty() && L == 8;
+    const bool lists_for_replay = p->mode == MCSIM_MODE_REPLAY;
+    if ((lists_for_packed || lists_for_replay) && !p->exhaustive && c->sat2_n < 65536 && c->n_pairs > 0 && c->n_poly == 0) {
         std::vector<double> key;
         cull_key(c, p->trajectory, 1, T, key);
         if (key == c->mc_cull_key) {
@@ -574,10 +579,14 @@ extern "C" int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* c, const mcsim_mc_params* p
             c->mc_cull_host = cull;
         }
     }
-    // the lists ride in shared memory next to the pair table; too large a plan x scene goes without them
-    if ((cull.size() * sizeof(unsigned) + sizeof(float4) * size_t(c->sat2_n)) * MC_P2_CTAS_PER_SM > 200 * 1024) cull.clear();
+    // the packed kernels keep the lists in shared memory next to the pair table; too large a plan x scene goes without them
+    c->mc_cull_fits_smem = (cull.size() * sizeof(unsigned) + sizeof(float4) * size_t(c->sat2_n)) * MC_P2_CTAS_PER_SM <= 200 * 1024;
+    if (!lists_for_replay && !c->mc_cull_fits_smem) cull.clear();
     c->mc_cull_words = int(cull.size());
+    std::vector<float2> nominal(T);
+    for (int t = 0; t < T; ++t) nominal[t] = make_float2(float(p->trajectory[t]), float(p->trajectory[T + t]));
     if (!cull.empty()) CK(c->mc_cull.reserve(cull.size() * sizeof(unsigned)));
+    CK(c->mc_nominal.reserve(sizeof(float2) * size_t(T)));
     CK(c->plan.reserve(plan.size() * sizeof(float)));
     CK(c->counters.reserve(sizeof(unsigned long long) * (4 + MCSIM_MAX_WAYPOINTS)));
     CK(cudaStreamSynchronize(c->stream));
@@ -587,6 +596,7 @@ extern "C" int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* c, const mcsim_mc_params* p
     CK(cudaMemcpyAsync(c->plan.p, plan.data(), plan.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
     c->mc_cull_uploaded = !cull.empty() && !cull_cached;
     if (!cull.empty() && !cull_cached) CK(cudaMemcpyAsync(c->mc_cull.p, cull.data(), cull.size() * sizeof(unsigned), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(c->mc_nominal.p, nominal.data(), sizeof(float2) * size_t(T), cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * (4 + T), c->stream));
     CK(cudaStreamSynchronize(c->stream));  // plan is a stack vector
     c->mc = *p;
@@ -660,9 +670,10 @@ static int mc_launch_impl(mcsim_cuda_ctx* c, uint64_t n, uint64_t offset, const 
     a.near_eps = float(p.near_eps);
     a.sat2 = (const float4*)c->sat2.p;
     a.sat2_n = c->sat2_n;
-    const bool cull = packed && c->mc_cull_words > 0;
+    const bool cull = c->mc_cull_words > 0 && (packed ? c->mc_cull_fits_smem : (p.mode == MCSIM_MODE_REPLAY && !audit));
     a.cull = cull ? (const unsigned*)c->mc_cull.p : nullptr;
     a.cull_words = cull ? c->mc_cull_words : 0;
+    a.nominal = (const float2*)c->mc_nominal.p;
     const int block = packed ? 128 : 256;
     const size_t smem = packed ? sizeof(float4) * size_t(c->sat2_n) + (cull ? sizeof(unsigned) * size_t(c->mc_cull_words) : 0)
                                : sizeof(float) * size_t(c->mc_T) * MC_PHILOX_STRIDE;
@@ -711,7 +722,7 @@ static int mc_run_begin(mcsim_cuda_ctx* c, const mcsim_mc_params* p, mcsim_mc_re
     if (rc) return rc;
     c->h2d_bytes = sizeof(McPlanConst) + sizeof(float) * size_t(p->T) * MC_PHILOX_STRIDE +
                    ((p->mode == MCSIM_MODE_PHILOX && p->T <= MC_PLAN2_MAX_T) ? sizeof(float) * size_t(p->T) * MC_PLAN2_STRIDE : 0) +
-                   (c->mc_cull_uploaded ? sizeof(unsigned) * size_t(c->mc_cull_words) : 0);
+                   (c->mc_cull_uploaded ? sizeof(unsigned) * size_t(c->mc_cull_words) : 0) + sizeof(float2) * size_t(p->T);
     c->d2h_bytes = sizeof(unsigned long long) * (4 + p->T);
     const uint64_t n = p->n_rollouts;
     const int T = p->T;

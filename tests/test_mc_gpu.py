@@ -78,6 +78,32 @@ def test_replay_early_exit_flags(ctx, plan, scenes):
     assert ee["executed_steps"] < full["executed_steps"]
 
 
+@pytest.mark.parametrize("name", ["pr2test2", "pr2custom"])
+def test_replay_broad_phase_equals_every_pair(ctx, plan, scenes, name):
+    """The replay kernel's broad phase (the plan's candidate lists, level chosen per warp: the reference driver's default
+    `shared` mode runs through it) against testing every live pair at every pose: identical per-rollout counts wherever
+    no pose is within 1e-4 m of contact (the listed pairs go through the grouped-table arithmetic, the exhaustive loop
+    through the pair table: they may round differently AT contact), with and without early exit; fewer pair tests."""
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    ctx.set_scene(scenes[name]["boxes"], scenes[name]["hulls"])
+    T = plan["trajectory"].shape[1]
+    N = 20011
+    draws = np.random.Generator(np.random.PCG64(77)).standard_normal(3 * N + 11 * (T - 1))
+    ht = abi.host_thread(plan, draws[3 * N:])
+    kw = dict(n_rollouts=N, mode=abi.MODE_REPLAY, applied=ht["applied_noisy"], z0=draws[:3 * N])
+    aud = ctx.mc_run(abi.make_mc_params(plan, early_exit=False, **kw)[0], audit=True)
+    near = (np.abs(aud["clearance"]) < NEAR_EPS).any(axis=0)
+    for ee in (False, True):
+        a = ctx.mc_run(abi.make_mc_params(plan, early_exit=ee, **kw)[0], want_counts=True, want_hist=True)
+        b = ctx.mc_run(abi.make_mc_params(plan, early_exit=ee, exhaustive=True, **kw)[0], want_counts=True, want_hist=True)
+        np.testing.assert_array_equal(a["counts"][~near], b["counts"][~near])
+        assert abs(a["hits"] - b["hits"]) <= int(near.sum())
+        assert b["pair_tests"] == b["executed_steps"] * ctx.n_pairs and a["pair_tests"] < 0.3 * b["pair_tests"]
+        print("%s ee=%d: replay kernel %.1f us with the lists (%.2f pair tests per pose), %.1f us testing all %d pairs" % (
+            name, ee, a["kernel_ms"] * 1e3, a["pair_tests"] / a["executed_steps"], b["kernel_ms"] * 1e3, ctx.n_pairs))
+
+
 def test_replay_vs_live_reference_random_draws(ctx, plan, scenes):
     """Fresh seeds and sizes (incl. ragged, non-multiple-of-warp N) against the reference run live."""
     import oracle_ref
