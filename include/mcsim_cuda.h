@@ -350,6 +350,41 @@ int mcsim_cuda_em_collect(mcsim_cuda_ctx* ctx, mcsim_em_result* r);
  * then sum of log-likelihoods. */
 void* mcsim_cuda_em_stats(mcsim_cuda_ctx* ctx, uint64_t* n_doubles);
 
+/* ---- EM fit that allocates nothing ----------------------------------------------------------- */
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The same E-step / M-step kernels as mcsim_cuda_em_fit, without a context: samples, parameters and
+ * results are the CALLER's device buffers, and the kernels' scratch (E-step constants, the FP64
+ * sufficient statistics, convergence state; MCSIM_EM_STATIC_SCRATCH_BYTES) is a file-scope __device__
+ * array of the library -- every GPU that loads the library holds it until exit.  The call makes no
+ * cudaMalloc / cudaFree / cudaMallocHost and no host heap allocation; it enqueues 1 + 1 + 2 * iters (K <= 16)
+ * launches on `stream` and returns without synchronising.  The first call on a device resolves the
+ * array's device address (cudaGetSymbolAddress), so make that call outside a capture.
+ * Limits (MCSIM_ERR_ARG beyond them): n_fits <= MCSIM_EM_STATIC_MAX_FITS, iters <= MCSIM_EM_STATIC_MAX_ITERS,
+ * K <= MCSIM_MAX_GAUSSIANS, n < 2^31 - 2^24.
+ * Every call on a device shares the one array: it is re-initialised by the call's first launch, and calls
+ * that OVERLAP on the same GPU (two streams, two threads, two processes' worth of this library in one
+ * context) race on it -- serialise them. */
+#define MCSIM_EM_STATIC_MAX_FITS 8
+#define MCSIM_EM_STATIC_MAX_ITERS 64
+#define MCSIM_EM_STATIC_SCRATCH_BYTES 32768
+typedef struct {
+    int device;                  /* CUDA device ordinal; made current by the call */
+    int K;                       /* components per fit */
+    int n_fits;                  /* independent fits, 1..MCSIM_EM_STATIC_MAX_FITS */
+    int iters;                   /* em_iter, 0..MCSIM_EM_STATIC_MAX_ITERS */
+    uint64_t n;                  /* samples per fit */
+    double var_floor;            /* <= 0: DBL_MIN */
+    const float* x;              /* DEVICE in  [n_fits][3][n] FP32, component-major per fit */
+    double* hefts;               /* DEVICE in/out [n_fits][K]: initial parameters in, fitted parameters out */
+    double* means;               /* DEVICE in/out [n_fits][K][3] */
+    double* fcovs;               /* DEVICE in/out [n_fits][K][9] */
+    double* avg_log_p;           /* DEVICE out [n_fits][iters], optional (NaN for iterations skipped after convergence) */
+    int* iters_run;              /* DEVICE out [n_fits], optional */
+    void* stream;                /* cudaStream_t; NULL = the default stream */
+} mcsim_em_static_params;
+int mcsim_cuda_em_fit_static(const mcsim_em_static_params* p);
+
 /* ---- batched plan scoring (BASELINE.json config 4) ------------------------------------------- */
 /* The Philox-mode rollout law of mcsim_cuda_mc_run (EKF_GaussProp, MCSimulator.h:649-864, one
  * real-robot / EKF thread and one particle per rollout) for n_plans plans of T waypoints against the

@@ -1802,4 +1802,114 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
     return MCSIM_OK;
 }
 
+// ---- EM fit that allocates nothing (mcsim_cuda_em_fit_static; no counterpart in the reference) ---------------------
+// The scratch of the E-step / M-step kernels lives in this file-scope array instead of a context's cudaMalloc'ed
+// buffers.  g_em_static_scratch is a HOST-side stand-in here: its device address is resolved once per device with
+// cudaGetSymbolAddress (that device current) and only that pointer is handed to kernels.
+static __device__ __align__(256) unsigned char g_em_static_scratch[MCSIM_EM_STATIC_SCRATCH_BYTES];
+
+namespace em_static {
+constexpr size_t al256(size_t v) { return (v + 255) & ~size_t(255); }
+constexpr size_t OFF_STATS = 0;
+constexpr size_t OFF_COMPS = al256(OFF_STATS + sizeof(double) * MCSIM_EM_STATIC_MAX_FITS * (MCSIM_MAX_GAUSSIANS * EM_NSTAT + 1));
+constexpr size_t OFF_TRACE = al256(OFF_COMPS + sizeof(float) * MCSIM_EM_STATIC_MAX_FITS * MCSIM_MAX_GAUSSIANS * EM_COMP_STRIDE);
+constexpr size_t OFF_OLD = al256(OFF_TRACE + sizeof(double) * MCSIM_EM_STATIC_MAX_FITS * MCSIM_EM_STATIC_MAX_ITERS);
+constexpr size_t OFF_DONE = al256(OFF_OLD + sizeof(double) * MCSIM_EM_STATIC_MAX_FITS);
+constexpr size_t OFF_ITERS = al256(OFF_DONE + sizeof(int) * MCSIM_EM_STATIC_MAX_FITS);
+constexpr size_t END = al256(OFF_ITERS + sizeof(int) * MCSIM_EM_STATIC_MAX_FITS);
+static_assert(END <= MCSIM_EM_STATIC_SCRATCH_BYTES, "mcsim_cuda_em_fit_static: scratch layout exceeds the stated maximum");
+
+struct PerDevice { unsigned char* scratch = nullptr; int n_sm = 0; };
+static PerDevice g_dev[64];
+static std::mutex g_mu;
+}  // namespace em_static
+
+// The array keeps the previous call's contents: statistics, convergence state and the trace start from scratch here.
+__global__ void __launch_bounds__(256) em_static_init_kernel(const EmLaunch a) {
+    const int F = a.n_fits, nstat = F * (a.K * EM_NSTAT + 1), ntrace = F * a.iters;
+    for (int i = threadIdx.x; i < nstat; i += blockDim.x) a.stats[i] = 0.0;
+    for (int i = threadIdx.x; i < ntrace; i += blockDim.x) a.trace[i] = __longlong_as_double(0x7ff8000000000000ll);
+    for (int i = threadIdx.x; i < F; i += blockDim.x) {
+        a.old_avg[i] = __longlong_as_double(0xfff0000000000000ll);   // -inf (:2436)
+        a.done[i] = 0;
+        a.iters_run[i] = 0;
+    }
+}
+
+extern "C" int mcsim_cuda_em_fit_static(const mcsim_em_static_params* p) {
+    using namespace em_static;
+    if (!p) return fail(MCSIM_ERR_ARG, "em_fit_static: NULL params");
+    if (p->K < 1 || p->K > MCSIM_MAX_GAUSSIANS) return fail(MCSIM_ERR_ARG, "em_fit_static: K=%d out of range 1..%d", p->K, MCSIM_MAX_GAUSSIANS);
+    if (p->n_fits < 1 || p->n_fits > MCSIM_EM_STATIC_MAX_FITS)
+        return fail(MCSIM_ERR_ARG, "em_fit_static: n_fits=%d beyond the static scratch (1..%d fits; use mcsim_cuda_em_fit for more)", p->n_fits, MCSIM_EM_STATIC_MAX_FITS);
+    if (p->iters < 0 || p->iters > MCSIM_EM_STATIC_MAX_ITERS)
+        return fail(MCSIM_ERR_ARG, "em_fit_static: iters=%d beyond the static scratch (0..%d; use mcsim_cuda_em_fit for more)", p->iters, MCSIM_EM_STATIC_MAX_ITERS);
+    if (p->n >= (1ull << 31) - (1ull << 24)) return fail(MCSIM_ERR_ARG, "em_fit_static: more than 2^31 samples per fit");
+    if (!p->x || !p->hefts || !p->means || !p->fcovs) return fail(MCSIM_ERR_ARG, "em_fit_static: x / hefts / means / fcovs must be device pointers, got NULL");
+    if (p->device < 0 || p->device >= 64) return fail(MCSIM_ERR_ARG, "em_fit_static: device %d out of range", p->device);
+    CK(cudaSetDevice(p->device));
+    PerDevice& pd = g_dev[p->device];
+    {   // set-up, once per device, with that device current
+        std::lock_guard<std::mutex> lk(g_mu);
+        if (!pd.scratch) {
+            void* ptr = nullptr;
+            CK(cudaGetSymbolAddress(&ptr, g_em_static_scratch));
+            int n_sm = 0;
+            CK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, p->device));
+            pd.n_sm = n_sm;
+            pd.scratch = (unsigned char*)ptr;
+        }
+    }
+    cudaStream_t st = (cudaStream_t)p->stream;
+    const int K = p->K, F = p->n_fits;
+    EmLaunch a;
+    memset(&a, 0, sizeof(a));
+    a.x = p->x; a.n = p->n; a.n_total = double(p->n);
+    a.K = K; a.n_fits = F; a.iters = p->iters; a.iter = 0;
+    a.var_floor = p->var_floor > 0 ? p->var_floor : DBL_MIN;
+    a.hefts = p->hefts; a.means = p->means; a.fcovs = p->fcovs;
+    a.stats = (double*)(pd.scratch + OFF_STATS);
+    a.comps = (float*)(pd.scratch + OFF_COMPS);
+    a.trace = p->avg_log_p ? p->avg_log_p : (double*)(pd.scratch + OFF_TRACE);
+    a.old_avg = (double*)(pd.scratch + OFF_OLD);
+    a.done = (int*)(pd.scratch + OFF_DONE);
+    a.iters_run = p->iters_run ? p->iters_run : (int*)(pd.scratch + OFF_ITERS);
+    em_static_init_kernel<<<1, 256, 0, st>>>(a);
+    em_mstep_kernel<<<F, 32, 0, st>>>(a, 1);   // init_constants of the initial parameters
+    CK(cudaGetLastError());
+    if (p->iters == 0) return MCSIM_OK;
+    // E-step kernel and grid: the choices of mcsim_cuda_em_estep (128-bit / bulk-copy path needs 16-byte aligned rows)
+    em_kernel_t k0, k1;
+    const bool vec = (p->n % 4) == 0 && p->n >= 4 && (reinterpret_cast<uintptr_t>(p->x) & 15) == 0;
+    size_t smem = 0;
+    if (!em_kernels(K, k0, k1, vec, smem)) return fail(MCSIM_ERR_ARG, "em_fit_static: bad K");
+    if (smem > 48 * 1024) CK(cudaFuncSetAttribute((const void*)k0, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    int occ = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)k0, 256, smem));
+    if (k1) { int o1 = 0; CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, (const void*)k1, 256, 0)); if (o1 < occ) occ = o1; }
+    if (occ < 1) occ = 1;
+    const unsigned long long resident = (unsigned long long)pd.n_sm * occ, per_cta = smem ? EM_TMA_TILE : 256ull * 8;
+    unsigned long long most = (p->n + per_cta - 1) / per_cta;
+    if (most < 1) most = 1;
+    unsigned long long chunks = 1;
+    double best = -1.0;
+    for (unsigned long long w = 1; w <= 4; ++w) {
+        unsigned long long ch = w * resident / (unsigned long long)F;
+        if (ch < 1) ch = 1;
+        if (ch > most) ch = most;
+        const unsigned long long ctas = ch * F, waves = (ctas + resident - 1) / resident;
+        const double eff = double(ctas) / double(waves * resident);
+        if (eff > best + 0.02) { best = eff; chunks = ch; }
+    }
+    const dim3 grid((unsigned)chunks, (unsigned)F);
+    for (int it = 0; it < p->iters; ++it) {
+        k0<<<grid, 256, smem, st>>>(a);
+        if (k1) k1<<<grid, 256, 0, st>>>(a);
+        em_mstep_kernel<<<F, 32, 0, st>>>(a, 0);
+        ++a.iter;
+    }
+    CK(cudaGetLastError());
+    return MCSIM_OK;
+}
+
 #include "mcsim_group.cuh"

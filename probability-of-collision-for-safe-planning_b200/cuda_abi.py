@@ -52,6 +52,18 @@ class EmParams(C.Structure):
     ]
 
 
+class EmStaticParams(C.Structure):
+    """mcsim_em_static_params (include/mcsim_cuda.h): every pointer is a DEVICE address owned by the caller."""
+    _fields_ = [
+        ("device", C.c_int), ("K", C.c_int), ("n_fits", C.c_int), ("iters", C.c_int), ("n", C.c_uint64),
+        ("var_floor", C.c_double), ("x", C.c_void_p), ("hefts", C.c_void_p), ("means", C.c_void_p), ("fcovs", C.c_void_p),
+        ("avg_log_p", C.c_void_p), ("iters_run", C.c_void_p), ("stream", C.c_void_p),
+    ]
+
+
+EM_STATIC_MAX_FITS, EM_STATIC_MAX_ITERS, EM_STATIC_SCRATCH_BYTES = 8, 64, 32768
+
+
 class EmResult(C.Structure):
     _fields_ = [
         ("hefts", _dp), ("means", _dp), ("fcovs", _dp), ("avg_log_p", _dp), ("iters_run", C.POINTER(C.c_int)),
@@ -172,6 +184,8 @@ def lib():
         L.mcsim_cuda_em_collect.argtypes = [vp, C.POINTER(EmResult)]
         L.mcsim_cuda_em_stats.argtypes = [vp, C.POINTER(C.c_uint64)]
         L.mcsim_cuda_em_stats.restype = vp
+        L.mcsim_cuda_em_fit_static.argtypes = [C.POINTER(EmStaticParams)]
+        L.mcsim_cuda_em_fit_static.restype = C.c_int
         L.mcsim_cuda_io_bytes.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.mcsim_cuda_io_bytes.restype = None
         L.mcsim_cuda_device_count.restype = C.c_int
@@ -266,6 +280,17 @@ def host_thread(plan, normals):
     if rc != 0:
         raise McsimCudaError("mcsim_host_thread error %d" % rc)
     return out
+
+
+def em_fit_static(device, x_ptr, n, K, n_fits, iters, hefts_ptr, means_ptr, fcovs_ptr, avg_log_p_ptr=None, iters_run_ptr=None,
+                  stream=None, var_floor=1e-10):
+    """mcsim_cuda_em_fit_static: the EM fit on the caller's DEVICE buffers (integer addresses), no allocation, asynchronous on
+    `stream`.  hefts / means / fcovs are updated in place."""
+    p = EmStaticParams()
+    p.device, p.K, p.n_fits, p.iters, p.n, p.var_floor = int(device), int(K), int(n_fits), int(iters), int(n), float(var_floor)
+    p.x, p.hefts, p.means, p.fcovs = x_ptr, hefts_ptr, means_ptr, fcovs_ptr
+    p.avg_log_p, p.iters_run, p.stream = avg_log_p_ptr, iters_run_ptr, stream
+    check(lib().mcsim_cuda_em_fit_static(C.byref(p)))
 
 
 class Context:
