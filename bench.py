@@ -462,6 +462,44 @@ def group_e2e_parent(a, world, per_rank):
         return per_rank
 
 
+def em_group_leg(G, n=1_000_000, iters=10, reps=5):
+    """Config 5's fit sharded over the G devices of ONE handle (mcsim_cuda_group_em_fit, samples resident): microseconds per
+    iteration with the statistics exchange fused into the M-step kernel (peer-memory push + gather) and with one
+    ncclAllReduce per iteration.  device = max over the devices of the CUDA-event time of the E / M launches; wall = host
+    clock around the call (parameter upload, download and, for the fused path, the per-device host threads included)."""
+    import pcoll_b200
+    abi, inp = pcoll_b200.cuda_abi, pcoll_b200.inputs
+    out = {}
+    try:
+        grp = abi.Group(list(range(G)))
+    except Exception as exc:
+        return {"error": repr(exc)}
+    try:
+        out["n"], out["iters"], out["default_exchange"] = n, iters, "peer" if grp.em_exchange == abi.EM_EXCHANGE_PEER else "nccl"
+        for K in (1, 3, 16):
+            x, h, m, c = inp.synthetic_em_problem(9000 + K, n, K)
+            rec = {}
+            for name, mode in (("peer", abi.EM_EXCHANGE_PEER), ("nccl", abi.EM_EXCHANGE_NCCL)):
+                try:
+                    grp.set_em_exchange(mode)
+                except abi.McsimCudaError as exc:
+                    rec[name] = {"unavailable": str(exc)}
+                    continue
+                grp.em_fit(x, h, m, c, iters)
+                dev, wall = [], []
+                for _ in range(reps):
+                    t0 = time.perf_counter()
+                    r = grp.em_fit(None, h, m, c, iters)
+                    wall.append((time.perf_counter() - t0) * 1e6 / iters)
+                    dev.append(r["kernel_ms"] * 1e3 / iters)
+                rec[name] = {"device_us_per_iter": float(np.median(dev)), "wall_us_per_iter": float(np.median(wall)),
+                             "iters_run": int(r["iters_run"][0]), "heft0": float(r["hefts"][0, 0])}
+            out["K%d" % K] = rec
+    finally:
+        grp.close()
+    return out
+
+
 def group_e2e_child(a):
     """Torch-free: one MCModule over `--group-e2e-child` devices; runSimulation of the whole e2e job, host wall clock."""
     import pcoll_b200
@@ -485,7 +523,7 @@ def group_e2e_child(a):
     hits = int(mod.SendCommand("getStats").split()[0])
     mod.close()
     print(json.dumps({"value": a.steps * n_job * T / dt, "unit": UNIT, "h2d_bytes_per_step": io[0] * G, "d2h_bytes_per_step": io[1] * G,
-                      "rollouts_per_step": n_job, "n_gpus": G, "hits_last_step": hits,
+                      "rollouts_per_step": n_job, "n_gpus": G, "hits_last_step": hits, "em_group": em_group_leg(G),
                       "api": "ONE MCModule, SendCommand('setDevices 0..%d') + SendCommand('runSimulation') -> libmcsim.so -> mcsim_cuda_group_mc_run "
                              "(rollout ids split over the devices, ncclAllReduce of the counters on the handle's communicators); no torch in this process" % (G - 1),
                       "timing": "host wall clock around K synchronous calls"}))

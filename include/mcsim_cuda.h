@@ -475,6 +475,17 @@ int mcsim_cuda_group_set_scene_ex(mcsim_cuda_group* g, const double* boxes, int 
                                   const double* poly_hulls, int n_poly);
 int mcsim_cuda_group_mc_run(mcsim_cuda_group* g, const mcsim_mc_params* p, mcsim_mc_result* r);
 int mcsim_cuda_group_em_fit(mcsim_cuda_group* g, const mcsim_em_params* p, mcsim_em_result* r);
+/* How group_em_fit exchanges the statistics every iteration.  PEER: fused into the kernels -- behind its E-step every
+ * device pushes its block into slot [rank] of every device's gather buffer with remote stores over NVLink peer memory
+ * and raises a counter there; the M-step kernel waits for the G counters and adds the slots in rank order itself
+ * (no collective launch between E- and M-step; totals bit-identical on every device).  NCCL: one ncclAllReduce per
+ * iteration.  AUTO (default): PEER when every device of the group can map every other one's memory and the group has
+ * at most 8 devices, else NCCL.  mcsim_cuda_group_em_exchange returns the mode group_em_fit will use. */
+#define MCSIM_EM_EXCHANGE_AUTO 0
+#define MCSIM_EM_EXCHANGE_NCCL 1
+#define MCSIM_EM_EXCHANGE_PEER 2
+int mcsim_cuda_group_set_em_exchange(mcsim_cuda_group* g, int mode);
+int mcsim_cuda_group_em_exchange(const mcsim_cuda_group* g);
 int mcsim_cuda_group_score_plans(mcsim_cuda_group* g, const mcsim_score_params* p, mcsim_score_result* r);
 int mcsim_cuda_group_gmm_run_batch(mcsim_cuda_group* g, const mcsim_mc_params* mc, const mcsim_gmm_batch_params* gp,
                                    mcsim_gmm_batch_result* r);

@@ -39,7 +39,19 @@ struct EmLaunch {
     int* done;             // [n_fits] 0 running, 1 converged, 2 non-finite likelihood (reference: learn() fails)
     int* iters_run;        // [n_fits]
     double* trace;         // [n_fits][iters] avg_log_p before each update
+    // ---- sharded fit with the exchange fused into the M-step kernel (mcsim_group.cuh); n_peers <= 1: stats are the totals
+    int n_peers, my_rank;                      // devices of the group, this device's position
+    double* peer_slots[8];                     // device q's gather buffer of this iteration (peer-mapped memory, q == my_rank
+                                               // included): [n_peers slots][n_fits][K * 10 + 1]; this device writes slot [my_rank]
+    unsigned long long* peer_flags[8];         // device q's arrival counters [n_fits][n_peers]; this device writes column [my_rank]
+    const double* my_slots;                    // = peer_slots[my_rank], my_flags = peer_flags[my_rank] (kept apart: a run-time
+    const unsigned long long* my_flags;        //   index into a kernel-parameter array would put the array on the stack)
+    unsigned long long wait_value;             // value a counter holds once the block of this iteration has arrived
 };
+#define EM_MAX_PEERS 8   // = the extents of peer_slots / peer_flags above
+#define EM_MSTEP_FUSED_THREADS 192   // block size of the M-step kernel when it carries the exchange (>= 10 * 16 + 1); 32 otherwise
+#define EM_DONE_EXCHANGE_TIMEOUT 3     // done[] value: a peer's statistics did not arrive within EM_PEER_TIMEOUT_CYCLES
+#define EM_PEER_TIMEOUT_CYCLES (40ll * 1000 * 1000 * 1000)   // ~20 s: a stuck peer ends the fit with an error instead of hanging the GPU
 
 // ---- E-step ------------------------------------------------------------------------------------------
 // K: components of the model; G0: first component whose statistics THIS launch accumulates (at most 8
@@ -661,7 +673,7 @@ __device__ __forceinline__ void em_constants(const double* mean, const double* C
 
 // One CTA per fit, thread g = component g.  prep_only: compute the E-step constants of the initial
 // parameters (the init_constants call that opens iteration 1) and nothing else.
-__global__ void __launch_bounds__(32) em_mstep_kernel(const EmLaunch a, int prep_only) {
+__global__ void __launch_bounds__(EM_MSTEP_FUSED_THREADS) em_mstep_kernel(const EmLaunch a, int prep_only) {
     const int fit = blockIdx.x, g = threadIdx.x, K = a.K;
     __shared__ double s_heft[MCSIM_MAX_GAUSSIANS];
     __shared__ double s_mean[MCSIM_MAX_GAUSSIANS][3];
@@ -670,6 +682,56 @@ __global__ void __launch_bounds__(32) em_mstep_kernel(const EmLaunch a, int prep
     double* fcovs = a.fcovs + (size_t)fit * K * 9;
     double* st = a.stats + (size_t)fit * (K * EM_NSTAT + 1);
     if (!prep_only && a.done[fit]) return;
+    __shared__ double s_tot[MCSIM_MAX_GAUSSIANS * EM_NSTAT + 1];
+    if (!prep_only && a.n_peers > 1) {
+        // Fused exchange (no collective launch between E- and M-step).  (1) push: this CTA stores its fit's local block
+        // into slot [my_rank] of EVERY device's gather buffer -- remote stores over NVLink peer memory, nobody waits for
+        // them -- clears the local block for the next E-step, and after a system-scope fence raises its arrival counter
+        // on every device.  (2) wait for the G counters of this fit on THIS device.  (3) add the G slots in rank order:
+        // the same order on every device, so totals, parameters and convergence decisions are bit-identical everywhere.
+        // Slots alternate between two buffers by iteration parity: a device can be one iteration ahead of a peer that
+        // is still adding up, never two (it would be waiting for that peer's next counter).
+        // Launched with EM_MSTEP_FUSED_THREADS >= 10 K + 1 threads in this mode: one statistic per thread, so the push and
+        // the gather are one round of memory latency each (with one warp the 161 doubles of K = 16 took 6 rounds, 3 us apiece).
+        const int nst = K * EM_NSTAT + 1, G = a.n_peers;
+        const size_t per_dev = (size_t)a.n_fits * nst;
+        for (int i = g; i < nst; i += blockDim.x) {
+            const double v = __ldcg(st + i);
+            st[i] = 0.0;
+#pragma unroll
+            for (int q = 0; q < EM_MAX_PEERS; ++q)
+                if (q < G) a.peer_slots[q][(size_t)a.my_rank * per_dev + (size_t)fit * nst + i] = v;
+        }
+        __threadfence_system();
+        __syncthreads();
+        unsigned long long* pf = nullptr;
+#pragma unroll
+        for (int q = 0; q < EM_MAX_PEERS; ++q)
+            if (q == g) pf = a.peer_flags[q];
+        if (g < G) *(volatile unsigned long long*)(pf + (size_t)fit * G + a.my_rank) = a.wait_value;
+        __shared__ int s_late;
+        if (g == 0) s_late = 0;
+        __syncthreads();
+        if (g < G) {
+            const volatile unsigned long long* f = a.my_flags + (size_t)fit * G + g;
+            const long long t0 = clock64();
+            while (*f < a.wait_value)
+                if (clock64() - t0 > EM_PEER_TIMEOUT_CYCLES) { s_late = 1; break; }
+            __threadfence_system();
+        }
+        __syncthreads();
+        if (s_late) { if (g == 0) a.done[fit] = EM_DONE_EXCHANGE_TIMEOUT; return; }
+        const double* slots = a.my_slots;
+        for (int i = g; i < nst; i += blockDim.x) {
+            double t = 0.0;
+#pragma unroll
+            for (int p = 0; p < EM_MAX_PEERS; ++p)
+                if (p < G) t += __ldcv(slots + p * per_dev + (size_t)fit * nst + i);
+            s_tot[i] = t;
+        }
+        __syncthreads();
+        st = s_tot;   // (the loop that clears the consumed statistics below then clears this copy)
+    }
     double C[9], mean[3], heft = 0.0;
     if (g < K) {
         heft = hefts[g];

@@ -127,6 +127,12 @@ struct mcsim_cuda_ctx {
     int sc_ee = 0, sc_est = 0;
     // EM state
     DevBuf em_x, em_comps, em_hefts, em_means, em_fcovs, em_stats, em_old, em_done, em_iters, em_trace;
+    // E-step launch configuration of the prepared fit (kernel choice, occupancy query and wave fitting done once, not per iteration)
+    void (*em_k0)(const EmLaunch) = nullptr;
+    void (*em_k1)(const EmLaunch) = nullptr;
+    size_t em_smem = 0;
+    unsigned em_chunks = 0;
+    DevBuf em_slots, em_flags;   // fused exchange of a sharded fit (mcsim_group.cuh): gather buffer [2][G][n_stats], counters [n_fits][G]
     EmLaunch em;
     bool em_prepared = false;
     bool em_x_valid = false;
@@ -202,6 +208,7 @@ extern "C" void mcsim_cuda_destroy(mcsim_cuda_ctx* c) {
     c->pairs_f.release(); c->sc_plans.release(); c->sc_hits.release(); c->sc_counters.release();
     c->em_x.release(); c->em_comps.release(); c->em_hefts.release(); c->em_means.release(); c->em_fcovs.release();
     c->em_stats.release(); c->em_old.release(); c->em_done.release(); c->em_iters.release(); c->em_trace.release();
+    c->em_slots.release(); c->em_flags.release();
     c->gmm_comps.release(); c->gmm_stats.release(); c->gmm_hist.release(); c->gmm_counts.release();
     c->gmm_normals.release(); c->gmm_steps.release(); c->gmm_prob.release(); c->gmm_pre.release();
     c->gmm_post.release(); c->gmm_trunc.release(); c->gmm_nout.release(); c->gmm_deg.release();
@@ -1453,6 +1460,7 @@ extern "C" int mcsim_cuda_em_prepare(mcsim_cuda_ctx* c, const mcsim_em_params* p
     a.n = p->n;
     a.n_total = double(p->n_total ? p->n_total : p->n);
     a.K = K; a.n_fits = F; a.iters = p->iters; a.iter = 0;
+    a.n_peers = 0; a.my_rank = 0; a.wait_value = 0;
     a.var_floor = p->var_floor > 0 ? p->var_floor : DBL_MIN;
     a.comps = (float*)c->em_comps.p; a.hefts = (double*)c->em_hefts.p; a.means = (double*)c->em_means.p;
     a.fcovs = (double*)c->em_fcovs.p; a.stats = (double*)c->em_stats.p; a.old_avg = (double*)c->em_old.p;
@@ -1461,12 +1469,21 @@ extern "C" int mcsim_cuda_em_prepare(mcsim_cuda_ctx* c, const mcsim_em_params* p
     ++c->launches;
     CK(cudaGetLastError());
     c->em_prepared = true;
+    c->em_chunks = 0;   // the next E-step picks kernel and grid for this shape
     return MCSIM_OK;
 }
 
 extern "C" int mcsim_cuda_em_estep(mcsim_cuda_ctx* c) {
     if (!c || !c->em_prepared) return fail(MCSIM_ERR_ARG, "em_estep: mcsim_cuda_em_prepare has not been called");
     CK(cudaSetDevice(c->device));
+    if (c->em_chunks) {   // configuration cached by the first E-step after mcsim_cuda_em_prepare
+        const dim3 grid(c->em_chunks, (unsigned)c->em.n_fits);
+        c->em_k0<<<grid, 256, c->em_smem, c->stream>>>(c->em);
+        ++c->launches;
+        if (c->em_k1) { c->em_k1<<<grid, 256, 0, c->stream>>>(c->em); ++c->launches; }
+        CK(cudaGetLastError());
+        return MCSIM_OK;
+    }
     em_kernel_t k0, k1;
     // 128-bit loads when every row of every fit is 16-byte aligned
     const bool vec = (c->em.n % 4) == 0 && c->em.n >= 4;
@@ -1493,6 +1510,7 @@ extern "C" int mcsim_cuda_em_estep(mcsim_cuda_ctx* c) {
         if (eff > best + 0.02) { best = eff; chunks = ch; }
     }
     const dim3 grid((unsigned)chunks, (unsigned)c->em.n_fits);
+    c->em_k0 = k0; c->em_k1 = k1; c->em_smem = smem; c->em_chunks = (unsigned)chunks;
     k0<<<grid, 256, smem, c->stream>>>(c->em);
     ++c->launches;
     if (k1) { k1<<<grid, 256, 0, c->stream>>>(c->em); ++c->launches; }
@@ -1503,7 +1521,7 @@ extern "C" int mcsim_cuda_em_estep(mcsim_cuda_ctx* c) {
 extern "C" int mcsim_cuda_em_mstep(mcsim_cuda_ctx* c) {
     if (!c || !c->em_prepared) return fail(MCSIM_ERR_ARG, "em_mstep: mcsim_cuda_em_prepare has not been called");
     CK(cudaSetDevice(c->device));
-    em_mstep_kernel<<<c->em.n_fits, 32, 0, c->stream>>>(c->em, 0);
+    em_mstep_kernel<<<c->em.n_fits, c->em.n_peers > 1 ? EM_MSTEP_FUSED_THREADS : 32, 0, c->stream>>>(c->em, 0);
     ++c->launches;
     ++c->em.iter;
     CK(cudaGetLastError());

@@ -62,6 +62,7 @@ class EmStaticParams(C.Structure):
 
 
 EM_STATIC_MAX_FITS, EM_STATIC_MAX_ITERS, EM_STATIC_SCRATCH_BYTES = 8, 64, 32768
+EM_EXCHANGE_AUTO, EM_EXCHANGE_NCCL, EM_EXCHANGE_PEER = 0, 1, 2
 
 
 class EmResult(C.Structure):
@@ -199,6 +200,8 @@ def lib():
         L.mcsim_cuda_group_set_scene.argtypes = [vp, _dp, C.c_int, _dp, C.c_int]
         L.mcsim_cuda_group_mc_run.argtypes = [vp, C.POINTER(McParams), C.POINTER(McResult)]
         L.mcsim_cuda_group_em_fit.argtypes = [vp, C.POINTER(EmParams), C.POINTER(EmResult)]
+        L.mcsim_cuda_group_set_em_exchange.argtypes = [vp, C.c_int]
+        L.mcsim_cuda_group_em_exchange.argtypes = [vp]
         L.mcsim_cuda_group_score_plans.argtypes = [vp, C.POINTER(ScoreParams), C.POINTER(ScoreResult)]
         L.mcsim_cuda_group_gmm_run_batch.argtypes = [vp, C.POINTER(McParams), C.POINTER(GmmBatchParams), C.POINTER(GmmBatchResult)]
         L.mcsim_cuda_group_stats.argtypes = [vp, _fp, C.POINTER(C.c_uint64)]
@@ -656,6 +659,14 @@ class Group(Context):
 
     def _entry(self, name):
         return getattr(lib(), "mcsim_cuda_group_" + name)
+
+    def set_em_exchange(self, mode):
+        """EM_EXCHANGE_AUTO | EM_EXCHANGE_NCCL | EM_EXCHANGE_PEER: how em_fit moves the statistics every iteration."""
+        check(lib().mcsim_cuda_group_set_em_exchange(self._g, int(mode)))
+
+    @property
+    def em_exchange(self):
+        return int(lib().mcsim_cuda_group_em_exchange(self._g))
 
     @property
     def _target(self):

@@ -13,6 +13,13 @@ GOLD = os.path.join(ROOT, "tests", "golden")
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a B200 (run by the driver with -m gpu)")
+    # torch before anything loads a libnccl.so.2: a device group (mcsim_cuda_group_create, > 1 GPU) dlopen's the system NCCL,
+    # and libtorch_cuda.so imported AFTER that would be bound to it instead of its own bundled, newer one (undefined
+    # ncclDevCommCreate).  With torch first, the group finds torch's already-loaded library under the same soname.
+    try:
+        import torch  # noqa: F401
+    except ImportError:
+        pass
 
 
 @pytest.fixture(scope="session")

@@ -86,7 +86,20 @@ def test_group_score_em_and_gmm_batch_equal_one_device(ctx, plan, scenes):
             np.testing.assert_allclose(many["hefts"], one["hefts"], rtol=1e-6)
             np.testing.assert_allclose(many["fcovs"], one["fcovs"], rtol=1e-4, atol=1e-10)
             np.testing.assert_allclose(many["avg_log_p"], one["avg_log_p"], rtol=1e-6)
-        assert g.collective_stats()[1] == 8
+            # the two ways the statistics travel (fused peer-memory push / ncclAllReduce) give the same fit, and the fused
+            # one again on the resident samples (FP64 atomics inside a shard are unordered: rounding-level differences)
+            assert g.em_exchange in (abi.EM_EXCHANGE_PEER, abi.EM_EXCHANGE_NCCL)
+            g.set_em_exchange(abi.EM_EXCHANGE_NCCL)
+            nccl = g.em_fit(x, h, m, c, 4)
+            g.set_em_exchange(abi.EM_EXCHANGE_AUTO)
+            again = g.em_fit(None, h, m, c, 4)
+            for other in (nccl, again):
+                np.testing.assert_allclose(other["means"], many["means"], rtol=1e-9, atol=1e-12)
+                np.testing.assert_allclose(other["fcovs"], many["fcovs"], rtol=1e-6, atol=1e-12)
+                np.testing.assert_allclose(other["hefts"], many["hefts"], rtol=1e-9)
+                np.testing.assert_array_equal(other["iters_run"], many["iters_run"])
+        print("EM exchange of this group:", "peer memory" if g.em_exchange == abi.EM_EXCHANGE_PEER else "NCCL")
+        assert g.collective_stats()[1] == 24
         # batched GMM runs: members split over the devices
         ctx.set_scene(scenes["pr2test2"]["boxes"], hulls)
         g.set_scene(scenes["pr2test2"]["boxes"], hulls)
