@@ -572,7 +572,7 @@ def extras_all_ranks(a, ctx, abi, plan, T, torch, dist, world, rank, barrier, fp
     import pcoll_b200
     out = {}
     n_sm = torch.cuda.get_device_properties(torch.cuda.current_device()).multi_processor_count
-    B, ns = 9 * n_sm, 10000
+    B, ns = 8 * n_sm, 10000   # two full waves of the 128-thread shape (4 runs in flight per SM)
     ctx.gmm_run_batch(plan, 3, ns, B, stream0=rank * 100000)
     best, rec = None, None
     for rep in range(3):

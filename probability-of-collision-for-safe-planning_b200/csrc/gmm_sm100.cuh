@@ -421,38 +421,28 @@ struct GmmAcc {
     }
 };
 
-// one pass of the sample loop: every thread draws and tests TWO samples, i0 = 2 j and i0 + 1, in the two lanes of
-// packed FP32 pairs (f32x2.cuh; the SAT is the packed kernel's, mc_philox2_sm100.cuh: same arithmetic for listed and
-// exhaustive tests); every thread of the warp calls it.  tab / ccnt / cidx: global or shared memory.
-__device__ __forceinline__ void gmm_philox_pass2(unsigned stream_id, unsigned ctr2, unsigned k0, unsigned k1, unsigned i0, unsigned i1, unsigned n, int K, int& g,
-                                                 const unsigned* s_prefix, const float (*s_mu)[3], const float (*s_L)[6], double (*s_stat)[GMM_STAT],
-                                                 const float4* tab, const unsigned char* ccnt, const ushort2* cidx, bool cull, float2 nom,
-                                                 GmmAcc& acc, unsigned& my_tests) {
-    const bool valid0 = i0 < n, valid1 = i1 < n;   // i1 = i0 + 1, or >= n when the launch spreads one sample per thread
-    while (valid0 && g < K - 1 && i0 >= s_prefix[g + 1]) ++g;  // i0 only grows: the component index is monotone
-    int g1 = g;
-    while (valid1 && g1 < K - 1 && i1 >= s_prefix[g1 + 1]) ++g1;
+// Two samples of one thread, i0 and i1, in the two lanes of packed FP32 pairs (f32x2.cuh): Philox block -> 3 normals ->
+// x = mu_g + L_g z -> packed SAT (mc_philox2_sm100.cuh: same arithmetic for listed and exhaustive tests).  L / mu: the
+// components' Cholesky factors and means, lane 0 for i0 and lane 1 for i1 (the same value twice unless the pair sits on a
+// component boundary).  Every thread of the warp calls it.  tab / ccnt / cidx: global or shared memory.
+struct GmmDraw2 {
+    f2 d0, d1, d2;   // L z of both samples (the moment sums are taken about the component mean)
+    bool hit0, hit1;
+};
+template <class V>   // V = f2: per-lane components; V = float: one component for both lanes (broadcast at use)
+__device__ __forceinline__ GmmDraw2 gmm_draw_test2(unsigned stream_id, unsigned ctr2, unsigned k0, unsigned k1, unsigned i0, unsigned i1, bool valid0, bool valid1,
+                                                   const V (&L)[6], const V (&mu)[3], const float4* tab, const unsigned char* ccnt, const ushort2* cidx,
+                                                   bool cull, float2 nom, unsigned& my_tests) {
     const mcsim_rng::u32x4 ca = mcsim_rng::philox4x32_10(mcsim_rng::u32x4{i0, stream_id, ctr2, unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)}, k0, k1);
     const mcsim_rng::u32x4 cb = mcsim_rng::philox4x32_10(mcsim_rng::u32x4{i1, stream_id, ctr2, unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)}, k0, k1);
     f2 z0, z1, z2, z3;
     box_muller2(ca.x, ca.y, cb.x, cb.y, z0, z1);
     box_muller2(ca.z, ca.w, cb.z, cb.w, z2, z3);
-    // component records per lane (the two samples share the component except across a boundary)
-    float La[6], Lb[6], ma[3], mb[3];
-#pragma unroll
-    for (int k = 0; k < 6; ++k) La[k] = Lb[k] = s_L[g][k];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) ma[k] = mb[k] = s_mu[g][k];
-    if (g1 != g) {
-#pragma unroll
-        for (int k = 0; k < 6; ++k) Lb[k] = s_L[g1][k];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) mb[k] = s_mu[g1][k];
-    }
-    const f2 d0 = mul2(mk2(La[0], Lb[0]), z0);
-    const f2 d1 = fma2(mk2(La[2], Lb[2]), z1, mul2(mk2(La[1], Lb[1]), z0));
-    const f2 d2 = fma2(mk2(La[5], Lb[5]), z2, fma2(mk2(La[4], Lb[4]), z1, mul2(mk2(La[3], Lb[3]), z0)));
-    const f2 x = add2(mk2(ma[0], mb[0]), d0), y = add2(mk2(ma[1], mb[1]), d1), th = add2(mk2(ma[2], mb[2]), d2);
+    GmmDraw2 o;
+    o.d0 = mul2(z0, L[0]);
+    o.d1 = fma2(z1, L[2], mul2(z0, L[1]));
+    o.d2 = fma2(z2, L[5], fma2(z1, L[4], mul2(z0, L[3])));
+    const f2 x = add2(o.d0, mu[0]), y = add2(o.d1, mu[1]), th = add2(o.d2, mu[2]);
     f2 sn, cs;
     sincos2(th, sn, cs);   // |theta| < 3 pi: mu_theta in [0, 2 pi] + O(sigma)
     // warp-uniform choice of the candidate list by the warp's largest deviation from x*_t (exact: sat_device.cuh)
@@ -465,7 +455,7 @@ __device__ __forceinline__ void gmm_philox_pass2(unsigned stream_id, unsigned ct
         if (lev < MC_CULL_LEVELS && ccnt[lev] == MC_CULL_OVERFLOW) lev = MC_CULL_LEVELS;
     }
     unsigned tested = 0;
-    bool hit0 = false, hit1 = false;
+    o.hit0 = o.hit1 = false;
     if (lev < MC_CULL_LEVELS) {
         for (int hI = 0; hI < c_scene.n_hulls; ++hI) {
             const int nc = ccnt[hI * MC_CULL_LEVELS + lev];
@@ -474,24 +464,152 @@ __device__ __forceinline__ void gmm_philox_pass2(unsigned stream_id, unsigned ct
             ClassFrame2 cf;
             unsigned cls = 0xffffffffu;
             for (int k = 0; k < nc; ++k) {
-                const ushort2 o = cidx[hI * MC_CULL_CAP + k];  // x: pair record, y: class header
-                if (o.y != cls) {
-                    cls = o.y;
-                    cf = class_frame2(tab[o.y], h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
+                const ushort2 oo = cidx[hI * MC_CULL_CAP + k];  // x: pair record, y: class header
+                if (oo.y != cls) {
+                    cls = oo.y;
+                    cf = class_frame2(tab[oo.y], h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
                 }
-                class_pair_test2(cf, h.ch, h.sh, h.nph, h.nqh, h.hhx, h.hhy, tab[o.x], *reinterpret_cast<const float2*>(tab + o.x + 1), hit0, hit1);
+                class_pair_test2(cf, h.ch, h.sh, h.nph, h.nqh, h.hhx, h.hhy, tab[oo.x], *reinterpret_cast<const float2*>(tab + oo.x + 1), o.hit0, o.hit1);
             }
             tested += nc;
         }
     } else {
-        robot_hits2(tab, x, y, cs, sn, hit0, hit1);
+        robot_hits2(tab, x, y, cs, sn, o.hit0, o.hit1);
         tested = c_scene.n_pairs;
     }
-    if (__any_sync(0xffffffffu, valid0 && acc.g_acc >= 0 && g != acc.g_acc)) acc.flush(s_stat);
-    if (valid0) acc.add(g, hit0, lo(d0), lo(d1), lo(d2));
-    if (__any_sync(0xffffffffu, valid1 && acc.g_acc >= 0 && g1 != acc.g_acc)) acc.flush(s_stat);
-    if (valid1) acc.add(g1, hit1, hi(d0), hi(d1), hi(d2));
     my_tests += tested * (unsigned(valid0) + unsigned(valid1));
+    return o;
+}
+
+// one pass of the generic sample loop (per-waypoint and cluster kernels): the thread's two samples may belong to any
+// component (per-thread monotone search in the prefix sums); per-thread sums are flushed when the component changes
+__device__ __forceinline__ void gmm_philox_pass2(unsigned stream_id, unsigned ctr2, unsigned k0, unsigned k1, unsigned i0, unsigned i1, unsigned n, int K, int& g,
+                                                 const unsigned* s_prefix, const float (*s_mu)[3], const float (*s_L)[6], double (*s_stat)[GMM_STAT],
+                                                 const float4* tab, const unsigned char* ccnt, const ushort2* cidx, bool cull, float2 nom,
+                                                 GmmAcc& acc, unsigned& my_tests) {
+    const bool valid0 = i0 < n, valid1 = i1 < n;   // i1 = i0 + 1, or >= n when the launch spreads one sample per thread
+    while (valid0 && g < K - 1 && i0 >= s_prefix[g + 1]) ++g;  // i0 only grows: the component index is monotone
+    int g1 = g;
+    while (valid1 && g1 < K - 1 && i1 >= s_prefix[g1 + 1]) ++g1;
+    // component records per lane (the two samples share the component except across a boundary)
+    float La[6], Lb[6], ma[3], mb[3];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) La[k] = Lb[k] = s_L[g][k];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) ma[k] = mb[k] = s_mu[g][k];
+    if (g1 != g) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) Lb[k] = s_L[g1][k];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) mb[k] = s_mu[g1][k];
+    }
+    f2 L[6], mu[3];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) L[k] = mk2(La[k], Lb[k]);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) mu[k] = mk2(ma[k], mb[k]);
+    const GmmDraw2 o = gmm_draw_test2(stream_id, ctr2, k0, k1, i0, i1, valid0, valid1, L, mu, tab, ccnt, cidx, cull, nom, my_tests);
+    if (__any_sync(0xffffffffu, valid0 && acc.g_acc >= 0 && g != acc.g_acc)) acc.flush(s_stat);
+    if (valid0) acc.add(g, o.hit0, lo(o.d0), lo(o.d1), lo(o.d2));
+    if (__any_sync(0xffffffffu, valid1 && acc.g_acc >= 0 && g1 != acc.g_acc)) acc.flush(s_stat);
+    if (valid1) acc.add(g1, o.hit1, hi(o.d0), hi(o.d1), hi(o.d2));
+}
+
+// ---- the one-CTA-per-run kernel's sample loop: warp-uniform components -------------------------------------------------
+// A warp's window of a pass is 64 consecutive sample indices, and samples are grouped by component (prefix sums), so all
+// but at most K - 1 windows per warp and waypoint lie inside ONE component.  Those "pure" windows run as tight loops per
+// component: the component's factor and mean sit in registers, there is no per-thread component search, no vote on
+// "has anybody's component changed", and the FP64 sums are reduced once at the end of the loop (the generic loop paid
+// ~20 % of its instructions for that bookkeeping: register moves at the flush merge points, two votes and the search
+// per pass).  Draws, FP32 arithmetic and hit flags are those of gmm_philox_pass2 (same counters per sample index); only
+// the order of the FP64 additions differs.
+// warp sums of the selected lanes' statistics -> one shared atomic per statistic (component gg)
+__device__ __forceinline__ void gmm_warp_flush(double (*s_stat)[GMM_STAT], int gg, bool sel, unsigned nf, unsigned nc, const double (&acc)[9]) {
+    const unsigned wf = __reduce_add_sync(0xffffffffu, sel ? nf : 0u);
+    const unsigned wc = __reduce_add_sync(0xffffffffu, sel ? nc : 0u);
+    if (wf) {
+        double v[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) {
+            v[k] = sel ? acc[k] : 0.0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(&s_stat[gg][0], double(wf));
+#pragma unroll
+            for (int k = 0; k < 9; ++k) atomicAdd(&s_stat[gg][2 + k], v[k]);
+        }
+    }
+    if (wc && (threadIdx.x & 31) == 0) atomicAdd(&s_stat[gg][1], double(wc));
+}
+__device__ __forceinline__ void gmm_acc_add(bool valid, bool hit, float d0, float d1, float d2, unsigned& nf, unsigned& nc, double (&acc)[9]) {
+    if (valid) {
+        if (hit) {
+            ++nc;
+        } else {
+            ++nf;
+            const double e0 = d0, e1 = d1, e2 = d2;
+            acc[0] += e0; acc[1] += e1; acc[2] += e2;
+            acc[3] = fma(e0, e0, acc[3]); acc[4] = fma(e0, e1, acc[4]); acc[5] = fma(e0, e2, acc[5]);
+            acc[6] = fma(e1, e1, acc[6]); acc[7] = fma(e1, e2, acc[7]); acc[8] = fma(e2, e2, acc[8]);
+        }
+    }
+}
+// all samples of a waypoint for one warp of a 256-thread CTA (pass stride 512 samples, window = 64 samples per warp)
+__device__ __forceinline__ void gmm_member_samples(unsigned stream_id, unsigned ctr2, unsigned k0, unsigned k1, unsigned n, int K,
+                                                   const unsigned* s_prefix, const float (*s_mu)[3], const float (*s_L)[6], double (*s_stat)[GMM_STAT],
+                                                   const float4* tab, const unsigned char* ccnt, const ushort2* cidx, bool cull, float2 nom, unsigned& my_tests) {
+    const unsigned lane2 = 2u * (threadIdx.x & 31u), wbase = 64u * (threadIdx.x >> 5);
+    const unsigned stride = 2u * blockDim.x;
+    int gw = 0;   // component of the window's first sample (warp-uniform)
+    for (unsigned w0 = wbase; w0 < n;) {
+        while (gw < K - 1 && w0 >= s_prefix[gw + 1]) ++gw;
+        const unsigned end_g = gw == K - 1 ? n : (s_prefix[gw + 1] < n ? s_prefix[gw + 1] : n);   // first index beyond the component
+        const unsigned w_end = w0 + 64u < n ? w0 + 64u : n;                                      // first index beyond the window
+        if (w_end <= end_g) {
+            // ---- pure windows: this one and every following one of the warp that still ends inside the component
+            const unsigned q_n = end_g == n ? (n - 1u - w0) / stride + 1u : (end_g - 64u - w0) / stride + 1u;
+            float L[6], mu[3];
+#pragma unroll
+            for (int k = 0; k < 6; ++k) L[k] = s_L[gw][k];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) mu[k] = s_mu[gw][k];
+            unsigned nf = 0, nc = 0;
+            double acc[9] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+            for (unsigned q = 0; q < q_n; ++q, w0 += stride) {
+                const unsigned i0 = w0 + lane2, i1 = i0 + 1u;
+                const bool valid0 = i0 < n, valid1 = i1 < n;
+                const GmmDraw2 o = gmm_draw_test2(stream_id, ctr2, k0, k1, i0, i1, valid0, valid1, L, mu, tab, ccnt, cidx, cull, nom, my_tests);
+                gmm_acc_add(valid0, o.hit0, lo(o.d0), lo(o.d1), lo(o.d2), nf, nc, acc);
+                gmm_acc_add(valid1, o.hit1, hi(o.d0), hi(o.d1), hi(o.d2), nf, nc, acc);
+            }
+            gmm_warp_flush(s_stat, gw, true, nf, nc, acc);
+        } else {
+            // ---- a window across one or more component boundaries: per-lane components, statistics reduced per component
+            const unsigned i0 = w0 + lane2, i1 = i0 + 1u;
+            const bool valid0 = i0 < n, valid1 = i1 < n;
+            int g0 = gw;
+            while (valid0 && g0 < K - 1 && i0 >= s_prefix[g0 + 1]) ++g0;
+            int g1 = g0;
+            while (valid1 && g1 < K - 1 && i1 >= s_prefix[g1 + 1]) ++g1;
+            f2 L[6], mu[3];
+#pragma unroll
+            for (int k = 0; k < 6; ++k) L[k] = mk2(s_L[g0][k], s_L[g1][k]);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) mu[k] = mk2(s_mu[g0][k], s_mu[g1][k]);
+            const GmmDraw2 o = gmm_draw_test2(stream_id, ctr2, k0, k1, i0, i1, valid0, valid1, L, mu, tab, ccnt, cidx, cull, nom, my_tests);
+            const int g_last = __reduce_max_sync(0xffffffffu, valid1 ? g1 : (valid0 ? g0 : gw));
+            for (int gg = gw; gg <= g_last; ++gg) {   // warp-uniform
+                unsigned nf = 0, nc = 0;
+                double acc[9] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+                gmm_acc_add(valid0 && g0 == gg, o.hit0, lo(o.d0), lo(o.d1), lo(o.d2), nf, nc, acc);
+                gmm_acc_add(valid1 && g1 == gg, o.hit1, hi(o.d0), hi(o.d1), hi(o.d2), nf, nc, acc);
+                gmm_warp_flush(s_stat, gg, true, nf, nc, acc);
+            }
+            w0 += stride;
+        }
+    }
 }
 
 __global__ void __launch_bounds__(256) gmm_sample_philox_kernel(const GmmLaunch a_in) {
@@ -729,10 +847,76 @@ __global__ void __launch_bounds__(32) gmm_linear_run_kernel(const GmmLaunch a_in
 // of 3 T.  Same draws, same component assignment, same refit code as the per-waypoint kernels (member b ==
 // mcsim_cuda_gmm_run on Philox subsequence stream0 + b up to the order of the FP64 sums).
 // Dynamic shared memory: pair table (a.sat2, sat2_n float4) | candidate lists (cull_words 32-bit words).
-#ifndef GMM_FUSED_CTAS
-#define GMM_FUSED_CTAS 3   // resident 256-thread CTAs per SM the fused kernel's register budget is set for
-#endif
-__global__ void __launch_bounds__(256, GMM_FUSED_CTAS) gmm_member_run_kernel(const GmmLaunch a_in, int sat2_n, int cull_words) {
+// cumulative distribution of the component draw from the weights (thread-serial; gmm_count_kernel's rule: entries behind
+// the last live component are 2 = never exceeded)
+__device__ __forceinline__ void gmm_member_cdf(const double* w, int K, float* s_cdf) {
+    double acc = 0, tot = 0;
+    for (int g = 0; g < K; ++g) tot += w[g];
+    for (int g = 0; g < K; ++g) { acc += w[g]; s_cdf[g] = float(acc / tot); }
+    for (int g = K - 1; g >= 0 && !(w[g] > 0); --g) s_cdf[g] = 2.0f;
+    int last = K - 1;
+    while (last > 0 && !(w[last] > 0)) --last;
+    s_cdf[last] = 2.0f;
+}
+// multinomial counts of waypoint t (gmm_count_kernel's draws: Philox block j -> 4 uniforms -> components of samples
+// 4 j .. 4 j + 3), by `n_threads` threads (whole warps) numbered `idx`; sums land in s_hist (zeroed by the caller)
+__device__ __forceinline__ void gmm_member_count(int t, unsigned idx, unsigned n_threads, int K, unsigned n_all, unsigned stream_id, unsigned k0, unsigned k1,
+                                                 const float* s_cdf, unsigned* s_hist) {
+    // per-thread counts in four registers of four 8-bit fields (component g: field g % 4 of register g / 4),
+    // flushed by warp sums before a field can overflow and after the last pass
+    const unsigned n4 = (n_all + 3) >> 2;
+    unsigned cnt[4] = {0u, 0u, 0u, 0u};
+    unsigned held = 0;
+    auto flush_counts = [&]() {
+        for (int gg = 0; gg < K; ++gg) {
+            const unsigned r = gg < 4 ? cnt[0] : (gg < 8 ? cnt[1] : (gg < 12 ? cnt[2] : cnt[3]));
+            const unsigned v = __reduce_add_sync(0xffffffffu, (r >> (8 * (gg & 3))) & 0xffu);
+            if (v && (threadIdx.x & 31) == 0) atomicAdd(&s_hist[gg], v);
+        }
+        cnt[0] = cnt[1] = cnt[2] = cnt[3] = 0u;
+        held = 0;
+    };
+    const float cdf0 = K > 1 ? s_cdf[0] : 2.0f, cdf1 = K > 2 ? s_cdf[1] : 2.0f, cdf2 = K > 3 ? s_cdf[2] : 2.0f;
+    for (unsigned base = 0; base < n4; base += n_threads) {
+        const unsigned j = base + idx;
+        mcsim_rng::u32x4 c = {j, stream_id, unsigned(2 * t + 1), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
+        c = mcsim_rng::philox4x32_10(c, k0, k1);
+        const unsigned w[4] = {c.x, c.y, c.z, c.w};
+        if (K <= 4) {
+            // the usual mixtures (K = 1 .. 4, the reference runs 1 .. 3): the three thresholds in registers (2 = never
+            // exceeded, like the entries behind the last live component), one counter register, no loop over k
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const bool valid = j < n4 && 4 * j + q < n_all;   // n <= 2^31: no overflow
+                const float u = mcsim_rng::u01(w[q]);
+                const int g = int(u > cdf0) + int(u > cdf1) + int(u > cdf2);
+                cnt[0] += valid ? 1u << (8 * g) : 0u;
+            }
+        } else {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const bool valid = j < n4 && 4 * j + q < n_all;   // n <= 2^31: no overflow
+                const float u = mcsim_rng::u01(w[q]);
+                int g = 0;
+                for (int k = 0; k < K - 1; ++k) g += u > s_cdf[k];   // the cdf is non-decreasing: first k with u <= cdf[k]
+                const unsigned inc = valid ? 1u << (8 * (g & 3)) : 0u;
+                cnt[0] += g < 4 ? inc : 0u;
+                cnt[1] += (g >= 4 && g < 8) ? inc : 0u;
+                cnt[2] += (g >= 8 && g < 12) ? inc : 0u;
+                cnt[3] += g >= 12 ? inc : 0u;
+            }
+        }
+        held += 4;
+        if (held > 248) flush_counts();   // warp-uniform
+    }
+    flush_counts();
+}
+
+// Register budget: 128 per thread (no spills: the draw + SAT + 9 FP64 sums need ~110), i.e. 512 resident threads per SM.
+// How they are cut into CTAs (= runs in flight per SM) is the launcher's choice -- 128, 256 or 512 threads per run
+// (gmm_member_threads in mcsim_cuda.cu): the kernel only assumes whole warps and at least two of them.
+#define GMM_MEMBER_MAX_THREADS 512
+__global__ void __launch_bounds__(GMM_MEMBER_MAX_THREADS, 1) gmm_member_run_kernel(const GmmLaunch a_in, int sat2_n, int cull_words) {
     extern __shared__ __align__(16) float4 s_tab[];
     __shared__ double s_comp[MCSIM_MAX_GAUSSIANS][GMM_COMP];
     __shared__ double s_stat[MCSIM_MAX_GAUSSIANS][GMM_STAT];
@@ -742,6 +926,7 @@ __global__ void __launch_bounds__(256, GMM_FUSED_CTAS) gmm_member_run_kernel(con
     __shared__ float s_cdf[MCSIM_MAX_GAUSSIANS];
     __shared__ unsigned s_hist[MCSIM_MAX_GAUSSIANS];
     __shared__ unsigned s_prefix[MCSIM_MAX_GAUSSIANS + 1];
+    __shared__ double s_wt[MCSIM_MAX_GAUSSIANS];
     const GmmLaunch& a = a_in;
     const GmmMember m = gmm_member(a_in, blockIdx.x);
     const int K = a.K, T = a.T, nh = c_scene.n_hulls;
@@ -758,83 +943,54 @@ __global__ void __launch_bounds__(256, GMM_FUSED_CTAS) gmm_member_run_kernel(con
     unsigned my_tests = 0;
     __syncthreads();
 
+    // The multinomial counts of waypoint t + 1 need the new WEIGHTS only, and those are known once every component's
+    // moments are (free counts); the rest of the refit -- EKF predict + 8 updates + Cholesky, ~6 us of dependent FP64 on
+    // K threads of warp 0 -- used to hold the other seven warps at a barrier (10 % of all stall samples, and with it a
+    // third of the SM's resident warps idle).  Now warps 1..7 draw the next waypoint's counts meanwhile.
+    if (threadIdx.x == 0) {
+        for (int g = 0; g < K; ++g) s_wt[g] = s_comp[g][0];
+        gmm_member_cdf(s_wt, K, s_cdf);
+    }
+    __syncthreads();
+    gmm_member_count(0, threadIdx.x, blockDim.x, K, n_all, stream_id, k0, k1, s_cdf, s_hist);
+    __syncthreads();
     for (int t = 0; t < T; ++t) {
-        // ---- multinomial counts of this waypoint (gmm_count_kernel)
+        // ---- the counts of this waypoint are in s_hist; the mixture of this waypoint is final in s_comp
         if (threadIdx.x == 0) {
-            double acc = 0, tot = 0;
-            for (int g = 0; g < K; ++g) tot += s_comp[g][0];
-            for (int g = 0; g < K; ++g) { acc += s_comp[g][0]; s_cdf[g] = float(acc / tot); }
-            for (int g = K - 1; g >= 0 && !(s_comp[g][0] > 0); --g) s_cdf[g] = 2.0f;
-            int last = K - 1;
-            while (last > 0 && !(s_comp[last][0] > 0)) --last;
-            s_cdf[last] = 2.0f;
+            unsigned acc = 0;
+            for (int g = 0; g < K; ++g) { s_prefix[g] = acc; acc += s_hist[g]; s_hist[g] = 0; }
+            s_prefix[K] = acc;
         }
         for (int i = threadIdx.x; i < K * 3; i += blockDim.x) s_mu[i / 3][i % 3] = float(s_comp[i / 3][1 + i % 3]);
         for (int i = threadIdx.x; i < K * 6; i += blockDim.x) s_L[i / 6][i % 6] = float(s_comp[i / 6][13 + i % 6]);
         __syncthreads();
-        // per-thread counts in four registers of four 8-bit fields (component g: field g % 4 of register g / 4),
-        // flushed by warp sums before a field can overflow and after the last pass
-        const unsigned n4 = (n_all + 3) >> 2;
-        unsigned cnt[4] = {0u, 0u, 0u, 0u};
-        unsigned held = 0;
-        auto flush_counts = [&]() {
-            for (int gg = 0; gg < K; ++gg) {
-                const unsigned r = gg < 4 ? cnt[0] : (gg < 8 ? cnt[1] : (gg < 12 ? cnt[2] : cnt[3]));
-                const unsigned v = __reduce_add_sync(0xffffffffu, (r >> (8 * (gg & 3))) & 0xffu);
-                if (v && (threadIdx.x & 31) == 0) atomicAdd(&s_hist[gg], v);
-            }
-            cnt[0] = cnt[1] = cnt[2] = cnt[3] = 0u;
-            held = 0;
-        };
-        for (unsigned base = 0; base < n4; base += blockDim.x) {
-            const unsigned j = base + threadIdx.x;
-            mcsim_rng::u32x4 c = {j, stream_id, unsigned(2 * t + 1), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
-            c = mcsim_rng::philox4x32_10(c, k0, k1);
-            const unsigned w[4] = {c.x, c.y, c.z, c.w};
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const bool valid = j < n4 && 4 * j + q < n_all;   // n <= 2^31: no overflow
-                const float u = mcsim_rng::u01(w[q]);
-                int g = 0;
-                for (int k = 0; k < K - 1; ++k) g += u > s_cdf[k];   // the cdf is non-decreasing: first k with u <= cdf[k]
-                const unsigned inc = valid ? 1u << (8 * (g & 3)) : 0u;
-                cnt[0] += g < 4 ? inc : 0u;
-                cnt[1] += (g >= 4 && g < 8) ? inc : 0u;
-                cnt[2] += (g >= 8 && g < 12) ? inc : 0u;
-                cnt[3] += g >= 12 ? inc : 0u;
-            }
-            held += 4;
-            if (held > 248) flush_counts();   // warp-uniform
-        }
-        flush_counts();
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            unsigned acc = 0;
-            for (int g = 0; g < K; ++g) { s_prefix[g] = acc; acc += s_hist[g]; }
-            s_prefix[K] = acc;
-        }
-        __syncthreads();
-        // ---- sample -> collide -> moments (gmm_sample_philox_kernel)
+        // ---- sample -> collide -> moments (the draws of gmm_sample_philox_kernel; loop structure: gmm_member_samples)
         {
-            int g = 0;
-            GmmAcc acc;
             const unsigned n = s_prefix[K] < n_all ? s_prefix[K] : n_all;
             const float2 nom = cull ? __ldg(m.nominal + t) : make_float2(0.f, 0.f);
             const unsigned char* cc = s_ccnt + t * nh * MC_CULL_LEVELS;
             const ushort2* ci = s_cidx + t * nh * MC_CULL_CAP;
-            for (unsigned base = 0; base < n; base += 2 * blockDim.x)   // two samples per thread and pass
-                gmm_philox_pass2(stream_id, unsigned(2 * t), k0, k1, base + 2 * threadIdx.x, base + 2 * threadIdx.x + 1, n, K, g, s_prefix, s_mu, s_L, s_stat, s_tab, cc, ci, cull, nom, acc, my_tests);
-            acc.flush(s_stat);
+            gmm_member_samples(stream_id, unsigned(2 * t), k0, k1, n, K, s_prefix, s_mu, s_L, s_stat, s_tab, cc, ci, cull, nom, my_tests);
         }
         __syncthreads();
         // ---- refit + propagate (gmm_refit_kernel)
         const int g = threadIdx.x;
         if (g < K) gmm_refit_moments(s_comp[g], s_stat[g], m.degenerate, s_free[g], s_coll[g]);
         __syncthreads();
-        if (g < K) {
-            gmm_refit_finish(a, m, t, g, s_comp[g], s_free, s_coll);
-            for (int k = 0; k < GMM_STAT; ++k) s_stat[g][k] = 0.0;
-            s_hist[g] = 0;
+        if (threadIdx.x < 32) {
+            if (g < K) {
+                gmm_refit_finish(a, m, t, g, s_comp[g], s_free, s_coll);
+                for (int k = 0; k < GMM_STAT; ++k) s_stat[g][k] = 0.0;
+            }
+        } else if (t < T - 1) {
+            if (threadIdx.x == 32) {   // the weights gmm_refit_finish is writing into s_comp[.][0] right now, from the same operands
+                double tf = 0;
+                for (int k = 0; k < K; ++k) tf += s_free[k];
+                for (int k = 0; k < K; ++k) s_wt[k] = s_free[k] / (tf > 0 ? tf : 1.0);
+                gmm_member_cdf(s_wt, K, s_cdf);
+            }
+            asm volatile("bar.sync 1, %0;" ::"r"(int(blockDim.x) - 32) : "memory");   // warps 1 .. 7 only
+            gmm_member_count(t + 1, threadIdx.x - 32, blockDim.x - 32, K, n_all, stream_id, k0, k1, s_cdf, s_hist);
         }
         __syncthreads();
     }

@@ -1717,6 +1717,24 @@ extern "C" int mcsim_cuda_score_plans(mcsim_cuda_ctx* c, const mcsim_score_param
 }
 
 // ---- batched GMM mode: n_traj independent runGMMEstimation runs in the same launches ----------------
+// Threads per run of the one-CTA-per-run kernel.  512 resident threads per SM (128 registers each) are 1, 2 or 4 runs in
+// flight per SM; a run on fewer threads takes longer but more of them overlap their serial stretches (refit, barriers).
+// Measured wave times on B200 (K = 3, 10^4 samples, 56 waypoints; profiles/r02_gmm_member_shapes.log): 1.5 / 2.45 / 4.63 ms
+// for a full wave of 148 / 296 / 592 runs -- small batches want the big CTA (latency), large ones the small CTA
+// (throughput: 98 / 121 / 128 thousand runs per second); the estimate below picks by whole waves.
+static int gmm_member_threads(int B, int n_sm) {
+    const int threads[3] = {512, 256, 128};
+    const double wave_ms[3] = {1.5, 2.45, 4.63};
+    int best = 256;
+    double best_ms = 1e300;
+    for (int i = 0; i < 3; ++i) {
+        const long long slots = (long long)n_sm * (GMM_MEMBER_MAX_THREADS / threads[i]);
+        const double ms = double((B + slots - 1) / slots) * wave_ms[i];
+        if (ms < best_ms) { best_ms = ms; best = threads[i]; }
+    }
+    return best;
+}
+
 extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, const mcsim_gmm_batch_params* g,
                                         mcsim_gmm_batch_result* r) {
     if (!c || !mc || !g || !r || !r->P) return fail(MCSIM_ERR_ARG, "gmm_run_batch: NULL argument");
@@ -1782,7 +1800,7 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
         SymbolLock sym;
         { const int rb = bind_symbols(c, nullptr, sym); if (rb) return rb; }
         if (fused_smem > 40 * 1024) CK(cudaFuncSetAttribute((const void*)gmm_member_run_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(fused_smem)));
-        gmm_member_run_kernel<<<B, 256, fused_smem, c->stream>>>(a, c->sat2_n, c->gmm_cull_words);
+        gmm_member_run_kernel<<<B, gmm_member_threads(B, c->n_sm), fused_smem, c->stream>>>(a, c->sat2_n, c->gmm_cull_words);
         ++c->launches;
         CK(cudaGetLastError());
     } else {

@@ -11,13 +11,17 @@ sys.path.insert(0, ROOT)
 import pcoll_b200  # noqa: E402
 
 abi = pcoll_b200.cuda_abi
+if "--lib" in sys.argv:     # a variant build (tools/build_variant.sh)
+    i = sys.argv.index("--lib")
+    abi.LIB_PATH = os.path.abspath(sys.argv[i + 1])
+    del sys.argv[i:i + 2]
 gold = os.path.join(ROOT, "tests", "golden")
 plan = pcoll_b200.load_plan_json(os.path.join(gold, "plan_committed.json"))
 sc = np.load(os.path.join(gold, "scene_pr2test2.npz"))
 if len(sys.argv) > 1 and sys.argv[1] == "sweep":
     K_LIST, B_LIST = (), ()
 else:
-    K_LIST, B_LIST = ((3, 10000), (1, 10000), (16, 10000), (3, 1000000)), (64, 256, 1332, 2664)
+    K_LIST, B_LIST = ((3, 10000), (1, 10000), (16, 10000), (3, 1000000)), (64, 256, 1184, 1332, 2368, 2664)
 ctx = abi.Context(0)
 fp32 = ctx.measure_peak(0, 100.0)
 ctx.set_scene(sc["boxes"], sc["hulls"])

@@ -11,6 +11,10 @@ sys.path.insert(0, ROOT)
 import pcoll_b200  # noqa: E402
 
 abi = pcoll_b200.cuda_abi
+if "--lib" in sys.argv:     # a variant build (tools/build_variant.sh)
+    i = sys.argv.index("--lib")
+    abi.LIB_PATH = os.path.abspath(sys.argv[i + 1])
+    del sys.argv[i:i + 2]
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 exhaustive = len(sys.argv) > 2 and sys.argv[2] == "exhaustive"
 gold = os.path.join(ROOT, "tests", "golden")
