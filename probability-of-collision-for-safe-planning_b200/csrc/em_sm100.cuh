@@ -57,8 +57,24 @@ struct EmLaunch {
 // K: components of the model; G0: first component whose statistics THIS launch accumulates (at most 8
 // per launch: 80 FP32 accumulators per thread).  K > 8 takes a second launch with G0 = 8 that
 // recomputes the log-likelihoods; the log-likelihood sum is accumulated by the G0 = 0 launch only.
+// The one-warp kernel for EM_OW_LO <= K <= 8 carries 10 K accumulators per thread.  Left alone it takes 183 - 227
+// registers (one 256-thread CTA per SM, 2 warps per scheduler, 56 % issue active); capped at 128 registers with one
+// sample in flight and 128-thread CTAs it spills 0.1 - 0.5 KB per thread but runs 4 warps per scheduler: K = 6 / 7 / 8
+// 0.340 / 0.361 / 0.375 -> 0.445 / 0.452 / 0.454 of the FP32 peak (profiles/r02_em_k68_occupancy.log).
+#ifndef EM_OW_LO
+#define EM_OW_LO 6
+#endif
+#ifndef EM_OW_U68
+#define EM_OW_U68 1      // samples in flight per thread for EM_OW_LO <= K <= 8
+#endif
+#ifndef EM_OW_THREADS68
+#define EM_OW_THREADS68 128   // CTA size for EM_OW_LO <= K <= 8 (the host launches it: em_pick in mcsim_cuda.cu)
+#endif
+#ifndef EM_OW_MINB68
+#define EM_OW_MINB68 4   // resident CTAs of that size per SM the register budget is set for: 128 registers, 16 warps per SM
+#endif
 template <int K, int G0>
-__global__ void __launch_bounds__(256) em_estep_kernel(const EmLaunch a) {
+__global__ void __launch_bounds__((K >= EM_OW_LO && K <= 8 && G0 == 0) ? EM_OW_THREADS68 : 256, (K >= EM_OW_LO && K <= 8 && G0 == 0) ? EM_OW_MINB68 : 1) em_estep_kernel(const EmLaunch a) {
     constexpr int KG = (K - G0) < 8 ? (K - G0) : 8;
     constexpr int NACC = KG * EM_NSTAT + 1;
     __shared__ __align__(16) float s_c[K * EM_COMP_STRIDE];
@@ -81,7 +97,7 @@ __global__ void __launch_bounds__(256) em_estep_kernel(const EmLaunch a) {
 
     // U samples per pass, the next pass's 3 U loads issued before this pass's arithmetic: enough bytes
     // in flight per SM to stream from HBM while the FP32 pipe works on the previous samples
-    constexpr int U = K <= 4 ? 4 : (K <= 8 ? 2 : 1);
+    constexpr int U = K <= 4 ? 4 : (K <= 8 ? (K >= EM_OW_LO ? EM_OW_U68 : 2) : 1);
     // 32-bit sample indices (mcsim_cuda_em_prepare rejects n >= 2^31 per fit and shard)
     const unsigned n = unsigned(a.n);
     const unsigned stride = gridDim.x * blockDim.x;

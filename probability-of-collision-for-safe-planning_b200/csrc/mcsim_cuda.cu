@@ -132,6 +132,7 @@ struct mcsim_cuda_ctx {
     void (*em_k1)(const EmLaunch) = nullptr;
     size_t em_smem = 0;
     unsigned em_chunks = 0;
+    int em_block = 256;
     DevBuf em_slots, em_flags;   // fused exchange of a sharded fit (mcsim_group.cuh): gather buffer [2][G][n_stats], counters [n_fits][G]
     EmLaunch em;
     bool em_prepared = false;
@@ -1368,10 +1369,11 @@ typedef void (*em_kernel_t)(const EmLaunch);
 #define EM_TMA_MAX_K 4   // fits with at most this many components stream through the bulk-copy kernel (packed pairs)
 #endif
 template <int K>
-static void em_pick(em_kernel_t& k0, em_kernel_t& k1, bool vec, size_t& smem) {
+static void em_pick(em_kernel_t& k0, em_kernel_t& k1, bool vec, size_t& smem, int& block) {
     k0 = em_estep_kernel<K, 0>;
     k1 = nullptr;
     smem = 0;
+    block = 256;
 #ifndef EM_PACKED_MAX_K
 #define EM_PACKED_MAX_K 5   // packed pairs while the 10 K accumulator pairs fit the register file (K = 5: 230 registers, 1.61 vs 2.15 ms; K = 6 spills)
 #endif
@@ -1394,17 +1396,18 @@ static void em_pick(em_kernel_t& k0, em_kernel_t& k1, bool vec, size_t& smem) {
         if constexpr (EM_SPLIT_MIN_K <= 16) k0 = em_estep_split_kernel<K, EM_SPLIT_S_HIGH>;
         else k1 = em_estep_kernel<K, 8>;
     }
+    if constexpr (K >= EM_OW_LO && K > EM_PACKED_MAX_K && K <= 8 && K < EM_SPLIT_MIN_K) block = EM_OW_THREADS68;   // the one-warp kernel's own CTA size there
 }
-static bool em_kernels(int K, em_kernel_t& k0, em_kernel_t& k1, bool vec, size_t& smem) {
+static bool em_kernels(int K, em_kernel_t& k0, em_kernel_t& k1, bool vec, size_t& smem, int& block) {
     switch (K) {
-        case 1: em_pick<1>(k0, k1, vec, smem); return true;    case 2: em_pick<2>(k0, k1, vec, smem); return true;
-        case 3: em_pick<3>(k0, k1, vec, smem); return true;    case 4: em_pick<4>(k0, k1, vec, smem); return true;
-        case 5: em_pick<5>(k0, k1, vec, smem); return true;    case 6: em_pick<6>(k0, k1, vec, smem); return true;
-        case 7: em_pick<7>(k0, k1, vec, smem); return true;    case 8: em_pick<8>(k0, k1, vec, smem); return true;
-        case 9: em_pick<9>(k0, k1, vec, smem); return true;    case 10: em_pick<10>(k0, k1, vec, smem); return true;
-        case 11: em_pick<11>(k0, k1, vec, smem); return true;  case 12: em_pick<12>(k0, k1, vec, smem); return true;
-        case 13: em_pick<13>(k0, k1, vec, smem); return true;  case 14: em_pick<14>(k0, k1, vec, smem); return true;
-        case 15: em_pick<15>(k0, k1, vec, smem); return true;  case 16: em_pick<16>(k0, k1, vec, smem); return true;
+        case 1: em_pick<1>(k0, k1, vec, smem, block); return true;    case 2: em_pick<2>(k0, k1, vec, smem, block); return true;
+        case 3: em_pick<3>(k0, k1, vec, smem, block); return true;    case 4: em_pick<4>(k0, k1, vec, smem, block); return true;
+        case 5: em_pick<5>(k0, k1, vec, smem, block); return true;    case 6: em_pick<6>(k0, k1, vec, smem, block); return true;
+        case 7: em_pick<7>(k0, k1, vec, smem, block); return true;    case 8: em_pick<8>(k0, k1, vec, smem, block); return true;
+        case 9: em_pick<9>(k0, k1, vec, smem, block); return true;    case 10: em_pick<10>(k0, k1, vec, smem, block); return true;
+        case 11: em_pick<11>(k0, k1, vec, smem, block); return true;  case 12: em_pick<12>(k0, k1, vec, smem, block); return true;
+        case 13: em_pick<13>(k0, k1, vec, smem, block); return true;  case 14: em_pick<14>(k0, k1, vec, smem, block); return true;
+        case 15: em_pick<15>(k0, k1, vec, smem, block); return true;  case 16: em_pick<16>(k0, k1, vec, smem, block); return true;
     }
     return false;
 }
@@ -1478,9 +1481,9 @@ extern "C" int mcsim_cuda_em_estep(mcsim_cuda_ctx* c) {
     CK(cudaSetDevice(c->device));
     if (c->em_chunks) {   // configuration cached by the first E-step after mcsim_cuda_em_prepare
         const dim3 grid(c->em_chunks, (unsigned)c->em.n_fits);
-        c->em_k0<<<grid, 256, c->em_smem, c->stream>>>(c->em);
+        c->em_k0<<<grid, c->em_block, c->em_smem, c->stream>>>(c->em);
         ++c->launches;
-        if (c->em_k1) { c->em_k1<<<grid, 256, 0, c->stream>>>(c->em); ++c->launches; }
+        if (c->em_k1) { c->em_k1<<<grid, c->em_block, 0, c->stream>>>(c->em); ++c->launches; }
         CK(cudaGetLastError());
         return MCSIM_OK;
     }
@@ -1488,16 +1491,17 @@ extern "C" int mcsim_cuda_em_estep(mcsim_cuda_ctx* c) {
     // 128-bit loads when every row of every fit is 16-byte aligned
     const bool vec = (c->em.n % 4) == 0 && c->em.n >= 4;
     size_t smem = 0;
-    if (!em_kernels(c->em.K, k0, k1, vec, smem)) return fail(MCSIM_ERR_ARG, "em_estep: bad K");
+    int block = 256;
+    if (!em_kernels(c->em.K, k0, k1, vec, smem, block)) return fail(MCSIM_ERR_ARG, "em_estep: bad K");
     if (smem > 48 * 1024) CK(cudaFuncSetAttribute((const void*)k0, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     // chunks per fit: whole waves of resident CTAs with as little tail as possible (616 CTAs on 444 resident slots
     // ran at 70 % of what 392 do), at least ~8 samples per thread so the per-CTA reduction stays small
     int occ = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)k0, 256, smem));
-    if (k1) { int o1 = 0; CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, (const void*)k1, 256, 0)); if (o1 < occ) occ = o1; }
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)k0, block, smem));
+    if (k1) { int o1 = 0; CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, (const void*)k1, block, 0)); if (o1 < occ) occ = o1; }
     if (occ < 1) occ = 1;
     const unsigned long long resident = (unsigned long long)c->n_sm * occ, F = (unsigned long long)c->em.n_fits;
-    const unsigned long long per_cta = smem ? EM_TMA_TILE : 256ull * 8;
+    const unsigned long long per_cta = smem ? EM_TMA_TILE : (unsigned long long)block * 8;
     const unsigned long long most = (c->em.n + per_cta - 1) / per_cta ? (c->em.n + per_cta - 1) / per_cta : 1;
     unsigned long long chunks = 1;
     double best = -1.0;
@@ -1510,10 +1514,10 @@ extern "C" int mcsim_cuda_em_estep(mcsim_cuda_ctx* c) {
         if (eff > best + 0.02) { best = eff; chunks = ch; }
     }
     const dim3 grid((unsigned)chunks, (unsigned)c->em.n_fits);
-    c->em_k0 = k0; c->em_k1 = k1; c->em_smem = smem; c->em_chunks = (unsigned)chunks;
-    k0<<<grid, 256, smem, c->stream>>>(c->em);
+    c->em_k0 = k0; c->em_k1 = k1; c->em_smem = smem; c->em_chunks = (unsigned)chunks; c->em_block = block;
+    k0<<<grid, block, smem, c->stream>>>(c->em);
     ++c->launches;
-    if (k1) { k1<<<grid, 256, 0, c->stream>>>(c->em); ++c->launches; }
+    if (k1) { k1<<<grid, block, 0, c->stream>>>(c->em); ++c->launches; }
     CK(cudaGetLastError());
     return MCSIM_OK;
 }
@@ -1918,13 +1922,14 @@ extern "C" int mcsim_cuda_em_fit_static(const mcsim_em_static_params* p) {
     em_kernel_t k0, k1;
     const bool vec = (p->n % 4) == 0 && p->n >= 4 && (reinterpret_cast<uintptr_t>(p->x) & 15) == 0;
     size_t smem = 0;
-    if (!em_kernels(K, k0, k1, vec, smem)) return fail(MCSIM_ERR_ARG, "em_fit_static: bad K");
+    int block = 256;
+    if (!em_kernels(K, k0, k1, vec, smem, block)) return fail(MCSIM_ERR_ARG, "em_fit_static: bad K");
     if (smem > 48 * 1024) CK(cudaFuncSetAttribute((const void*)k0, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     int occ = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)k0, 256, smem));
-    if (k1) { int o1 = 0; CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, (const void*)k1, 256, 0)); if (o1 < occ) occ = o1; }
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, (const void*)k0, block, smem));
+    if (k1) { int o1 = 0; CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o1, (const void*)k1, block, 0)); if (o1 < occ) occ = o1; }
     if (occ < 1) occ = 1;
-    const unsigned long long resident = (unsigned long long)pd.n_sm * occ, per_cta = smem ? EM_TMA_TILE : 256ull * 8;
+    const unsigned long long resident = (unsigned long long)pd.n_sm * occ, per_cta = smem ? EM_TMA_TILE : (unsigned long long)block * 8;
     unsigned long long most = (p->n + per_cta - 1) / per_cta;
     if (most < 1) most = 1;
     unsigned long long chunks = 1;
@@ -1939,8 +1944,8 @@ extern "C" int mcsim_cuda_em_fit_static(const mcsim_em_static_params* p) {
     }
     const dim3 grid((unsigned)chunks, (unsigned)F);
     for (int it = 0; it < p->iters; ++it) {
-        k0<<<grid, 256, smem, st>>>(a);
-        if (k1) k1<<<grid, 256, 0, st>>>(a);
+        k0<<<grid, block, smem, st>>>(a);
+        if (k1) k1<<<grid, block, 0, st>>>(a);
         em_mstep_kernel<<<F, 32, 0, st>>>(a, 0);
         ++a.iter;
     }
