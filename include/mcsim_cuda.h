@@ -133,10 +133,18 @@ typedef struct {
                                     next launch runs full warps of them (same flags, hits and histogram; executed
                                     rollout-steps drop to the free ones); 1: one launch, a warp leaves when all its
                                     rollouts have hit */
+    int gmm_filter;              /* GMM / linear runs only: how a component's belief moves from waypoint t to t + 1.
+                                    MCSIM_FILTER_STATE (0): the reference's EKF on the state, linearised at the
+                                    component mean (MCSimulator.h:868-929).  MCSIM_FILTER_DEVIATION: method variant
+                                    (the paper's future work, finalpaper/ajaay_paper.tex:893, 901): a Kalman
+                                    filter on the deviation from the nominal plan, motion and sensor models linearised once
+                                    about (x*_t, u*_t) as in Patil et al. -- csrc/estimator_math.h lkf_*.  No reference
+                                    implementation exists: PARITY UNPINNED, checked against a NumPy restatement */
 } mcsim_mc_params;
 
 enum { MCSIM_MODE_REPLAY = 0, MCSIM_MODE_PHILOX = 1 };
 enum { MCSIM_EST_REFERENCE = 0, MCSIM_EST_CLOSEDLOOP = 1 };
+enum { MCSIM_FILTER_STATE = 0, MCSIM_FILTER_DEVIATION = 1 };
 
 typedef struct {
     uint64_t hits;               /* rollouts with >= 1 colliding waypoint */

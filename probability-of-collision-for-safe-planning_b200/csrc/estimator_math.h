@@ -187,6 +187,80 @@ MCSIM_HD void ekf_update_one(const T lx, const T ly, const T Q, T mu[3], T S[9],
     for (int j = 0; j < 9; ++j) S[j] = N[j];
 }
 
+// ---- deviation-state filter (method variant; the reference has none) ----------------------------
+// The paper's first item of future work (finalpaper/ajaay_paper.tex:893, 901): "produce a KF estimate of the deviation of
+// a robot's configuration from the nominal configuration", as Patil et al. / van den Berg's LQG-MP do.  State
+// delta_t = x_t - x*_t; motion and sensor models are linearised ONCE about the nominal plan (x*_t, u*_t), not about the
+// current estimate:
+//   predict   delta' = G* delta + V* (u - u*_t),   Sigma' = G* Sigma G*^T + V* M V*^T,   G*, V* at (x*_t, u*_t)
+//   update l  nu = z_l - |x*_{t+1} - m_l| - H*_l delta,  K = Sigma H*^T / (H* Sigma H*^T + Q),
+//             delta += K nu,  Sigma <- (I - K H*) Sigma,  H*_l at x*_{t+1} for every landmark (no relinearisation)
+// The filter is linear in the state, so mean and covariance of the belief do not interact.  Interfaces mirror
+// ekf_predict / ekf_update_one with the mean kept as an absolute pose (mu = x* + delta): xs = x*_t, xn = x*_{t+1},
+// us = u*_t, u = the command applied by the real robot.
+template <typename T>
+MCSIM_HD T wrap_pm_pi(T a) {
+    while (a > T(MCSIM_PI)) a -= T(2 * MCSIM_PI);
+    while (a <= -T(MCSIM_PI)) a += T(2 * MCSIM_PI);
+    return a;
+}
+template <typename T>
+MCSIM_HD void lkf_predict(const T mu[3], const T S[9], const T xs[3], const T xn[3], const T us[3], const T u[3], const T M[3], T pmu[3], T pS[9]) {
+    T sn, cs;
+    sincos_t(xs[2] + us[0], sn, cs);
+    const T g02 = -us[1] * sn, g12 = us[1] * cs;
+    T GS[9];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        GS[0 + j] = S[0 + j] + g02 * S[6 + j];
+        GS[3 + j] = S[3 + j] + g12 * S[6 + j];
+        GS[6 + j] = S[6 + j];
+    }
+    const T V[9] = {g02, cs, T(0), g12, sn, T(0), T(1), T(0), T(1)};
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const T a[3] = {GS[3 * i + 0] + GS[3 * i + 2] * g02, GS[3 * i + 1] + GS[3 * i + 2] * g12, GS[3 * i + 2]};
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            pS[3 * i + j] = a[j] + V[3 * i + 0] * M[0] * V[3 * j + 0] + V[3 * i + 1] * M[1] * V[3 * j + 1] + V[3 * i + 2] * M[2] * V[3 * j + 2];
+    }
+    // delta' = G* delta + V* du
+    // heading and rotation deviations are differences of angles kept in [0, 2 pi] (angleWrap): taken on (-pi, pi]
+    const T d0 = mu[0] - xs[0], d1 = mu[1] - xs[1], d2 = wrap_pm_pi(mu[2] - xs[2]);
+    const T du0 = wrap_pm_pi(u[0] - us[0]), du1 = u[1] - us[1], du2 = wrap_pm_pi(u[2] - us[2]);
+    pmu[0] = xn[0] + d0 + g02 * d2 + g02 * du0 + cs * du1;
+    pmu[1] = xn[1] + d1 + g12 * d2 + g12 * du0 + sn * du1;
+    pmu[2] = xn[2] + d2 + du0 + du2;
+}
+template <typename T>
+MCSIM_HD void lkf_update_one(const T lx, const T ly, const T Q, const T xn[3], T mu[3], T S[9], const T zl) {
+    const T dx = xn[0] - lx, dy = xn[1] - ly;
+    const T rq = sqrt_t(dx * dx + dy * dy);
+    const T h0 = dx / rq, h1 = dy / rq;
+    const T hs0 = h0 * S[0] + h1 * S[3];
+    const T hs1 = h0 * S[1] + h1 * S[4];
+    const T inv = T(1) / (hs0 * h0 + hs1 * h1 + Q);
+    const T k0 = (S[0] * h0 + S[1] * h1) * inv;
+    const T k1 = (S[3] * h0 + S[4] * h1) * inv;
+    const T k2 = (S[6] * h0 + S[7] * h1) * inv;
+    const T innov = zl - rq - (h0 * (mu[0] - xn[0]) + h1 * (mu[1] - xn[1]));
+    mu[0] += k0 * innov;
+    mu[1] += k1 * innov;
+    mu[2] += k2 * innov;
+    const T a00 = T(1) - k0 * h0, a01 = -k0 * h1;
+    const T a10 = -k1 * h0, a11 = T(1) - k1 * h1;
+    const T a20 = -k2 * h0, a21 = -k2 * h1;
+    T N[9];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        N[0 + j] = a00 * S[0 + j] + a01 * S[3 + j];
+        N[3 + j] = a10 * S[0 + j] + a11 * S[3 + j];
+        N[6 + j] = a20 * S[0 + j] + a21 * S[3 + j] + S[6 + j];
+    }
+#pragma unroll
+    for (int j = 0; j < 9; ++j) S[j] = N[j];
+}
+
 template <typename T>
 MCSIM_HD void ekf_update(const NoiseModel<T>& nm, T mu[3], T S[9], const T* z, const int L) {
 #pragma unroll

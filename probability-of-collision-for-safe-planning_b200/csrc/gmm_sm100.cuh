@@ -44,6 +44,7 @@ struct GmmStepTable {      // per step t (0..T-2), FP64: applied command, motion
     double u[3];
     double M[3];
     double z[MCSIM_MAX_LANDMARKS];
+    double xs[3], xn[3], us[3];   // nominal plan: x*_t, x*_{t+1}, u*_t (the deviation-state filter linearises about them)
 };
 
 struct GmmLaunch {
@@ -71,7 +72,8 @@ struct GmmLaunch {
     double* trunc_out;            // [K][GMM_REC] mixture right after THIS truncation (optional; gmm_truncate)
     unsigned long long* n_out;    // [2K] n_coll, n_free of this truncation (optional)
     int* degenerate;              // count of (waypoint, component) refits with < 2 free samples
-    int do_ekf;                   // refit kernel: propagate to waypoint t+1 (0 for the single-shot API)
+    int do_ekf;                   // refit kernel: propagate to waypoint t+1 (0 for the single-shot API); 1: the reference's EKF
+                                  // on the state, 2: deviation-state filter about the nominal plan (mcsim_mc_params.gmm_filter)
     int B;                        // batch: independent trajectories in the same launches (Philox mode; 0/1 = single)
     const float4* sat2;           // orientation-grouped FP32 pair table (Philox mode SAT)
     const unsigned* cull;         // Philox mode: the plan's candidate lists (sat_device.cuh), NULL = every pair
@@ -700,6 +702,18 @@ __device__ __forceinline__ void gmm_refit_moments(double* cp, const double* st, 
         atomicAdd(degenerate, 1);
     }
 }
+// one component's belief from waypoint t to t+1: EKFpredict (:766-772) + EKFupdate (:804-812) of the reference, or the
+// deviation-state filter (estimator_math.h) when the launch asks for it
+__device__ __forceinline__ void gmm_filter_step(const GmmLaunch& a, const GmmStepTable& s, const double* mu, const double* S, double* pmu, double* pS) {
+    using namespace mcsim_math;
+    if (a.do_ekf == 2) {
+        lkf_predict(mu, S, s.xs, s.xn, s.us, s.u, s.M, pmu, pS);
+        for (int l = 0; l < a.L; ++l) lkf_update_one(a.lx[l], a.ly[l], a.Q, s.xn, pmu, pS, s.z[l]);
+    } else {
+        ekf_predict(mu, S, s.u, s.M, pmu, pS);
+        for (int l = 0; l < a.L; ++l) ekf_update_one(a.lx[l], a.ly[l], a.Q, pmu, pS, s.z[l]);   // landmarks straight from the launch struct
+    }
+}
 // Part 2 (after every component's part 1): weight, p_t, records, EKFpredict + EKFupdate to waypoint t+1, Cholesky.
 __device__ __forceinline__ void gmm_refit_finish(const GmmLaunch& a, const GmmMember& m, int t, int g, double* cp, const double* s_free, const double* s_coll,
                                                  const GmmStepTable* staged_step = nullptr) {
@@ -717,8 +731,7 @@ __device__ __forceinline__ void gmm_refit_finish(const GmmLaunch& a, const GmmMe
     if (a.do_ekf && t < a.T - 1) {
         const GmmStepTable& s = staged_step ? *staged_step : m.steps[t];
         double pmu[3], pS[9];
-        ekf_predict(cp + 1, cp + 4, s.u, s.M, pmu, pS);
-        for (int l = 0; l < a.L; ++l) ekf_update_one(a.lx[l], a.ly[l], a.Q, pmu, pS, s.z[l]);   // landmarks straight from the launch struct
+        gmm_filter_step(a, s, cp + 1, cp + 4, pmu, pS);
         for (int k = 0; k < 3; ++k) cp[1 + k] = pmu[k];
         for (int k = 0; k < 9; ++k) cp[4 + k] = pS[k];
         if (a.rec_pre) for (int k = 0; k < GMM_REC; ++k) a.rec_pre[(size_t(t + 1) * K + g) * GMM_REC + k] = cp[k];
@@ -774,8 +787,7 @@ __global__ void __launch_bounds__(32) gmm_propagate_kernel(const GmmLaunch a_in)
     if (a.do_ekf && t < a.T - 1) {
         const GmmStepTable& s = m.steps[t];
         double pmu[3], pS[9];
-        ekf_predict(cp + 1, cp + 4, s.u, s.M, pmu, pS);
-        for (int l = 0; l < a.L; ++l) ekf_update_one(a.lx[l], a.ly[l], a.Q, pmu, pS, s.z[l]);
+        gmm_filter_step(a, s, cp + 1, cp + 4, pmu, pS);
         for (int k = 0; k < 3; ++k) cp[1 + k] = pmu[k];
         for (int k = 0; k < 9; ++k) cp[4 + k] = pS[k];
         if (a.rec_pre) for (int k = 0; k < GMM_REC; ++k) a.rec_pre[(size_t(t + 1) * K + g) * GMM_REC + k] = cp[k];
@@ -830,8 +842,7 @@ __global__ void __launch_bounds__(32) gmm_linear_run_kernel(const GmmLaunch a_in
             if (t < T - 1) {
                 const GmmStepTable& s = m.steps[t];
                 double pmu[3], pS[9];
-                ekf_predict(cp + 1, cp + 4, s.u, s.M, pmu, pS);
-                for (int l = 0; l < a.L; ++l) ekf_update_one(a.lx[l], a.ly[l], a.Q, pmu, pS, s.z[l]);
+                gmm_filter_step(a, s, cp + 1, cp + 4, pmu, pS);
                 for (int k = 0; k < 3; ++k) cp[1 + k] = pmu[k];
                 for (int k = 0; k < 9; ++k) cp[4 + k] = pS[k];
             }
@@ -1250,7 +1261,7 @@ __global__ void __launch_bounds__(32) gmm_robot_thread_kernel(const RobotThreadL
         for (int k = 0; k < 3; ++k) real[k] = nxt[k];
         for (int l = 0; l < L; ++l) zobs[l] = range_to(nm, real, l) + z[3 + l] * sq;
         ekf_update(nm, pmu, pS, zobs, L);
-        for (int k = 0; k < 3; ++k) { mu[k] = pmu[k]; st.u[k] = u[k]; st.M[k] = M[k]; }
+        for (int k = 0; k < 3; ++k) { mu[k] = pmu[k]; st.u[k] = u[k]; st.M[k] = M[k]; st.xs[k] = xs[k]; st.xn[k] = xg[k]; st.us[k] = ustar[k]; }
         for (int k = 0; k < 9; ++k) S[k] = pS[k];
         for (int l = 0; l < L; ++l) st.z[l] = zobs[l];
     }

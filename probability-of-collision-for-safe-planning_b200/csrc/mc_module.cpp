@@ -83,6 +83,7 @@ const MCModule::Command MCModule::kCommands[] = {
     {"setBroadPhase", &MCModule::setBroadPhase, "setBroadPhase 0|1: 1 (default) tests only the obstacles within reach of each waypoint, 0 every obstacle at every step (the returned P does not change)"},
     {"setEstimator", &MCModule::setEstimator, "setEstimator reference|closedloop: collision tested on the particle (reference) or on the real state"},
     {"setRolloutOffset", &MCModule::setRolloutOffset, "setRolloutOffset <u64>: global id of this module's first rollout (shards of one job over several modules / processes)"},
+    {"setFilter", &MCModule::setFilter, "setFilter state | deviation: runGMMEstimation / runLinearEstimation propagate each component with the reference's EKF on the state (default) or with a Kalman filter on the deviation from the nominal plan, linearised about the plan"},
     {"setRefit", &MCModule::setRefit, "setRefit moments | em [iterations]: runGMMEstimation refits each component by moment matching (the reference, default) or refits the whole mixture to the collision-free samples by EM started from the moment-matched one (default 5 iterations)"},
     {"setConstraints", &MCModule::setConstraints, "setConstraints <n> then n x (ax ay b xmin xmax ymin ymax): the free space as linear constraints ax x + ay y <= b inside a window (linConstraint.py:4-11; 'inf' / '-inf' for an open side)"},
     {"runLinearEstimation", &MCModule::runLinearEstimation, "P(collision) by propagating the mixture with the analytic (Patil) truncation against the constraints of setConstraints instead of sampling"},

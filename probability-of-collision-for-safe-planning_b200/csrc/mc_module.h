@@ -80,6 +80,7 @@ class MCModule {
     bool setEstimator(std::ostream&, std::istream&);
     bool setRolloutOffset(std::ostream&, std::istream&);
     bool setRefit(std::ostream&, std::istream&);
+    bool setFilter(std::ostream&, std::istream&);
     bool setConstraints(std::ostream&, std::istream&);
     bool runLinearEstimation(std::ostream&, std::istream&);
     bool setDevices(std::ostream&, std::istream&);
@@ -132,6 +133,7 @@ class MCModule {
     std::vector<double> draws_;
     std::vector<int> gmm_counts_;
     int refit_ = MCSIM_GMM_REFIT_MOMENTS;   // setRefit: how truncateGMM refits the mixture
+    int gmm_filter_ = MCSIM_FILTER_STATE;   // setFilter: EKF on the state (reference) or Kalman filter on the deviation from the plan
     int em_iters_ = 0;
     std::vector<double> con_A_, con_b_;     // setConstraints, expanded into half-planes A (x, y, theta) <= b
     // results of the last run

@@ -58,6 +58,7 @@ void MCModule::fill_params(mcsim_mc_params& p) const {
     p.estimator = estimator_;
     p.early_exit = early_exit_;
     p.exhaustive = exhaustive_;
+    p.gmm_filter = gmm_filter_;
     p.seed = seed_;
     p.near_eps = 1e-4;
 }
@@ -270,6 +271,18 @@ bool MCModule::setRefit(std::ostream&, std::istream& sinput) {
     if (sinput >> it) { if (it < 1 || it > 1000) throw std::runtime_error("setRefit: 1..1000 EM iterations expected"); }
     refit_ = MCSIM_GMM_REFIT_EM;
     em_iters_ = it;
+    return true;
+}
+
+// setFilter state | deviation: how runGMMEstimation / runLinearEstimation move a component's belief to the next waypoint --
+// the reference's EKF on the state (MCSimulator.h:868-929), or a Kalman filter on the deviation from the nominal plan,
+// linearised about the plan (the paper's future work, finalpaper/ajaay_paper.tex:893, 901; mcsim_mc_params.gmm_filter)
+bool MCModule::setFilter(std::ostream&, std::istream& sinput) {
+    std::string m;
+    sinput >> m;
+    if (m == "state") gmm_filter_ = MCSIM_FILTER_STATE;
+    else if (m == "deviation") gmm_filter_ = MCSIM_FILTER_DEVIATION;
+    else throw std::runtime_error("setFilter: state | deviation expected, got '" + m + "'");
     return true;
 }
 

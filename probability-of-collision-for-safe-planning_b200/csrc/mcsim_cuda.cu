@@ -1050,6 +1050,12 @@ static int gmm_em_refit(mcsim_cuda_ctx* c, int K, uint64_t N, int iters, double 
     }
     return MCSIM_OK;
 }
+// GmmLaunch.do_ekf of a run: 1 = the reference's EKF on the state, 2 = the deviation-state filter (mcsim_mc_params.gmm_filter)
+static int gmm_filter_code(const mcsim_mc_params* mc, int* code) {
+    if (mc->gmm_filter != MCSIM_FILTER_STATE && mc->gmm_filter != MCSIM_FILTER_DEVIATION) return fail(MCSIM_ERR_ARG, "gmm: unknown gmm_filter %d", mc->gmm_filter);
+    *code = mc->gmm_filter == MCSIM_FILTER_DEVIATION ? 2 : 1;
+    return MCSIM_OK;
+}
 static int gmm_keep_free_samples(mcsim_cuda_ctx* c, GmmLaunch& a, uint64_t N) {
     if (N >= (1ull << 31)) return fail(MCSIM_ERR_ARG, "gmm: the EM-refit variant takes fewer than 2^31 samples per waypoint");
     CK(c->gmm_free.reserve(sizeof(float) * 3 * size_t(N)));
@@ -1075,6 +1081,7 @@ static int gmm_host_steps(const mcsim_mc_params* mc, const std::vector<double>& 
     for (int t = 0; t < T - 1; ++t) {
         double us[3];
         for (int k = 0; k < 3; ++k) { us[k] = mc->odometry[k * (T - 1) + t]; steps[t].u[k] = applied[k * (T - 1) + t]; }
+        for (int k = 0; k < 3; ++k) { steps[t].xs[k] = mc->trajectory[k * T + t]; steps[t].xn[k] = mc->trajectory[k * T + t + 1]; steps[t].us[k] = us[k]; }
         mcsim_math::motion_noise(nmd, us, steps[t].M);
         for (int l = 0; l < L; ++l) steps[t].z[l] = obs[size_t(t) * L + l];
     }
@@ -1125,6 +1132,7 @@ extern "C" int mcsim_cuda_linear_run(mcsim_cuda_ctx* c, const mcsim_mc_params* m
     for (int l = 0; l < L; ++l) { a.lx[l] = mc->landmarks[l]; a.ly[l] = mc->landmarks[L + l]; }
     a.rec_pre = r->gmm_pre ? (double*)c->gmm_pre.p : nullptr;
     a.rec_post = (double*)c->gmm_post.p;
+    if ((rc = gmm_filter_code(mc, &a.do_ekf))) return rc;
     CK(cudaEventRecord(c->ev0, c->stream));
     gmm_linear_run_kernel<<<1, 32, 0, c->stream>>>(a, (const double*)c->lin_A.p, (const double*)c->lin_b.p, n_con);
     ++c->launches;
@@ -1219,7 +1227,9 @@ extern "C" int mcsim_cuda_gmm_run(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, 
     for (int l = 0; l < L; ++l) { a.lx[l] = mc->landmarks[l]; a.ly[l] = mc->landmarks[L + l]; }
     a.rec_pre = (double*)c->gmm_pre.p;
     a.rec_post = (double*)c->gmm_post.p;
-    a.do_ekf = 1;
+    int filter_code = 1;
+    if ((rc = gmm_filter_code(mc, &filter_code))) return rc;
+    a.do_ekf = filter_code;
     a.counts_replay = (const int*)c->gmm_counts.p;
     if (mode == MCSIM_MODE_PHILOX) { rc = gmm_upload_cull(c, a, mc->trajectory, 1, T, mc->exhaustive != 0); if (rc) return rc; }
     const bool em_refit = g->refit == MCSIM_GMM_REFIT_EM;
@@ -1246,7 +1256,7 @@ extern "C" int mcsim_cuda_gmm_run(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, 
             for (int k = 0; k < K; ++k) memcpy(&cps[size_t(k) * GMM_COMP], &mix[size_t(k) * GMM_REC], sizeof(double) * GMM_REC);
             CK(cudaMemcpyAsync(c->gmm_comps.p, cps.data(), sizeof(double) * cps.size(), cudaMemcpyHostToDevice, c->stream));
             GmmLaunch pa = a;
-            pa.do_ekf = 1;
+            pa.do_ekf = filter_code;
             gmm_propagate_kernel<<<1, 32, 0, c->stream>>>(pa);
             ++c->launches;
             CK(cudaGetLastError());
@@ -1789,7 +1799,7 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
     gmm_fill_launch(c, a, K, T, L, N, mc->seed, unsigned(g->stream0));
     a.Q = mc->Q;
     for (int l = 0; l < L; ++l) { a.lx[l] = mc->landmarks[l]; a.ly[l] = mc->landmarks[L + l]; }
-    a.do_ekf = 1;
+    if ((rc = gmm_filter_code(mc, &a.do_ekf))) return rc;
     a.B = B;
     rc = g->trajectories ? gmm_upload_cull(c, a, g->trajectories, B, T, mc->exhaustive != 0)
                          : gmm_upload_cull(c, a, mc->trajectory, 1, T, mc->exhaustive != 0);

@@ -31,7 +31,7 @@ class McParams(C.Structure):
         ("n_rollouts", C.c_uint64), ("rollout_offset", C.c_uint64),
         ("mode", C.c_int), ("estimator", C.c_int), ("early_exit", C.c_int), ("seed", C.c_uint64),
         ("applied", _dp), ("z0", _dp), ("near_eps", C.c_double), ("precise", C.c_int), ("exhaustive", C.c_int),
-        ("no_compaction", C.c_int),
+        ("no_compaction", C.c_int), ("gmm_filter", C.c_int),
     ]
 
 
@@ -63,6 +63,7 @@ class EmStaticParams(C.Structure):
 
 EM_STATIC_MAX_FITS, EM_STATIC_MAX_ITERS, EM_STATIC_SCRATCH_BYTES = 8, 64, 32768
 EM_EXCHANGE_AUTO, EM_EXCHANGE_NCCL, EM_EXCHANGE_PEER = 0, 1, 2
+FILTER_STATE, FILTER_DEVIATION = 0, 1
 
 
 class EmResult(C.Structure):
@@ -228,7 +229,8 @@ def dptr(a):
 
 
 def make_mc_params(plan, n_rollouts=0, mode=MODE_PHILOX, estimator=EST_REFERENCE, early_exit=True,
-                   seed=0x5AFEC0DE, rollout_offset=0, applied=None, z0=None, near_eps=1e-4, precise=False, exhaustive=False, no_compaction=False):
+                   seed=0x5AFEC0DE, rollout_offset=0, applied=None, z0=None, near_eps=1e-4, precise=False, exhaustive=False, no_compaction=False,
+                   gmm_filter=0):
     """plan: dict(trajectory[3,T], odometry[3,T-1], alphas[4], Q, landmarks[2,L], cov0[3,3]).
     Returns (McParams, keepalive list of the arrays its pointers refer to)."""
     tr = np.ascontiguousarray(plan["trajectory"], dtype=np.float64)
@@ -256,6 +258,7 @@ def make_mc_params(plan, n_rollouts=0, mode=MODE_PHILOX, estimator=EST_REFERENCE
     p.precise = int(bool(precise))
     p.exhaustive = int(bool(exhaustive))
     p.no_compaction = int(bool(no_compaction))
+    p.gmm_filter = int(gmm_filter)
     return p, keep
 
 
@@ -424,10 +427,10 @@ class Context:
         return int(a.value), int(b.value)
 
     def gmm_run(self, plan, K, n_samples, mode=MODE_PHILOX, seed=0x5AFEC0DE, stream_id=0, draws=None, counts=None,
-                record=False, exhaustive=False, kernel=GMM_KERNEL_AUTO, refit=GMM_REFIT_MOMENTS, em_iters=0):
+                record=False, exhaustive=False, kernel=GMM_KERNEL_AUTO, refit=GMM_REFIT_MOMENTS, em_iters=0, gmm_filter=0):
         """runGMMEstimation of one plan (MCSimulator.h:354-358 -> the GMM branch of EKF_GaussProp).
         Replay mode: draws = the reference's normal stream of the run, counts[T, K] = multinomial counts."""
-        p, keep = make_mc_params(plan, mode=mode, seed=seed, rollout_offset=stream_id, exhaustive=exhaustive)
+        p, keep = make_mc_params(plan, mode=mode, seed=seed, rollout_offset=stream_id, exhaustive=exhaustive, gmm_filter=gmm_filter)
         T = int(p.T)
         g = GmmRunParams()
         g.K, g.n_samples, g.kernel, g.refit, g.em_iters = int(K), int(n_samples), int(kernel), int(refit), int(em_iters)
@@ -564,10 +567,10 @@ class Context:
         return torch.as_tensor(raw, device="cuda:%d" % self.device)
 
     def gmm_run_batch(self, plan, K, n_samples, n_traj, trajectories=None, odometry=None, seed=0x5AFEC0DE, stream0=0,
-                      exhaustive=False, kernel=GMM_KERNEL_AUTO):
+                      exhaustive=False, kernel=GMM_KERNEL_AUTO, gmm_filter=0):
         """n_traj independent runGMMEstimation runs in the same launches (Philox mode); member b ==
         gmm_run(..., stream_id=stream0 + b) on plan b (trajectories [n_traj, 3, T]) or on `plan`."""
-        p, keep = make_mc_params(plan, mode=MODE_PHILOX, seed=seed, exhaustive=exhaustive)
+        p, keep = make_mc_params(plan, mode=MODE_PHILOX, seed=seed, exhaustive=exhaustive, gmm_filter=gmm_filter)
         T = int(p.T)
         g = GmmBatchParams()
         g.K, g.n_samples, g.n_traj, g.stream0, g.kernel = int(K), int(n_samples), int(n_traj), int(stream0), int(kernel)
@@ -584,10 +587,10 @@ class Context:
         out.update(degenerate=int(r.degenerate), kernel_ms=float(r.kernel_ms), pair_tests=int(r.pair_tests))
         return out
 
-    def linear_run(self, plan, K, A, b, seed=0x5AFEC0DE, stream_id=0, normals=None, record=False):
+    def linear_run(self, plan, K, A, b, seed=0x5AFEC0DE, stream_id=0, normals=None, record=False, gmm_filter=0):
         """The GMM belief propagation with the analytic linear-constraint truncation (mcsim_cuda_linear_run):
         free region = all x with A[k] . x <= b[k]."""
-        p, keep = make_mc_params(plan, mode=MODE_PHILOX, seed=seed, rollout_offset=stream_id)
+        p, keep = make_mc_params(plan, mode=MODE_PHILOX, seed=seed, rollout_offset=stream_id, gmm_filter=gmm_filter)
         T = int(p.T)
         Aa = np.ascontiguousarray(A, dtype=np.float64).reshape(-1, 3)
         bb = np.ascontiguousarray(b, dtype=np.float64).reshape(-1)
