@@ -120,6 +120,13 @@ def test_command_grammar_parse_only(plan, scenes):
     with pytest.raises(pcoll_b200.McsimError):
         mod.SendCommand("setMode sometimes")
     assert mod.SendCommand("setMode deterministic") == ""
+    # method-variant switches (round 2) parse without a device too
+    assert mod.SendCommand("setFilter deviation") == "" and mod.SendCommand("setFilter state") == ""
+    assert mod.SendCommand("setRefit em 3") == "" and mod.SendCommand("setRefit moments") == ""
+    with pytest.raises(pcoll_b200.McsimError, match="state \\| deviation"):
+        mod.SendCommand("setFilter both")
+    for name in ("setFilter", "setRefit", "setConstraints", "runLinearEstimation", "setDevices", "runGMMEstimationBatch"):
+        assert re.search(r"^%s : " % name, h, re.M), name
     mod.close()
 
 
