@@ -187,6 +187,30 @@ MCSIM_HD void ekf_update_one(const T lx, const T ly, const T Q, T mu[3], T S[9],
     for (int j = 0; j < 9; ++j) S[j] = N[j];
 }
 
+// EKFupdate for one landmark with ONE division on the dependent chain mu_l -> mu_{l+1} (the 8 updates of a step are
+// serial per component, and in FP64 a square root and each division cost ~200 dependent cycles).  With d = (mu - m_l)_xy,
+// q = |d|^2 and H = d^T / sqrt(q):  c = Sigma_{.,xy} d  (= Sigma H^T sqrt(q)),  r = d^T Sigma_{xy,.}  (= H Sigma sqrt(q)),
+// D = d . r_xy + Q q  (= q S of :905),   K (z - zhat) = c (sqrt(q) z - q) / D,   K H Sigma = c r^T / D
+// -- the reference's update (ekf_update_one above, non-Joseph, Sigma's asymmetry kept: c and r are computed separately)
+// up to rounding; sqrt(q) is off the chain.  Used by the device GMM path in Philox mode, where the bar is statistical;
+// replay mode and the real-robot thread keep the reference's order of operations.
+template <typename T>
+MCSIM_HD void ekf_update_one_chain1(const T lx, const T ly, const T Q, T mu[3], T S[9], const T zl) {
+    const T dx = mu[0] - lx, dy = mu[1] - ly;
+    const T q = dx * dx + dy * dy;
+    const T c0 = S[0] * dx + S[1] * dy, c1 = S[3] * dx + S[4] * dy, c2 = S[6] * dx + S[7] * dy;
+    const T r0 = dx * S[0] + dy * S[3], r1 = dx * S[1] + dy * S[4], r2 = dx * S[2] + dy * S[5];
+    const T inv = T(1) / (dx * r0 + dy * r1 + Q * q);
+    const T w = (sqrt_t(q) * zl - q) * inv;
+    mu[0] += c0 * w;
+    mu[1] += c1 * w;
+    mu[2] += c2 * w;
+    const T b0 = c0 * inv, b1 = c1 * inv, b2 = c2 * inv;
+    S[0] -= b0 * r0; S[1] -= b0 * r1; S[2] -= b0 * r2;
+    S[3] -= b1 * r0; S[4] -= b1 * r1; S[5] -= b1 * r2;
+    S[6] -= b2 * r0; S[7] -= b2 * r1; S[8] -= b2 * r2;
+}
+
 // ---- deviation-state filter (method variant; the reference has none) ----------------------------
 // The paper's first item of future work (finalpaper/ajaay_paper.tex:893, 901): "produce a KF estimate of the deviation of
 // a robot's configuration from the nominal configuration", as Patil et al. / van den Berg's LQG-MP do.  State

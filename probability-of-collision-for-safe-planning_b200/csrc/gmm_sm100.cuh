@@ -74,6 +74,7 @@ struct GmmLaunch {
     int* degenerate;              // count of (waypoint, component) refits with < 2 free samples
     int do_ekf;                   // refit kernel: propagate to waypoint t+1 (0 for the single-shot API); 1: the reference's EKF
                                   // on the state, 2: deviation-state filter about the nominal plan (mcsim_mc_params.gmm_filter)
+    int fast_filter;              // Philox mode: EKF updates with one division on the dependent chain (same update up to rounding)
     int B;                        // batch: independent trajectories in the same launches (Philox mode; 0/1 = single)
     const float4* sat2;           // orientation-grouped FP32 pair table (Philox mode SAT)
     const unsigned* cull;         // Philox mode: the plan's candidate lists (sat_device.cuh), NULL = every pair
@@ -709,6 +710,9 @@ __device__ __forceinline__ void gmm_filter_step(const GmmLaunch& a, const GmmSte
     if (a.do_ekf == 2) {
         lkf_predict(mu, S, s.xs, s.xn, s.us, s.u, s.M, pmu, pS);
         for (int l = 0; l < a.L; ++l) lkf_update_one(a.lx[l], a.ly[l], a.Q, s.xn, pmu, pS, s.z[l]);
+    } else if (a.fast_filter) {   // Philox mode: the same update with one division on the serial chain (estimator_math.h)
+        ekf_predict(mu, S, s.u, s.M, pmu, pS);
+        for (int l = 0; l < a.L; ++l) ekf_update_one_chain1(a.lx[l], a.ly[l], a.Q, pmu, pS, s.z[l]);
     } else {
         ekf_predict(mu, S, s.u, s.M, pmu, pS);
         for (int l = 0; l < a.L; ++l) ekf_update_one(a.lx[l], a.ly[l], a.Q, pmu, pS, s.z[l]);   // landmarks straight from the launch struct

@@ -1230,6 +1230,7 @@ extern "C" int mcsim_cuda_gmm_run(mcsim_cuda_ctx* c, const mcsim_mc_params* mc, 
     int filter_code = 1;
     if ((rc = gmm_filter_code(mc, &filter_code))) return rc;
     a.do_ekf = filter_code;
+    a.fast_filter = mode == MCSIM_MODE_PHILOX;
     a.counts_replay = (const int*)c->gmm_counts.p;
     if (mode == MCSIM_MODE_PHILOX) { rc = gmm_upload_cull(c, a, mc->trajectory, 1, T, mc->exhaustive != 0); if (rc) return rc; }
     const bool em_refit = g->refit == MCSIM_GMM_REFIT_EM;
@@ -1800,6 +1801,7 @@ extern "C" int mcsim_cuda_gmm_run_batch(mcsim_cuda_ctx* c, const mcsim_mc_params
     a.Q = mc->Q;
     for (int l = 0; l < L; ++l) { a.lx[l] = mc->landmarks[l]; a.ly[l] = mc->landmarks[L + l]; }
     if ((rc = gmm_filter_code(mc, &a.do_ekf))) return rc;
+    a.fast_filter = 1;   // batches are Philox mode
     a.B = B;
     rc = g->trajectories ? gmm_upload_cull(c, a, g->trajectories, B, T, mc->exhaustive != 0)
                          : gmm_upload_cull(c, a, mc->trajectory, 1, T, mc->exhaustive != 0);
