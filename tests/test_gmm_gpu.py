@@ -238,6 +238,20 @@ def test_gmm_batch_fused_kernel_edge_cases(ctx, plan, scenes, K, N):
     np.testing.assert_allclose(f2["probabilities"][:2], p2["probabilities"], rtol=1e-9, atol=1e-12)
 
 
+@pytest.mark.parametrize("B,K,N", [(256, 3, 2000), (592, 5, 1500), (592, 2, 2049)])
+def test_gmm_batch_fused_kernel_cta_shapes(ctx, plan, scenes, B, K, N):
+    """The one-CTA-per-run kernel is launched with 512, 256 or 128 threads per run depending on the batch size
+    (gmm_member_threads: 148-SM B200 -> 256 runs take 256 threads, 592 take 128); the sample -> thread mapping changes with
+    the shape, the draws per sample index do not: members equal the per-waypoint kernels' runs whatever the shape.
+    K = 5 takes the count pass's generic path (more than 4 components), 2,049 samples leave a one-sample tail window."""
+    ctx.set_scene(scenes["pr2test2"]["boxes"], scenes["pr2test2"]["hulls"])
+    fused = ctx.gmm_run_batch(plan, K, N, B, stream0=4000)
+    for b0 in (0, B // 2 - 1, B - 2):
+        pair = ctx.gmm_run_batch(plan, K, N, 2, stream0=4000 + b0)
+        np.testing.assert_allclose(fused["probabilities"][b0:b0 + 2], pair["probabilities"], rtol=1e-9, atol=1e-12)
+    assert np.all((fused["P"] >= 0) & (fused["P"] <= 1)) and fused["P"].std() > 0
+
+
 @pytest.mark.parametrize("K,N", [(3, 10000), (1, 10001), (16, 3000), (2, 100), (3, 32768)])
 def test_gmm_cluster_kernel_equals_per_waypoint_kernels(ctx, plan, scenes, K, N, monkeypatch):
     """One-cluster-per-run kernel (single runs and batches below 64 in Philox mode, N <= 32,768) against the
