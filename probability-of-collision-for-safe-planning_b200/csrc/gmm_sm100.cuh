@@ -559,12 +559,13 @@ __device__ __forceinline__ void gmm_acc_add(bool valid, bool hit, float d0, floa
         }
     }
 }
-// all samples of a waypoint for one warp of a 256-thread CTA (pass stride 512 samples, window = 64 samples per warp)
+// all samples of a waypoint that fall to one warp: its 64-sample windows start at wbase, wbase + stride, ... (one CTA per
+// run: wbase = 64 warp, stride = 2 blockDim; a cluster per run: the CTAs' passes interleave, gmm_cluster_run_kernel)
 __device__ __forceinline__ void gmm_member_samples(unsigned stream_id, unsigned ctr2, unsigned k0, unsigned k1, unsigned n, int K,
                                                    const unsigned* s_prefix, const float (*s_mu)[3], const float (*s_L)[6], double (*s_stat)[GMM_STAT],
-                                                   const float4* tab, const unsigned char* ccnt, const ushort2* cidx, bool cull, float2 nom, unsigned& my_tests) {
-    const unsigned lane2 = 2u * (threadIdx.x & 31u), wbase = 64u * (threadIdx.x >> 5);
-    const unsigned stride = 2u * blockDim.x;
+                                                   const float4* tab, const unsigned char* ccnt, const ushort2* cidx, bool cull, float2 nom, unsigned& my_tests,
+                                                   unsigned wbase, unsigned stride) {
+    const unsigned lane2 = 2u * (threadIdx.x & 31u);
     int gw = 0;   // component of the window's first sample (warp-uniform)
     for (unsigned w0 = wbase; w0 < n;) {
         while (gw < K - 1 && w0 >= s_prefix[gw + 1]) ++gw;
@@ -985,7 +986,8 @@ __global__ void __launch_bounds__(GMM_MEMBER_MAX_THREADS, 1) gmm_member_run_kern
             const float2 nom = cull ? __ldg(m.nominal + t) : make_float2(0.f, 0.f);
             const unsigned char* cc = s_ccnt + t * nh * MC_CULL_LEVELS;
             const ushort2* ci = s_cidx + t * nh * MC_CULL_CAP;
-            gmm_member_samples(stream_id, unsigned(2 * t), k0, k1, n, K, s_prefix, s_mu, s_L, s_stat, s_tab, cc, ci, cull, nom, my_tests);
+            gmm_member_samples(stream_id, unsigned(2 * t), k0, k1, n, K, s_prefix, s_mu, s_L, s_stat, s_tab, cc, ci, cull, nom, my_tests,
+                               64u * (threadIdx.x >> 5), 2u * blockDim.x);
         }
         __syncthreads();
         // ---- refit + propagate (gmm_refit_kernel)
@@ -1149,15 +1151,14 @@ __global__ void __launch_bounds__(GMM_CLUSTER_THREADS, 1) gmm_cluster_run_kernel
         __syncthreads();
         // ---- sample -> collide -> moments: this CTA's share of the sample pairs
         {
-            int g = 0;
-            GmmAcc acc;
             const unsigned n = s_prefix[K] < n_all ? s_prefix[K] : n_all;
             const float2 nom = cull ? __ldg(m.nominal + t) : make_float2(0.f, 0.f);
             const unsigned char* cc = s_ccnt + t * nh * MC_CULL_LEVELS;
             const ushort2* ci = s_cidx + t * nh * MC_CULL_CAP;
-            for (unsigned base = 2 * blockDim.x * rank; base < n; base += 2 * blockDim.x * CL)
-                gmm_philox_pass2(stream_id, unsigned(2 * t), k0, k1, base + 2 * threadIdx.x, base + 2 * threadIdx.x + 1, n, K, g, s_prefix, s_mu, s_L, s_stat, s_tab, cc, ci, cull, nom, acc, my_tests);
-            acc.flush(s_stat);
+            // the same sample -> thread mapping as before (pass p of CTA `rank` covers 2 blockDim samples from
+            // 2 blockDim (rank + p CL)), walked as per-warp windows: component in registers, one reduction per component
+            gmm_member_samples(stream_id, unsigned(2 * t), k0, k1, n, K, s_prefix, s_mu, s_L, s_stat, s_tab, cc, ci, cull, nom, my_tests,
+                               2u * blockDim.x * rank + 64u * (threadIdx.x >> 5), 2u * blockDim.x * CL);
         }
         __syncthreads();
         // ---- partial statistics -> slot [rank] of every CTA
