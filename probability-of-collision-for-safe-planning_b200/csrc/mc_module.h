@@ -89,6 +89,7 @@ class MCModule {
     bool setGeometry(std::ostream&, std::istream&);
     bool setScene(std::ostream&, std::istream&);
     bool setRobotPolygons(std::ostream&, std::istream&);
+    bool setRobotModel(std::ostream&, std::istream&);
     bool getWaypointProbabilities(std::ostream&, std::istream&);
     bool getFirstHitHistogram(std::ostream&, std::istream&);
     bool getGMM(std::ostream&, std::istream&);

@@ -6,6 +6,7 @@
 #include <stdexcept>
 
 #include "mc_module.h"
+#include "collada_hulls.h"
 
 namespace mcsim {
 namespace {
@@ -415,6 +416,26 @@ bool MCModule::setRobotPolygons(std::ostream&, std::istream& sinput) {
     }
     scene_.poly_hulls.swap(rows);
     upload_scene();
+    return true;
+}
+
+// setRobotModel <path.zae | path.dae> [z0 z1 ... zk]: the robot's hull set from a COLLADA model (what the reference's scenes
+// name as their robot, pr2test2.env.xml:120) -- one convex footprint per z-band, replacing box and polygon hulls alike.
+// Band boundaries are in the model frame (k <= MCSIM_MAX_POLY_HULLS bands; none given: that many equal bands).
+bool MCModule::setRobotModel(std::ostream& sout, std::istream& sinput) {
+    std::string path;
+    if (!(sinput >> path)) throw std::runtime_error("setRobotModel: a .zae / .dae path expected");
+    ColladaOptions opt;
+    opt.max_bands = MCSIM_MAX_POLY_HULLS;
+    double z;
+    while (sinput >> z) opt.z_edges.push_back(z);
+    if (opt.z_edges.size() == 1) throw std::runtime_error("setRobotModel: one band boundary is not a band");
+    if (opt.z_edges.size() > size_t(MCSIM_MAX_POLY_HULLS) + 1) throw std::runtime_error("setRobotModel: at most " + std::to_string(MCSIM_MAX_POLY_HULLS) + " bands");
+    std::vector<double> rows = load_collada_hulls(path, opt);
+    scene_.hulls.clear();
+    scene_.poly_hulls.swap(rows);
+    upload_scene();
+    sout << scene_.n_poly_hulls();
     return true;
 }
 

@@ -9,6 +9,8 @@
 //   frame of a sibling body; KinBody-level <Translation>/<RotationAxis> move the whole body; file="..." pulls
 //   geometry from another file, resolved next to the env file and then on the fixture path (ikeatable.kinbody.xml
 //   and the PR2 model are not in the reference repository); tag case varies (<translation>, pr2test2.env.xml:121).
+//   A <Robot file> that resolves to a COLLADA model (.zae / .dae, what the reference's scenes name) is reduced to convex
+//   footprints per z-band by collada_hulls.cpp; when only the box fixture is there, that is read instead.
 // Beyond the reference's files (robot hull sets that are not boxes): <Geom type="prism"> with
 //   <Vertices>x0 y0 x1 y1 ...</Vertices> (3..8 vertices of a convex polygon, either orientation) and <Height>zlo zhi
 //   </Height> in the geom's frame; accepted inside <Robot> only (obstacles stay boxes).
@@ -21,6 +23,7 @@
 #include <map>
 #include <sstream>
 
+#include "collada_hulls.h"
 #include "xml_lite.h"
 
 namespace mcsim {
@@ -95,7 +98,7 @@ std::string resolve(const std::string& ref, const std::string& base_dir, const s
     }
     std::string tried;
     for (const auto& c : cands) {
-        if (!ends_with(c, ".zae") && readable(c)) return c;  // a COLLADA archive is not readable here
+        if (readable(c)) return c;   // a COLLADA model (.zae / .dae) that is really there wins over the box fixture
         tried += (tried.empty() ? "" : ", ") + c;
     }
     throw std::runtime_error("cannot resolve '" + ref + "' (tried " + tried + ")");
@@ -195,8 +198,18 @@ Scene load_scene_xml(const std::string& env_path, const std::vector<std::string>
         std::vector<Prism> prisms;
         std::vector<PolyPrism> polys;
         if (const auto* file = rob->attr("file")) {
-            const std::string sub = read_file(resolve(*file, base_dir, fixture_dirs));
-            collect(*xml_lite::parse(sub), zonly, prisms, &polys);
+            const std::string path = resolve(*file, base_dir, fixture_dirs);
+            if (ends_with(path, ".zae") || ends_with(path, ".dae")) {
+                // the COLLADA model itself: one convex footprint per z-band (collada_hulls.h).  zbands="z0 z1 .."
+                // on the <Robot> element (not OpenRAVE's: this build's) gives the band boundaries in the model frame.
+                ColladaOptions opt;
+                if (const auto* zb = rob->attr("zbands")) opt.z_edges = numbers(*zb, "Robot zbands");
+                std::vector<double> rows = load_collada_hulls(path, opt);
+                for (size_t i = 0; i < rows.size(); i += 19) { rows[i + 1] += top.z; rows[i + 2] += top.z; }
+                sc.poly_hulls.insert(sc.poly_hulls.end(), rows.begin(), rows.end());
+            } else {
+                collect(*xml_lite::parse(read_file(path)), zonly, prisms, &polys);
+            }
         } else {
             collect(*rob, zonly, prisms, &polys);
         }

@@ -132,3 +132,31 @@ def test_robot_fixture_with_a_prism_geom_through_the_plugin(plan, tmp_path):
     P_upper_only = float(mod.SendCommand("runSimulation"))
     assert 0.0 < P_upper_only <= P_oct <= 1.0
     mod.close()
+
+
+def test_collada_model_of_the_box_fixture_gives_the_fixture_answers(plan, tmp_path):
+    """The robot as a COLLADA archive (what the reference's env files name, pr2test2.env.xml:120): a .zae holding the box
+    fixture's two prisms as meshes, reduced to footprints by csrc/collada_hulls.cpp, against the box fixture itself -- the
+    reference's default `shared` mode draws one real-robot thread per run from the seed, so both modules see the same
+    particles; the polygon SAT of a rectangle is the box SAT (tests/test_sat_known_answers.py), so the estimates agree up
+    to rollouts at rounding distance from contact."""
+    import os
+    import pcoll_b200
+    from conftest import ROOT
+    from test_collada_hulls import _two_box_robot, _zae
+    env = os.path.join(ROOT, "data", "scenes", "pr2test2.env.xml")
+    path = str(tmp_path / "pr2-like.zae")
+    _zae(path, _two_box_robot())
+    box = pcoll_b200.MCModule(env, device=0)
+    dae = pcoll_b200.MCModule(env, device=0)
+    assert dae.SendCommand("setRobotModel %s 0.05 0.35 1.4" % path) == "2"
+    assert dae.scene()["hulls"].shape[0] == 0 and dae.scene()["poly_hulls"].shape == (2, 19)
+    N = 20000
+    for mod in (box, dae):
+        pcoll_b200.push_parameters(mod, plan, num_particles=N)
+        mod.SendCommand("setSeed 9")
+    Pb = [float(box.SendCommand("runSimulation")) for _ in range(3)]
+    Pd = [float(dae.SendCommand("runSimulation")) for _ in range(3)]
+    assert 0.0 < min(Pb) and max(Pb) <= 1.0
+    np.testing.assert_allclose(Pd, Pb, atol=3.0 / N)      # a handful of near-contact rollouts may flip between the two SAT forms
+    box.close(); dae.close()
