@@ -208,11 +208,11 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
     __shared__ double s_comp[MCSIM_MAX_GAUSSIANS][GMM_COMP];
     __shared__ double s_stat[MCSIM_MAX_GAUSSIANS][GMM_STAT];
     __shared__ unsigned long long s_prefix[MCSIM_MAX_GAUSSIANS + 1];
-    __shared__ unsigned char s_ccnt[MCSIM_MAX_HULLS * MC_CULL_LEVELS];
-    __shared__ ushort2 s_cidx[MCSIM_MAX_HULLS * MC_CULL_CAP];
+    __shared__ unsigned char s_ccnt[(MCSIM_MAX_HULLS + MCSIM_MAX_POLY_HULLS) * MC_CULL_LEVELS];
+    __shared__ ushort2 s_cidx[(MCSIM_MAX_HULLS + MCSIM_MAX_POLY_HULLS) * MC_CULL_CAP];
     const int K = a.K;
     if (MODE != MCSIM_MODE_REPLAY && m.cull) {
-        const int nh = c_scene.n_hulls;
+        const int nh = c_scene.n_hulls + c_scene.n_poly;   // the lists' hull index: box hulls, then polygon hulls
         const unsigned char* gc = reinterpret_cast<const unsigned char*>(m.cull) + size_t(a.t) * nh * MC_CULL_LEVELS;
         const ushort2* gi = reinterpret_cast<const ushort2*>(m.cull + (size_t(a.T) * nh * MC_CULL_LEVELS + 3) / 4) + size_t(a.t) * nh * MC_CULL_CAP;
         for (int i = threadIdx.x; i < nh * MC_CULL_LEVELS; i += blockDim.x) s_ccnt[i] = gc[i];
@@ -323,12 +323,12 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
             }
             unsigned tested = 0;
             if (lev < MC_CULL_LEVELS) {
-                hit = robot_hits_listed(a.sat2, s_ccnt, s_cidx, lev, xf, yf, cs, sn, tested);
+                hit = robot_hits_listed(a.sat2, s_ccnt, s_cidx, lev, xf, yf, cs, sn, tested);   // box and polygon hulls
             } else {
                 hit = robot_hits_grouped(a.sat2, xf, yf, cs, sn);
                 tested = c_scene.n_pairs;
+                if (c_scene.n_poly && poly_clearance(xf, yf, cs, sn, tested) <= 0.f) hit = true;   // polygon hulls: every live pair
             }
-            if (c_scene.n_poly && poly_clearance(xf, yf, cs, sn, tested) <= 0.f) hit = true;   // polygon hulls: every live pair
             if (valid) my_tests += tested;
         }
         if (a.free_out) {   // warp-aggregated append of the free samples

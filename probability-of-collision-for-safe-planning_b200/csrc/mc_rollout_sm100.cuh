@@ -80,8 +80,9 @@ __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
     // exact broad phase of the replay mode (sat_device.cuh): the plan's candidate lists, chosen per warp and waypoint by
     // the largest deviation of its live rollouts from x*_t -- the reference driver's default mode (one shared real robot,
     // MCSimulation.py:238-247) spends its time in this kernel, 63 pair tests per pose without the lists
-    const bool listed = (MODE == MCSIM_MODE_REPLAY) && !AUDIT && a.cull != nullptr;
-    const int nh = c_scene.n_hulls;
+    // (Philox mode comes here with polygon robot hulls only: box-hull scenes run the packed kernel, which has its own lists)
+    const bool listed = !AUDIT && a.cull != nullptr;
+    const int nh = c_scene.n_hulls + c_scene.n_poly;   // the lists' hull index: box hulls, then polygon hulls
     const unsigned char* g_ccnt = reinterpret_cast<const unsigned char*>(a.cull);
     const ushort2* g_cidx = reinterpret_cast<const ushort2*>(a.cull + (size_t(T) * nh * MC_CULL_LEVELS + 3) / 4);
     // block-uniform trip count: lanes past the end are masked (the warp-wide reductions of the broad phase need every lane)

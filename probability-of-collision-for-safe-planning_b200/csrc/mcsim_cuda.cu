@@ -102,6 +102,10 @@ struct mcsim_cuda_ctx {
     // exact broad phase of the packed Philox kernel: host copy of the live pairs, per-plan candidate lists
     std::vector<double> h_pairgeom;  // per pair: cx, cy, cos, sin, hx, hy
     std::vector<int> h_pair_hull;    // per pair: hull index
+    // polygon hulls' pairs (they follow the box hulls' in c_pairs): box geometry, polygon hull, index in c_pairs; reach per polygon
+    std::vector<double> h_poly_pairgeom;
+    std::vector<int> h_poly_pair_hull, h_poly_pair_index;
+    double h_poly_reach[MCSIM_MAX_POLY_HULLS] = {0};
     std::vector<unsigned> h_pair_sat2;  // per pair: record offset | class header offset << 16 in the grouped table
     double h_reach[MCSIM_MAX_HULLS] = {0};
     DevBuf mc_cull, mc_nominal;
@@ -289,6 +293,9 @@ extern "C" int mcsim_cuda_set_scene_ex(mcsim_cuda_ctx* c, const double* boxes, i
     sc.n_hulls = n_hulls;
     c->h_pairgeom.clear();
     c->h_pair_hull.clear();
+    c->h_poly_pairgeom.clear();
+    c->h_poly_pair_hull.clear();
+    c->h_poly_pair_index.clear();
     c->h_pair_sat2.clear();
     ++c->scene_epoch;
     c->mc_prepared = false;  // candidate lists of a prepared plan refer to the old scene
@@ -385,10 +392,14 @@ extern "C" int mcsim_cuda_set_scene_ex(mcsim_cuda_ctx* c, const double* boxes, i
             const double* bx = boxes + b * MCSIM_PRISM_STRIDE;
             if (!((po[1] < bx[7]) && (bx[6] < po[2]))) continue;
             const double p = bx[2] * bx[0] + bx[3] * bx[1], q = bx[2] * bx[1] - bx[3] * bx[0];
+            c->h_poly_pair_index.push_back(int(pairs.size() / 2));
+            c->h_poly_pair_hull.push_back(h);
+            for (int k = 0; k < 6; ++k) c->h_poly_pairgeom.push_back(bx[k]);
             pairs.push_back(make_float4(float(bx[0]), float(bx[1]), float(bx[2]), float(bx[3])));
             pairs.push_back(make_float4(float(bx[4]), float(bx[5]), -float(p), -float(q)));
         }
         r.count = int(pairs.size() / 2) - r.first;
+        c->h_poly_reach[h] = reach;
     }
     c->n_poly = n_poly;
     if (int(pairs.size() / 2) > MCSIM_MAX_PAIRS)
@@ -485,8 +496,10 @@ static void cull_key(const mcsim_cuda_ctx* c, const double* trajectory, int n_pl
 // Candidate lists of the packed kernel's broad phase (layout and exactness argument: mc_philox2_sm100.cuh).
 // need(pair) = distance from x*_t to the box footprint - reach of the pair's hull - 1 mm of slack for the FP32
 // plan record and the FP32 deviation test of the kernel.
+// With polygon hulls (scalar kernels only) the hull index runs over the box hulls and then the polygon hulls; a polygon
+// pair's entry is its index in c_pairs, its reach the largest vertex radius.
 static void build_cull_lists(const mcsim_cuda_ctx* c, const double* trajectory, int T, std::vector<unsigned>& words) {
-    const int nh = c->n_hulls, np = int(c->h_pair_hull.size());
+    const int nb = c->n_hulls, nh = c->n_hulls + c->n_poly, np = int(c->h_pair_hull.size()), npp = int(c->h_poly_pair_hull.size());
     const size_t cnt_words = (size_t(T) * nh * MC_CULL_LEVELS + 3) / 4, idx_words = size_t(T) * nh * MC_CULL_CAP;
     words.assign(cnt_words + idx_words, 0u);
     unsigned char* cnt = reinterpret_cast<unsigned char*>(words.data());
@@ -497,13 +510,14 @@ static void build_cull_lists(const mcsim_cuda_ctx* c, const double* trajectory, 
         bool overflow[MC_CULL_LEVELS] = {false};
         for (int h = 0; h < nh; ++h) {
             need.clear();
-            for (int b = 0; b < np; ++b) {
-                if (c->h_pair_hull[b] != h) continue;
-                const double* g = &c->h_pairgeom[size_t(b) * 6];
+            const bool poly = h >= nb;
+            for (int b = 0; b < (poly ? npp : np); ++b) {
+                if ((poly ? c->h_poly_pair_hull[b] + nb : c->h_pair_hull[b]) != h) continue;
+                const double* g = poly ? &c->h_poly_pairgeom[size_t(b) * 6] : &c->h_pairgeom[size_t(b) * 6];
                 const double dx = px - g[0], dy = py - g[1];
                 const double lx = fabs(g[2] * dx + g[3] * dy) - g[4], ly = fabs(g[2] * dy - g[3] * dx) - g[5];
                 const double dist = hypot(lx > 0 ? lx : 0, ly > 0 ? ly : 0);
-                need.emplace_back(dist - c->h_reach[h] - 1e-3, b);
+                need.emplace_back(dist - (poly ? c->h_poly_reach[h - nb] : c->h_reach[h]) - 1e-3, b);
             }
             std::sort(need.begin(), need.end());
             for (int k = 0; k < MC_CULL_LEVELS; ++k) {
@@ -513,7 +527,8 @@ static void build_cull_lists(const mcsim_cuda_ctx* c, const double* trajectory, 
                 if (n > MC_CULL_CAP) overflow[k] = true;
                 cnt[(size_t(t) * nh + h) * MC_CULL_LEVELS + k] = (unsigned char)(n > MC_CULL_CAP ? MC_CULL_CAP : n);
             }
-            for (size_t k = 0; k < need.size() && k < MC_CULL_CAP; ++k) idx[(size_t(t) * nh + h) * MC_CULL_CAP + k] = c->h_pair_sat2[need[k].second];
+            for (size_t k = 0; k < need.size() && k < MC_CULL_CAP; ++k)
+                idx[(size_t(t) * nh + h) * MC_CULL_CAP + k] = poly ? unsigned(c->h_poly_pair_index[need[k].second]) : c->h_pair_sat2[need[k].second];
         }
         for (int k = 0; k < MC_CULL_LEVELS; ++k)
             if (overflow[k]) for (int h = 0; h < nh; ++h) cnt[(size_t(t) * nh + h) * MC_CULL_LEVELS + k] = MC_CULL_OVERFLOW;
@@ -573,9 +588,11 @@ extern "C" int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* c, const mcsim_mc_params* p
     bool cull_cached = false;
     // candidate lists of the exact broad phase: the packed Philox kernels (lists in shared memory) and the replay kernel
     // (lists read from global memory); box hulls only
-    const bool lists_for_packed = !plan2.empty() && L == 8;
+    const bool lists_for_packed = !plan2.empty() && L == 8 && c->n_poly == 0;
     const bool lists_for_replay = p->mode == MCSIM_MODE_REPLAY;
-    if ((lists_for_packed || lists_for_replay) && !p->exhaustive && c->sat2_n < 65536 && c->n_pairs > 0 && c->n_poly == 0) {
+    const bool lists_for_poly = c->n_poly > 0;   // polygon hulls: the scalar kernel runs in both modes and walks the lists
+    const int all_pairs = c->n_pairs + int(c->h_poly_pair_hull.size());
+    if ((lists_for_packed || lists_for_replay || lists_for_poly) && !p->exhaustive && c->sat2_n < 65536 && all_pairs > 0 && all_pairs < 65536) {
         std::vector<double> key;
         cull_key(c, p->trajectory, 1, T, key);
         if (key == c->mc_cull_key) {
@@ -589,7 +606,7 @@ extern "C" int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* c, const mcsim_mc_params* p
     }
     // the packed kernels keep the lists in shared memory next to the pair table; too large a plan x scene goes without them
     c->mc_cull_fits_smem = (cull.size() * sizeof(unsigned) + sizeof(float4) * size_t(c->sat2_n)) * MC_P2_CTAS_PER_SM <= 200 * 1024;
-    if (!lists_for_replay && !c->mc_cull_fits_smem) cull.clear();
+    if (!lists_for_replay && !lists_for_poly && !c->mc_cull_fits_smem) cull.clear();
     c->mc_cull_words = int(cull.size());
     std::vector<float2> nominal(T);
     for (int t = 0; t < T; ++t) nominal[t] = make_float2(float(p->trajectory[t]), float(p->trajectory[T + t]));
@@ -678,7 +695,7 @@ static int mc_launch_impl(mcsim_cuda_ctx* c, uint64_t n, uint64_t offset, const 
     a.near_eps = float(p.near_eps);
     a.sat2 = (const float4*)c->sat2.p;
     a.sat2_n = c->sat2_n;
-    const bool cull = c->mc_cull_words > 0 && (packed ? c->mc_cull_fits_smem : (p.mode == MCSIM_MODE_REPLAY && !audit));
+    const bool cull = c->mc_cull_words > 0 && (packed ? c->mc_cull_fits_smem : ((p.mode == MCSIM_MODE_REPLAY || c->n_poly > 0) && !audit));
     a.cull = cull ? (const unsigned*)c->mc_cull.p : nullptr;
     a.cull_words = cull ? c->mc_cull_words : 0;
     a.nominal = (const float2*)c->mc_nominal.p;
@@ -874,8 +891,9 @@ static int gmm_upload_cull(mcsim_cuda_ctx* c, GmmLaunch& a, const double* trajec
     a.cull = nullptr;
     a.cull_stride = 0;
     c->gmm_cull_words = 0;
-    if (exhaustive || c->sat2_n >= 65536 || c->n_pairs == 0) return MCSIM_OK;
-    if (size_t(n_plans) * T * c->n_hulls * (MC_CULL_CAP + 1) > (size_t(64) << 20)) return MCSIM_OK;  // 256 MB of lists: go without
+    const int all_pairs = c->n_pairs + int(c->h_poly_pair_hull.size());
+    if (exhaustive || c->sat2_n >= 65536 || all_pairs == 0 || all_pairs >= 65536) return MCSIM_OK;
+    if (size_t(n_plans) * T * (c->n_hulls + c->n_poly) * (MC_CULL_CAP + 1) > (size_t(64) << 20)) return MCSIM_OK;  // 256 MB of lists: go without
     std::vector<double> key;
     cull_key(c, trajectories, n_plans, T, key);
     if (key == c->gmm_cull_key && c->gmm_cull_words_cached > 0) {   // same scene, same plan(s): the lists are on the device

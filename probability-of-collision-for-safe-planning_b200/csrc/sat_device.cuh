@@ -254,6 +254,16 @@ __device__ __forceinline__ bool robot_hits_listed(const float4* __restrict__ tab
         }
         tested += n;
     }
+    // polygon hulls follow the box hulls in the lists; an entry is the pair's index in c_pairs
+    for (int pI = 0; pI < c_scene.n_poly; ++pI) {
+        const int hI = c_scene.n_hulls + pI;
+        const int n = cnt[hI * MC_CULL_LEVELS + lev];
+        for (int k = 0; k < n; ++k) {
+            const int b = idx[hI * MC_CULL_CAP + k].x;
+            if (poly_pair_gap(c_scene.poly[pI], x, y, ct, st, c_pairs[2 * b], c_pairs[2 * b + 1]) <= 0.f) hit = true;
+        }
+        tested += n;
+    }
     return hit;
 }
 

@@ -160,3 +160,44 @@ def test_collada_model_of_the_box_fixture_gives_the_fixture_answers(plan, tmp_pa
     assert 0.0 < min(Pb) and max(Pb) <= 1.0
     np.testing.assert_allclose(Pd, Pb, atol=3.0 / N)      # a handful of near-contact rollouts may flip between the two SAT forms
     box.close(); dae.close()
+
+
+def test_broad_phase_with_polygon_hulls_is_exact(ctx, plan, scenes):
+    """The candidate lists of the exact broad phase now cover polygon hulls too (hull index: box hulls, then polygon hulls;
+    reach = the largest vertex radius): per-rollout counts equal testing every live pair, in replay mode and in Philox mode
+    (both run the scalar kernel when the robot has polygon hulls), with a fraction of the pair tests; the GMM estimate of the
+    scalar sample kernel is unchanged too."""
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    sc = scenes["pr2test2"]
+    hulls, polys = _robot()
+    ctx.set_scene(sc["boxes"], hulls, polys)
+    T = plan["trajectory"].shape[1]
+    N = 30001
+    outs = {}
+    for ex in (False, True):
+        p, keep = abi.make_mc_params(plan, n_rollouts=N, mode=abi.MODE_PHILOX, early_exit=False, exhaustive=ex)
+        outs[ex] = ctx.mc_run(p, want_counts=True, want_hist=True)
+    np.testing.assert_array_equal(outs[False]["counts"], outs[True]["counts"])
+    np.testing.assert_array_equal(outs[False]["first_hit_hist"], outs[True]["first_hit_hist"])
+    assert outs[True]["pair_tests"] == N * T * 63 and outs[False]["pair_tests"] < 0.2 * outs[True]["pair_tests"]
+    draws = np.random.Generator(np.random.PCG64(33)).standard_normal(3 * N + 11 * (T - 1))
+    ht = abi.host_thread(plan, draws[3 * N:])
+    for ex in (False, True):
+        p, keep = abi.make_mc_params(plan, n_rollouts=N, mode=abi.MODE_REPLAY, applied=ht["applied_noisy"], z0=draws[:3 * N], early_exit=False, exhaustive=ex)
+        outs[ex] = ctx.mc_run(p, want_counts=True)
+    np.testing.assert_array_equal(outs[False]["counts"], outs[True]["counts"])
+    assert outs[False]["pair_tests"] < 0.2 * outs[True]["pair_tests"]
+    # only polygon hulls (no box hull at all): the lists still work
+    ctx.set_scene(sc["boxes"], np.zeros((0, 8)), polys)
+    for ex in (False, True):
+        p, keep = abi.make_mc_params(plan, n_rollouts=N, mode=abi.MODE_PHILOX, early_exit=True, exhaustive=ex)
+        outs[ex] = ctx.mc_run(p, want_counts=True)
+    np.testing.assert_array_equal(outs[False]["counts"], outs[True]["counts"])
+    assert 0 < outs[False]["hits"] < N
+    ctx.set_scene(sc["boxes"], hulls, polys)
+    a = ctx.gmm_run(plan, 3, 6000, mode=abi.MODE_PHILOX, stream_id=5)
+    b = ctx.gmm_run(plan, 3, 6000, mode=abi.MODE_PHILOX, stream_id=5, exhaustive=True)
+    np.testing.assert_array_equal(a["probabilities"], b["probabilities"])
+    assert a["pair_tests"] < 0.3 * b["pair_tests"]
+    ctx.set_scene(sc["boxes"], sc["hulls"])
