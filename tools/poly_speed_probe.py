@@ -1,10 +1,14 @@
+"""Developer probe: Philox-mode MC rate with the box fixture (packed kernel) and with a polygon-hull robot (scalar kernel +
+exact broad phase), committed plan, pr2test2 scene."""
 import sys, time
-sys.path.insert(0, "/root/repo"); sys.path.insert(0, "/root/repo/tests")
+import os
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import numpy as np, pcoll_b200
 from test_polygon_hulls_gpu import _robot
 abi = pcoll_b200.cuda_abi
-plan = pcoll_b200.load_plan_json("/root/repo/tests/golden/plan_committed.json")
-sc = np.load("/root/repo/tests/golden/scene_pr2test2.npz")
+plan = pcoll_b200.load_plan_json(os.path.join(ROOT, "tests", "golden", "plan_committed.json"))
+sc = np.load(os.path.join(ROOT, "tests", "golden", "scene_pr2test2.npz"))
 ctx = abi.Context(0)
 hulls, polys = _robot()
 T = plan["trajectory"].shape[1]
