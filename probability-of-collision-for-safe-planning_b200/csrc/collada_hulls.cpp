@@ -488,6 +488,35 @@ std::vector<double> collada_hulls_from_text(const std::string& text, const Colla
         if (pts.empty()) continue;
         std::vector<P2> h = convex_hull(pts);
         if (h.size() < 3) continue;   // a line or a point has no footprint
+        if (opt.as_boxes) {
+            // minimum-area bounding rectangle: one of its sides lies along an edge of the convex hull (rotating calipers)
+            double best = 1e300, r[8] = {0, 0, 1, 0, 0, 0, lo, hi};
+            for (size_t i = 0; i < h.size(); ++i) {
+                const P2 &a = h[i], &b = h[(i + 1) % h.size()];
+                const double len = std::hypot(b.x - a.x, b.y - a.y);
+                if (!(len > 0)) continue;
+                double ux = (b.x - a.x) / len, uy = (b.y - a.y) / len;
+                double u0 = 1e300, u1 = -1e300, v0 = 1e300, v1 = -1e300;
+                for (const P2& q : h) {
+                    const double pu = q.x * ux + q.y * uy, pv = -q.x * uy + q.y * ux;
+                    u0 = std::min(u0, pu); u1 = std::max(u1, pu); v0 = std::min(v0, pv); v1 = std::max(v1, pv);
+                }
+                const double area = (u1 - u0) * (v1 - v0);
+                if (area < best * (1 - 1e-12)) {
+                    best = area;
+                    const double cu = 0.5 * (u0 + u1), cv = 0.5 * (v0 + v1);
+                    r[0] = cu * ux - cv * uy; r[1] = cu * uy + cv * ux;
+                    r[2] = ux; r[3] = uy; r[4] = 0.5 * (u1 - u0); r[5] = 0.5 * (v1 - v0);
+                }
+            }
+            // axis in the right half-plane, nearest to +x among the four equivalent ones (a rectangle is its own 90-degree turn)
+            for (int turn = 0; turn < 4 && !(r[2] > 0 && std::fabs(r[3]) <= r[2] * (1 + 1e-12)); ++turn) {
+                const double c = r[2]; r[2] = -r[3]; r[3] = c; std::swap(r[4], r[5]);
+            }
+            if (std::fabs(r[3]) < 1e-15) r[3] = 0;
+            rows.insert(rows.end(), r, r + 8);
+            continue;
+        }
         while (int(h.size()) > opt.max_vertices)
             if (!drop_cheapest_edge(h)) fail(what, "cannot simplify a footprint to " + std::to_string(opt.max_vertices) + " vertices");
         double r[19] = {double(h.size()), lo, hi};

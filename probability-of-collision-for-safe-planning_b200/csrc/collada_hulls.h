@@ -19,9 +19,13 @@ struct ColladaOptions {
     std::vector<double> z_edges;   // band boundaries z0 < z1 < ... (model frame, metres); empty: max_bands equal bands over the model's height
     int max_bands = 4;             // = MCSIM_MAX_POLY_HULLS
     int max_vertices = 8;          // = MCSIM_POLY_MAX_VERTICES
+    bool as_boxes = false;         // rows of 8 doubles instead: each band's footprint replaced by its minimum-area bounding rectangle
+                                   // (cx, cy, cos(yaw), sin(yaw), hx, hy, zlo, zhi) -- looser than the polygon, but box hulls run on the
+                                   // packed kernels (3-4 x the rollout rate of polygon hulls)
 };
 
-// Rows of 19 doubles, one per non-empty band: n, zlo, zhi, x0, y0, ..., x7, y7 (counter-clockwise, model frame).
+// Rows of 19 doubles, one per non-empty band: n, zlo, zhi, x0, y0, ..., x7, y7 (counter-clockwise, model frame); with
+// opt.as_boxes rows of 8 doubles (the box hull layout of mcsim_cuda_set_scene).
 // Throws std::runtime_error naming the file and the construct on any problem.
 std::vector<double> load_collada_hulls(const std::string& path, const ColladaOptions& opt);
 

@@ -91,7 +91,7 @@ const MCModule::Command MCModule::kCommands[] = {
     {"getDevices", &MCModule::getDevices, "the CUDA ordinals in use"},
     {"describeRun", &MCModule::describeRun, "describeRun [k]: Philox key, first rollout id and rollout count of the k-th runSimulation from now (default 0 = the next one), then key and stream id of the k-th runGMMEstimation"},
     {"setGeometry", &MCModule::setGeometry, "setGeometry <n_boxes> <n_hulls> <8 numbers per prism ...>: replace the collision geometry"},
-    {"setRobotModel", &MCModule::setRobotModel, "setRobotModel <file.zae | file.dae> [z0 z1 ... zk]: robot hulls from a COLLADA model -- one convex footprint (at most 8 vertices) per z-band of the model; returns the number of hulls"},
+    {"setRobotModel", &MCModule::setRobotModel, "setRobotModel <file.zae | file.dae> [boxes | polygons] [z0 z1 ... zk]: robot hulls from a COLLADA model -- per z-band of the model one convex footprint (polygons, at most 8 vertices; default) or its minimum-area bounding rectangle (boxes: looser, but the packed kernels run); returns the number of hulls"},
     {"setRobotPolygons", &MCModule::setRobotPolygons, "setRobotPolygons <n> then per hull: zlo zhi m x0 y0 ... x(m-1) y(m-1): convex-polygon robot hulls (robot frame, 3..8 vertices) next to / instead of the box hulls"},
     {"setScene", &MCModule::setScene, "setScene <env.xml> [fixture_dir ...]: extract the collision geometry from an OpenRAVE env XML"},
     {"getWaypointProbabilities", &MCModule::getWaypointProbabilities, "per-waypoint colliding fraction of the last runGMMEstimation"},

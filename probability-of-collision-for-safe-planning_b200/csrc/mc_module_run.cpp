@@ -419,23 +419,29 @@ bool MCModule::setRobotPolygons(std::ostream&, std::istream& sinput) {
     return true;
 }
 
-// setRobotModel <path.zae | path.dae> [z0 z1 ... zk]: the robot's hull set from a COLLADA model (what the reference's scenes
+// setRobotModel <path.zae | path.dae> [boxes | polygons] [z0 z1 ... zk]: the robot's hull set from a COLLADA model (what the reference's scenes
 // name as their robot, pr2test2.env.xml:120) -- one convex footprint per z-band, replacing box and polygon hulls alike.
 // Band boundaries are in the model frame (k <= MCSIM_MAX_POLY_HULLS bands; none given: that many equal bands).
 bool MCModule::setRobotModel(std::ostream& sout, std::istream& sinput) {
     std::string path;
     if (!(sinput >> path)) throw std::runtime_error("setRobotModel: a .zae / .dae path expected");
     ColladaOptions opt;
-    opt.max_bands = MCSIM_MAX_POLY_HULLS;
-    double z;
-    while (sinput >> z) opt.z_edges.push_back(z);
+    std::string tok;
+    while (sinput >> tok) {
+        if (tok == "boxes") { opt.as_boxes = true; continue; }       // minimum-area bounding rectangles: box hulls, packed kernels
+        if (tok == "polygons") { opt.as_boxes = false; continue; }   // the footprints themselves (default)
+        try { size_t used = 0; opt.z_edges.push_back(std::stod(tok, &used)); if (used != tok.size()) throw std::invalid_argument(tok); }
+        catch (const std::exception&) { throw std::runtime_error("setRobotModel: '" + tok + "' is neither boxes | polygons nor a band boundary"); }
+    }
+    const int max_bands = opt.as_boxes ? MCSIM_MAX_HULLS : MCSIM_MAX_POLY_HULLS;
+    opt.max_bands = opt.as_boxes ? 4 : MCSIM_MAX_POLY_HULLS;   // default split when no boundaries are given
     if (opt.z_edges.size() == 1) throw std::runtime_error("setRobotModel: one band boundary is not a band");
-    if (opt.z_edges.size() > size_t(MCSIM_MAX_POLY_HULLS) + 1) throw std::runtime_error("setRobotModel: at most " + std::to_string(MCSIM_MAX_POLY_HULLS) + " bands");
+    if (opt.z_edges.size() > size_t(max_bands) + 1) throw std::runtime_error("setRobotModel: at most " + std::to_string(max_bands) + " bands");
     std::vector<double> rows = load_collada_hulls(path, opt);
-    scene_.hulls.clear();
-    scene_.poly_hulls.swap(rows);
+    if (opt.as_boxes) { scene_.poly_hulls.clear(); scene_.hulls.swap(rows); }
+    else { scene_.hulls.clear(); scene_.poly_hulls.swap(rows); }
     upload_scene();
-    sout << scene_.n_poly_hulls();
+    sout << (opt.as_boxes ? scene_.n_hulls() : scene_.n_poly_hulls());
     return true;
 }
 

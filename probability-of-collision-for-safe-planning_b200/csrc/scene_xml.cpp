@@ -202,11 +202,21 @@ Scene load_scene_xml(const std::string& env_path, const std::vector<std::string>
             if (ends_with(path, ".zae") || ends_with(path, ".dae")) {
                 // the COLLADA model itself: one convex footprint per z-band (collada_hulls.h).  zbands="z0 z1 .."
                 // on the <Robot> element (not OpenRAVE's: this build's) gives the band boundaries in the model frame.
+                // hulls="boxes" replaces every footprint by its minimum-area bounding rectangle (box hulls: the packed kernels).
                 ColladaOptions opt;
                 if (const auto* zb = rob->attr("zbands")) opt.z_edges = numbers(*zb, "Robot zbands");
+                if (const auto* hk = rob->attr("hulls")) {
+                    if (xml_lite::lower(*hk) == "boxes") { opt.as_boxes = true; opt.max_bands = 8; }
+                    else if (xml_lite::lower(*hk) != "polygons") throw std::runtime_error("<Robot hulls=\"" + *hk + "\">: boxes | polygons expected");
+                }
                 std::vector<double> rows = load_collada_hulls(path, opt);
-                for (size_t i = 0; i < rows.size(); i += 19) { rows[i + 1] += top.z; rows[i + 2] += top.z; }
-                sc.poly_hulls.insert(sc.poly_hulls.end(), rows.begin(), rows.end());
+                if (opt.as_boxes) {
+                    for (size_t i = 0; i < rows.size(); i += 8) { rows[i + 6] += top.z; rows[i + 7] += top.z; }
+                    sc.hulls.insert(sc.hulls.end(), rows.begin(), rows.end());
+                } else {
+                    for (size_t i = 0; i < rows.size(); i += 19) { rows[i + 1] += top.z; rows[i + 2] += top.z; }
+                    sc.poly_hulls.insert(sc.poly_hulls.end(), rows.begin(), rows.end());
+                }
             } else {
                 collect(*xml_lite::parse(read_file(path)), zonly, prisms, &polys);
             }

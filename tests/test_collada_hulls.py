@@ -120,6 +120,31 @@ def test_two_box_model_gives_the_fixture_rectangles(tmp_path, deflate):
     mod.close()
 
 
+def test_boxes_option_gives_the_fixture_box_hulls(tmp_path):
+    """`boxes`: every band's footprint replaced by its minimum-area bounding rectangle -> box hulls (the packed kernels'
+    path).  The model of the box fixture must give the fixture's own hull rows; a part turned by 30 degrees its turned box."""
+    import pcoll_b200
+    path = str(tmp_path / "pr2-like.zae")
+    _zae(path, _two_box_robot())
+    mod = _module()
+    fixture = mod.scene()["hulls"].copy()
+    assert mod.SendCommand("setRobotModel %s boxes 0.05 0.35 1.4" % path) == "2"
+    scn = mod.scene()
+    assert scn["poly_hulls"].shape[0] == 0
+    np.testing.assert_allclose(scn["hulls"], fixture, atol=1e-12)
+    geoms = _box_mesh("b", 0.4, 0.1, 0.25)
+    nodes = '<node id="r"><translate>0.5 -0.2 0.25</translate><rotate>0 0 1 30</rotate><instance_geometry url="#b"/></node>'
+    turned = str(tmp_path / "turned.dae")
+    open(turned, "w").write(_dae(geoms, nodes))
+    assert mod.SendCommand("setRobotModel %s boxes 0 0.5" % turned) == "1"
+    h = mod.scene()["hulls"][0]
+    c, s = np.cos(np.radians(30)), np.sin(np.radians(30))
+    np.testing.assert_allclose(h, [0.5, -0.2, c, s, 0.4, 0.1, 0.0, 0.5], atol=1e-9)
+    with pytest.raises(pcoll_b200.McsimError, match="neither"):
+        mod.SendCommand("setRobotModel %s cubes" % turned)
+    mod.close()
+
+
 def test_bare_dae_y_up_and_a_band_through_a_tilted_part(tmp_path):
     """A .dae read directly; Y_UP document (model y is up: robot z = y, robot y = -z); a box rotated 45 degrees about the
     vertical; a band boundary cutting through it: both bands carry the full rotated footprint."""
