@@ -49,6 +49,7 @@ struct McLaunch {
     // exact broad phase of the packed kernel (mc_philox2_sm100.cuh); cull == nullptr: every live pair at every step
     const unsigned* cull;         // per-waypoint candidate lists, cull_words 32-bit words
     int cull_words;
+    int smem_lists;               // scalar kernels: pair table and lists were given room in dynamic shared memory behind the plan
     const float2* nominal;        // [T] (x*_t, y*_t): centres of the lists for the replay kernel (the packed kernels read c_plan2)
 };
 
@@ -70,6 +71,15 @@ __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
     constexpr int STRIDE = (MODE == MCSIM_MODE_REPLAY) ? MC_REPLAY_STRIDE : MC_PHILOX_STRIDE;
     const int n_plan = (MODE == MCSIM_MODE_REPLAY) ? (T - 1) * STRIDE : T * STRIDE;
     for (int i = threadIdx.x; i < n_plan; i += blockDim.x) s_plan[i] = a.plan[i];
+    // broad phase: pair table and candidate lists behind the plan.  Every step walks count -> index -> table record, three
+    // DEPENDENT loads; from global memory that chain was half of the stall samples of a 1,000-particle run
+    // (long_scoreboard 5.6 per issue, profiles/r02_replay_ncu_summary.csv): the reference driver's default mode is latency-bound
+    float4* s_tab = reinterpret_cast<float4*>(s_plan + ((n_plan + 3) & ~3));
+    unsigned* s_cull = reinterpret_cast<unsigned*>(s_tab + a.sat2_n);
+    if (a.smem_lists) {
+        for (int i = threadIdx.x; i < a.sat2_n; i += blockDim.x) s_tab[i] = a.sat2[i];
+        for (int i = threadIdx.x; i < a.cull_words; i += blockDim.x) s_cull[i] = a.cull[i];
+    }
     for (int i = threadIdx.x; i < T; i += blockDim.x) s_hist[i] = 0;
     if (threadIdx.x < 4) s_cnt[threadIdx.x] = 0;
     __syncthreads();
@@ -83,8 +93,9 @@ __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
     // (Philox mode comes here with polygon robot hulls only: box-hull scenes run the packed kernel, which has its own lists)
     const bool listed = !AUDIT && a.cull != nullptr;
     const int nh = c_scene.n_hulls + c_scene.n_poly;   // the lists' hull index: box hulls, then polygon hulls
-    const unsigned char* g_ccnt = reinterpret_cast<const unsigned char*>(a.cull);
-    const ushort2* g_cidx = reinterpret_cast<const ushort2*>(a.cull + (size_t(T) * nh * MC_CULL_LEVELS + 3) / 4);
+    const unsigned* lists = a.smem_lists ? s_cull : a.cull;
+    const unsigned char* g_ccnt = reinterpret_cast<const unsigned char*>(lists);
+    const ushort2* g_cidx = reinterpret_cast<const ushort2*>(lists + (size_t(T) * nh * MC_CULL_LEVELS + 3) / 4);
     // block-uniform trip count: lanes past the end are masked (the warp-wide reductions of the broad phase need every lane)
     for (unsigned long long base = (unsigned long long)blockIdx.x * blockDim.x; base < a.n; base += stride) {
         const unsigned long long i = base + threadIdx.x;
@@ -165,7 +176,8 @@ __global__ void __launch_bounds__(256) mc_rollout_kernel(const McLaunch a) {
                 int lev = cull_level(dm);
                 const unsigned char* cc = g_ccnt + size_t(t) * nh * MC_CULL_LEVELS;
                 if (lev < MC_CULL_LEVELS && cc[lev] == MC_CULL_OVERFLOW) lev = MC_CULL_LEVELS;
-                if (lev < MC_CULL_LEVELS) hit = robot_hits_listed(a.sat2, cc, g_cidx + size_t(t) * nh * MC_CULL_CAP, lev, q[0], q[1], cs, sn, tested);
+                if (lev < MC_CULL_LEVELS && a.smem_lists) hit = robot_hits_listed<true>(s_tab, cc, g_cidx + size_t(t) * nh * MC_CULL_CAP, lev, q[0], q[1], cs, sn, tested);
+                else if (lev < MC_CULL_LEVELS) hit = robot_hits_listed(a.sat2, cc, g_cidx + size_t(t) * nh * MC_CULL_CAP, lev, q[0], q[1], cs, sn, tested);
                 else hit = robot_hits(q[0], q[1], cs, sn, tested);
             } else {
                 hit = robot_hits(q[0], q[1], cs, sn, tested);

@@ -700,8 +700,12 @@ static int mc_launch_impl(mcsim_cuda_ctx* c, uint64_t n, uint64_t offset, const 
     a.cull_words = cull ? c->mc_cull_words : 0;
     a.nominal = (const float2*)c->mc_nominal.p;
     const int block = packed ? 128 : 256;
+    // scalar kernels: plan (rounded up to 16 bytes) | pair table | lists, when the lists are used and all of it fits 96 KB
+    const size_t plan_smem = (sizeof(float) * size_t(c->mc_T) * MC_PHILOX_STRIDE + 15) & ~size_t(15);
+    const size_t lists_smem = sizeof(float4) * size_t(c->sat2_n) + sizeof(unsigned) * size_t(c->mc_cull_words);
+    a.smem_lists = !packed && cull && plan_smem + lists_smem <= 96 * 1024;
     const size_t smem = packed ? sizeof(float4) * size_t(c->sat2_n) + (cull ? sizeof(unsigned) * size_t(c->mc_cull_words) : 0)
-                               : sizeof(float) * size_t(c->mc_T) * MC_PHILOX_STRIDE;
+                               : plan_smem + (a.smem_lists ? lists_smem : 0);
     unsigned long long want = packed ? ((n + 1) / 2 + block - 1) / block : (n + block - 1) / block;
     // persistent: whole waves of resident CTAs
     const unsigned long long cap = (unsigned long long)c->n_sm * (packed ? MC_P2_CTAS_PER_SM : 8);
