@@ -67,6 +67,7 @@ struct DeviceSymbols {
 };
 static DeviceSymbols g_symbols[64];
 static std::atomic<uint64_t> g_next_tag{1};
+#define MCSIM_STAGE_BYTES (64 * 1024)
 struct PlanSymbols {           // what a prepare call wants in c_mc / c_plan2
     McPlanConst pc;
     std::vector<float> plan2;
@@ -124,6 +125,7 @@ struct mcsim_cuda_ctx {
     DevBuf gmm_comps, gmm_stats, gmm_hist, gmm_counts, gmm_normals, gmm_steps, gmm_prob, gmm_pre, gmm_post, gmm_trunc, gmm_nout, gmm_deg;
     DevBuf gmm_free, gmm_free_n, lin_A, lin_b;   // EM-refit variant: free samples of a waypoint; linear variant: half-planes
     double* h_gmm = nullptr;  // pinned staging
+    char* h_stage = nullptr;  // pinned staging of the per-run plan upload (MCSIM_STAGE_BYTES)
     // scoring state
     DevBuf pairs_f, sc_plans, sc_hits, sc_counters;
     ScoreLaunch sc;
@@ -196,6 +198,7 @@ extern "C" int mcsim_cuda_create(int device, mcsim_cuda_ctx** out) {
     CK(cudaEventCreate(&c->ev1));
     CK(cudaMallocHost((void**)&c->h_counters, sizeof(unsigned long long) * (4 + MCSIM_MAX_WAYPOINTS)));
     CK(cudaMallocHost((void**)&c->h_gmm, sizeof(double) * 4096));
+    CK(cudaMallocHost((void**)&c->h_stage, MCSIM_STAGE_BYTES));
     CK(c->counters.reserve(sizeof(unsigned long long) * (4 + MCSIM_MAX_WAYPOINTS)));
     CK(cudaMemset(c->counters.p, 0, sizeof(unsigned long long) * (4 + MCSIM_MAX_WAYPOINTS)));
     *out = c;
@@ -220,6 +223,7 @@ extern "C" void mcsim_cuda_destroy(mcsim_cuda_ctx* c) {
     c->gmm_free.release(); c->gmm_free_n.release(); c->lin_A.release(); c->lin_b.release();
     if (c->h_counters) cudaFreeHost(c->h_counters);
     if (c->h_gmm) cudaFreeHost(c->h_gmm);
+    if (c->h_stage) cudaFreeHost(c->h_stage);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
     cudaStreamDestroy(c->stream);
@@ -615,15 +619,31 @@ extern "C" int mcsim_cuda_mc_prepare(mcsim_cuda_ctx* c, const mcsim_mc_params* p
     CK(c->plan.reserve(plan.size() * sizeof(float)));
     CK(c->counters.reserve(sizeof(unsigned long long) * (4 + MCSIM_MAX_WAYPOINTS)));
     CK(cudaStreamSynchronize(c->stream));
-    c->mc_sym.pc = pc;                     // uploaded to c_mc / c_plan2 by the launch (bind_symbols)
-    c->mc_sym.plan2 = plan2;
-    c->mc_sym.tag = g_next_tag++;
-    CK(cudaMemcpyAsync(c->plan.p, plan.data(), plan.size() * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    // uploaded to c_mc / c_plan2 by the launch (bind_symbols) when the tag is new.  Repeated runs of one plan (the reference
+    // driver's 200-run loop: only the applied commands of the shared real robot change, and those travel in c->plan) keep
+    // their tag, so the launch does not synchronise and re-upload the symbols every call.
+    if (c->mc_sym.tag == 0 || memcmp(&c->mc_sym.pc, &pc, sizeof(pc)) != 0 || c->mc_sym.plan2 != plan2) {
+        c->mc_sym.pc = pc;
+        c->mc_sym.plan2 = plan2;
+        c->mc_sym.tag = g_next_tag++;
+    }
+    // plan and list centres through the context's pinned staging buffer when they fit: truly asynchronous copies, and no
+    // synchronisation at the end of the call (the buffer is rewritten by the next prepare only, after this run was collected)
+    const size_t plan_bytes = plan.size() * sizeof(float), nom_bytes = sizeof(float2) * size_t(T);
+    const bool staged = c->h_stage && plan_bytes + nom_bytes <= MCSIM_STAGE_BYTES;
+    if (staged) {
+        memcpy(c->h_stage, plan.data(), plan_bytes);
+        memcpy(c->h_stage + plan_bytes, nominal.data(), nom_bytes);
+        CK(cudaMemcpyAsync(c->plan.p, c->h_stage, plan_bytes, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->mc_nominal.p, c->h_stage + plan_bytes, nom_bytes, cudaMemcpyHostToDevice, c->stream));
+    } else {
+        CK(cudaMemcpyAsync(c->plan.p, plan.data(), plan_bytes, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->mc_nominal.p, nominal.data(), nom_bytes, cudaMemcpyHostToDevice, c->stream));
+    }
     c->mc_cull_uploaded = !cull.empty() && !cull_cached;
     if (!cull.empty() && !cull_cached) CK(cudaMemcpyAsync(c->mc_cull.p, cull.data(), cull.size() * sizeof(unsigned), cudaMemcpyHostToDevice, c->stream));
-    CK(cudaMemcpyAsync(c->mc_nominal.p, nominal.data(), sizeof(float2) * size_t(T), cudaMemcpyHostToDevice, c->stream));
     CK(cudaMemsetAsync(c->counters.p, 0, sizeof(unsigned long long) * (4 + T), c->stream));
-    CK(cudaStreamSynchronize(c->stream));  // plan is a stack vector
+    if (!staged || c->mc_cull_uploaded) CK(cudaStreamSynchronize(c->stream));  // stack vectors
     c->mc = *p;
     c->mc.trajectory = c->mc.odometry = c->mc.landmarks = c->mc.applied = c->mc.z0 = nullptr;
     c->mc_prepared = true;
