@@ -354,9 +354,27 @@ int mcsim_cuda_em_estep(mcsim_cuda_ctx* ctx);
 int mcsim_cuda_em_mstep(mcsim_cuda_ctx* ctx);
 int mcsim_cuda_em_collect(mcsim_cuda_ctx* ctx, mcsim_em_result* r);
 /* DEVICE pointer and length (doubles) of the statistics block: [n_fits][K * 10 + 1] =
- * per component {sum r, sum r d (3), sum r d d^T (xx xy xz yy yz zz)} with d = x - current mean,
- * then sum of log-likelihoods. */
+ * per component {sum r, sum r d (3), sum r d d^T (xx xy xz yy yz zz)} with d = x - a reference point
+ * (below), then sum of log-likelihoods.  Additive over shards: every shard uses the same reference
+ * points because every shard holds the same parameters. */
 void* mcsim_cuda_em_stats(mcsim_cuda_ctx* ctx, uint64_t* n_doubles);
+/* Reference point of the statistics.  The reference accumulates raw sums in FP64 (em_generate_acc,
+ * gmm_full_meat.hpp:2646-2734); the FP32 kernels here accumulate about a point near the data instead:
+ *   MCSIM_EM_MOMENTS_CENTRED  the component's own current mean (most exact; 16 FP32 instructions per sample and
+ *                             component for the accumulation),
+ *   MCSIM_EM_MOMENTS_SHIFTED  one point per fit, the heft-weighted mean of the current means (x - c and its products
+ *                             once per sample, 11 instructions per component; the M-step's covariance then cancels
+ *                             (|mean - c|^2 + sigma^2) / sigma^2 digits-worth of the FP32 partial sums),
+ *   MCSIM_EM_MOMENTS_AUTO     (default) SHIFTED for the fits and iterations whose components lie close enough together for
+ *                             that loss to stay below ~1e-5 relative (decided on the device per fit and iteration,
+ *                             DESIGN.md section 3), CENTRED otherwise -- and for K = 4, whose kernel is measured
+ *                             faster in the centred form.  K = 1 is always CENTRED.
+ * Applies to the fits prepared after the call. */
+enum { MCSIM_EM_MOMENTS_AUTO = 0, MCSIM_EM_MOMENTS_CENTRED = 1, MCSIM_EM_MOMENTS_SHIFTED = 2 };
+int mcsim_cuda_em_set_moments(mcsim_cuda_ctx* ctx, int form);
+/* Which of the two the NEXT E-step of fit `fit` will use (the decision the last M-step, or prepare, took):
+ * *form = MCSIM_EM_MOMENTS_CENTRED or _SHIFTED.  Synchronises the context's stream. */
+int mcsim_cuda_em_moments_in_use(mcsim_cuda_ctx* ctx, int fit, int* form);
 
 /* ---- EM fit that allocates nothing ----------------------------------------------------------- */
 /* NO COUNTERPART IN THE REFERENCE: added for callers that cannot

@@ -7,11 +7,12 @@
 // :2447-2465 + init_constants :980-1046 become em_mstep_kernel (one CTA per fit, FP64).
 //
 // Samples: FP32, component-major per fit (x[n], y[n], theta[n]) -- 12 B per sample and iteration
-// from HBM.  Sufficient statistics are accumulated about the CURRENT component mean
-// (d = x - mu_g, which the Mahalanobis form needs anyway):  sum r, sum r d, sum r d d^T;
-// new mean = mu_g + sum r d / sum r, new cov = sum r d d^T / sum r - delta delta^T.  Algebraically
-// this is the reference's sum r x x^T / sum r - mean mean^T (:2591-2600) without its cancellation,
-// which FP32 partial sums could not afford (|x|^2 ~ 10, cov ~ 1e-3).
+// from HBM.  Sufficient statistics are accumulated about a reference point near the data (d = x - ref):
+// sum r, sum r d, sum r d d^T; new mean = ref + sum r d / sum r, new cov = sum r d d^T / sum r - delta delta^T.
+// Algebraically this is the reference's sum r x x^T / sum r - mean mean^T (:2591-2600) without its cancellation,
+// which FP32 partial sums could not afford (|x|^2 ~ 10, cov ~ 1e-3).  ref is ONE point per fit while the fit's
+// components lie close together (the usual case: 11 instead of 16 instructions per sample and component, no
+// per-component d to keep in registers), else each component's own mean -- see "reference point" below.
 #ifndef MCSIM_EM_CUH
 #define MCSIM_EM_CUH
 
@@ -47,11 +48,49 @@ struct EmLaunch {
     const double* my_slots;                    // = peer_slots[my_rank], my_flags = peer_flags[my_rank] (kept apart: a run-time
     const unsigned long long* my_flags;        //   index into a kernel-parameter array would put the array on the stack)
     unsigned long long wait_value;             // value a counter holds once the block of this iteration has arrived
+    int moments;                               // EM_MOMENTS_AUTO / _CENTRED / _SHIFTED: reference point of the statistics (see em_header)
 };
 #define EM_MAX_PEERS 8   // = the extents of peer_slots / peer_flags above
 #define EM_MSTEP_FUSED_THREADS 192   // block size of the M-step kernel when it carries the exchange (>= 10 * 16 + 1); 32 otherwise
 #define EM_DONE_EXCHANGE_TIMEOUT 3     // done[] value: a peer's statistics did not arrive within EM_PEER_TIMEOUT_CYCLES
 #define EM_PEER_TIMEOUT_CYCLES (40ll * 1000 * 1000 * 1000)   // ~20 s: a stuck peer ends the fit with an error instead of hanging the GPU
+
+// ---- reference point of the sufficient statistics ---------------------------------------------------------------------
+// The statistics of component g are sums of r, r d and r d d^T with d = x - (a reference point); the M-step turns them
+// into the new mean (reference + sum r d / sum r) and covariance (sum r d d^T / sum r - the outer product of that step)
+// in FP64 (em_update_params, :2583-2638, computes the same quantities about zero in FP64).  Two choices:
+//  * CENTRED: the component's own current mean.  d is small (a few sigma), FP32 products lose nothing -- but d and its
+//    products are per component: 3 + 3 + 10 instructions per sample and component for the accumulation alone.
+//  * SHIFTED: ONE point c per fit (the heft-weighted mean of the current means, rounded to FP32).  e = x - c and its six
+//    products are computed once per sample and every component accumulates r * (1, e, e e^T): 1 + 10 instructions.  The
+//    price is cancellation in the M-step's covariance, (|mean - c|^2 + sigma^2) / sigma^2 times the FP32 rounding of the
+//    per-thread partial sums, so the form is taken only while T = 1/2 ||Sigma^-1||_inf (|mean_g - c| + 6 sigma_g)^2 stays
+//    below EM_SHIFT_LIMIT for every component of the fit (propagated beliefs: T = 100 .. 1,500 -- components of one
+//    mixture lie within a few sigma of each other); otherwise the fit uses the centred form for that iteration.
+//    What it buys depends on the kernel: the scalar kernels for K >= 6 no longer keep (or recompute) 3 K differences
+//    and stop spilling (+7 .. +20 %); the packed-pair kernels for K <= 5 have the registers anyway (+-2 %; K = 4 stays
+//    centred, EM_SHIFT_SKIP_K).
+// The log-likelihoods are computed about the component means in both forms.  Header of a fit, in the spare floats of
+// its first two records: rec0[10], rec0[11], rec1[10] = c; rec1[11] = 1.f if SHIFTED (K = 1 is always centred: its
+// responsibilities are 1 and it has no second record).
+#ifndef EM_SHIFT_LIMIT
+#define EM_SHIFT_LIMIT 2048.0
+#endif
+#ifndef EM_SHIFT_SKIP_K
+#define EM_SHIFT_SKIP_K 4
+#endif
+#define EM_MOMENTS_AUTO 0
+#define EM_MOMENTS_CENTRED 1
+#define EM_MOMENTS_SHIFTED 2
+struct EmHeader { float cx, cy, ct; bool shifted; };
+template <bool V> struct EmFormTag { static constexpr bool value = V; };
+template <int K>
+__device__ __forceinline__ EmHeader em_header(const float* s_c) {
+    EmHeader h;
+    if (K >= 2) { h.cx = s_c[10]; h.cy = s_c[11]; h.ct = s_c[EM_COMP_STRIDE + 10]; h.shifted = s_c[EM_COMP_STRIDE + 11] != 0.f; }
+    else { h.cx = h.cy = h.ct = 0.f; h.shifted = false; }
+    return h;
+}
 
 // ---- E-step ------------------------------------------------------------------------------------------
 // K: components of the model; G0: first component whose statistics THIS launch accumulates (at most 8
@@ -59,8 +98,13 @@ struct EmLaunch {
 // recomputes the log-likelihoods; the log-likelihood sum is accumulated by the G0 = 0 launch only.
 // The one-warp kernel for EM_OW_LO <= K <= 8 carries 10 K accumulators per thread.  Left alone it takes 183 - 227
 // registers (one 256-thread CTA per SM, 2 warps per scheduler, 56 % issue active); capped at 128 registers with one
-// sample in flight and 128-thread CTAs it spills 0.1 - 0.5 KB per thread but runs 4 warps per scheduler: K = 6 / 7 / 8
-// 0.340 / 0.361 / 0.375 -> 0.445 / 0.452 / 0.454 of the FP32 peak (profiles/r02_em_k68_occupancy.log).
+// sample in flight and 128-thread CTAs it runs 4 warps per scheduler: K = 6 / 7 / 8 0.340 / 0.361 / 0.375 -> 0.445 /
+// 0.452 / 0.454 of the FP32 peak with 0.1 - 0.5 KB of spills per thread (profiles/r02_em_k68_occupancy.log), and
+// 0.507 / 0.555 / 0.536 without spills once the statistics took the shifted form and the exponentials lost their
+// denormal handling (346 -> 278 instructions per sample at K = 8; profiles/r02_em_shifted_moments.log).
+#ifndef EM_SPLIT_U1_KG
+#define EM_SPLIT_U1_KG 6   // the split kernel runs one sample per thread between barriers when a member owns more components than this
+#endif
 #ifndef EM_OW_LO
 #define EM_OW_LO 6
 #endif
@@ -73,33 +117,12 @@ struct EmLaunch {
 #ifndef EM_OW_MINB68
 #define EM_OW_MINB68 4   // resident CTAs of that size per SM the register budget is set for: 128 registers, 16 warps per SM
 #endif
-template <int K, int G0>
-__global__ void __launch_bounds__((K >= EM_OW_LO && K <= 8 && G0 == 0) ? EM_OW_THREADS68 : 256, (K >= EM_OW_LO && K <= 8 && G0 == 0) ? EM_OW_MINB68 : 1) em_estep_kernel(const EmLaunch a) {
-    constexpr int KG = (K - G0) < 8 ? (K - G0) : 8;
-    constexpr int NACC = KG * EM_NSTAT + 1;
-    __shared__ __align__(16) float s_c[K * EM_COMP_STRIDE];
-    __shared__ double s_acc[NACC];
-    const int fit = blockIdx.y;
-    if (a.done[fit]) return;
-    for (int i = threadIdx.x; i < K * EM_COMP_STRIDE; i += blockDim.x) s_c[i] = a.comps[(size_t)fit * K * EM_COMP_STRIDE + i];
-    for (int i = threadIdx.x; i < NACC; i += blockDim.x) s_acc[i] = 0.0;
-    __syncthreads();
-
-    const float* xs = a.x + (size_t)fit * 3 * a.n;
-    const float* ys = xs + a.n;
-    const float* ts = ys + a.n;
-    float acc[KG][EM_NSTAT];
-#pragma unroll
-    for (int g = 0; g < KG; ++g)
-#pragma unroll
-        for (int k = 0; k < EM_NSTAT; ++k) acc[g][k] = 0.f;
-    float lsum = 0.f;
-
-    // U samples per pass, the next pass's 3 U loads issued before this pass's arithmetic: enough bytes
-    // in flight per SM to stream from HBM while the FP32 pipe works on the previous samples
-    constexpr int U = K <= 4 ? 4 : (K <= 8 ? (K >= EM_OW_LO ? EM_OW_U68 : 2) : 1);
-    // 32-bit sample indices (mcsim_cuda_em_prepare rejects n >= 2^31 per fit and shard)
-    const unsigned n = unsigned(a.n);
+// The sample loop of em_estep_kernel for one form of the statistics.  The two forms are separate instantiations (chosen per
+// fit at the top of the kernel): inside one loop ptxas hoists the centred form's d = x - mu_g into the shared part and
+// the shifted form pays for it (measured: 346 against 356 instructions per sample at K = 8 instead of 275).
+template <int K, int G0, int KG, int U, bool SHIFTED>
+__device__ __forceinline__ void em_ow_loop(const float* s_c, const EmHeader hd, const float* __restrict__ xs, const float* __restrict__ ys,
+                                           const float* __restrict__ ts, unsigned n, float (&acc)[KG][EM_NSTAT], float& lsum) {
     const unsigned stride = gridDim.x * blockDim.x;
     unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
     float bx[U], by[U], bt[U];
@@ -136,33 +159,88 @@ __global__ void __launch_bounds__((K >= EM_OW_LO && K <= 8 && G0 == 0) ? EM_OW_T
                 ll[g] = fmaf(d0, q0, fmaf(d1, q1, fmaf(cc.x * d2, d2, cc.y)));
                 m = fmaxf(m, ll[g]);
             }
+            // exp(ll - m) as one FFMA + MUFU.EX2 per component (exp2f adds a compare and two scalings for denormal results:
+            // a responsibility below 2^-126 is zero here), 1 / s as MUFU.RCP (1 ulp; __frcp_rn is a 9-instruction sequence)
             float s = 0.f;
+            const float ms = -m * 1.4426950408889634f;
 #pragma unroll
             for (int g = 0; g < K; ++g) {
-                ll[g] = exp2f((ll[g] - m) * 1.4426950408889634f);
+                ll[g] = mufu_ex2(fmaf(ll[g], 1.4426950408889634f, ms));
                 s += ll[g];
             }
-            if (G0 == 0) lsum += m + __logf(s);
-            const float inv = __frcp_rn(s);
+            if (G0 == 0) lsum += fmaf(mufu_lg2(s), 0.6931471805599453f, m);
+            const float inv = mufu_rcp(s);
+            if (SHIFTED) {
+                // statistics about the fit's common point: e and its products once per sample, 1 + 10 instructions per component
+                const float e0 = x - hd.cx, e1 = y - hd.cy, e2 = t - hd.ct;
+                const float p00 = e0 * e0, p01 = e0 * e1, p02 = e0 * e2, p11 = e1 * e1, p12 = e1 * e2, p22 = e2 * e2;
 #pragma unroll
-            for (int gg = 0; gg < KG; ++gg) {
-                const float4 ca = *reinterpret_cast<const float4*>(s_c + (G0 + gg) * EM_COMP_STRIDE);
-                const float r = ll[G0 + gg] * inv;
-                const float d0 = x - ca.x, d1 = y - ca.y, d2 = t - ca.z;
-                const float r0 = r * d0, r1 = r * d1, r2 = r * d2;
-                acc[gg][0] += r;
-                acc[gg][1] += r0;
-                acc[gg][2] += r1;
-                acc[gg][3] += r2;
-                acc[gg][4] = fmaf(r0, d0, acc[gg][4]);
-                acc[gg][5] = fmaf(r0, d1, acc[gg][5]);
-                acc[gg][6] = fmaf(r0, d2, acc[gg][6]);
-                acc[gg][7] = fmaf(r1, d1, acc[gg][7]);
-                acc[gg][8] = fmaf(r1, d2, acc[gg][8]);
-                acc[gg][9] = fmaf(r2, d2, acc[gg][9]);
+                for (int gg = 0; gg < KG; ++gg) {
+                    const float r = ll[G0 + gg] * inv;
+                    acc[gg][0] += r;
+                    acc[gg][1] = fmaf(r, e0, acc[gg][1]);
+                    acc[gg][2] = fmaf(r, e1, acc[gg][2]);
+                    acc[gg][3] = fmaf(r, e2, acc[gg][3]);
+                    acc[gg][4] = fmaf(r, p00, acc[gg][4]);
+                    acc[gg][5] = fmaf(r, p01, acc[gg][5]);
+                    acc[gg][6] = fmaf(r, p02, acc[gg][6]);
+                    acc[gg][7] = fmaf(r, p11, acc[gg][7]);
+                    acc[gg][8] = fmaf(r, p12, acc[gg][8]);
+                    acc[gg][9] = fmaf(r, p22, acc[gg][9]);
+                }
+            } else {
+#pragma unroll
+                for (int gg = 0; gg < KG; ++gg) {
+                    const float4 ca = *reinterpret_cast<const float4*>(s_c + (G0 + gg) * EM_COMP_STRIDE);
+                    const float r = ll[G0 + gg] * inv;
+                    const float d0 = x - ca.x, d1 = y - ca.y, d2 = t - ca.z;
+                    const float r0 = r * d0, r1 = r * d1, r2 = r * d2;
+                    acc[gg][0] += r;
+                    acc[gg][1] += r0;
+                    acc[gg][2] += r1;
+                    acc[gg][3] += r2;
+                    acc[gg][4] = fmaf(r0, d0, acc[gg][4]);
+                    acc[gg][5] = fmaf(r0, d1, acc[gg][5]);
+                    acc[gg][6] = fmaf(r0, d2, acc[gg][6]);
+                    acc[gg][7] = fmaf(r1, d1, acc[gg][7]);
+                    acc[gg][8] = fmaf(r1, d2, acc[gg][8]);
+                    acc[gg][9] = fmaf(r2, d2, acc[gg][9]);
+                }
             }
         }
     }
+}
+
+template <int K, int G0>
+__global__ void __launch_bounds__((K >= EM_OW_LO && K <= 8 && G0 == 0) ? EM_OW_THREADS68 : 256, (K >= EM_OW_LO && K <= 8 && G0 == 0) ? EM_OW_MINB68 : 1) em_estep_kernel(const EmLaunch a) {
+    constexpr int KG = (K - G0) < 8 ? (K - G0) : 8;
+    constexpr int NACC = KG * EM_NSTAT + 1;
+    __shared__ __align__(16) float s_c[K * EM_COMP_STRIDE];
+    __shared__ double s_acc[NACC];
+    const int fit = blockIdx.y;
+    if (a.done[fit]) return;
+    for (int i = threadIdx.x; i < K * EM_COMP_STRIDE; i += blockDim.x) s_c[i] = a.comps[(size_t)fit * K * EM_COMP_STRIDE + i];
+    for (int i = threadIdx.x; i < NACC; i += blockDim.x) s_acc[i] = 0.0;
+    __syncthreads();
+
+    const float* xs = a.x + (size_t)fit * 3 * a.n;
+    const float* ys = xs + a.n;
+    const float* ts = ys + a.n;
+    const EmHeader hd = em_header<K>(s_c);
+    float acc[KG][EM_NSTAT];
+#pragma unroll
+    for (int g = 0; g < KG; ++g)
+#pragma unroll
+        for (int k = 0; k < EM_NSTAT; ++k) acc[g][k] = 0.f;
+    float lsum = 0.f;
+
+    // U samples per pass, the next pass's 3 U loads issued before this pass's arithmetic: enough bytes
+    // in flight per SM to stream from HBM while the FP32 pipe works on the previous samples
+    constexpr int U = K <= 4 ? 4 : (K <= 8 ? (K >= EM_OW_LO ? EM_OW_U68 : 2) : 1);
+    // 32-bit sample indices (mcsim_cuda_em_prepare rejects n >= 2^31 per fit and shard)
+    const unsigned n = unsigned(a.n);
+    if (K >= 2 && hd.shifted) em_ow_loop<K, G0, KG, U, true>(s_c, hd, xs, ys, ts, n, acc, lsum);
+    else em_ow_loop<K, G0, KG, U, false>(s_c, hd, xs, ys, ts, n, acc, lsum);
 
     // warp shuffle reduction (FP32 within the warp's <= 32 partial sums is widened to FP64 first)
 #pragma unroll
@@ -186,41 +264,12 @@ __global__ void __launch_bounds__((K >= EM_OW_LO && K <= 8 && G0 == 0) ? EM_OW_T
     if (G0 == 0 && threadIdx.x == 0) atomicAdd(&st[K * EM_NSTAT], s_acc[NACC - 1]);
 }
 
-// ---- E-step, components split over the warps of a group (K >= 5) ----------------------------------------------------
-// One thread of em_estep_kernel carries 10 accumulators per component: 80 for K = 8 (227 registers, two warps per
-// scheduler), and K = 16 needed a second launch that recomputed all 16 log-likelihoods.  Here S consecutive warps form a
-// group that walks the SAME samples (lane l of every member holds sample l of the group's tile); member w owns the
-// components g = w, w + S, w + 2 S, ... -- their quadratic forms, exponentials and 10 accumulators each.  What the
-// members owe each other is the normaliser of the responsibilities: each writes its partial (max, sum of exponentials)
-// per sample to shared memory, a named barrier over the S warps (bar.sync id, 32 S) makes them visible, and everyone
-// combines them to the log-sum-exp of all K components (gmm_full_meat.hpp:2707-2723).  Per sample and member that is one
-// STS.64, S - 1 LDS.64, S + 1 MUFU and a barrier shared by U samples; the accumulators per thread drop to 10 ceil(K / S),
-// one launch covers any K <= 16, and twice to four times the warps are resident.  Member 0 also sums the log-likelihood.
-template <int K, int S>
-__global__ void __launch_bounds__(256, (K + S - 1) / S <= 2 ? 3 : 2) em_estep_split_kernel(const EmLaunch a) {
-    constexpr int KG = (K + S - 1) / S;   // components per member (strided: counts differ by at most one)
-    constexpr int NG = 8 / S;             // groups per CTA
-    constexpr int U = KG > 6 ? 1 : 2;     // samples per thread between two barriers
-    constexpr int NACC = K * EM_NSTAT + 1;
+// The round loop of em_estep_split_kernel for one form of the statistics (separate instantiations, as em_ow_loop).
+template <int K, int S, int KG, int NG, int U, bool SHIFTED>
+__device__ __forceinline__ void em_split_loop(const EmLaunch& a, const float* s_c, float2 (&s_ex)[2][8][U][32], const EmHeader hd, const float* __restrict__ xs,
+                                              const float* __restrict__ ys, const float* __restrict__ ts, unsigned lane, unsigned warp, unsigned grp, unsigned w,
+                                              float (&acc)[KG][EM_NSTAT], float& lsum) {
     constexpr float LOG2E = 1.4426950408889634f;
-    __shared__ __align__(16) float s_c[K * EM_COMP_STRIDE];
-    __shared__ double s_acc[NACC];
-    __shared__ float2 s_ex[2][8][U][32];  // [round parity][warp][sample of the round][lane]: partial (max, sum)
-    const int fit = blockIdx.y;
-    if (a.done[fit]) return;
-    for (int i = threadIdx.x; i < K * EM_COMP_STRIDE; i += blockDim.x) s_c[i] = a.comps[(size_t)fit * K * EM_COMP_STRIDE + i];
-    for (int i = threadIdx.x; i < NACC; i += blockDim.x) s_acc[i] = 0.0;
-    __syncthreads();
-    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, grp = warp / S, w = warp % S;
-    const float* xs = a.x + (size_t)fit * 3 * a.n;
-    const float* ys = xs + a.n;
-    const float* ts = ys + a.n;
-    float acc[KG][EM_NSTAT];
-#pragma unroll
-    for (int g = 0; g < KG; ++g)
-#pragma unroll
-        for (int k = 0; k < EM_NSTAT; ++k) acc[g][k] = 0.f;
-    float lsum = 0.f;
     const unsigned n = unsigned(a.n);
     const unsigned stride = gridDim.x * NG * 32u;                 // samples per round of the whole grid, per u
     unsigned i = (blockIdx.x * NG + grp) * 32u + lane;            // sample u of this round: i + u * stride
@@ -263,9 +312,10 @@ __global__ void __launch_bounds__(256, (K + S - 1) / S <= 2 ? 3 : 2) em_estep_sp
                 }
             }
             sm[u] = 0.f;
+            const float msu = -m[u] * LOG2E;
 #pragma unroll
             for (int gg = 0; gg < KG; ++gg) {
-                e[u][gg] = exp2f((e[u][gg] - m[u]) * LOG2E);   // a member without component gg: exp2(-huge) = 0
+                e[u][gg] = mufu_ex2(fmaf(e[u][gg], LOG2E, msu));   // a member without component gg: exp2(-huge) = 0
                 sm[u] += e[u][gg];
             }
             s_ex[par][warp][u][lane] = make_float2(m[u], sm[u]);
@@ -283,10 +333,30 @@ __global__ void __launch_bounds__(256, (K + S - 1) / S <= 2 ? 3 : 2) em_estep_sp
             }
             float tot = 0.f;
 #pragma unroll
-            for (int q = 0; q < S; ++q) tot = fmaf(os[q], exp2f((om[q] - M) * LOG2E), tot);
+            for (int q = 0; q < S; ++q) tot = fmaf(os[q], mufu_ex2((om[q] - M) * LOG2E), tot);
             const bool ok = i + u * stride < n;
-            const float scale = ok ? exp2f((m[u] - M) * LOG2E) * __frcp_rn(tot) : 0.f;
-            if (w == 0 && ok) lsum += M + __logf(tot);
+            const float scale = ok ? mufu_ex2((m[u] - M) * LOG2E) * mufu_rcp(tot) : 0.f;
+            if (w == 0 && ok) lsum += fmaf(mufu_lg2(tot), 0.6931471805599453f, M);
+            if (SHIFTED) {
+                const float e0 = cx[u] - hd.cx, e1 = cy[u] - hd.cy, e2 = ct[u] - hd.ct;
+                const float p00 = e0 * e0, p01 = e0 * e1, p02 = e0 * e2, p11 = e1 * e1, p12 = e1 * e2, p22 = e2 * e2;
+#pragma unroll
+                for (int gg = 0; gg < KG; ++gg) {
+                    if (int(w) + gg * S < K) {
+                        const float r = e[u][gg] * scale;
+                        acc[gg][0] += r;
+                        acc[gg][1] = fmaf(r, e0, acc[gg][1]);
+                        acc[gg][2] = fmaf(r, e1, acc[gg][2]);
+                        acc[gg][3] = fmaf(r, e2, acc[gg][3]);
+                        acc[gg][4] = fmaf(r, p00, acc[gg][4]);
+                        acc[gg][5] = fmaf(r, p01, acc[gg][5]);
+                        acc[gg][6] = fmaf(r, p02, acc[gg][6]);
+                        acc[gg][7] = fmaf(r, p11, acc[gg][7]);
+                        acc[gg][8] = fmaf(r, p12, acc[gg][8]);
+                        acc[gg][9] = fmaf(r, p22, acc[gg][9]);
+                    }
+                }
+            } else {
 #pragma unroll
             for (int gg = 0; gg < KG; ++gg) {
                 const int g = int(w) + gg * S;
@@ -307,8 +377,48 @@ __global__ void __launch_bounds__(256, (K + S - 1) / S <= 2 ? 3 : 2) em_estep_sp
                     acc[gg][9] = fmaf(r2, d2, acc[gg][9]);
                 }
             }
+            }
         }
     }
+}
+
+// ---- E-step, components split over the warps of a group (K >= 5) ----------------------------------------------------
+// One thread of em_estep_kernel carries 10 accumulators per component: 80 for K = 8 (227 registers, two warps per
+// scheduler), and K = 16 needed a second launch that recomputed all 16 log-likelihoods.  Here S consecutive warps form a
+// group that walks the SAME samples (lane l of every member holds sample l of the group's tile); member w owns the
+// components g = w, w + S, w + 2 S, ... -- their quadratic forms, exponentials and 10 accumulators each.  What the
+// members owe each other is the normaliser of the responsibilities: each writes its partial (max, sum of exponentials)
+// per sample to shared memory, a named barrier over the S warps (bar.sync id, 32 S) makes them visible, and everyone
+// combines them to the log-sum-exp of all K components (gmm_full_meat.hpp:2707-2723).  Per sample and member that is one
+// STS.64, S - 1 LDS.64, S + 1 MUFU and a barrier shared by U samples; the accumulators per thread drop to 10 ceil(K / S),
+// one launch covers any K <= 16, and twice to four times the warps are resident.  Member 0 also sums the log-likelihood.
+template <int K, int S>
+__global__ void __launch_bounds__(256, (K + S - 1) / S <= 2 ? 3 : 2) em_estep_split_kernel(const EmLaunch a) {
+    constexpr int KG = (K + S - 1) / S;   // components per member (strided: counts differ by at most one)
+    constexpr int NG = 8 / S;             // groups per CTA
+    constexpr int U = KG > EM_SPLIT_U1_KG ? 1 : 2;     // samples per thread between two barriers
+    constexpr int NACC = K * EM_NSTAT + 1;
+    __shared__ __align__(16) float s_c[K * EM_COMP_STRIDE];
+    __shared__ double s_acc[NACC];
+    __shared__ float2 s_ex[2][8][U][32];  // [round parity][warp][sample of the round][lane]: partial (max, sum)
+    const int fit = blockIdx.y;
+    if (a.done[fit]) return;
+    for (int i = threadIdx.x; i < K * EM_COMP_STRIDE; i += blockDim.x) s_c[i] = a.comps[(size_t)fit * K * EM_COMP_STRIDE + i];
+    for (int i = threadIdx.x; i < NACC; i += blockDim.x) s_acc[i] = 0.0;
+    __syncthreads();
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, grp = warp / S, w = warp % S;
+    const EmHeader hd = em_header<K>(s_c);
+    const float* xs = a.x + (size_t)fit * 3 * a.n;
+    const float* ys = xs + a.n;
+    const float* ts = ys + a.n;
+    float acc[KG][EM_NSTAT];
+#pragma unroll
+    for (int g = 0; g < KG; ++g)
+#pragma unroll
+        for (int k = 0; k < EM_NSTAT; ++k) acc[g][k] = 0.f;
+    float lsum = 0.f;
+    if (hd.shifted) em_split_loop<K, S, KG, NG, U, true>(a, s_c, s_ex, hd, xs, ys, ts, lane, warp, grp, w, acc, lsum);
+    else em_split_loop<K, S, KG, NG, U, false>(a, s_c, s_ex, hd, xs, ys, ts, lane, warp, grp, w, acc, lsum);
 #pragma unroll
     for (int gg = 0; gg < KG; ++gg) {
         const int g = int(w) + gg * S;
@@ -338,8 +448,8 @@ __global__ void __launch_bounds__(256, (K + S - 1) / S <= 2 ? 3 : 2) em_estep_sp
 // pairs pay on sm_100a (tools/pipe_probe.cu): half the FMA-pipe issue slots per sample.  Same arithmetic
 // per lane as em_estep_kernel; MUFU (ex2, lg2, rcp) and the running maximum stay per lane.
 // one pair of samples (the two lanes of x, y, t) against the K components in s_c; v1 = 0 masks lane 1
-template <int K>
-__device__ __forceinline__ void em_pair2(const float* s_c, f2 x, f2 y, f2 t, float v1, f2 (&acc)[K][EM_NSTAT], f2& lsum) {
+template <int K, bool SHIFTED>
+__device__ __forceinline__ void em_pair2(const float* s_c, const EmHeader& hd, f2 x, f2 y, f2 t, float v1, f2 (&acc)[K][EM_NSTAT], f2& lsum) {
     if (K == 1) {
         // one component: the responsibility is 1 and the log-sum-exp is the log-likelihood itself; the general
         // path below computes the same up to the rounding of its ex2 / rcp (1e-7), with 6 MUFU per pair more
@@ -394,6 +504,24 @@ __device__ __forceinline__ void em_pair2(const float* s_c, f2 x, f2 y, f2 t, flo
     const f2 valid = mk2(1.f, v1);
     lsum = fma2(fma2(lg, 0.6931471805599453f, mm), valid, lsum);   // (m + ln s) per valid lane
     const f2 inv = mul2(rcp2(s), valid);
+    if (SHIFTED) {
+        const f2 e0 = add2(x, -hd.cx), e1 = add2(y, -hd.cy), e2 = add2(t, -hd.ct);
+        const f2 p00 = mul2(e0, e0), p01 = mul2(e0, e1), p02 = mul2(e0, e2), p11 = mul2(e1, e1), p12 = mul2(e1, e2), p22 = mul2(e2, e2);
+#pragma unroll
+        for (int g = 0; g < K; ++g) {
+            const f2 r = mul2(ll[g], inv);
+            acc[g][0] = add2(acc[g][0], r);
+            acc[g][1] = fma2(r, e0, acc[g][1]);
+            acc[g][2] = fma2(r, e1, acc[g][2]);
+            acc[g][3] = fma2(r, e2, acc[g][3]);
+            acc[g][4] = fma2(r, p00, acc[g][4]);
+            acc[g][5] = fma2(r, p01, acc[g][5]);
+            acc[g][6] = fma2(r, p02, acc[g][6]);
+            acc[g][7] = fma2(r, p11, acc[g][7]);
+            acc[g][8] = fma2(r, p12, acc[g][8]);
+            acc[g][9] = fma2(r, p22, acc[g][9]);
+        }
+    } else {
 #pragma unroll
     for (int g = 0; g < K; ++g) {
         const float4 ca = *reinterpret_cast<const float4*>(s_c + g * EM_COMP_STRIDE);
@@ -411,6 +539,7 @@ __device__ __forceinline__ void em_pair2(const float* s_c, f2 x, f2 y, f2 t, flo
         acc[g][8] = fma2(r1, d2, acc[g][8]);
         acc[g][9] = fma2(r2, d2, acc[g][9]);
     }
+    }
 }
 
 // VEC: the sample count is a multiple of 4, so every row of x is 16-byte aligned: one LDG.128 per row brings 4
@@ -426,6 +555,7 @@ __global__ void __launch_bounds__(256, (VEC && K == 1) ? 3 : ((VEC && K == 2) ? 
     for (int i = threadIdx.x; i < K * EM_COMP_STRIDE; i += blockDim.x) s_c[i] = a.comps[(size_t)fit * K * EM_COMP_STRIDE + i];
     for (int i = threadIdx.x; i < NACC; i += blockDim.x) s_acc[i] = 0.0;
     __syncthreads();
+    const EmHeader hd = em_header<K>(s_c);
     const float* xs = a.x + (size_t)fit * 3 * a.n;
     const float* ys = xs + a.n;
     const float* ts = ys + a.n;
@@ -438,6 +568,9 @@ __global__ void __launch_bounds__(256, (VEC && K == 1) ? 3 : ((VEC && K == 2) ? 
     const unsigned n = unsigned(a.n);
     const unsigned stride = gridDim.x * blockDim.x;
 
+    // the sample loops, instantiated once per form of the statistics (as em_ow_loop)
+    auto loops = [&](auto form) {
+    constexpr bool SH = decltype(form)::value;
     if (VEC) {
         const float4* x4 = reinterpret_cast<const float4*>(xs);
         const float4* y4 = reinterpret_cast<const float4*>(ys);
@@ -465,8 +598,8 @@ __global__ void __launch_bounds__(256, (VEC && K == 1) ? 3 : ((VEC && K == 2) ? 
 #pragma unroll
             for (int u = 0; u < 2; ++u) {
                 if (j + u * stride >= n4) break;
-                em_pair2<K>(s_c, mk2(cx[u].x, cx[u].y), mk2(cy[u].x, cy[u].y), mk2(ct[u].x, ct[u].y), 1.f, acc, lsum);
-                em_pair2<K>(s_c, mk2(cx[u].z, cx[u].w), mk2(cy[u].z, cy[u].w), mk2(ct[u].z, ct[u].w), 1.f, acc, lsum);
+                em_pair2<K, SH>(s_c, hd, mk2(cx[u].x, cx[u].y), mk2(cy[u].x, cy[u].y), mk2(ct[u].x, ct[u].y), 1.f, acc, lsum);
+                em_pair2<K, SH>(s_c, hd, mk2(cx[u].z, cx[u].w), mk2(cy[u].z, cy[u].w), mk2(ct[u].z, ct[u].w), 1.f, acc, lsum);
             }
         }
     } else {
@@ -493,10 +626,13 @@ __global__ void __launch_bounds__(256, (VEC && K == 1) ? 3 : ((VEC && K == 2) ? 
             for (int u = 0; u < U; ++u) {
                 if (i + 2 * u * stride >= n) break;
                 const float v1 = (i + (2 * u + 1) * stride < n) ? 1.f : 0.f;   // lane 1 may be past the end
-                em_pair2<K>(s_c, mk2(cx[2 * u], cx[2 * u + 1]), mk2(cy[2 * u], cy[2 * u + 1]), mk2(ct[2 * u], ct[2 * u + 1]), v1, acc, lsum);
+                em_pair2<K, SH>(s_c, hd, mk2(cx[2 * u], cx[2 * u + 1]), mk2(cy[2 * u], cy[2 * u + 1]), mk2(ct[2 * u], ct[2 * u + 1]), v1, acc, lsum);
             }
         }
     }
+    };
+    if (K >= 2 && hd.shifted) loops(EmFormTag<true>{});
+    else loops(EmFormTag<false>{});
 #pragma unroll
     for (int g = 0; g < K; ++g)
 #pragma unroll
@@ -582,6 +718,7 @@ __global__ void __launch_bounds__(256, K == 1 ? 3 : (K <= 3 ? 2 : 1)) em_estep_t
     for (int i = threadIdx.x; i < K * EM_COMP_STRIDE; i += blockDim.x) s_c[i] = a.comps[(size_t)fit * K * EM_COMP_STRIDE + i];
     for (int i = threadIdx.x; i < NACC; i += blockDim.x) s_acc[i] = 0.0;
     __syncthreads();
+    const EmHeader hd = em_header<K>(s_c);
     f2 acc[K][EM_NSTAT];
 #pragma unroll
     for (int g = 0; g < K; ++g)
@@ -589,6 +726,8 @@ __global__ void __launch_bounds__(256, K == 1 ? 3 : (K <= 3 ? 2 : 1)) em_estep_t
         for (int k = 0; k < EM_NSTAT; ++k) acc[g][k] = bc(0.f);
     f2 lsum = bc(0.f);
 
+    auto tiles = [&](auto form) {   // the tile loop, instantiated once per form of the statistics (as em_ow_loop)
+    constexpr bool SH = decltype(form)::value;
     for (unsigned i = 0; i < my_tiles; ++i) {
         const unsigned stage = i % EM_TMA_STAGES;
         const unsigned first = (blockIdx.x + i * gridDim.x) * EM_TMA_TILE;
@@ -600,14 +739,17 @@ __global__ void __launch_bounds__(256, K == 1 ? 3 : (K <= 3 ? 2 : 1)) em_estep_t
 #pragma unroll 1
         for (unsigned q = threadIdx.x; 4 * q < count; q += 256) {
             const float4 vx = tx[q], vy = ty[q], vt = tt[q];
-            em_pair2<K>(s_c, mk2(vx.x, vx.y), mk2(vy.x, vy.y), mk2(vt.x, vt.y), 1.f, acc, lsum);
-            em_pair2<K>(s_c, mk2(vx.z, vx.w), mk2(vy.z, vy.w), mk2(vt.z, vt.w), 1.f, acc, lsum);
+            em_pair2<K, SH>(s_c, hd, mk2(vx.x, vx.y), mk2(vy.x, vy.y), mk2(vt.x, vt.y), 1.f, acc, lsum);
+            em_pair2<K, SH>(s_c, hd, mk2(vx.z, vx.w), mk2(vy.z, vy.w), mk2(vt.z, vt.w), 1.f, acc, lsum);
         }
         // every thread is done reading the stage before the bulk-copy engine may overwrite it
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncthreads();
         if (threadIdx.x == 0 && i + EM_TMA_STAGES < my_tiles) issue(i + EM_TMA_STAGES);
     }
+    };
+    if (K >= 2 && hd.shifted) tiles(EmFormTag<true>{});
+    else tiles(EmFormTag<false>{});
 #pragma unroll
     for (int g = 0; g < K; ++g)
 #pragma unroll
@@ -650,10 +792,10 @@ __device__ __forceinline__ double em_det3(const double* A) {
 }
 
 // init_constants (:980-1046) for one component: inverse covariance (from the Cholesky factor, as
-// inv_sympd does), log|Sigma|; "last resort" diagonal treatment when either fails.  Writes the
-// FP32 E-step record: mu, b = -1/2 Sigma^-1 (off-diagonals doubled), cst = log_det_etc + log heft.
-__device__ __forceinline__ void em_constants(const double* mean, const double* C, double heft, float* rec) {
-    double Lo[6], inv[6], log_det;
+// inv_sympd does), log|Sigma|; "last resort" diagonal treatment when either fails.
+// inv = Sigma^-1 (00 01 02 11 12 22), cst = log_det_etc + log heft.
+__device__ __forceinline__ void em_precision(const double* C, double heft, double* inv, double& cst) {
+    double Lo[6], log_det;
     const double det = em_det3(C);
     const bool ok = em_chol3(C, Lo) && isfinite(log(det)) && det > 0.0;
     if (ok) {
@@ -679,12 +821,16 @@ __device__ __forceinline__ void em_constants(const double* mean, const double* C
             log_det += log(v);
         }
     }
-    const double cst = -(1.5 * log(2.0 * 3.14159265358979323846) + 0.5 * log_det) + log(fmax(heft, DBL_MIN));
+    cst = -(1.5 * log(2.0 * 3.14159265358979323846) + 0.5 * log_det) + log(fmax(heft, DBL_MIN));
+}
+// The FP32 E-step record of a component: mu, b = -1/2 Sigma^-1 (off-diagonals doubled), cst; the two spare floats of
+// the records of components 0 and 1 carry the fit's header (below).
+__device__ __forceinline__ void em_record(const double* mean, const double* inv, double cst, float pad0, float pad1, float* rec) {
     rec[0] = float(mean[0]); rec[1] = float(mean[1]); rec[2] = float(mean[2]);
     rec[3] = float(-0.5 * inv[0]); rec[4] = float(-inv[1]); rec[5] = float(-inv[2]);
     rec[6] = float(-0.5 * inv[3]); rec[7] = float(-inv[4]); rec[8] = float(-0.5 * inv[5]);
     rec[9] = float(cst);
-    rec[10] = rec[11] = 0.f;
+    rec[10] = pad0; rec[11] = pad1;
 }
 
 // One CTA per fit, thread g = component g.  prep_only: compute the E-step constants of the initial
@@ -698,6 +844,12 @@ __global__ void __launch_bounds__(EM_MSTEP_FUSED_THREADS) em_mstep_kernel(const 
     double* fcovs = a.fcovs + (size_t)fit * K * 9;
     double* st = a.stats + (size_t)fit * (K * EM_NSTAT + 1);
     if (!prep_only && a.done[fit]) return;
+    // reference point the E-step that produced these statistics used (header written by the previous M-step / prep launch;
+    // read by every thread here, overwritten at the end of this kernel behind two barriers)
+    float* recs = a.comps + (size_t)fit * K * EM_COMP_STRIDE;
+    const bool was_shifted = !prep_only && K >= 2 && recs[EM_COMP_STRIDE + 11] != 0.f;
+    double ref_c[3] = {0.0, 0.0, 0.0};
+    if (was_shifted) { ref_c[0] = recs[10]; ref_c[1] = recs[11]; ref_c[2] = recs[EM_COMP_STRIDE + 10]; }
     __shared__ double s_tot[MCSIM_MAX_GAUSSIANS * EM_NSTAT + 1];
     if (!prep_only && a.n_peers > 1) {
         // Fused exchange (no collective launch between E- and M-step).  (1) push: this CTA stores its fit's local block
@@ -774,7 +926,8 @@ __global__ void __launch_bounds__(EM_MSTEP_FUSED_THREADS) em_mstep_kernel(const 
                 const double det = em_det3(N);
                 if (fin && det > 0.0 && isfinite(log(det)) && em_chol3(N, Lo)) {
                     heft = sr / a.n_total;
-                    mean[0] += d0; mean[1] += d1; mean[2] += d2;
+                    if (was_shifted) { mean[0] = ref_c[0] + d0; mean[1] = ref_c[1] + d1; mean[2] = ref_c[2] + d2; }
+                    else { mean[0] += d0; mean[1] += d1; mean[2] += d2; }
                     for (int k = 0; k < 9; ++k) C[k] = N[k];
                 }
             }
@@ -828,10 +981,45 @@ __global__ void __launch_bounds__(EM_MSTEP_FUSED_THREADS) em_mstep_kernel(const 
         // statistics consumed: zero them for the next E-step
         for (int i = g; i < K * EM_NSTAT + 1; i += blockDim.x) st[i] = 0.0;
     }
-    // ---- init_constants for the next E-step (also floors the hefts at DBL_MIN, :1040-1045)
+    // ---- init_constants for the next E-step (also floors the hefts at DBL_MIN, :1040-1045), and the reference point of
+    // its statistics: c = sum_g heft_g mean_g (every thread adds the same K terms in the same order)
+    __shared__ double s_T[MCSIM_MAX_GAUSSIANS];
+    double inv[6], cst = 0.0;
     if (g < K) {
         if (heft < DBL_MIN) { heft = DBL_MIN; hefts[g] = heft; }
-        em_constants(mean, C, heft, a.comps + ((size_t)fit * K + g) * EM_COMP_STRIDE);
+        s_heft[g] = heft;
+        for (int d = 0; d < 3; ++d) s_mean[g][d] = mean[d];
+        em_precision(C, heft, inv, cst);
+    }
+    __syncthreads();
+    double c[3] = {0.0, 0.0, 0.0}, hs = 0.0;
+    for (int k = 0; k < K; ++k) {
+        hs += s_heft[k];
+        for (int d = 0; d < 3; ++d) c[d] += s_heft[k] * s_mean[k][d];
+    }
+    float c32[3];
+    for (int d = 0; d < 3; ++d) c32[d] = float(c[d] / hs);
+    if (g < K) {
+        const double row0 = fabs(inv[0]) + fabs(inv[1]) + fabs(inv[2]), row1 = fabs(inv[1]) + fabs(inv[3]) + fabs(inv[4]),
+                     row2 = fabs(inv[2]) + fabs(inv[4]) + fabs(inv[5]);
+        const double e0 = mean[0] - c32[0], e1 = mean[1] - c32[1], e2 = mean[2] - c32[2];
+        const double R = sqrt(e0 * e0 + e1 * e1 + e2 * e2) + 6.0 * sqrt(fmax(C[0], 0.0) + fmax(C[4], 0.0) + fmax(C[8], 0.0));
+        const double T = 0.5 * fmax(row0, fmax(row1, row2)) * R * R;
+        s_T[g] = isfinite(T) ? T : DBL_MAX;
+    }
+    __syncthreads();
+    bool shifted = K >= 2 && a.moments != EM_MOMENTS_CENTRED && isfinite(c32[0]) && isfinite(c32[1]) && isfinite(c32[2]);
+    if (shifted && a.moments == EM_MOMENTS_AUTO) {
+        for (int k = 0; k < K; ++k) shifted = shifted && s_T[k] < EM_SHIFT_LIMIT;
+        // K = 4 runs on packed pairs with all d in registers (212 of them): there the shifted form only trades FADD2 / FMUL2
+        // for three-operand FFMA2, which hold the dispatch port longer -- 0.583 against 0.606 of the FP32 peak on config 5
+        // (K = 2, 3, 5: +1 .. +2 %; K >= 6: +7 .. +20 %, profiles/r02_em_shifted_moments.log)
+        if (K == EM_SHIFT_SKIP_K) shifted = false;
+    }
+    if (g < K) {
+        const float pad0 = g == 0 ? c32[0] : (g == 1 ? c32[2] : 0.f);
+        const float pad1 = g == 0 ? c32[1] : (g == 1 ? (shifted ? 1.f : 0.f) : 0.f);
+        em_record(mean, inv, cst, pad0, pad1, recs + (size_t)g * EM_COMP_STRIDE);
     }
 }
 

@@ -133,6 +133,7 @@ struct mcsim_cuda_ctx {
     int sc_ee = 0, sc_est = 0;
     // EM state
     DevBuf em_x, em_comps, em_hefts, em_means, em_fcovs, em_stats, em_old, em_done, em_iters, em_trace;
+    int em_moments = EM_MOMENTS_AUTO;   // reference point of the EM statistics (mcsim_cuda_em_set_moments)
     // E-step launch configuration of the prepared fit (kernel choice, occupancy query and wave fitting done once, not per iteration)
     void (*em_k0)(const EmLaunch) = nullptr;
     void (*em_k1)(const EmLaunch) = nullptr;
@@ -1428,7 +1429,9 @@ static void em_pick(em_kernel_t& k0, em_kernel_t& k1, bool vec, size_t& smem, in
     smem = 0;
     block = 256;
 #ifndef EM_PACKED_MAX_K
-#define EM_PACKED_MAX_K 5   // packed pairs while the 10 K accumulator pairs fit the register file (K = 5: 230 registers, 1.61 vs 2.15 ms; K = 6 spills)
+#define EM_PACKED_MAX_K 5   // packed pairs while the 10 K accumulator pairs fit the register file (K = 5: 230 registers; K = 6 spills).  On config 5
+                            // (56 fits) the packed kernel beats the 128-register one-warp kernel for K = 4 (0.606 vs 0.549 of the FP32 peak) and
+                            // K = 5 (0.577 vs 0.499); on 16 fits it is the other way round (profiles/r02_em_shifted_moments.log)
 #endif
     if constexpr (K <= EM_PACKED_MAX_K) k0 = em_estep2_kernel<K, false>;  // packed: two samples per thread
     if constexpr (K <= EM_TMA_MAX_K) {  // fed by the bulk-copy engine: K = 1 is HBM-bound; K = 2..4 gain the prefetch registers back
@@ -1463,6 +1466,27 @@ static bool em_kernels(int K, em_kernel_t& k0, em_kernel_t& k1, bool vec, size_t
         case 15: em_pick<15>(k0, k1, vec, smem, block); return true;  case 16: em_pick<16>(k0, k1, vec, smem, block); return true;
     }
     return false;
+}
+
+extern "C" int mcsim_cuda_em_set_moments(mcsim_cuda_ctx* c, int form) {
+    if (!c) return fail(MCSIM_ERR_ARG, "em_set_moments: NULL context");
+    if (form != MCSIM_EM_MOMENTS_AUTO && form != MCSIM_EM_MOMENTS_CENTRED && form != MCSIM_EM_MOMENTS_SHIFTED)
+        return fail(MCSIM_ERR_ARG, "em_set_moments: form %d is none of MCSIM_EM_MOMENTS_AUTO / _CENTRED / _SHIFTED", form);
+    c->em_moments = form;
+    return MCSIM_OK;
+}
+
+extern "C" int mcsim_cuda_em_moments_in_use(mcsim_cuda_ctx* c, int fit, int* form) {
+    if (!c || !form || !c->em_prepared) return fail(MCSIM_ERR_ARG, "em_moments_in_use: nothing prepared");
+    if (fit < 0 || fit >= c->em.n_fits) return fail(MCSIM_ERR_ARG, "em_moments_in_use: fit %d out of range", fit);
+    *form = MCSIM_EM_MOMENTS_CENTRED;
+    if (c->em.K < 2) return MCSIM_OK;
+    CK(cudaSetDevice(c->device));
+    float flag = 0.f;   // header of the fit: spare floats of its first two records (em_sm100.cuh, em_header)
+    CK(cudaMemcpyAsync(&flag, c->em.comps + (size_t(fit) * c->em.K + 1) * EM_COMP_STRIDE + 11, sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    if (flag != 0.f) *form = MCSIM_EM_MOMENTS_SHIFTED;
+    return MCSIM_OK;
 }
 
 extern "C" int mcsim_cuda_em_prepare(mcsim_cuda_ctx* c, const mcsim_em_params* p) {
@@ -1517,6 +1541,7 @@ extern "C" int mcsim_cuda_em_prepare(mcsim_cuda_ctx* c, const mcsim_em_params* p
     a.n_total = double(p->n_total ? p->n_total : p->n);
     a.K = K; a.n_fits = F; a.iters = p->iters; a.iter = 0;
     a.n_peers = 0; a.my_rank = 0; a.wait_value = 0;
+    a.moments = c->em_moments;
     a.var_floor = p->var_floor > 0 ? p->var_floor : DBL_MIN;
     a.comps = (float*)c->em_comps.p; a.hefts = (double*)c->em_hefts.p; a.means = (double*)c->em_means.p;
     a.fcovs = (double*)c->em_fcovs.p; a.stats = (double*)c->em_stats.p; a.old_avg = (double*)c->em_old.p;

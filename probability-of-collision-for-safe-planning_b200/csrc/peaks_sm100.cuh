@@ -19,7 +19,7 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(float* out, int iters, fl
     if (s == 12345.678f) out[0] = s;  // never true in practice; keeps the chains alive
 }
 
-__device__ __forceinline__ float mufu_ex2(float x) {
+__device__ __forceinline__ float mufu_ex2_chain(float x) {   // volatile: the peak kernel's chain must not be folded
     float y;
     asm volatile("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
@@ -31,8 +31,8 @@ __global__ void __launch_bounds__(256) mufu_peak_kernel(float* out, int iters) {
     float x4 = x0 + .4f, x5 = x0 + .5f, x6 = x0 + .6f, x7 = x0 + .7f;
 #pragma unroll 8
     for (int i = 0; i < iters; ++i) {
-        x0 = mufu_ex2(x0); x1 = mufu_ex2(x1); x2 = mufu_ex2(x2); x3 = mufu_ex2(x3);
-        x4 = mufu_ex2(x4); x5 = mufu_ex2(x5); x6 = mufu_ex2(x6); x7 = mufu_ex2(x7);
+        x0 = mufu_ex2_chain(x0); x1 = mufu_ex2_chain(x1); x2 = mufu_ex2_chain(x2); x3 = mufu_ex2_chain(x3);
+        x4 = mufu_ex2_chain(x4); x5 = mufu_ex2_chain(x5); x6 = mufu_ex2_chain(x6); x7 = mufu_ex2_chain(x7);
     }
     const float s = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
     if (s == 12345.678f) out[0] = s;

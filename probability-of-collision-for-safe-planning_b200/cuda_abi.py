@@ -64,6 +64,7 @@ class EmStaticParams(C.Structure):
 EM_STATIC_MAX_FITS, EM_STATIC_MAX_ITERS, EM_STATIC_SCRATCH_BYTES = 8, 64, 32768
 EM_EXCHANGE_AUTO, EM_EXCHANGE_NCCL, EM_EXCHANGE_PEER = 0, 1, 2
 FILTER_STATE, FILTER_DEVIATION = 0, 1
+EM_MOMENTS_AUTO, EM_MOMENTS_CENTRED, EM_MOMENTS_SHIFTED = 0, 1, 2
 
 
 class EmResult(C.Structure):
@@ -186,6 +187,8 @@ def lib():
         L.mcsim_cuda_em_collect.argtypes = [vp, C.POINTER(EmResult)]
         L.mcsim_cuda_em_stats.argtypes = [vp, C.POINTER(C.c_uint64)]
         L.mcsim_cuda_em_stats.restype = vp
+        L.mcsim_cuda_em_set_moments.argtypes = [vp, C.c_int]
+        L.mcsim_cuda_em_moments_in_use.argtypes = [vp, C.c_int, C.POINTER(C.c_int)]
         L.mcsim_cuda_em_fit_static.argtypes = [C.POINTER(EmStaticParams)]
         L.mcsim_cuda_em_fit_static.restype = C.c_int
         L.mcsim_cuda_io_bytes.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
@@ -547,6 +550,16 @@ class Context:
 
     def em_mstep(self):
         check(lib().mcsim_cuda_em_mstep(self._h))
+
+    def em_set_moments(self, form):
+        """Reference point of the EM statistics for the fits prepared from now on: EM_MOMENTS_AUTO (default) / _CENTRED / _SHIFTED."""
+        check(lib().mcsim_cuda_em_set_moments(self._h, int(form)))
+
+    def em_moments_in_use(self, fit=0):
+        """EM_MOMENTS_CENTRED or EM_MOMENTS_SHIFTED: what the next E-step of `fit` uses (decided by the last M-step)."""
+        form = C.c_int()
+        check(lib().mcsim_cuda_em_moments_in_use(self._h, int(fit), C.byref(form)))
+        return int(form.value)
 
     def em_collect(self):
         F, K = self._em_shape

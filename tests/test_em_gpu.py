@@ -152,3 +152,77 @@ def test_em_bulk_copy_path_vs_live_reference(ctx):
             assert max(eh, em, ec) < RTOL, (K, n, f, eh, em, ec)
         shorter = ctx.em_fit(np.ascontiguousarray(x[:, :, :n - 1]), h, m, c, 4)
         np.testing.assert_allclose(shorter["means"], out["means"], rtol=1e-3, atol=1e-4)
+
+
+@pytest.mark.parametrize("K,n", [(2, 40000), (3, 39999), (4, 40000), (5, 30001), (8, 30000), (12, 30000), (16, 30000)])
+def test_em_moment_forms_agree(ctx, K, n):
+    """The statistics about one common point per fit (MCSIM_EM_MOMENTS_SHIFTED: x - c and its products once per sample)
+    and about each component's own mean (_CENTRED) are the same sufficient statistics; on mixtures whose components lie
+    within a few sigma of each other -- the propagated beliefs this operator is for -- AUTO picks SHIFTED, and both forms
+    meet the 1e-4 bar against Armadillo (run here when oracle/_ref is built) and agree far more closely with each other.
+    The shapes cover every E-step kernel: bulk-copy packed (K <= 4, n % 4 == 0), register-prefetch packed (K <= 5),
+    one warp per sample tile (K = 6..8), components split over two warps (K > 8)."""
+    import oracle_ref
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    x, h, m, c = pcoll_b200.inputs.synthetic_em_problem(300 + K, n, K)
+    outs = {}
+    try:
+        for form in (abi.EM_MOMENTS_CENTRED, abi.EM_MOMENTS_SHIFTED, abi.EM_MOMENTS_AUTO):
+            ctx.em_set_moments(form)
+            outs[form] = ctx.em_fit(x, h, m, c, 6)
+            used = ctx.em_moments_in_use(0)
+            if form != abi.EM_MOMENTS_AUTO:
+                assert used == form
+            else:   # components a few sigma apart: AUTO takes the shifted form, except where it is measured slower (K = 4)
+                auto_form = abi.EM_MOMENTS_CENTRED if K == 4 else abi.EM_MOMENTS_SHIFTED
+                assert used == auto_form
+    finally:
+        ctx.em_set_moments(abi.EM_MOMENTS_AUTO)
+    cen, shf, aut = (outs[f] for f in (abi.EM_MOMENTS_CENTRED, abi.EM_MOMENTS_SHIFTED, abi.EM_MOMENTS_AUTO))
+    eh, em, ec = _errors(shf, cen["hefts"][0], cen["means"][0], cen["fcovs"][0])
+    print("K=%d n=%d shifted vs centred: heft %.2e mean %.2e cov %.2e" % (K, n, eh, em, ec))
+    assert max(eh, em, ec) < 2e-5
+    same = outs[auto_form]
+    eh, em, ec = _errors(aut, same["hefts"][0], same["means"][0], same["fcovs"][0])
+    assert max(eh, em, ec) < 1e-9      # the same kernels and form: only the order of the FP64 atomics differs
+    if oracle_ref.available():
+        rm, rc, rh, rl = oracle_ref.em_fit(x.T.astype(np.float64), m, c.reshape(K, 9), h, 6)
+        for name, o in (("centred", cen), ("shifted", shf)):
+            eh, em, ec = _errors(o, rh, rm, rc.reshape(K, 3, 3))
+            print("   %s vs Armadillo: heft %.2e mean %.2e cov %.2e" % (name, eh, em, ec))
+            assert max(eh, em, ec) < RTOL
+
+
+def test_em_far_apart_components_keep_the_centred_form(ctx):
+    """Clusters 40 m apart with sigma = 0.03 m: about a common point the FP32 second moments would carry
+    (40 / 0.03)^2 = 2e6 times the rounding of the centred ones, so AUTO must stay with the centred form -- and the
+    forced shifted form visibly loses the covariances (that is what the guard is for)."""
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    rng = np.random.Generator(np.random.PCG64(77))
+    n, K = 60000, 3
+    centres = np.array([[0.0, 0.0, 0.0], [40.0, 0.0, 1.0], [0.0, 40.0, 2.0]])
+    lab = rng.integers(0, K, size=n)
+    x = (centres[lab] + rng.normal(0.0, 0.03, size=(n, 3))).T.astype(np.float32)
+    h = np.full(K, 1.0 / K); m = centres + 0.01; c = np.tile(np.eye(3) * 0.01, (K, 1, 1))
+    try:
+        ctx.em_set_moments(abi.EM_MOMENTS_AUTO)
+        aut = ctx.em_fit(x, h, m, c, 4)
+        assert ctx.em_moments_in_use(0) == abi.EM_MOMENTS_CENTRED
+        ctx.em_set_moments(abi.EM_MOMENTS_CENTRED)
+        cen = ctx.em_fit(x, h, m, c, 4)
+        ctx.em_set_moments(abi.EM_MOMENTS_SHIFTED)
+        shf = ctx.em_fit(x, h, m, c, 4)
+    finally:
+        ctx.em_set_moments(abi.EM_MOMENTS_AUTO)
+    eh, em, ec = _errors(aut, cen["hefts"][0], cen["means"][0], cen["fcovs"][0])
+    assert max(eh, em, ec) < 1e-9
+    x64 = x.astype(np.float64)
+    for g in range(K):
+        pts = x64[:, lab == g]
+        np.testing.assert_allclose(aut["means"][0][g], pts.mean(axis=1), atol=1e-5)
+        np.testing.assert_allclose(aut["fcovs"][0][g], np.cov(pts, bias=True), rtol=1e-3, atol=1e-7)
+    worst = max(np.max(np.abs(shf["fcovs"][0][g] - cen["fcovs"][0][g])) / np.max(np.abs(cen["fcovs"][0][g])) for g in range(K))
+    print("forced shifted form on far-apart clusters: covariance error %.2e relative" % worst)
+    assert worst > 1e-4

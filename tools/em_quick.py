@@ -1,6 +1,6 @@
 """Developer probe: E-step rate over K (16 fits x 10^6 samples resident, 10 iterations): sample-iterations/s, fraction of
 the FP32 peak at 61 flops per (sample, component, iteration), fraction of the HBM peak at 12 B per sample-iteration.
-`python tools/em_quick.py [lib.so ...]`"""
+`[EM_KS="3 8"] [EM_MOMENTS=0|1|2] python tools/em_quick.py [lib.so ...]`"""
 import os
 import subprocess
 import sys
@@ -17,9 +17,16 @@ def one(lib_path):
         abi.LIB_PATH = lib_path
     ctx = abi.Context(0)
     fp32 = ctx.measure_peak(0, 100.0)
-    F, n, iters = 16, 10 ** 6, 10
-    probs = [pcoll_b200.inputs.synthetic_em_problem(9000 + f % 4, n, 16, centre=(0.3 * f, 0.0, 0.0)) for f in range(F)]
-    x = np.stack([q[0] for q in probs])
+    ctx.em_set_moments(int(os.environ.get("EM_MOMENTS", "0")))   # 0 auto, 1 centred, 2 shifted
+    F, n, iters = int(os.environ.get("EM_F", "16")), 10 ** 6, 10
+    if F == 56:   # BASELINE config 5 exactly as bench.py builds it (56 waypoint buffers, 672 MB)
+        import bench
+        plan = pcoll_b200.load_plan_json(os.path.join(ROOT, "tests", "golden", "plan_committed.json"))
+        x, m16, c16 = bench.config5_buffers(plan, n, F)
+        probs = [(None, None, m16[f], c16[f]) for f in range(F)]
+    else:
+        probs = [pcoll_b200.inputs.synthetic_em_problem(9000 + f % 4, n, 16, centre=(0.3 * f, 0.0, 0.0)) for f in range(F)]
+        x = np.stack([q[0] for q in probs])
     first = True
     for K in (int(k) for k in os.environ.get("EM_KS", "1 2 3 4 5 6 8 9 12 13 16").split()):
         h = np.full((F, K), 1.0 / K); m = np.stack([q[2][:K] for q in probs]); c = np.stack([q[3][:K] for q in probs])

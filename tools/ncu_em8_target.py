@@ -13,7 +13,7 @@ ctx = abi.Context(0)
 probs = [pcoll_b200.inputs.synthetic_em_problem(9000 + f, 10 ** 6, 16) for f in range(8)]
 x = np.stack([q[0] for q in probs])
 first = True
-for K in (8, 16, 6):
+for K in (8, 16, 4, 12):
     h = np.stack([np.full(K, 1.0 / K) for q in probs]); m = np.stack([q[2][:K] for q in probs]); c = np.stack([q[3][:K] for q in probs])
     r = ctx.em_fit(x if first else None, h, m, c, 2)
     first = False
