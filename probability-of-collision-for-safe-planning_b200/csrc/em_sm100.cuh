@@ -108,6 +108,10 @@ __device__ __forceinline__ EmHeader em_header(const float* s_c) {
 #ifndef EM_OW_LO
 #define EM_OW_LO 6
 #endif
+#ifndef EM_OW_HI
+#define EM_OW_HI 9       // most components the one-warp kernel takes in one launch (10 accumulators each): K = 9 spills 0.25 KB per thread at
+                         // 128 registers and still beats the group of two (0.559 vs 0.481 of the FP32 peak on config 5); K = 10 ties, K >= 11 loses
+#endif
 #ifndef EM_OW_U68
 #define EM_OW_U68 1      // samples in flight per thread for EM_OW_LO <= K <= 8
 #endif
@@ -212,8 +216,8 @@ __device__ __forceinline__ void em_ow_loop(const float* s_c, const EmHeader hd, 
 }
 
 template <int K, int G0>
-__global__ void __launch_bounds__((K >= EM_OW_LO && K <= 8 && G0 == 0) ? EM_OW_THREADS68 : 256, (K >= EM_OW_LO && K <= 8 && G0 == 0) ? EM_OW_MINB68 : 1) em_estep_kernel(const EmLaunch a) {
-    constexpr int KG = (K - G0) < 8 ? (K - G0) : 8;
+__global__ void __launch_bounds__((K >= EM_OW_LO && K <= EM_OW_HI && G0 == 0) ? EM_OW_THREADS68 : 256, (K >= EM_OW_LO && K <= EM_OW_HI && G0 == 0) ? EM_OW_MINB68 : 1) em_estep_kernel(const EmLaunch a) {
+    constexpr int KG = (K - G0) < EM_OW_HI ? (K - G0) : EM_OW_HI;
     constexpr int NACC = KG * EM_NSTAT + 1;
     __shared__ __align__(16) float s_c[K * EM_COMP_STRIDE];
     __shared__ double s_acc[NACC];
@@ -236,7 +240,7 @@ __global__ void __launch_bounds__((K >= EM_OW_LO && K <= 8 && G0 == 0) ? EM_OW_T
 
     // U samples per pass, the next pass's 3 U loads issued before this pass's arithmetic: enough bytes
     // in flight per SM to stream from HBM while the FP32 pipe works on the previous samples
-    constexpr int U = K <= 4 ? 4 : (K <= 8 ? (K >= EM_OW_LO ? EM_OW_U68 : 2) : 1);
+    constexpr int U = K <= 4 ? 4 : (K <= EM_OW_HI ? (K >= EM_OW_LO ? EM_OW_U68 : 2) : 1);
     // 32-bit sample indices (mcsim_cuda_em_prepare rejects n >= 2^31 per fit and shard)
     const unsigned n = unsigned(a.n);
     if (K >= 2 && hd.shifted) em_ow_loop<K, G0, KG, U, true>(s_c, hd, xs, ys, ts, n, acc, lsum);

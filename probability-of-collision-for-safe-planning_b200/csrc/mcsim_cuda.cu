@@ -1444,15 +1444,15 @@ static void em_pick(em_kernel_t& k0, em_kernel_t& k1, bool vec, size_t& smem, in
 #define EM_SPLIT_S_HIGH 2   // for K > 8 (measured: 16 components 8.08 ms in two launches, 6.07 ms with 4 warps per group, 5.38 ms with 2)
 #endif
 #ifndef EM_SPLIT_MIN_K
-#define EM_SPLIT_MIN_K 9    // 5 <= K <= 8: the one-warp kernel is still 5-15 % faster than a group of two
+#define EM_SPLIT_MIN_K (EM_OW_HI + 1)    // 5 <= K <= 8: the one-warp kernel is still 5-15 % faster than a group of two
 #endif
     // K >= 5: the components are split over the warps of a group (em_estep_split_kernel): one launch for any K <= 16
-    if constexpr (K >= EM_SPLIT_MIN_K && K <= 8) k0 = em_estep_split_kernel<K, EM_SPLIT_S_LOW>;
-    if constexpr (K > 8) {
+    if constexpr (K >= EM_SPLIT_MIN_K && K <= EM_OW_HI) k0 = em_estep_split_kernel<K, EM_SPLIT_S_LOW>;
+    if constexpr (K > EM_OW_HI) {
         if constexpr (EM_SPLIT_MIN_K <= 16) k0 = em_estep_split_kernel<K, EM_SPLIT_S_HIGH>;
-        else k1 = em_estep_kernel<K, 8>;
+        else k1 = em_estep_kernel<K, EM_OW_HI>;
     }
-    if constexpr (K >= EM_OW_LO && K > EM_PACKED_MAX_K && K <= 8 && K < EM_SPLIT_MIN_K) block = EM_OW_THREADS68;   // the one-warp kernel's own CTA size there
+    if constexpr (K >= EM_OW_LO && K > EM_PACKED_MAX_K && K <= EM_OW_HI && K < EM_SPLIT_MIN_K) block = EM_OW_THREADS68;   // the one-warp kernel's own CTA size there
 }
 static bool em_kernels(int K, em_kernel_t& k0, em_kernel_t& k1, bool vec, size_t& smem, int& block) {
     switch (K) {
