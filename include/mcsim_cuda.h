@@ -367,8 +367,8 @@ void* mcsim_cuda_em_stats(mcsim_cuda_ctx* ctx, uint64_t* n_doubles);
  *                             (|mean - c|^2 + sigma^2) / sigma^2 digits-worth of the FP32 partial sums),
  *   MCSIM_EM_MOMENTS_AUTO     (default) SHIFTED for the fits and iterations whose components lie close enough together for
  *                             that loss to stay below ~1e-5 relative (decided on the device per fit and iteration,
- *                             DESIGN.md section 3), CENTRED otherwise -- and for K = 4, whose kernel is measured
- *                             faster in the centred form.  K = 1 is always CENTRED.
+ *                             DESIGN.md section 3), CENTRED otherwise -- and for K <= 5, whose packed-pair kernels
+ *                             gain nothing from it.  K = 1 is always CENTRED.
  * Applies to the fits prepared after the call. */
 enum { MCSIM_EM_MOMENTS_AUTO = 0, MCSIM_EM_MOMENTS_CENTRED = 1, MCSIM_EM_MOMENTS_SHIFTED = 2 };
 int mcsim_cuda_em_set_moments(mcsim_cuda_ctx* ctx, int form);

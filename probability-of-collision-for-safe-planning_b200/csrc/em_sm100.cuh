@@ -68,16 +68,16 @@ struct EmLaunch {
 //    below EM_SHIFT_LIMIT for every component of the fit (propagated beliefs: T = 100 .. 1,500 -- components of one
 //    mixture lie within a few sigma of each other); otherwise the fit uses the centred form for that iteration.
 //    What it buys depends on the kernel: the scalar kernels for K >= 6 no longer keep (or recompute) 3 K differences
-//    and stop spilling (+7 .. +20 %); the packed-pair kernels for K <= 5 have the registers anyway (+-2 %; K = 4 stays
-//    centred, EM_SHIFT_SKIP_K).
+//    and stop spilling (+7 .. +20 %); the packed-pair kernels for K <= 5 have the registers anyway (+-2 %) and stay
+//    centred under AUTO (EM_SHIFT_MIN_K).
 // The log-likelihoods are computed about the component means in both forms.  Header of a fit, in the spare floats of
 // its first two records: rec0[10], rec0[11], rec1[10] = c; rec1[11] = 1.f if SHIFTED (K = 1 is always centred: its
 // responsibilities are 1 and it has no second record).
 #ifndef EM_SHIFT_LIMIT
 #define EM_SHIFT_LIMIT 2048.0
 #endif
-#ifndef EM_SHIFT_SKIP_K
-#define EM_SHIFT_SKIP_K 4
+#ifndef EM_SHIFT_MIN_K
+#define EM_SHIFT_MIN_K 6    // AUTO takes the shifted form from this many components on (the scalar kernels)
 #endif
 #define EM_MOMENTS_AUTO 0
 #define EM_MOMENTS_CENTRED 1
@@ -1015,10 +1015,11 @@ __global__ void __launch_bounds__(EM_MSTEP_FUSED_THREADS) em_mstep_kernel(const 
     bool shifted = K >= 2 && a.moments != EM_MOMENTS_CENTRED && isfinite(c32[0]) && isfinite(c32[1]) && isfinite(c32[2]);
     if (shifted && a.moments == EM_MOMENTS_AUTO) {
         for (int k = 0; k < K; ++k) shifted = shifted && s_T[k] < EM_SHIFT_LIMIT;
-        // K = 4 runs on packed pairs with all d in registers (212 of them): there the shifted form only trades FADD2 / FMUL2
-        // for three-operand FFMA2, which hold the dispatch port longer -- 0.583 against 0.606 of the FP32 peak on config 5
-        // (K = 2, 3, 5: +1 .. +2 %; K >= 6: +7 .. +20 %, profiles/r02_em_shifted_moments.log)
-        if (K == EM_SHIFT_SKIP_K) shifted = false;
+        // K <= 5 runs on packed pairs with every d in registers: there the shifted form only trades FADD2 / FMUL2 for
+        // three-operand FFMA2 (config 5: K = 4 0.583 against 0.606 of the FP32 peak, K = 2, 3, 5 +1 .. +2 %), while its
+        // cancellation amplifies the run-to-run noise of a fit whose samples arrive in varying order (the EM-refit
+        // truncation compacts its free samples with atomics) -- not worth it.  K >= 6: +7 .. +20 %.
+        if (K < EM_SHIFT_MIN_K) shifted = false;
     }
     if (g < K) {
         const float pad0 = g == 0 ? c32[0] : (g == 1 ? c32[2] : 0.f);

@@ -284,12 +284,15 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
             if (MODE == MCSIM_MODE_REPLAY) {
                 z0 = a.normals[3 * i]; z1 = a.normals[3 * i + 1]; z2 = a.normals[3 * i + 2];
             } else {
-                mcsim_rng::u32x4 c = {unsigned(i), m.stream_id, unsigned(2 * a.t) | unsigned((i >> 32) << 16), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
+                // samples 2 j and 2 j + 1 share one block (philox.h, "GMM sample draws")
+                const unsigned long long j = i >> 1;
+                const bool odd = (i & 1ull) != 0;
+                mcsim_rng::u32x4 c = {unsigned(j), m.stream_id, unsigned(2 * a.t) | unsigned((j >> 32) << 16), unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)};
                 c = mcsim_rng::philox4x32_10(c, a.k0, a.k1);
                 float f0, f1, f2, f3;
-                mcsim_rng::box_muller(c.x, c.y, f0, f1);
-                mcsim_rng::box_muller(c.z, c.w, f2, f3);
-                z0 = f0; z1 = f1; z2 = f2;
+                mcsim_rng::box_muller_bits(odd ? c.y >> 8 : c.x >> 8, odd ? c.z >> 16 : c.z & 0xffffu, f0, f1);
+                mcsim_rng::box_muller_bits(c.w >> 8, mcsim_rng::gmm_pair_c_angle(c), f2, f3);
+                z0 = f0; z1 = f1; z2 = odd ? f3 : f2;
             }
             const double* cp = s_comp[g];
             const double* Lc = cp + 13;
@@ -436,11 +439,18 @@ template <class V>   // V = f2: per-lane components; V = float: one component fo
 __device__ __forceinline__ GmmDraw2 gmm_draw_test2(unsigned stream_id, unsigned ctr2, unsigned k0, unsigned k1, unsigned i0, unsigned i1, bool valid0, bool valid1,
                                                    const V (&L)[6], const V (&mu)[3], const float4* tab, const unsigned char* ccnt, const ushort2* cidx,
                                                    bool cull, float2 nom, unsigned& my_tests) {
-    const mcsim_rng::u32x4 ca = mcsim_rng::philox4x32_10(mcsim_rng::u32x4{i0, stream_id, ctr2, unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)}, k0, k1);
-    const mcsim_rng::u32x4 cb = mcsim_rng::philox4x32_10(mcsim_rng::u32x4{i1, stream_id, ctr2, unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)}, k0, k1);
-    f2 z0, z1, z2, z3;
-    box_muller2(ca.x, ca.y, cb.x, cb.y, z0, z1);
-    box_muller2(ca.z, ca.w, cb.z, cb.w, z2, z3);
+    // ONE block for the thread's two samples (philox.h, "GMM sample draws"): lane 0 = sample i0, lane 1 = i1 = i0 + 1 with i0
+    // even -- except in a launch that spreads one sample per thread (i1 invalid), where an odd i0 takes the odd sample's share
+    const unsigned odd = i0 & 1u;
+    const mcsim_rng::u32x4 c = mcsim_rng::philox4x32_10(mcsim_rng::u32x4{i0 >> 1, stream_id, ctr2, unsigned(mcsim_rng::PURPOSE_GMM_SAMPLE)}, k0, k1);
+    f2 z0, z1, z2;
+    box_muller2_bits(odd ? c.y >> 8 : c.x >> 8, half16f(c.z, int(odd)), c.y >> 8, half16f(c.z, 1), z0, z1);
+    {
+        const float rc = mufu_sqrt(mufu_lg2(fmaf(float(c.w >> 8), MCSIM_U24_SCALE, MCSIM_U24_HALF)) * -1.3862943611198906f);
+        const float tc = fmaf(float(mcsim_rng::gmm_pair_c_angle(c)), MCSIM_A16_SCALE, MCSIM_A16_HALF);
+        const float zs = rc * mufu_sin(tc);
+        z2 = mk2(odd ? zs : rc * mufu_cos(tc), zs);
+    }
     GmmDraw2 o;
     o.d0 = mul2(z0, L[0]);
     o.d1 = fma2(z1, L[2], mul2(z0, L[1]));

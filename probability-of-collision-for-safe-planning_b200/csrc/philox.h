@@ -81,6 +81,15 @@ MCSIM_PHD void step_bits(const u32x4& a, const u32x4& b, uint32_t rad[6], uint32
 #define MCSIM_A16_SCALE 9.587379924285257e-5f
 #define MCSIM_A16_HALF 4.7936899621426287e-5f
 
+// ---- GMM sample draws: the 3 normals of TWO samples from ONE Philox block ---------------------------
+// Samples 2 j and 2 j + 1 of a waypoint share the block with counter (j, stream, 2 t, PURPOSE_GMM_SAMPLE): three
+// Box-Muller pairs at 24 + 16 bits use 120 of its 128 bits (a block per sample used 80 and threw a fourth normal away;
+// Philox was 22 % of the batch kernel's instructions).  Layout (shared by the packed and the scalar sample kernels):
+//   pair A -> z0, z1 of the even sample: radius c.x >> 8, angle c.z & 0xffff
+//   pair B -> z0, z1 of the odd sample:  radius c.y >> 8, angle c.z >> 16
+//   pair C -> z2 of both (cos: even, sin: odd): radius c.w >> 8, angle (c.x & 0xff) << 8 | (c.y & 0xff)
+MCSIM_PHD uint32_t gmm_pair_c_angle(const u32x4& c) { return ((c.x & 0xffu) << 8) | (c.y & 0xffu); }
+
 #ifdef __CUDACC__
 // two standard normals from the 24 + 16 bits of one step pair (scalar kernels)
 __device__ __forceinline__ void box_muller_bits(uint32_t rad, uint32_t ang, float& n0, float& n1) {

@@ -174,8 +174,8 @@ def test_em_moment_forms_agree(ctx, K, n):
             used = ctx.em_moments_in_use(0)
             if form != abi.EM_MOMENTS_AUTO:
                 assert used == form
-            else:   # components a few sigma apart: AUTO takes the shifted form, except where it is measured slower (K = 4)
-                auto_form = abi.EM_MOMENTS_CENTRED if K == 4 else abi.EM_MOMENTS_SHIFTED
+            else:   # components a few sigma apart: AUTO takes the shifted form where it pays (the scalar kernels, K >= 6)
+                auto_form = abi.EM_MOMENTS_SHIFTED if K >= 6 else abi.EM_MOMENTS_CENTRED
                 assert used == auto_form
     finally:
         ctx.em_set_moments(abi.EM_MOMENTS_AUTO)
