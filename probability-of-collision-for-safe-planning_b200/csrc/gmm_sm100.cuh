@@ -1275,7 +1275,9 @@ __global__ void __launch_bounds__(32) gmm_robot_thread_kernel(const RobotThreadL
         predict_pose(real, un, nxt);
         for (int k = 0; k < 3; ++k) real[k] = nxt[k];
         for (int l = 0; l < L; ++l) zobs[l] = range_to(nm, real, l) + z[3 + l] * sq;
-        ekf_update(nm, pmu, pS, zobs, L);
+        // the 8 updates with one division each on the dependent chain (estimator_math.h; the reference's update up to rounding):
+        // this lane's chain of FP64 square roots and divisions is what the kernel's 0.41 ms per batch were made of
+        for (int l = 0; l < L; ++l) ekf_update_one_chain1(nm.lx[l], nm.ly[l], nm.Q, pmu, pS, zobs[l]);
         for (int k = 0; k < 3; ++k) { mu[k] = pmu[k]; st.u[k] = u[k]; st.M[k] = M[k]; st.xs[k] = xs[k]; st.xn[k] = xg[k]; st.us[k] = ustar[k]; }
         for (int k = 0; k < 9; ++k) S[k] = pS[k];
         for (int l = 0; l < L; ++l) st.z[l] = zobs[l];
