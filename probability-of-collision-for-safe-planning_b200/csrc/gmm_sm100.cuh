@@ -82,9 +82,12 @@ struct GmmLaunch {
     const float2* nominal;        // [T] (x*_t, y*_t), the centres of the lists; batch: [B][T] when cull_stride != 0
     unsigned long long* tests;    // optional: executed pair tests (all members)
     int spread;                   // Philox sample kernel: one sample per thread instead of two (small n, single run)
-    // EM-refit variant (8f-4): the collision-free samples of this waypoint, FP32, rows x | y | theta at stride free_cap,
-    // appended in no particular order (gmm_sample_kernel only); NULL: not kept
+    // EM-refit variant (8f-4): the poses of this waypoint's samples, FP32, rows x | y | theta at stride free_cap, written at
+    // the sample's own index, and free_flag[i] = 1 for the collision-free ones (gmm_sample_kernel only); NULL: not kept.
+    // gmm_compact_free_kernel then packs the free ones IN SAMPLE ORDER (an atomic append handed the EM fit a different
+    // order every run, and the truncate -> EM -> EKF chain amplified the 1e-10 that made to a flipped hit flag or thirty).
     float* free_out;
+    unsigned char* free_flag;
     unsigned* free_n;
     unsigned free_cap;
 };
@@ -334,17 +337,12 @@ __global__ void __launch_bounds__(256) gmm_sample_kernel(const GmmLaunch a_in) {
             }
             if (valid) my_tests += tested;
         }
-        if (a.free_out) {   // warp-aggregated append of the free samples
-            const unsigned keep = __ballot_sync(0xffffffffu, valid && !hit);
-            if (keep) {
-                unsigned at = 0;
-                if ((threadIdx.x & 31) == 0) at = atomicAdd(a.free_n, unsigned(__popc(keep)));
-                at = __shfl_sync(0xffffffffu, at, 0) + __popc(keep & ((1u << (threadIdx.x & 31)) - 1u));
-                if (valid && !hit && at < a.free_cap) {
-                    a.free_out[at] = px;
-                    a.free_out[size_t(a.free_cap) + at] = py;
-                    a.free_out[2 * size_t(a.free_cap) + at] = pth;
-                }
+        if (a.free_out && valid) {   // kept at the sample's own index; packed in sample order by gmm_compact_free_kernel
+            a.free_flag[i] = hit ? 0 : 1;
+            if (!hit) {
+                a.free_out[i] = px;
+                a.free_out[size_t(a.free_cap) + i] = py;
+                a.free_out[2 * size_t(a.free_cap) + i] = pth;
             }
         }
         if (__any_sync(0xffffffffu, valid && g_acc >= 0 && g != g_acc)) flush();
@@ -1202,6 +1200,47 @@ __global__ void __launch_bounds__(GMM_CLUSTER_THREADS, 1) gmm_cluster_run_kernel
         if ((threadIdx.x & 31) == 0 && t64) atomicAdd(a.tests, t64);
     }
     cl.sync();   // no CTA leaves while a peer may still store into its shared memory
+}
+
+// ---- EM-refit variant: the free samples of a waypoint, packed in sample order -------------------------------------------
+// One CTA walks the n flags in chunks of its size (ballot + popc within a warp, a scan of the warp totals, a running
+// offset): out rows x | y | theta at stride cap hold the flagged samples in increasing sample index, *n_out their number.
+// n = 10^4 is ten chunks (3 us); 10^6 is ~0.5 ms -- next to the host round trip per waypoint this variant already makes.
+__global__ void __launch_bounds__(1024) gmm_compact_free_kernel(const float* __restrict__ in, const unsigned char* __restrict__ flag, unsigned n, unsigned cap,
+                                                                float* __restrict__ out, unsigned* __restrict__ n_out) {
+    __shared__ unsigned s_warp[32];
+    __shared__ unsigned s_base, s_total;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    if (threadIdx.x == 0) s_base = 0;
+    for (unsigned base = 0; base < n; base += blockDim.x) {
+        const unsigned i = base + threadIdx.x;
+        const bool keep = i < n && flag[i] != 0;
+        const unsigned bal = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) s_warp[warp] = __popc(bal);
+        __syncthreads();
+        if (warp == 0) {
+            const unsigned v = lane < nw ? s_warp[lane] : 0u;
+            unsigned incl = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned u = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= unsigned(o)) incl += u;
+            }
+            s_warp[lane] = incl - v;       // exclusive prefix of the warp totals
+            if (lane == 31) s_total = incl;
+        }
+        __syncthreads();
+        const unsigned at = s_base + s_warp[warp] + __popc(bal & ((1u << lane) - 1u));
+        if (keep) {
+            out[at] = in[i];
+            out[size_t(cap) + at] = in[size_t(cap) + i];
+            out[2 * size_t(cap) + at] = in[2 * size_t(cap) + i];
+        }
+        __syncthreads();                   // everyone has read s_base and s_warp of this chunk
+        if (threadIdx.x == 0) s_base += s_total;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) *n_out = s_base;
 }
 
 // ---- batch: the members' shared real-robot threads on the device -------------------------------------------------------

@@ -123,7 +123,7 @@ struct mcsim_cuda_ctx {
     int mc_cull_words = 0;           // 0: no lists for the prepared plan (every live pair is tested)
     // GMM state
     DevBuf gmm_comps, gmm_stats, gmm_hist, gmm_counts, gmm_normals, gmm_steps, gmm_prob, gmm_pre, gmm_post, gmm_trunc, gmm_nout, gmm_deg;
-    DevBuf gmm_free, gmm_free_n, lin_A, lin_b;   // EM-refit variant: free samples of a waypoint; linear variant: half-planes
+    DevBuf gmm_free, gmm_free_u, gmm_free_flag, gmm_free_n, lin_A, lin_b;   // EM-refit variant: free samples of a waypoint; linear variant: half-planes
     double* h_gmm = nullptr;  // pinned staging
     char* h_stage = nullptr;  // pinned staging of the per-run plan upload (MCSIM_STAGE_BYTES)
     // scoring state
@@ -221,7 +221,7 @@ extern "C" void mcsim_cuda_destroy(mcsim_cuda_ctx* c) {
     c->gmm_comps.release(); c->gmm_stats.release(); c->gmm_hist.release(); c->gmm_counts.release();
     c->gmm_normals.release(); c->gmm_steps.release(); c->gmm_prob.release(); c->gmm_pre.release();
     c->gmm_post.release(); c->gmm_trunc.release(); c->gmm_nout.release(); c->gmm_deg.release();
-    c->gmm_free.release(); c->gmm_free_n.release(); c->lin_A.release(); c->lin_b.release();
+    c->gmm_free.release(); c->gmm_free_u.release(); c->gmm_free_flag.release(); c->gmm_free_n.release(); c->lin_A.release(); c->lin_b.release();
     if (c->h_counters) cudaFreeHost(c->h_counters);
     if (c->h_gmm) cudaFreeHost(c->h_gmm);
     if (c->h_stage) cudaFreeHost(c->h_stage);
@@ -1055,10 +1055,14 @@ static int gmm_launch_cluster(mcsim_cuda_ctx* c, const GmmLaunch& a, int n_runs)
 // After the moment refit of truncateGMM (:592-629) the K-component mixture is refitted to ALL collision-free samples of
 // the waypoint by `iters` EM iterations started from the moment-matched mixture (arma::gmm_full::learn with
 // keep_existing: the EM operator of this library, em_sm100.cuh).  The free samples were kept by gmm_sample_kernel
-// (a.free_out, rows at stride N); they are packed into the EM sample buffer, the mixture makes one host round trip.
+// (a.free_out / a.free_flag, at their own index) and are packed here in sample order; the mixture makes one host round trip.
 // `mix` in / out: K x GMM_REC (w, mu[3], cov[9]).  Returns the number of free samples through n_free_out.
 static int gmm_em_refit(mcsim_cuda_ctx* c, int K, uint64_t N, int iters, double var_floor, double* mix, unsigned* n_free_out) {
     unsigned n_free = 0;
+    gmm_compact_free_kernel<<<1, 1024, 0, c->stream>>>((const float*)c->gmm_free_u.p, (const unsigned char*)c->gmm_free_flag.p, unsigned(N), unsigned(N),
+                                                       (float*)c->gmm_free.p, (unsigned*)c->gmm_free_n.p);
+    ++c->launches;
+    CK(cudaGetLastError());
     CK(cudaMemcpyAsync(&n_free, c->gmm_free_n.p, sizeof(unsigned), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     if (n_free > N) n_free = unsigned(N);
@@ -1101,9 +1105,12 @@ static int gmm_filter_code(const mcsim_mc_params* mc, int* code) {
 }
 static int gmm_keep_free_samples(mcsim_cuda_ctx* c, GmmLaunch& a, uint64_t N) {
     if (N >= (1ull << 31)) return fail(MCSIM_ERR_ARG, "gmm: the EM-refit variant takes fewer than 2^31 samples per waypoint");
-    CK(c->gmm_free.reserve(sizeof(float) * 3 * size_t(N)));
+    CK(c->gmm_free.reserve(sizeof(float) * 3 * size_t(N)));       // packed in sample order (gmm_compact_free_kernel)
+    CK(c->gmm_free_u.reserve(sizeof(float) * 3 * size_t(N)));     // as the sample kernel leaves them: at the sample's own index
+    CK(c->gmm_free_flag.reserve(size_t(N)));
     CK(c->gmm_free_n.reserve(sizeof(unsigned)));
-    a.free_out = (float*)c->gmm_free.p;
+    a.free_out = (float*)c->gmm_free_u.p;
+    a.free_flag = (unsigned char*)c->gmm_free_flag.p;
     a.free_n = (unsigned*)c->gmm_free_n.p;
     a.free_cap = unsigned(N);
     return MCSIM_OK;
