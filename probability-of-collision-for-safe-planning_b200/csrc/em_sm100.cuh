@@ -664,6 +664,9 @@ __global__ void __launch_bounds__(256, (VEC && K == 1) ? 3 : ((VEC && K == 2) ? 
 // hand the stage back with one __syncthreads.  Nothing of the stream sits in registers, so three CTAs per SM keep
 // up to 216 KB of loads in flight per SM (the register-prefetch kernel above: 74 KB).  Needs n % 4 == 0 (16-byte
 // aligned rows and tile sizes).
+#ifndef EM_TMA_TWO_CTAS_K
+#define EM_TMA_TWO_CTAS_K 3   // the bulk-copy kernel is held to 128 registers (two CTAs per SM) up to this many components
+#endif
 #define EM_TMA_TILE 2048
 #define EM_TMA_STAGES 3
 
@@ -691,7 +694,7 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
 }
 
 template <int K>
-__global__ void __launch_bounds__(256, K == 1 ? 3 : (K <= 3 ? 2 : 1)) em_estep_tma_kernel(const EmLaunch a) {
+__global__ void __launch_bounds__(256, K == 1 ? 3 : (K <= EM_TMA_TWO_CTAS_K ? 2 : 1)) em_estep_tma_kernel(const EmLaunch a) {
     constexpr int NACC = K * EM_NSTAT + 1;
     extern __shared__ __align__(128) float s_tile[];   // [EM_TMA_STAGES][3][EM_TMA_TILE]
     __shared__ __align__(8) unsigned long long s_bar[EM_TMA_STAGES];
