@@ -433,7 +433,7 @@ struct GmmDraw2 {
     f2 d0, d1, d2;   // L z of both samples (the moment sums are taken about the component mean)
     bool hit0, hit1;
 };
-template <class V>   // V = f2: per-lane components; V = float: one component for both lanes (broadcast at use)
+template <class V, bool AX = false>   // V = f2: per-lane components; V = float: one component for both lanes (broadcast at use); AX: axis-aligned scene
 __device__ __forceinline__ GmmDraw2 gmm_draw_test2(unsigned stream_id, unsigned ctr2, unsigned k0, unsigned k1, unsigned i0, unsigned i1, bool valid0, bool valid1,
                                                    const V (&L)[6], const V (&mu)[3], const float4* tab, const unsigned char* ccnt, const ushort2* cidx,
                                                    bool cull, float2 nom, unsigned& my_tests) {
@@ -471,21 +471,21 @@ __device__ __forceinline__ GmmDraw2 gmm_draw_test2(unsigned stream_id, unsigned 
         for (int hI = 0; hI < c_scene.n_hulls; ++hI) {
             const int nc = ccnt[hI * MC_CULL_LEVELS + lev];
             if (nc == 0) continue;
-            const HullFrame2 h = hull_frame2(c_scene.hulls[hI], x, y, cs, sn);
+            const HullFrame2 h = hull_frame2<AX>(c_scene.hulls[hI], x, y, cs, sn);
             ClassFrame2 cf;
             unsigned cls = 0xffffffffu;
             for (int k = 0; k < nc; ++k) {
                 const ushort2 oo = cidx[hI * MC_CULL_CAP + k];  // x: pair record, y: class header
                 if (oo.y != cls) {
                     cls = oo.y;
-                    cf = class_frame2(tab[oo.y], h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
+                    cf = class_frame2<AX>(tab[oo.y], h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
                 }
                 class_pair_test2(cf, h.ch, h.sh, h.nph, h.nqh, h.hhx, h.hhy, tab[oo.x], *reinterpret_cast<const float2*>(tab + oo.x + 1), o.hit0, o.hit1);
             }
             tested += nc;
         }
     } else {
-        robot_hits2(tab, x, y, cs, sn, o.hit0, o.hit1);
+        robot_hits2<AX>(tab, x, y, cs, sn, o.hit0, o.hit1);
         tested = c_scene.n_pairs;
     }
     my_tests += tested * (unsigned(valid0) + unsigned(valid1));
@@ -569,6 +569,7 @@ __device__ __forceinline__ void gmm_acc_add(bool valid, bool hit, float d0, floa
 }
 // all samples of a waypoint that fall to one warp: its 64-sample windows start at wbase, wbase + stride, ... (one CTA per
 // run: wbase = 64 warp, stride = 2 blockDim; a cluster per run: the CTAs' passes interleave, gmm_cluster_run_kernel)
+template <bool AX = false>
 __device__ __forceinline__ void gmm_member_samples(unsigned stream_id, unsigned ctr2, unsigned k0, unsigned k1, unsigned n, int K,
                                                    const unsigned* s_prefix, const float (*s_mu)[3], const float (*s_L)[6], double (*s_stat)[GMM_STAT],
                                                    const float4* tab, const unsigned char* ccnt, const ushort2* cidx, bool cull, float2 nom, unsigned& my_tests,
@@ -592,7 +593,7 @@ __device__ __forceinline__ void gmm_member_samples(unsigned stream_id, unsigned 
             for (unsigned q = 0; q < q_n; ++q, w0 += stride) {
                 const unsigned i0 = w0 + lane2, i1 = i0 + 1u;
                 const bool valid0 = i0 < n, valid1 = i1 < n;
-                const GmmDraw2 o = gmm_draw_test2(stream_id, ctr2, k0, k1, i0, i1, valid0, valid1, L, mu, tab, ccnt, cidx, cull, nom, my_tests);
+                const GmmDraw2 o = gmm_draw_test2<float, AX>(stream_id, ctr2, k0, k1, i0, i1, valid0, valid1, L, mu, tab, ccnt, cidx, cull, nom, my_tests);
                 gmm_acc_add(valid0, o.hit0, lo(o.d0), lo(o.d1), lo(o.d2), nf, nc, acc);
                 gmm_acc_add(valid1, o.hit1, hi(o.d0), hi(o.d1), hi(o.d2), nf, nc, acc);
             }
@@ -610,7 +611,7 @@ __device__ __forceinline__ void gmm_member_samples(unsigned stream_id, unsigned 
             for (int k = 0; k < 6; ++k) L[k] = mk2(s_L[g0][k], s_L[g1][k]);
 #pragma unroll
             for (int k = 0; k < 3; ++k) mu[k] = mk2(s_mu[g0][k], s_mu[g1][k]);
-            const GmmDraw2 o = gmm_draw_test2(stream_id, ctr2, k0, k1, i0, i1, valid0, valid1, L, mu, tab, ccnt, cidx, cull, nom, my_tests);
+            const GmmDraw2 o = gmm_draw_test2<f2, AX>(stream_id, ctr2, k0, k1, i0, i1, valid0, valid1, L, mu, tab, ccnt, cidx, cull, nom, my_tests);
             const int g_last = __reduce_max_sync(0xffffffffu, valid1 ? g1 : (valid0 ? g0 : gw));
             for (int gg = gw; gg <= g_last; ++gg) {   // warp-uniform
                 unsigned nf = 0, nc = 0;
@@ -940,6 +941,7 @@ __device__ __forceinline__ void gmm_member_count(int t, unsigned idx, unsigned n
 // How they are cut into CTAs (= runs in flight per SM) is the launcher's choice -- 128, 256 or 512 threads per run
 // (gmm_member_threads in mcsim_cuda.cu): the kernel only assumes whole warps and at least two of them.
 #define GMM_MEMBER_MAX_THREADS 512
+template <bool AX>   // AX: axis-aligned scene (mc_philox2_sm100.cuh, class_frame2<AX>)
 __global__ void __launch_bounds__(GMM_MEMBER_MAX_THREADS, 1) gmm_member_run_kernel(const GmmLaunch a_in, int sat2_n, int cull_words) {
     extern __shared__ __align__(16) float4 s_tab[];
     __shared__ double s_comp[MCSIM_MAX_GAUSSIANS][GMM_COMP];
@@ -994,7 +996,7 @@ __global__ void __launch_bounds__(GMM_MEMBER_MAX_THREADS, 1) gmm_member_run_kern
             const float2 nom = cull ? __ldg(m.nominal + t) : make_float2(0.f, 0.f);
             const unsigned char* cc = s_ccnt + t * nh * MC_CULL_LEVELS;
             const ushort2* ci = s_cidx + t * nh * MC_CULL_CAP;
-            gmm_member_samples(stream_id, unsigned(2 * t), k0, k1, n, K, s_prefix, s_mu, s_L, s_stat, s_tab, cc, ci, cull, nom, my_tests,
+            gmm_member_samples<AX>(stream_id, unsigned(2 * t), k0, k1, n, K, s_prefix, s_mu, s_L, s_stat, s_tab, cc, ci, cull, nom, my_tests,
                                64u * (threadIdx.x >> 5), 2u * blockDim.x);
         }
         __syncthreads();

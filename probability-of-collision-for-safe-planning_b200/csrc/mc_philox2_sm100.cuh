@@ -114,8 +114,17 @@ struct ClassFrame2 {
     f2 c, s, gx, gy, rbx, rby;
 };
 // per orientation class: |relative rotation|, hull centre in the class frame, hull radii on the class axes
+// AX: every class axis of the scene is (1, 0) and every hull's yaw is 0 (an axis-aligned scene, the usual OpenRAVE env):
+// the rotations into the class and hull frames multiply by 1 and add 0 -- dropped at compile time, same bits.
+template <bool AX = false>
 __device__ __forceinline__ ClassFrame2 class_frame2(const float4 head, f2 ch, f2 sh, f2 hcx, f2 hcy, f2 hhx, f2 hhy) {  // @phase sat_frames
     ClassFrame2 k;
+    if (AX) {
+        k.c = abs2(ch); k.s = abs2(sh); k.gx = hcx; k.gy = hcy;
+        k.rbx = fma2(k.c, hhx, mul2(k.s, hhy));
+        k.rby = fma2(k.s, hhx, mul2(k.c, hhy));
+        return k;
+    }
     k.c = abs2(fma2(ch, head.x, mul2(sh, head.y)));
     k.s = abs2(fma2(sh, head.x, mul2(neg2(ch), head.y)));
     k.gx = fma2(hcx, head.x, mul2(hcy, head.y));
@@ -141,12 +150,13 @@ __device__ __forceinline__ void class_pair_test2(const ClassFrame2& k, f2 ch, f2
 struct HullFrame2 {
     f2 hcx, hcy, ch, sh, nph, nqh, hhx, hhy;
 };
+template <bool AX = false>
 __device__ __forceinline__ HullFrame2 hull_frame2(const HullRec& hr, f2 x, f2 y, f2 ct, f2 st) {  // @phase sat_frames
     HullFrame2 h;
     h.hcx = fma2(ct, hr.ox, fma2(neg2(st), hr.oy, x));
     h.hcy = fma2(st, hr.ox, fma2(ct, hr.oy, y));
-    h.ch = fma2(ct, hr.cp, mul2(neg2(st), hr.sp));
-    h.sh = fma2(st, hr.cp, mul2(ct, hr.sp));
+    h.ch = AX ? ct : fma2(ct, hr.cp, mul2(neg2(st), hr.sp));
+    h.sh = AX ? st : fma2(st, hr.cp, mul2(ct, hr.sp));
     h.nph = neg2(fma2(h.ch, h.hcx, mul2(h.sh, h.hcy)));
     h.nqh = neg2(fma2(h.ch, h.hcy, mul2(neg2(h.sh), h.hcx)));
     h.hhx = bc(hr.hx);
@@ -154,16 +164,17 @@ __device__ __forceinline__ HullFrame2 hull_frame2(const HullRec& hr, f2 x, f2 y,
     return h;
 }
 
+template <bool AX = false>
 __device__ __forceinline__ void robot_hits2(const float4* __restrict__ tab, f2 x, f2 y, f2 ct, f2 st, bool& hit0, bool& hit1) {  // @phase sat_exhaustive
     const int nh = c_scene.n_hulls;
     for (int hI = 0; hI < nh; ++hI) {
         const HullRec& hr = c_scene.hulls[hI];
-        const HullFrame2 h = hull_frame2(hr, x, y, ct, st);
+        const HullFrame2 h = hull_frame2<AX>(hr, x, y, ct, st);
         const float4* g = tab + hr.g_first;
         for (int gi = 0; gi < hr.n_groups; ++gi) {
             const float4 head = g[0];
             const int cnt = __float_as_int(head.z);
-            const ClassFrame2 k = class_frame2(head, h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
+            const ClassFrame2 k = class_frame2<AX>(head, h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
             ++g;
 #pragma unroll 4
             for (int b = 0; b < cnt; ++b)
@@ -372,6 +383,7 @@ __device__ __forceinline__ SatTables stage_tables(float4* s_tab, const McLaunch&
 
 // collision test of both lanes at waypoint t (q = the tested pose).  in0 / in1: lanes whose result matters (they set
 // the warp's list level); returns the pair tests executed per such lane.
+template <bool AX = false>
 __device__ __forceinline__ unsigned collide2(const SatTables& tb, const f2* q, int t, bool in0, bool in1, bool& h0, bool& h1) {  // @phase sat_select
     f2 sn, cs;
     sincos2(q[2], sn, cs);
@@ -392,7 +404,7 @@ __device__ __forceinline__ unsigned collide2(const SatTables& tb, const f2* q, i
         for (int hI = 0; hI < nh; ++hI) {
             const int n = tb.ccnt[(t * nh + hI) * MC_CULL_LEVELS + lev];
             if (n == 0) continue;
-            const HullFrame2 h = hull_frame2(c_scene.hulls[hI], q[0], q[1], cs, sn);
+            const HullFrame2 h = hull_frame2<AX>(c_scene.hulls[hI], q[0], q[1], cs, sn);
             const ushort2* ci = reinterpret_cast<const ushort2*>(tb.cidx) + (t * nh + hI) * MC_CULL_CAP;
             ClassFrame2 cf;
             unsigned cls = 0xffffffffu;
@@ -400,7 +412,7 @@ __device__ __forceinline__ unsigned collide2(const SatTables& tb, const f2* q, i
                 const ushort2 o = ci[k];  // x: pair record, y: class header
                 if (o.y != cls) {         // consecutive candidates mostly share their class (axis-aligned scenes)
                     cls = o.y;
-                    cf = class_frame2(tb.tab[o.y], h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
+                    cf = class_frame2<AX>(tb.tab[o.y], h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
                 }
                 class_pair_test2(cf, h.ch, h.sh, h.nph, h.nqh, h.hhx, h.hhy, tb.tab[o.x], *reinterpret_cast<const float2*>(tb.tab + o.x + 1), h0, h1);
             }
@@ -408,7 +420,7 @@ __device__ __forceinline__ unsigned collide2(const SatTables& tb, const f2* q, i
         }
         return tested;
     }
-    robot_hits2(tb.tab, q[0], q[1], cs, sn, h0, h1);
+    robot_hits2<AX>(tb.tab, q[0], q[1], cs, sn, h0, h1);
     return tb.n_pairs;
 }
 
@@ -432,7 +444,7 @@ __device__ __forceinline__ void flush_counters(const McLaunch& a, int T, unsigne
         if (s_hist[t]) atomicAdd(&a.counters[CNT_HIST + t], (unsigned long long)s_hist[t]);
 }
 
-template <bool EARLY_EXIT, int EST, int NL>
+template <bool EARLY_EXIT, int EST, int NL, bool AX = false>
 __global__ void __launch_bounds__(128, MC_P2_CTAS_PER_SM) mc_philox2_kernel(const McLaunch a) {
     extern __shared__ __align__(16) float4 s_tab[];  // @phase prologue
     __shared__ unsigned s_cnt[2];
@@ -466,7 +478,7 @@ __global__ void __launch_bounds__(128, MC_P2_CTAS_PER_SM) mc_philox2_kernel(cons
             const bool in0 = EARLY_EXIT ? (valid0 && cnt0 == 0) : valid0, in1 = EARLY_EXIT ? (valid1 && cnt1 == 0) : valid1;
             const unsigned live = unsigned(in0) + unsigned(in1);
             bool h0 = false, h1 = false;
-            const unsigned tested = collide2(tb, (EST == MCSIM_EST_CLOSEDLOOP) ? st.real : st.p, t, in0, in1, h0, h1);
+            const unsigned tested = collide2<AX>(tb, (EST == MCSIM_EST_CLOSEDLOOP) ? st.real : st.p, t, in0, in1, h0, h1);
             pass_tests += live * tested;
             pass_steps += live;  // @phase bookkeeping
             if (h0) { if (first0 < 0) first0 = t; ++cnt0; }
@@ -511,7 +523,7 @@ struct McSegLaunch {
     unsigned cap;
 };
 
-template <int EST, int NL>
+template <int EST, int NL, bool AX = false>
 __global__ void __launch_bounds__(128, MC_P2_CTAS_PER_SM) mc_philox2_segment_kernel(const McSegLaunch g) {
     extern __shared__ __align__(16) float4 s_tab[];  // @phase prologue
     __shared__ unsigned s_cnt[2];
@@ -557,7 +569,7 @@ __global__ void __launch_bounds__(128, MC_P2_CTAS_PER_SM) mc_philox2_segment_ker
         for (int t = g.t0; t < g.t1; ++t) {
             const unsigned live = unsigned(free0) + unsigned(free1);
             bool h0 = false, h1 = false;
-            const unsigned tested = collide2(tb, (EST == MCSIM_EST_CLOSEDLOOP) ? st.real : st.p, t, free0, free1, h0, h1);
+            const unsigned tested = collide2<AX>(tb, (EST == MCSIM_EST_CLOSEDLOOP) ? st.real : st.p, t, free0, free1, h0, h1);
             pass_tests += live * tested;
             pass_steps += live;  // @phase bookkeeping
             if (h0 && free0) { free0 = false; ++my_hits; atomicAdd(&s_hist[t], 1u); if (a.counts) a.counts[id0 - a.offset] = 1u; }

@@ -366,3 +366,32 @@ def test_philox_edge_cases_empty_scene_single_waypoint_other_landmark_counts(ctx
     assert out["executed_steps"] == 20000 * T
     sc = ctx.score_plans(long_plan, tr[None], od[None], 20000, margin=-1.0)   # packed law, plan table in shared memory
     assert abs(sc["P"][0] - out["P"]) < 0.02, (sc["P"][0], out["P"])
+
+
+@pytest.mark.parametrize("est", ["reference", "closedloop"])
+@pytest.mark.parametrize("name", ["pr2test2", "pr2custom"])
+def test_axis_aligned_instantiations_equal_the_generic_kernel(ctx, plan, scenes, name, est):
+    """On an axis-aligned scene (every box class axis (1, 0), every hull's yaw 0 -- both committed scenes) the packed
+    kernels run instantiations that drop the rotations into the class and hull frames (multiplications by 1, additions
+    of 0: the same bits).  One more box, rotated by 30 degrees and 100 m away, makes the scene generic without touching a
+    single collision: per-rollout counts, first-hit histogram and executed steps must be identical -- plain launch,
+    one-launch early exit and the survivor-compaction path (N >= 2^18)."""
+    import pcoll_b200
+    abi = pcoll_b200.cuda_abi
+    e = abi.EST_REFERENCE if est == "reference" else abi.EST_CLOSEDLOOP
+    boxes = np.asarray(scenes[name]["boxes"], dtype=np.float64)
+    far = np.array([[100.0, 100.0, np.cos(np.pi / 6), np.sin(np.pi / 6), 0.3, 0.2, boxes[:, 6].min(), boxes[:, 7].max()]])
+    outs = {}
+    for label, bx in (("axis-aligned", boxes), ("generic", np.vstack([boxes, far]))):
+        ctx.set_scene(bx, scenes[name]["hulls"])
+        for ee, N in ((False, 150001), (True, 150001), (True, (1 << 18) + 77)):
+            p, keep = abi.make_mc_params(plan, n_rollouts=N, mode=abi.MODE_PHILOX, estimator=e, early_exit=ee, rollout_offset=4242)
+            outs[(label, ee, N)] = ctx.mc_run(p, want_counts=True, want_hist=True)
+    for (label, ee, N), a in outs.items():
+        if label != "axis-aligned":
+            continue
+        b = outs[("generic", ee, N)]
+        np.testing.assert_array_equal(a["counts"], b["counts"])
+        np.testing.assert_array_equal(a["first_hit_hist"], b["first_hit_hist"])
+        assert a["hits"] == b["hits"] and a["executed_steps"] == b["executed_steps"]
+    ctx.set_scene(scenes[name]["boxes"], scenes[name]["hulls"])
