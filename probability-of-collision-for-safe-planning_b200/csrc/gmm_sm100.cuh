@@ -472,15 +472,23 @@ __device__ __forceinline__ GmmDraw2 gmm_draw_test2(unsigned stream_id, unsigned 
             const int nc = ccnt[hI * MC_CULL_LEVELS + lev];
             if (nc == 0) continue;
             const HullFrame2 h = hull_frame2<AX>(c_scene.hulls[hI], x, y, cs, sn);
-            ClassFrame2 cf;
-            unsigned cls = 0xffffffffu;
-            for (int k = 0; k < nc; ++k) {
-                const ushort2 oo = cidx[hI * MC_CULL_CAP + k];  // x: pair record, y: class header
-                if (oo.y != cls) {
-                    cls = oo.y;
-                    cf = class_frame2<AX>(tab[oo.y], h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
+            if (AX) {   // one class, and its frame is the hull's (mc_philox2_sm100.cuh, collide2)
+                const ClassFrame2 cf = class_frame2<true>(make_float4(1.f, 0.f, 0.f, 0.f), h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
+                for (int k = 0; k < nc; ++k) {
+                    const unsigned ox = cidx[hI * MC_CULL_CAP + k].x;
+                    class_pair_test2(cf, h.ch, h.sh, h.nph, h.nqh, h.hhx, h.hhy, tab[ox], *reinterpret_cast<const float2*>(tab + ox + 1), o.hit0, o.hit1);
                 }
-                class_pair_test2(cf, h.ch, h.sh, h.nph, h.nqh, h.hhx, h.hhy, tab[oo.x], *reinterpret_cast<const float2*>(tab + oo.x + 1), o.hit0, o.hit1);
+            } else {
+                ClassFrame2 cf;
+                unsigned cls = 0xffffffffu;
+                for (int k = 0; k < nc; ++k) {
+                    const ushort2 oo = cidx[hI * MC_CULL_CAP + k];  // x: pair record, y: class header
+                    if (oo.y != cls) {
+                        cls = oo.y;
+                        cf = class_frame2<false>(tab[oo.y], h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
+                    }
+                    class_pair_test2(cf, h.ch, h.sh, h.nph, h.nqh, h.hhx, h.hhy, tab[oo.x], *reinterpret_cast<const float2*>(tab + oo.x + 1), o.hit0, o.hit1);
+                }
             }
             tested += nc;
         }

@@ -406,15 +406,23 @@ __device__ __forceinline__ unsigned collide2(const SatTables& tb, const f2* q, i
             if (n == 0) continue;
             const HullFrame2 h = hull_frame2<AX>(c_scene.hulls[hI], q[0], q[1], cs, sn);
             const ushort2* ci = reinterpret_cast<const ushort2*>(tb.cidx) + (t * nh + hI) * MC_CULL_CAP;
-            ClassFrame2 cf;
-            unsigned cls = 0xffffffffu;
-            for (int k = 0; k < n; ++k) {
-                const ushort2 o = ci[k];  // x: pair record, y: class header
-                if (o.y != cls) {         // consecutive candidates mostly share their class (axis-aligned scenes)
-                    cls = o.y;
-                    cf = class_frame2<AX>(tb.tab[o.y], h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
+            if (AX) {   // one class, and its frame is the hull's: nothing depends on the class header
+                const ClassFrame2 cf = class_frame2<true>(make_float4(1.f, 0.f, 0.f, 0.f), h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
+                for (int k = 0; k < n; ++k) {
+                    const unsigned ox = ci[k].x;
+                    class_pair_test2(cf, h.ch, h.sh, h.nph, h.nqh, h.hhx, h.hhy, tb.tab[ox], *reinterpret_cast<const float2*>(tb.tab + ox + 1), h0, h1);
                 }
-                class_pair_test2(cf, h.ch, h.sh, h.nph, h.nqh, h.hhx, h.hhy, tb.tab[o.x], *reinterpret_cast<const float2*>(tb.tab + o.x + 1), h0, h1);
+            } else {
+                ClassFrame2 cf;
+                unsigned cls = 0xffffffffu;
+                for (int k = 0; k < n; ++k) {
+                    const ushort2 o = ci[k];  // x: pair record, y: class header
+                    if (o.y != cls) {         // consecutive candidates mostly share their class
+                        cls = o.y;
+                        cf = class_frame2<false>(tb.tab[o.y], h.ch, h.sh, h.hcx, h.hcy, h.hhx, h.hhy);
+                    }
+                    class_pair_test2(cf, h.ch, h.sh, h.nph, h.nqh, h.hhx, h.hhy, tb.tab[o.x], *reinterpret_cast<const float2*>(tb.tab + o.x + 1), h0, h1);
+                }
             }
             tested += n;
         }
