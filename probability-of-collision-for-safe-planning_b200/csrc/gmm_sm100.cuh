@@ -502,6 +502,7 @@ __device__ __forceinline__ GmmDraw2 gmm_draw_test2(unsigned stream_id, unsigned 
 
 // one pass of the generic sample loop (per-waypoint and cluster kernels): the thread's two samples may belong to any
 // component (per-thread monotone search in the prefix sums); per-thread sums are flushed when the component changes
+template <bool AX = false>
 __device__ __forceinline__ void gmm_philox_pass2(unsigned stream_id, unsigned ctr2, unsigned k0, unsigned k1, unsigned i0, unsigned i1, unsigned n, int K, int& g,
                                                  const unsigned* s_prefix, const float (*s_mu)[3], const float (*s_L)[6], double (*s_stat)[GMM_STAT],
                                                  const float4* tab, const unsigned char* ccnt, const ushort2* cidx, bool cull, float2 nom,
@@ -527,7 +528,7 @@ __device__ __forceinline__ void gmm_philox_pass2(unsigned stream_id, unsigned ct
     for (int k = 0; k < 6; ++k) L[k] = mk2(La[k], Lb[k]);
 #pragma unroll
     for (int k = 0; k < 3; ++k) mu[k] = mk2(ma[k], mb[k]);
-    const GmmDraw2 o = gmm_draw_test2(stream_id, ctr2, k0, k1, i0, i1, valid0, valid1, L, mu, tab, ccnt, cidx, cull, nom, my_tests);
+    const GmmDraw2 o = gmm_draw_test2<f2, AX>(stream_id, ctr2, k0, k1, i0, i1, valid0, valid1, L, mu, tab, ccnt, cidx, cull, nom, my_tests);
     if (__any_sync(0xffffffffu, valid0 && acc.g_acc >= 0 && g != acc.g_acc)) acc.flush(s_stat);
     if (valid0) acc.add(g, o.hit0, lo(o.d0), lo(o.d1), lo(o.d2));
     if (__any_sync(0xffffffffu, valid1 && acc.g_acc >= 0 && g1 != acc.g_acc)) acc.flush(s_stat);
@@ -633,6 +634,7 @@ __device__ __forceinline__ void gmm_member_samples(unsigned stream_id, unsigned 
     }
 }
 
+template <bool AX>
 __global__ void __launch_bounds__(256) gmm_sample_philox_kernel(const GmmLaunch a_in) {
     const GmmLaunch& a = a_in;
     const GmmMember m = gmm_member(a_in, blockIdx.y);
@@ -670,7 +672,7 @@ __global__ void __launch_bounds__(256) gmm_sample_philox_kernel(const GmmLaunch 
     // so that twice as many warps share the waypoint's latency
     const unsigned per = a.spread ? 1u : 2u;
     for (unsigned base = per * blockIdx.x * blockDim.x; base < n; base += per * stride)
-        gmm_philox_pass2(m.stream_id, unsigned(2 * a.t), a.k0, a.k1, base + per * threadIdx.x, a.spread ? 0xffffffffu : base + per * threadIdx.x + 1, n, K, g, s_prefix, s_mu, s_L, s_stat, a.sat2, s_ccnt, s_cidx, m.cull != nullptr, nom, acc, my_tests);
+        gmm_philox_pass2<AX>(m.stream_id, unsigned(2 * a.t), a.k0, a.k1, base + per * threadIdx.x, a.spread ? 0xffffffffu : base + per * threadIdx.x + 1, n, K, g, s_prefix, s_mu, s_L, s_stat, a.sat2, s_ccnt, s_cidx, m.cull != nullptr, nom, acc, my_tests);
     acc.flush(s_stat);
     __syncthreads();
     for (int i = threadIdx.x; i < K * GMM_STAT; i += blockDim.x) {
@@ -1054,6 +1056,7 @@ __global__ void __launch_bounds__(GMM_MEMBER_MAX_THREADS, 1) gmm_member_run_kern
 #define GMM_CLUSTER 8          // CTAs per cluster for small batches; single runs take 16 (non-portable size)
 #define GMM_CLUSTER_MAX 16
 #define GMM_CLUSTER_THREADS 512
+template <bool AX>   // AX: axis-aligned scene (mc_philox2_sm100.cuh, class_frame2<AX>)
 __global__ void __launch_bounds__(GMM_CLUSTER_THREADS, 1) gmm_cluster_run_kernel(const GmmLaunch a_in, int sat2_n, int cull_words) {
     namespace cg = cooperative_groups;
     cg::cluster_group cl = cg::this_cluster();
@@ -1175,7 +1178,7 @@ __global__ void __launch_bounds__(GMM_CLUSTER_THREADS, 1) gmm_cluster_run_kernel
             const ushort2* ci = s_cidx + t * nh * MC_CULL_CAP;
             // the same sample -> thread mapping as before (pass p of CTA `rank` covers 2 blockDim samples from
             // 2 blockDim (rank + p CL)), walked as per-warp windows: component in registers, one reduction per component
-            gmm_member_samples(stream_id, unsigned(2 * t), k0, k1, n, K, s_prefix, s_mu, s_L, s_stat, s_tab, cc, ci, cull, nom, my_tests,
+            gmm_member_samples<AX>(stream_id, unsigned(2 * t), k0, k1, n, K, s_prefix, s_mu, s_L, s_stat, s_tab, cc, ci, cull, nom, my_tests,
                                2u * blockDim.x * rank + 64u * (threadIdx.x >> 5), 2u * blockDim.x * CL);
         }
         __syncthreads();

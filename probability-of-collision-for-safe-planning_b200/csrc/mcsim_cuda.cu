@@ -1018,7 +1018,8 @@ static int gmm_launch_waypoint(mcsim_cuda_ctx* c, const GmmLaunch& a_in, int mod
         c->launches += 2;
     } else if (mode == MCSIM_MODE_PHILOX) {
         gmm_count_kernel<<<grid, block, 0, c->stream>>>(a);
-        gmm_sample_philox_kernel<<<grid, block, 0, c->stream>>>(a);
+        if (c->scene_axis_aligned) gmm_sample_philox_kernel<true><<<grid, block, 0, c->stream>>>(a);
+        else gmm_sample_philox_kernel<false><<<grid, block, 0, c->stream>>>(a);
         c->launches += 2;
     } else {
         gmm_sample_kernel<MCSIM_MODE_REPLAY><<<grid, block, 0, c->stream>>>(a);
@@ -1043,12 +1044,13 @@ static bool gmm_cluster_fits(const mcsim_cuda_ctx* c, uint64_t n_samples, int n_
 static int gmm_launch_cluster(mcsim_cuda_ctx* c, const GmmLaunch& a, int n_runs) {
     SymbolLock sym;
     { const int rb = bind_symbols(c, nullptr, sym); if (rb) return rb; }
+    void (*ck)(const GmmLaunch, int, int) = c->scene_axis_aligned ? gmm_cluster_run_kernel<true> : gmm_cluster_run_kernel<false>;
     const size_t smem = sizeof(float4) * size_t(c->sat2_n) + sizeof(unsigned) * size_t(c->gmm_cull_words);
     // the kernel holds ~30 KB of static shared memory (the peers' slots): static + dynamic pass 48 KB early
-    if (smem > 12 * 1024) CK(cudaFuncSetAttribute((const void*)gmm_cluster_run_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    if (smem > 12 * 1024) CK(cudaFuncSetAttribute((const void*)ck, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
     // up to 8 runs: 16 CTAs per cluster (one pass over 10^4 samples; a GPC holds one such cluster), else 8
     int cl = n_runs <= 8 ? 16 : GMM_CLUSTER;
-    if (cl > 8) CK(cudaFuncSetAttribute((const void*)gmm_cluster_run_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    if (cl > 8) CK(cudaFuncSetAttribute((const void*)ck, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
     cudaLaunchConfig_t cfg;
     cudaLaunchAttribute attr[1];
     for (;;) {
@@ -1064,13 +1066,13 @@ static int gmm_launch_cluster(mcsim_cuda_ctx* c, const GmmLaunch& a, int n_runs)
         cfg.attrs = attr;
         cfg.numAttrs = 1;
         int fit = 0;
-        const cudaError_t q = cudaOccupancyMaxActiveClusters(&fit, gmm_cluster_run_kernel, &cfg);
+        const cudaError_t q = cudaOccupancyMaxActiveClusters(&fit, ck, &cfg);
         if (q == cudaSuccess && fit >= 1) break;
         (void)cudaGetLastError();
         if (cl == GMM_CLUSTER) return -1;   // no cluster shape fits (e.g. a partitioned device): the caller keeps the per-waypoint kernels
         cl = GMM_CLUSTER;
     }
-    CK(cudaLaunchKernelEx(&cfg, gmm_cluster_run_kernel, a, c->sat2_n, c->gmm_cull_words));
+    CK(cudaLaunchKernelEx(&cfg, ck, a, c->sat2_n, c->gmm_cull_words));
     ++c->launches;
     return MCSIM_OK;
 }
